@@ -1,0 +1,184 @@
+"""ctypes front end of the CPU oracle (oracle/oracle.cpp).
+
+TEST INFRASTRUCTURE ONLY — see the header of oracle.cpp.  Only tests/, __graft_entry__.smoke() and
+bench.py's cpu_baseline / --impl reference legs may import this module; the product package
+(langsplat_b200) never does.
+
+`forward()` / `backward()` mirror CudaRasterizer::Rasterizer::forward/backward
+(RAST/cuda_rasterizer/rasterizer_impl.cu:198-355, 359-463) and return every intermediate the
+reference keeps in its geometry / binning / image buffers so tests can compare stage by stage.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+from typing import Dict, Optional
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "liboracle.so")
+_lib = None
+
+
+def build(force: bool = False) -> str:
+    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < os.path.getmtime(
+            os.path.join(_HERE, "oracle.cpp")):
+        subprocess.check_call(["make", "-C", _HERE, "-s"] + (["-B"] if force else []))
+    return _LIB_PATH
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        _lib = ctypes.CDLL(_LIB_PATH)
+        _lib.orc_preprocess_f32.restype = ctypes.c_int64
+        _lib.orc_preprocess_f64.restype = ctypes.c_int64
+        _lib.orc_higher_msb.restype = ctypes.c_uint32
+        _lib.orc_num_threads.restype = ctypes.c_int
+    return _lib
+
+
+def num_threads() -> int:
+    return int(lib().orc_num_threads())
+
+
+def set_num_threads(n: int) -> None:
+    lib().orc_set_num_threads(ctypes.c_int(n))
+
+
+def higher_msb(n: int) -> int:
+    return int(lib().orc_higher_msb(ctypes.c_uint32(n)))
+
+
+def _np(x, dtype):
+    if x is None:
+        return None
+    if hasattr(x, "detach"):
+        x = x.detach().cpu().numpy()
+    return np.ascontiguousarray(x, dtype=dtype)
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
+
+
+def forward(means3D, opacities, viewmatrix, projmatrix, campos, W, H, tanfovx, tanfovy, bg, shs=None,
+            colors_precomp=None, language_feature=None, scales=None, rotations=None, cov3D_precomp=None,
+            scale_modifier=1.0, sh_degree=3, include_feature=True, dtype=np.float32) -> Dict[str, np.ndarray]:
+    L = lib()
+    suf = "f32" if dtype == np.float32 else "f64"
+    real = ctypes.c_float if dtype == np.float32 else ctypes.c_double
+    means3D = _np(means3D, dtype)
+    P = means3D.shape[0]
+    opacities = _np(opacities, dtype).reshape(-1)
+    shs = _np(shs, dtype)
+    colors_precomp = _np(colors_precomp, dtype)
+    language_feature = _np(language_feature, dtype)
+    scales = _np(scales, dtype)
+    rotations = _np(rotations, dtype)
+    cov3D_precomp = _np(cov3D_precomp, dtype)
+    viewmatrix = _np(viewmatrix, dtype).reshape(-1)
+    projmatrix = _np(projmatrix, dtype).reshape(-1)
+    campos = _np(campos, dtype).reshape(-1)
+    bg = _np(bg, dtype).reshape(-1)
+    M = 0 if shs is None else shs.shape[1]
+    # the C++ signatures narrow tanfov / scale_modifier to f32 (rasterize_points.cu:44,48-49)
+    if dtype == np.float32:
+        tanfovx, tanfovy, scale_modifier = float(np.float32(tanfovx)), float(np.float32(tanfovy)), float(
+            np.float32(scale_modifier))
+    o = dict(P=P, W=W, H=H)
+    o["radii"] = np.zeros(P, np.int32)
+    o["means2D"] = np.zeros((P, 2), dtype)
+    o["depths"] = np.zeros(P, dtype)
+    o["cov3D"] = np.zeros((P, 6), dtype)
+    o["rgb"] = np.zeros((P, 3), dtype)
+    o["conic_opacity"] = np.zeros((P, 4), dtype)
+    o["clamped"] = np.zeros((P, 3), np.uint8)
+    o["tiles_touched"] = np.zeros(P, np.uint32)
+    o["point_offsets"] = np.zeros(P, np.uint32)
+    R = getattr(L, "orc_preprocess_" + suf)(
+        ctypes.c_int(P), ctypes.c_int(sh_degree), ctypes.c_int(M), _p(means3D), _p(scales), real(scale_modifier),
+        _p(rotations), _p(opacities), _p(shs), _p(cov3D_precomp), _p(colors_precomp), _p(viewmatrix), _p(projmatrix),
+        _p(campos), ctypes.c_int(W), ctypes.c_int(H), real(tanfovx), real(tanfovy), _p(o["radii"]), _p(o["means2D"]),
+        _p(o["depths"]), _p(o["cov3D"]), _p(o["rgb"]), _p(o["conic_opacity"]), _p(o["clamped"]),
+        _p(o["tiles_touched"]), _p(o["point_offsets"]))
+    R = int(R)
+    o["num_rendered"] = R
+    gx, gy = (W + 15) // 16, (H + 15) // 16
+    T = gx * gy
+    o["keys_unsorted"] = np.zeros(R, np.uint64)
+    o["values_unsorted"] = np.zeros(R, np.uint32)
+    o["keys"] = np.zeros(R, np.uint64)
+    o["point_list"] = np.zeros(R, np.uint32)
+    o["ranges"] = np.zeros((T, 2), np.uint32)
+    getattr(L, "orc_binning_" + suf)(
+        ctypes.c_int(P), ctypes.c_int(W), ctypes.c_int(H), _p(o["radii"]), _p(o["means2D"]), _p(o["depths"]),
+        _p(o["point_offsets"]), ctypes.c_int64(R), _p(o["keys_unsorted"]), _p(o["values_unsorted"]), _p(o["keys"]),
+        _p(o["point_list"]), _p(o["ranges"]))
+    colors = colors_precomp if colors_precomp is not None else o["rgb"]
+    o["final_T"] = np.zeros((H, W), dtype)
+    o["n_contrib"] = np.zeros((H, W), np.uint32)
+    o["color"] = np.zeros((3, H, W), dtype)
+    o["feature"] = np.zeros((3, H, W), dtype) if include_feature else np.zeros(1, dtype)
+    kex, kco = ctypes.c_int64(0), ctypes.c_int64(0)
+    getattr(L, "orc_render_" + suf)(
+        ctypes.c_int(W), ctypes.c_int(H), _p(o["ranges"]), _p(o["point_list"]), _p(o["means2D"]), _p(colors),
+        _p(language_feature if include_feature else None), _p(o["conic_opacity"]), _p(bg),
+        ctypes.c_int(1 if include_feature else 0), _p(o["final_T"]), _p(o["n_contrib"]), _p(o["color"]),
+        _p(o["feature"]), ctypes.byref(kex), ctypes.byref(kco))
+    o["k_exam"], o["k_contrib"] = int(kex.value), int(kco.value)
+    o["_inputs"] = dict(means3D=means3D, opacities=opacities, shs=shs, colors_precomp=colors_precomp,
+                        language_feature=language_feature, scales=scales, rotations=rotations,
+                        cov3D_precomp=cov3D_precomp, viewmatrix=viewmatrix, projmatrix=projmatrix, campos=campos,
+                        bg=bg, tanfovx=tanfovx, tanfovy=tanfovy, scale_modifier=scale_modifier, sh_degree=sh_degree,
+                        include_feature=include_feature, M=M, dtype=dtype)
+    return o
+
+
+def backward(fw: Dict[str, np.ndarray], dL_dcolor, dL_dfeature: Optional[np.ndarray]) -> Dict[str, np.ndarray]:
+    L = lib()
+    i = fw["_inputs"]
+    dtype = i["dtype"]
+    suf = "f32" if dtype == np.float32 else "f64"
+    real = ctypes.c_float if dtype == np.float32 else ctypes.c_double
+    P, W, H, M = fw["P"], fw["W"], fw["H"], i["M"]
+    inc = i["include_feature"]
+    dL_dcolor = _np(dL_dcolor, dtype)
+    dL_dfeature = _np(dL_dfeature, dtype) if inc else None
+    g = dict()
+    g["means2D"] = np.zeros((P, 3), dtype)
+    g["conic"] = np.zeros((P, 4), dtype)
+    g["opacities"] = np.zeros((P, 1), dtype)
+    g["colors"] = np.zeros((P, 3), dtype)
+    g["language_feature"] = np.zeros((P, 3), dtype) if inc else np.zeros(1, dtype)
+    g["means3D"] = np.zeros((P, 3), dtype)
+    g["cov3D"] = np.zeros((P, 6), dtype)
+    g["shs"] = np.zeros((P, M, 3), dtype)
+    g["scales"] = np.zeros((P, 3), dtype)
+    g["rotations"] = np.zeros((P, 4), dtype)
+    colors = i["colors_precomp"] if i["colors_precomp"] is not None else fw["rgb"]
+    getattr(L, "orc_render_bw_" + suf)(
+        ctypes.c_int(P), ctypes.c_int(W), ctypes.c_int(H), _p(fw["ranges"]), _p(fw["point_list"]), _p(i["bg"]),
+        _p(fw["means2D"]), _p(fw["conic_opacity"]), _p(colors), _p(i["language_feature"] if inc else None),
+        _p(fw["final_T"]), _p(fw["n_contrib"]), _p(dL_dcolor), _p(dL_dfeature), ctypes.c_int(1 if inc else 0),
+        _p(g["means2D"]), _p(g["conic"]), _p(g["opacities"]), _p(g["colors"]), _p(g["language_feature"]))
+    cov3Ds = i["cov3D_precomp"] if i["cov3D_precomp"] is not None else fw["cov3D"]
+    getattr(L, "orc_preprocess_bw_" + suf)(
+        ctypes.c_int(P), ctypes.c_int(i["sh_degree"]), ctypes.c_int(M), _p(i["means3D"]), _p(fw["radii"]),
+        _p(i["shs"]), _p(fw["clamped"]), _p(i["scales"]), _p(i["rotations"]), real(i["scale_modifier"]), _p(cov3Ds),
+        _p(i["viewmatrix"]), _p(i["projmatrix"]), ctypes.c_int(W), ctypes.c_int(H), real(i["tanfovx"]),
+        real(i["tanfovy"]), _p(i["campos"]), _p(g["means2D"]), _p(g["conic"]), _p(g["means3D"]), _p(g["colors"]),
+        _p(g["cov3D"]), _p(g["shs"]), _p(g["scales"]), _p(g["rotations"]))
+    return g
+
+
+def mark_visible(means3D, viewmatrix, dtype=np.float32) -> np.ndarray:
+    means3D = _np(means3D, dtype)
+    viewmatrix = _np(viewmatrix, dtype).reshape(-1)
+    out = np.zeros(means3D.shape[0], np.uint8)
+    getattr(lib(), "orc_mark_visible_" + ("f32" if dtype == np.float32 else "f64"))(
+        ctypes.c_int(means3D.shape[0]), _p(means3D), _p(viewmatrix), _p(out))
+    return out.astype(bool)
