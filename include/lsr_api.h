@@ -1,0 +1,167 @@
+/* lsr_api.h — C ABI of liblsr.so, the B200-native (sm_100a) Gaussian-splatting rasterizer.
+ *
+ * This is the drop-in boundary for LangSplat's hot path.  The reference has no C ABI of its own; its
+ * boundary is the pybind module `diff_gaussian_rasterization._C` (RAST/ext.cpp:15-19, RAST =
+ * submodules/langsplat-rasterization) whose three functions hand raw device pointers to
+ * CudaRasterizer::Rasterizer::{forward,backward,markVisible} (RAST/cuda_rasterizer/rasterizer.h:20-92).
+ * Each entry point below replaces one of those and cites it.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer to float32 / int32 data allocated by the caller (PyTorch),
+ *    except where a parameter is documented as "host";
+ *  - the library never allocates tensors, never frees caller memory, launches only on `stream`;
+ *  - return value: LSR_OK (0) or a negative lsr_status; lsr_last_error() gives a thread-local message;
+ *  - `stream` is a cudaStream_t passed as void* so that this header needs no CUDA headers.
+ */
+#ifndef LSR_API_H_INCLUDED
+#define LSR_API_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LSR_VERSION 1
+
+typedef enum lsr_status {
+  LSR_OK = 0,
+  LSR_ERR_INVALID = -1,     /* bad argument (null pointer, P < 0, exclusive inputs both / neither given) */
+  LSR_ERR_CAPACITY = -2,    /* instance list / scratch too small: *num_rendered holds the needed count, call again */
+  LSR_ERR_CUDA = -3,        /* a CUDA call failed; message in lsr_last_error() */
+  LSR_ERR_PREFILTERED = -4  /* prefiltered=1 but a Gaussian was culled (reference: __trap, auxiliary.h:156-160) */
+} lsr_status;
+
+/* Per-call constants.  Replaces GaussianRasterizationSettings (RAST/diff_gaussian_rasterization/__init__.py:166-179)
+ * plus the scalar arguments of RasterizeGaussiansCUDA (RAST/rasterize_points.cu:35-57). */
+typedef struct lsr_frame {
+  int32_t P;               /* number of Gaussians */
+  int32_t M;               /* SH coefficients per Gaussian (sh.size(1)); 0 when colors are precomputed */
+  int32_t D;               /* active SH degree 0..3 */
+  int32_t width, height;
+  float tanfovx, tanfovy;
+  float scale_modifier;
+  int32_t prefiltered;
+  int32_t debug;           /* 1: synchronise + check after every stage (CHECK_CUDA, auxiliary.h:166-173) */
+  int32_t include_feature; /* blend the 3-channel language feature too */
+  const float* bg;         /* [3] */
+  const float* viewmatrix; /* [16], transposed world->view, flat index m[0]*x + m[4]*y + m[8]*z + m[12] */
+  const float* projmatrix; /* [16], full projection, same convention */
+  const float* campos;     /* [3] */
+} lsr_frame;
+
+/* Per-Gaussian inputs (null = absent).  Exactly one of shs / colors_precomp, and exactly one of
+ * (scales, rotations) / cov3D_precomp — RAST/diff_gaussian_rasterization/__init__.py:201-205. */
+typedef struct lsr_inputs {
+  const float* means3D;          /* [P,3] */
+  const float* shs;              /* [P,M,3] */
+  const float* colors_precomp;   /* [P,3] */
+  const float* language_feature; /* [P,3] (required when include_feature) */
+  const float* opacities;        /* [P] */
+  const float* scales;           /* [P,3] */
+  const float* rotations;        /* [P,4] */
+  const float* cov3D_precomp;    /* [P,6] */
+} lsr_inputs;
+
+/* Gradient outputs of lsr_backward (null = not wanted).  Order/shape as returned by
+ * RasterizeGaussiansBackwardCUDA (RAST/rasterize_points.cu:129-224). */
+typedef struct lsr_grads {
+  float* dL_dmeans3D;           /* [P,3] */
+  float* dL_dmeans2D;           /* [P,3] (z component always 0) */
+  float* dL_dsh;                /* [P,M,3] */
+  float* dL_dcolors;            /* [P,3] */
+  float* dL_dlanguage_feature;  /* [P,3] */
+  float* dL_dopacity;           /* [P] */
+  float* dL_dscales;            /* [P,3] */
+  float* dL_drotations;         /* [P,4] */
+  float* dL_dcov3D;             /* [P,6] */
+  float* dL_dconic;             /* [P,4] (internal in the reference; exposed for tests) */
+} lsr_grads;
+
+/* need_mask bits for lsr_backward: which groups of gradients the caller will read
+ * (ctx.needs_input_grad on the Python side).  LSR_NEED_ALL reproduces the reference. */
+#define LSR_NEED_GEOMETRY 1u /* means3D, opacity, scales, rotations, cov3D (=> conic/opacity accumulation + K8/K9) */
+#define LSR_NEED_COLOR 2u    /* colors_precomp or sh */
+#define LSR_NEED_FEATURE 4u  /* language_feature */
+#define LSR_NEED_MEANS2D 8u  /* screen-space positional gradient */
+#define LSR_NEED_ALL 15u
+
+/* ---- buffer sizes.  The caller allocates byte buffers (>=256-B aligned) of at least these sizes. ----
+ * geom  : per-call saved state, P-sized   (replaces geomBuffer,    rasterizer_impl.cu:155-170)
+ * image : per-call saved state, W*H-sized (replaces imgBuffer,     rasterizer_impl.cu:172-179)
+ * list  : per-call saved sorted Gaussian ids, 4 B * capacity (the part of binningBuffer backward needs)
+ * scratch: transient sort / scan workspace, may be shared by all calls on one stream
+ *           (replaces the rest of binningBuffer + CUB temp storage, rasterizer_impl.cu:181-194). */
+size_t lsr_geom_bytes(int32_t P);
+size_t lsr_image_bytes(int32_t width, int32_t height);
+size_t lsr_list_bytes(int64_t capacity);
+size_t lsr_scratch_bytes(int32_t P, int32_t width, int32_t height, int64_t capacity);
+
+/* Byte offsets of the arrays inside geom / image / scratch, for tests that compare stage by stage.
+ * `which` is one of the LSR_ARR_* ids; returns (size_t)-1 for an unknown id. */
+enum {
+  LSR_ARR_GEOM_REC = 0,      /* float[P][12]: x, y, conic.x, conic.y, conic.z, opacity, r, g, b, f0, f1, f2 */
+  LSR_ARR_GEOM_DEPTH = 1,    /* float[P] */
+  LSR_ARR_GEOM_TILES = 2,    /* uint32[P] tiles_touched */
+  LSR_ARR_GEOM_OFFSETS = 3,  /* uint32[P] inclusive scan of tiles_touched */
+  LSR_ARR_GEOM_COV3D = 4,    /* float[P][6] */
+  LSR_ARR_GEOM_CLAMPED = 5,  /* uint8[P] bit ch set when colour channel ch was clamped */
+  LSR_ARR_IMG_FINAL_T = 10,  /* float[H*W] */
+  LSR_ARR_IMG_NCONTRIB = 11, /* uint32[H*W] */
+  LSR_ARR_IMG_RANGES = 12,   /* uint32[T][2] */
+  LSR_ARR_SCR_KEYS_UNSORTED = 20, /* uint64[capacity] */
+  LSR_ARR_SCR_VALS_UNSORTED = 21, /* uint32[capacity] */
+  LSR_ARR_SCR_KEYS_SORTED = 22    /* uint64[capacity] (valid after lsr_forward; position depends on pass parity) */
+};
+size_t lsr_array_offset(int which, int32_t P, int32_t width, int32_t height, int64_t capacity);
+
+/* Forward.  Replaces _C.rasterize_gaussians -> RasterizeGaussiansCUDA (RAST/rasterize_points.cu:35-127) ->
+ * CudaRasterizer::Rasterizer::forward (RAST/cuda_rasterizer/rasterizer_impl.cu:198-355).
+ * out_color [3,H,W]; out_feature [3,H,W] (ignored when !include_feature); radii int32[P].  All three are fully
+ * written (no pre-zeroing needed).  *num_rendered (HOST) receives R, the number of Gaussian/tile instances.
+ * If R > list_capacity returns LSR_ERR_CAPACITY having written only radii and *num_rendered. */
+int lsr_forward(const lsr_frame* frame, const lsr_inputs* in, float* out_color, float* out_feature, int32_t* radii,
+                void* geom, void* image, void* list, int64_t list_capacity, void* scratch, size_t scratch_bytes,
+                int64_t* num_rendered, void* stream);
+
+/* Backward.  Replaces _C.rasterize_gaussians_backward -> RasterizeGaussiansBackwardCUDA
+ * (RAST/rasterize_points.cu:129-224) -> Rasterizer::backward (rasterizer_impl.cu:359-463).
+ * dL_dcolor / dL_dfeature are [3,H,W]; dL_dcolor may be null (treated as zero, as in feature-only training);
+ * dL_dfeature may be null when !include_feature.  Every non-null lsr_grads pointer is fully written
+ * (the library zero-fills what it accumulates into; no pre-zeroing by the caller). */
+int lsr_backward(const lsr_frame* frame, const lsr_inputs* in, const int32_t* radii, const void* geom,
+                 const void* image, const void* list, const float* dL_dcolor, const float* dL_dfeature,
+                 uint32_t need_mask, const lsr_grads* grads, void* stream);
+
+/* Replaces _C.mark_visible -> markVisible (rasterize_points.cu:226-245) -> checkFrustum (rasterizer_impl.cu:54-66). */
+int lsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present, void* stream);
+
+/* Stable ascending radix sort of (uint64 key, uint32 value) pairs on bits [0, end_bit) — the sort the forward uses
+ * in place of cub::DeviceRadixSort::SortPairs (rasterizer_impl.cu:306-311); exported for unit tests.
+ * keys_tmp / vals_tmp are n-sized ping-pong buffers; result lands in keys_out / vals_out.
+ * `work` needs lsr_sort_work_bytes(n) bytes. */
+size_t lsr_sort_work_bytes(int64_t n);
+int lsr_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                   uint64_t* keys_tmp, uint32_t* vals_tmp, int64_t n, int end_bit, void* work, size_t work_bytes,
+                   void* stream);
+
+/* Per-stage device timing (CUDA events on `stream`), used by bench.py for the live roofline figures.
+ * lsr_profile_enable(1) makes forward/backward record events; lsr_profile_read() synchronises the events of the
+ * most recent forward+backward and writes up to n stage durations in ms, returning the number of stages.
+ * Stage order: see lsr_profile_stage_name(). */
+void lsr_profile_enable(int on);
+int lsr_profile_read(float* ms, int n);
+const char* lsr_profile_stage_name(int i);
+
+/* Number of kernel launches issued by this library since load (for bench.py's gpu_launches). */
+uint64_t lsr_launch_count(void);
+
+const char* lsr_last_error(void);
+int lsr_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LSR_API_H_INCLUDED */

@@ -1,0 +1,95 @@
+"""ctypes binding of liblsr.so (include/lsr_api.h).
+
+There is no fallback: if the CUDA library is missing or does not export the expected symbols the
+import fails loudly (build it with `python -c "import __graft_entry__ as g; g.build()"` or
+`make -C langsplat_b200/csrc`).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_int32, c_int64, c_size_t, c_uint32, c_uint64, c_void_p
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "liblsr.so")
+
+LSR_OK = 0
+LSR_ERR_INVALID = -1
+LSR_ERR_CAPACITY = -2
+LSR_ERR_CUDA = -3
+LSR_ERR_PREFILTERED = -4
+
+NEED_GEOMETRY, NEED_COLOR, NEED_FEATURE, NEED_MEANS2D, NEED_ALL = 1, 2, 4, 8, 15
+
+# lsr_array_offset ids
+ARR_GEOM_REC, ARR_GEOM_DEPTH, ARR_GEOM_TILES, ARR_GEOM_OFFSETS, ARR_GEOM_COV3D, ARR_GEOM_CLAMPED = 0, 1, 2, 3, 4, 5
+ARR_IMG_FINAL_T, ARR_IMG_NCONTRIB, ARR_IMG_RANGES = 10, 11, 12
+ARR_SCR_KEYS_UNSORTED, ARR_SCR_VALS_UNSORTED, ARR_SCR_KEYS_SORTED = 20, 21, 22
+
+
+class Frame(Structure):
+    _fields_ = [("P", c_int32), ("M", c_int32), ("D", c_int32), ("width", c_int32), ("height", c_int32),
+                ("tanfovx", c_float), ("tanfovy", c_float), ("scale_modifier", c_float), ("prefiltered", c_int32),
+                ("debug", c_int32), ("include_feature", c_int32), ("bg", c_void_p), ("viewmatrix", c_void_p),
+                ("projmatrix", c_void_p), ("campos", c_void_p)]
+
+
+class Inputs(Structure):
+    _fields_ = [(n, c_void_p) for n in ("means3D", "shs", "colors_precomp", "language_feature", "opacities",
+                                         "scales", "rotations", "cov3D_precomp")]
+
+
+class Grads(Structure):
+    _fields_ = [(n, c_void_p) for n in ("dL_dmeans3D", "dL_dmeans2D", "dL_dsh", "dL_dcolors",
+                                         "dL_dlanguage_feature", "dL_dopacity", "dL_dscales", "dL_drotations",
+                                         "dL_dcov3D", "dL_dconic")]
+
+
+EXPORTS = {
+    "lsr_geom_bytes": (c_size_t, [c_int32]),
+    "lsr_image_bytes": (c_size_t, [c_int32, c_int32]),
+    "lsr_list_bytes": (c_size_t, [c_int64]),
+    "lsr_scratch_bytes": (c_size_t, [c_int32, c_int32, c_int32, c_int64]),
+    "lsr_array_offset": (c_size_t, [c_int, c_int32, c_int32, c_int32, c_int64]),
+    "lsr_forward": (c_int, [POINTER(Frame), POINTER(Inputs), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                            c_void_p, c_int64, c_void_p, c_size_t, POINTER(c_int64), c_void_p]),
+    "lsr_backward": (c_int, [POINTER(Frame), POINTER(Inputs), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                             c_void_p, c_uint32, POINTER(Grads), c_void_p]),
+    "lsr_mark_visible": (c_int, [c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "lsr_sort_work_bytes": (c_size_t, [c_int64]),
+    "lsr_sort_pairs": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p,
+                               c_size_t, c_void_p]),
+    "lsr_profile_enable": (None, [c_int]),
+    "lsr_profile_read": (c_int, [POINTER(c_float), c_int]),
+    "lsr_profile_stage_name": (c_char_p, [c_int]),
+    "lsr_launch_count": (c_uint64, []),
+    "lsr_last_error": (c_char_p, []),
+    "lsr_version": (c_int, []),
+}
+
+_lib = None
+
+
+def load() -> ctypes.CDLL:
+    """Load liblsr.so and bind every symbol include/lsr_api.h declares.  Raises if anything is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} not found: the CUDA extension is not built and langsplat_b200 has no CPU fallback. "
+            "Run `make -C langsplat_b200/csrc` (needs nvcc).")
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in EXPORTS.items():
+        try:
+            fn = getattr(lib, name)
+        except AttributeError as e:
+            raise ImportError(f"liblsr.so does not export {name}") from e
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def last_error() -> str:
+    return load().lsr_last_error().decode("utf-8", "replace")

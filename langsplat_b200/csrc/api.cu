@@ -1,0 +1,346 @@
+// api.cu — the C ABI of liblsr.so (include/lsr_api.h): argument checks, buffer carving, stage orchestration.
+// Orchestration replaces CudaRasterizer::Rasterizer::forward / backward / markVisible
+// (RAST/cuda_rasterizer/rasterizer_impl.cu:141-153, 198-355, 359-463).
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <algorithm>
+#include <utility>
+#include <vector>
+
+#include "common.cuh"
+
+namespace lsr {
+
+static std::atomic<uint64_t> g_launches{0};
+void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+
+static thread_local char g_err[512] = "";
+static int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+#define LSR_CUDA(expr)                                                                                   \
+  do {                                                                                                   \
+    cudaError_t _e = (expr);                                                                             \
+    if (_e != cudaSuccess) return fail(LSR_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(_e));    \
+  } while (0)
+
+static int stage_check(const lsr_frame* f, cudaStream_t s, const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess && f->debug) e = cudaStreamSynchronize(s);  // CHECK_CUDA(..., debug), auxiliary.h:166-173
+  if (e != cudaSuccess) return fail(LSR_ERR_CUDA, "[CUDA ERROR] in stage %s: %s", what, cudaGetErrorString(e));
+  return LSR_OK;
+}
+#define LSR_STAGE(what)                            \
+  do {                                             \
+    int _r = stage_check(frame, s, what);          \
+    if (_r != LSR_OK) return _r;                   \
+  } while (0)
+
+// getHigherMsb, RAST/cuda_rasterizer/rasterizer_impl.cu:35-50
+static uint32_t higher_msb(uint32_t n) {
+  uint32_t msb = sizeof(n) * 4, step = msb;
+  while (step > 1) {
+    step /= 2;
+    if (n >> msb) msb += step; else msb -= step;
+  }
+  if (n >> msb) msb++;
+  return msb;
+}
+
+// ---- per-stage profiling with CUDA events on the caller's stream ----
+enum { ST_PRE = 0, ST_SCAN, ST_SYNC, ST_DUP, ST_SORT, ST_RANGES, ST_RENDER, ST_BZERO, ST_BRENDER, ST_BPRE, ST_COUNT };
+static const char* kStageNames[ST_COUNT] = {"preprocess_fwd", "scan", "host_sync_gap", "duplicate", "sort",
+                                            "tile_ranges",    "render_fwd", "bwd_zero_fill", "render_bwd",
+                                            "preprocess_bwd"};
+static bool g_profile = false;
+static cudaEvent_t g_ev_f[8], g_ev_b[4];
+static bool g_ev_init = false, g_have_f = false, g_have_b = false;
+static void prof_init() {
+  if (g_ev_init) return;
+  for (auto& e : g_ev_f) cudaEventCreate(&e);
+  for (auto& e : g_ev_b) cudaEventCreate(&e);
+  g_ev_init = true;
+}
+static inline void prof(cudaEvent_t* arr, int i, cudaStream_t s) {
+  if (g_profile) cudaEventRecord(arr[i], s);
+}
+
+static uint32_t* pinned_ctrl() {
+  static thread_local uint32_t* p = nullptr;
+  if (!p) cudaMallocHost(&p, 64 * sizeof(uint32_t));
+  return p;
+}
+
+}  // namespace lsr
+
+using namespace lsr;
+
+#pragma GCC visibility push(default)
+extern "C" {
+
+size_t lsr_geom_bytes(int32_t P) { return geom_bytes(P); }
+size_t lsr_image_bytes(int32_t width, int32_t height) { return image_bytes(width, height); }
+size_t lsr_list_bytes(int64_t capacity) { return align_up((size_t)(capacity > 0 ? capacity : 0) * 4) + 256; }
+size_t lsr_scratch_bytes(int32_t P, int32_t width, int32_t height, int64_t capacity) {
+  (void)width; (void)height;
+  return scratch_bytes(P, capacity);
+}
+size_t lsr_sort_work_bytes(int64_t n) { return sort_work_bytes(n); }
+
+size_t lsr_array_offset(int which, int32_t P, int32_t width, int32_t height, int64_t capacity) {
+  char* base = (char*)4096;  // never dereferenced
+  GeomView g = geom_view(base, P);
+  ImageView im = image_view(base, width, height);
+  ScratchView sc = scratch_view(base, P, capacity);
+  const int T = ((width + TILE_X - 1) / TILE_X) * ((height + TILE_Y - 1) / TILE_Y);
+  const int passes = (32 + (int)higher_msb((uint32_t)T) + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
+  switch (which) {
+    case LSR_ARR_GEOM_REC: return (char*)g.rec - base;
+    case LSR_ARR_GEOM_DEPTH: return (char*)g.depth - base;
+    case LSR_ARR_GEOM_TILES: return (char*)g.tiles - base;
+    case LSR_ARR_GEOM_OFFSETS: return (char*)g.offsets - base;
+    case LSR_ARR_GEOM_COV3D: return (char*)g.cov3D - base;
+    case LSR_ARR_GEOM_CLAMPED: return (char*)g.clamped - base;
+    case LSR_ARR_IMG_FINAL_T: return (char*)im.final_T - base;
+    case LSR_ARR_IMG_NCONTRIB: return (char*)im.n_contrib - base;
+    case LSR_ARR_IMG_RANGES: return (char*)im.ranges - base;
+    case LSR_ARR_SCR_KEYS_UNSORTED: return (char*)sc.keys_a - base;
+    case LSR_ARR_SCR_VALS_UNSORTED: return (char*)sc.vals_a - base;
+    case LSR_ARR_SCR_KEYS_SORTED: return (char*)((passes & 1) ? sc.keys_b : sc.keys_a) - base;
+    default: return (size_t)-1;
+  }
+}
+
+const char* lsr_last_error(void) { return g_err; }
+int lsr_version(void) { return LSR_VERSION; }
+uint64_t lsr_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+void lsr_profile_enable(int on) {
+  g_profile = on != 0;
+  if (g_profile) prof_init();
+  g_have_f = g_have_b = false;
+}
+const char* lsr_profile_stage_name(int i) { return (i >= 0 && i < ST_COUNT) ? kStageNames[i] : ""; }
+int lsr_profile_read(float* ms, int n) {
+  if (!g_profile) return 0;
+  float v[ST_COUNT];
+  for (int i = 0; i < ST_COUNT; i++) v[i] = 0.f;
+  if (g_have_f) {
+    cudaEventSynchronize(g_ev_f[7]);
+    for (int i = 0; i < 7; i++) cudaEventElapsedTime(&v[ST_PRE + i], g_ev_f[i], g_ev_f[i + 1]);
+  }
+  if (g_have_b) {
+    cudaEventSynchronize(g_ev_b[3]);
+    for (int i = 0; i < 3; i++) cudaEventElapsedTime(&v[ST_BZERO + i], g_ev_b[i], g_ev_b[i + 1]);
+  }
+  for (int i = 0; i < ST_COUNT && i < n; i++) ms[i] = v[i];
+  return ST_COUNT;
+}
+
+int lsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present, void* stream) {
+  (void)projmatrix;  // the reference's in_frustum computes p_proj but only tests p_view.z (auxiliary.h:139-164)
+  if (P < 0) return fail(LSR_ERR_INVALID, "P < 0");
+  if (P == 0) return LSR_OK;
+  if (!means3D || !viewmatrix || !present) return fail(LSR_ERR_INVALID, "null pointer");
+  launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream);
+  LSR_CUDA(cudaGetLastError());
+  return LSR_OK;
+}
+
+int lsr_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                   uint64_t* keys_tmp, uint32_t* vals_tmp, int64_t n, int end_bit, void* work, size_t work_bytes,
+                   void* stream) {
+  if (n < 0) return fail(LSR_ERR_INVALID, "n < 0");
+  if (n == 0) return LSR_OK;
+  if (n >= (1ll << 30)) return fail(LSR_ERR_INVALID, "n must be < 2^30");
+  if (!keys_in || !vals_in || !keys_out || !vals_out || !keys_tmp || !vals_tmp || !work)
+    return fail(LSR_ERR_INVALID, "null pointer");
+  if (work_bytes < sort_work_bytes(n)) return fail(LSR_ERR_CAPACITY, "sort work buffer too small");
+  sort_pairs(keys_in, vals_in, keys_out, vals_out, keys_tmp, vals_tmp, n, end_bit, work, (cudaStream_t)stream);
+  LSR_CUDA(cudaGetLastError());
+  return LSR_OK;
+}
+
+static int check_frame(const lsr_frame* f, const lsr_inputs* in) {
+  if (!f || !in) return fail(LSR_ERR_INVALID, "null frame / inputs");
+  if (f->P < 0 || f->width <= 0 || f->height <= 0) return fail(LSR_ERR_INVALID, "bad P / image size");
+  if (f->P == 0) return LSR_OK;
+  if (!in->means3D) return fail(LSR_ERR_INVALID, "means3D must have dimensions (num_points, 3)");
+  if (!in->opacities || !f->bg || !f->viewmatrix || !f->projmatrix || !f->campos)
+    return fail(LSR_ERR_INVALID, "null opacities / bg / viewmatrix / projmatrix / campos");
+  if ((in->shs == nullptr) == (in->colors_precomp == nullptr))
+    return fail(LSR_ERR_INVALID, "Please provide excatly one of either SHs or precomputed colors!");
+  const bool sr = in->scales != nullptr && in->rotations != nullptr;
+  if (sr == (in->cov3D_precomp != nullptr) || ((in->scales != nullptr) != (in->rotations != nullptr)))
+    return fail(LSR_ERR_INVALID,
+                "Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!");
+  if (in->shs && (f->D < 0 || f->D > 3 || f->M < (f->D + 1) * (f->D + 1)))
+    return fail(LSR_ERR_INVALID, "sh_degree %d needs at least %d SH coefficients, got %d", f->D,
+                (f->D + 1) * (f->D + 1), f->M);
+  if (f->include_feature && !in->language_feature)
+    return fail(LSR_ERR_INVALID, "include_feature is set but language_feature_precomp is missing");
+  return LSR_OK;
+}
+
+int lsr_forward(const lsr_frame* frame, const lsr_inputs* in, float* out_color, float* out_feature, int32_t* radii,
+                void* geom, void* image, void* list, int64_t list_capacity, void* scratch, size_t scratch_nbytes,
+                int64_t* num_rendered, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  int rc = check_frame(frame, in);
+  if (rc != LSR_OK) return rc;
+  if (!out_color || !image || !num_rendered || (frame->include_feature && !out_feature))
+    return fail(LSR_ERR_INVALID, "null output pointer");
+  const int P = frame->P, W = frame->width, H = frame->height;
+  const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+  const int T = gx * gy;
+  ImageView img = image_view(image, W, H);
+  *num_rendered = 0;
+  if (g_profile) g_have_f = false;
+  LSR_CUDA(cudaMemsetAsync(img.ranges, 0, (size_t)T * sizeof(uint2), s));  // rasterizer_impl.cu:313
+  int64_t R = 0;
+  GeomView g = geom_view(geom, P);
+  ScratchView sc = scratch_view(scratch, P, list_capacity);
+  const uint64_t* keys_sorted = nullptr;
+  if (P > 0) {
+    if (!radii || !geom || !scratch) return fail(LSR_ERR_INVALID, "null radii / geom / scratch");
+    if (list_capacity < 0 || list_capacity >= (1ll << 30)) return fail(LSR_ERR_INVALID, "list_capacity out of range");
+    if (scratch_nbytes < scratch_bytes(P, list_capacity))
+      return fail(LSR_ERR_INVALID, "scratch buffer smaller than lsr_scratch_bytes(P, capacity)");
+    // focal lengths exactly as the reference computes them on the host in f32 (rasterizer_impl.cu:225-226)
+    const float focal_y = H / (2.0f * frame->tanfovy);
+    const float focal_x = W / (2.0f * frame->tanfovx);
+    LSR_CUDA(cudaMemsetAsync(scratch, 0, sc.head_zero_bytes, s));
+    prof(g_ev_f, 0, s);
+    launch_preprocess_fwd(*frame, *in, focal_x, focal_y, radii, g, sc.ctrl, s);
+    LSR_STAGE("preprocess_fwd");
+    prof(g_ev_f, 1, s);
+    launch_scan_tiles(P, g.tiles, g.offsets, sc.scan_status, sc.ctrl, s);
+    LSR_STAGE("scan");
+    prof(g_ev_f, 2, s);
+    // R decides the launch geometry of the sort; read it back like the reference does (rasterizer_impl.cu:284)
+    uint32_t* h = pinned_ctrl();
+    LSR_CUDA(cudaMemcpyAsync(h, sc.ctrl, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    LSR_CUDA(cudaStreamSynchronize(s));
+    R = (int64_t)h[CTRL_NUM_RENDERED];
+    *num_rendered = R;
+    if (h[CTRL_ERROR] & 1u)
+      return fail(LSR_ERR_PREFILTERED, "Point is filtered although prefiltered is set. This shouldn't happen!");
+    if (R > list_capacity) return fail(LSR_ERR_CAPACITY, "num_rendered %lld exceeds list capacity %lld",
+                                       (long long)R, (long long)list_capacity);
+    if (R > 0 && !list) return fail(LSR_ERR_INVALID, "null list buffer");
+    prof(g_ev_f, 3, s);
+    if (R > 0) {
+      launch_duplicate(P, gx, gy, radii, g, sc.keys_a, sc.vals_a, list_capacity, s);
+      LSR_STAGE("duplicate");
+    }
+    prof(g_ev_f, 4, s);
+    if (R > 0) {
+      const int end_bit = 32 + (int)higher_msb((uint32_t)T);  // rasterizer_impl.cu:303,311
+      const int passes = (end_bit + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
+      uint64_t* kout = (passes & 1) ? sc.keys_b : sc.keys_a;
+      uint64_t* ktmp = (passes & 1) ? sc.keys_a : sc.keys_b;
+      sort_pairs(sc.keys_a, sc.vals_a, kout, (uint32_t*)list, ktmp, sc.vals_b, R, end_bit, sc.sort_work, s);
+      keys_sorted = kout;
+      LSR_STAGE("sort");
+    }
+    prof(g_ev_f, 5, s);
+    if (R > 0) {
+      launch_tile_ranges(R, keys_sorted, img.ranges, s);
+      LSR_STAGE("tile_ranges");
+    }
+    prof(g_ev_f, 6, s);
+  } else if (g_profile) {
+    for (int i = 0; i <= 6; i++) prof(g_ev_f, i, s);
+  }
+  // P == 0 (rasterize_points.cu:91): the reference returns zero-filled images; blending empty ranges gives
+  // colour = bg, which differs, so reproduce the zero fill.
+  if (P == 0) {
+    const size_t N = (size_t)W * H;
+    LSR_CUDA(cudaMemsetAsync(out_color, 0, 3 * N * sizeof(float), s));
+    if (frame->include_feature) LSR_CUDA(cudaMemsetAsync(out_feature, 0, 3 * N * sizeof(float), s));
+  } else {
+    launch_render_fwd(W, H, img.ranges, (const uint32_t*)list, g.rec, frame->bg, frame->include_feature != 0,
+                      img.final_T, img.n_contrib, out_color, out_feature, s);
+    LSR_STAGE("render_fwd");
+  }
+  prof(g_ev_f, 7, s);
+  if (g_profile) g_have_f = true;
+  return LSR_OK;
+}
+
+int lsr_backward(const lsr_frame* frame, const lsr_inputs* in, const int32_t* radii, const void* geom,
+                 const void* image, const void* list, const float* dL_dcolor, const float* dL_dfeature,
+                 uint32_t need_mask, const lsr_grads* grads, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  int rc = check_frame(frame, in);
+  if (rc != LSR_OK) return rc;
+  if (!grads) return fail(LSR_ERR_INVALID, "null grads");
+  const int P = frame->P, W = frame->width, H = frame->height;
+  if (P == 0) return LSR_OK;
+  if (!radii || !geom || !image) return fail(LSR_ERR_INVALID, "null radii / geom / image");
+  const lsr_grads& gr = *grads;
+  const bool feat = frame->include_feature != 0 && dL_dfeature != nullptr;
+  const bool dcol = dL_dcolor != nullptr;
+  const bool geom_need = (need_mask & LSR_NEED_GEOMETRY) != 0;
+  if (!gr.dL_dmeans2D) return fail(LSR_ERR_INVALID, "dL_dmeans2D buffer is required");
+  if (geom_need && (!gr.dL_dconic || !gr.dL_dopacity)) return fail(LSR_ERR_INVALID, "dL_dconic / dL_dopacity required");
+  if (dcol && !gr.dL_dcolors) return fail(LSR_ERR_INVALID, "dL_dcolors buffer required when dL_dcolor is given");
+  if (feat && !gr.dL_dlanguage_feature) return fail(LSR_ERR_INVALID, "dL_dlanguage_feature buffer required");
+  if (g_profile) g_have_b = false;
+  prof(g_ev_b, 0, s);
+  // zero what the blend kernel accumulates into; adjacent buffers are merged into one memset
+  {
+    std::vector<std::pair<char*, size_t>> z;
+    const size_t n = (size_t)P * sizeof(float);
+    auto add = [&](float* p, size_t k) { if (p) z.push_back({(char*)p, n * k}); };
+    add(gr.dL_dmeans2D, 3);
+    add(gr.dL_dconic, 4);
+    add(gr.dL_dopacity, 1);
+    add(gr.dL_dcolors, 3);
+    add(gr.dL_dlanguage_feature, 3);
+    // outputs the per-Gaussian kernel will not write in this configuration
+    const bool run_pre = geom_need || (in->shs && gr.dL_dsh && dcol);
+    if (!run_pre) { add(gr.dL_dmeans3D, 3); add(gr.dL_dcov3D, 6); add(gr.dL_dscales, 3); add(gr.dL_drotations, 4); }
+    if (!run_pre || !in->shs || !gr.dL_dcolors) { if (gr.dL_dsh && frame->M > 0) add(gr.dL_dsh, (size_t)frame->M * 3); }
+    if (run_pre && !in->scales) { add(gr.dL_dscales, 3); add(gr.dL_drotations, 4); }
+    std::sort(z.begin(), z.end());
+    size_t i = 0;
+    while (i < z.size()) {
+      char* b = z[i].first;
+      char* e = b + z[i].second;
+      size_t j = i + 1;
+      while (j < z.size() && z[j].first <= e) { e = std::max(e, z[j].first + z[j].second); j++; }
+      LSR_CUDA(cudaMemsetAsync(b, 0, (size_t)(e - b), s));
+      i = j;
+    }
+  }
+  prof(g_ev_b, 1, s);
+  GeomView g = geom_view(const_cast<void*>(geom), P);
+  ImageView img = image_view(const_cast<void*>(image), W, H);
+  launch_render_bwd(W, H, img.ranges, (const uint32_t*)list, g.rec, frame->bg, frame->include_feature != 0,
+                    img.final_T, img.n_contrib, dL_dcolor, dL_dfeature, need_mask, gr.dL_dmeans2D, gr.dL_dconic,
+                    gr.dL_dopacity, gr.dL_dcolors, gr.dL_dlanguage_feature, s);
+  LSR_STAGE("render_bwd");
+  prof(g_ev_b, 2, s);
+  if (geom_need || (in->shs && gr.dL_dsh && dcol)) {
+    if (!gr.dL_dconic) return fail(LSR_ERR_INVALID, "dL_dconic required for the per-Gaussian backward");
+    const float focal_y = H / (2.0f * frame->tanfovy);
+    const float focal_x = W / (2.0f * frame->tanfovx);
+    launch_preprocess_bwd(*frame, *in, focal_x, focal_y, radii, g, need_mask, gr, s);
+    LSR_STAGE("preprocess_bwd");
+  }
+  prof(g_ev_b, 3, s);
+  if (g_profile) g_have_b = true;
+  (void)feat;
+  return LSR_OK;
+}
+
+}  // extern "C"
+#pragma GCC visibility pop

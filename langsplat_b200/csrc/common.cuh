@@ -1,0 +1,160 @@
+// common.cuh — shared definitions for the sm_100a rasterizer kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/lsr_api.h"
+
+namespace lsr {
+
+constexpr int TILE_X = 16, TILE_Y = 16;  // reference: BLOCK_X/BLOCK_Y, RAST/cuda_rasterizer/config.h:17-18
+constexpr int TILE_PIX = TILE_X * TILE_Y;
+
+// One 48-byte record per Gaussian holds everything the blend kernels gather per instance, so a gather touches
+// two 32-B sectors instead of the reference's four to six (means2D, conic_opacity, rgb, feature are separate
+// arrays there: rasterizer_impl.cu:155-170).
+struct __align__(16) GeomRec {
+  float x, y, cx, cy;   // pixel centre, conic.x, conic.y
+  float cz, o, r, g;    // conic.z, opacity, colour r g
+  float b, f0, f1, f2;  // colour b, language feature
+};
+static_assert(sizeof(GeomRec) == 48, "GeomRec must be 48 bytes");
+
+struct GeomView {
+  GeomRec* rec;
+  float* depth;
+  uint32_t* tiles;
+  uint32_t* offsets;
+  float* cov3D;
+  uint8_t* clamped;
+};
+struct ImageView {
+  float* final_T;
+  uint32_t* n_contrib;
+  uint2* ranges;
+};
+
+__host__ __device__ inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
+
+inline GeomView geom_view(void* base, int P) {
+  char* p = (char*)base;
+  GeomView g;
+  size_t n = (size_t)(P > 0 ? P : 0);
+  g.rec = (GeomRec*)p;       p += align_up(n * sizeof(GeomRec));
+  g.depth = (float*)p;       p += align_up(n * 4);
+  g.tiles = (uint32_t*)p;    p += align_up(n * 4);
+  g.offsets = (uint32_t*)p;  p += align_up(n * 4);
+  g.cov3D = (float*)p;       p += align_up(n * 24);
+  g.clamped = (uint8_t*)p;   p += align_up(n);
+  return g;
+}
+inline size_t geom_bytes(int P) {
+  size_t n = (size_t)(P > 0 ? P : 0);
+  return align_up(n * sizeof(GeomRec)) + 3 * align_up(n * 4) + align_up(n * 24) + align_up(n) + 256;
+}
+inline ImageView image_view(void* base, int W, int H) {
+  char* p = (char*)base;
+  size_t N = (size_t)W * H;
+  size_t T = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+  ImageView v;
+  v.final_T = (float*)p;       p += align_up(N * 4);
+  v.n_contrib = (uint32_t*)p;  p += align_up(N * 4);
+  v.ranges = (uint2*)p;        p += align_up(T * 8);
+  return v;
+}
+inline size_t image_bytes(int W, int H) {
+  size_t N = (size_t)W * H;
+  size_t T = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+  return 2 * align_up(N * 4) + align_up(T * 8) + 256;
+}
+
+// ---- radix sort geometry (radix_sort.cu) ----
+constexpr int SORT_RADIX_BITS = 8;
+constexpr int SORT_BINS = 1 << SORT_RADIX_BITS;
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS = 16;
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // keys per CTA per pass
+constexpr int SORT_MAX_PASSES = 8;
+
+struct SortWork {  // carved from the `work` buffer
+  uint32_t* hist;      // [SORT_MAX_PASSES][SORT_BINS] global digit histograms -> exclusive bases
+  uint32_t* tickets;   // [SORT_MAX_PASSES] dynamic tile ids
+  uint32_t* lookback;  // [SORT_MAX_PASSES][nblocks][SORT_BINS]
+  size_t zero_bytes;   // bytes from hist to the end that must be zero before a sort
+};
+inline size_t sort_nblocks(int64_t n) { return (size_t)((n + SORT_TILE - 1) / SORT_TILE) + 1; }
+inline size_t sort_work_bytes(int64_t n) {
+  return align_up(SORT_MAX_PASSES * SORT_BINS * 4) + align_up(SORT_MAX_PASSES * 4) +
+         align_up((size_t)SORT_MAX_PASSES * sort_nblocks(n) * SORT_BINS * 4) + 256;
+}
+inline SortWork sort_work_view(void* base, int64_t n) {
+  char* p = (char*)base;
+  SortWork w;
+  w.hist = (uint32_t*)p;      p += align_up(SORT_MAX_PASSES * SORT_BINS * 4);
+  w.tickets = (uint32_t*)p;   p += align_up(SORT_MAX_PASSES * 4);
+  w.lookback = (uint32_t*)p;  p += align_up((size_t)SORT_MAX_PASSES * sort_nblocks(n) * SORT_BINS * 4);
+  w.zero_bytes = (size_t)(p - (char*)base);
+  return w;
+}
+
+// ---- scan workspace (binning.cu) ----
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 8;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+inline size_t scan_nblocks(int P) { return (size_t)((P + SCAN_TILE - 1) / SCAN_TILE) + 1; }
+
+struct ScratchView {
+  uint32_t* ctrl;  // [64] control words: [0] num_rendered, [1] scan ticket, [2] error flags
+  uint64_t* scan_status;  // [scan_nblocks]
+  uint64_t* keys_a;
+  uint64_t* keys_b;
+  uint32_t* vals_a;
+  uint32_t* vals_b;
+  void* sort_work;
+  size_t head_zero_bytes;  // ctrl + scan_status must be zero at the start of every forward
+};
+inline ScratchView scratch_view(void* base, int P, int64_t cap) {
+  char* p = (char*)base;
+  ScratchView s;
+  size_t c = (size_t)(cap > 0 ? cap : 0);
+  s.ctrl = (uint32_t*)p;          p += 256;
+  s.scan_status = (uint64_t*)p;   p += align_up(scan_nblocks(P) * 8);
+  s.head_zero_bytes = (size_t)(p - (char*)base);
+  s.keys_a = (uint64_t*)p;        p += align_up(c * 8);
+  s.keys_b = (uint64_t*)p;        p += align_up(c * 8);
+  s.vals_a = (uint32_t*)p;        p += align_up(c * 4);
+  s.vals_b = (uint32_t*)p;        p += align_up(c * 4);
+  s.sort_work = (void*)p;
+  return s;
+}
+inline size_t scratch_bytes(int P, int64_t cap) {
+  size_t c = (size_t)(cap > 0 ? cap : 0);
+  return 256 + align_up(scan_nblocks(P) * 8) + 2 * align_up(c * 8) + 2 * align_up(c * 4) + sort_work_bytes(cap) + 256;
+}
+
+enum CtrlWord { CTRL_NUM_RENDERED = 0, CTRL_SCAN_TICKET = 1, CTRL_ERROR = 2 };
+
+// ---- launchers implemented in the .cu files ----
+void launch_preprocess_fwd(const lsr_frame& f, const lsr_inputs& in, float focal_x, float focal_y, int32_t* radii,
+                           GeomView g, uint32_t* ctrl, cudaStream_t s);
+void launch_scan_tiles(int P, const uint32_t* tiles, uint32_t* offsets, uint64_t* status, uint32_t* ctrl,
+                       cudaStream_t s);
+void launch_duplicate(int P, int grid_x, int grid_y, const int32_t* radii, GeomView g, uint64_t* keys, uint32_t* vals,
+                      int64_t capacity, cudaStream_t s);
+void launch_tile_ranges(int64_t R, const uint64_t* keys, uint2* ranges, cudaStream_t s);
+int sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+               uint64_t* keys_tmp, uint32_t* vals_tmp, int64_t n, int end_bit, void* work, cudaStream_t s);
+void launch_render_fwd(int W, int H, const uint2* ranges, const uint32_t* list, const GeomRec* rec, const float* bg,
+                       bool include_feature, float* final_T, uint32_t* n_contrib, float* out_color,
+                       float* out_feature, cudaStream_t s);
+void launch_render_bwd(int W, int H, const uint2* ranges, const uint32_t* list, const GeomRec* rec, const float* bg,
+                       bool include_feature, const float* final_T, const uint32_t* n_contrib, const float* dL_dcolor,
+                       const float* dL_dfeature, uint32_t need_mask, float* dL_dmean2D, float* dL_dconic,
+                       float* dL_dopacity, float* dL_dcolors, float* dL_dfeat, cudaStream_t s);
+void launch_preprocess_bwd(const lsr_frame& f, const lsr_inputs& in, float focal_x, float focal_y,
+                           const int32_t* radii, GeomView g, uint32_t need_mask, const lsr_grads& gr, cudaStream_t s);
+void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, uint8_t* present, cudaStream_t s);
+
+void count_launch(int n = 1);
+
+}  // namespace lsr

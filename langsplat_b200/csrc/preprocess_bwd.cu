@@ -1,0 +1,266 @@
+// preprocess_bwd.cu — K8'+K9' fused: per-Gaussian backward through conic -> cov2D -> cov3D -> (scale, rotation),
+// through the projection (mean2D -> mean3D) and through the SH colour.
+// Replaces computeCov2DCUDA (RAST/cuda_rasterizer/backward.cu:144-274), preprocessCUDA (backward.cu:346-396),
+// computeColorFromSH backward (:20-139) and computeCov3D backward (:278-341), which the reference runs as two
+// kernels with dL_dcov3D / dL_dmean3D round-tripping through global memory, after zero-filling ten tensors
+// (RAST/rasterize_points.cu:166-183).  Here one kernel writes every output element exactly once (zeros for
+// Gaussians with radius 0), so the caller can hand in uninitialised memory.  HBM-bound.
+#include "common.cuh"
+#include "gs_math.cuh"
+
+namespace lsr {
+
+namespace {
+
+__device__ __forceinline__ float3 dnormvdv(float3 v, float3 dv) {  // RAST/cuda_rasterizer/auxiliary.h:107-117
+  const float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
+  const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+  float3 o;
+  o.x = ((+sum2 - v.x * v.x) * dv.x - v.y * v.x * dv.y - v.z * v.x * dv.z) * invsum32;
+  o.y = (-v.x * v.y * dv.x + (sum2 - v.y * v.y) * dv.y - v.z * v.y * dv.z) * invsum32;
+  o.z = (-v.x * v.z * dv.x - v.y * v.z * dv.y + (sum2 - v.z * v.z) * dv.z) * invsum32;
+  return o;
+}
+
+// SH backward: writes dL_dsh rows [0,(D+1)^2), zero for the rest up to M, returns dL/d(mean) through the direction.
+__device__ __forceinline__ float3 sh_backward(int deg, int M, const float* __restrict__ sh, float3 dir_orig,
+                                              float3 dL_dRGB, float* __restrict__ dsh) {
+  const float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
+  const float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
+  const float g[3] = {dL_dRGB.x, dL_dRGB.y, dL_dRGB.z};
+  float dRGBdx[3] = {0, 0, 0}, dRGBdy[3] = {0, 0, 0}, dRGBdz[3] = {0, 0, 0};
+  auto put = [&](int k, float w) {
+    dsh[k * 3 + 0] = w * g[0];
+    dsh[k * 3 + 1] = w * g[1];
+    dsh[k * 3 + 2] = w * g[2];
+  };
+  int written = 1;
+  put(0, LSR_SH_C0);
+  if (deg > 0) {
+    put(1, -LSR_SH_C1 * y);
+    put(2, LSR_SH_C1 * z);
+    put(3, -LSR_SH_C1 * x);
+    written = 4;
+#pragma unroll
+    for (int ch = 0; ch < 3; ch++) {
+      dRGBdx[ch] = -LSR_SH_C1 * sh[3 * 3 + ch];
+      dRGBdy[ch] = -LSR_SH_C1 * sh[1 * 3 + ch];
+      dRGBdz[ch] = LSR_SH_C1 * sh[2 * 3 + ch];
+    }
+    if (deg > 1) {
+      const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+      put(4, LSR_SH_C2_0 * xy);
+      put(5, LSR_SH_C2_1 * yz);
+      put(6, LSR_SH_C2_2 * (2.f * zz - xx - yy));
+      put(7, LSR_SH_C2_3 * xz);
+      put(8, LSR_SH_C2_4 * (xx - yy));
+      written = 9;
+#pragma unroll
+      for (int ch = 0; ch < 3; ch++) {
+        const float s4 = sh[4 * 3 + ch], s5 = sh[5 * 3 + ch], s6 = sh[6 * 3 + ch], s7 = sh[7 * 3 + ch],
+                    s8 = sh[8 * 3 + ch];
+        dRGBdx[ch] += LSR_SH_C2_0 * y * s4 + LSR_SH_C2_2 * 2.f * -x * s6 + LSR_SH_C2_3 * z * s7 +
+                      LSR_SH_C2_4 * 2.f * x * s8;
+        dRGBdy[ch] += LSR_SH_C2_0 * x * s4 + LSR_SH_C2_1 * z * s5 + LSR_SH_C2_2 * 2.f * -y * s6 +
+                      LSR_SH_C2_4 * 2.f * -y * s8;
+        dRGBdz[ch] += LSR_SH_C2_1 * y * s5 + LSR_SH_C2_2 * 2.f * 2.f * z * s6 + LSR_SH_C2_3 * x * s7;
+      }
+      if (deg > 2) {
+        put(9, LSR_SH_C3_0 * y * (3.f * xx - yy));
+        put(10, LSR_SH_C3_1 * xy * z);
+        put(11, LSR_SH_C3_2 * y * (4.f * zz - xx - yy));
+        put(12, LSR_SH_C3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy));
+        put(13, LSR_SH_C3_4 * x * (4.f * zz - xx - yy));
+        put(14, LSR_SH_C3_5 * z * (xx - yy));
+        put(15, LSR_SH_C3_6 * x * (xx - 3.f * yy));
+        written = 16;
+#pragma unroll
+        for (int ch = 0; ch < 3; ch++) {
+          const float s9 = sh[9 * 3 + ch], s10 = sh[10 * 3 + ch], s11 = sh[11 * 3 + ch], s12 = sh[12 * 3 + ch],
+                      s13 = sh[13 * 3 + ch], s14 = sh[14 * 3 + ch], s15 = sh[15 * 3 + ch];
+          dRGBdx[ch] += (LSR_SH_C3_0 * s9 * 3.f * 2.f * xy + LSR_SH_C3_1 * s10 * yz + LSR_SH_C3_2 * s11 * -2.f * xy +
+                         LSR_SH_C3_3 * s12 * -3.f * 2.f * xz + LSR_SH_C3_4 * s13 * (-3.f * xx + 4.f * zz - yy) +
+                         LSR_SH_C3_5 * s14 * 2.f * xz + LSR_SH_C3_6 * s15 * 3.f * (xx - yy));
+          dRGBdy[ch] += (LSR_SH_C3_0 * s9 * 3.f * (xx - yy) + LSR_SH_C3_1 * s10 * xz +
+                         LSR_SH_C3_2 * s11 * (-3.f * yy + 4.f * zz - xx) + LSR_SH_C3_3 * s12 * -3.f * 2.f * yz +
+                         LSR_SH_C3_4 * s13 * -2.f * xy + LSR_SH_C3_5 * s14 * -2.f * yz +
+                         LSR_SH_C3_6 * s15 * -3.f * 2.f * xy);
+          dRGBdz[ch] += (LSR_SH_C3_1 * s10 * xy + LSR_SH_C3_2 * s11 * 4.f * 2.f * yz +
+                         LSR_SH_C3_3 * s12 * 3.f * (2.f * zz - xx - yy) + LSR_SH_C3_4 * s13 * 4.f * 2.f * xz +
+                         LSR_SH_C3_5 * s14 * (xx - yy));
+        }
+      }
+    }
+  }
+  for (int k = written; k < M; k++) put(k, 0.f);  // entries above the active degree stay zero
+  float3 dL_ddir;
+  dL_ddir.x = dRGBdx[0] * g[0] + dRGBdx[1] * g[1] + dRGBdx[2] * g[2];
+  dL_ddir.y = dRGBdy[0] * g[0] + dRGBdy[1] * g[1] + dRGBdy[2] * g[2];
+  dL_ddir.z = dRGBdz[0] * g[0] + dRGBdz[1] * g[1] + dRGBdz[2] * g[2];
+  return dnormvdv(dir_orig, dL_ddir);
+}
+
+__global__ void __launch_bounds__(256)
+preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, const int32_t* __restrict__ radii,
+                      const float* __restrict__ shs, const uint8_t* __restrict__ clamped,
+                      const float* __restrict__ scales, const float* __restrict__ rotations, float scale_modifier,
+                      const float* __restrict__ cov3Ds, const float* __restrict__ viewmatrix,
+                      const float* __restrict__ projmatrix, float h_x, float h_y, float tan_fovx, float tan_fovy,
+                      const float* __restrict__ campos, const float* __restrict__ dL_dmean2D,
+                      const float* __restrict__ dL_dconic, const float* __restrict__ dL_dcolor,
+                      float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
+                      float* __restrict__ dL_dscale, float* __restrict__ dL_drot) {
+  __shared__ float s_view[16], s_proj[16], s_cam[3];
+  if (threadIdx.x < 16) {
+    s_view[threadIdx.x] = viewmatrix[threadIdx.x];
+    s_proj[threadIdx.x] = projmatrix[threadIdx.x];
+  }
+  if (threadIdx.x < 3) s_cam[threadIdx.x] = campos[threadIdx.x];
+  __syncthreads();
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P) return;
+  if (!(radii[idx] > 0)) {
+    if (dL_dmean3D) { dL_dmean3D[3 * (size_t)idx] = 0.f; dL_dmean3D[3 * (size_t)idx + 1] = 0.f; dL_dmean3D[3 * (size_t)idx + 2] = 0.f; }
+    if (dL_dcov3D) for (int i = 0; i < 6; i++) dL_dcov3D[6 * (size_t)idx + i] = 0.f;
+    if (dL_dsh) for (int i = 0; i < M * 3; i++) dL_dsh[(size_t)idx * M * 3 + i] = 0.f;
+    if (dL_dscale) for (int i = 0; i < 3; i++) dL_dscale[3 * (size_t)idx + i] = 0.f;
+    if (dL_drot) reinterpret_cast<float4*>(dL_drot)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+    return;
+  }
+  const float mx = means3D[3 * (size_t)idx], my = means3D[3 * (size_t)idx + 1], mz = means3D[3 * (size_t)idx + 2];
+  float cov3D[6];
+#pragma unroll
+  for (int i = 0; i < 6; i++) cov3D[i] = cov3Ds[6 * (size_t)idx + i];
+
+  // ---------------- computeCov2DCUDA (backward.cu:144-274) ----------------
+  Cov2D c2;
+  compute_cov2D(mx, my, mz, h_x, h_y, tan_fovx, tan_fovy, cov3D, s_view, c2);
+  const float4 dcon = reinterpret_cast<const float4*>(dL_dconic)[idx];
+  const float dLc_x = dcon.x, dLc_y = dcon.y, dLc_z = dcon.w;
+  const float x_grad_mul = (c2.txtz < -c2.limx || c2.txtz > c2.limx) ? 0.f : 1.f;
+  const float y_grad_mul = (c2.tytz < -c2.limy || c2.tytz > c2.limy) ? 0.f : 1.f;
+  const Mat3& T = c2.T;
+  const Mat3& Vrk = c2.Vrk;
+  const Mat3& Wm = c2.W;
+  const float a = c2.a, b = c2.b, c = c2.c;
+  const float denom = a * c - b * b;
+  float dL_da = 0, dL_db = 0, dL_dc = 0;
+  const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+  float dcov[6] = {0, 0, 0, 0, 0, 0};
+  if (denom2inv != 0) {
+    dL_da = denom2inv * (-c * c * dLc_x + 2 * b * c * dLc_y + (denom - a * c) * dLc_z);
+    dL_dc = denom2inv * (-a * a * dLc_z + 2 * a * b * dLc_y + (denom - a * c) * dLc_x);
+    dL_db = denom2inv * 2 * (b * c * dLc_x - (denom + 2 * b * b) * dLc_y + a * b * dLc_z);
+    dcov[0] = (T.m[0][0] * T.m[0][0] * dL_da + T.m[0][0] * T.m[1][0] * dL_db + T.m[1][0] * T.m[1][0] * dL_dc);
+    dcov[3] = (T.m[0][1] * T.m[0][1] * dL_da + T.m[0][1] * T.m[1][1] * dL_db + T.m[1][1] * T.m[1][1] * dL_dc);
+    dcov[5] = (T.m[0][2] * T.m[0][2] * dL_da + T.m[0][2] * T.m[1][2] * dL_db + T.m[1][2] * T.m[1][2] * dL_dc);
+    dcov[1] = 2 * T.m[0][0] * T.m[0][1] * dL_da + (T.m[0][0] * T.m[1][1] + T.m[0][1] * T.m[1][0]) * dL_db +
+              2 * T.m[1][0] * T.m[1][1] * dL_dc;
+    dcov[2] = 2 * T.m[0][0] * T.m[0][2] * dL_da + (T.m[0][0] * T.m[1][2] + T.m[0][2] * T.m[1][0]) * dL_db +
+              2 * T.m[1][0] * T.m[1][2] * dL_dc;
+    dcov[4] = 2 * T.m[0][2] * T.m[0][1] * dL_da + (T.m[0][1] * T.m[1][2] + T.m[0][2] * T.m[1][1]) * dL_db +
+              2 * T.m[1][1] * T.m[1][2] * dL_dc;
+  }
+  if (dL_dcov3D) {
+#pragma unroll
+    for (int i = 0; i < 6; i++) dL_dcov3D[6 * (size_t)idx + i] = dcov[i];
+  }
+  auto row = [&](int r, int k) { return T.m[r][0] * Vrk.m[k][0] + T.m[r][1] * Vrk.m[k][1] + T.m[r][2] * Vrk.m[k][2]; };
+  const float dL_dT00 = 2 * row(0, 0) * dL_da + row(1, 0) * dL_db;
+  const float dL_dT01 = 2 * row(0, 1) * dL_da + row(1, 1) * dL_db;
+  const float dL_dT02 = 2 * row(0, 2) * dL_da + row(1, 2) * dL_db;
+  const float dL_dT10 = 2 * row(1, 0) * dL_dc + row(0, 0) * dL_db;
+  const float dL_dT11 = 2 * row(1, 1) * dL_dc + row(0, 1) * dL_db;
+  const float dL_dT12 = 2 * row(1, 2) * dL_dc + row(0, 2) * dL_db;
+  const float dL_dJ00 = Wm.m[0][0] * dL_dT00 + Wm.m[0][1] * dL_dT01 + Wm.m[0][2] * dL_dT02;
+  const float dL_dJ02 = Wm.m[2][0] * dL_dT00 + Wm.m[2][1] * dL_dT01 + Wm.m[2][2] * dL_dT02;
+  const float dL_dJ11 = Wm.m[1][0] * dL_dT10 + Wm.m[1][1] * dL_dT11 + Wm.m[1][2] * dL_dT12;
+  const float dL_dJ12 = Wm.m[2][0] * dL_dT10 + Wm.m[2][1] * dL_dT11 + Wm.m[2][2] * dL_dT12;
+  const float tz = 1.f / c2.tz, tz2 = tz * tz, tz3 = tz2 * tz;
+  const float dL_dtx = x_grad_mul * -h_x * tz2 * dL_dJ02;
+  const float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
+  const float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * c2.tx) * tz3 * dL_dJ02 +
+                       (2 * h_y * c2.ty) * tz3 * dL_dJ12;
+  float3 dmean;  // transformVec4x3Transpose
+  dmean.x = s_view[0] * dL_dtx + s_view[1] * dL_dty + s_view[2] * dL_dtz;
+  dmean.y = s_view[4] * dL_dtx + s_view[5] * dL_dty + s_view[6] * dL_dtz;
+  dmean.z = s_view[8] * dL_dtx + s_view[9] * dL_dty + s_view[10] * dL_dtz;
+
+  // ---------------- preprocessCUDA backward (backward.cu:346-396) ----------------
+  {
+    const float* proj = s_proj;
+    const float m_hw = proj[3] * mx + proj[7] * my + proj[11] * mz + proj[15];
+    const float m_w = 1.0f / (m_hw + 0.0000001f);
+    const float mul1 = (proj[0] * mx + proj[4] * my + proj[8] * mz + proj[12]) * m_w * m_w;
+    const float mul2 = (proj[1] * mx + proj[5] * my + proj[9] * mz + proj[13]) * m_w * m_w;
+    const float gx_ = dL_dmean2D[3 * (size_t)idx], gy_ = dL_dmean2D[3 * (size_t)idx + 1];
+    dmean.x += (proj[0] * m_w - proj[3] * mul1) * gx_ + (proj[1] * m_w - proj[3] * mul2) * gy_;
+    dmean.y += (proj[4] * m_w - proj[7] * mul1) * gx_ + (proj[5] * m_w - proj[7] * mul2) * gy_;
+    dmean.z += (proj[8] * m_w - proj[11] * mul1) * gx_ + (proj[9] * m_w - proj[11] * mul2) * gy_;
+  }
+  if (shs != nullptr && dL_dsh != nullptr && dL_dcolor != nullptr) {
+    const uint8_t cl = clamped[idx];
+    float3 g;
+    g.x = (cl & 1) ? 0.f : dL_dcolor[3 * (size_t)idx];
+    g.y = (cl & 2) ? 0.f : dL_dcolor[3 * (size_t)idx + 1];
+    g.z = (cl & 4) ? 0.f : dL_dcolor[3 * (size_t)idx + 2];
+    const float3 dir = make_float3(mx - s_cam[0], my - s_cam[1], mz - s_cam[2]);
+    const float3 dm = sh_backward(D, M, shs + (size_t)idx * M * 3, dir, g, dL_dsh + (size_t)idx * M * 3);
+    dmean.x += dm.x; dmean.y += dm.y; dmean.z += dm.z;
+  }
+  if (dL_dmean3D) {
+    dL_dmean3D[3 * (size_t)idx] = dmean.x;
+    dL_dmean3D[3 * (size_t)idx + 1] = dmean.y;
+    dL_dmean3D[3 * (size_t)idx + 2] = dmean.z;
+  }
+  if (scales != nullptr && dL_dscale != nullptr) {  // computeCov3D backward (backward.cu:278-341)
+    const float4 q = reinterpret_cast<const float4*>(rotations)[idx];
+    const float r = q.x, x = q.y, y = q.z, z = q.w;
+    const Mat3 R = quat_to_mat(r, x, y, z);
+    const float s[3] = {scale_modifier * scales[3 * (size_t)idx], scale_modifier * scales[3 * (size_t)idx + 1],
+                        scale_modifier * scales[3 * (size_t)idx + 2]};
+    Mat3 M2, dSig;
+#pragma unroll
+    for (int cc = 0; cc < 3; cc++)
+#pragma unroll
+      for (int rr = 0; rr < 3; rr++) M2.m[cc][rr] = 2.0f * (s[rr] * R.m[cc][rr]);
+    dSig.m[0][0] = dcov[0]; dSig.m[0][1] = 0.5f * dcov[1]; dSig.m[0][2] = 0.5f * dcov[2];
+    dSig.m[1][0] = 0.5f * dcov[1]; dSig.m[1][1] = dcov[3]; dSig.m[1][2] = 0.5f * dcov[4];
+    dSig.m[2][0] = 0.5f * dcov[2]; dSig.m[2][1] = 0.5f * dcov[4]; dSig.m[2][2] = dcov[5];
+    const Mat3 dL_dM = mat3_mul(M2, dSig);
+    const Mat3 Rt = mat3_transpose(R);
+    Mat3 dMt = mat3_transpose(dL_dM);
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+      dL_dscale[3 * (size_t)idx + k] = Rt.m[k][0] * dMt.m[k][0] + Rt.m[k][1] * dMt.m[k][1] + Rt.m[k][2] * dMt.m[k][2];
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+#pragma unroll
+      for (int rr = 0; rr < 3; rr++) dMt.m[k][rr] *= s[k];
+    float4 dq;
+    dq.x = 2 * z * (dMt.m[0][1] - dMt.m[1][0]) + 2 * y * (dMt.m[2][0] - dMt.m[0][2]) + 2 * x * (dMt.m[1][2] - dMt.m[2][1]);
+    dq.y = 2 * y * (dMt.m[1][0] + dMt.m[0][1]) + 2 * z * (dMt.m[2][0] + dMt.m[0][2]) + 2 * r * (dMt.m[1][2] - dMt.m[2][1]) -
+           4 * x * (dMt.m[2][2] + dMt.m[1][1]);
+    dq.z = 2 * x * (dMt.m[1][0] + dMt.m[0][1]) + 2 * r * (dMt.m[2][0] - dMt.m[0][2]) + 2 * z * (dMt.m[1][2] + dMt.m[2][1]) -
+           4 * y * (dMt.m[2][2] + dMt.m[0][0]);
+    dq.w = 2 * r * (dMt.m[0][1] - dMt.m[1][0]) + 2 * x * (dMt.m[2][0] + dMt.m[0][2]) + 2 * y * (dMt.m[1][2] + dMt.m[2][1]) -
+           4 * z * (dMt.m[1][1] + dMt.m[0][0]);
+    reinterpret_cast<float4*>(dL_drot)[idx] = dq;
+  }
+}
+
+}  // namespace
+
+void launch_preprocess_bwd(const lsr_frame& f, const lsr_inputs& in, float focal_x, float focal_y,
+                           const int32_t* radii, GeomView g, uint32_t need_mask, const lsr_grads& gr, cudaStream_t s) {
+  if (f.P <= 0) return;
+  (void)need_mask;
+  const float* cov3Ds = in.cov3D_precomp ? in.cov3D_precomp : g.cov3D;
+  preprocess_bwd_kernel<<<(f.P + 255) / 256, 256, 0, s>>>(
+      f.P, f.D, f.M, in.means3D, radii, in.shs, g.clamped, in.scales, in.rotations, f.scale_modifier, cov3Ds,
+      f.viewmatrix, f.projmatrix, focal_x, focal_y, f.tanfovx, f.tanfovy, f.campos, gr.dL_dmeans2D, gr.dL_dconic,
+      gr.dL_dcolors, gr.dL_dmeans3D, gr.dL_dcov3D, gr.dL_dsh, gr.dL_dscales, gr.dL_drotations);
+  count_launch();
+}
+
+}  // namespace lsr

@@ -1,0 +1,202 @@
+// preprocess_fwd.cu — K1': per-Gaussian cull, cov3D, EWA cov2D, conic, radius, tile rect, SH colour.
+// Replaces FORWARD::preprocess / preprocessCUDA (RAST/cuda_rasterizer/forward.cu:156-257) and in_frustum
+// (RAST/cuda_rasterizer/auxiliary.h:139-164).  HBM-bound: algorithmic bytes 20*P + 291*V.
+//
+// Layout choices (B200): inputs are the API's AoS tensors; a CTA of 256 threads stages its 256 xyz / scale
+// triplets through shared memory with fully coalesced 128-bit loads, reads quaternions as float4, and pulls each
+// visible Gaussian's 192-byte SH row with 12 x LDG.128.  All per-instance data the blend kernels need is written
+// as one 48-byte GeomRec.
+#include "common.cuh"
+#include "gs_math.cuh"
+
+namespace lsr {
+
+namespace {
+
+constexpr int PRE_THREADS = 256;
+
+__device__ __forceinline__ float3 sh_to_rgb(int deg, const float* __restrict__ sh, float x, float y, float z,
+                                            int stride /*floats between coefficients = 3*/) {
+  // RAST/cuda_rasterizer/forward.cu:21-72
+  float3 res;
+  float* rp = &res.x;
+#pragma unroll
+  for (int ch = 0; ch < 3; ch++) {
+    const float* s = sh + ch;
+    float v = LSR_SH_C0 * s[0];
+    if (deg > 0) {
+      v = v - LSR_SH_C1 * y * s[1 * stride] + LSR_SH_C1 * z * s[2 * stride] - LSR_SH_C1 * x * s[3 * stride];
+      if (deg > 1) {
+        const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+        v = v + LSR_SH_C2_0 * xy * s[4 * stride] + LSR_SH_C2_1 * yz * s[5 * stride] +
+            LSR_SH_C2_2 * (2.0f * zz - xx - yy) * s[6 * stride] + LSR_SH_C2_3 * xz * s[7 * stride] +
+            LSR_SH_C2_4 * (xx - yy) * s[8 * stride];
+        if (deg > 2) {
+          v = v + LSR_SH_C3_0 * y * (3.0f * xx - yy) * s[9 * stride] + LSR_SH_C3_1 * xy * z * s[10 * stride] +
+              LSR_SH_C3_2 * y * (4.0f * zz - xx - yy) * s[11 * stride] +
+              LSR_SH_C3_3 * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * s[12 * stride] +
+              LSR_SH_C3_4 * x * (4.0f * zz - xx - yy) * s[13 * stride] + LSR_SH_C3_5 * z * (xx - yy) * s[14 * stride] +
+              LSR_SH_C3_6 * x * (xx - 3.0f * yy) * s[15 * stride];
+        }
+      }
+    }
+    rp[ch] = v + 0.5f;
+  }
+  return res;
+}
+
+// Cooperative, coalesced load of `count` consecutive float triplets starting at element `first` into smem.
+__device__ __forceinline__ void stage_triplets(const float* __restrict__ src, float* dst, int first, int count,
+                                               int tid) {
+  const float* base = src + (size_t)first * 3;
+  const int n = count * 3;
+  // base is 16-B aligned whenever first % 4 == 0 (first = blockIdx * 256) and src is 16-B aligned.
+  if ((((uintptr_t)base) & 15) == 0) {
+    const int n4 = n >> 2;
+    for (int i = tid; i < n4; i += PRE_THREADS) {
+      float4 v = __ldg(reinterpret_cast<const float4*>(base) + i);
+      reinterpret_cast<float4*>(dst)[i] = v;
+    }
+    for (int i = (n4 << 2) + tid; i < n; i += PRE_THREADS) dst[i] = __ldg(base + i);
+  } else {
+    for (int i = tid; i < n; i += PRE_THREADS) dst[i] = __ldg(base + i);
+  }
+}
+
+__global__ void __launch_bounds__(PRE_THREADS)
+preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, const float* __restrict__ scales,
+                      float scale_modifier, const float* __restrict__ rotations, const float* __restrict__ opacities,
+                      const float* __restrict__ shs, const float* __restrict__ cov3D_precomp,
+                      const float* __restrict__ colors_precomp, const float* __restrict__ lang,
+                      const float* __restrict__ viewmatrix, const float* __restrict__ projmatrix,
+                      const float* __restrict__ campos, int W, int H, float tan_fovx, float tan_fovy, float focal_x,
+                      float focal_y, int gx, int gy, int prefiltered, int32_t* __restrict__ radii, GeomRec* __restrict__ rec,
+                      float* __restrict__ depths, uint32_t* __restrict__ tiles_touched, float* __restrict__ cov3Ds,
+                      uint8_t* __restrict__ clamped, uint32_t* __restrict__ ctrl) {
+  __shared__ __align__(16) float s_xyz[PRE_THREADS * 3];
+  __shared__ __align__(16) float s_scl[PRE_THREADS * 3];
+  __shared__ float s_view[16], s_proj[16], s_cam[3];
+  const int tid = threadIdx.x;
+  const int first = blockIdx.x * PRE_THREADS;
+  const int count = min(PRE_THREADS, P - first);
+  if (tid < 16) {
+    s_view[tid] = viewmatrix[tid];
+    s_proj[tid] = projmatrix[tid];
+  }
+  if (tid < 3) s_cam[tid] = campos[tid];
+  stage_triplets(means3D, s_xyz, first, count, tid);
+  if (scales) stage_triplets(scales, s_scl, first, count, tid);
+  __syncthreads();
+  if (tid >= count) return;
+  const int idx = first + tid;
+  const float mx = s_xyz[3 * tid], my = s_xyz[3 * tid + 1], mz = s_xyz[3 * tid + 2];
+
+  int radius_out = 0;
+  uint32_t tiles_out = 0;
+  do {
+    // in_frustum: the only cull is p_view.z <= 0.2 (auxiliary.h:152-154)
+    const float viewz = tp_row(s_view, 2, mx, my, mz);
+    if (viewz <= 0.2f) {
+      if (prefiltered) atomicOr(&ctrl[CTRL_ERROR], 1u);
+      break;
+    }
+    const float hx = tp_row(s_proj, 0, mx, my, mz);
+    const float hy = tp_row(s_proj, 1, mx, my, mz);
+    const float hw = tp_row(s_proj, 3, mx, my, mz);
+    const float p_w = __fdiv_rn(1.0f, __fadd_rn(hw, 0.0000001f));
+    const float projx = __fmul_rn(hx, p_w), projy = __fmul_rn(hy, p_w);
+
+    float cov3D[6];
+    if (cov3D_precomp) {
+#pragma unroll
+      for (int i = 0; i < 6; i++) cov3D[i] = __ldg(cov3D_precomp + (size_t)idx * 6 + i);
+    } else {
+      const float4 q = __ldg(reinterpret_cast<const float4*>(rotations) + idx);
+      compute_cov3D(s_scl[3 * tid], s_scl[3 * tid + 1], s_scl[3 * tid + 2], scale_modifier, q.x, q.y, q.z, q.w,
+                    cov3D);
+      float2* dst = reinterpret_cast<float2*>(cov3Ds + (size_t)idx * 6);
+      dst[0] = make_float2(cov3D[0], cov3D[1]);
+      dst[1] = make_float2(cov3D[2], cov3D[3]);
+      dst[2] = make_float2(cov3D[4], cov3D[5]);
+    }
+    Cov2D c2;
+    compute_cov2D(mx, my, mz, focal_x, focal_y, tan_fovx, tan_fovy, cov3D, s_view, c2);
+    const float det = __fmaf_rn(c2.a, c2.c, -__fmul_rn(c2.b, c2.b));
+    if (det == 0.0f) break;
+    const float det_inv = __fdiv_rn(1.f, det);
+    const float conx = __fmul_rn(c2.c, det_inv), cony = __fmul_rn(-c2.b, det_inv), conz = __fmul_rn(c2.a, det_inv);
+    const float mid = __fmul_rn(0.5f, __fadd_rn(c2.a, c2.c));
+    const float sq = __fsqrt_rn(fmaxf(0.1f, __fmaf_rn(mid, mid, -det)));
+    const float lambda1 = __fadd_rn(mid, sq), lambda2 = __fadd_rn(mid, -sq);
+    const int my_radius = __float2int_rz(ceilf(__fmul_rn(3.f, __fsqrt_rn(fmaxf(lambda1, lambda2)))));
+    const float px = ndc2pix(projx, W), py = ndc2pix(projy, H);
+    uint32_t x0, y0, x1, y1;
+    get_rect(px, py, my_radius, gx, gy, x0, y0, x1, y1);
+    const uint32_t nt = (x1 - x0) * (y1 - y0);
+    if (nt == 0) break;
+
+    float3 col;
+    uint8_t clamp_bits = 0;
+    if (colors_precomp == nullptr) {
+      float dx = mx - s_cam[0], dy = my - s_cam[1], dz = mz - s_cam[2];
+      const float len = sqrtf(dx * dx + dy * dy + dz * dz);
+      dx = dx / len; dy = dy / len; dz = dz / len;
+      const float* sh = shs + (size_t)idx * M * 3;
+      col = sh_to_rgb(D, sh, dx, dy, dz, 3);
+      clamp_bits = (col.x < 0.f ? 1 : 0) | (col.y < 0.f ? 2 : 0) | (col.z < 0.f ? 4 : 0);
+      col.x = fmaxf(col.x, 0.f); col.y = fmaxf(col.y, 0.f); col.z = fmaxf(col.z, 0.f);
+    } else {
+      col.x = __ldg(colors_precomp + (size_t)idx * 3);
+      col.y = __ldg(colors_precomp + (size_t)idx * 3 + 1);
+      col.z = __ldg(colors_precomp + (size_t)idx * 3 + 2);
+    }
+    float f0 = 0.f, f1 = 0.f, f2 = 0.f;
+    if (lang) {
+      f0 = __ldg(lang + (size_t)idx * 3);
+      f1 = __ldg(lang + (size_t)idx * 3 + 1);
+      f2 = __ldg(lang + (size_t)idx * 3 + 2);
+    }
+    float4* r4 = reinterpret_cast<float4*>(rec + idx);
+    r4[0] = make_float4(px, py, conx, cony);
+    r4[1] = make_float4(conz, __ldg(opacities + idx), col.x, col.y);
+    r4[2] = make_float4(col.z, f0, f1, f2);
+    depths[idx] = viewz;
+    clamped[idx] = clamp_bits;
+    radius_out = my_radius;
+    tiles_out = nt;
+  } while (0);
+  radii[idx] = radius_out;
+  tiles_touched[idx] = tiles_out;
+}
+
+__global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ viewmatrix,
+                                    uint8_t* __restrict__ present) {
+  // checkFrustum, RAST/cuda_rasterizer/rasterizer_impl.cu:54-66: present = p_view.z > 0.2
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P) return;
+  const float x = means3D[3 * (size_t)idx], y = means3D[3 * (size_t)idx + 1], z = means3D[3 * (size_t)idx + 2];
+  present[idx] = tp_row(viewmatrix, 2, x, y, z) > 0.2f ? 1 : 0;
+}
+
+}  // namespace
+
+void launch_preprocess_fwd(const lsr_frame& f, const lsr_inputs& in, float focal_x, float focal_y, int32_t* radii,
+                           GeomView g, uint32_t* ctrl, cudaStream_t s) {
+  const int gx = (f.width + TILE_X - 1) / TILE_X, gy = (f.height + TILE_Y - 1) / TILE_Y;
+  const int blocks = (f.P + PRE_THREADS - 1) / PRE_THREADS;
+  if (blocks == 0) return;
+  preprocess_fwd_kernel<<<blocks, PRE_THREADS, 0, s>>>(
+      f.P, f.D, f.M, in.means3D, in.scales, f.scale_modifier, in.rotations, in.opacities, in.shs, in.cov3D_precomp,
+      in.colors_precomp, f.include_feature ? in.language_feature : nullptr, f.viewmatrix, f.projmatrix, f.campos,
+      f.width, f.height, f.tanfovx, f.tanfovy, focal_x, focal_y, gx, gy, f.prefiltered, radii, g.rec, g.depth,
+      g.tiles, g.cov3D, g.clamped, ctrl);
+  count_launch();
+}
+
+void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, uint8_t* present, cudaStream_t s) {
+  if (P <= 0) return;
+  mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means3D, viewmatrix, present);
+  count_launch();
+}
+
+}  // namespace lsr

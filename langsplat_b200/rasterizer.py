@@ -1,0 +1,345 @@
+"""Host-side mirror of the reference's `diff_gaussian_rasterization` module over the liblsr.so C ABI.
+
+Same names, argument meaning and error behaviour as
+submodules/langsplat-rasterization/diff_gaussian_rasterization/__init__.py (RAST/...):
+`GaussianRasterizationSettings` (:166-179), `GaussianRasterizer` (:181-233), `rasterize_gaussians` (:21-44) and the
+autograd function (:46-164).  PyTorch is used for device memory, streams and autograd plumbing only; every kernel
+lives in liblsr.so.  There is no CPU path: tensors must be CUDA float32.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict, NamedTuple, Optional, Tuple
+
+import torch
+import torch.nn as nn
+
+from . import _lib as L
+
+
+class GaussianRasterizationSettings(NamedTuple):  # RAST/diff_gaussian_rasterization/__init__.py:166-179
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+    debug: bool
+    include_feature: bool
+
+
+def cpu_deep_copy_tuple(input_tuple):  # RAST/diff_gaussian_rasterization/__init__.py:17-19
+    return tuple(item.cpu().clone() if isinstance(item, torch.Tensor) else item for item in input_tuple)
+
+
+class LsrError(RuntimeError):
+    pass
+
+
+_MSG_COLORS = "Please provide excatly one of either SHs or precomputed colors!"
+_MSG_COV = "Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!"
+
+# Per (device, stream) transient workspace and the last instance count, used as the next capacity guess.
+_scratch: Dict[Tuple[int, int], torch.Tensor] = {}
+_last_R: Dict[int, int] = {}
+
+
+def _present(t: Optional[torch.Tensor]) -> bool:
+    return t is not None and t.numel() != 0
+
+
+def _prep(t: Optional[torch.Tensor], device) -> Optional[torch.Tensor]:
+    """`.contiguous()` as rasterize_points.cu:103-122 does (required: Camera.world_view_transform is a transposed
+    view, scene/cameras.py:54); absent -> None."""
+    if not _present(t):
+        return None
+    if t.device != device or t.dtype != torch.float32:
+        t = t.to(device=device, dtype=torch.float32)
+    return t.contiguous()
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _make_frame(rs: GaussianRasterizationSettings, P: int, M: int, bg, view, proj, campos) -> L.Frame:
+    f = L.Frame()
+    f.P, f.M, f.D = P, M, int(rs.sh_degree)
+    f.width, f.height = int(rs.image_width), int(rs.image_height)
+    f.tanfovx, f.tanfovy, f.scale_modifier = float(rs.tanfovx), float(rs.tanfovy), float(rs.scale_modifier)
+    f.prefiltered, f.debug, f.include_feature = int(bool(rs.prefiltered)), int(bool(rs.debug)), int(
+        bool(rs.include_feature))
+    f.bg, f.viewmatrix, f.projmatrix, f.campos = bg.data_ptr(), view.data_ptr(), proj.data_ptr(), campos.data_ptr()
+    return f
+
+
+def _make_inputs(means3D, sh, colors, lang, opac, scales, rots, cov3D) -> L.Inputs:
+    i = L.Inputs()
+    for name, t in (("means3D", means3D), ("shs", sh), ("colors_precomp", colors), ("language_feature", lang),
+                    ("opacities", opac), ("scales", scales), ("rotations", rots), ("cov3D_precomp", cov3D)):
+        setattr(i, name, None if t is None else t.data_ptr())
+    return i
+
+
+def _get_scratch(device, stream_ptr: int, nbytes: int) -> torch.Tensor:
+    key = (device.index if device.index is not None else torch.cuda.current_device(), stream_ptr)
+    buf = _scratch.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(int(nbytes * 1.25) + 1024, dtype=torch.uint8, device=device)
+        _scratch[key] = buf
+    return buf
+
+
+def _check(rc: int, what: str):
+    if rc != L.LSR_OK:
+        raise LsrError(f"{what}: {L.last_error()} (status {rc})")
+
+
+def _forward_impl(rs: GaussianRasterizationSettings, means3D, sh, colors, lang, opac, scales, rots, cov3D,
+                  keep_scratch: bool = False):
+    """Runs lsr_forward.  Returns (color, feature, radii, state) where state holds what backward needs."""
+    lib = L.load()
+    if means3D.dim() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")  # rasterize_points.cu:59-61
+    if not means3D.is_cuda:
+        raise LsrError("langsplat_b200 has no CPU path: means3D must be a CUDA tensor")
+    device = means3D.device
+    P = means3D.size(0)
+    H, W = int(rs.image_height), int(rs.image_width)
+    means3D = _prep(means3D, device)
+    sh, colors, opac = _prep(sh, device), _prep(colors, device), _prep(opac, device)
+    scales, rots, cov3D = _prep(scales, device), _prep(rots, device), _prep(cov3D, device)
+    include_feature = bool(rs.include_feature)
+    lang = _prep(lang, device) if include_feature else None
+    bg, view, proj, campos = (_prep(rs.bg, device), _prep(rs.viewmatrix, device), _prep(rs.projmatrix, device),
+                              _prep(rs.campos, device))
+    M = sh.size(1) if sh is not None else 0
+    frame = _make_frame(rs, P, M, bg, view, proj, campos)
+    inputs = _make_inputs(means3D, sh, colors, lang, opac, scales, rots, cov3D)
+
+    color = torch.empty((3, H, W), dtype=torch.float32, device=device)
+    feature = (torch.empty((3, H, W), dtype=torch.float32, device=device) if include_feature else torch.zeros(
+        (1,), dtype=torch.float32, device=device))
+    radii = torch.empty((P,), dtype=torch.int32, device=device)
+    geom = torch.empty((lib.lsr_geom_bytes(P),), dtype=torch.uint8, device=device)
+    image = torch.empty((lib.lsr_image_bytes(W, H),), dtype=torch.uint8, device=device)
+    stream = torch.cuda.current_stream(device).cuda_stream
+    dev_idx = device.index if device.index is not None else torch.cuda.current_device()
+    capacity = max(int(_last_R.get(dev_idx, 0) * 1.25), 4 * P, 1 << 16)
+    nr = ctypes.c_int64(0)
+    with torch.cuda.device(device):
+        while True:
+            point_list = torch.empty((lib.lsr_list_bytes(capacity),), dtype=torch.uint8, device=device)
+            need = lib.lsr_scratch_bytes(P, W, H, capacity)
+            scratch = (torch.empty((need,), dtype=torch.uint8, device=device) if keep_scratch else _get_scratch(
+                device, stream, need))
+            rc = lib.lsr_forward(ctypes.byref(frame), ctypes.byref(inputs), _ptr(color), _ptr(feature), _ptr(radii),
+                                 _ptr(geom), _ptr(image), _ptr(point_list), capacity, _ptr(scratch), scratch.numel(),
+                                 ctypes.byref(nr), ctypes.c_void_p(stream))
+            if rc == L.LSR_ERR_CAPACITY:
+                capacity = int(nr.value * 1.1) + 1024
+                continue
+            break
+    _check(rc, "lsr_forward")
+    _last_R[dev_idx] = int(nr.value)
+    state = dict(frame=frame, inputs=inputs, geom=geom, image=image, point_list=point_list, num_rendered=int(nr.value),
+                 capacity=capacity, keep=(means3D, sh, colors, lang, opac, scales, rots, cov3D, bg, view, proj, campos),
+                 radii=radii, P=P, M=M, W=W, H=H, device=device)
+    if keep_scratch:
+        state["scratch"] = scratch
+    return color, feature, radii, state
+
+
+def _backward_impl(state, grad_color, grad_feature, need_mask: int, want_sh: bool):
+    lib = L.load()
+    P, M, W, H, device = state["P"], state["M"], state["W"], state["H"], state["device"]
+    (means3D, sh, colors, lang, opac, scales, rots, cov3D, *_rest) = state["keep"]
+    f32 = dict(dtype=torch.float32, device=device)
+    include_feature = bool(state["frame"].include_feature)
+    gc = grad_color.contiguous() if grad_color is not None else None
+    gf = grad_feature.contiguous() if (grad_feature is not None and include_feature) else None
+    # accumulators packed into one buffer so the library zero-fills them with a single memset
+    acc = torch.empty((14 * P,), **f32)
+    d_conic = acc[0:4 * P].view(P, 4)
+    d_means2D = acc[4 * P:7 * P].view(P, 3)
+    d_opac = acc[7 * P:8 * P].view(P, 1)
+    d_colors = acc[8 * P:11 * P].view(P, 3)
+    d_feat = acc[11 * P:14 * P].view(P, 3)
+    geom_need = bool(need_mask & L.NEED_GEOMETRY)
+    run_pre = geom_need or (sh is not None and want_sh and gc is not None)
+    g = L.Grads()
+    g.dL_dmeans2D, g.dL_dconic, g.dL_dopacity = d_means2D.data_ptr(), d_conic.data_ptr(), d_opac.data_ptr()
+    g.dL_dcolors, g.dL_dlanguage_feature = d_colors.data_ptr(), d_feat.data_ptr()
+    d_means3D = d_cov3D = d_sh = d_scales = d_rots = None
+    if run_pre:
+        d_means3D = torch.empty((P, 3), **f32)
+        d_cov3D = torch.empty((P, 6), **f32)
+        g.dL_dmeans3D, g.dL_dcov3D = d_means3D.data_ptr(), d_cov3D.data_ptr()
+        if sh is not None:
+            d_sh = torch.empty((P, M, 3), **f32)
+            g.dL_dsh = d_sh.data_ptr()
+        d_scales = torch.empty((P, 3), **f32)
+        d_rots = torch.empty((P, 4), **f32)
+        g.dL_dscales, g.dL_drotations = d_scales.data_ptr(), d_rots.data_ptr()
+    stream = torch.cuda.current_stream(device).cuda_stream
+    with torch.cuda.device(device):
+        rc = lib.lsr_backward(ctypes.byref(state["frame"]), ctypes.byref(state["inputs"]), _ptr(state["radii"]),
+                              _ptr(state["geom"]), _ptr(state["image"]), _ptr(state["point_list"]), _ptr(gc), _ptr(gf),
+                              need_mask | (L.NEED_GEOMETRY if run_pre else 0), ctypes.byref(g),
+                              ctypes.c_void_p(stream))
+    _check(rc, "lsr_backward")
+    return dict(means3D=d_means3D, means2D=d_means2D, sh=d_sh, colors=d_colors, language_feature=d_feat,
+                opacities=d_opac, scales=d_scales, rotations=d_rots, cov3D=d_cov3D, conic=d_conic)
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, language_feature_precomp, opacities, scales, rotations,
+                cov3Ds_precomp, raster_settings):
+        args = (means3D, sh, colors_precomp, language_feature_precomp, opacities, scales, rotations, cov3Ds_precomp)
+        if raster_settings.debug:  # RAST/diff_gaussian_rasterization/__init__.py:87-95
+            cpu_args = cpu_deep_copy_tuple((raster_settings.bg,) + args + tuple(raster_settings))
+            try:
+                color, feature, radii, state = _forward_impl(raster_settings, *args)
+            except Exception as ex:
+                torch.save(cpu_args, "snapshot_fw.dump")
+                print("\nAn error occured in forward. Please forward snapshot_fw.dump for debugging.")
+                raise ex
+        else:
+            color, feature, radii, state = _forward_impl(raster_settings, *args)
+        ctx.raster_settings = raster_settings
+        ctx.num_rendered = state["num_rendered"]
+        ctx.state = state
+        ctx.set_materialize_grads(False)
+        ctx.mark_non_differentiable(radii)
+        return color, feature, radii
+
+    @staticmethod
+    def backward(ctx, grad_out_color, grad_out_language_feature, _):
+        state = ctx.state
+        need = ctx.needs_input_grad  # (means3D, means2D, sh, colors, lang, opac, scales, rots, cov3D, settings)
+        mask = 0
+        if need[0] or need[5] or need[6] or need[7] or need[8]:
+            mask |= L.NEED_GEOMETRY
+        if need[2] or need[3]:
+            mask |= L.NEED_COLOR
+        if need[4]:
+            mask |= L.NEED_FEATURE
+        if need[1]:
+            mask |= L.NEED_MEANS2D
+        include_feature = bool(ctx.raster_settings.include_feature)
+        if grad_out_color is None and (grad_out_language_feature is None or not include_feature):
+            return (None,) * 10
+        want_sh = bool(need[2] or need[0])
+        if ctx.raster_settings.debug:  # :139-147
+            try:
+                g = _backward_impl(state, grad_out_color, grad_out_language_feature, mask, want_sh)
+            except Exception as ex:
+                torch.save(cpu_deep_copy_tuple((grad_out_color, grad_out_language_feature)), "snapshot_bw.dump")
+                print("\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
+                raise ex
+        else:
+            g = _backward_impl(state, grad_out_color, grad_out_language_feature, mask, want_sh)
+        lang_grad = None
+        if need[4]:
+            lang_grad = g["language_feature"] if include_feature else torch.zeros(
+                (1,), dtype=torch.float32, device=state["device"])  # rasterize_points.cu:176-178
+        return (
+            g["means3D"] if need[0] else None,
+            g["means2D"] if need[1] else None,
+            g["sh"] if need[2] else None,
+            g["colors"] if need[3] else None,
+            lang_grad,
+            g["opacities"] if need[5] else None,
+            g["scales"] if need[6] else None,
+            g["rotations"] if need[7] else None,
+            g["cov3D"] if need[8] else None,
+            None,
+        )
+
+
+def rasterize_gaussians(means3D, means2D, sh, colors_precomp, language_feature_precomp, opacities, scales, rotations,
+                        cov3Ds_precomp, raster_settings):  # RAST/diff_gaussian_rasterization/__init__.py:21-44
+    return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, language_feature_precomp, opacities, scales,
+                                     rotations, cov3Ds_precomp, raster_settings)
+
+
+class GaussianRasterizer(nn.Module):  # RAST/diff_gaussian_rasterization/__init__.py:181-233
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions):
+        """Boolean mask of points passing the frustum test (p_view.z > 0.2), :186-195."""
+        with torch.no_grad():
+            rs = self.raster_settings
+            lib = L.load()
+            if not positions.is_cuda:
+                raise LsrError("langsplat_b200 has no CPU path: positions must be a CUDA tensor")
+            device = positions.device
+            pos = _prep(positions, device)
+            P = positions.size(0)
+            present = torch.zeros((P,), dtype=torch.bool, device=device)
+            if P:
+                view, proj = _prep(rs.viewmatrix, device), _prep(rs.projmatrix, device)
+                with torch.cuda.device(device):
+                    rc = lib.lsr_mark_visible(P, _ptr(pos), _ptr(view), _ptr(proj), _ptr(present),
+                                              ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream))
+                _check(rc, "lsr_mark_visible")
+        return present
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, language_feature_precomp=None,
+                scales=None, rotations=None, cov3D_precomp=None):
+        raster_settings = self.raster_settings
+        if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
+            raise Exception(_MSG_COLORS)
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or (
+                (scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception(_MSG_COV)
+        empty = torch.Tensor([])
+        shs = empty if shs is None else shs
+        colors_precomp = empty if colors_precomp is None else colors_precomp
+        language_feature_precomp = empty if language_feature_precomp is None else language_feature_precomp
+        scales = empty if scales is None else scales
+        rotations = empty if rotations is None else rotations
+        cov3D_precomp = empty if cov3D_precomp is None else cov3D_precomp
+        return rasterize_gaussians(means3D, means2D, shs, colors_precomp, language_feature_precomp, opacities, scales,
+                                   rotations, cov3D_precomp, raster_settings)
+
+
+# ---- test / bench helpers (not part of the reference surface) ----
+def debug_arrays(state) -> Dict[str, torch.Tensor]:
+    """Typed views of the arrays inside a forward's geom / image / scratch buffers (include/lsr_api.h LSR_ARR_*)."""
+    lib = L.load()
+    P, W, H, cap, R = state["P"], state["W"], state["H"], state["capacity"], state["num_rendered"]
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+
+    def view(buf, which, dtype, count):
+        off = lib.lsr_array_offset(which, P, W, H, cap)
+        nbytes = count * torch.empty((), dtype=dtype).element_size()
+        return buf[off:off + nbytes].view(dtype)
+
+    geom, image = state["geom"], state["image"]
+    out = dict(
+        rec=view(geom, L.ARR_GEOM_REC, torch.float32, P * 12).view(P, 12),
+        depths=view(geom, L.ARR_GEOM_DEPTH, torch.float32, P),
+        tiles_touched=view(geom, L.ARR_GEOM_TILES, torch.int32, P),
+        point_offsets=view(geom, L.ARR_GEOM_OFFSETS, torch.int32, P),
+        cov3D=view(geom, L.ARR_GEOM_COV3D, torch.float32, P * 6).view(P, 6),
+        clamped=view(geom, L.ARR_GEOM_CLAMPED, torch.uint8, P),
+        final_T=view(image, L.ARR_IMG_FINAL_T, torch.float32, W * H).view(H, W),
+        n_contrib=view(image, L.ARR_IMG_NCONTRIB, torch.int32, W * H).view(H, W),
+        ranges=view(image, L.ARR_IMG_RANGES, torch.int32, T * 2).view(T, 2),
+        point_list=state["point_list"][:R * 4].view(torch.int32),
+    )
+    if "scratch" in state:
+        sc = state["scratch"]
+        # (the unsorted keys are overwritten by the sort's ping-pong; the sorted keys are the same multiset)
+        out["values_unsorted"] = view(sc, L.ARR_SCR_VALS_UNSORTED, torch.int32, R)
+        out["keys"] = view(sc, L.ARR_SCR_KEYS_SORTED, torch.int64, R)
+    return out

@@ -1,0 +1,120 @@
+"""Shared helpers for the parity tests: run the same seeded scene through the CUDA path (via the public module,
+hence through the C ABI), the CPU oracle, and — on the GPU box — the unmodified reference extension in baseline/_ref."""
+from __future__ import annotations
+
+import importlib
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+from langsplat_b200 import synthetic as syn  # noqa: E402
+from langsplat_b200 import rasterizer as R  # noqa: E402
+from oracle import oracle as orc  # noqa: E402
+
+
+def settings_for(cam, device, include_feature=True, sh_degree=3, bg=(0.0, 0.0, 0.0), scale_modifier=1.0, debug=False,
+                 cls=R.GaussianRasterizationSettings):
+    return cls(image_height=cam.image_height, image_width=cam.image_width, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
+               bg=torch.tensor(bg, dtype=torch.float32, device=device), scale_modifier=scale_modifier,
+               viewmatrix=cam.viewmatrix.to(device), projmatrix=cam.projmatrix.to(device), sh_degree=sh_degree,
+               campos=cam.campos.to(device), prefiltered=False, debug=debug, include_feature=include_feature)
+
+
+def oracle_forward(scene, cam, include_feature=True, sh_degree=3, bg=(0.0, 0.0, 0.0), scale_modifier=1.0,
+                   colors_precomp=None, cov3D_precomp=None, dtype=np.float32):
+    return orc.forward(
+        scene["means3D"], scene["opacities"], cam.viewmatrix, cam.projmatrix, cam.campos, cam.image_width,
+        cam.image_height, cam.tanfovx, cam.tanfovy, np.asarray(bg), shs=None if colors_precomp is not None else scene["shs"],
+        colors_precomp=colors_precomp, language_feature=scene["language_feature"] if include_feature else None,
+        scales=None if cov3D_precomp is not None else scene["scales"],
+        rotations=None if cov3D_precomp is not None else scene["rotations"], cov3D_precomp=cov3D_precomp,
+        scale_modifier=scale_modifier, sh_degree=sh_degree, include_feature=include_feature, dtype=dtype)
+
+
+def cuda_forward_state(scene, cam, device="cuda", include_feature=True, sh_degree=3, bg=(0.0, 0.0, 0.0),
+                       scale_modifier=1.0, colors_precomp=None, cov3D_precomp=None):
+    """Forward through the product's internal entry (keeps the scratch so sorted keys can be inspected)."""
+    rs = settings_for(cam, device, include_feature, sh_degree, bg, scale_modifier)
+    d = {k: v.to(device) for k, v in scene.items()}
+    color, feat, radii, state = R._forward_impl(
+        rs, d["means3D"], None if colors_precomp is not None else d["shs"],
+        None if colors_precomp is None else colors_precomp.to(device), d["language_feature"], d["opacities"],
+        None if cov3D_precomp is not None else d["scales"], None if cov3D_precomp is not None else d["rotations"],
+        None if cov3D_precomp is None else cov3D_precomp.to(device), keep_scratch=True)
+    torch.cuda.synchronize()
+    return color, feat, radii, state
+
+
+def run_module(module_GR, module_GS, scene, cam, device="cuda", include_feature=True, sh_degree=3, bg=(0.0, 0.0, 0.0),
+               grads=None, requires=("means3D", "shs", "language_feature", "opacities", "scales", "rotations"),
+               scale_modifier=1.0, use_colors_precomp=None, use_cov3D_precomp=None):
+    """Forward (+ backward if grads=(dcol, dfeat)) through a GaussianRasterizer-shaped public API."""
+    rs = settings_for(cam, device, include_feature, sh_degree, bg, scale_modifier, cls=module_GS)
+    t = {k: v.to(device).clone().requires_grad_(k in requires) for k, v in scene.items()}
+    means2D = torch.zeros_like(t["means3D"], requires_grad=True)
+    colors_precomp = cov3D_precomp = None
+    if use_colors_precomp is not None:
+        colors_precomp = use_colors_precomp.to(device).clone().requires_grad_("colors_precomp" in requires)
+    if use_cov3D_precomp is not None:
+        cov3D_precomp = use_cov3D_precomp.to(device).clone().requires_grad_("cov3D_precomp" in requires)
+    rast = module_GR(raster_settings=rs)
+    lang = t["language_feature"] if include_feature else torch.zeros((1,), dtype=torch.float32, device=device)
+    color, feat, radii = rast(means3D=t["means3D"], means2D=means2D, shs=None if colors_precomp is not None else t["shs"],
+                              colors_precomp=colors_precomp, language_feature_precomp=lang, opacities=t["opacities"],
+                              scales=None if cov3D_precomp is not None else t["scales"],
+                              rotations=None if cov3D_precomp is not None else t["rotations"],
+                              cov3D_precomp=cov3D_precomp)
+    out = dict(color=color.detach(), feature=feat.detach(), radii=radii.detach())
+    if grads is not None:
+        dcol, dfeat = grads
+        loss = 0
+        if dcol is not None:
+            loss = loss + (color * dcol.to(device)).sum()
+        if dfeat is not None and include_feature:
+            loss = loss + (feat * dfeat.to(device)).sum()
+        loss.backward()
+        g = {k: (v.grad.detach() if v.grad is not None else None) for k, v in t.items()}
+        g["means2D"] = means2D.grad.detach() if means2D.grad is not None else None
+        if colors_precomp is not None:
+            g["colors_precomp"] = colors_precomp.grad
+        if cov3D_precomp is not None:
+            g["cov3D_precomp"] = cov3D_precomp.grad
+        out["grads"] = g
+    torch.cuda.synchronize()
+    return out
+
+
+def load_reference():
+    """The unmodified reference extension built into baseline/_ref; None if absent."""
+    ref_dir = os.path.join(ROOT, "baseline", "_ref")
+    if not os.path.isdir(os.path.join(ref_dir, "diff_gaussian_rasterization")):
+        return None
+    saved = sys.modules.pop("diff_gaussian_rasterization", None)
+    saved_c = sys.modules.pop("diff_gaussian_rasterization._C", None)
+    sys.path.insert(0, ref_dir)
+    try:
+        mod = importlib.import_module("diff_gaussian_rasterization")
+        assert os.path.realpath(mod.__file__).startswith(os.path.realpath(ref_dir)), mod.__file__
+    except Exception:
+        mod = None
+    finally:
+        sys.path.remove(ref_dir)
+        sys.modules.pop("diff_gaussian_rasterization", None)
+        sys.modules.pop("diff_gaussian_rasterization._C", None)
+        if saved is not None:
+            sys.modules["diff_gaussian_rasterization"] = saved
+        if saved_c is not None:
+            sys.modules["diff_gaussian_rasterization._C"] = saved_c
+    return mod
+
+
+def rel_err(a, b):
+    """max |a-b| / max |b| — the relative metric used for gradients (the reference sums with unordered atomics)."""
+    a = a.detach().double().cpu() if hasattr(a, "detach") else torch.as_tensor(a).double()
+    b = b.detach().double().cpu() if hasattr(b, "detach") else torch.as_tensor(b).double()
+    denom = b.abs().max().item()
+    return (a - b).abs().max().item() / (denom if denom > 0 else 1.0)
