@@ -1,0 +1,407 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the rasterizer hot path (BASELINE.json configs[1]):
+forward+backward frames/s at 1M Gaussians, 1080p, SH degree 3 colour + 3-channel language feature.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config 2]
+
+One JSON line on stdout (rank 0).  Contract notes:
+  * a "step" is one GaussianRasterizer.forward + backward through both outputs for one camera view; `value` is timed
+    with CUDA events, inputs and upstream gradients resident in HBM (the Gaussian tensors alone are ~250 MB > L2);
+  * `e2e` is the same step through the public module with HOST buffers for the step's inputs: the camera matrices and
+    the ground-truth colour / feature images are copied from pinned host memory every step, an L1 loss is formed, and
+    the scalar loss is read back (what train.py:84-104 does per iteration; Gaussian parameters are model state and
+    stay on the device, like weights);
+  * N > 1: one process per GPU, rank r renders view r of the same replicated scene (weak scaling) and the step ends
+    with a NCCL sum-allreduce of the Gaussian-parameter gradients (the path's one real exchange step);
+  * --impl reference times the UNMODIFIED reference CUDA extension from baseline/_ref through its own Python API on
+    the same workload (the reference has no CPU implementation of this path); if it is not built, the CPU oracle
+    (a port) is timed on a bounded sample instead.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+from langsplat_b200 import synthetic as syn  # noqa: E402
+
+METRIC = "fwd+bwd frames/s @1M Gaussians 1080p RGB+3-ch lang feature"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--config", type=int, default=2, help="BASELINE.json config (2 = headline)")
+    ap.add_argument("--P", type=int, default=None, help="override Gaussian count (tests)")
+    ap.add_argument("--width", type=int, default=None)
+    ap.add_argument("--height", type=int, default=None)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-frames", type=int, default=3)
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """Samples SM clocks and throttle reasons with nvidia-smi while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def init_dist(n_gpus: int):
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    else:
+        torch.cuda.set_device(0)
+        local = 0
+    return rank, world, torch.device("cuda", local)
+
+
+def load_impl(impl: str):
+    if impl == "ours":
+        from langsplat_b200 import GaussianRasterizationSettings, GaussianRasterizer
+        from langsplat_b200 import _lib
+        _lib.load()  # fail loudly if liblsr.so is missing
+        return GaussianRasterizer, GaussianRasterizationSettings, "langsplat_b200 (liblsr.so)"
+    ref_dir = os.path.join(ROOT, "baseline", "_ref")
+    if os.path.isdir(os.path.join(ref_dir, "diff_gaussian_rasterization")):
+        sys.path.insert(0, ref_dir)
+        sys.modules.pop("diff_gaussian_rasterization", None)
+        import diff_gaussian_rasterization as ref
+        assert os.path.realpath(ref.__file__).startswith(os.path.realpath(ref_dir)), ref.__file__
+        return ref.GaussianRasterizer, ref.GaussianRasterizationSettings, "reference CUDA extension (baseline/_ref)"
+    return None, None, None
+
+
+def settings(GS, cam, dev, include_feature=True):
+    return GS(image_height=cam.image_height, image_width=cam.image_width, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
+              bg=torch.zeros(3, device=dev), scale_modifier=1.0, viewmatrix=cam.viewmatrix.to(dev),
+              projmatrix=cam.projmatrix.to(dev), sh_degree=3, campos=cam.campos.to(dev), prefiltered=False,
+              debug=False, include_feature=include_feature)
+
+
+def barrier(world):
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def max_over_ranks(x: float, world: int, dev) -> float:
+    if world == 1:
+        return x
+    t = torch.tensor([x], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def cpu_oracle_frames(scene, cam, n_frames: int, budget_s: float = 25.0):
+    """Times the CPU oracle (forward+backward) on whole frames of the same workload; returns (fps, frames, stats)."""
+    from oracle import oracle as orc
+    dcol, dfeat = syn.make_grads(cam.image_width, cam.image_height, 2002)
+    done, t0, stats = 0, time.perf_counter(), {}
+    while done < n_frames and (done == 0 or time.perf_counter() - t0 < budget_s):
+        fw = orc.forward(scene["means3D"], scene["opacities"], cam.viewmatrix, cam.projmatrix, cam.campos,
+                         cam.image_width, cam.image_height, cam.tanfovx, cam.tanfovy, np.zeros(3), shs=scene["shs"],
+                         language_feature=scene["language_feature"], scales=scene["scales"],
+                         rotations=scene["rotations"])
+        orc.backward(fw, dcol, dfeat)
+        done += 1
+        stats = dict(V=int((fw["radii"] > 0).sum()), R=int(fw["num_rendered"]), K_exam=int(fw["k_exam"]),
+                     K_contrib=int(fw["k_contrib"]))
+    dt = time.perf_counter() - t0
+    return done / dt, done, stats, orc.num_threads()
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            j = json.load(open(p))
+            return float(j["hbm_gbs"]), float(j.get("sm_max_mhz", 1965.0)), "measured"
+        except Exception:
+            pass
+    return 6650.0, 1965.0, "fallback"
+
+
+def main():
+    args = parse_args()
+    rank, world, dev = init_dist(args.gpus)
+    GR, GS, impl_name = load_impl(args.impl)
+    scene, cams = syn.make_config(args.config, P=args.P, W=args.width, H=args.height, n_cameras=8)
+    cam = cams[rank % 8]
+    W, H = cam.image_width, cam.image_height
+    P = scene["means3D"].shape[0]
+    workload = (f"config{args.config}: {P} Gaussians, {W}x{H}, SH deg 3 + 3-ch language feature, fwd+bwd, "
+                f"one camera view per GPU per step" + (", NCCL allreduce of Gaussian grads" if world > 1 else ""))
+
+    if GR is None:  # reference extension not built: time the CPU oracle (a port) on a bounded sample
+        if rank == 0:
+            fps, frames, stats, cores = cpu_oracle_frames(scene, cams[0], max(1, min(args.steps, args.cpu_frames)))
+            line = {"impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
+                    "steps": frames, "warmup": 0, "ms_per_step": 1000.0 / fps, "higher_is_better": True,
+                    "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                    "config": {"workload": workload},
+                    "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
+                                     "sample": f"{frames} whole frames of the same workload on the CPU oracle"},
+                    "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                    "gpu_launches": 0}
+            print(json.dumps(line))
+        return
+
+    rs = settings(GS, cam, dev)
+    rast = GR(raster_settings=rs)
+    names = ["means3D", "shs", "opacities", "scales", "rotations", "language_feature"]
+    params = {k: scene[k].to(dev).requires_grad_(True) for k in names}
+    means2D = torch.zeros((P, 3), device=dev, requires_grad=True)
+    dcol, dfeat = [t.to(dev) for t in syn.make_grads(W, H, 2000 + args.config)]
+
+    def forward():
+        return rast(means3D=params["means3D"], means2D=means2D, shs=params["shs"],
+                    language_feature_precomp=params["language_feature"], opacities=params["opacities"],
+                    scales=params["scales"], rotations=params["rotations"])
+
+    def reduce_grads():
+        if world > 1:
+            from langsplat_b200.dist import allreduce_gradients
+            allreduce_gradients([p.grad for p in params.values()])
+
+    def step():
+        for p in params.values():
+            p.grad = None
+        means2D.grad = None
+        color, feat, radii = forward()
+        torch.autograd.backward([color, feat], [dcol, dfeat])
+        reduce_grads()
+
+    # ---- host-buffer (end-to-end) step: camera + ground truth come from pinned host memory, loss goes back ----
+    g = torch.Generator().manual_seed(77 + rank)
+    gt_c_h = torch.rand(3, H, W, generator=g).pin_memory()
+    gt_f_h = torch.rand(3, H, W, generator=g).pin_memory()
+    view_h, proj_h, cam_h = cam.viewmatrix.pin_memory(), cam.projmatrix.pin_memory(), cam.campos.pin_memory()
+    h2d_bytes = sum(t.numel() * 4 for t in (gt_c_h, gt_f_h, view_h, proj_h, cam_h))
+
+    def e2e_step():
+        for p in params.values():
+            p.grad = None
+        means2D.grad = None
+        gt_c, gt_f = gt_c_h.to(dev, non_blocking=True), gt_f_h.to(dev, non_blocking=True)
+        rs2 = rs._replace(viewmatrix=view_h.to(dev, non_blocking=True), projmatrix=proj_h.to(dev, non_blocking=True),
+                          campos=cam_h.to(dev, non_blocking=True))
+        color, feat, radii = GR(raster_settings=rs2)(
+            means3D=params["means3D"], means2D=means2D, shs=params["shs"],
+            language_feature_precomp=params["language_feature"], opacities=params["opacities"],
+            scales=params["scales"], rotations=params["rotations"])
+        loss = (color - gt_c).abs().mean() + (feat - gt_f).abs().mean()
+        loss.backward()
+        reduce_grads()
+        return float(loss.item())  # device -> host read of the step's result
+
+    lib = None
+    if args.impl == "ours":
+        from langsplat_b200 import _lib
+        lib = _lib.load()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier(world)
+    sampler = ClockSampler(dev.index or 0)
+    if rank == 0:
+        sampler.start()
+    launches0 = lib.lsr_launch_count() if lib else 0
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier(world)
+    ev0.record()
+    for _ in range(args.steps):
+        step()
+    ev1.record()
+    barrier(world)
+    ms_total = max_over_ranks(ev0.elapsed_time(ev1), world, dev)
+    launches = (lib.lsr_launch_count() - launches0) if lib else None
+
+    # forward-only ms/frame (second half of BASELINE.json's metric)
+    with torch.no_grad():
+        for _ in range(3):
+            forward()
+        barrier(world)
+        ev0.record()
+        for _ in range(args.steps):
+            forward()
+        ev1.record()
+        barrier(world)
+    fwd_ms = max_over_ranks(ev0.elapsed_time(ev1), world, dev) / args.steps
+
+    for _ in range(3):
+        e2e_step()
+    barrier(world)
+    ev0.record()
+    for _ in range(args.steps):
+        e2e_step()
+    ev1.record()
+    barrier(world)
+    e2e_ms_total = max_over_ranks(ev0.elapsed_time(ev1), world, dev)
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- per-stage device times (CUDA events inside liblsr.so, same stream), one profiled pass of K steps ----
+    stages, stage_ms = {}, None
+    if lib is not None:
+        lib.lsr_profile_enable(1)
+        n_st = lib.lsr_profile_read(None, 0) or 10
+        acc = np.zeros(16)
+        buf = (ctypes.c_float * 16)()
+        for _ in range(args.steps):
+            step()
+            n_st = lib.lsr_profile_read(buf, 16)
+            acc[:n_st] += np.array(buf[:n_st])
+        lib.lsr_profile_enable(0)
+        stage_ms = acc[:n_st] / args.steps
+        stages = {lib.lsr_profile_stage_name(i).decode(): float(stage_ms[i]) for i in range(n_st)}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    fps = world * args.steps / (ms_total / 1000.0)
+    line = {"metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload, "P": P, "width": W, "height": H, "cameras_per_step": world,
+                       "l2_policy": "inputs larger than L2 (Gaussian tensors ~250 MB), no explicit flush",
+                       "impl": impl_name},
+            "fwd_only_ms_per_frame": fwd_ms, "clocks": clocks,
+            "e2e": {"value": world * args.steps / (e2e_ms_total / 1000.0), "unit": "frames/s",
+                    "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4,
+                    "what": "camera + GT colour/feature images from pinned host memory, L1 loss, loss.item()"},
+            "gpu_launches": launches}
+    if args.impl == "reference":
+        line["impl"] = "reference"
+        line["gpu_launches"] = None
+        line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": 0, "kind": "reference",
+                                "sample": "NOT a CPU run: the reference has no CPU implementation of this path; this "
+                                          "is its unmodified CUDA extension (baseline/_ref, sm_100a) on the same GPU, "
+                                          "same workload, all steps"}
+        print(json.dumps(line))
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- CPU baseline (oracle port) on whole frames; also yields V, R, K_exam, K_contrib for the roofline ----
+    stats = {}
+    if world == 1 and not args.no_cpu_baseline:
+        cfps, frames, stats, cores = cpu_oracle_frames(scene, cam, args.cpu_frames)
+        line["cpu_baseline"] = {"value": cfps, "unit": "frames/s", "cores": cores, "kind": "port",
+                                "sample": f"{frames} whole frames (fwd+bwd) of the same workload, OpenMP over all "
+                                          f"{cores} host threads"}
+    hbm, sm_mhz, src = measured_peaks()
+    n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
+    fp32_peak = n_sm * 128 * sm_mhz * 1e6  # FP32-pipe instructions / s (FMA = 1)
+    if stats and stage_ms is not None:
+        V, Rn, Kx, Kc = stats["V"], stats["R"], stats["K_exam"], stats["K_contrib"]
+        N, T = W * H, ((W + 15) // 16) * ((H + 15) // 16)
+        bits = 32 + int(math.ceil(math.log2(T))) if T > 1 else 33
+        passes = (bits + 7) // 8
+        byt = {"preprocess_fwd": 20 * P + 291 * V, "scan": 8 * P, "duplicate": 4 * P + 16 * V + 12 * Rn,
+               "sort": Rn * (8 + 24 * passes), "tile_ranges": 8 * Rn + 8 * T, "render_fwd": 52 * Rn + 32 * N,
+               "bwd_zero_fill": 56 * P, "render_bwd": 52 * Rn + 32 * N + 48 * V, "preprocess_bwd": 236 * P + 303 * V}
+        ins = {"render_fwd": 20 * Kx + 15 * Kc, "render_bwd": 20 * Kx + 54 * Kc}
+        table = {}
+        for k, ms in stages.items():
+            if k not in byt or ms <= 0:
+                continue
+            e = {"ms": ms, "alg_bytes": byt[k], "GBps": byt[k] / ms / 1e6, "hbm_frac": byt[k] / ms / 1e6 / hbm}
+            if k in ins:
+                e["fp32_instr"] = ins[k]
+                e["Tinstr_s"] = ins[k] / ms / 1e9
+                e["fp32_frac"] = ins[k] / (ms / 1e3) / fp32_peak
+                e["roofline_frac"] = (byt[k] / (hbm * 1e9) + ins[k] / fp32_peak) / (ms / 1e3)
+            table[k] = e
+        line["stages"] = table
+        line["scene"] = dict(P=P, V=V, R=Rn, N=N, T=T, K_exam=Kx, K_contrib=Kc, sort_bits=bits)
+        dom = max(table, key=lambda k: table[k]["ms"])
+        d = table[dom]
+        if "fp32_instr" in d:
+            line["roofline"] = {"kernel": dom, "bound": "fp32", "achieved": d["Tinstr_s"], "peak": fp32_peak / 1e12,
+                                "unit": "TInstr/s", "frac": d["fp32_frac"], "traffic": None,
+                                "peak_source": f"{n_sm} SMs x 128 lanes x {sm_mhz:.0f} MHz ({src} clock)",
+                                "note": "blend kernels are FP32-pipe bound (no dense contraction, SURVEY 8d); "
+                                        "roofline_frac in `stages` adds the HBM term"}
+        else:
+            line["roofline"] = {"kernel": dom, "bound": "hbm", "achieved": d["GBps"], "peak": hbm, "unit": "GB/s",
+                                "frac": d["hbm_frac"], "traffic": None, "peak_source": src}
+        s = table.get("sort")
+        if s:
+            line["roofline_hbm"] = {"kernel": "sort (onesweep, %d passes)" % passes, "bound": "hbm",
+                                    "achieved": s["GBps"], "peak": hbm, "unit": "GB/s", "frac": s["hbm_frac"],
+                                    "traffic": None, "peak_source": src}
+    elif stages:
+        line["stages"] = {k: {"ms": v} for k, v in stages.items()}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

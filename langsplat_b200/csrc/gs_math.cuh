@@ -45,17 +45,20 @@ __device__ __forceinline__ float tp_row(const float* __restrict__ m, int i, floa
   return __fadd_rn(t, m[12 + i]);
 }
 
-// rotation matrix from the quaternion as given (not normalised) — RAST/cuda_rasterizer/forward.cu:127-139
+// rotation matrix from the quaternion as given (not normalised) — RAST/cuda_rasterizer/forward.cu:127-139.
+// Contraction read off the reference build's SASS (nvcc 12.9, sm_100a): products with several uses stay separate
+// FMULs, so  yy+zz = (y*y) + (z*z)  [no fma],  xz+ry = fma(r,y, x*z),  xz-ry = fma(-r,y, x*z);  the others fuse
+// their left product:  xy-rz = fma(x,y,-(r*z)),  xx+zz = fma(x,x, z*z), ...
 __device__ __forceinline__ Mat3 quat_to_mat(float r, float x, float y, float z) {
   Mat3 R;
   float t;
-  t = __fmaf_rn(y, y, __fmul_rn(z, z));           R.m[0][0] = __fadd_rn(1.f, -__fadd_rn(t, t));
+  t = __fadd_rn(__fmul_rn(y, y), __fmul_rn(z, z)); R.m[0][0] = __fadd_rn(1.f, -__fadd_rn(t, t));
   t = __fmaf_rn(x, y, -__fmul_rn(r, z));          R.m[0][1] = __fadd_rn(t, t);
-  t = __fmaf_rn(x, z, __fmul_rn(r, y));           R.m[0][2] = __fadd_rn(t, t);
+  t = __fmaf_rn(r, y, __fmul_rn(x, z));           R.m[0][2] = __fadd_rn(t, t);
   t = __fmaf_rn(x, y, __fmul_rn(r, z));           R.m[1][0] = __fadd_rn(t, t);
   t = __fmaf_rn(x, x, __fmul_rn(z, z));           R.m[1][1] = __fadd_rn(1.f, -__fadd_rn(t, t));
   t = __fmaf_rn(y, z, -__fmul_rn(r, x));          R.m[1][2] = __fadd_rn(t, t);
-  t = __fmaf_rn(x, z, -__fmul_rn(r, y));          R.m[2][0] = __fadd_rn(t, t);
+  t = __fmaf_rn(-r, y, __fmul_rn(x, z));          R.m[2][0] = __fadd_rn(t, t);
   t = __fmaf_rn(y, z, __fmul_rn(r, x));           R.m[2][1] = __fadd_rn(t, t);
   t = __fmaf_rn(x, x, __fmul_rn(y, y));           R.m[2][2] = __fadd_rn(1.f, -__fadd_rn(t, t));
   return R;

@@ -114,13 +114,13 @@ inline M3<R> quatR(const R* q) {
   R r = q[0], x = q[1], y = q[2], z = q[3];
   auto two = [](R v) { return v + v; };
   M3<R> Rm;
-  Rm.m[0][0] = (R)1 - two(std::fma(y, y, z * z));
+  Rm.m[0][0] = (R)1 - two(y * y + z * z);  // both products have other uses: no fma in the reference SASS
   Rm.m[0][1] = two(std::fma(x, y, -(r * z)));
-  Rm.m[0][2] = two(std::fma(x, z, r * y));
+  Rm.m[0][2] = two(std::fma(r, y, x * z));
   Rm.m[1][0] = two(std::fma(x, y, r * z));
   Rm.m[1][1] = (R)1 - two(std::fma(x, x, z * z));
   Rm.m[1][2] = two(std::fma(y, z, -(r * x)));
-  Rm.m[2][0] = two(std::fma(x, z, -(r * y)));
+  Rm.m[2][0] = two(std::fma(-r, y, x * z));
   Rm.m[2][1] = two(std::fma(y, z, r * x));
   Rm.m[2][2] = (R)1 - two(std::fma(x, x, y * y));
   return Rm;
