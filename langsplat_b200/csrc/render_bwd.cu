@@ -10,11 +10,13 @@
 // Template switches specialise on what the caller needs (ctx.needs_input_grad): FEAT = language feature blended,
 // DCOL = a colour upstream gradient exists, GEOM = conic/opacity gradients wanted.  LangSplat's feature-only training
 // (train.py:96-99 with gaussian_model.py:212-217) runs <FEAT=1, DCOL=0, GEOM=0>: 5 values instead of 12.
-#include "common.cuh"
+#include "render_common.cuh"
 
 namespace lsr {
 
 namespace {
+
+constexpr int SPARSE_LANES = 2;
 
 // Butterfly reduction of N per-lane values; afterwards lane `l` with held_index<N>(l) >= 0 holds in v[0] the warp
 // total of value held_index(l).
@@ -71,10 +73,7 @@ render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
   constexpr int I_FEAT = I_COL + (DCOL ? 3 : 0);
   constexpr int NV = I_FEAT + (FEAT ? 3 : 0);
 
-  __shared__ float4 s_a[TILE_PIX];
-  __shared__ float4 s_b[TILE_PIX];
-  __shared__ float4 s_c[TILE_PIX];
-  __shared__ uint32_t s_id[TILE_PIX];
+  __shared__ BatchSmem sm;
   __shared__ uint32_t s_max[TILE_PIX / 32];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -83,6 +82,7 @@ render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
   const uint32_t px = blockIdx.x * TILE_X + tx, py = blockIdx.y * TILE_Y + ty;
   const bool inside = px < (uint32_t)W && py < (uint32_t)H;
   const float pxf = (float)px, pyf = (float)py;
+  const float X0 = (float)(blockIdx.x * TILE_X), Y0 = (float)(blockIdx.y * TILE_Y);
   const size_t N = (size_t)W * H;
   const size_t pix = (size_t)py * W + px;
   const uint2 range = ranges[blockIdx.y * tiles_x + blockIdx.x];
@@ -91,7 +91,7 @@ render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
   float T = T_final;
   const uint32_t last_contributor = inside ? n_contrib[pix] : 0u;
 
-  // CTA / warp maxima of n_contrib bound the part of the list anyone needs
+  // The CTA-wide maximum of n_contrib bounds the part of the list anyone needs.
   uint32_t wmax = last_contributor;
 #pragma unroll
   for (int d = 16; d > 0; d >>= 1) wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, d));
@@ -135,45 +135,38 @@ render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
 
   const int rounds = (eff_len + TILE_PIX - 1) / TILE_PIX;
   for (int b = 0; b < rounds; b++) {
-    __syncthreads();
-    {
-      const int fwd = eff_len - 1 - (b * TILE_PIX + tid);
-      if (fwd >= 0) {
-        const uint32_t id = __ldg(list + range.x + fwd);
-        const float4* r4 = reinterpret_cast<const float4*>(rec + id);
-        s_id[tid] = id;
-        s_a[tid] = __ldg(r4);
-        s_b[tid] = __ldg(r4 + 1);
-        s_c[tid] = __ldg(r4 + 2);
-      }
-    }
-    __syncthreads();
-    const int nb = min(TILE_PIX, eff_len - b * TILE_PIX);
-    // skip the entries beyond this warp's own maximum
-    int j0 = (eff_len - b * TILE_PIX) - (int)wmax;
-    if (j0 < 0) j0 = 0;
-    for (int j = j0; j < nb; j++) {
-      const uint32_t fwd = (uint32_t)(eff_len - 1 - (b * TILE_PIX + j));
-      const float4 a = s_a[j];
-      const float4 bb = s_b[j];
+    // back to front: this batch covers forward indices eff_len-1-b*256 downwards (backward.cu:486-498)
+    const int fwd_fetch = eff_len - 1 - (b * TILE_PIX + tid);
+    const int nb = stage_batch(sm, list, rec, range.x, fwd_fetch >= 0 ? fwd_fetch : -1, X0, Y0);
+    for (int j = 0; j < nb; j++) {
+      const float4 a = sm.A[j];
+      const float4 bb = sm.B[j];  // cz, thr_m, opacity, position
+      const uint32_t fwd = __float_as_uint(bb.w);
       const float dx = __fadd_rn(a.x, -pxf), dy = __fadd_rn(a.y, -pyf);
       const float q = __fmaf_rn(dx, __fmul_rn(a.z, dx), __fmul_rn(__fmul_rn(bb.x, dy), dy));
       const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(__fmul_rn(a.w, dx), dy));
+      // entries at or beyond n_contrib were never blended (backward.cu:504-506); power > 0 and the alpha threshold
+      // as in the forward.  The pre-test against thr_m avoids expf for pairs that certainly fail alpha >= 1/255.
+      const bool maybe = (fwd < last_contributor) && !(power > 0.0f) && !(power < bb.y);
+      if (__ballot_sync(0xffffffffu, maybe) == 0u) continue;
       const float G = expf(power);
-      const float alpha = fminf(0.99f, __fmul_rn(bb.y, G));
-      const bool contrib = (fwd < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-      if (__ballot_sync(0xffffffffu, contrib) == 0u) continue;
+      const float alpha = fminf(0.99f, __fmul_rn(bb.z, G));
+      const bool contrib = maybe && !(alpha < kAlphaMin);
+      const uint32_t cmask = __ballot_sync(0xffffffffu, contrib);
+      if (cmask == 0u) continue;
 
       float v[12];
 #pragma unroll
       for (int k = 0; k < 12; k++) v[k] = 0.f;
+      const float4 c = sm.C[j];  // r, g, b, f0
+      const float4 d = sm.D[j];  // f1, f2, id
       if (contrib) {
         const float one_m_alpha = __fadd_rn(1.f, -alpha);
         T = __fdiv_rn(T, one_m_alpha);
         const float dchannel_dcolor = alpha * T;
         float dL_dalpha = 0.0f;
         if (DCOL) {
-          const float col[3] = {bb.z, bb.w, s_c[j].x};
+          const float col[3] = {c.x, c.y, c.z};
 #pragma unroll
           for (int ch = 0; ch < 3; ch++) {
             accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
@@ -183,8 +176,7 @@ render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
           }
         }
         if (FEAT) {
-          const float4 c = s_c[j];
-          const float ft[3] = {c.y, c.z, c.w};
+          const float ft[3] = {c.w, d.x, d.y};
 #pragma unroll
           for (int ch = 0; ch < 3; ch++) {
             accum_recF[ch] = last_alpha * last_F[ch] + (1.f - last_alpha) * accum_recF[ch];
@@ -198,7 +190,7 @@ render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
         if (DCOL) {
           if (bg_dot != 0.f) dL_dalpha += (-T_final / one_m_alpha) * bg_dot;
         }
-        const float dL_dG = bb.y * dL_dalpha;
+        const float dL_dG = bb.z * dL_dalpha;
         const float gdx = G * dx, gdy = G * dy;
         const float dG_ddelx = -gdx * a.z - gdy * a.w;
         const float dG_ddely = -gdy * bb.x - gdx * a.w;
@@ -211,8 +203,31 @@ render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
           v[I_OPAC] = G * dL_dalpha;
         }
       }
-      multi_reduce<NV, 16>(v, lane);
-      if (out_base != nullptr) atomicAdd(out_base + (size_t)s_id[j] * out_stride, v[0]);
+      const uint32_t gid = __float_as_uint(d.z);
+      if (__popc(cmask) <= SPARSE_LANES) {
+        // very few lanes contribute: their own REDs cost fewer issue slots than the 13-shuffle butterfly
+        if (contrib) {
+          atomicAdd(dL_dmean2D + (size_t)gid * 3, v[I_MEAN]);
+          atomicAdd(dL_dmean2D + (size_t)gid * 3 + 1, v[I_MEAN + 1]);
+          if (GEOM) {
+            atomicAdd(dL_dconic + (size_t)gid * 4, v[I_CONIC]);
+            atomicAdd(dL_dconic + (size_t)gid * 4 + 1, v[I_CONIC + 1]);
+            atomicAdd(dL_dconic + (size_t)gid * 4 + 3, v[I_CONIC + 2]);
+            atomicAdd(dL_dopacity + gid, v[I_OPAC]);
+          }
+          if (DCOL) {
+#pragma unroll
+            for (int ch = 0; ch < 3; ch++) atomicAdd(dL_dcolors + (size_t)gid * 3 + ch, v[I_COL + ch]);
+          }
+          if (FEAT) {
+#pragma unroll
+            for (int ch = 0; ch < 3; ch++) atomicAdd(dL_dfeat + (size_t)gid * 3 + ch, v[I_FEAT + ch]);
+          }
+        }
+      } else {
+        multi_reduce<NV, 16>(v, lane);
+        if (out_base != nullptr) atomicAdd(out_base + (size_t)gid * out_stride, v[0]);
+      }
     }
   }
 }

@@ -2,13 +2,15 @@
 // Replaces FORWARD::render / renderCUDA (RAST/cuda_rasterizer/forward.cu:262-426).
 //
 // One CTA per tile, one thread per pixel.  Per 256-instance batch the CTA gathers one 48-byte GeomRec per instance
-// into shared memory (position, conic, opacity, colour AND feature — the reference re-reads colour/feature from
-// global memory for every contributing pair, forward.cu:359-366), then every pixel walks the batch.
+// (position, conic, opacity, colour AND feature — the reference re-reads colour/feature from global memory for every
+// contributing pair, forward.cu:359-366), drops instances that provably cannot contribute anywhere in the tile and
+// compacts the rest into shared memory (render_common.cuh); then every pixel walks the survivors.
 // The per-pair arithmetic is written with explicit round-to-nearest intrinsics in the exact order of the reference's
 // SASS so that the skip / stop decisions, hence n_contrib, are bit-identical:
 //   power = fma(fma(dx, cx*dx, (cz*dy)*dy), -0.5, -((cy*dx)*dy));  alpha = min(0.99, o*expf(power)).
-// include_feature is a template parameter (a runtime branch in the reference).
-#include "common.cuh"
+// expf is only evaluated when power >= thr_m (see render_common.cuh).  include_feature is a template parameter
+// (a runtime branch in the reference).  Kernel is FP32-issue bound; shared-memory reads are warp broadcasts.
+#include "render_common.cuh"
 
 namespace lsr {
 
@@ -19,9 +21,7 @@ __global__ void __launch_bounds__(TILE_PIX)
 render_fwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t* __restrict__ list,
                   const GeomRec* __restrict__ rec, const float* __restrict__ bg, float* __restrict__ final_T,
                   uint32_t* __restrict__ n_contrib, float* __restrict__ out_color, float* __restrict__ out_feature) {
-  __shared__ float4 s_a[TILE_PIX];  // x, y, cx, cy
-  __shared__ float4 s_b[TILE_PIX];  // cz, o, r, g
-  __shared__ float4 s_c[TILE_PIX];  // b, f0, f1, f2
+  __shared__ BatchSmem sm;
 
   const int tx = threadIdx.x & (TILE_X - 1), ty = threadIdx.x >> 4;
   const int tid = threadIdx.x;
@@ -29,53 +29,46 @@ render_fwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
   const uint32_t px = blockIdx.x * TILE_X + tx, py = blockIdx.y * TILE_Y + ty;
   const bool inside = px < (uint32_t)W && py < (uint32_t)H;
   const float pxf = (float)px, pyf = (float)py;
+  const float X0 = (float)(blockIdx.x * TILE_X), Y0 = (float)(blockIdx.y * TILE_Y);
   const uint2 range = ranges[blockIdx.y * tiles_x + blockIdx.x];
-  const int rounds = (int)((range.y - range.x + TILE_PIX - 1) / TILE_PIX);
-  int todo = (int)(range.y - range.x);
+  const int len = (int)(range.y - range.x);
+  const int rounds = (len + TILE_PIX - 1) / TILE_PIX;
 
   bool done = !inside;
   float T = 1.0f;
-  uint32_t contributor = 0, last_contributor = 0;
+  uint32_t last_contributor = 0;
   float C0 = 0.f, C1 = 0.f, C2 = 0.f, F0 = 0.f, F1 = 0.f, F2 = 0.f;
 
-  for (int i = 0; i < rounds; i++, todo -= TILE_PIX) {
+  for (int i = 0; i < rounds; i++) {
     if (__syncthreads_count(done) == TILE_PIX) break;
-    const uint32_t progress = (uint32_t)i * TILE_PIX + tid;
-    if (range.x + progress < range.y) {
-      const uint32_t id = __ldg(list + range.x + progress);
-      const float4* r4 = reinterpret_cast<const float4*>(rec + id);
-      s_a[tid] = __ldg(r4);
-      s_b[tid] = __ldg(r4 + 1);
-      s_c[tid] = __ldg(r4 + 2);
-    }
-    __syncthreads();
-    const int nb = min(TILE_PIX, todo);
+    const int li = i * TILE_PIX + tid;
+    const int nb = stage_batch(sm, list, rec, range.x, li < len ? li : -1, X0, Y0);
     for (int j = 0; !done && j < nb; j++) {
-      contributor++;
-      const float4 a = s_a[j];
-      const float4 b = s_b[j];
+      const float4 a = sm.A[j];
+      const float4 b = sm.B[j];
       const float dx = __fadd_rn(a.x, -pxf), dy = __fadd_rn(a.y, -pyf);
       const float q = __fmaf_rn(dx, __fmul_rn(a.z, dx), __fmul_rn(__fmul_rn(b.x, dy), dy));
       const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(__fmul_rn(a.w, dx), dy));
-      if (power > 0.0f) continue;
-      const float alpha = fminf(0.99f, __fmul_rn(b.y, expf(power)));
-      if (alpha < 1.0f / 255.0f) continue;
+      if (power > 0.0f || power < b.y) continue;  // b.y = thr_m: below it alpha < 1/255 for certain
+      const float alpha = fminf(0.99f, __fmul_rn(b.z, expf(power)));
+      if (alpha < kAlphaMin) continue;
       const float test_T = __fmul_rn(T, __fadd_rn(1.0f, -alpha));
       if (test_T < 0.0001f) {
         done = true;
         continue;
       }
-      const float4 c = s_c[j];
-      C0 = __fmaf_rn(T, __fmul_rn(b.z, alpha), C0);
-      C1 = __fmaf_rn(T, __fmul_rn(b.w, alpha), C1);
-      C2 = __fmaf_rn(T, __fmul_rn(c.x, alpha), C2);
+      const float4 c = sm.C[j];
+      C0 = __fmaf_rn(T, __fmul_rn(c.x, alpha), C0);
+      C1 = __fmaf_rn(T, __fmul_rn(c.y, alpha), C1);
+      C2 = __fmaf_rn(T, __fmul_rn(c.z, alpha), C2);
       if (FEAT) {
-        F0 = __fmaf_rn(T, __fmul_rn(c.y, alpha), F0);
-        F1 = __fmaf_rn(T, __fmul_rn(c.z, alpha), F1);
-        F2 = __fmaf_rn(T, __fmul_rn(c.w, alpha), F2);
+        const float4 d = sm.D[j];
+        F0 = __fmaf_rn(T, __fmul_rn(c.w, alpha), F0);
+        F1 = __fmaf_rn(T, __fmul_rn(d.x, alpha), F1);
+        F2 = __fmaf_rn(T, __fmul_rn(d.y, alpha), F2);
       }
       T = test_T;
-      last_contributor = contributor;
+      last_contributor = __float_as_uint(b.w) + 1u;  // 1-based position in the tile's list (forward.cu:372)
     }
   }
   if (inside) {
