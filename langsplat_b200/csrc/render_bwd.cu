@@ -77,7 +77,8 @@ render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
   __shared__ uint32_t s_max[TILE_PIX / 32];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int tx = tid & (TILE_X - 1), ty = tid >> 4;
+  // warp w owns an 8x4-pixel footprint (compact, instead of the reference's 16x2 strips)
+  const int tx = (warp & 1) * 8 + (lane & 7), ty = (warp >> 1) * 4 + (lane >> 3);
   const int tiles_x = (W + TILE_X - 1) / TILE_X;
   const uint32_t px = blockIdx.x * TILE_X + tx, py = blockIdx.y * TILE_Y + ty;
   const bool inside = px < (uint32_t)W && py < (uint32_t)H;

@@ -23,8 +23,9 @@ render_fwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
                   uint32_t* __restrict__ n_contrib, float* __restrict__ out_color, float* __restrict__ out_feature) {
   __shared__ BatchSmem sm;
 
-  const int tx = threadIdx.x & (TILE_X - 1), ty = threadIdx.x >> 4;
   const int tid = threadIdx.x;
+  // warp w owns an 8x4-pixel footprint (compact, instead of the reference's 16x2 strips)
+  const int tx = ((tid >> 5) & 1) * 8 + (tid & 7), ty = (tid >> 6) * 4 + ((tid & 31) >> 3);
   const int tiles_x = (W + TILE_X - 1) / TILE_X;
   const uint32_t px = blockIdx.x * TILE_X + tx, py = blockIdx.y * TILE_Y + ty;
   const bool inside = px < (uint32_t)W && py < (uint32_t)H;
