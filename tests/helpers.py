@@ -112,9 +112,83 @@ def load_reference():
     return mod
 
 
+def _al(x, a=128):
+    return (x + a - 1) // a * a
+
+
+def ref_forward_buffers(REF, scene, cam, include_feature=True, sh_degree=3, bg=(0.0, 0.0, 0.0)):
+    """Calls the reference extension's _C.rasterize_gaussians and parses its three opaque byte buffers
+    (RAST/cuda_rasterizer/rasterizer_impl.cu:155-194, 128-byte `obtain` alignment)."""
+    d = {k: v.cuda() for k, v in scene.items()}
+    rs = settings_for(cam, "cuda", include_feature, sh_degree, bg)
+    lang = d["language_feature"] if include_feature else torch.zeros((1,), device="cuda")
+    e = torch.Tensor([])
+    args = (rs.bg, d["means3D"], e, lang, d["opacities"], d["scales"], d["rotations"], rs.scale_modifier, e,
+            rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, d["shs"],
+            rs.sh_degree, rs.campos, rs.prefiltered, rs.debug, rs.include_feature)
+    num_rendered, color, feat, radii, geomB, binB, imgB = REF._C.rasterize_gaussians(*args)
+    torch.cuda.synchronize()
+    P = d["means3D"].shape[0]
+    N = cam.image_width * cam.image_height
+    T = ((cam.image_width + 15) // 16) * ((cam.image_height + 15) // 16)
+    geom = geomB.cpu().numpy()
+    off = 0
+    out = dict(num_rendered=num_rendered, color=color, feature=feat, radii=radii)
+
+    def take(buf, off, dtype, count):
+        off = _al(off)
+        nbytes = np.dtype(dtype).itemsize * count
+        return buf[off:off + nbytes].view(dtype), off + nbytes
+
+    out["depths"], off = take(geom, off, np.float32, P)
+    _, off = take(geom, off, np.uint8, 3 * P)
+    _, off = take(geom, off, np.int32, P)
+    out["means2D"], off = take(geom, off, np.float32, 2 * P)
+    out["cov3D"], off = take(geom, off, np.float32, 6 * P)
+    out["conic_opacity"], off = take(geom, off, np.float32, 4 * P)
+    out["rgb"], off = take(geom, off, np.float32, 3 * P)
+    out["tiles_touched"], off = take(geom, off, np.uint32, P)
+    Rn = num_rendered
+    binb = binB.cpu().numpy()
+    off = 0
+    out["point_list"], off = take(binb, off, np.uint32, Rn)
+    _, off = take(binb, off, np.uint32, Rn)
+    out["keys"], off = take(binb, off, np.uint64, Rn)
+    img = imgB.cpu().numpy()
+    off = 0
+    out["final_T"], off = take(img, off, np.float32, N)
+    out["n_contrib"], off = take(img, off, np.uint32, N)
+    ranges, off = take(img, off, np.uint32, 2 * N)
+    out["ranges"] = ranges[:2 * T].reshape(T, 2)
+    return out
+
+
 def rel_err(a, b):
     """max |a-b| / max |b| — the relative metric used for gradients (the reference sums with unordered atomics)."""
     a = a.detach().double().cpu() if hasattr(a, "detach") else torch.as_tensor(a).double()
     b = b.detach().double().cpu() if hasattr(b, "detach") else torch.as_tensor(b).double()
     denom = b.abs().max().item()
     return (a - b).abs().max().item() / (denom if denom > 0 else 1.0)
+
+
+# ---- golden vectors (tests/golden/*.npz, produced by tests/golden/make_golden.py from the reference extension) ----
+GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
+GOLDEN_CASES = ("rgb_feat_bg", "feature_only_ragged", "rgb_only_deg1")
+
+
+def load_golden(name):
+    """Returns (fixture dict, scene dict of CPU tensors, Camera, kwargs for oracle_forward / run_module)."""
+    path = os.path.join(GOLDEN_DIR, name + ".npz")
+    fx = dict(np.load(path))
+    scene = {k[3:]: torch.from_numpy(fx[k]) for k in ("in_means3D", "in_scales", "in_rotations", "in_opacities",
+                                                      "in_shs", "in_language_feature")}
+    W, H = int(fx["in_size"][0]), int(fx["in_size"][1])
+    cam = syn.Camera(W, H, float(fx["in_tanfov"][0]), float(fx["in_tanfov"][1]), torch.from_numpy(fx["in_viewmatrix"]),
+                     torch.from_numpy(fx["in_projmatrix"]), torch.from_numpy(fx["in_campos"]))
+    kw = dict(include_feature=bool(fx["in_include_feature"]), sh_degree=int(fx["in_sh_degree"]),
+              bg=tuple(float(x) for x in fx["in_bg"]))
+    return fx, scene, cam, kw
+
+
+def golden_available():
+    return all(os.path.exists(os.path.join(GOLDEN_DIR, n + ".npz")) for n in GOLDEN_CASES)

@@ -1,0 +1,90 @@
+"""CPU, world_size 2 over gloo: the view-sharded step (BASELINE.json config 4).  Each rank rasterises
+its share of the step's camera views against the replicated Gaussians (here with the CPU oracle standing in for the
+kernels — the host-side sharding / reduction logic is what is under test), sums its views' gradients, and one
+sum-allreduce leaves every rank with the gradient of the whole step."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from helpers import oracle_forward, orc, syn
+from langsplat_b200 import dist as D
+
+N_VIEWS = 4
+NAMES = ("means3D", "shs", "opacities", "scales", "rotations", "language_feature")
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _view_grads(scene, cam, seed):
+    dcol, dfeat = syn.make_grads(cam.image_width, cam.image_height, seed)
+    fw = oracle_forward(scene, cam)
+    g = orc.backward(fw, dcol.numpy(), dfeat.numpy())
+    stats = dict(norm=np.linalg.norm(g["means2D"][:, :2], axis=1), vis=(fw["radii"] > 0), radii=fw["radii"])
+    return {k: torch.from_numpy(np.asarray(g[k], np.float32).reshape(scene[k].shape)) for k in NAMES}, stats
+
+
+def _worker(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        orc.set_num_threads(2)
+        scene, cams = syn.make_config(4, P=1500, W=96, H=64, n_cameras=N_VIEWS)
+        mine = D.views_for_rank(N_VIEWS, rank, world)
+        acc = {k: torch.zeros_like(scene[k]) for k in NAMES}
+        s_sum, s_cnt = torch.zeros(1500), torch.zeros(1500)
+        s_max = torch.zeros(1500, dtype=torch.int32)
+        for v in mine:
+            g, st = _view_grads(scene, cams[v], 100 + v)
+            for k in NAMES:
+                acc[k] += g[k]
+            s_sum += torch.from_numpy(st["norm"]).float() * torch.from_numpy(st["vis"])
+            s_cnt += torch.from_numpy(st["vis"]).float()
+            s_max = torch.maximum(s_max, torch.from_numpy(st["radii"]))
+        handles = D.allreduce_gradients([acc[k] for k in NAMES] + [None], async_op=True)
+        for h in handles:
+            h.wait()
+        D.reduce_view_statistics(s_sum, s_cnt, s_max)
+        torch.save(dict(acc=acc, views=mine, s_sum=s_sum, s_cnt=s_cnt, s_max=s_max),
+                   os.path.join(out_dir, f"rank{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_views_for_rank_partitions_the_step():
+    for world in (1, 2, 3, 4, 8):
+        seen = sorted(v for r in range(world) for v in D.views_for_rank(8, r, world))
+        assert seen == list(range(8))
+    assert D.views_for_rank(8, 1, 4) == [1, 5]
+    assert D.allreduce_gradients([torch.ones(3)]) == []  # no process group: a no-op, not an error
+
+
+@pytest.mark.timeout(300)
+def test_view_sharded_step_equals_serial_sum(tmp_path):
+    world = 2
+    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    r0 = torch.load(tmp_path / "rank0.pt")
+    r1 = torch.load(tmp_path / "rank1.pt")
+    assert sorted(r0["views"] + r1["views"]) == list(range(N_VIEWS))
+    scene, cams = syn.make_config(4, P=1500, W=96, H=64, n_cameras=N_VIEWS)
+    want = {k: torch.zeros_like(scene[k]) for k in NAMES}
+    cnt = torch.zeros(1500)
+    for v in range(N_VIEWS):
+        g, st = _view_grads(scene, cams[v], 100 + v)
+        for k in NAMES:
+            want[k] += g[k]
+        cnt += torch.from_numpy(st["vis"]).float()
+    for k in NAMES:
+        assert torch.equal(r0["acc"][k], r1["acc"][k]), k  # every rank ends with the same reduced gradient
+        scale = want[k].abs().max().item()
+        assert (r0["acc"][k] - want[k]).abs().max().item() <= 1e-5 * scale, k
+    assert torch.equal(r0["s_cnt"], cnt) and torch.equal(r1["s_cnt"], cnt)
+    assert torch.equal(r0["s_max"], r1["s_max"]) and r0["s_max"].max() > 0

@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 import torch
 
-from helpers import R, cuda_forward_state, load_reference, rel_err, run_module, settings_for, syn
+from helpers import R, cuda_forward_state, load_reference, ref_forward_buffers, rel_err, run_module, syn
 
 pytestmark = pytest.mark.gpu
 
@@ -17,53 +17,8 @@ REF = load_reference()
 needs_ref = pytest.mark.skipif(REF is None, reason="baseline/_ref reference extension not built")
 
 
-def _al(x, a=128):
-    return (x + a - 1) // a * a
-
-
 def _ref_forward_buffers(scene, cam, include_feature=True):
-    d = {k: v.cuda() for k, v in scene.items()}
-    rs = settings_for(cam, "cuda", include_feature)
-    lang = d["language_feature"] if include_feature else torch.zeros((1,), device="cuda")
-    e = torch.Tensor([])
-    args = (rs.bg, d["means3D"], e, lang, d["opacities"], d["scales"], d["rotations"], rs.scale_modifier, e,
-            rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, d["shs"],
-            rs.sh_degree, rs.campos, rs.prefiltered, rs.debug, rs.include_feature)
-    num_rendered, color, feat, radii, geomB, binB, imgB = REF._C.rasterize_gaussians(*args)
-    torch.cuda.synchronize()
-    P = d["means3D"].shape[0]
-    N = cam.image_width * cam.image_height
-    T = ((cam.image_width + 15) // 16) * ((cam.image_height + 15) // 16)
-    geom = geomB.cpu().numpy()
-    off = 0
-    out = dict(num_rendered=num_rendered, color=color, feature=feat, radii=radii)
-
-    def take(buf, off, dtype, count):
-        off = _al(off)
-        nbytes = np.dtype(dtype).itemsize * count
-        return buf[off:off + nbytes].view(dtype), off + nbytes
-
-    out["depths"], off = take(geom, off, np.float32, P)
-    _, off = take(geom, off, np.uint8, 3 * P)
-    _, off = take(geom, off, np.int32, P)
-    out["means2D"], off = take(geom, off, np.float32, 2 * P)
-    out["cov3D"], off = take(geom, off, np.float32, 6 * P)
-    out["conic_opacity"], off = take(geom, off, np.float32, 4 * P)
-    out["rgb"], off = take(geom, off, np.float32, 3 * P)
-    out["tiles_touched"], off = take(geom, off, np.uint32, P)
-    Rn = num_rendered
-    binb = binB.cpu().numpy()
-    off = 0
-    out["point_list"], off = take(binb, off, np.uint32, Rn)
-    _, off = take(binb, off, np.uint32, Rn)
-    out["keys"], off = take(binb, off, np.uint64, Rn)
-    img = imgB.cpu().numpy()
-    off = 0
-    out["final_T"], off = take(img, off, np.float32, N)
-    out["n_contrib"], off = take(img, off, np.uint32, N)
-    ranges, off = take(img, off, np.uint32, 2 * N)
-    out["ranges"] = ranges[:2 * T].reshape(T, 2)
-    return out
+    return ref_forward_buffers(REF, scene, cam, include_feature)
 
 
 def _np(t):
