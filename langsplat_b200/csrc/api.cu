@@ -98,8 +98,6 @@ size_t lsr_array_offset(int which, int32_t P, int32_t width, int32_t height, int
   GeomView g = geom_view(base, P);
   ImageView im = image_view(base, width, height);
   ScratchView sc = scratch_view(base, P, capacity);
-  const int T = ((width + TILE_X - 1) / TILE_X) * ((height + TILE_Y - 1) / TILE_Y);
-  const int passes = (32 + (int)higher_msb((uint32_t)T) + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
   switch (which) {
     case LSR_ARR_GEOM_REC: return (char*)g.rec - base;
     case LSR_ARR_GEOM_DEPTH: return (char*)g.depth - base;
@@ -112,7 +110,7 @@ size_t lsr_array_offset(int which, int32_t P, int32_t width, int32_t height, int
     case LSR_ARR_IMG_RANGES: return (char*)im.ranges - base;
     case LSR_ARR_SCR_KEYS_UNSORTED: return (char*)sc.keys_a - base;
     case LSR_ARR_SCR_VALS_UNSORTED: return (char*)sc.vals_a - base;
-    case LSR_ARR_SCR_KEYS_SORTED: return (char*)((passes & 1) ? sc.keys_b : sc.keys_a) - base;
+    case LSR_ARR_SCR_KEYS_SORTED: return (char*)sc.keys_b - base;
     default: return (size_t)-1;
   }
 }
@@ -163,7 +161,8 @@ int lsr_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* k
   if (!keys_in || !vals_in || !keys_out || !vals_out || !keys_tmp || !vals_tmp || !work)
     return fail(LSR_ERR_INVALID, "null pointer");
   if (work_bytes < sort_work_bytes(n)) return fail(LSR_ERR_CAPACITY, "sort work buffer too small");
-  sort_pairs(keys_in, vals_in, keys_out, vals_out, keys_tmp, vals_tmp, n, end_bit, work, (cudaStream_t)stream);
+  sort_pairs(keys_in, vals_in, keys_out, vals_out, keys_tmp, vals_tmp, n, make_sort_plan_bits(end_bit), false, work,
+             (cudaStream_t)stream);
   LSR_CUDA(cudaGetLastError());
   return LSR_OK;
 }
@@ -224,9 +223,10 @@ int lsr_forward(const lsr_frame* frame, const lsr_inputs* in, float* out_color, 
     launch_scan_tiles(P, g.tiles, g.offsets, sc.scan_status, sc.ctrl, s);
     LSR_STAGE("scan");
     prof(g_ev_f, 2, s);
-    // R decides the launch geometry of the sort; read it back like the reference does (rasterizer_impl.cu:284)
+    // R decides the launch geometry of the sort; read it back like the reference does (rasterizer_impl.cu:284),
+    // together with the range of the depth word, which decides how many digits the sort needs
     uint32_t* h = pinned_ctrl();
-    LSR_CUDA(cudaMemcpyAsync(h, sc.ctrl, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    LSR_CUDA(cudaMemcpyAsync(h, sc.ctrl, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
     LSR_CUDA(cudaStreamSynchronize(s));
     R = (int64_t)h[CTRL_NUM_RENDERED];
     *num_rendered = R;
@@ -236,18 +236,22 @@ int lsr_forward(const lsr_frame* frame, const lsr_inputs* in, float* out_color, 
                                        (long long)R, (long long)list_capacity);
     if (R > 0 && !list) return fail(LSR_ERR_INVALID, "null list buffer");
     prof(g_ev_f, 3, s);
+    // the reference sorts bits [0, 32 + getHigherMsb(T)) (rasterizer_impl.cu:303,311); the depth word only spans
+    // [min, max], so the same order is obtained from hi_bits + bitlength(max - min) bits
+    const SortPlan plan = make_sort_plan(~h[CTRL_DEPTH_NEGMIN], h[CTRL_DEPTH_MAX], (int)higher_msb((uint32_t)T));
+    // the sorted keys always end up in keys_b: the unsorted ones start in keys_a (odd pass count) or keys_b (even)
+    uint64_t* kin = (plan.passes & 1) ? sc.keys_a : sc.keys_b;
+    uint64_t* ktmp = sc.keys_a;
     if (R > 0) {
-      launch_duplicate(P, gx, gy, radii, g, sc.keys_a, sc.vals_a, list_capacity, s);
+      sort_prepare(sc.sort_work, R, plan, s);
+      launch_duplicate(P, gx, gy, radii, g, kin, sc.vals_a, list_capacity, plan,
+                       sort_work_view(sc.sort_work, R).hist, s);
       LSR_STAGE("duplicate");
     }
     prof(g_ev_f, 4, s);
     if (R > 0) {
-      const int end_bit = 32 + (int)higher_msb((uint32_t)T);  // rasterizer_impl.cu:303,311
-      const int passes = (end_bit + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
-      uint64_t* kout = (passes & 1) ? sc.keys_b : sc.keys_a;
-      uint64_t* ktmp = (passes & 1) ? sc.keys_a : sc.keys_b;
-      sort_pairs(sc.keys_a, sc.vals_a, kout, (uint32_t*)list, ktmp, sc.vals_b, R, end_bit, sc.sort_work, s);
-      keys_sorted = kout;
+      sort_pairs(kin, sc.vals_a, sc.keys_b, (uint32_t*)list, ktmp, sc.vals_b, R, plan, true, sc.sort_work, s);
+      keys_sorted = sc.keys_b;
       LSR_STAGE("sort");
     }
     prof(g_ev_f, 5, s);

@@ -103,54 +103,102 @@ scan_tiles_kernel(int P, const uint32_t* __restrict__ in, uint32_t* __restrict__
 // ------------------------------------------------------------------------------------------------------------
 // K3': one (key, value) pair per Gaussian/tile overlap; key = tile_id << 32 | float_bits(depth); rect walked y-major
 // then x, pairs written consecutively from offsets[idx-1]  (rasterizer_impl.cu:85-109).
-// Warp-cooperative: the 32 Gaussians of a warp are emitted one after another by all 32 lanes, so a large rect is
-// written with coalesced stores instead of one thread looping over it.  Small rects (<= 4 tiles) stay per-thread.
+//
+// Load-balanced: a warp owns 32 consecutive Gaussians, whose instances occupy one contiguous output range; the 32
+// lanes walk that range together (lane = consecutive output slot), finding the owning Gaussian of each slot with a
+// 5-step binary search over the lanes' start offsets (shuffles).  Every store instruction therefore writes 32
+// consecutive keys (256 B) / values (128 B) — the reference's one-thread-per-Gaussian loop scatters them.
+// The division by the rect width uses a per-Gaussian magic reciprocal (exact for slot, width < 2^16).
+//
+// The kernel also accumulates the radix sort's digit histograms for every pass (in shared memory, flushed once per
+// CTA), so the sort never reads the keys just to count them.  Passes whose digit lies entirely inside the depth word
+// are counted once per Gaussian with weight tiles_touched; the others per instance, with runs of equal digits in a
+// warp collapsed into one shared-memory atomic.
 // ------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
+constexpr int DUP_THREADS = 256;
+
+__global__ void __launch_bounds__(DUP_THREADS)
 duplicate_kernel(int P, int gx, int gy, const int32_t* __restrict__ radii, const GeomRec* __restrict__ rec,
                  const float* __restrict__ depths, const uint32_t* __restrict__ offsets, uint64_t* __restrict__ keys,
-                 uint32_t* __restrict__ vals, uint32_t capacity) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  const int lane = threadIdx.x & 31;
-  uint32_t x0 = 0, y0 = 0, x1 = 0, y1 = 0, off = 0, dbits = 0;
-  int radius = 0;
-  if (idx < P) radius = radii[idx];
-  if (radius > 0) {
-    const float2 xy = *reinterpret_cast<const float2*>(rec + idx);
-    get_rect(xy.x, xy.y, radius, gx, gy, x0, y0, x1, y1);
-    off = idx == 0 ? 0u : offsets[idx - 1];
-    dbits = __float_as_uint(depths[idx]);
-  }
-  const uint32_t w = x1 - x0;
-  const uint32_t n = w * (y1 - y0);
-  constexpr uint32_t SMALL = 4;
-  if (n > 0 && n <= SMALL) {
-    for (uint32_t i = 0; i < n; i++) {
-      const uint32_t y = y0 + i / w, x = x0 + i % w;
-      const uint32_t o = off + i;
-      if (o < capacity) {
-        keys[o] = ((uint64_t)(y * gx + x) << 32) | dbits;
-        vals[o] = (uint32_t)idx;
+                 uint32_t* __restrict__ vals, uint32_t capacity, SortPlan plan, uint32_t* __restrict__ ghist) {
+  __shared__ uint32_t s_hist[SORT_MAX_PASSES * SORT_BINS];
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int passes = plan.passes;
+  for (int j = tid; j < passes * SORT_BINS; j += DUP_THREADS) s_hist[j] = 0;
+  __syncthreads();
+  // passes [0, per_gaussian) take their digit from the depth word only
+  const int per_gaussian = min(passes, plan.lo_bits / SORT_RADIX_BITS);
+  const int nblocks = (P + DUP_THREADS - 1) / DUP_THREADS;
+  for (int blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
+    const int idx = blk * DUP_THREADS + tid;
+    uint32_t x0 = 0, y0 = 0, x1 = 0, y1 = 0, incl = 0, dbits = 0;
+    int radius = 0;
+    if (idx < P) radius = radii[idx];
+    incl = offsets[min(idx, P - 1)];  // lanes past the end sit at the end of the output range with zero instances
+    if (radius > 0) {
+      const float2 xy = *reinterpret_cast<const float2*>(rec + idx);
+      get_rect(xy.x, xy.y, radius, gx, gy, x0, y0, x1, y1);
+      dbits = __float_as_uint(depths[idx]);
+    }
+    const uint32_t w = x1 - x0;
+    const uint32_t cnt = w * (y1 - y0);
+    const uint32_t start = incl - cnt;                                  // exclusive offset of this Gaussian
+    const uint32_t wstart = __shfl_sync(0xffffffffu, start, 0);          // warp's output range [wstart, wend)
+    const uint32_t wend = __shfl_sync(0xffffffffu, incl, 31);
+    const uint32_t rel = start - wstart;
+    const uint32_t magic = w > 1 ? (uint32_t)((0x100000000ull + w - 1) / w) : 0u;
+    const uint32_t origin = (y0 << 16) | x0;
+    const uint32_t lo = dbits - plan.lo_min;
+    if (cnt > 0) {
+      for (int p = 0; p < per_gaussian; p++)
+        atomicAdd(&s_hist[p * SORT_BINS + ((lo >> (p * SORT_RADIX_BITS)) & (SORT_BINS - 1))], cnt);
+    }
+    const uint32_t total = wend - wstart;
+    const int wbase_idx = blk * DUP_THREADS + (tid & ~31);
+    for (uint32_t k0 = 0; k0 < total; k0 += 32) {
+      const uint32_t k = k0 + lane;
+      // last lane j with rel_j <= k (zero-count lanes share their successor's start, so they are never picked)
+      int j = 0;
+#pragma unroll
+      for (int step = 16; step > 0; step >>= 1) {
+        const uint32_t r = __shfl_sync(0xffffffffu, rel, (j + step) & 31);
+        if (r <= k) j += step;
+      }
+      const uint32_t jrel = __shfl_sync(0xffffffffu, rel, j);
+      const uint32_t jw = __shfl_sync(0xffffffffu, w, j);
+      const uint32_t jmagic = __shfl_sync(0xffffffffu, magic, j);
+      const uint32_t jorigin = __shfl_sync(0xffffffffu, origin, j);
+      const uint32_t jd = __shfl_sync(0xffffffffu, dbits, j);
+      const bool ok = k < total;
+      const uint32_t r = k - jrel;
+      const uint32_t q = jw > 1 ? __umulhi(r, jmagic) : r;  // r / jw
+      const uint32_t y = (jorigin >> 16) + q, x = (jorigin & 0xffffu) + (r - q * jw);
+      const uint32_t tile = y * (uint32_t)gx + x;
+      const uint32_t o = wstart + k;
+      if (ok && o < capacity) {
+        keys[o] = ((uint64_t)tile << 32) | jd;
+        vals[o] = (uint32_t)(wbase_idx + j);
+      }
+      // digits that involve tile bits: one shared atomic per run of equal digits
+      const uint64_t c = ((uint64_t)tile << plan.lo_bits) | (uint64_t)(jd - plan.lo_min);
+      for (int p = per_gaussian; p < passes; p++) {
+        const int shift = p * SORT_RADIX_BITS;
+        const int bits = min(SORT_RADIX_BITS, plan.total_bits - shift);
+        const uint32_t d = ok ? ((uint32_t)(c >> shift) & ((1u << bits) - 1)) : 0xffffffffu;
+        const uint32_t prev = __shfl_up_sync(0xffffffffu, d, 1);
+        const bool head = (lane == 0) || (prev != d);
+        const uint32_t heads = __ballot_sync(0xffffffffu, head);
+        if (head && ok) {
+          const uint32_t later = lane == 31 ? 0u : (heads >> (lane + 1));
+          const int run = later ? __ffs(later) : (32 - lane);
+          atomicAdd(&s_hist[p * SORT_BINS + d], (uint32_t)run);
+        }
       }
     }
   }
-  uint32_t big = __ballot_sync(0xffffffffu, n > SMALL);
-  while (big) {
-    const int src = __ffs(big) - 1;
-    big &= big - 1;
-    const uint32_t bx0 = __shfl_sync(0xffffffffu, x0, src), by0 = __shfl_sync(0xffffffffu, y0, src);
-    const uint32_t bw = __shfl_sync(0xffffffffu, w, src), bn = __shfl_sync(0xffffffffu, n, src);
-    const uint32_t boff = __shfl_sync(0xffffffffu, off, src), bd = __shfl_sync(0xffffffffu, dbits, src);
-    const uint32_t bidx = __shfl_sync(0xffffffffu, (uint32_t)idx, src);
-    for (uint32_t i = lane; i < bn; i += 32) {
-      const uint32_t y = by0 + i / bw, x = bx0 + i % bw;
-      const uint32_t o = boff + i;
-      if (o < capacity) {
-        keys[o] = ((uint64_t)(y * gx + x) << 32) | bd;
-        vals[o] = bidx;
-      }
-    }
-  }
+  __syncthreads();
+  for (int j = tid; j < passes * SORT_BINS; j += DUP_THREADS)
+    if (s_hist[j]) atomicAdd(&ghist[j], s_hist[j]);
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -184,10 +232,12 @@ void launch_scan_tiles(int P, const uint32_t* tiles, uint32_t* offsets, uint64_t
 }
 
 void launch_duplicate(int P, int grid_x, int grid_y, const int32_t* radii, GeomView g, uint64_t* keys, uint32_t* vals,
-                      int64_t capacity, cudaStream_t s) {
+                      int64_t capacity, const SortPlan& plan, uint32_t* ghist, cudaStream_t s) {
   if (P <= 0) return;
-  duplicate_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, grid_x, grid_y, radii, g.rec, g.depth, g.offsets, keys, vals,
-                                                   (uint32_t)capacity);
+  const int nblocks = (P + DUP_THREADS - 1) / DUP_THREADS;
+  const int grid = nblocks < 148 * 8 ? nblocks : 148 * 8;  // persistent CTAs: one histogram flush each
+  duplicate_kernel<<<grid, DUP_THREADS, 0, s>>>(P, grid_x, grid_y, radii, g.rec, g.depth, g.offsets, keys, vals,
+                                                (uint32_t)capacity, plan, ghist);
   count_launch();
 }
 

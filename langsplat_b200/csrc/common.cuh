@@ -77,7 +77,7 @@ constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // keys per CTA per pass
 constexpr int SORT_MAX_PASSES = 8;
 
 struct SortWork {  // carved from the `work` buffer
-  uint32_t* hist;      // [SORT_MAX_PASSES][SORT_BINS] global digit histograms -> exclusive bases
+  uint32_t* hist;      // [SORT_MAX_PASSES][SORT_BINS] global digit histograms (raw counts)
   uint32_t* tickets;   // [SORT_MAX_PASSES] dynamic tile ids
   uint32_t* lookback;  // [SORT_MAX_PASSES][nblocks][SORT_BINS]
   size_t zero_bytes;   // bytes from hist to the end that must be zero before a sort
@@ -132,7 +132,16 @@ inline size_t scratch_bytes(int P, int64_t cap) {
   return 256 + align_up(scan_nblocks(P) * 8) + 2 * align_up(c * 8) + 2 * align_up(c * 4) + sort_work_bytes(cap) + 256;
 }
 
-enum CtrlWord { CTRL_NUM_RENDERED = 0, CTRL_SCAN_TICKET = 1, CTRL_ERROR = 2 };
+// ctrl words (zeroed at the start of every forward).  DEPTH_NEGMIN holds max(~bits) so that zero-init works.
+enum CtrlWord { CTRL_NUM_RENDERED = 0, CTRL_SCAN_TICKET = 1, CTRL_ERROR = 2, CTRL_DEPTH_NEGMIN = 3, CTRL_DEPTH_MAX = 4 };
+
+// Which bits the sort has to look at: digits are taken from (hi << lo_bits) | (lo - lo_min)  (radix_sort.cu).
+struct SortPlan {
+  uint32_t lo_min;
+  int lo_bits, hi_bits, total_bits, passes;
+};
+SortPlan make_sort_plan(uint32_t lo_min, uint32_t lo_max, int hi_bits);
+SortPlan make_sort_plan_bits(int end_bit);
 
 // ---- launchers implemented in the .cu files ----
 void launch_preprocess_fwd(const lsr_frame& f, const lsr_inputs& in, float focal_x, float focal_y, int32_t* radii,
@@ -140,10 +149,13 @@ void launch_preprocess_fwd(const lsr_frame& f, const lsr_inputs& in, float focal
 void launch_scan_tiles(int P, const uint32_t* tiles, uint32_t* offsets, uint64_t* status, uint32_t* ctrl,
                        cudaStream_t s);
 void launch_duplicate(int P, int grid_x, int grid_y, const int32_t* radii, GeomView g, uint64_t* keys, uint32_t* vals,
-                      int64_t capacity, cudaStream_t s);
+                      int64_t capacity, const SortPlan& plan, uint32_t* ghist, cudaStream_t s);
 void launch_tile_ranges(int64_t R, const uint64_t* keys, uint2* ranges, cudaStream_t s);
+// hist_ready: the per-pass digit histograms are already in the work buffer (sort_prepare + duplication kernel)
+void sort_prepare(void* work, int64_t n, const SortPlan& pl, cudaStream_t s);
 int sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
-               uint64_t* keys_tmp, uint32_t* vals_tmp, int64_t n, int end_bit, void* work, cudaStream_t s);
+               uint64_t* keys_tmp, uint32_t* vals_tmp, int64_t n, const SortPlan& pl, bool hist_ready, void* work,
+               cudaStream_t s);
 void launch_render_fwd(int W, int H, const uint2* ranges, const uint32_t* list, const GeomRec* rec, const float* bg,
                        bool include_feature, float* final_T, uint32_t* n_contrib, float* out_color,
                        float* out_feature, cudaStream_t s);

@@ -7,6 +7,7 @@
 // Gaussians with radius 0), so the caller can hand in uninitialised memory.  HBM-bound.
 #include "common.cuh"
 #include "gs_math.cuh"
+#include "stage.cuh"
 
 namespace lsr {
 
@@ -23,13 +24,15 @@ __device__ __forceinline__ float3 dnormvdv(float3 v, float3 dv) {  // RAST/cuda_
 }
 
 // SH backward: writes dL_dsh rows [0,(D+1)^2), zero for the rest up to M, returns dL/d(mean) through the direction.
-__device__ __forceinline__ float3 sh_backward(int deg, int M, const float* __restrict__ sh, float3 dir_orig,
-                                              float3 dL_dRGB, float* __restrict__ dsh) {
+template <bool WRITE>
+__device__ __forceinline__ float3 sh_backward_t(int deg, int M, const float* __restrict__ sh, float3 dir_orig,
+                                                float3 dL_dRGB, float* __restrict__ dsh) {
   const float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
   const float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
   const float g[3] = {dL_dRGB.x, dL_dRGB.y, dL_dRGB.z};
   float dRGBdx[3] = {0, 0, 0}, dRGBdy[3] = {0, 0, 0}, dRGBdz[3] = {0, 0, 0};
   auto put = [&](int k, float w) {
+    if (!WRITE) return;
     dsh[k * 3 + 0] = w * g[0];
     dsh[k * 3 + 1] = w * g[1];
     dsh[k * 3 + 2] = w * g[2];
@@ -92,7 +95,8 @@ __device__ __forceinline__ float3 sh_backward(int deg, int M, const float* __res
       }
     }
   }
-  for (int k = written; k < M; k++) put(k, 0.f);  // entries above the active degree stay zero
+  if (WRITE)
+    for (int k = written; k < M; k++) put(k, 0.f);  // entries above the active degree stay zero
   float3 dL_ddir;
   dL_ddir.x = dRGBdx[0] * g[0] + dRGBdx[1] * g[1] + dRGBdx[2] * g[2];
   dL_ddir.y = dRGBdy[0] * g[0] + dRGBdy[1] * g[1] + dRGBdy[2] * g[2];
@@ -100,7 +104,43 @@ __device__ __forceinline__ float3 sh_backward(int deg, int M, const float* __res
   return dnormvdv(dir_orig, dL_ddir);
 }
 
-__global__ void __launch_bounds__(256)
+__device__ __forceinline__ float3 sh_backward(int deg, int M, const float* __restrict__ sh, float3 dir_orig,
+                                              float3 dL_dRGB, float* __restrict__ dsh) {
+  return sh_backward_t<true>(deg, M, sh, dir_orig, dL_dRGB, dsh);
+}
+// direction gradient only (the dL_dsh rows are produced from sh_basis by the caller)
+__device__ __forceinline__ float3 sh_dir_backward(int deg, const float* sh, float3 dir_orig, const float (&g)[3]) {
+  return sh_backward_t<false>(deg, 16, sh, dir_orig, make_float3(g[0], g[1], g[2]), nullptr);
+}
+
+// SH basis values b[k] with dRGB/dsh[k][ch] = b[k] * dL_dRGB[ch]; zero above the active degree (backward.cu:36-129).
+__device__ __forceinline__ void sh_basis(int deg, float x, float y, float z, float (&b)[16]) {
+#pragma unroll
+  for (int k = 0; k < 16; k++) b[k] = 0.f;
+  b[0] = LSR_SH_C0;
+  if (deg > 0) {
+    b[1] = -LSR_SH_C1 * y; b[2] = LSR_SH_C1 * z; b[3] = -LSR_SH_C1 * x;
+    if (deg > 1) {
+      const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+      b[4] = LSR_SH_C2_0 * xy; b[5] = LSR_SH_C2_1 * yz; b[6] = LSR_SH_C2_2 * (2.f * zz - xx - yy);
+      b[7] = LSR_SH_C2_3 * xz; b[8] = LSR_SH_C2_4 * (xx - yy);
+      if (deg > 2) {
+        b[9] = LSR_SH_C3_0 * y * (3.f * xx - yy); b[10] = LSR_SH_C3_1 * xy * z;
+        b[11] = LSR_SH_C3_2 * y * (4.f * zz - xx - yy); b[12] = LSR_SH_C3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy);
+        b[13] = LSR_SH_C3_4 * x * (4.f * zz - xx - yy); b[14] = LSR_SH_C3_5 * z * (xx - yy);
+        b[15] = LSR_SH_C3_6 * x * (xx - 3.f * yy);
+      }
+    }
+  }
+}
+
+constexpr int BPRE_THREADS = 256;
+constexpr int SH_ROW = 12;
+constexpr size_t BPRE_SH_SMEM = (size_t)(BPRE_THREADS / 32) * 32 * (SH_ROW + 1) * sizeof(float4);
+
+// SH16: shs / dL_dsh are [P,16,3], 16-byte aligned -> rows move through shared memory as coalesced 16-byte chunks.
+template <bool SH16>
+__global__ void __launch_bounds__(BPRE_THREADS)
 preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, const int32_t* __restrict__ radii,
                       const float* __restrict__ shs, const uint8_t* __restrict__ clamped,
                       const float* __restrict__ scales, const float* __restrict__ rotations, float scale_modifier,
@@ -110,115 +150,193 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
                       const float* __restrict__ dL_dconic, const float* __restrict__ dL_dcolor,
                       float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
                       float* __restrict__ dL_dscale, float* __restrict__ dL_drot) {
+  extern __shared__ __align__(16) float4 s_dyn[];
+  __shared__ __align__(16) float s_xyz[BPRE_THREADS * 3];   // means3D in, dL_dmean3D out
+  __shared__ __align__(16) float s_scl[BPRE_THREADS * 3];   // scales in, dL_dscale out
+  __shared__ __align__(16) float s_m2d[BPRE_THREADS * 3];   // dL_dmean2D in
+  __shared__ __align__(16) float s_dcol[BPRE_THREADS * 3];  // dL_dcolor in
   __shared__ float s_view[16], s_proj[16], s_cam[3];
-  if (threadIdx.x < 16) {
-    s_view[threadIdx.x] = viewmatrix[threadIdx.x];
-    s_proj[threadIdx.x] = projmatrix[threadIdx.x];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int first = blockIdx.x * BPRE_THREADS;
+  const int count = min(BPRE_THREADS, P - first);
+  if (tid < 16) {
+    s_view[tid] = viewmatrix[tid];
+    s_proj[tid] = projmatrix[tid];
   }
-  if (threadIdx.x < 3) s_cam[threadIdx.x] = campos[threadIdx.x];
+  if (tid < 3) s_cam[tid] = campos[tid];
+  const bool do_sh = shs != nullptr && dL_dsh != nullptr && dL_dcolor != nullptr;
+  const bool do_scale = scales != nullptr && dL_dscale != nullptr;
+  stage_flat<BPRE_THREADS>(means3D, s_xyz, (size_t)first * 3, count * 3, tid);
+  stage_flat<BPRE_THREADS>(dL_dmean2D, s_m2d, (size_t)first * 3, count * 3, tid);
+  if (do_scale) stage_flat<BPRE_THREADS>(scales, s_scl, (size_t)first * 3, count * 3, tid);
+  if (do_sh) stage_flat<BPRE_THREADS>(dL_dcolor, s_dcol, (size_t)first * 3, count * 3, tid);
   __syncthreads();
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= P) return;
-  if (!(radii[idx] > 0)) {
-    if (dL_dmean3D) { dL_dmean3D[3 * (size_t)idx] = 0.f; dL_dmean3D[3 * (size_t)idx + 1] = 0.f; dL_dmean3D[3 * (size_t)idx + 2] = 0.f; }
-    if (dL_dcov3D) for (int i = 0; i < 6; i++) dL_dcov3D[6 * (size_t)idx + i] = 0.f;
-    if (dL_dsh) for (int i = 0; i < M * 3; i++) dL_dsh[(size_t)idx * M * 3 + i] = 0.f;
-    if (dL_dscale) for (int i = 0; i < 3; i++) dL_dscale[3 * (size_t)idx + i] = 0.f;
-    if (dL_drot) reinterpret_cast<float4*>(dL_drot)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
-    return;
-  }
-  const float mx = means3D[3 * (size_t)idx], my = means3D[3 * (size_t)idx + 1], mz = means3D[3 * (size_t)idx + 2];
-  float cov3D[6];
-#pragma unroll
-  for (int i = 0; i < 6; i++) cov3D[i] = cov3Ds[6 * (size_t)idx + i];
+  const bool valid = tid < count;
+  const int idx = first + tid;
+  const bool vis = valid && radii[idx] > 0;
+  const uint32_t vis_mask = __ballot_sync(0xffffffffu, vis);
+  const uint32_t valid_mask = __ballot_sync(0xffffffffu, valid);
+  float4* wsm = s_dyn + (size_t)warp * 32 * (SH_ROW + 1);
+  const size_t wfirst = (size_t)(first + warp * 32);
 
-  // ---------------- computeCov2DCUDA (backward.cu:144-274) ----------------
-  Cov2D c2;
-  compute_cov2D(mx, my, mz, h_x, h_y, tan_fovx, tan_fovy, cov3D, s_view, c2);
-  const float4 dcon = reinterpret_cast<const float4*>(dL_dconic)[idx];
-  const float dLc_x = dcon.x, dLc_y = dcon.y, dLc_z = dcon.w;
-  const float x_grad_mul = (c2.txtz < -c2.limx || c2.txtz > c2.limx) ? 0.f : 1.f;
-  const float y_grad_mul = (c2.tytz < -c2.limy || c2.tytz > c2.limy) ? 0.f : 1.f;
-  const Mat3& T = c2.T;
-  const Mat3& Vrk = c2.Vrk;
-  const Mat3& Wm = c2.W;
-  const float a = c2.a, b = c2.b, c = c2.c;
-  const float denom = a * c - b * b;
-  float dL_da = 0, dL_db = 0, dL_dc = 0;
-  const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
-  float dcov[6] = {0, 0, 0, 0, 0, 0};
-  if (denom2inv != 0) {
-    dL_da = denom2inv * (-c * c * dLc_x + 2 * b * c * dLc_y + (denom - a * c) * dLc_z);
-    dL_dc = denom2inv * (-a * a * dLc_z + 2 * a * b * dLc_y + (denom - a * c) * dLc_x);
-    dL_db = denom2inv * 2 * (b * c * dLc_x - (denom + 2 * b * b) * dLc_y + a * b * dLc_z);
-    dcov[0] = (T.m[0][0] * T.m[0][0] * dL_da + T.m[0][0] * T.m[1][0] * dL_db + T.m[1][0] * T.m[1][0] * dL_dc);
-    dcov[3] = (T.m[0][1] * T.m[0][1] * dL_da + T.m[0][1] * T.m[1][1] * dL_db + T.m[1][1] * T.m[1][1] * dL_dc);
-    dcov[5] = (T.m[0][2] * T.m[0][2] * dL_da + T.m[0][2] * T.m[1][2] * dL_db + T.m[1][2] * T.m[1][2] * dL_dc);
-    dcov[1] = 2 * T.m[0][0] * T.m[0][1] * dL_da + (T.m[0][0] * T.m[1][1] + T.m[0][1] * T.m[1][0]) * dL_db +
-              2 * T.m[1][0] * T.m[1][1] * dL_dc;
-    dcov[2] = 2 * T.m[0][0] * T.m[0][2] * dL_da + (T.m[0][0] * T.m[1][2] + T.m[0][2] * T.m[1][0]) * dL_db +
-              2 * T.m[1][0] * T.m[1][2] * dL_dc;
-    dcov[4] = 2 * T.m[0][2] * T.m[0][1] * dL_da + (T.m[0][1] * T.m[1][2] + T.m[0][2] * T.m[1][1]) * dL_db +
-              2 * T.m[1][1] * T.m[1][2] * dL_dc;
-  }
-  if (dL_dcov3D) {
-#pragma unroll
-    for (int i = 0; i < 6; i++) dL_dcov3D[6 * (size_t)idx + i] = dcov[i];
-  }
-  auto row = [&](int r, int k) { return T.m[r][0] * Vrk.m[k][0] + T.m[r][1] * Vrk.m[k][1] + T.m[r][2] * Vrk.m[k][2]; };
-  const float dL_dT00 = 2 * row(0, 0) * dL_da + row(1, 0) * dL_db;
-  const float dL_dT01 = 2 * row(0, 1) * dL_da + row(1, 1) * dL_db;
-  const float dL_dT02 = 2 * row(0, 2) * dL_da + row(1, 2) * dL_db;
-  const float dL_dT10 = 2 * row(1, 0) * dL_dc + row(0, 0) * dL_db;
-  const float dL_dT11 = 2 * row(1, 1) * dL_dc + row(0, 1) * dL_db;
-  const float dL_dT12 = 2 * row(1, 2) * dL_dc + row(0, 2) * dL_db;
-  const float dL_dJ00 = Wm.m[0][0] * dL_dT00 + Wm.m[0][1] * dL_dT01 + Wm.m[0][2] * dL_dT02;
-  const float dL_dJ02 = Wm.m[2][0] * dL_dT00 + Wm.m[2][1] * dL_dT01 + Wm.m[2][2] * dL_dT02;
-  const float dL_dJ11 = Wm.m[1][0] * dL_dT10 + Wm.m[1][1] * dL_dT11 + Wm.m[1][2] * dL_dT12;
-  const float dL_dJ12 = Wm.m[2][0] * dL_dT10 + Wm.m[2][1] * dL_dT11 + Wm.m[2][2] * dL_dT12;
-  const float tz = 1.f / c2.tz, tz2 = tz * tz, tz3 = tz2 * tz;
-  const float dL_dtx = x_grad_mul * -h_x * tz2 * dL_dJ02;
-  const float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
-  const float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * c2.tx) * tz3 * dL_dJ02 +
-                       (2 * h_y * c2.ty) * tz3 * dL_dJ12;
-  float3 dmean;  // transformVec4x3Transpose
-  dmean.x = s_view[0] * dL_dtx + s_view[1] * dL_dty + s_view[2] * dL_dtz;
-  dmean.y = s_view[4] * dL_dtx + s_view[5] * dL_dty + s_view[6] * dL_dtz;
-  dmean.z = s_view[8] * dL_dtx + s_view[9] * dL_dty + s_view[10] * dL_dtz;
-
-  // ---------------- preprocessCUDA backward (backward.cu:346-396) ----------------
+  // cov3D rows of the warp's visible Gaussians: coalesced 8-byte chunks through shared memory
+  float cov3D[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   {
+    float2* w2 = reinterpret_cast<float2*>(wsm);
+    const float2* src = reinterpret_cast<const float2*>(cov3Ds + wfirst * 6);
+#pragma unroll
+    for (int it = 0; it < 3; it++) {
+      const int c = it * 32 + lane;
+      if ((vis_mask >> (c / 3)) & 1u) w2[c] = __ldg(src + c);
+    }
+    __syncwarp();
+    if (vis) {
+      const float2 a = w2[lane * 3], b = w2[lane * 3 + 1], c = w2[lane * 3 + 2];
+      cov3D[0] = a.x; cov3D[1] = a.y; cov3D[2] = b.x; cov3D[3] = b.y; cov3D[4] = c.x; cov3D[5] = c.y;
+    }
+    __syncwarp();
+  }
+  const float mx = s_xyz[3 * tid], my = s_xyz[3 * tid + 1], mz = s_xyz[3 * tid + 2];
+  float dcov[6] = {0, 0, 0, 0, 0, 0};
+  float3 dmean = make_float3(0.f, 0.f, 0.f);
+  if (vis) {
+    // ---------------- computeCov2DCUDA (backward.cu:144-274) ----------------
+    Cov2D c2;
+    compute_cov2D(mx, my, mz, h_x, h_y, tan_fovx, tan_fovy, cov3D, s_view, c2);
+    const float4 dcon = __ldg(reinterpret_cast<const float4*>(dL_dconic) + idx);
+    const float dLc_x = dcon.x, dLc_y = dcon.y, dLc_z = dcon.w;
+    const float x_grad_mul = (c2.txtz < -c2.limx || c2.txtz > c2.limx) ? 0.f : 1.f;
+    const float y_grad_mul = (c2.tytz < -c2.limy || c2.tytz > c2.limy) ? 0.f : 1.f;
+    const Mat3& T = c2.T;
+    const Mat3& Vrk = c2.Vrk;
+    const Mat3& Wm = c2.W;
+    const float a = c2.a, b = c2.b, c = c2.c;
+    const float denom = a * c - b * b;
+    float dL_da = 0, dL_db = 0, dL_dc = 0;
+    const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+    if (denom2inv != 0) {
+      dL_da = denom2inv * (-c * c * dLc_x + 2 * b * c * dLc_y + (denom - a * c) * dLc_z);
+      dL_dc = denom2inv * (-a * a * dLc_z + 2 * a * b * dLc_y + (denom - a * c) * dLc_x);
+      dL_db = denom2inv * 2 * (b * c * dLc_x - (denom + 2 * b * b) * dLc_y + a * b * dLc_z);
+      dcov[0] = (T.m[0][0] * T.m[0][0] * dL_da + T.m[0][0] * T.m[1][0] * dL_db + T.m[1][0] * T.m[1][0] * dL_dc);
+      dcov[3] = (T.m[0][1] * T.m[0][1] * dL_da + T.m[0][1] * T.m[1][1] * dL_db + T.m[1][1] * T.m[1][1] * dL_dc);
+      dcov[5] = (T.m[0][2] * T.m[0][2] * dL_da + T.m[0][2] * T.m[1][2] * dL_db + T.m[1][2] * T.m[1][2] * dL_dc);
+      dcov[1] = 2 * T.m[0][0] * T.m[0][1] * dL_da + (T.m[0][0] * T.m[1][1] + T.m[0][1] * T.m[1][0]) * dL_db +
+                2 * T.m[1][0] * T.m[1][1] * dL_dc;
+      dcov[2] = 2 * T.m[0][0] * T.m[0][2] * dL_da + (T.m[0][0] * T.m[1][2] + T.m[0][2] * T.m[1][0]) * dL_db +
+                2 * T.m[1][0] * T.m[1][2] * dL_dc;
+      dcov[4] = 2 * T.m[0][2] * T.m[0][1] * dL_da + (T.m[0][1] * T.m[1][2] + T.m[0][2] * T.m[1][1]) * dL_db +
+                2 * T.m[1][1] * T.m[1][2] * dL_dc;
+    }
+    auto row = [&](int r, int k) { return T.m[r][0] * Vrk.m[k][0] + T.m[r][1] * Vrk.m[k][1] + T.m[r][2] * Vrk.m[k][2]; };
+    const float dL_dT00 = 2 * row(0, 0) * dL_da + row(1, 0) * dL_db;
+    const float dL_dT01 = 2 * row(0, 1) * dL_da + row(1, 1) * dL_db;
+    const float dL_dT02 = 2 * row(0, 2) * dL_da + row(1, 2) * dL_db;
+    const float dL_dT10 = 2 * row(1, 0) * dL_dc + row(0, 0) * dL_db;
+    const float dL_dT11 = 2 * row(1, 1) * dL_dc + row(0, 1) * dL_db;
+    const float dL_dT12 = 2 * row(1, 2) * dL_dc + row(0, 2) * dL_db;
+    const float dL_dJ00 = Wm.m[0][0] * dL_dT00 + Wm.m[0][1] * dL_dT01 + Wm.m[0][2] * dL_dT02;
+    const float dL_dJ02 = Wm.m[2][0] * dL_dT00 + Wm.m[2][1] * dL_dT01 + Wm.m[2][2] * dL_dT02;
+    const float dL_dJ11 = Wm.m[1][0] * dL_dT10 + Wm.m[1][1] * dL_dT11 + Wm.m[1][2] * dL_dT12;
+    const float dL_dJ12 = Wm.m[2][0] * dL_dT10 + Wm.m[2][1] * dL_dT11 + Wm.m[2][2] * dL_dT12;
+    const float tz = 1.f / c2.tz, tz2 = tz * tz, tz3 = tz2 * tz;
+    const float dL_dtx = x_grad_mul * -h_x * tz2 * dL_dJ02;
+    const float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
+    const float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * c2.tx) * tz3 * dL_dJ02 +
+                         (2 * h_y * c2.ty) * tz3 * dL_dJ12;
+    // transformVec4x3Transpose
+    dmean.x = s_view[0] * dL_dtx + s_view[1] * dL_dty + s_view[2] * dL_dtz;
+    dmean.y = s_view[4] * dL_dtx + s_view[5] * dL_dty + s_view[6] * dL_dtz;
+    dmean.z = s_view[8] * dL_dtx + s_view[9] * dL_dty + s_view[10] * dL_dtz;
+
+    // ---------------- preprocessCUDA backward (backward.cu:346-396) ----------------
     const float* proj = s_proj;
     const float m_hw = proj[3] * mx + proj[7] * my + proj[11] * mz + proj[15];
     const float m_w = 1.0f / (m_hw + 0.0000001f);
     const float mul1 = (proj[0] * mx + proj[4] * my + proj[8] * mz + proj[12]) * m_w * m_w;
     const float mul2 = (proj[1] * mx + proj[5] * my + proj[9] * mz + proj[13]) * m_w * m_w;
-    const float gx_ = dL_dmean2D[3 * (size_t)idx], gy_ = dL_dmean2D[3 * (size_t)idx + 1];
+    const float gx_ = s_m2d[3 * tid], gy_ = s_m2d[3 * tid + 1];
     dmean.x += (proj[0] * m_w - proj[3] * mul1) * gx_ + (proj[1] * m_w - proj[3] * mul2) * gy_;
     dmean.y += (proj[4] * m_w - proj[7] * mul1) * gx_ + (proj[5] * m_w - proj[7] * mul2) * gy_;
     dmean.z += (proj[8] * m_w - proj[11] * mul1) * gx_ + (proj[9] * m_w - proj[11] * mul2) * gy_;
   }
-  if (shs != nullptr && dL_dsh != nullptr && dL_dcolor != nullptr) {
-    const uint8_t cl = clamped[idx];
-    float3 g;
-    g.x = (cl & 1) ? 0.f : dL_dcolor[3 * (size_t)idx];
-    g.y = (cl & 2) ? 0.f : dL_dcolor[3 * (size_t)idx + 1];
-    g.z = (cl & 4) ? 0.f : dL_dcolor[3 * (size_t)idx + 2];
-    const float3 dir = make_float3(mx - s_cam[0], my - s_cam[1], mz - s_cam[2]);
-    const float3 dm = sh_backward(D, M, shs + (size_t)idx * M * 3, dir, g, dL_dsh + (size_t)idx * M * 3);
-    dmean.x += dm.x; dmean.y += dm.y; dmean.z += dm.z;
+  // dL_dcov3D: coalesced write-out (zeros for Gaussians with radius 0)
+  if (dL_dcov3D) {
+    float2* w2 = reinterpret_cast<float2*>(wsm);
+    w2[lane * 3] = make_float2(dcov[0], dcov[1]);
+    w2[lane * 3 + 1] = make_float2(dcov[2], dcov[3]);
+    w2[lane * 3 + 2] = make_float2(dcov[4], dcov[5]);
+    __syncwarp();
+    float2* dst = reinterpret_cast<float2*>(dL_dcov3D + wfirst * 6);
+#pragma unroll
+    for (int it = 0; it < 3; it++) {
+      const int c = it * 32 + lane;
+      if ((valid_mask >> (c / 3)) & 1u) dst[c] = w2[c];
+    }
+    __syncwarp();
   }
-  if (dL_dmean3D) {
-    dL_dmean3D[3 * (size_t)idx] = dmean.x;
-    dL_dmean3D[3 * (size_t)idx + 1] = dmean.y;
-    dL_dmean3D[3 * (size_t)idx + 2] = dmean.z;
+  // ---------------- SH colour backward (backward.cu:20-139) ----------------
+  if (do_sh) {
+    if (SH16) {
+      warp_load_rows<SH_ROW>(reinterpret_cast<const float4*>(shs) + wfirst * SH_ROW, wsm, vis_mask, lane);
+      __syncwarp();
+      if (vis) {
+        const uint8_t cl = clamped[idx];
+        const float g[3] = {(cl & 1) ? 0.f : s_dcol[3 * tid], (cl & 2) ? 0.f : s_dcol[3 * tid + 1],
+                            (cl & 4) ? 0.f : s_dcol[3 * tid + 2]};
+        const float3 dir = make_float3(mx - s_cam[0], my - s_cam[1], mz - s_cam[2]);
+        float v[48];
+#pragma unroll
+        for (int i = 0; i < SH_ROW; i++) {
+          const float4 t = wsm[row_slot<SH_ROW>(lane, i)];
+          v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+        }
+        const float3 dm = sh_dir_backward(D, v, dir, g);
+        dmean.x += dm.x; dmean.y += dm.y; dmean.z += dm.z;
+        const float len = sqrtf(dir.x * dir.x + dir.y * dir.y + dir.z * dir.z);
+        float bs[16];
+        sh_basis(D, dir.x / len, dir.y / len, dir.z / len, bs);
+#pragma unroll
+        for (int i = 0; i < SH_ROW; i++) {
+          float4 o;
+          o.x = bs[(4 * i) / 3] * g[(4 * i) % 3];
+          o.y = bs[(4 * i + 1) / 3] * g[(4 * i + 1) % 3];
+          o.z = bs[(4 * i + 2) / 3] * g[(4 * i + 2) % 3];
+          o.w = bs[(4 * i + 3) / 3] * g[(4 * i + 3) % 3];
+          wsm[row_slot<SH_ROW>(lane, i)] = o;
+        }
+      }
+      __syncwarp();
+      warp_store_rows<SH_ROW>(reinterpret_cast<float4*>(dL_dsh) + wfirst * SH_ROW, wsm, vis_mask, valid_mask, true,
+                              lane);
+      __syncwarp();
+    } else if (valid) {
+      float* dsh = dL_dsh + (size_t)idx * M * 3;
+      if (vis) {
+        const uint8_t cl = clamped[idx];
+        float3 g;
+        g.x = (cl & 1) ? 0.f : s_dcol[3 * tid];
+        g.y = (cl & 2) ? 0.f : s_dcol[3 * tid + 1];
+        g.z = (cl & 4) ? 0.f : s_dcol[3 * tid + 2];
+        const float3 dir = make_float3(mx - s_cam[0], my - s_cam[1], mz - s_cam[2]);
+        const float3 dm = sh_backward(D, M, shs + (size_t)idx * M * 3, dir, g, dsh);
+        dmean.x += dm.x; dmean.y += dm.y; dmean.z += dm.z;
+      } else {
+        for (int i = 0; i < M * 3; i++) dsh[i] = 0.f;
+      }
+    }
+  } else if (dL_dsh != nullptr && valid && M > 0 && !vis) {
+    // (the caller zero-fills dL_dsh when the SH backward does not run at all; nothing to do here)
   }
-  if (scales != nullptr && dL_dscale != nullptr) {  // computeCov3D backward (backward.cu:278-341)
-    const float4 q = reinterpret_cast<const float4*>(rotations)[idx];
+  // ---------------- computeCov3D backward (backward.cu:278-341) ----------------
+  float dscale[3] = {0.f, 0.f, 0.f};
+  float4 dq = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (do_scale && vis) {
+    const float4 q = __ldg(reinterpret_cast<const float4*>(rotations) + idx);
     const float r = q.x, x = q.y, y = q.z, z = q.w;
     const Mat3 R = quat_to_mat(r, x, y, z);
-    const float s[3] = {scale_modifier * scales[3 * (size_t)idx], scale_modifier * scales[3 * (size_t)idx + 1],
-                        scale_modifier * scales[3 * (size_t)idx + 2]};
+    const float s[3] = {scale_modifier * s_scl[3 * tid], scale_modifier * s_scl[3 * tid + 1],
+                        scale_modifier * s_scl[3 * tid + 2]};
     Mat3 M2, dSig;
 #pragma unroll
     for (int cc = 0; cc < 3; cc++)
@@ -232,12 +350,11 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
     Mat3 dMt = mat3_transpose(dL_dM);
 #pragma unroll
     for (int k = 0; k < 3; k++)
-      dL_dscale[3 * (size_t)idx + k] = Rt.m[k][0] * dMt.m[k][0] + Rt.m[k][1] * dMt.m[k][1] + Rt.m[k][2] * dMt.m[k][2];
+      dscale[k] = Rt.m[k][0] * dMt.m[k][0] + Rt.m[k][1] * dMt.m[k][1] + Rt.m[k][2] * dMt.m[k][2];
 #pragma unroll
     for (int k = 0; k < 3; k++)
 #pragma unroll
       for (int rr = 0; rr < 3; rr++) dMt.m[k][rr] *= s[k];
-    float4 dq;
     dq.x = 2 * z * (dMt.m[0][1] - dMt.m[1][0]) + 2 * y * (dMt.m[2][0] - dMt.m[0][2]) + 2 * x * (dMt.m[1][2] - dMt.m[2][1]);
     dq.y = 2 * y * (dMt.m[1][0] + dMt.m[0][1]) + 2 * z * (dMt.m[2][0] + dMt.m[0][2]) + 2 * r * (dMt.m[1][2] - dMt.m[2][1]) -
            4 * x * (dMt.m[2][2] + dMt.m[1][1]);
@@ -245,8 +362,15 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
            4 * y * (dMt.m[2][2] + dMt.m[0][0]);
     dq.w = 2 * r * (dMt.m[0][1] - dMt.m[1][0]) + 2 * x * (dMt.m[2][0] + dMt.m[0][2]) + 2 * y * (dMt.m[1][2] + dMt.m[2][1]) -
            4 * z * (dMt.m[1][1] + dMt.m[0][0]);
-    reinterpret_cast<float4*>(dL_drot)[idx] = dq;
   }
+  if (do_scale && valid) reinterpret_cast<float4*>(dL_drot)[idx] = dq;
+  // dL_dmean3D / dL_dscale leave through the arrays their inputs came in by (each thread owns its triplet)
+  __syncthreads();
+  s_xyz[3 * tid] = dmean.x; s_xyz[3 * tid + 1] = dmean.y; s_xyz[3 * tid + 2] = dmean.z;
+  s_scl[3 * tid] = dscale[0]; s_scl[3 * tid + 1] = dscale[1]; s_scl[3 * tid + 2] = dscale[2];
+  __syncthreads();
+  if (dL_dmean3D) unstage_flat<BPRE_THREADS>(dL_dmean3D, s_xyz, (size_t)first * 3, count * 3, tid);
+  if (do_scale) unstage_flat<BPRE_THREADS>(dL_dscale, s_scl, (size_t)first * 3, count * 3, tid);
 }
 
 }  // namespace
@@ -256,10 +380,22 @@ void launch_preprocess_bwd(const lsr_frame& f, const lsr_inputs& in, float focal
   if (f.P <= 0) return;
   (void)need_mask;
   const float* cov3Ds = in.cov3D_precomp ? in.cov3D_precomp : g.cov3D;
-  preprocess_bwd_kernel<<<(f.P + 255) / 256, 256, 0, s>>>(
-      f.P, f.D, f.M, in.means3D, radii, in.shs, g.clamped, in.scales, in.rotations, f.scale_modifier, cov3Ds,
-      f.viewmatrix, f.projmatrix, focal_x, focal_y, f.tanfovx, f.tanfovy, f.campos, gr.dL_dmeans2D, gr.dL_dconic,
-      gr.dL_dcolors, gr.dL_dmeans3D, gr.dL_dcov3D, gr.dL_dsh, gr.dL_dscales, gr.dL_drotations);
+  const bool sh16 = in.shs != nullptr && gr.dL_dsh != nullptr && f.M == 16 && (((uintptr_t)in.shs) & 15) == 0 &&
+                    (((uintptr_t)gr.dL_dsh) & 15) == 0;
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaFuncSetAttribute(preprocess_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BPRE_SH_SMEM);
+    cudaFuncSetAttribute(preprocess_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BPRE_SH_SMEM);
+    attr_done = true;
+  }
+  const int blocks = (f.P + BPRE_THREADS - 1) / BPRE_THREADS;
+#define LSR_BPRE_ARGS                                                                                              \
+  f.P, f.D, f.M, in.means3D, radii, in.shs, g.clamped, in.scales, in.rotations, f.scale_modifier, cov3Ds,          \
+      f.viewmatrix, f.projmatrix, focal_x, focal_y, f.tanfovx, f.tanfovy, f.campos, gr.dL_dmeans2D, gr.dL_dconic,  \
+      gr.dL_dcolors, gr.dL_dmeans3D, gr.dL_dcov3D, gr.dL_dsh, gr.dL_dscales, gr.dL_drotations
+  if (sh16) preprocess_bwd_kernel<true><<<blocks, BPRE_THREADS, BPRE_SH_SMEM, s>>>(LSR_BPRE_ARGS);
+  else preprocess_bwd_kernel<false><<<blocks, BPRE_THREADS, BPRE_SH_SMEM, s>>>(LSR_BPRE_ARGS);
+#undef LSR_BPRE_ARGS
   count_launch();
 }
 

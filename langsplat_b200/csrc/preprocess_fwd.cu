@@ -8,6 +8,7 @@
 // as one 48-byte GeomRec.
 #include "common.cuh"
 #include "gs_math.cuh"
+#include "stage.cuh"
 
 namespace lsr {
 
@@ -45,24 +46,10 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, const float* __restrict__ s
   return res;
 }
 
-// Cooperative, coalesced load of `count` consecutive float triplets starting at element `first` into smem.
-__device__ __forceinline__ void stage_triplets(const float* __restrict__ src, float* dst, int first, int count,
-                                               int tid) {
-  const float* base = src + (size_t)first * 3;
-  const int n = count * 3;
-  // base is 16-B aligned whenever first % 4 == 0 (first = blockIdx * 256) and src is 16-B aligned.
-  if ((((uintptr_t)base) & 15) == 0) {
-    const int n4 = n >> 2;
-    for (int i = tid; i < n4; i += PRE_THREADS) {
-      float4 v = __ldg(reinterpret_cast<const float4*>(base) + i);
-      reinterpret_cast<float4*>(dst)[i] = v;
-    }
-    for (int i = (n4 << 2) + tid; i < n; i += PRE_THREADS) dst[i] = __ldg(base + i);
-  } else {
-    for (int i = tid; i < n; i += PRE_THREADS) dst[i] = __ldg(base + i);
-  }
-}
+constexpr int SH_ROW = 12;  // float4 chunks per [16,3] SH row
+constexpr size_t PRE_SH_SMEM = (size_t)(PRE_THREADS / 32) * 32 * (SH_ROW + 1) * sizeof(float4);
 
+template <bool SH16>
 __global__ void __launch_bounds__(PRE_THREADS)
 preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, const float* __restrict__ scales,
                       float scale_modifier, const float* __restrict__ rotations, const float* __restrict__ opacities,
@@ -73,10 +60,13 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
                       float focal_y, int gx, int gy, int prefiltered, int32_t* __restrict__ radii, GeomRec* __restrict__ rec,
                       float* __restrict__ depths, uint32_t* __restrict__ tiles_touched, float* __restrict__ cov3Ds,
                       uint8_t* __restrict__ clamped, uint32_t* __restrict__ ctrl) {
+  extern __shared__ __align__(16) float4 s_dyn[];  // per warp: 32 padded SH rows; reused to stage rec / cov3D
   __shared__ __align__(16) float s_xyz[PRE_THREADS * 3];
   __shared__ __align__(16) float s_scl[PRE_THREADS * 3];
+  __shared__ __align__(16) float s_lng[PRE_THREADS * 3];
   __shared__ float s_view[16], s_proj[16], s_cam[3];
-  const int tid = threadIdx.x;
+  __shared__ uint32_t s_negmin, s_max;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int first = blockIdx.x * PRE_THREADS;
   const int count = min(PRE_THREADS, P - first);
   if (tid < 16) {
@@ -84,18 +74,23 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
     s_proj[tid] = projmatrix[tid];
   }
   if (tid < 3) s_cam[tid] = campos[tid];
-  stage_triplets(means3D, s_xyz, first, count, tid);
-  if (scales) stage_triplets(scales, s_scl, first, count, tid);
+  if (tid == 0) { s_negmin = 0u; s_max = 0u; }
+  stage_flat<PRE_THREADS>(means3D, s_xyz, (size_t)first * 3, count * 3, tid);
+  if (scales) stage_flat<PRE_THREADS>(scales, s_scl, (size_t)first * 3, count * 3, tid);
+  if (lang) stage_flat<PRE_THREADS>(lang, s_lng, (size_t)first * 3, count * 3, tid);
   __syncthreads();
-  if (tid >= count) return;
+  const bool valid = tid < count;
   const int idx = first + tid;
-  const float mx = s_xyz[3 * tid], my = s_xyz[3 * tid + 1], mz = s_xyz[3 * tid + 2];
+  const float mx = valid ? s_xyz[3 * tid] : 0.f, my = valid ? s_xyz[3 * tid + 1] : 0.f,
+              mz = valid ? s_xyz[3 * tid + 2] : 0.f;
 
   int radius_out = 0;
   uint32_t tiles_out = 0;
-  do {
+  float viewz = 0.f, px = 0.f, py = 0.f, conx = 0.f, cony = 0.f, conz = 0.f;
+  float cov3D[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (valid) do {
     // in_frustum: the only cull is p_view.z <= 0.2 (auxiliary.h:152-154)
-    const float viewz = tp_row(s_view, 2, mx, my, mz);
+    viewz = tp_row(s_view, 2, mx, my, mz);
     if (viewz <= 0.2f) {
       if (prefiltered) atomicOr(&ctrl[CTRL_ERROR], 1u);
       break;
@@ -105,8 +100,6 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
     const float hw = tp_row(s_proj, 3, mx, my, mz);
     const float p_w = __fdiv_rn(1.0f, __fadd_rn(hw, 0.0000001f));
     const float projx = __fmul_rn(hx, p_w), projy = __fmul_rn(hy, p_w);
-
-    float cov3D[6];
     if (cov3D_precomp) {
 #pragma unroll
       for (int i = 0; i < 6; i++) cov3D[i] = __ldg(cov3D_precomp + (size_t)idx * 6 + i);
@@ -114,59 +107,109 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
       const float4 q = __ldg(reinterpret_cast<const float4*>(rotations) + idx);
       compute_cov3D(s_scl[3 * tid], s_scl[3 * tid + 1], s_scl[3 * tid + 2], scale_modifier, q.x, q.y, q.z, q.w,
                     cov3D);
-      float2* dst = reinterpret_cast<float2*>(cov3Ds + (size_t)idx * 6);
-      dst[0] = make_float2(cov3D[0], cov3D[1]);
-      dst[1] = make_float2(cov3D[2], cov3D[3]);
-      dst[2] = make_float2(cov3D[4], cov3D[5]);
     }
     Cov2D c2;
     compute_cov2D(mx, my, mz, focal_x, focal_y, tan_fovx, tan_fovy, cov3D, s_view, c2);
     const float det = __fmaf_rn(c2.a, c2.c, -__fmul_rn(c2.b, c2.b));
     if (det == 0.0f) break;
     const float det_inv = __fdiv_rn(1.f, det);
-    const float conx = __fmul_rn(c2.c, det_inv), cony = __fmul_rn(-c2.b, det_inv), conz = __fmul_rn(c2.a, det_inv);
+    conx = __fmul_rn(c2.c, det_inv); cony = __fmul_rn(-c2.b, det_inv); conz = __fmul_rn(c2.a, det_inv);
     const float mid = __fmul_rn(0.5f, __fadd_rn(c2.a, c2.c));
     const float sq = __fsqrt_rn(fmaxf(0.1f, __fmaf_rn(mid, mid, -det)));
     const float lambda1 = __fadd_rn(mid, sq), lambda2 = __fadd_rn(mid, -sq);
     const int my_radius = __float2int_rz(ceilf(__fmul_rn(3.f, __fsqrt_rn(fmaxf(lambda1, lambda2)))));
-    const float px = ndc2pix(projx, W), py = ndc2pix(projy, H);
+    px = ndc2pix(projx, W); py = ndc2pix(projy, H);
     uint32_t x0, y0, x1, y1;
     get_rect(px, py, my_radius, gx, gy, x0, y0, x1, y1);
     const uint32_t nt = (x1 - x0) * (y1 - y0);
     if (nt == 0) break;
-
-    float3 col;
-    uint8_t clamp_bits = 0;
-    if (colors_precomp == nullptr) {
-      float dx = mx - s_cam[0], dy = my - s_cam[1], dz = mz - s_cam[2];
-      const float len = sqrtf(dx * dx + dy * dy + dz * dz);
-      dx = dx / len; dy = dy / len; dz = dz / len;
-      const float* sh = shs + (size_t)idx * M * 3;
-      col = sh_to_rgb(D, sh, dx, dy, dz, 3);
-      clamp_bits = (col.x < 0.f ? 1 : 0) | (col.y < 0.f ? 2 : 0) | (col.z < 0.f ? 4 : 0);
-      col.x = fmaxf(col.x, 0.f); col.y = fmaxf(col.y, 0.f); col.z = fmaxf(col.z, 0.f);
-    } else {
-      col.x = __ldg(colors_precomp + (size_t)idx * 3);
-      col.y = __ldg(colors_precomp + (size_t)idx * 3 + 1);
-      col.z = __ldg(colors_precomp + (size_t)idx * 3 + 2);
-    }
-    float f0 = 0.f, f1 = 0.f, f2 = 0.f;
-    if (lang) {
-      f0 = __ldg(lang + (size_t)idx * 3);
-      f1 = __ldg(lang + (size_t)idx * 3 + 1);
-      f2 = __ldg(lang + (size_t)idx * 3 + 2);
-    }
-    float4* r4 = reinterpret_cast<float4*>(rec + idx);
-    r4[0] = make_float4(px, py, conx, cony);
-    r4[1] = make_float4(conz, __ldg(opacities + idx), col.x, col.y);
-    r4[2] = make_float4(col.z, f0, f1, f2);
-    depths[idx] = viewz;
-    clamped[idx] = clamp_bits;
     radius_out = my_radius;
     tiles_out = nt;
   } while (0);
-  radii[idx] = radius_out;
-  tiles_touched[idx] = tiles_out;
+  const bool vis = radius_out > 0;
+  const uint32_t vis_mask = __ballot_sync(0xffffffffu, vis);
+
+  // ---- colour: SH rows of the warp's visible Gaussians come in as one coalesced sweep ----
+  float4* wsm = s_dyn + (size_t)warp * 32 * (SH_ROW + 1);
+  float3 col = make_float3(0.f, 0.f, 0.f);
+  uint8_t clamp_bits = 0;
+  if (colors_precomp == nullptr) {
+    if (SH16) {
+      warp_load_rows<SH_ROW>(reinterpret_cast<const float4*>(shs) + (size_t)(first + warp * 32) * SH_ROW, wsm, vis_mask,
+                             lane);
+      __syncwarp();
+    }
+    if (vis) {
+      float dx = mx - s_cam[0], dy = my - s_cam[1], dz = mz - s_cam[2];
+      const float len = sqrtf(dx * dx + dy * dy + dz * dz);
+      dx = dx / len; dy = dy / len; dz = dz / len;
+      if (SH16) {
+        float v[48];
+#pragma unroll
+        for (int i = 0; i < SH_ROW; i++) {
+          const float4 t = wsm[row_slot<SH_ROW>(lane, i)];
+          v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+        }
+        col = sh_to_rgb(D, v, dx, dy, dz, 3);
+      } else {
+        col = sh_to_rgb(D, shs + (size_t)idx * M * 3, dx, dy, dz, 3);
+      }
+      clamp_bits = (col.x < 0.f ? 1 : 0) | (col.y < 0.f ? 2 : 0) | (col.z < 0.f ? 4 : 0);
+      col.x = fmaxf(col.x, 0.f); col.y = fmaxf(col.y, 0.f); col.z = fmaxf(col.z, 0.f);
+    }
+    __syncwarp();
+  } else if (vis) {
+    col.x = __ldg(colors_precomp + (size_t)idx * 3);
+    col.y = __ldg(colors_precomp + (size_t)idx * 3 + 1);
+    col.z = __ldg(colors_precomp + (size_t)idx * 3 + 2);
+  }
+
+  // ---- outputs: the 48-byte records and cov3D go out through shared memory as coalesced 16-byte chunks ----
+  if (vis) {
+    float f0 = 0.f, f1 = 0.f, f2 = 0.f;
+    if (lang) { f0 = s_lng[3 * tid]; f1 = s_lng[3 * tid + 1]; f2 = s_lng[3 * tid + 2]; }
+    wsm[row_slot<3>(lane, 0)] = make_float4(px, py, conx, cony);
+    wsm[row_slot<3>(lane, 1)] = make_float4(conz, __ldg(opacities + idx), col.x, col.y);
+    wsm[row_slot<3>(lane, 2)] = make_float4(col.z, f0, f1, f2);
+  }
+  __syncwarp();
+  warp_store_rows<3>(reinterpret_cast<float4*>(rec + first + warp * 32), wsm, vis_mask, 0u, false, lane);
+  __syncwarp();
+  if (!cov3D_precomp) {
+    float2* w2 = reinterpret_cast<float2*>(wsm);
+    if (vis) {
+      w2[lane * 3] = make_float2(cov3D[0], cov3D[1]);
+      w2[lane * 3 + 1] = make_float2(cov3D[2], cov3D[3]);
+      w2[lane * 3 + 2] = make_float2(cov3D[4], cov3D[5]);
+    }
+    __syncwarp();
+    float2* dst = reinterpret_cast<float2*>(cov3Ds + (size_t)(first + warp * 32) * 6);
+#pragma unroll
+    for (int it = 0; it < 3; it++) {
+      const int c = it * 32 + lane;
+      if ((vis_mask >> (c / 3)) & 1u) dst[c] = w2[c];
+    }
+  }
+  if (vis) {
+    depths[idx] = viewz;
+    clamped[idx] = clamp_bits;
+  }
+  if (valid) {
+    radii[idx] = radius_out;
+    tiles_touched[idx] = tiles_out;
+  }
+  // range of the depth word over the visible Gaussians (feeds the sort's digit plan)
+  if (vis_mask) {
+    const uint32_t bits = __float_as_uint(viewz);
+    const uint32_t wmax = __reduce_max_sync(0xffffffffu, vis ? bits : 0u);
+    const uint32_t wneg = __reduce_max_sync(0xffffffffu, vis ? ~bits : 0u);
+    if (lane == 0) { atomicMax(&s_max, wmax); atomicMax(&s_negmin, wneg); }
+  }
+  __syncthreads();
+  if (tid == 0 && s_max != 0u) {
+    atomicMax(&ctrl[CTRL_DEPTH_MAX], s_max);
+    atomicMax(&ctrl[CTRL_DEPTH_NEGMIN], s_negmin);
+  }
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ viewmatrix,
@@ -185,11 +228,22 @@ void launch_preprocess_fwd(const lsr_frame& f, const lsr_inputs& in, float focal
   const int gx = (f.width + TILE_X - 1) / TILE_X, gy = (f.height + TILE_Y - 1) / TILE_Y;
   const int blocks = (f.P + PRE_THREADS - 1) / PRE_THREADS;
   if (blocks == 0) return;
-  preprocess_fwd_kernel<<<blocks, PRE_THREADS, 0, s>>>(
-      f.P, f.D, f.M, in.means3D, in.scales, f.scale_modifier, in.rotations, in.opacities, in.shs, in.cov3D_precomp,
-      in.colors_precomp, f.include_feature ? in.language_feature : nullptr, f.viewmatrix, f.projmatrix, f.campos,
-      f.width, f.height, f.tanfovx, f.tanfovy, focal_x, focal_y, gx, gy, f.prefiltered, radii, g.rec, g.depth,
-      g.tiles, g.cov3D, g.clamped, ctrl);
+  // fast path: the usual [P,16,3] SH tensor, 16-byte aligned -> rows staged through shared memory
+  const bool sh16 = in.shs != nullptr && f.M == 16 && (((uintptr_t)in.shs) & 15) == 0;
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaFuncSetAttribute(preprocess_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PRE_SH_SMEM);
+    cudaFuncSetAttribute(preprocess_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PRE_SH_SMEM);
+    attr_done = true;
+  }
+#define LSR_PRE_ARGS                                                                                                  \
+  f.P, f.D, f.M, in.means3D, in.scales, f.scale_modifier, in.rotations, in.opacities, in.shs, in.cov3D_precomp,       \
+      in.colors_precomp, f.include_feature ? in.language_feature : nullptr, f.viewmatrix, f.projmatrix, f.campos,     \
+      f.width, f.height, f.tanfovx, f.tanfovy, focal_x, focal_y, gx, gy, f.prefiltered, radii, g.rec, g.depth, g.tiles, \
+      g.cov3D, g.clamped, ctrl
+  if (sh16) preprocess_fwd_kernel<true><<<blocks, PRE_THREADS, PRE_SH_SMEM, s>>>(LSR_PRE_ARGS);
+  else preprocess_fwd_kernel<false><<<blocks, PRE_THREADS, PRE_SH_SMEM, s>>>(LSR_PRE_ARGS);
+#undef LSR_PRE_ARGS
   count_launch();
 }
 

@@ -3,13 +3,22 @@
 // sort on bits [0, end_bit) is fully specified, so any correct implementation yields the reference's exact
 // permutation.
 //
-// Structure: one histogram kernel computes the digit histograms of every pass in a single read of the keys; a tiny
-// kernel turns them into exclusive bin bases; then one kernel per 8-bit digit does rank + scatter in a single sweep,
-// chaining CTA prefixes through global memory with decoupled look-back (no separate scan pass between digits).
-// Ranking inside a CTA is a warp-level multi-split: __match_any_sync groups equal digits, the group leader bumps a
-// per-warp shared histogram, ranks come from popc of the lower-lane mask.  Keys and values are then staged in shared
-// memory in CTA-sorted order so the global scatter is written as long coalesced runs.
-// HBM-bound: algorithmic bytes per element 8 (histogram read) + 24 per pass.
+// Structure
+//  * The digit histograms of every pass come from ONE upstream read: in the forward they are accumulated by the
+//    duplication kernel while it emits the keys (binning.cu), so the sort never re-reads the keys for counting; the
+//    stand-alone entry point (lsr_sort_pairs) runs sort_hist_kernel instead.
+//  * One kernel per digit does rank + scatter in a single sweep, chaining tile prefixes through global memory with
+//    decoupled look-back (no scan pass between digits).  Each CTA turns the raw global histogram into exclusive bin
+//    bases itself (256-bin block scan), so there is no separate scan launch either.
+//  * Ranking inside a CTA is a warp-level multi-split built from BITS ballots per key (MATCH.ANY goes through the
+//    slow MIO path on sm_100a: the first version's histogram kernel spent 134 us on it); the group leader bumps a
+//    per-warp shared histogram, ranks come from popc of the lower-lane mask.  Keys, then values, are staged in
+//    shared memory in CTA-sorted order so the global scatter is written as coalesced runs.
+//  * Digits are taken from a COMPACTED view of the key, (hi << lo_bits) | (lo - lo_min): the forward knows the range
+//    of the depth word (min / max of the float bits, reduced in the preprocess kernel), and depth bits minus their
+//    minimum need ~25 bits instead of 32, so a 45-bit key sorts in 5 eight-bit passes instead of 6.  The transform is
+//    order preserving and the keys in memory stay the reference's exact values.
+// HBM-bound: algorithmic bytes per element 24 per pass (12 read + 12 written).
 #include <algorithm>
 #include "common.cuh"
 
@@ -19,120 +28,182 @@ namespace {
 
 constexpr uint32_t LB_AGG = 1u << 30, LB_INC = 2u << 30, LB_FLAG = 3u << 30, LB_VAL = ~LB_FLAG;
 constexpr int WARPS = SORT_THREADS / 32;
-constexpr size_t SORT_SMEM = (size_t)SORT_TILE * 12 + (size_t)WARPS * SORT_BINS * 4 + 2 * SORT_BINS * 4;
+constexpr int BITS = SORT_RADIX_BITS;
+constexpr int BINS = SORT_BINS;
+static_assert(BINS == SORT_THREADS, "one bin per thread in the look-back");
+// keys (8 B) staged first, the same region is reused for the values; per-warp histograms; bin starts; global offsets
+constexpr size_t SORT_SMEM = (size_t)SORT_TILE * 8 + (size_t)WARPS * BINS * 4 + BINS * 4 + SORT_TILE;
 
+struct DigitMap {  // compacted key = (hi << lo_bits) | (lo - lo_min)
+  uint32_t lo_min;
+  int lo_bits;
+};
+__device__ __forceinline__ uint32_t digit_of(uint64_t key, const DigitMap m, int shift, uint32_t mask) {
+  const uint32_t lo = (uint32_t)key - m.lo_min;
+  const uint64_t c = ((key >> 32) << m.lo_bits) | (uint64_t)lo;
+  return (uint32_t)(c >> shift) & mask;
+}
+
+// Stand-alone histogram of all passes (lsr_sort_pairs only; the forward fuses this into the duplication kernel).
 __global__ void __launch_bounds__(256)
-sort_hist_kernel(const uint64_t* __restrict__ keys, uint32_t n, int passes, int end_bit, uint32_t* __restrict__ ghist) {
-  __shared__ uint32_t sh[SORT_MAX_PASSES * SORT_BINS];
-  for (int j = threadIdx.x; j < passes * SORT_BINS; j += 256) sh[j] = 0;
+sort_hist_kernel(const uint64_t* __restrict__ keys, uint32_t n, int passes, int total_bits, DigitMap dm,
+                 uint32_t* __restrict__ ghist) {
+  __shared__ uint32_t sh[SORT_MAX_PASSES * BINS];
+  for (int j = threadIdx.x; j < passes * BINS; j += 256) sh[j] = 0;
   __syncthreads();
   const uint32_t stride = gridDim.x * 256;
-  const uint32_t n_round = (n + 31) & ~31u;  // keep warps converged for match_any
-  for (uint32_t i = blockIdx.x * 256 + threadIdx.x; i < n_round; i += stride) {
-    const bool ok = i < n;
-    const uint64_t key = ok ? __ldg(keys + i) : 0ull;
-    const uint32_t act = __ballot_sync(0xffffffffu, ok);
-    if (!ok) continue;
+  for (uint32_t i = blockIdx.x * 256 + threadIdx.x; i < n; i += stride) {
+    const uint64_t key = __ldg(keys + i);
     for (int p = 0; p < passes; p++) {
-      const int shift = p * SORT_RADIX_BITS;
-      const int bits = min(SORT_RADIX_BITS, end_bit - shift);
-      const uint32_t d = (uint32_t)(key >> shift) & ((1u << bits) - 1);
-      const uint32_t peers = __match_any_sync(act, d);
-      if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&sh[p * SORT_BINS + d], __popc(peers));
+      const int shift = p * BITS;
+      const int bits = min(BITS, total_bits - shift);
+      atomicAdd(&sh[p * BINS + digit_of(key, dm, shift, (1u << bits) - 1)], 1u);
     }
   }
   __syncthreads();
-  for (int j = threadIdx.x; j < passes * SORT_BINS; j += 256)
+  for (int j = threadIdx.x; j < passes * BINS; j += 256)
     if (sh[j]) atomicAdd(&ghist[j], sh[j]);
 }
 
-// exclusive scan of each pass's 256-bin histogram, in place (one CTA per pass)
-__global__ void __launch_bounds__(SORT_BINS) sort_scan_kernel(uint32_t* __restrict__ ghist) {
-  __shared__ uint32_t s_w[SORT_BINS / 32];
-  uint32_t* h = ghist + blockIdx.x * SORT_BINS;
-  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  const uint32_t c = h[t];
-  uint32_t w = c;
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    uint32_t x = __shfl_up_sync(0xffffffffu, w, d);
-    if (lane >= d) w += x;
-  }
-  if (lane == 31) s_w[warp] = w;
-  __syncthreads();
-  uint32_t pre = 0;
-#pragma unroll
-  for (int i = 0; i < SORT_BINS / 32; i++)
-    if (i < warp) pre += s_w[i];
-  h[t] = pre + w - c;
+// Per-pass digit extraction with all shift amounts precomputed on the host (PTX shifts clamp at 32, so the terms
+// that do not apply to a pass vanish):  d = (((lo - lo_min) >> s1) | (hi << s2) | (hi >> s3)) & mask.
+struct PassDigit {
+  uint32_t lo_min, s1, s2, s3, mask;
+};
+__device__ __forceinline__ uint32_t shr32(uint32_t v, uint32_t s) {
+  uint32_t r;
+  asm("shr.b32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(s));
+  return r;
+}
+__device__ __forceinline__ uint32_t shl32(uint32_t v, uint32_t s) {
+  uint32_t r;
+  asm("shl.b32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(s));
+  return r;
+}
+__device__ __forceinline__ uint32_t pass_digit(uint64_t key, const PassDigit& pd) {
+  const uint32_t lo = (uint32_t)key - pd.lo_min, hi = (uint32_t)(key >> 32);
+  return (shr32(lo, pd.s1) | shl32(hi, pd.s2) | shr32(hi, pd.s3)) & pd.mask;
 }
 
-__global__ void __launch_bounds__(SORT_THREADS)
+// lanes of the warp holding the same NB-bit digit: NB ballots, 4 instructions per bit
+template <int NB>
+__device__ __forceinline__ uint32_t match_digit(uint32_t d) {
+  uint32_t peers = 0xffffffffu;
+#pragma unroll
+  for (int b = 0; b < NB; b++) {
+    uint32_t m;
+    asm("{\n\t.reg .pred p;\n\t.reg .b32 t;\n\t"
+        "and.b32 t, %1, %2;\n\t"
+        "setp.ne.u32 p, t, 0;\n\t"
+        "vote.sync.ballot.b32 %0, p, 0xffffffff;\n\t"
+        "@!p not.b32 %0, %0;\n\t}"
+        : "=r"(m)
+        : "r"(d), "r"(1u << b));
+    peers &= m;
+  }
+  return peers;
+}
+
+template <int NB>
+__global__ void __launch_bounds__(SORT_THREADS, 4)
 onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, const uint32_t* __restrict__ vin,
                 uint32_t* __restrict__ vout, uint32_t n, uint32_t* __restrict__ ticket,
-                volatile uint32_t* __restrict__ lookback, const uint32_t* __restrict__ bin_base, int shift,
-                uint32_t mask) {
+                volatile uint32_t* __restrict__ lookback, const uint32_t* __restrict__ ghist, PassDigit pd) {
   extern __shared__ __align__(16) unsigned char smem[];
   uint64_t* s_keys = reinterpret_cast<uint64_t*>(smem);
-  uint32_t* s_vals = reinterpret_cast<uint32_t*>(smem + (size_t)SORT_TILE * 8);
-  uint32_t* s_whist = reinterpret_cast<uint32_t*>(smem + (size_t)SORT_TILE * 12);
-  uint32_t* s_binstart = s_whist + WARPS * SORT_BINS;
-  uint32_t* s_gofs = s_binstart + SORT_BINS;
+  uint32_t* s_vals = reinterpret_cast<uint32_t*>(smem);  // reuses the key region after the keys are written out
+  uint32_t* s_whist = reinterpret_cast<uint32_t*>(smem + (size_t)SORT_TILE * 8);  // [WARPS][BINS]
+  uint32_t* s_gofs = s_whist + WARPS * BINS;
+  uint8_t* s_dig = reinterpret_cast<uint8_t*>(s_gofs + BINS);  // digit of the element at CTA-sorted position p
   __shared__ uint32_t s_tile;
-  __shared__ uint32_t s_wsum[WARPS];
+  __shared__ uint32_t s_wsum[WARPS], s_wsum2[WARPS];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) s_tile = atomicAdd(ticket, 1u);
 #pragma unroll
-  for (int j = tid; j < WARPS * SORT_BINS; j += SORT_THREADS) s_whist[j] = 0;
+  for (int j = tid; j < WARPS * BINS; j += SORT_THREADS) s_whist[j] = 0;
   __syncthreads();
   const uint32_t tile = s_tile;
   const uint32_t tile_base = tile * SORT_TILE;
   if (tile_base >= n) return;
   const uint32_t valid = min((uint32_t)SORT_TILE, n - tile_base);
+  const bool full = valid == SORT_TILE;
 
   // ---- load (warp-striped: warp w owns a contiguous 32*ITEMS chunk; item i of lane l is element i*32+l) ----
-  const uint32_t wbase = tile_base + warp * (32 * SORT_ITEMS);
+  const uint32_t wofs = warp * (32 * SORT_ITEMS) + lane;  // + i*32 = position inside the tile
+  const uint64_t* kp = kin + tile_base + wofs;
   uint64_t key[SORT_ITEMS];
+  if (full) {
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++) key[i] = __ldg(kp + i * 32);
+  } else {
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++) key[i] = (wofs + i * 32 < valid) ? __ldg(kp + i * 32) : 0ull;
+  }
+  // exclusive bin bases of this pass from the raw global histogram (every CTA redoes this 256-element scan)
+  uint32_t gbase;
+  {
+    const uint32_t c = __ldg(ghist + tid);
+    uint32_t inc = c;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t x = __shfl_up_sync(0xffffffffu, inc, d);
+      if (lane >= d) inc += x;
+    }
+    if (lane == 31) s_wsum2[warp] = inc;
+    __syncthreads();
+    uint32_t pre = 0;
+#pragma unroll
+    for (int w = 0; w < WARPS; w++)
+      if (w < warp) pre += s_wsum2[w];
+    gbase = pre + inc - c;
+  }
+  // ---- digits (once), packed four to a register ----
+  // padding items of a partial last tile take the highest digit and, being the last elements, rank last inside it
+  uint32_t dig[SORT_ITEMS / 4];
 #pragma unroll
   for (int i = 0; i < SORT_ITEMS; i++) {
-    const uint32_t gi = wbase + i * 32 + lane;
-    key[i] = gi < n ? __ldg(kin + gi) : ~0ull;
+    uint32_t d = pass_digit(key[i], pd);
+    if (!full && !(wofs + i * 32 < valid)) d = BINS - 1;
+    if ((i & 3) == 0) dig[i >> 2] = d; else dig[i >> 2] |= d << (8 * (i & 3));
   }
   // ---- warp-level multi-split ranking (stable: items in ascending i, lanes in ascending order) ----
-  uint32_t rank[SORT_ITEMS];
-  uint32_t* wh = s_whist + warp * SORT_BINS;
+  uint16_t rank[SORT_ITEMS];
+  uint32_t* wh = s_whist + warp * BINS;
   const uint32_t lt = (1u << lane) - 1;
 #pragma unroll
   for (int i = 0; i < SORT_ITEMS; i++) {
-    const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
-    const uint32_t peers = __match_any_sync(0xffffffffu, d);
-    const int leader = __ffs(peers) - 1;
-    uint32_t prev = 0;
-    if (lane == leader) {
-      prev = wh[d];
-      wh[d] = prev + __popc(peers);
-    }
-    prev = __shfl_sync(0xffffffffu, prev, leader);
-    rank[i] = prev + __popc(peers & lt);
+    const uint32_t d = (dig[i >> 2] >> (8 * (i & 3))) & 0xffu;
+    // padding digits may exceed NB bits only in the last tile; matching on NB bits would alias them with real keys
+    const uint32_t peers = full ? match_digit<NB>(d) : match_digit<BITS>(d);
+    const uint32_t lower = peers & lt;
+    const uint32_t prev = wh[d];             // every lane of the group reads the running count ...
+    __syncwarp();
+    if (lower == 0) wh[d] = prev + __popc(peers);  // ... then its lowest lane bumps it
+    rank[i] = (uint16_t)(prev + __popc(lower));
     __syncwarp();
   }
   __syncthreads();
 
   // ---- per bin (thread t == bin t): exclusive scan over warps, CTA bin scan, decoupled look-back ----
+  uint32_t vcnt, bin_start;
   {
     const int t = tid;
+    uint32_t wcnt[WARPS];
     uint32_t cnt = 0;
 #pragma unroll
     for (int w = 0; w < WARPS; w++) {
-      const uint32_t c = s_whist[w * SORT_BINS + t];
-      s_whist[w * SORT_BINS + t] = cnt;
-      cnt += c;
+      wcnt[w] = cnt;
+      cnt += s_whist[w * BINS + t];
     }
+    vcnt = cnt;
+    if (t == BINS - 1) vcnt -= (SORT_TILE - valid);
+    volatile uint32_t* mine = lookback + (size_t)tile * BINS + t;
+    *mine = (tile == 0 ? LB_INC : LB_AGG) | vcnt;  // publish before the CTA-wide scan
     uint32_t inc = cnt;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
-      uint32_t x = __shfl_up_sync(0xffffffffu, inc, d);
+      const uint32_t x = __shfl_up_sync(0xffffffffu, inc, d);
       if (lane >= d) inc += x;
     }
     if (lane == 31) s_wsum[warp] = inc;
@@ -141,91 +212,187 @@ onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, c
 #pragma unroll
     for (int w = 0; w < WARPS; w++)
       if (w < warp) pre += s_wsum[w];
-    const uint32_t bin_start = pre + inc - cnt;
-    s_binstart[t] = bin_start;
-    // padding keys (~0) of a partial last tile all carry digit == mask and sort to the very end of the CTA
-    uint32_t vcnt = cnt;
-    if ((uint32_t)t == mask) vcnt -= (SORT_TILE - valid);
-    uint32_t prefix = 0;
-    volatile uint32_t* mine = lookback + (size_t)tile * SORT_BINS + t;
-    if (tile == 0) {
-      *mine = LB_INC | vcnt;
-    } else {
-      *mine = LB_AGG | vcnt;
-      int k = (int)tile - 1;
-      while (true) {
-        uint32_t v;
-        do { v = lookback[(size_t)k * SORT_BINS + t]; } while ((v & LB_FLAG) == 0);
-        prefix += v & LB_VAL;
-        if ((v & LB_FLAG) == LB_INC) break;
-        k--;
-      }
-      *mine = LB_INC | (prefix + vcnt);
-    }
-    s_gofs[t] = __ldg(bin_base + t) + prefix - bin_start;
+    bin_start = pre + inc - cnt;
+    // s_whist[w][t] becomes the CTA-sorted position of warp w's first element of bin t
+#pragma unroll
+    for (int w = 0; w < WARPS; w++) s_whist[w * BINS + t] = bin_start + wcnt[w];
   }
   __syncthreads();
 
-  // ---- stage keys and values in CTA-sorted order ----
+  // ---- stage keys in CTA-sorted order, write them out as coalesced runs ----
+  // (rank[] now holds the CTA-sorted position, < SORT_TILE <= 65536)
 #pragma unroll
   for (int i = 0; i < SORT_ITEMS; i++) {
-    const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
-    const uint32_t pos = s_binstart[d] + wh[d] + rank[i];
-    rank[i] = pos;
+    const uint32_t d = (dig[i >> 2] >> (8 * (i & 3))) & 0xffu;
+    const uint32_t pos = wh[d] + rank[i];
+    rank[i] = (uint16_t)pos;
     s_keys[pos] = key[i];
+    s_dig[pos] = (uint8_t)d;
   }
+  // the values are fetched now: their latency overlaps the key write-out
+  uint32_t val[SORT_ITEMS];
+  {
+    const uint32_t* vp = vin + tile_base + wofs;
+    if (full) {
 #pragma unroll
-  for (int i = 0; i < SORT_ITEMS; i++) {
-    const uint32_t gi = wbase + i * 32 + lane;
-    s_vals[rank[i]] = gi < n ? __ldg(vin + gi) : 0u;
+      for (int i = 0; i < SORT_ITEMS; i++) val[i] = __ldg(vp + i * 32);
+    } else {
+#pragma unroll
+      for (int i = 0; i < SORT_ITEMS; i++) val[i] = (wofs + i * 32 < valid) ? __ldg(vp + i * 32) : 0u;
+    }
+  }
+  // ---- decoupled look-back (thread t == bin t); the staged keys and the value loads are already in flight ----
+  {
+    const int t = tid;
+    volatile uint32_t* mine = lookback + (size_t)tile * BINS + t;
+    uint32_t prefix = 0;
+    if (tile != 0) {
+      // look back four tiles at a time (independent loads in flight), consume them nearest first
+      int k = (int)tile - 1;
+      bool done = false;
+      while (!done) {
+        uint32_t v[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) v[j] = (k - j >= 0) ? lookback[(size_t)(k - j) * BINS + t] : (uint32_t)(2u << 30);
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          if (done) break;
+          while ((v[j] & LB_FLAG) == 0) v[j] = lookback[(size_t)(k - j) * BINS + t];
+          prefix += v[j] & LB_VAL;
+          if ((v[j] & LB_FLAG) == LB_INC) done = true;
+        }
+        k -= 4;
+      }
+      *mine = LB_INC | (prefix + vcnt);
+    }
+    s_gofs[t] = gbase + prefix - bin_start;
+  }
+
+  __syncthreads();
+  if (full) {
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++) {
+      const uint32_t p = tid + i * SORT_THREADS;
+      kout[s_gofs[s_dig[p]] + p] = s_keys[p];
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++) {
+      const uint32_t p = tid + i * SORT_THREADS;
+      if (p < valid) kout[s_gofs[s_dig[p]] + p] = s_keys[p];
+    }
   }
   __syncthreads();
-  // ---- coalesced scatter ----
-  for (uint32_t p = tid; p < valid; p += SORT_THREADS) {
-    const uint64_t k = s_keys[p];
-    const uint32_t d = (uint32_t)(k >> shift) & mask;
-    const uint32_t g = s_gofs[d] + p;
-    kout[g] = k;
-    vout[g] = s_vals[p];
+#pragma unroll
+  for (int i = 0; i < SORT_ITEMS; i++) s_vals[rank[i]] = val[i];
+  __syncthreads();
+  if (full) {
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++) {
+      const uint32_t p = tid + i * SORT_THREADS;
+      vout[s_gofs[s_dig[p]] + p] = s_vals[p];
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++) {
+      const uint32_t p = tid + i * SORT_THREADS;
+      if (p < valid) vout[s_gofs[s_dig[p]] + p] = s_vals[p];
+    }
+  }
+}
+
+using OnesweepFn = void (*)(const uint64_t*, uint64_t*, const uint32_t*, uint32_t*, uint32_t, uint32_t*,
+                            volatile uint32_t*, const uint32_t*, PassDigit);
+OnesweepFn onesweep_for_bits(int nb) {
+  switch (nb) {
+    case 1: return onesweep_kernel<1>;
+    case 2: return onesweep_kernel<2>;
+    case 3: return onesweep_kernel<3>;
+    case 4: return onesweep_kernel<4>;
+    case 5: return onesweep_kernel<5>;
+    case 6: return onesweep_kernel<6>;
+    case 7: return onesweep_kernel<7>;
+    default: return onesweep_kernel<8>;
   }
 }
 
 }  // namespace
 
-int sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
-               uint64_t* keys_tmp, uint32_t* vals_tmp, int64_t n, int end_bit, void* work, cudaStream_t s) {
-  if (n <= 0) return 0;
+SortPlan make_sort_plan(uint32_t lo_min, uint32_t lo_max, int hi_bits) {
+  SortPlan pl;
+  pl.lo_min = lo_min;
+  uint32_t span = lo_max >= lo_min ? lo_max - lo_min : 0u;
+  int lb = 0;
+  while (lb < 32 && (span >> lb) != 0) lb++;
+  pl.lo_bits = lb < 1 ? 1 : lb;
+  pl.hi_bits = hi_bits < 0 ? 0 : hi_bits;
+  pl.total_bits = pl.lo_bits + pl.hi_bits;
+  if (pl.total_bits > 64) pl.total_bits = 64;
+  pl.passes = (pl.total_bits + BITS - 1) / BITS;
+  return pl;
+}
+
+SortPlan make_sort_plan_bits(int end_bit) {
   if (end_bit < 1) end_bit = 1;
   if (end_bit > 64) end_bit = 64;
-  const int passes = (end_bit + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
+  SortPlan pl;
+  pl.lo_min = 0;
+  pl.lo_bits = end_bit < 32 ? end_bit : 32;
+  pl.hi_bits = end_bit - pl.lo_bits;
+  pl.total_bits = end_bit;
+  pl.passes = (end_bit + BITS - 1) / BITS;
+  return pl;
+}
+
+void sort_prepare(void* work, int64_t n, const SortPlan& pl, cudaStream_t s) {
+  // histograms + tickets + the look-back words of the passes that will run must be zero
   SortWork w = sort_work_view(work, n);
-  cudaMemsetAsync(work, 0, w.zero_bytes, s);
+  const size_t lb_bytes = (size_t)pl.passes * sort_nblocks(n) * BINS * 4;
+  cudaMemsetAsync(work, 0, (size_t)((char*)w.lookback - (char*)work) + lb_bytes, s);
+}
+
+int sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+               uint64_t* keys_tmp, uint32_t* vals_tmp, int64_t n, const SortPlan& pl, bool hist_ready, void* work,
+               cudaStream_t s) {
+  if (n <= 0) return 0;
+  SortWork w = sort_work_view(work, n);
   const uint32_t nblocks = (uint32_t)((n + SORT_TILE - 1) / SORT_TILE);
   static bool attr_done = false;
   if (!attr_done) {
-    cudaFuncSetAttribute(onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM);
+    for (int nb = 1; nb <= BITS; nb++)
+      cudaFuncSetAttribute(onesweep_for_bits(nb), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM);
     attr_done = true;
   }
-  const uint32_t hist_blocks = (uint32_t)std::min<int64_t>((n + 2047) / 2048, (int64_t)148 * 8);
-  sort_hist_kernel<<<hist_blocks, 256, 0, s>>>(keys_in, (uint32_t)n, passes, end_bit, w.hist);
-  sort_scan_kernel<<<passes, SORT_BINS, 0, s>>>(w.hist);
-  count_launch(2);
+  const DigitMap dm{pl.lo_min, pl.lo_bits};
+  if (!hist_ready) {
+    sort_prepare(work, n, pl, s);
+    const uint32_t hist_blocks = (uint32_t)std::min<int64_t>((n + 2047) / 2048, (int64_t)148 * 8);
+    sort_hist_kernel<<<hist_blocks, 256, 0, s>>>(keys_in, (uint32_t)n, pl.passes, pl.total_bits, dm, w.hist);
+    count_launch();
+  }
   const uint64_t* ksrc = keys_in;
   const uint32_t* vsrc = vals_in;
-  for (int p = 0; p < passes; p++) {
-    const bool to_out = ((passes - 1 - p) & 1) == 0;
+  for (int p = 0; p < pl.passes; p++) {
+    const bool to_out = ((pl.passes - 1 - p) & 1) == 0;
     uint64_t* kdst = to_out ? keys_out : keys_tmp;
     uint32_t* vdst = to_out ? vals_out : vals_tmp;
-    const int shift = p * SORT_RADIX_BITS;
-    const int bits = min(SORT_RADIX_BITS, end_bit - shift);
-    onesweep_kernel<<<nblocks, SORT_THREADS, SORT_SMEM, s>>>(
-        ksrc, kdst, vsrc, vdst, (uint32_t)n, w.tickets + p, w.lookback + (size_t)p * sort_nblocks(n) * SORT_BINS,
-        w.hist + p * SORT_BINS, shift, (1u << bits) - 1);
+    const int shift = p * BITS;
+    const int bits = std::min(BITS, pl.total_bits - shift);
+    // d = (((lo - lo_min) >> s1) | (hi << s2) | (hi >> s3)) & mask of the compacted key (hi << lo_bits) | (lo - lo_min)
+    PassDigit pd;
+    pd.lo_min = pl.lo_min;
+    pd.mask = (1u << bits) - 1;
+    pd.s1 = shift < pl.lo_bits ? (uint32_t)shift : 32u;
+    pd.s2 = (shift < pl.lo_bits && pl.lo_bits - shift < 32) ? (uint32_t)(pl.lo_bits - shift) : 32u;
+    pd.s3 = shift >= pl.lo_bits ? (uint32_t)std::min(shift - pl.lo_bits, 32) : 32u;
+    onesweep_for_bits(bits)<<<nblocks, SORT_THREADS, SORT_SMEM, s>>>(
+        ksrc, kdst, vsrc, vdst, (uint32_t)n, w.tickets + p, w.lookback + (size_t)p * sort_nblocks(n) * BINS,
+        w.hist + p * BINS, pd);
     count_launch();
     ksrc = kdst;
     vsrc = vdst;
   }
-  return passes;
+  return pl.passes;
 }
 
 }  // namespace lsr
