@@ -1,12 +1,25 @@
 // render_bwd.cu — K7': per-pixel reverse blend; gradients w.r.t. mean2D, conic, opacity, colour, language feature.
 // Replaces BACKWARD::render / renderCUDA (RAST/cuda_rasterizer/backward.cu:399-593).
 //
-// The reference issues 12 global atomicAdds per contributing (pixel, Gaussian) pair (backward.cu:541-590).  Here all
-// 32 lanes of a warp walk the same instance in lock-step, so the (up to) 12 per-lane contributions are first summed
-// across the warp with a value-halving butterfly (13 shuffles for 12 values instead of 60: each round a lane keeps half
-// of its values and sends the other half to its partner), leaving each value's warp total on one lane, which issues a
-// single RED.ADD.F32.  Instances no lane contributes to are dropped after one ballot.
-// The walk starts at the CTA-wide maximum of n_contrib, so the never-blended tail of a tile's list is not even fetched.
+// The kernel is instruction-issue bound (ncu: 85 % issue-active), so everything here is about instructions per
+// contributing (pixel, Gaussian) pair:
+//  * Reduction instead of atomics.  The reference issues 12 global atomicAdds per contributing pair
+//    (backward.cu:541-590).  Here all lanes of a warp walk the same instance in lock-step, so the (up to) 12 per-lane
+//    contributions are summed across the warp with a value-halving butterfly (13 shuffles for 12 values instead of
+//    60: each round a lane keeps half of its values and sends the other half to its partner), leaving each value's
+//    warp total on one lane, which issues a single RED.ADD.F32.
+//  * Two pixels per thread.  A warp owns an 8x8 pixel block (a 16x16 tile is 4 warps = 128 threads); each thread
+//    blends rows r and r+4 of its column and adds both pixels' contributions before the butterfly, so the reduction,
+//    the shared-memory broadcasts and the loop overhead are paid once per 64 pixels (measured on the bench scene: 3.6 M
+//    working (warp, instance) pairs instead of 6.2 M with 8x4 footprints).
+//  * Scalar "colour behind" recurrence.  The reference keeps accum_rec[ch] / last_color[ch] per channel
+//    (backward.cu:527-538) only to form sum_ch (c[ch] - accum_rec[ch]) * dL_dpixel[ch]; the recurrence is linear, so
+//    it is carried for the dot product itself: A <- last_alpha * (last_color . dL_dpixel) + (1 - last_alpha) * A.
+//    One scalar recurrence serves the three colour and the three feature channels (6 FMAs + 3 instead of ~30).
+//  * T is walked back with a reciprocal (MUFU.RCP) instead of the reference's IEEE division; gradients carry a 1e-4
+//    relative tolerance (the reference's own sums are unordered atomics), the forward decisions are untouched.
+//  * The walk starts at the CTA-wide maximum of n_contrib, so the never-blended tail of a tile's list is not fetched;
+//    instances that cannot reach alpha >= 1/255 anywhere in the tile are dropped at staging (render_common.cuh).
 // Template switches specialise on what the caller needs (ctx.needs_input_grad): FEAT = language feature blended,
 // DCOL = a colour upstream gradient exists, GEOM = conic/opacity gradients wanted.  LangSplat's feature-only training
 // (train.py:96-99 with gaussian_model.py:212-217) runs <FEAT=1, DCOL=0, GEOM=0>: 5 values instead of 12.
@@ -58,8 +71,11 @@ __device__ __forceinline__ int held_index(int lane) {
   }
 }
 
+constexpr int BWD_THREADS = 128;  // 4 warps x (8x8 pixels), two pixels per thread
+constexpr int BWD_SLOTS = 2;
+
 template <bool FEAT, bool DCOL, bool GEOM>
-__global__ void __launch_bounds__(TILE_PIX)
+__global__ void __launch_bounds__(BWD_THREADS)
 render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t* __restrict__ list,
                   const GeomRec* __restrict__ rec, const float* __restrict__ bg, const float* __restrict__ final_Ts,
                   const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
@@ -73,53 +89,52 @@ render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
   constexpr int I_FEAT = I_COL + (DCOL ? 3 : 0);
   constexpr int NV = I_FEAT + (FEAT ? 3 : 0);
 
-  __shared__ BatchSmem sm;
-  __shared__ uint32_t s_max[TILE_PIX / 32];
+  __shared__ BatchSmemT<BWD_THREADS> sm;
+  __shared__ uint32_t s_max[BWD_THREADS / 32];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  // warp w owns an 8x4-pixel footprint (compact, instead of the reference's 16x2 strips)
-  const int tx = (warp & 1) * 8 + (lane & 7), ty = (warp >> 1) * 4 + (lane >> 3);
+  const int tx = (warp & 1) * 8 + (lane & 7), ty = (warp >> 1) * 8 + (lane >> 3);  // slot s adds 4*s rows
   const int tiles_x = (W + TILE_X - 1) / TILE_X;
-  const uint32_t px = blockIdx.x * TILE_X + tx, py = blockIdx.y * TILE_Y + ty;
-  const bool inside = px < (uint32_t)W && py < (uint32_t)H;
-  const float pxf = (float)px, pyf = (float)py;
+  const uint32_t px = blockIdx.x * TILE_X + tx;
+  const float pxf = (float)px;
   const float X0 = (float)(blockIdx.x * TILE_X), Y0 = (float)(blockIdx.y * TILE_Y);
   const size_t N = (size_t)W * H;
-  const size_t pix = (size_t)py * W + px;
   const uint2 range = ranges[blockIdx.y * tiles_x + blockIdx.x];
 
-  const float T_final = inside ? final_Ts[pix] : 0.f;
-  float T = T_final;
-  const uint32_t last_contributor = inside ? n_contrib[pix] : 0u;
-
+  float pyf[BWD_SLOTS], T[BWD_SLOTS], bgT[BWD_SLOTS];
+  uint32_t lastc[BWD_SLOTS];
+  float dpix[BWD_SLOTS][3], dpixF[BWD_SLOTS][3];
+  float accA[BWD_SLOTS], cd_last[BWD_SLOTS], alpha_last[BWD_SLOTS];
+  uint32_t wmax = 0;
+#pragma unroll
+  for (int s = 0; s < BWD_SLOTS; s++) {
+    const uint32_t py = blockIdx.y * TILE_Y + ty + 4 * s;
+    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+    const size_t pix = (size_t)py * W + px;
+    pyf[s] = (float)py;
+    const float T_final = inside ? final_Ts[pix] : 0.f;
+    T[s] = T_final;
+    lastc[s] = inside ? n_contrib[pix] : 0u;
+    wmax = max(wmax, lastc[s]);
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+      dpix[s][i] = (DCOL && inside) ? dL_dpixels[i * N + pix] : 0.f;
+      dpixF[s][i] = (FEAT && inside) ? dL_dpixels_F[i * N + pix] : 0.f;
+    }
+    bgT[s] = 0.f;
+    if (DCOL) bgT[s] = -T_final * (__ldg(bg) * dpix[s][0] + __ldg(bg + 1) * dpix[s][1] + __ldg(bg + 2) * dpix[s][2]);
+    accA[s] = 0.f; cd_last[s] = 0.f; alpha_last[s] = 0.f;
+  }
   // The CTA-wide maximum of n_contrib bounds the part of the list anyone needs.
-  uint32_t wmax = last_contributor;
 #pragma unroll
   for (int d = 16; d > 0; d >>= 1) wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, d));
   if (lane == 0) s_max[warp] = wmax;
   __syncthreads();
   uint32_t bmax = 0;
 #pragma unroll
-  for (int i = 0; i < TILE_PIX / 32; i++) bmax = max(bmax, s_max[i]);
+  for (int i = 0; i < BWD_THREADS / 32; i++) bmax = max(bmax, s_max[i]);
   const int eff_len = (int)bmax;  // forward indices [0, eff_len) are the only ones examined
 
-  float dpix[3] = {0.f, 0.f, 0.f}, dpixF[3] = {0.f, 0.f, 0.f};
-  if (inside) {
-    if (DCOL) {
-#pragma unroll
-      for (int i = 0; i < 3; i++) dpix[i] = dL_dpixels[i * N + pix];
-    }
-    if (FEAT) {
-#pragma unroll
-      for (int i = 0; i < 3; i++) dpixF[i] = dL_dpixels_F[i * N + pix];
-    }
-  }
-  float bg_dot = 0.f;
-  if (DCOL) bg_dot = __ldg(bg) * dpix[0] + __ldg(bg + 1) * dpix[1] + __ldg(bg + 2) * dpix[2];
-
-  float accum_rec[3] = {0.f, 0.f, 0.f}, last_color[3] = {0.f, 0.f, 0.f};
-  float accum_recF[3] = {0.f, 0.f, 0.f}, last_F[3] = {0.f, 0.f, 0.f};
-  float last_alpha = 0.f;
   const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
 
   // which reduced value this lane ends up holding, and where it goes
@@ -134,80 +149,88 @@ render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
     else if (FEAT && held >= I_FEAT) { out_base = dL_dfeat + (held - I_FEAT); out_stride = 3; }
   }
 
-  const int rounds = (eff_len + TILE_PIX - 1) / TILE_PIX;
+  const int rounds = (eff_len + BWD_THREADS - 1) / BWD_THREADS;
   for (int b = 0; b < rounds; b++) {
-    // back to front: this batch covers forward indices eff_len-1-b*256 downwards (backward.cu:486-498)
-    const int fwd_fetch = eff_len - 1 - (b * TILE_PIX + tid);
-    const int nb = stage_batch(sm, list, rec, range.x, fwd_fetch >= 0 ? fwd_fetch : -1, X0, Y0);
+    // back to front: this batch covers forward indices eff_len-1-b*128 downwards (backward.cu:486-498)
+    const int fwd_fetch = eff_len - 1 - (b * BWD_THREADS + tid);
+    const int nb = stage_batch<BWD_THREADS>(sm, list, rec, range.x, fwd_fetch >= 0 ? fwd_fetch : -1, X0, Y0);
     for (int j = 0; j < nb; j++) {
       const float4 a = sm.A[j];
       const float4 bb = sm.B[j];  // cz, thr_m, opacity, position
       const uint32_t fwd = __float_as_uint(bb.w);
-      const float dx = __fadd_rn(a.x, -pxf), dy = __fadd_rn(a.y, -pyf);
-      const float q = __fmaf_rn(dx, __fmul_rn(a.z, dx), __fmul_rn(__fmul_rn(bb.x, dy), dy));
-      const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(__fmul_rn(a.w, dx), dy));
-      // entries at or beyond n_contrib were never blended (backward.cu:504-506); power > 0 and the alpha threshold
-      // as in the forward.  The pre-test against thr_m avoids expf for pairs that certainly fail alpha >= 1/255.
-      const bool maybe = (fwd < last_contributor) && !(power > 0.0f) && !(power < bb.y);
-      if (__ballot_sync(0xffffffffu, maybe) == 0u) continue;
-      const float G = expf(power);
-      const float alpha = fminf(0.99f, __fmul_rn(bb.z, G));
-      const bool contrib = maybe && !(alpha < kAlphaMin);
-      const uint32_t cmask = __ballot_sync(0xffffffffu, contrib);
-      if (cmask == 0u) continue;
+      const float dx = __fadd_rn(a.x, -pxf);
+      const float qx = __fmul_rn(a.z, dx), hx = __fmul_rn(a.w, dx);
+      float dy[BWD_SLOTS], power[BWD_SLOTS];
+      bool maybe[BWD_SLOTS];
+#pragma unroll
+      for (int s = 0; s < BWD_SLOTS; s++) {
+        dy[s] = __fadd_rn(a.y, -pyf[s]);
+        const float q = __fmaf_rn(dx, qx, __fmul_rn(__fmul_rn(bb.x, dy[s]), dy[s]));
+        power[s] = __fmaf_rn(q, -0.5f, -__fmul_rn(hx, dy[s]));
+        // entries at or beyond n_contrib were never blended (backward.cu:504-506); power > 0 and the alpha threshold
+        // as in the forward.  The pre-test against thr_m avoids expf for pairs that certainly fail alpha >= 1/255.
+        maybe[s] = (fwd < lastc[s]) && !(power[s] > 0.0f) && !(power[s] < bb.y);
+      }
+      if (!__any_sync(0xffffffffu, maybe[0] || maybe[1])) continue;
+      float G[BWD_SLOTS], alpha[BWD_SLOTS];
+      bool contrib[BWD_SLOTS];
+      uint32_t cmask[BWD_SLOTS];
+#pragma unroll
+      for (int s = 0; s < BWD_SLOTS; s++) {
+        G[s] = expf(power[s]);
+        alpha[s] = fminf(0.99f, __fmul_rn(bb.z, G[s]));
+        contrib[s] = maybe[s] && !(alpha[s] < kAlphaMin);
+        cmask[s] = __ballot_sync(0xffffffffu, contrib[s]);
+      }
+      if ((cmask[0] | cmask[1]) == 0u) continue;
 
       float v[12];
 #pragma unroll
       for (int k = 0; k < 12; k++) v[k] = 0.f;
       const float4 c = sm.C[j];  // r, g, b, f0
       const float4 d = sm.D[j];  // f1, f2, id
-      if (contrib) {
-        const float one_m_alpha = __fadd_rn(1.f, -alpha);
-        T = __fdiv_rn(T, one_m_alpha);
-        const float dchannel_dcolor = alpha * T;
-        float dL_dalpha = 0.0f;
-        if (DCOL) {
-          const float col[3] = {c.x, c.y, c.z};
 #pragma unroll
-          for (int ch = 0; ch < 3; ch++) {
-            accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
-            last_color[ch] = col[ch];
-            dL_dalpha += (col[ch] - accum_rec[ch]) * dpix[ch];
-            v[I_COL + ch] = dchannel_dcolor * dpix[ch];
+      for (int s = 0; s < BWD_SLOTS; s++) {
+        if (cmask[s] == 0u) continue;  // warp-uniform
+        if (contrib[s]) {
+          const float one_m_alpha = __fadd_rn(1.f, -alpha[s]);
+          const float rcp = __fdividef(1.f, one_m_alpha);
+          T[s] *= rcp;
+          const float w = alpha[s] * T[s];  // d(channel)/d(colour)
+          float cd = 0.f;                   // colour . dL_dpixel over all blended channels
+          if (DCOL) {
+            cd = c.x * dpix[s][0] + c.y * dpix[s][1] + c.z * dpix[s][2];
+            v[I_COL + 0] += w * dpix[s][0]; v[I_COL + 1] += w * dpix[s][1]; v[I_COL + 2] += w * dpix[s][2];
           }
-        }
-        if (FEAT) {
-          const float ft[3] = {c.w, d.x, d.y};
-#pragma unroll
-          for (int ch = 0; ch < 3; ch++) {
-            accum_recF[ch] = last_alpha * last_F[ch] + (1.f - last_alpha) * accum_recF[ch];
-            last_F[ch] = ft[ch];
-            dL_dalpha += (ft[ch] - accum_recF[ch]) * dpixF[ch];
-            v[I_FEAT + ch] = dchannel_dcolor * dpixF[ch];
+          if (FEAT) {
+            cd += c.w * dpixF[s][0] + d.x * dpixF[s][1] + d.y * dpixF[s][2];
+            v[I_FEAT + 0] += w * dpixF[s][0]; v[I_FEAT + 1] += w * dpixF[s][1]; v[I_FEAT + 2] += w * dpixF[s][2];
           }
-        }
-        dL_dalpha *= T;
-        last_alpha = alpha;
-        if (DCOL) {
-          if (bg_dot != 0.f) dL_dalpha += (-T_final / one_m_alpha) * bg_dot;
-        }
-        const float dL_dG = bb.z * dL_dalpha;
-        const float gdx = G * dx, gdy = G * dy;
-        const float dG_ddelx = -gdx * a.z - gdy * a.w;
-        const float dG_ddely = -gdy * bb.x - gdx * a.w;
-        v[I_MEAN + 0] = dL_dG * dG_ddelx * ddelx_dx;
-        v[I_MEAN + 1] = dL_dG * dG_ddely * ddely_dy;
-        if (GEOM) {
-          v[I_CONIC + 0] = -0.5f * gdx * dx * dL_dG;
-          v[I_CONIC + 1] = -0.5f * gdx * dy * dL_dG;
-          v[I_CONIC + 2] = -0.5f * gdy * dy * dL_dG;
-          v[I_OPAC] = G * dL_dalpha;
+          // "colour behind" recurrence on the dot product (backward.cu:527-538, per channel there)
+          accA[s] = alpha_last[s] * cd_last[s] + (1.f - alpha_last[s]) * accA[s];
+          cd_last[s] = cd;
+          alpha_last[s] = alpha[s];
+          float dL_dalpha = (cd - accA[s]) * T[s];
+          if (DCOL) dL_dalpha += bgT[s] * rcp;  // background term (backward.cu:545-550)
+          const float dL_dG = bb.z * dL_dalpha;
+          const float gdx = G[s] * dx, gdy = G[s] * dy[s];
+          const float dG_ddelx = -gdx * a.z - gdy * a.w;
+          const float dG_ddely = -gdy * bb.x - gdx * a.w;
+          v[I_MEAN + 0] += dL_dG * dG_ddelx * ddelx_dx;
+          v[I_MEAN + 1] += dL_dG * dG_ddely * ddely_dy;
+          if (GEOM) {
+            v[I_CONIC + 0] += -0.5f * gdx * dx * dL_dG;
+            v[I_CONIC + 1] += -0.5f * gdx * dy[s] * dL_dG;
+            v[I_CONIC + 2] += -0.5f * gdy * dy[s] * dL_dG;
+            v[I_OPAC] += G[s] * dL_dalpha;
+          }
         }
       }
       const uint32_t gid = __float_as_uint(d.z);
-      if (__popc(cmask) <= SPARSE_LANES) {
+      const bool any_mine = contrib[0] || contrib[1];
+      if (__popc(cmask[0] | cmask[1]) <= SPARSE_LANES) {
         // very few lanes contribute: their own REDs cost fewer issue slots than the 13-shuffle butterfly
-        if (contrib) {
+        if (any_mine) {
           atomicAdd(dL_dmean2D + (size_t)gid * 3, v[I_MEAN]);
           atomicAdd(dL_dmean2D + (size_t)gid * 3 + 1, v[I_MEAN + 1]);
           if (GEOM) {
@@ -238,7 +261,7 @@ void launch_one(dim3 grid, cudaStream_t s, int W, int H, const uint2* ranges, co
                 const float* bg, const float* final_T, const uint32_t* n_contrib, const float* dL_dcolor,
                 const float* dL_dfeature, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolors,
                 float* dL_dfeat) {
-  render_bwd_kernel<FEAT, DCOL, GEOM><<<grid, TILE_PIX, 0, s>>>(W, H, ranges, list, rec, bg, final_T, n_contrib,
+  render_bwd_kernel<FEAT, DCOL, GEOM><<<grid, BWD_THREADS, 0, s>>>(W, H, ranges, list, rec, bg, final_T, n_contrib,
                                                                  dL_dcolor, dL_dfeature, dL_dmean2D, dL_dconic,
                                                                  dL_dopacity, dL_dcolors, dL_dfeat);
 }

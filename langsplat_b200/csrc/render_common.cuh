@@ -15,13 +15,15 @@
 
 namespace lsr {
 
-struct BatchSmem {
-  float4 A[TILE_PIX];  // x, y, conic.x, conic.y
-  float4 B[TILE_PIX];  // conic.z, thr_m (pre-test threshold), opacity, position in the tile list (uint bits)
-  float4 C[TILE_PIX];  // r, g, b, f0
-  float4 D[TILE_PIX];  // f1, f2, gaussian id (uint bits), unused
-  uint32_t wcnt[TILE_PIX / 32];
+template <int NT>  // NT = threads per CTA = instances staged per batch
+struct BatchSmemT {
+  float4 A[NT];  // x, y, conic.x, conic.y
+  float4 B[NT];  // conic.z, thr_m (pre-test threshold), opacity, position in the tile list (uint bits)
+  float4 C[NT];  // r, g, b, f0
+  float4 D[NT];  // f1, f2, gaussian id (uint bits), unused
+  uint32_t wcnt[NT / 32];
 };
+using BatchSmem = BatchSmemT<TILE_PIX>;
 
 constexpr float kAlphaMin = 1.0f / 255.0f;
 
@@ -52,8 +54,9 @@ __device__ __forceinline__ bool tile_may_contribute(float mx, float my, float a,
 }
 
 // Stage one batch.  `list_index` is the index into the tile's range (0-based from range.x) this thread fetches, or -1.
-// Returns the number of surviving entries (identical in all threads).  Must be called by all TILE_PIX threads.
-__device__ __forceinline__ int stage_batch(BatchSmem& sm, const uint32_t* __restrict__ list,
+// Returns the number of surviving entries (identical in all threads).  Must be called by all NT threads of the CTA.
+template <int NT>
+__device__ __forceinline__ int stage_batch(BatchSmemT<NT>& sm, const uint32_t* __restrict__ list,
                                            const GeomRec* __restrict__ rec, uint32_t range_x, int list_index,
                                            float X0, float Y0) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -79,7 +82,7 @@ __device__ __forceinline__ int stage_batch(BatchSmem& sm, const uint32_t* __rest
   __syncthreads();
   int base = 0, total = 0;
 #pragma unroll
-  for (int w = 0; w < TILE_PIX / 32; w++) {
+  for (int w = 0; w < NT / 32; w++) {
     const int n = (int)sm.wcnt[w];
     if (w < warp) base += n;
     total += n;
