@@ -71,8 +71,11 @@ __device__ __forceinline__ int held_index(int lane) {
   }
 }
 
-constexpr int BWD_THREADS = 128;  // 4 warps x (8x8 pixels), two pixels per thread
-constexpr int BWD_SLOTS = 2;
+#ifndef LSR_BWD_SLOTS
+#define LSR_BWD_SLOTS 2
+#endif
+constexpr int BWD_SLOTS = LSR_BWD_SLOTS;             // pixels per thread (rows r, r+4, ...)
+constexpr int BWD_THREADS = TILE_PIX / BWD_SLOTS;     // 2 slots: 4 warps x (8x8 pixels)
 
 template <bool FEAT, bool DCOL, bool GEOM>
 __global__ void __launch_bounds__(BWD_THREADS)
@@ -93,7 +96,7 @@ render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
   __shared__ uint32_t s_max[BWD_THREADS / 32];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int tx = (warp & 1) * 8 + (lane & 7), ty = (warp >> 1) * 8 + (lane >> 3);  // slot s adds 4*s rows
+  const int tx = (warp & 1) * 8 + (lane & 7), ty = (warp >> 1) * (4 * BWD_SLOTS) + (lane >> 3);  // slot s adds 4*s rows
   const int tiles_x = (W + TILE_X - 1) / TILE_X;
   const uint32_t px = blockIdx.x * TILE_X + tx;
   const float pxf = (float)px;
@@ -171,7 +174,10 @@ render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
         // as in the forward.  The pre-test against thr_m avoids expf for pairs that certainly fail alpha >= 1/255.
         maybe[s] = (fwd < lastc[s]) && !(power[s] > 0.0f) && !(power[s] < bb.y);
       }
-      if (!__any_sync(0xffffffffu, maybe[0] || maybe[1])) continue;
+      bool any_maybe = false;
+#pragma unroll
+      for (int s = 0; s < BWD_SLOTS; s++) any_maybe |= maybe[s];
+      if (!__any_sync(0xffffffffu, any_maybe)) continue;
       float G[BWD_SLOTS], alpha[BWD_SLOTS];
       bool contrib[BWD_SLOTS];
       uint32_t cmask[BWD_SLOTS];
@@ -182,7 +188,11 @@ render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
         contrib[s] = maybe[s] && !(alpha[s] < kAlphaMin);
         cmask[s] = __ballot_sync(0xffffffffu, contrib[s]);
       }
-      if ((cmask[0] | cmask[1]) == 0u) continue;
+      uint32_t call = 0u;
+      bool any_mine = false;
+#pragma unroll
+      for (int s = 0; s < BWD_SLOTS; s++) { call |= cmask[s]; any_mine |= contrib[s]; }
+      if (call == 0u) continue;
 
       float v[12];
 #pragma unroll
@@ -227,8 +237,7 @@ render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
         }
       }
       const uint32_t gid = __float_as_uint(d.z);
-      const bool any_mine = contrib[0] || contrib[1];
-      if (__popc(cmask[0] | cmask[1]) <= SPARSE_LANES) {
+      if (__popc(call) <= SPARSE_LANES) {
         // very few lanes contribute: their own REDs cost fewer issue slots than the 13-shuffle butterfly
         if (any_mine) {
           atomicAdd(dL_dmean2D + (size_t)gid * 3, v[I_MEAN]);

@@ -43,7 +43,7 @@ render_fwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
   for (int i = 0; i < rounds; i++) {
     if (__syncthreads_count(done) == TILE_PIX) break;
     const int li = i * TILE_PIX + tid;
-    const int nb = stage_batch(sm, list, rec, range.x, li < len ? li : -1, X0, Y0);
+    const int nb = stage_batch<TILE_PIX>(sm, list, rec, range.x, li < len ? li : -1, X0, Y0);
     for (int j = 0; !done && j < nb; j++) {
       const float4 a = sm.A[j];
       const float4 b = sm.B[j];
