@@ -112,7 +112,8 @@ enum {
   LSR_ARR_IMG_RANGES = 12,   /* uint32[T][2] */
   LSR_ARR_SCR_KEYS_UNSORTED = 20, /* uint64[capacity] */
   LSR_ARR_SCR_VALS_UNSORTED = 21, /* uint32[capacity] */
-  LSR_ARR_SCR_KEYS_SORTED = 22    /* uint64[capacity] (valid after lsr_forward; position depends on pass parity) */
+  LSR_ARR_SCR_KEYS_SORTED = 22    /* uint64[capacity] sorted words as the forward keeps them (packed: use
+                                     lsr_debug_sorted_keys for the reference's key format) */
 };
 size_t lsr_array_offset(int which, int32_t P, int32_t width, int32_t height, int64_t capacity);
 
@@ -146,6 +147,13 @@ size_t lsr_sort_work_bytes(int64_t n);
 int lsr_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
                    uint64_t* keys_tmp, uint32_t* vals_tmp, int64_t n, int end_bit, void* work, size_t work_bytes,
                    void* stream);
+
+/* Tests / debugging: writes the sorted instance keys of the most recent lsr_forward issued from this thread, in the
+ * reference's format (tile_id << 32 | float bits of depth; point_list_keys of rasterizer_impl.cu:181-194), into
+ * keys_out[num_rendered].  The forward sorts a packed form of the same keys (compacted key | Gaussian id in one
+ * 64-bit word); this is its exact inverse.  `scratch` is the buffer that forward was given. */
+int lsr_debug_sorted_keys(const void* scratch, int32_t P, int64_t capacity, int64_t num_rendered, uint64_t* keys_out,
+                          void* stream);
 
 /* Per-stage device timing (CUDA events on `stream`), used by bench.py for the live roofline figures.
  * lsr_profile_enable(1) makes forward/backward record events; lsr_profile_read() synchronises the events of the

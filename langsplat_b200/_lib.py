@@ -59,6 +59,7 @@ EXPORTS = {
     "lsr_sort_work_bytes": (c_size_t, [c_int64]),
     "lsr_sort_pairs": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p,
                                c_size_t, c_void_p]),
+    "lsr_debug_sorted_keys": (c_int, [c_void_p, c_int32, c_int64, c_int64, c_void_p, c_void_p]),
     "lsr_profile_enable": (None, [c_int]),
     "lsr_profile_read": (c_int, [POINTER(c_float), c_int]),
     "lsr_profile_stage_name": (c_char_p, [c_int]),

@@ -71,6 +71,9 @@ static inline void prof(cudaEvent_t* arr, int i, cudaStream_t s) {
   if (g_profile) cudaEventRecord(arr[i], s);
 }
 
+// plan of the most recent forward on this thread (lsr_debug_sorted_keys decodes the packed words with it)
+static thread_local SortPlan g_last_plan = {0u, 32, 0, 32, 4, 0, false};
+
 static uint32_t* pinned_ctrl() {
   static thread_local uint32_t* p = nullptr;
   if (!p) cudaMallocHost(&p, 64 * sizeof(uint32_t));
@@ -149,6 +152,21 @@ int lsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, c
   if (!means3D || !viewmatrix || !present) return fail(LSR_ERR_INVALID, "null pointer");
   launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream);
   LSR_CUDA(cudaGetLastError());
+  return LSR_OK;
+}
+
+int lsr_debug_sorted_keys(const void* scratch, int32_t P, int64_t capacity, int64_t num_rendered, uint64_t* keys_out,
+                          void* stream) {
+  if (num_rendered == 0) return LSR_OK;
+  if (!scratch || !keys_out || num_rendered < 0 || num_rendered > capacity) return fail(LSR_ERR_INVALID, "bad argument");
+  ScratchView sc = scratch_view(const_cast<void*>(scratch), P, capacity);
+  if (g_last_plan.packed) {
+    launch_unpack_keys(num_rendered, sc.keys_b, keys_out, g_last_plan, (cudaStream_t)stream);
+    LSR_CUDA(cudaGetLastError());
+  } else {
+    LSR_CUDA(cudaMemcpyAsync(keys_out, sc.keys_b, (size_t)num_rendered * 8, cudaMemcpyDeviceToDevice,
+                             (cudaStream_t)stream));
+  }
   return LSR_OK;
 }
 
@@ -238,7 +256,11 @@ int lsr_forward(const lsr_frame* frame, const lsr_inputs* in, float* out_color, 
     prof(g_ev_f, 3, s);
     // the reference sorts bits [0, 32 + getHigherMsb(T)) (rasterizer_impl.cu:303,311); the depth word only spans
     // [min, max], so the same order is obtained from hi_bits + bitlength(max - min) bits
-    const SortPlan plan = make_sort_plan(~h[CTRL_DEPTH_NEGMIN], h[CTRL_DEPTH_MAX], (int)higher_msb((uint32_t)T));
+    int id_bits = 1;
+    while (id_bits < 32 && (((uint32_t)P - 1u) >> id_bits) != 0) id_bits++;
+    const SortPlan plan =
+        make_sort_plan(~h[CTRL_DEPTH_NEGMIN], h[CTRL_DEPTH_MAX], (int)higher_msb((uint32_t)T), id_bits);
+    g_last_plan = plan;
     // the sorted keys always end up in keys_b: the unsorted ones start in keys_a (odd pass count) or keys_b (even)
     uint64_t* kin = (plan.passes & 1) ? sc.keys_a : sc.keys_b;
     uint64_t* ktmp = sc.keys_a;
@@ -256,7 +278,7 @@ int lsr_forward(const lsr_frame* frame, const lsr_inputs* in, float* out_color, 
     }
     prof(g_ev_f, 5, s);
     if (R > 0) {
-      launch_tile_ranges(R, keys_sorted, img.ranges, s);
+      launch_tile_ranges(R, keys_sorted, plan.packed ? plan.id_bits + plan.lo_bits : 32, img.ranges, s);
       LSR_STAGE("tile_ranges");
     }
     prof(g_ev_f, 6, s);

@@ -113,7 +113,8 @@ scan_tiles_kernel(int P, const uint32_t* __restrict__ in, uint32_t* __restrict__
 // The kernel also accumulates the radix sort's digit histograms for every pass (in shared memory, flushed once per
 // CTA), so the sort never reads the keys just to count them.  Passes whose digit lies entirely inside the depth word
 // are counted once per Gaussian with weight tiles_touched; the others per instance, with runs of equal digits in a
-// warp collapsed into one shared-memory atomic.
+// warp collapsed into one shared-memory atomic (a full-warp shared atomic costs ~34 SM-cycles on B200, so only run
+// heads issue one).
 // ------------------------------------------------------------------------------------------------------------
 constexpr int DUP_THREADS = 256;
 
@@ -146,7 +147,7 @@ duplicate_kernel(int P, int gx, int gy, const int32_t* __restrict__ radii, const
     const uint32_t wstart = __shfl_sync(0xffffffffu, start, 0);          // warp's output range [wstart, wend)
     const uint32_t wend = __shfl_sync(0xffffffffu, incl, 31);
     const uint32_t rel = start - wstart;
-    const uint32_t magic = w > 1 ? (uint32_t)((0x100000000ull + w - 1) / w) : 0u;
+    const uint32_t magic = w > 1 ? 0xffffffffu / w + 1u : 0u;  // ceil(2^32 / w)
     const uint32_t origin = (y0 << 16) | x0;
     const uint32_t lo = dbits - plan.lo_min;
     if (cnt > 0) {
@@ -175,12 +176,17 @@ duplicate_kernel(int P, int gx, int gy, const int32_t* __restrict__ radii, const
       const uint32_t y = (jorigin >> 16) + q, x = (jorigin & 0xffffu) + (r - q * jw);
       const uint32_t tile = y * (uint32_t)gx + x;
       const uint32_t o = wstart + k;
+      // compacted key (radix_sort.cu): tile above the depth word's offset from its minimum
+      const uint64_t c = ((uint64_t)tile << plan.lo_bits) | (uint64_t)(jd - plan.lo_min);
       if (ok && o < capacity) {
-        keys[o] = ((uint64_t)tile << 32) | jd;
-        vals[o] = (uint32_t)(wbase_idx + j);
+        if (plan.packed) {
+          keys[o] = (c << plan.id_bits) | (uint64_t)(uint32_t)(wbase_idx + j);  // id rides in the low bits
+        } else {
+          keys[o] = ((uint64_t)tile << 32) | jd;
+          vals[o] = (uint32_t)(wbase_idx + j);
+        }
       }
       // digits that involve tile bits: one shared atomic per run of equal digits
-      const uint64_t c = ((uint64_t)tile << plan.lo_bits) | (uint64_t)(jd - plan.lo_min);
       for (int p = per_gaussian; p < passes; p++) {
         const int shift = p * SORT_RADIX_BITS;
         const int bits = min(SORT_RADIX_BITS, plan.total_bits - shift);
@@ -205,20 +211,30 @@ duplicate_kernel(int P, int gx, int gy, const int32_t* __restrict__ radii, const
 // K5': identifyTileRanges (rasterizer_impl.cu:116-138).  ranges must be zero on entry (cudaMemset, :313).
 // ------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-tile_ranges_kernel(uint32_t L, const uint64_t* __restrict__ keys, uint2* __restrict__ ranges) {
+tile_ranges_kernel(uint32_t L, const uint64_t* __restrict__ keys, int tile_shift, uint2* __restrict__ ranges) {
   const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= L) return;
-  const uint32_t cur = (uint32_t)(keys[idx] >> 32);
+  const uint32_t cur = (uint32_t)(keys[idx] >> tile_shift);
   if (idx == 0) {
     ranges[cur].x = 0;
   } else {
-    const uint32_t prev = (uint32_t)(keys[idx - 1] >> 32);
+    const uint32_t prev = (uint32_t)(keys[idx - 1] >> tile_shift);
     if (cur != prev) {
       ranges[prev].y = idx;
       ranges[cur].x = idx;
     }
   }
   if (idx == L - 1) ranges[cur].y = L;
+}
+
+// packed sorted word -> the reference's key format (tile << 32 | depth bits); exact inverse of the packing above
+__global__ void __launch_bounds__(256)
+unpack_keys_kernel(uint32_t L, const uint64_t* __restrict__ words, uint64_t* __restrict__ keys, SortPlan plan) {
+  const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= L) return;
+  const uint64_t c = words[idx] >> plan.id_bits;
+  const uint32_t lo = (uint32_t)(c & ((1ull << plan.lo_bits) - 1)) + plan.lo_min;
+  keys[idx] = ((c >> plan.lo_bits) << 32) | lo;
 }
 
 }  // namespace
@@ -237,13 +253,19 @@ void launch_duplicate(int P, int grid_x, int grid_y, const int32_t* radii, GeomV
   const int nblocks = (P + DUP_THREADS - 1) / DUP_THREADS;
   const int grid = nblocks < 148 * 8 ? nblocks : 148 * 8;  // persistent CTAs: one histogram flush each
   duplicate_kernel<<<grid, DUP_THREADS, 0, s>>>(P, grid_x, grid_y, radii, g.rec, g.depth, g.offsets, keys, vals,
-                                                (uint32_t)capacity, plan, ghist);
+                                                   (uint32_t)capacity, plan, ghist);
   count_launch();
 }
 
-void launch_tile_ranges(int64_t R, const uint64_t* keys, uint2* ranges, cudaStream_t s) {
+void launch_tile_ranges(int64_t R, const uint64_t* keys, int tile_shift, uint2* ranges, cudaStream_t s) {
   if (R <= 0) return;
-  tile_ranges_kernel<<<(unsigned)((R + 255) / 256), 256, 0, s>>>((uint32_t)R, keys, ranges);
+  tile_ranges_kernel<<<(unsigned)((R + 255) / 256), 256, 0, s>>>((uint32_t)R, keys, tile_shift, ranges);
+  count_launch();
+}
+
+void launch_unpack_keys(int64_t R, const uint64_t* words, uint64_t* keys, const SortPlan& plan, cudaStream_t s) {
+  if (R <= 0) return;
+  unpack_keys_kernel<<<(unsigned)((R + 255) / 256), 256, 0, s>>>((uint32_t)R, words, keys, plan);
   count_launch();
 }
 

@@ -136,11 +136,14 @@ inline size_t scratch_bytes(int P, int64_t cap) {
 enum CtrlWord { CTRL_NUM_RENDERED = 0, CTRL_SCAN_TICKET = 1, CTRL_ERROR = 2, CTRL_DEPTH_NEGMIN = 3, CTRL_DEPTH_MAX = 4 };
 
 // Which bits the sort has to look at: digits are taken from (hi << lo_bits) | (lo - lo_min)  (radix_sort.cu).
+// packed: the Gaussian id (id_bits) rides in the low bits of the 64-bit word, above it the compacted key; the sort
+// then moves 8-byte words only.  Falls back to (key, value) pairs when hi_bits + lo_bits + id_bits > 64.
 struct SortPlan {
   uint32_t lo_min;
-  int lo_bits, hi_bits, total_bits, passes;
+  int lo_bits, hi_bits, total_bits, passes, id_bits;
+  bool packed;
 };
-SortPlan make_sort_plan(uint32_t lo_min, uint32_t lo_max, int hi_bits);
+SortPlan make_sort_plan(uint32_t lo_min, uint32_t lo_max, int hi_bits, int id_bits);
 SortPlan make_sort_plan_bits(int end_bit);
 
 // ---- launchers implemented in the .cu files ----
@@ -150,7 +153,10 @@ void launch_scan_tiles(int P, const uint32_t* tiles, uint32_t* offsets, uint64_t
                        cudaStream_t s);
 void launch_duplicate(int P, int grid_x, int grid_y, const int32_t* radii, GeomView g, uint64_t* keys, uint32_t* vals,
                       int64_t capacity, const SortPlan& plan, uint32_t* ghist, cudaStream_t s);
-void launch_tile_ranges(int64_t R, const uint64_t* keys, uint2* ranges, cudaStream_t s);
+// tile id of a sorted word = word >> tile_shift (32 for reference-format keys)
+void launch_tile_ranges(int64_t R, const uint64_t* keys, int tile_shift, uint2* ranges, cudaStream_t s);
+// reference-format keys (tile << 32 | depth bits) from the packed sorted words (tests / debugging)
+void launch_unpack_keys(int64_t R, const uint64_t* words, uint64_t* keys, const SortPlan& plan, cudaStream_t s);
 // hist_ready: the per-pass digit histograms are already in the work buffer (sort_prepare + duplication kernel)
 void sort_prepare(void* work, int64_t n, const SortPlan& pl, cudaStream_t s);
 int sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,

@@ -10,9 +10,10 @@
 //  * One kernel per digit does rank + scatter in a single sweep, chaining tile prefixes through global memory with
 //    decoupled look-back (no scan pass between digits).  Each CTA turns the raw global histogram into exclusive bin
 //    bases itself (256-bin block scan), so there is no separate scan launch either.
-//  * Ranking inside a CTA is a warp-level multi-split built from BITS ballots per key (MATCH.ANY goes through the
-//    slow MIO path on sm_100a: the first version's histogram kernel spent 134 us on it); the group leader bumps a
-//    per-warp shared histogram, ranks come from popc of the lower-lane mask.  Keys, then values, are staged in
+//  * Ranking inside a CTA is a warp-level multi-split: 8 ballots group the lanes holding the same digit (measured on
+//    B200, profiles/tools/ubench_rank.cu, SM-cycles per warp instruction: 8 ballots 14; MATCH.ANY 5 when all lanes
+//    agree but 66 when all differ; a shared-memory atomic 34), the group's lowest lane bumps a per-warp shared
+//    histogram with a plain read-modify-write, ranks come from popc of the lower-lane mask.  Keys, then values, are staged in
 //    shared memory in CTA-sorted order so the global scatter is written as coalesced runs.
 //  * Digits are taken from a COMPACTED view of the key, (hi << lo_bits) | (lo - lo_min): the forward knows the range
 //    of the depth word (min / max of the float bits, reduced in the preprocess kernel), and depth bits minus their
@@ -45,24 +46,36 @@ __device__ __forceinline__ uint32_t digit_of(uint64_t key, const DigitMap m, int
 }
 
 // Stand-alone histogram of all passes (lsr_sort_pairs only; the forward fuses this into the duplication kernel).
+// Warp-private shared histograms, one plain read-modify-write per group of equal digits (no shared atomics).
 __global__ void __launch_bounds__(256)
 sort_hist_kernel(const uint64_t* __restrict__ keys, uint32_t n, int passes, int total_bits, DigitMap dm,
                  uint32_t* __restrict__ ghist) {
-  __shared__ uint32_t sh[SORT_MAX_PASSES * BINS];
-  for (int j = threadIdx.x; j < passes * BINS; j += 256) sh[j] = 0;
+  extern __shared__ uint32_t sh_hist[];  // [8 warps][passes][BINS]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int j = tid; j < 8 * passes * BINS; j += 256) sh_hist[j] = 0;
   __syncthreads();
+  uint32_t* wh = sh_hist + warp * passes * BINS;
   const uint32_t stride = gridDim.x * 256;
-  for (uint32_t i = blockIdx.x * 256 + threadIdx.x; i < n; i += stride) {
-    const uint64_t key = __ldg(keys + i);
+  const uint32_t n_round = (n + 31) & ~31u;  // keep warps converged for match.any
+  for (uint32_t i = blockIdx.x * 256 + tid; i < n_round; i += stride) {
+    const bool ok = i < n;
+    const uint64_t key = ok ? __ldg(keys + i) : 0ull;
     for (int p = 0; p < passes; p++) {
       const int shift = p * BITS;
       const int bits = min(BITS, total_bits - shift);
-      atomicAdd(&sh[p * BINS + digit_of(key, dm, shift, (1u << bits) - 1)], 1u);
+      const uint32_t d = ok ? digit_of(key, dm, shift, (1u << bits) - 1) : 0xffffffffu;
+      const uint32_t peers = __match_any_sync(0xffffffffu, d);
+      if (ok && (peers & ((1u << lane) - 1)) == 0) wh[p * BINS + d] += __popc(peers);
+      __syncwarp();
     }
   }
   __syncthreads();
-  for (int j = threadIdx.x; j < passes * BINS; j += 256)
-    if (sh[j]) atomicAdd(&ghist[j], sh[j]);
+  for (int j = tid; j < passes * BINS; j += 256) {
+    uint32_t c = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) c += sh_hist[w * passes * BINS + j];
+    if (c) atomicAdd(&ghist[j], c);
+  }
 }
 
 // Per-pass digit extraction with all shift amounts precomputed on the host (PTX shifts clamp at 32, so the terms
@@ -85,7 +98,9 @@ __device__ __forceinline__ uint32_t pass_digit(uint64_t key, const PassDigit& pd
   return (shr32(lo, pd.s1) | shl32(hi, pd.s2) | shr32(hi, pd.s3)) & pd.mask;
 }
 
-// lanes of the warp holding the same NB-bit digit: NB ballots, 4 instructions per bit
+// Lanes of the warp holding the same digit, from NB ballots.  MATCH.ANY would be one instruction, but on B200 its cost
+// grows with the number of DISTINCT values in the warp (profiles/tools/ubench_rank.cu: 5 SM-cycles per warp
+// instruction when all lanes agree, 66 when all differ — and radix digits mostly differ); 8 ballots cost ~14.
 template <int NB>
 __device__ __forceinline__ uint32_t match_digit(uint32_t d) {
   uint32_t peers = 0xffffffffu;
@@ -104,11 +119,21 @@ __device__ __forceinline__ uint32_t match_digit(uint32_t d) {
   return peers;
 }
 
-template <int NB>
+// Shared-memory staging index of CTA-sorted position p.  Keys whose digits are consecutive (instances of one Gaussian
+// cover consecutive tiles) land ~SORT_TILE/BINS = 16 positions apart, i.e. in the same bank for 8-byte elements; the
+// XOR swizzle spreads them (ncu: the tile-id pass ran at 99 us against 53 us for the depth passes without it).
+__device__ __forceinline__ uint32_t sw(uint32_t p) { return p ^ ((p >> 4) & 15u); }
+
+// PAIRS = true: (key, value) pairs in separate arrays (lsr_sort_pairs, and forwards whose key + id exceed 64 bits).
+// PAIRS = false: the value rides in the low bits of the 64-bit word (binning.cu packs compacted key | Gaussian id), so
+// a pass moves 8 instead of 12 bytes per element and the whole value phase disappears; the last pass additionally
+// writes the ids out as the u32 point list (`ids_out`).
+template <int NB, bool PAIRS>
 __global__ void __launch_bounds__(SORT_THREADS, 4)
 onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, const uint32_t* __restrict__ vin,
                 uint32_t* __restrict__ vout, uint32_t n, uint32_t* __restrict__ ticket,
-                volatile uint32_t* __restrict__ lookback, const uint32_t* __restrict__ ghist, PassDigit pd) {
+                volatile uint32_t* __restrict__ lookback, const uint32_t* __restrict__ ghist, PassDigit pd,
+                uint32_t* __restrict__ ids_out, uint32_t id_mask) {
   extern __shared__ __align__(16) unsigned char smem[];
   uint64_t* s_keys = reinterpret_cast<uint64_t*>(smem);
   uint32_t* s_vals = reinterpret_cast<uint32_t*>(smem);  // reuses the key region after the keys are written out
@@ -174,8 +199,8 @@ onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, c
 #pragma unroll
   for (int i = 0; i < SORT_ITEMS; i++) {
     const uint32_t d = (dig[i >> 2] >> (8 * (i & 3))) & 0xffu;
-    // padding digits may exceed NB bits only in the last tile; matching on NB bits would alias them with real keys
-    const uint32_t peers = full ? match_digit<NB>(d) : match_digit<BITS>(d);
+    // (padding digits of a partial last tile may exceed NB bits, so that tile matches on all 8)
+    const uint32_t peers = NB == 0 ? __match_any_sync(0xffffffffu, d) : (full ? match_digit<NB>(d) : match_digit<BITS>(d));
     const uint32_t lower = peers & lt;
     const uint32_t prev = wh[d];             // every lane of the group reads the running count ...
     __syncwarp();
@@ -226,12 +251,12 @@ onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, c
     const uint32_t d = (dig[i >> 2] >> (8 * (i & 3))) & 0xffu;
     const uint32_t pos = wh[d] + rank[i];
     rank[i] = (uint16_t)pos;
-    s_keys[pos] = key[i];
-    s_dig[pos] = (uint8_t)d;
+    s_keys[sw(pos)] = key[i];
+    s_dig[sw(pos)] = (uint8_t)d;
   }
   // the values are fetched now: their latency overlaps the key write-out
-  uint32_t val[SORT_ITEMS];
-  {
+  uint32_t val[PAIRS ? SORT_ITEMS : 1];
+  if (PAIRS) {
     const uint32_t* vp = vin + tile_base + wofs;
     if (full) {
 #pragma unroll
@@ -273,53 +298,68 @@ onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, c
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
       const uint32_t p = tid + i * SORT_THREADS;
-      kout[s_gofs[s_dig[p]] + p] = s_keys[p];
+      const uint64_t k = s_keys[sw(p)];
+      const uint32_t g = s_gofs[s_dig[sw(p)]] + p;
+      kout[g] = k;
+      if (!PAIRS && ids_out != nullptr) ids_out[g] = (uint32_t)k & id_mask;
     }
   } else {
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
       const uint32_t p = tid + i * SORT_THREADS;
-      if (p < valid) kout[s_gofs[s_dig[p]] + p] = s_keys[p];
+      if (p < valid) {
+        const uint64_t k = s_keys[sw(p)];
+        const uint32_t g = s_gofs[s_dig[sw(p)]] + p;
+        kout[g] = k;
+        if (!PAIRS && ids_out != nullptr) ids_out[g] = (uint32_t)k & id_mask;
+      }
     }
   }
+  if (!PAIRS) return;
   __syncthreads();
 #pragma unroll
-  for (int i = 0; i < SORT_ITEMS; i++) s_vals[rank[i]] = val[i];
+  for (int i = 0; i < SORT_ITEMS; i++) s_vals[sw(rank[i])] = val[PAIRS ? i : 0];
   __syncthreads();
   if (full) {
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
       const uint32_t p = tid + i * SORT_THREADS;
-      vout[s_gofs[s_dig[p]] + p] = s_vals[p];
+      vout[s_gofs[s_dig[sw(p)]] + p] = s_vals[sw(p)];
     }
   } else {
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
       const uint32_t p = tid + i * SORT_THREADS;
-      if (p < valid) vout[s_gofs[s_dig[p]] + p] = s_vals[p];
+      if (p < valid) vout[s_gofs[s_dig[sw(p)]] + p] = s_vals[sw(p)];
     }
   }
 }
 
 using OnesweepFn = void (*)(const uint64_t*, uint64_t*, const uint32_t*, uint32_t*, uint32_t, uint32_t*,
-                            volatile uint32_t*, const uint32_t*, PassDigit);
-OnesweepFn onesweep_for_bits(int nb) {
+                            volatile uint32_t*, const uint32_t*, PassDigit, uint32_t*, uint32_t);
+template <bool PAIRS>
+OnesweepFn onesweep_for_bits_t(int nb) {
   switch (nb) {
-    case 1: return onesweep_kernel<1>;
-    case 2: return onesweep_kernel<2>;
-    case 3: return onesweep_kernel<3>;
-    case 4: return onesweep_kernel<4>;
-    case 5: return onesweep_kernel<5>;
-    case 6: return onesweep_kernel<6>;
-    case 7: return onesweep_kernel<7>;
-    default: return onesweep_kernel<8>;
+    case 0: return onesweep_kernel<0, PAIRS>;
+    case 1: return onesweep_kernel<1, PAIRS>;
+    case 2: return onesweep_kernel<2, PAIRS>;
+    case 3: return onesweep_kernel<3, PAIRS>;
+    case 4: return onesweep_kernel<4, PAIRS>;
+    case 5: return onesweep_kernel<5, PAIRS>;
+    case 6: return onesweep_kernel<6, PAIRS>;
+    case 7: return onesweep_kernel<7, PAIRS>;
+    default: return onesweep_kernel<8, PAIRS>;
   }
+}
+OnesweepFn onesweep_for_bits(int nb, bool pairs) {
+  return pairs ? onesweep_for_bits_t<true>(nb) : onesweep_for_bits_t<false>(nb);
 }
 
 }  // namespace
 
-SortPlan make_sort_plan(uint32_t lo_min, uint32_t lo_max, int hi_bits) {
+SortPlan make_sort_plan(uint32_t lo_min, uint32_t lo_max, int hi_bits, int id_bits) {
   SortPlan pl;
+  pl.id_bits = id_bits;
   pl.lo_min = lo_min;
   uint32_t span = lo_max >= lo_min ? lo_max - lo_min : 0u;
   int lb = 0;
@@ -329,6 +369,7 @@ SortPlan make_sort_plan(uint32_t lo_min, uint32_t lo_max, int hi_bits) {
   pl.total_bits = pl.lo_bits + pl.hi_bits;
   if (pl.total_bits > 64) pl.total_bits = 64;
   pl.passes = (pl.total_bits + BITS - 1) / BITS;
+  pl.packed = id_bits > 0 && pl.total_bits + id_bits <= 64;
   return pl;
 }
 
@@ -341,6 +382,8 @@ SortPlan make_sort_plan_bits(int end_bit) {
   pl.hi_bits = end_bit - pl.lo_bits;
   pl.total_bits = end_bit;
   pl.passes = (end_bit + BITS - 1) / BITS;
+  pl.id_bits = 0;
+  pl.packed = false;
   return pl;
 }
 
@@ -359,15 +402,19 @@ int sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_
   const uint32_t nblocks = (uint32_t)((n + SORT_TILE - 1) / SORT_TILE);
   static bool attr_done = false;
   if (!attr_done) {
-    for (int nb = 1; nb <= BITS; nb++)
-      cudaFuncSetAttribute(onesweep_for_bits(nb), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM);
+    for (int nb = 0; nb <= BITS; nb++) {
+      cudaFuncSetAttribute(onesweep_for_bits(nb, true), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM);
+      cudaFuncSetAttribute(onesweep_for_bits(nb, false), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM);
+    }
     attr_done = true;
   }
   const DigitMap dm{pl.lo_min, pl.lo_bits};
   if (!hist_ready) {
     sort_prepare(work, n, pl, s);
     const uint32_t hist_blocks = (uint32_t)std::min<int64_t>((n + 2047) / 2048, (int64_t)148 * 8);
-    sort_hist_kernel<<<hist_blocks, 256, 0, s>>>(keys_in, (uint32_t)n, pl.passes, pl.total_bits, dm, w.hist);
+    const size_t hist_smem = (size_t)8 * pl.passes * BINS * 4;
+    cudaFuncSetAttribute(sort_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_smem);
+    sort_hist_kernel<<<hist_blocks, 256, hist_smem, s>>>(keys_in, (uint32_t)n, pl.passes, pl.total_bits, dm, w.hist);
     count_launch();
   }
   const uint64_t* ksrc = keys_in;
@@ -382,12 +429,24 @@ int sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_
     PassDigit pd;
     pd.lo_min = pl.lo_min;
     pd.mask = (1u << bits) - 1;
-    pd.s1 = shift < pl.lo_bits ? (uint32_t)shift : 32u;
-    pd.s2 = (shift < pl.lo_bits && pl.lo_bits - shift < 32) ? (uint32_t)(pl.lo_bits - shift) : 32u;
-    pd.s3 = shift >= pl.lo_bits ? (uint32_t)std::min(shift - pl.lo_bits, 32) : 32u;
-    onesweep_for_bits(bits)<<<nblocks, SORT_THREADS, SORT_SMEM, s>>>(
+    if (pl.packed) {
+      // word = (compacted key << id_bits) | id:  d = (word >> (id_bits + shift)) & mask
+      const int sh = pl.id_bits + shift;
+      pd.lo_min = 0;
+      pd.s1 = sh < 32 ? (uint32_t)sh : 32u;
+      pd.s2 = (sh < 32 && sh > 0) ? (uint32_t)(32 - sh) : 32u;
+      pd.s3 = sh >= 32 ? (uint32_t)(sh - 32) : 32u;
+    } else {
+      pd.s1 = shift < pl.lo_bits ? (uint32_t)shift : 32u;
+      pd.s2 = (shift < pl.lo_bits && pl.lo_bits - shift < 32) ? (uint32_t)(pl.lo_bits - shift) : 32u;
+      pd.s3 = shift >= pl.lo_bits ? (uint32_t)std::min(shift - pl.lo_bits, 32) : 32u;
+    }
+    const bool last = p == pl.passes - 1;
+    const bool depth_only = shift + bits <= pl.lo_bits && bits == BITS;  // digit inside the depth word: MATCH.ANY
+    onesweep_for_bits(depth_only ? 0 : bits, !pl.packed)<<<nblocks, SORT_THREADS, SORT_SMEM, s>>>(
         ksrc, kdst, vsrc, vdst, (uint32_t)n, w.tickets + p, w.lookback + (size_t)p * sort_nblocks(n) * BINS,
-        w.hist + p * BINS, pd);
+        w.hist + p * BINS, pd, (pl.packed && last) ? vals_out : nullptr,
+        pl.id_bits >= 32 ? 0xffffffffu : ((1u << pl.id_bits) - 1));
     count_launch();
     ksrc = kdst;
     vsrc = vdst;

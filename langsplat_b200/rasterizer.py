@@ -340,6 +340,9 @@ def debug_arrays(state) -> Dict[str, torch.Tensor]:
     if "scratch" in state:
         sc = state["scratch"]
         # (the unsorted keys are overwritten by the sort's ping-pong; the sorted keys are the same multiset)
-        out["values_unsorted"] = view(sc, L.ARR_SCR_VALS_UNSORTED, torch.int32, R)
-        out["keys"] = view(sc, L.ARR_SCR_KEYS_SORTED, torch.int64, R)
+        keys = torch.empty((R,), dtype=torch.int64, device=sc.device)
+        rc = lib.lsr_debug_sorted_keys(_ptr(sc), P, cap, R, _ptr(keys),
+                                       ctypes.c_void_p(torch.cuda.current_stream(sc.device).cuda_stream))
+        _check(rc, "lsr_debug_sorted_keys")
+        out["keys"] = keys
     return out
