@@ -136,11 +136,12 @@ __device__ __forceinline__ void sh_basis(int deg, float x, float y, float z, flo
 
 constexpr int BPRE_THREADS = 256;
 constexpr int SH_ROW = 12;
-constexpr size_t BPRE_SH_SMEM = (size_t)(BPRE_THREADS / 32) * 32 * (SH_ROW + 1) * sizeof(float4);
+constexpr int BPRE_WARP_F4 = 32 * (SH_ROW + 1) + 48;  // per warp: 32 padded SH rows + 32 cov3D rows (24 B each)
+constexpr size_t BPRE_SH_SMEM = (size_t)(BPRE_THREADS / 32) * BPRE_WARP_F4 * sizeof(float4);
 
 // SH16: shs / dL_dsh are [P,16,3], 16-byte aligned -> rows move through shared memory as coalesced 16-byte chunks.
 template <bool SH16>
-__global__ void __launch_bounds__(BPRE_THREADS)
+__global__ void __launch_bounds__(BPRE_THREADS, 3)
 preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, const int32_t* __restrict__ radii,
                       const float* __restrict__ shs, const uint8_t* __restrict__ clamped,
                       const float* __restrict__ scales, const float* __restrict__ rotations, float scale_modifier,
@@ -166,36 +167,41 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   if (tid < 3) s_cam[tid] = campos[tid];
   const bool do_sh = shs != nullptr && dL_dsh != nullptr && dL_dcolor != nullptr;
   const bool do_scale = scales != nullptr && dL_dscale != nullptr;
-  stage_flat<BPRE_THREADS>(means3D, s_xyz, (size_t)first * 3, count * 3, tid);
-  stage_flat<BPRE_THREADS>(dL_dmean2D, s_m2d, (size_t)first * 3, count * 3, tid);
-  if (do_scale) stage_flat<BPRE_THREADS>(scales, s_scl, (size_t)first * 3, count * 3, tid);
-  if (do_sh) stage_flat<BPRE_THREADS>(dL_dcolor, s_dcol, (size_t)first * 3, count * 3, tid);
-  __syncthreads();
   const bool valid = tid < count;
   const int idx = first + tid;
   const bool vis = valid && radii[idx] > 0;
   const uint32_t vis_mask = __ballot_sync(0xffffffffu, vis);
   const uint32_t valid_mask = __ballot_sync(0xffffffffu, valid);
-  float4* wsm = s_dyn + (size_t)warp * 32 * (SH_ROW + 1);
+  float4* wsm = s_dyn + (size_t)warp * BPRE_WARP_F4;
+  float2* wcov = reinterpret_cast<float2*>(wsm + 32 * (SH_ROW + 1));
   const size_t wfirst = (size_t)(first + warp * 32);
 
-  // cov3D rows of the warp's visible Gaussians: coalesced 8-byte chunks through shared memory
-  float cov3D[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  // Everything this CTA reads is requested up front with cp.async: group 0 = the flat triplet arrays and the cov3D
+  // rows (needed first), group 1 = the SH rows of the visible Gaussians, which then fly during the geometry backward.
+  stage_flat_async<BPRE_THREADS>(means3D, s_xyz, (size_t)first * 3, count * 3, tid);
+  stage_flat_async<BPRE_THREADS>(dL_dmean2D, s_m2d, (size_t)first * 3, count * 3, tid);
+  if (do_scale) stage_flat_async<BPRE_THREADS>(scales, s_scl, (size_t)first * 3, count * 3, tid);
+  if (do_sh) stage_flat_async<BPRE_THREADS>(dL_dcolor, s_dcol, (size_t)first * 3, count * 3, tid);
   {
-    float2* w2 = reinterpret_cast<float2*>(wsm);
     const float2* src = reinterpret_cast<const float2*>(cov3Ds + wfirst * 6);
 #pragma unroll
     for (int it = 0; it < 3; it++) {
       const int c = it * 32 + lane;
-      if ((vis_mask >> (c / 3)) & 1u) w2[c] = __ldg(src + c);
+      if ((vis_mask >> (c / 3)) & 1u) cp_async8(wcov + c, src + c);
     }
-    __syncwarp();
-    if (vis) {
-      const float2 a = w2[lane * 3], b = w2[lane * 3 + 1], c = w2[lane * 3 + 2];
-      cov3D[0] = a.x; cov3D[1] = a.y; cov3D[2] = b.x; cov3D[3] = b.y; cov3D[4] = c.x; cov3D[5] = c.y;
-    }
-    __syncwarp();
   }
+  cp_async_commit();
+  if (do_sh && SH16)
+    warp_load_rows_async<SH_ROW>(reinterpret_cast<const float4*>(shs) + wfirst * SH_ROW, wsm, vis_mask, lane);
+  cp_async_commit();
+  cp_async_wait<1>();
+  __syncthreads();
+  float cov3D[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (vis) {
+    const float2 a = wcov[lane * 3], b = wcov[lane * 3 + 1], c = wcov[lane * 3 + 2];
+    cov3D[0] = a.x; cov3D[1] = a.y; cov3D[2] = b.x; cov3D[3] = b.y; cov3D[4] = c.x; cov3D[5] = c.y;
+  }
+  __syncwarp();
   const float mx = s_xyz[3 * tid], my = s_xyz[3 * tid + 1], mz = s_xyz[3 * tid + 2];
   float dcov[6] = {0, 0, 0, 0, 0, 0};
   float3 dmean = make_float3(0.f, 0.f, 0.f);
@@ -262,7 +268,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   }
   // dL_dcov3D: coalesced write-out (zeros for Gaussians with radius 0)
   if (dL_dcov3D) {
-    float2* w2 = reinterpret_cast<float2*>(wsm);
+    float2* w2 = wcov;
     w2[lane * 3] = make_float2(dcov[0], dcov[1]);
     w2[lane * 3 + 1] = make_float2(dcov[2], dcov[3]);
     w2[lane * 3 + 2] = make_float2(dcov[4], dcov[5]);
@@ -278,7 +284,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   // ---------------- SH colour backward (backward.cu:20-139) ----------------
   if (do_sh) {
     if (SH16) {
-      warp_load_rows<SH_ROW>(reinterpret_cast<const float4*>(shs) + wfirst * SH_ROW, wsm, vis_mask, lane);
+      cp_async_wait<0>();
       __syncwarp();
       if (vis) {
         const uint8_t cl = clamped[idx];

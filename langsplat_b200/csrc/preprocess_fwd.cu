@@ -75,14 +75,36 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   }
   if (tid < 3) s_cam[tid] = campos[tid];
   if (tid == 0) { s_negmin = 0u; s_max = 0u; }
-  stage_flat<PRE_THREADS>(means3D, s_xyz, (size_t)first * 3, count * 3, tid);
-  if (scales) stage_flat<PRE_THREADS>(scales, s_scl, (size_t)first * 3, count * 3, tid);
-  if (lang) stage_flat<PRE_THREADS>(lang, s_lng, (size_t)first * 3, count * 3, tid);
+  stage_flat_async<PRE_THREADS>(means3D, s_xyz, (size_t)first * 3, count * 3, tid);
+  if (scales) stage_flat_async<PRE_THREADS>(scales, s_scl, (size_t)first * 3, count * 3, tid);
+  if (lang) stage_flat_async<PRE_THREADS>(lang, s_lng, (size_t)first * 3, count * 3, tid);
+  cp_async_commit();
+  cp_async_wait<0>();
   __syncthreads();
   const bool valid = tid < count;
   const int idx = first + tid;
   const float mx = valid ? s_xyz[3 * tid] : 0.f, my = valid ? s_xyz[3 * tid + 1] : 0.f,
               mz = valid ? s_xyz[3 * tid + 2] : 0.f;
+  float4* wsm = s_dyn + (size_t)warp * 32 * (SH_ROW + 1);
+  // Speculative prefetch of the SH rows (cp.async), so that they fly during the projection arithmetic below: a
+  // Gaussian in front of the camera whose centre projects inside the image (plus a 16-pixel band) is almost surely
+  // visible.  Rows guessed wrongly cost a little bandwidth; visible Gaussians the guess missed (large splats centred
+  // off-screen) are fetched synchronously afterwards, so the result never depends on the guess.
+  uint32_t spec_mask = 0u;
+  if (SH16 && colors_precomp == nullptr) {
+    bool guess = false;
+    if (valid) {
+      const float vz = tp_row(s_view, 2, mx, my, mz);
+      const float hw = tp_row(s_proj, 3, mx, my, mz) + 0.0000001f;
+      const float ax = ((tp_row(s_proj, 0, mx, my, mz) / hw + 1.f) * (float)W - 1.f) * 0.5f;
+      const float ay = ((tp_row(s_proj, 1, mx, my, mz) / hw + 1.f) * (float)H - 1.f) * 0.5f;
+      guess = vz > 0.2f && ax > -16.f && ax < (float)W + 16.f && ay > -16.f && ay < (float)H + 16.f;
+    }
+    spec_mask = __ballot_sync(0xffffffffu, guess);
+    warp_load_rows_async<SH_ROW>(reinterpret_cast<const float4*>(shs) + (size_t)(first + warp * 32) * SH_ROW, wsm,
+                                 spec_mask, lane);
+    cp_async_commit();
+  }
 
   int radius_out = 0;
   uint32_t tiles_out = 0;
@@ -129,14 +151,16 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   const bool vis = radius_out > 0;
   const uint32_t vis_mask = __ballot_sync(0xffffffffu, vis);
 
-  // ---- colour: SH rows of the warp's visible Gaussians come in as one coalesced sweep ----
-  float4* wsm = s_dyn + (size_t)warp * 32 * (SH_ROW + 1);
+  // ---- colour: SH rows of the warp's visible Gaussians (prefetched above; the missed ones are fetched now) ----
   float3 col = make_float3(0.f, 0.f, 0.f);
   uint8_t clamp_bits = 0;
   if (colors_precomp == nullptr) {
     if (SH16) {
-      warp_load_rows<SH_ROW>(reinterpret_cast<const float4*>(shs) + (size_t)(first + warp * 32) * SH_ROW, wsm, vis_mask,
-                             lane);
+      const uint32_t missed = vis_mask & ~spec_mask;
+      if (missed)
+        warp_load_rows<SH_ROW>(reinterpret_cast<const float4*>(shs) + (size_t)(first + warp * 32) * SH_ROW, wsm, missed,
+                               lane);
+      cp_async_wait<0>();
       __syncwarp();
     }
     if (vis) {
