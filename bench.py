@@ -40,6 +40,12 @@ import torch.distributed as dist  # noqa: E402
 from langsplat_b200 import synthetic as syn  # noqa: E402
 
 METRIC = "fwd+bwd frames/s @1M Gaussians 1080p RGB+3-ch lang feature"
+# BASELINE.json configs other than the headline (2): parity / side measurements, selected with --config
+METRICS = {2: METRIC,
+           1: "fwd+bwd frames/s @16k Gaussians 256x256 RGB+3-ch lang feature",
+           3: "fwd+bwd frames/s @500k Gaussians 1440x1080 language-feature-only training",
+           4: "fwd+bwd frames/s @3M Gaussians 1080p, 8 camera views per step, view-sharded",
+           5: "fwd-only frames/s @6M Gaussians 3840x2160, three feature levels back to back"}
 
 
 def parse_args():
@@ -191,11 +197,22 @@ def main():
     rank, world, dev = init_dist(args.gpus)
     GR, GS, impl_name = load_impl(args.impl)
     scene, cams = syn.make_config(args.config, P=args.P, W=args.width, H=args.height, n_cameras=8)
-    cam = cams[rank % 8]
+    cfg = args.config
+    feature_only = cfg == 3   # train.py --include_feature: only language_feature (and means2D) carry gradients
+    fwd_only = cfg == 5       # render.py sweep: three feature levels against the same geometry, no backward
+    # config 4 is a strong-scaling case (8 views per step shared by the ranks); every other config renders one view
+    # per GPU per step (weak scaling)
+    my_views = list(range(rank, 8, world)) if cfg == 4 else [rank % 8]
+    views_per_step = 8 if cfg == 4 else world
+    cam = cams[my_views[0]]
     W, H = cam.image_width, cam.image_height
     P = scene["means3D"].shape[0]
-    workload = (f"config{args.config}: {P} Gaussians, {W}x{H}, SH deg 3 + 3-ch language feature, fwd+bwd, "
-                f"one camera view per GPU per step" + (", NCCL allreduce of Gaussian grads" if world > 1 else ""))
+    metric = METRICS.get(cfg, METRIC)
+    what = ("language-feature-only fwd+bwd" if feature_only else "forward only, 3 feature levels" if fwd_only
+            else "fwd+bwd")
+    workload = (f"config{cfg}: {P} Gaussians, {W}x{H}, SH deg 3 + 3-ch language feature, {what}, "
+                + (f"8 camera views per step over {world} GPU(s)" if cfg == 4 else "one camera view per GPU per step")
+                + (", NCCL allreduce of Gaussian grads" if world > 1 and not fwd_only else ""))
 
     if GR is None:  # reference extension not built: time the CPU oracle (a port) on a bounded sample
         if rank == 0:
@@ -212,28 +229,42 @@ def main():
         return
 
     rs = settings(GS, cam, dev)
-    rast = GR(raster_settings=rs)
+    rasts = [GR(raster_settings=settings(GS, cams[v], dev)) for v in my_views]
+    rast = rasts[0]
     names = ["means3D", "shs", "opacities", "scales", "rotations", "language_feature"]
-    params = {k: scene[k].to(dev).requires_grad_(True) for k in names}
-    means2D = torch.zeros((P, 3), device=dev, requires_grad=True)
-    dcol, dfeat = [t.to(dev) for t in syn.make_grads(W, H, 2000 + args.config)]
+    trainable = ["language_feature"] if feature_only else ([] if fwd_only else names)
+    params = {k: scene[k].to(dev).requires_grad_(k in trainable) for k in names}
+    means2D = torch.zeros((P, 3), device=dev, requires_grad=not fwd_only)
+    dcol, dfeat = [t.to(dev) for t in syn.make_grads(W, H, 2000 + cfg, feature_only=feature_only)]
+    levels = [params["language_feature"]]
+    if fwd_only:  # three language_feature_precomp tensors (seeds 1005, 1105, 1205), same geometry
+        levels = [syn.make_gaussians(P, 1005 + 100 * i)["language_feature"].to(dev) for i in range(3)]
 
-    def forward():
-        return rast(means3D=params["means3D"], means2D=means2D, shs=params["shs"],
-                    language_feature_precomp=params["language_feature"], opacities=params["opacities"],
-                    scales=params["scales"], rotations=params["rotations"])
+    def forward(r=None, lang=None):
+        return (r or rast)(means3D=params["means3D"], means2D=means2D, shs=params["shs"],
+                           language_feature_precomp=params["language_feature"] if lang is None else lang,
+                           opacities=params["opacities"], scales=params["scales"], rotations=params["rotations"])
 
     def reduce_grads():
         if world > 1:
             from langsplat_b200.dist import allreduce_gradients
-            allreduce_gradients([p.grad for p in params.values()])
+            allreduce_gradients([p.grad for p in params.values() if p.grad is not None])
 
     def step():
+        if fwd_only:
+            with torch.no_grad():
+                for lang in levels:
+                    forward(lang=lang)
+            return
         for p in params.values():
             p.grad = None
         means2D.grad = None
-        color, feat, radii = forward()
-        torch.autograd.backward([color, feat], [dcol, dfeat])
+        for r in rasts:  # gradients of this rank's views accumulate in .grad
+            color, feat, radii = forward(r)
+            if feature_only:
+                torch.autograd.backward([feat], [dfeat])
+            else:
+                torch.autograd.backward([color, feat], [dcol, dfeat])
         reduce_grads()
 
     # ---- host-buffer (end-to-end) step: camera + ground truth come from pinned host memory, loss goes back ----
@@ -261,12 +292,23 @@ def main():
         gt_f.record_stream(main)
         rs2 = rs._replace(viewmatrix=view_h.to(dev, non_blocking=True), projmatrix=proj_h.to(dev, non_blocking=True),
                           campos=cam_h.to(dev, non_blocking=True))
+        if fwd_only:
+            with torch.no_grad():
+                acc = None
+                for lang in levels:
+                    color, feat, radii = forward(GR(raster_settings=rs2), lang)
+                    acc = feat.mean() if acc is None else acc + feat.mean()
+            main.wait_event(gt_ready)
+            return float((acc + (feat - gt_f).abs().mean()).item())
         color, feat, radii = GR(raster_settings=rs2)(
             means3D=params["means3D"], means2D=means2D, shs=params["shs"],
             language_feature_precomp=params["language_feature"], opacities=params["opacities"],
             scales=params["scales"], rotations=params["rotations"])
         main.wait_event(gt_ready)
-        loss = (color - gt_c).abs().mean() + (feat - gt_f).abs().mean()
+        if feature_only:
+            loss = (feat - gt_f).abs().mean()
+        else:
+            loss = (color - gt_c).abs().mean() + (feat - gt_f).abs().mean()
         loss.backward()
         reduce_grads()
         return float(loss.item())  # device -> host read of the step's result
@@ -336,15 +378,17 @@ def main():
             dist.destroy_process_group()
         return
 
-    fps = world * args.steps / (ms_total / 1000.0)
-    line = {"metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+    frames_per_step = views_per_step * (len(levels) if fwd_only else 1)
+    fps = frames_per_step * args.steps / (ms_total / 1000.0)
+    line = {"metric": metric, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload, "P": P, "width": W, "height": H, "cameras_per_step": world,
+            "scaling": "strong" if cfg == 4 else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload, "P": P, "width": W, "height": H, "cameras_per_step": views_per_step,
                        "l2_policy": "inputs larger than L2 (Gaussian tensors ~250 MB), no explicit flush",
                        "impl": impl_name},
             "fwd_only_ms_per_frame": fwd_ms, "clocks": clocks,
-            "e2e": {"value": world * args.steps / (e2e_ms_total / 1000.0), "unit": "frames/s",
+            "e2e": {"value": (world * (len(levels) if fwd_only else 1)) * args.steps / (e2e_ms_total / 1000.0),
+                    "unit": "frames/s",
                     "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4,
                     "what": "camera + GT colour/feature images from pinned host memory (GT copy on a side stream, "
                             "overlapping the same step's forward), L1 loss, loss.item()"},

@@ -210,21 +210,33 @@ duplicate_kernel(int P, int gx, int gy, const int32_t* __restrict__ radii, const
 // ------------------------------------------------------------------------------------------------------------
 // K5': identifyTileRanges (rasterizer_impl.cu:116-138).  ranges must be zero on entry (cudaMemset, :313).
 // ------------------------------------------------------------------------------------------------------------
+// Four consecutive words per thread (two 128-bit loads), one extra load for the predecessor of the first.
 __global__ void __launch_bounds__(256)
 tile_ranges_kernel(uint32_t L, const uint64_t* __restrict__ keys, int tile_shift, uint2* __restrict__ ranges) {
-  const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= L) return;
-  const uint32_t cur = (uint32_t)(keys[idx] >> tile_shift);
-  if (idx == 0) {
-    ranges[cur].x = 0;
+  const uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4u;
+  if (i0 >= L) return;
+  uint64_t k[4];
+  if (i0 + 4 <= L) {
+    const ulonglong2 a = __ldg(reinterpret_cast<const ulonglong2*>(keys + i0));
+    const ulonglong2 b = __ldg(reinterpret_cast<const ulonglong2*>(keys + i0) + 1);
+    k[0] = a.x; k[1] = a.y; k[2] = b.x; k[3] = b.y;
   } else {
-    const uint32_t prev = (uint32_t)(keys[idx - 1] >> tile_shift);
+#pragma unroll
+    for (int j = 0; j < 4; j++) k[j] = i0 + j < L ? keys[i0 + j] : 0ull;
+  }
+  uint32_t prev = i0 == 0 ? 0xffffffffu : (uint32_t)(__ldg(keys + i0 - 1) >> tile_shift);
+#pragma unroll
+  for (int j = 0; j < 4; j++) {
+    const uint32_t idx = i0 + j;
+    if (idx >= L) break;
+    const uint32_t cur = (uint32_t)(k[j] >> tile_shift);
     if (cur != prev) {
-      ranges[prev].y = idx;
+      if (idx != 0) ranges[prev].y = idx;
       ranges[cur].x = idx;
     }
+    if (idx == L - 1) ranges[cur].y = L;
+    prev = cur;
   }
-  if (idx == L - 1) ranges[cur].y = L;
 }
 
 // packed sorted word -> the reference's key format (tile << 32 | depth bits); exact inverse of the packing above
@@ -259,7 +271,7 @@ void launch_duplicate(int P, int grid_x, int grid_y, const int32_t* radii, GeomV
 
 void launch_tile_ranges(int64_t R, const uint64_t* keys, int tile_shift, uint2* ranges, cudaStream_t s) {
   if (R <= 0) return;
-  tile_ranges_kernel<<<(unsigned)((R + 255) / 256), 256, 0, s>>>((uint32_t)R, keys, tile_shift, ranges);
+  tile_ranges_kernel<<<(unsigned)((R + 1023) / 1024), 256, 0, s>>>((uint32_t)R, keys, tile_shift, ranges);
   count_launch();
 }
 
