@@ -192,8 +192,20 @@ def measured_peaks():
     return 6650.0, 1965.0, "fallback"
 
 
+def emit(line: dict) -> None:
+    """Exactly one JSON line on the real stdout (libraries such as NCCL may print to fd 1; it is parked on stderr)."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
 def main():
+    global _REAL_STDOUT
     args = parse_args()
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)  # anything else written to stdout (NCCL's version banner, warnings) goes to stderr
     rank, world, dev = init_dist(args.gpus)
     GR, GS, impl_name = load_impl(args.impl)
     scene, cams = syn.make_config(args.config, P=args.P, W=args.width, H=args.height, n_cameras=8)
@@ -225,7 +237,7 @@ def main():
                                      "sample": f"{frames} whole frames of the same workload on the CPU oracle"},
                     "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                     "gpu_launches": 0}
-            print(json.dumps(line))
+            emit(line)
         return
 
     rs = settings(GS, cam, dev)
@@ -400,7 +412,7 @@ def main():
                                 "sample": "NOT a CPU run: the reference has no CPU implementation of this path; this "
                                           "is its unmodified CUDA extension (baseline/_ref, sm_100a) on the same GPU, "
                                           "same workload, all steps"}
-        print(json.dumps(line))
+        emit(line)
         if world > 1:
             dist.destroy_process_group()
         return
@@ -455,7 +467,7 @@ def main():
                                     "traffic": None, "peak_source": src}
     elif stages:
         line["stages"] = {k: {"ms": v} for k, v in stages.items()}
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 

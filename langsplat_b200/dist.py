@@ -25,13 +25,45 @@ def allreduce_gradients(grads: Sequence[Optional[torch.Tensor]], group=None, asy
     if not dist.is_available() or not dist.is_initialized() or dist.get_world_size(group) == 1:
         return []
     handles = []
-    for g in grads:
-        if g is None:
-            continue
+    for g in coalesce(grads):
         h = dist.all_reduce(g, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
         if async_op:
             handles.append(h)
     return handles
+
+
+def coalesce(grads: Sequence[Optional[torch.Tensor]]) -> List[torch.Tensor]:
+    """Merges gradient tensors that sit back to back in one allocation into a single flat view, so that they travel
+    as one collective.  The rasterizer's backward returns the parameter gradients (means3D, sh, opacity, scales,
+    rotations, language feature) as adjacent slices of one buffer precisely for this."""
+    live = [g for g in grads if g is not None]
+    out: List[torch.Tensor] = []
+    by_store = {}
+    for g in live:
+        if g.is_contiguous() and g.dtype == torch.float32:
+            by_store.setdefault(g.untyped_storage().data_ptr(), []).append(g)
+        else:
+            out.append(g)
+    for gs in by_store.values():
+        gs.sort(key=lambda t: t.data_ptr())
+        run = [gs[0]]
+        for t in gs[1:]:
+            prev = run[-1]
+            if t.data_ptr() == prev.data_ptr() + prev.numel() * 4:
+                run.append(t)
+            else:
+                out.append(_flat(run))
+                run = [t]
+        out.append(_flat(run))
+    return out
+
+
+def _flat(run: List[torch.Tensor]) -> torch.Tensor:
+    if len(run) == 1:
+        return run[0]
+    first = run[0]
+    n = sum(t.numel() for t in run)
+    return first.new_empty(0).set_(first.untyped_storage(), first.storage_offset(), (n,), (1,))
 
 
 def accumulate_view_gradients(params: Dict[str, torch.Tensor], render_and_loss, views: Iterable[int]) -> None:

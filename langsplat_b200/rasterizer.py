@@ -163,28 +163,43 @@ def _backward_impl(state, grad_color, grad_feature, need_mask: int, want_sh: boo
     include_feature = bool(state["frame"].include_feature)
     gc = grad_color.contiguous() if grad_color is not None else None
     gf = grad_feature.contiguous() if (grad_feature is not None and include_feature) else None
-    # accumulators packed into one buffer so the library zero-fills them with a single memset
-    acc = torch.empty((14 * P,), **f32)
-    d_conic = acc[0:4 * P].view(P, 4)
-    d_means2D = acc[4 * P:7 * P].view(P, 3)
-    d_opac = acc[7 * P:8 * P].view(P, 1)
-    d_colors = acc[8 * P:11 * P].view(P, 3)
-    d_feat = acc[11 * P:14 * P].view(P, 3)
     geom_need = bool(need_mask & L.NEED_GEOMETRY)
     run_pre = geom_need or (sh is not None and want_sh and gc is not None)
+    # One allocation for everything.  The parameter gradients come first and back to back (rotations, sh, means3D,
+    # scales, language feature, opacity — the two the kernels access as float4 lead, so they stay 16-byte aligned
+    # for any P), so a data-parallel caller can all-reduce them as ONE flat message (langsplat_b200.dist.coalesce);
+    # the internal accumulators (conic, means2D, colours, cov3D) follow from the next 16-byte boundary.  The library
+    # zero-fills what the blend kernel accumulates into (adjacent ranges merge into one memset).
+    n_sh = M * 3 if (run_pre and sh is not None) else 0
+    sizes = [("rots", 4 if run_pre else 0), ("sh", n_sh), ("means3D", 3 if run_pre else 0),
+             ("scales", 3 if run_pre else 0), ("feat", 3), ("opac", 1), ("|", 0), ("conic", 4), ("means2D", 3),
+             ("colors", 3), ("cov3D", 6 if run_pre else 0)]
+    flat = torch.empty((sum(n for _, n in sizes) * P + 4,), **f32)
+    part, off = {}, 0
+    for name, n in sizes:
+        if name == "|":
+            off = (off + 3) // 4 * 4
+            continue
+        part[name] = flat[off:off + n * P] if n else None
+        off += n * P
+    d_conic = part["conic"].view(P, 4)
+    d_means2D = part["means2D"].view(P, 3)
+    d_opac = part["opac"].view(P, 1)
+    d_colors = part["colors"].view(P, 3)
+    d_feat = part["feat"].view(P, 3)
     g = L.Grads()
     g.dL_dmeans2D, g.dL_dconic, g.dL_dopacity = d_means2D.data_ptr(), d_conic.data_ptr(), d_opac.data_ptr()
     g.dL_dcolors, g.dL_dlanguage_feature = d_colors.data_ptr(), d_feat.data_ptr()
     d_means3D = d_cov3D = d_sh = d_scales = d_rots = None
     if run_pre:
-        d_means3D = torch.empty((P, 3), **f32)
-        d_cov3D = torch.empty((P, 6), **f32)
+        d_means3D = part["means3D"].view(P, 3)
+        d_cov3D = part["cov3D"].view(P, 6)
         g.dL_dmeans3D, g.dL_dcov3D = d_means3D.data_ptr(), d_cov3D.data_ptr()
         if sh is not None:
-            d_sh = torch.empty((P, M, 3), **f32)
+            d_sh = part["sh"].view(P, M, 3)
             g.dL_dsh = d_sh.data_ptr()
-        d_scales = torch.empty((P, 3), **f32)
-        d_rots = torch.empty((P, 4), **f32)
+        d_scales = part["scales"].view(P, 3)
+        d_rots = part["rots"].view(P, 4)
         g.dL_dscales, g.dL_drotations = d_scales.data_ptr(), d_rots.data_ptr()
     stream = torch.cuda.current_stream(device).cuda_stream
     with torch.cuda.device(device):

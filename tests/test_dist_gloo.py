@@ -88,3 +88,17 @@ def test_view_sharded_step_equals_serial_sum(tmp_path):
         assert (r0["acc"][k] - want[k]).abs().max().item() <= 1e-5 * scale, k
     assert torch.equal(r0["s_cnt"], cnt) and torch.equal(r1["s_cnt"], cnt)
     assert torch.equal(r0["s_max"], r1["s_max"]) and r0["s_max"].max() > 0
+
+
+def test_coalesce_merges_adjacent_gradient_slices():
+    flat = torch.arange(100, dtype=torch.float32)
+    a, b, c = flat[0:12].view(4, 3), flat[12:60].view(4, 4, 3), flat[60:64].view(4, 1)
+    gap = flat[70:76].view(2, 3)
+    other = torch.ones(5)
+    out = D.coalesce([b, None, a, gap, c, other])
+    sizes = sorted(t.numel() for t in out)
+    assert sizes == [5, 6, 64]
+    big = [t for t in out if t.numel() == 64][0]
+    assert big.data_ptr() == flat.data_ptr() and torch.equal(big, flat[:64])
+    big += 1.0  # the merged view aliases the original slices
+    assert a[0, 0].item() == 1.0 and c[3, 0].item() == 64.0
