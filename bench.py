@@ -451,20 +451,33 @@ def main():
         line["scene"] = dict(P=P, V=V, R=Rn, N=N, T=T, K_exam=Kx, K_contrib=Kc, sort_bits=bits)
         dom = max(table, key=lambda k: table[k]["ms"])
         d = table[dom]
+        # DRAM bytes per launch from the committed `ncu --set full` capture of this same workload (profiles/)
+        traffic = {}
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+            if args.config == 2 and args.P is None:
+                names_k = {"sort": "onesweep_kernel"}
+                traffic = {k: tj.get(names_k.get(k, k + "_kernel"), {}).get("dram_bytes_per_launch") for k in table}
+                for k, e in table.items():
+                    if traffic.get(k):
+                        e["ncu_dram_bytes_per_launch"] = traffic[k]
+        except Exception:
+            traffic = {}
         if "fp32_instr" in d:
             line["roofline"] = {"kernel": dom, "bound": "fp32", "achieved": d["Tinstr_s"], "peak": fp32_peak / 1e12,
-                                "unit": "TInstr/s", "frac": d["fp32_frac"], "traffic": None,
+                                "unit": "TInstr/s", "frac": d["fp32_frac"], "traffic": traffic.get(dom),
                                 "peak_source": f"{n_sm} SMs x 128 lanes x {sm_mhz:.0f} MHz ({src} clock)",
                                 "note": "blend kernels are FP32-pipe bound (no dense contraction, SURVEY 8d); "
                                         "roofline_frac in `stages` adds the HBM term"}
         else:
             line["roofline"] = {"kernel": dom, "bound": "hbm", "achieved": d["GBps"], "peak": hbm, "unit": "GB/s",
-                                "frac": d["hbm_frac"], "traffic": None, "peak_source": src}
+                                "frac": d["hbm_frac"], "traffic": traffic.get(dom), "peak_source": src}
         s = table.get("sort")
         if s:
             line["roofline_hbm"] = {"kernel": "sort (onesweep, %d passes)" % passes, "bound": "hbm",
                                     "achieved": s["GBps"], "peak": hbm, "unit": "GB/s", "frac": s["hbm_frac"],
-                                    "traffic": None, "peak_source": src}
+                                    "traffic": traffic.get("sort"), "traffic_note": "per pass (one launch)",
+                                    "peak_source": src}
     elif stages:
         line["stages"] = {k: {"ms": v} for k, v in stages.items()}
     emit(line)
