@@ -47,6 +47,10 @@ _MSG_COV = "Please provide exactly one of either scale/rotation pair or precompu
 # Per (device, stream) transient workspace and the last instance count, used as the next capacity guess.
 _scratch: Dict[Tuple[int, int], torch.Tensor] = {}
 _last_R: Dict[int, int] = {}
+# first guess of the instance-list capacity: max(1.25 x the previous frame's count, 4 per Gaussian, 64 Ki)
+_CAPACITY_PER_GAUSSIAN = 4
+_INITIAL_CAPACITY_FLOOR = 1 << 16
+_capacity_retries = 0  # how often lsr_forward had to be repeated with a larger list (diagnostics / tests)
 
 
 def _present(t: Optional[torch.Tensor]) -> bool:
@@ -130,7 +134,8 @@ def _forward_impl(rs: GaussianRasterizationSettings, means3D, sh, colors, lang, 
     image = torch.empty((lib.lsr_image_bytes(W, H),), dtype=torch.uint8, device=device)
     stream = torch.cuda.current_stream(device).cuda_stream
     dev_idx = device.index if device.index is not None else torch.cuda.current_device()
-    capacity = max(int(_last_R.get(dev_idx, 0) * 1.25), 4 * P, 1 << 16)
+    global _capacity_retries
+    capacity = max(int(_last_R.get(dev_idx, 0) * 1.25), _CAPACITY_PER_GAUSSIAN * P, _INITIAL_CAPACITY_FLOOR)
     nr = ctypes.c_int64(0)
     with torch.cuda.device(device):
         while True:
@@ -142,6 +147,7 @@ def _forward_impl(rs: GaussianRasterizationSettings, means3D, sh, colors, lang, 
                                  _ptr(geom), _ptr(image), _ptr(point_list), capacity, _ptr(scratch), scratch.numel(),
                                  ctypes.byref(nr), ctypes.c_void_p(stream))
             if rc == L.LSR_ERR_CAPACITY:
+                _capacity_retries += 1
                 capacity = int(nr.value * 1.1) + 1024
                 continue
             break
