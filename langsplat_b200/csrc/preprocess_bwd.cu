@@ -5,6 +5,9 @@
 // kernels with dL_dcov3D / dL_dmean3D round-tripping through global memory, after zero-filling ten tensors
 // (RAST/rasterize_points.cu:166-183).  Here one kernel writes every output element exactly once (zeros for
 // Gaussians with radius 0), so the caller can hand in uninitialised memory.  HBM-bound.
+// With `moments` set, the blend kernel (render_bwd.cu) left the pair-weighted moments M0, (Mx, My), (Mxx, Mxy, Myy) of the
+// pixel offsets in dL_dopacity / dL_dmean2D / dL_dconic instead of the reference's sums (backward.cu:552-582); the
+// per-Gaussian coefficients are applied here, and dL_dmean2D is rewritten in place with the actual gradient.
 #include "common.cuh"
 #include "gs_math.cuh"
 #include "stage.cuh"
@@ -147,7 +150,8 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
                       const float* __restrict__ scales, const float* __restrict__ rotations, float scale_modifier,
                       const float* __restrict__ cov3Ds, const float* __restrict__ viewmatrix,
                       const float* __restrict__ projmatrix, float h_x, float h_y, float tan_fovx, float tan_fovy,
-                      const float* __restrict__ campos, const float* __restrict__ dL_dmean2D,
+                      const float* __restrict__ campos, const float* __restrict__ opacities, int moments, float ddelx_dx,
+                      float ddely_dy, float* __restrict__ dL_dmean2D,
                       const float* __restrict__ dL_dconic, const float* __restrict__ dL_dcolor,
                       float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
                       float* __restrict__ dL_dscale, float* __restrict__ dL_drot) {
@@ -210,7 +214,20 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
     Cov2D c2;
     compute_cov2D(mx, my, mz, h_x, h_y, tan_fovx, tan_fovy, cov3D, s_view, c2);
     const float4 dcon = __ldg(reinterpret_cast<const float4*>(dL_dconic) + idx);
-    const float dLc_x = dcon.x, dLc_y = dcon.y, dLc_z = dcon.w;
+    float dLc_x = dcon.x, dLc_y = dcon.y, dLc_z = dcon.w;
+    if (moments) {
+      // dL_dconic = -0.5 * o * (Mxx, Mxy, Myy);  dL_dmean2D = -o * (cx*Mx + cy*My, cz*My + cy*Mx) * (W/2, H/2).
+      // The conic is re-derived from the covariance just computed, exactly as the forward does (forward.cu:219-224).
+      const float det = __fmaf_rn(c2.a, c2.c, -__fmul_rn(c2.b, c2.b));
+      const float det_inv = __fdiv_rn(1.f, det);
+      const float cx = __fmul_rn(c2.c, det_inv), cy = __fmul_rn(-c2.b, det_inv), cz = __fmul_rn(c2.a, det_inv);
+      const float o = __ldg(opacities + idx);
+      const float mo = -0.5f * o;
+      dLc_x *= mo; dLc_y *= mo; dLc_z *= mo;
+      const float Mx = s_m2d[3 * tid], My = s_m2d[3 * tid + 1];
+      s_m2d[3 * tid] = -o * (cx * Mx + cy * My) * ddelx_dx;
+      s_m2d[3 * tid + 1] = -o * (cz * My + cy * Mx) * ddely_dy;
+    }
     const float x_grad_mul = (c2.txtz < -c2.limx || c2.txtz > c2.limx) ? 0.f : 1.f;
     const float y_grad_mul = (c2.tytz < -c2.limy || c2.tytz > c2.limy) ? 0.f : 1.f;
     const Mat3& T = c2.T;
@@ -376,6 +393,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   s_scl[3 * tid] = dscale[0]; s_scl[3 * tid + 1] = dscale[1]; s_scl[3 * tid + 2] = dscale[2];
   __syncthreads();
   if (dL_dmean3D) unstage_flat<BPRE_THREADS>(dL_dmean3D, s_xyz, (size_t)first * 3, count * 3, tid);
+  if (moments) unstage_flat<BPRE_THREADS>(dL_dmean2D, s_m2d, (size_t)first * 3, count * 3, tid);
   if (do_scale) unstage_flat<BPRE_THREADS>(dL_dscale, s_scl, (size_t)first * 3, count * 3, tid);
 }
 
@@ -384,7 +402,8 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
 void launch_preprocess_bwd(const lsr_frame& f, const lsr_inputs& in, float focal_x, float focal_y,
                            const int32_t* radii, GeomView g, uint32_t need_mask, const lsr_grads& gr, cudaStream_t s) {
   if (f.P <= 0) return;
-  (void)need_mask;
+  // the blend kernel leaves moments instead of gradients exactly when it ran in its GEOM mode (render_bwd.cu)
+  const int moments = (need_mask & LSR_NEED_GEOMETRY) ? 1 : 0;
   const float* cov3Ds = in.cov3D_precomp ? in.cov3D_precomp : g.cov3D;
   const bool sh16 = in.shs != nullptr && gr.dL_dsh != nullptr && f.M == 16 && (((uintptr_t)in.shs) & 15) == 0 &&
                     (((uintptr_t)gr.dL_dsh) & 15) == 0;
@@ -397,7 +416,9 @@ void launch_preprocess_bwd(const lsr_frame& f, const lsr_inputs& in, float focal
   const int blocks = (f.P + BPRE_THREADS - 1) / BPRE_THREADS;
 #define LSR_BPRE_ARGS                                                                                              \
   f.P, f.D, f.M, in.means3D, radii, in.shs, g.clamped, in.scales, in.rotations, f.scale_modifier, cov3Ds,          \
-      f.viewmatrix, f.projmatrix, focal_x, focal_y, f.tanfovx, f.tanfovy, f.campos, gr.dL_dmeans2D, gr.dL_dconic,  \
+      f.viewmatrix, f.projmatrix, focal_x, focal_y, f.tanfovx, f.tanfovy, f.campos, in.opacities, moments,       \
+      0.5f * f.width,                                                                                              \
+      0.5f * f.height, gr.dL_dmeans2D, gr.dL_dconic,                                                               \
       gr.dL_dcolors, gr.dL_dmeans3D, gr.dL_dcov3D, gr.dL_dsh, gr.dL_dscales, gr.dL_drotations
   if (sh16) preprocess_bwd_kernel<true><<<blocks, BPRE_THREADS, BPRE_SH_SMEM, s>>>(LSR_BPRE_ARGS);
   else preprocess_bwd_kernel<false><<<blocks, BPRE_THREADS, BPRE_SH_SMEM, s>>>(LSR_BPRE_ARGS);

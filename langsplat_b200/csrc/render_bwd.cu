@@ -8,7 +8,7 @@
 //    contributions are summed across the warp with a value-halving butterfly (13 shuffles for 12 values instead of
 //    60: each round a lane keeps half of its values and sends the other half to its partner), leaving each value's
 //    warp total on one lane, which issues a single RED.ADD.F32.
-//  * Two pixels per thread.  A warp owns an 8x8 pixel block (a 16x16 tile is 4 warps = 128 threads); each thread
+//  * Two pixels per thread.  A warp owns an 8x8 pixel quadrant (and is a CTA of its own: no barriers); each thread
 //    blends rows r and r+4 of its column and adds both pixels' contributions before the butterfly, so the reduction,
 //    the shared-memory broadcasts and the loop overhead are paid once per 64 pixels (measured on the bench scene: 3.6 M
 //    working (warp, instance) pairs instead of 6.2 M with 8x4 footprints).
@@ -18,8 +18,16 @@
 //    One scalar recurrence serves the three colour and the three feature channels (6 FMAs + 3 instead of ~30).
 //  * T is walked back with a reciprocal (MUFU.RCP) instead of the reference's IEEE division; gradients carry a 1e-4
 //    relative tolerance (the reference's own sums are unordered atomics), the forward decisions are untouched.
-//  * The walk starts at the CTA-wide maximum of n_contrib, so the never-blended tail of a tile's list is not fetched;
-//    instances that cannot reach alpha >= 1/255 anywhere in the tile are dropped at staging (render_common.cuh).
+//  * The walk starts at the quadrant's maximum of n_contrib, so the never-blended tail of the tile's list is not
+//    fetched; instances that cannot reach alpha >= 1/255 anywhere in the quadrant are dropped at staging
+//    (render_common.cuh); the next batch's records are fetched while the current one is processed.
+//  * Moments instead of gradients (GEOM).  With s = G * dL_dalpha per pair, the reference's six geometric sums
+//    (backward.cu:552-582) are linear in the moments  M0 = sum s, Mx = sum s*dx, My = sum s*dy, Mxx = sum s*dx*dx,
+//    Mxy = sum s*dx*dy, Myy = sum s*dy*dy  of the pixel offsets about the Gaussian centre, with per-Gaussian
+//    coefficients (opacity, conic).  The kernel accumulates the moments (9 instructions per pixel instead of 21) into
+//    the dL_dopacity / dL_dmean2D / dL_dconic buffers, and the per-Gaussian kernel that follows (preprocess_bwd.cu)
+//    applies the coefficients once per Gaussian:  dL_dopacity = M0,  dL_dmean2D = -o * (cx*Mx + cy*My) * W/2, ...,
+//    dL_dconic = -0.5 * o * (Mxx, Mxy, Myy).
 // Template switches specialise on what the caller needs (ctx.needs_input_grad): FEAT = language feature blended,
 // DCOL = a colour upstream gradient exists, GEOM = conic/opacity gradients wanted.  LangSplat's feature-only training
 // (train.py:96-99 with gaussian_model.py:212-217) runs <FEAT=1, DCOL=0, GEOM=0>: 5 values instead of 12.
@@ -71,15 +79,14 @@ __device__ __forceinline__ int held_index(int lane) {
   }
 }
 
-#ifndef LSR_BWD_SLOTS
-#define LSR_BWD_SLOTS 2
-#endif
-constexpr int BWD_SLOTS = LSR_BWD_SLOTS;             // pixels per thread (rows r, r+4, ...)
-constexpr int BWD_THREADS = TILE_PIX / BWD_SLOTS;     // 2 slots: 4 warps x (8x8 pixels)
+constexpr int BWD_SLOTS = BLEND_SLOTS;  // pixels per thread (rows r, r+4)
 
+#ifndef LSR_BWD_MINB
+#define LSR_BWD_MINB 25  // caps ptxas at 80 registers: 25 instead of 23 warps per SM (measured: 958 -> 905 us)
+#endif
 template <bool FEAT, bool DCOL, bool GEOM>
-__global__ void __launch_bounds__(BWD_THREADS)
-render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t* __restrict__ list,
+__global__ void __launch_bounds__(32, LSR_BWD_MINB)
+render_bwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, const uint32_t* __restrict__ list,
                   const GeomRec* __restrict__ rec, const float* __restrict__ bg, const float* __restrict__ final_Ts,
                   const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
                   const float* __restrict__ dL_dpixels_F, float* __restrict__ dL_dmean2D,
@@ -92,17 +99,17 @@ render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
   constexpr int I_FEAT = I_COL + (DCOL ? 3 : 0);
   constexpr int NV = I_FEAT + (FEAT ? 3 : 0);
 
-  __shared__ BatchSmemT<BWD_THREADS> sm;
-  __shared__ uint32_t s_max[BWD_THREADS / 32];
+  __shared__ WarpBatch sm;
 
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int tx = (warp & 1) * 8 + (lane & 7), ty = (warp >> 1) * (4 * BWD_SLOTS) + (lane >> 3);  // slot s adds 4*s rows
-  const int tiles_x = (W + TILE_X - 1) / TILE_X;
-  const uint32_t px = blockIdx.x * TILE_X + tx;
+  const int lane = threadIdx.x;
+  const uint32_t tile = blockIdx.x / QUADS, quad = blockIdx.x % QUADS;
+  const uint32_t qx0 = (tile % tiles_x) * TILE_X + (quad % QUADS_X) * QUAD_X;
+  const uint32_t qy0 = (tile / tiles_x) * TILE_Y + (quad / QUADS_X) * QUAD_Y;
+  const uint32_t px = qx0 + (lane & 7), py0 = qy0 + (lane >> 3);  // slot s adds 4*s rows
   const float pxf = (float)px;
-  const float X0 = (float)(blockIdx.x * TILE_X), Y0 = (float)(blockIdx.y * TILE_Y);
+  const float X0 = (float)qx0, Y0 = (float)qy0;
   const size_t N = (size_t)W * H;
-  const uint2 range = ranges[blockIdx.y * tiles_x + blockIdx.x];
+  const uint2 range = ranges[tile];
 
   float pyf[BWD_SLOTS], T[BWD_SLOTS], bgT[BWD_SLOTS];
   uint32_t lastc[BWD_SLOTS];
@@ -111,7 +118,7 @@ render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
   uint32_t wmax = 0;
 #pragma unroll
   for (int s = 0; s < BWD_SLOTS; s++) {
-    const uint32_t py = blockIdx.y * TILE_Y + ty + 4 * s;
+    const uint32_t py = py0 + 4 * s;
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
     const size_t pix = (size_t)py * W + px;
     pyf[s] = (float)py;
@@ -128,15 +135,10 @@ render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
     if (DCOL) bgT[s] = -T_final * (__ldg(bg) * dpix[s][0] + __ldg(bg + 1) * dpix[s][1] + __ldg(bg + 2) * dpix[s][2]);
     accA[s] = 0.f; cd_last[s] = 0.f; alpha_last[s] = 0.f;
   }
-  // The CTA-wide maximum of n_contrib bounds the part of the list anyone needs.
+  // The quadrant's maximum of n_contrib bounds the part of the list anyone here needs.
 #pragma unroll
   for (int d = 16; d > 0; d >>= 1) wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, d));
-  if (lane == 0) s_max[warp] = wmax;
-  __syncthreads();
-  uint32_t bmax = 0;
-#pragma unroll
-  for (int i = 0; i < BWD_THREADS / 32; i++) bmax = max(bmax, s_max[i]);
-  const int eff_len = (int)bmax;  // forward indices [0, eff_len) are the only ones examined
+  const int eff_len = (int)wmax;  // forward indices [0, eff_len) are the only ones examined
 
   const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
 
@@ -152,14 +154,18 @@ render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
     else if (FEAT && held >= I_FEAT) { out_base = dL_dfeat + (held - I_FEAT); out_stride = 3; }
   }
 
-  const int rounds = (eff_len + BWD_THREADS - 1) / BWD_THREADS;
-  for (int b = 0; b < rounds; b++) {
-    // back to front: this batch covers forward indices eff_len-1-b*128 downwards (backward.cu:486-498)
-    const int fwd_fetch = eff_len - 1 - (b * BWD_THREADS + tid);
-    const int nb = stage_batch<BWD_THREADS>(sm, list, rec, range.x, fwd_fetch >= 0 ? fwd_fetch : -1, X0, Y0);
+  // back to front: the batch starting at `top` covers forward indices top-lane, top = eff_len-1 downwards
+  // (backward.cu:486-498)
+  const uint32_t smA = smem_u32(&sm.A[0]);
+  Fetched nxt = fetch_instance(list, rec, range.x, eff_len - 1 - lane);
+  for (int top = eff_len - 1; top >= 0; top -= 32) {
+    __syncwarp();  // everyone has left the previous batch
+    const int nb = commit_batch(sm, nxt, X0, Y0);
+    nxt = fetch_instance(list, rec, range.x, top - 32 - lane);
     for (int j = 0; j < nb; j++) {
-      const float4 a = sm.A[j];
-      const float4 bb = sm.B[j];  // cz, thr_m, opacity, position
+      const uint32_t ad = smA + (uint32_t)j * (uint32_t)sizeof(float4);
+      const float4 a = lds128(ad);
+      const float4 bb = lds128(ad + SM_B);  // cz, thr_m, opacity, position
       const uint32_t fwd = __float_as_uint(bb.w);
       const float dx = __fadd_rn(a.x, -pxf);
       const float qx = __fmul_rn(a.z, dx), hx = __fmul_rn(a.w, dx);
@@ -197,8 +203,8 @@ render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
       float v[12];
 #pragma unroll
       for (int k = 0; k < 12; k++) v[k] = 0.f;
-      const float4 c = sm.C[j];  // r, g, b, f0
-      const float4 d = sm.D[j];  // f1, f2, id
+      const float4 c = lds128(ad + SM_C);  // r, g, b, f0
+      const float4 d = lds128(ad + SM_D);  // f1, f2, id
 #pragma unroll
       for (int s = 0; s < BWD_SLOTS; s++) {
         if (cmask[s] == 0u) continue;  // warp-uniform
@@ -222,17 +228,23 @@ render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
           alpha_last[s] = alpha[s];
           float dL_dalpha = (cd - accA[s]) * T[s];
           if (DCOL) dL_dalpha += bgT[s] * rcp;  // background term (backward.cu:545-550)
-          const float dL_dG = bb.z * dL_dalpha;
-          const float gdx = G[s] * dx, gdy = G[s] * dy[s];
-          const float dG_ddelx = -gdx * a.z - gdy * a.w;
-          const float dG_ddely = -gdy * bb.x - gdx * a.w;
-          v[I_MEAN + 0] += dL_dG * dG_ddelx * ddelx_dx;
-          v[I_MEAN + 1] += dL_dG * dG_ddely * ddely_dy;
           if (GEOM) {
-            v[I_CONIC + 0] += -0.5f * gdx * dx * dL_dG;
-            v[I_CONIC + 1] += -0.5f * gdx * dy[s] * dL_dG;
-            v[I_CONIC + 2] += -0.5f * gdy * dy[s] * dL_dG;
-            v[I_OPAC] += G[s] * dL_dalpha;
+            // moments of the pixel offset about the Gaussian centre, weighted by s = G * dL_dalpha
+            const float sw = G[s] * dL_dalpha;
+            const float sx = sw * dx, sy = sw * dy[s];
+            v[I_OPAC] += sw;
+            v[I_MEAN + 0] += sx;
+            v[I_MEAN + 1] += sy;
+            v[I_CONIC + 0] += sx * dx;
+            v[I_CONIC + 1] += sx * dy[s];
+            v[I_CONIC + 2] += sy * dy[s];
+          } else {
+            const float dL_dG = bb.z * dL_dalpha;
+            const float gdx = G[s] * dx, gdy = G[s] * dy[s];
+            const float dG_ddelx = -gdx * a.z - gdy * a.w;
+            const float dG_ddely = -gdy * bb.x - gdx * a.w;
+            v[I_MEAN + 0] += dL_dG * dG_ddelx * ddelx_dx;
+            v[I_MEAN + 1] += dL_dG * dG_ddely * ddely_dy;
           }
         }
       }
@@ -266,13 +278,13 @@ render_bwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
 }
 
 template <bool FEAT, bool DCOL, bool GEOM>
-void launch_one(dim3 grid, cudaStream_t s, int W, int H, const uint2* ranges, const uint32_t* list, const GeomRec* rec,
-                const float* bg, const float* final_T, const uint32_t* n_contrib, const float* dL_dcolor,
-                const float* dL_dfeature, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolors,
-                float* dL_dfeat) {
-  render_bwd_kernel<FEAT, DCOL, GEOM><<<grid, BWD_THREADS, 0, s>>>(W, H, ranges, list, rec, bg, final_T, n_contrib,
-                                                                 dL_dcolor, dL_dfeature, dL_dmean2D, dL_dconic,
-                                                                 dL_dopacity, dL_dcolors, dL_dfeat);
+void launch_one(unsigned grid, cudaStream_t s, int W, int H, int tiles_x, const uint2* ranges, const uint32_t* list,
+                const GeomRec* rec, const float* bg, const float* final_T, const uint32_t* n_contrib,
+                const float* dL_dcolor, const float* dL_dfeature, float* dL_dmean2D, float* dL_dconic,
+                float* dL_dopacity, float* dL_dcolors, float* dL_dfeat) {
+  render_bwd_kernel<FEAT, DCOL, GEOM><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, list, rec, bg, final_T, n_contrib,
+                                                        dL_dcolor, dL_dfeature, dL_dmean2D, dL_dconic, dL_dopacity,
+                                                        dL_dcolors, dL_dfeat);
 }
 
 }  // namespace
@@ -281,15 +293,16 @@ void launch_render_bwd(int W, int H, const uint2* ranges, const uint32_t* list, 
                        bool include_feature, const float* final_T, const uint32_t* n_contrib, const float* dL_dcolor,
                        const float* dL_dfeature, uint32_t need_mask, float* dL_dmean2D, float* dL_dconic,
                        float* dL_dopacity, float* dL_dcolors, float* dL_dfeat, cudaStream_t s) {
-  dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y);
-  if (grid.x == 0 || grid.y == 0) return;
+  const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
+  if (tiles_x == 0 || tiles_y == 0) return;
+  const unsigned grid = (unsigned)tiles_x * (unsigned)tiles_y * QUADS;
   const bool feat = include_feature && dL_dfeature != nullptr;
   const bool dcol = dL_dcolor != nullptr;
   const bool geom = (need_mask & LSR_NEED_GEOMETRY) != 0;
   if (!feat && !dcol) return;  // no upstream gradient at all: everything stays zero
-#define LSR_BWD(F, D, G)                                                                                           \
-  launch_one<F, D, G>(grid, s, W, H, ranges, list, rec, bg, final_T, n_contrib, dL_dcolor, dL_dfeature, dL_dmean2D, \
-                      dL_dconic, dL_dopacity, dL_dcolors, dL_dfeat)
+#define LSR_BWD(F, D, G)                                                                                      \
+  launch_one<F, D, G>(grid, s, W, H, tiles_x, ranges, list, rec, bg, final_T, n_contrib, dL_dcolor, dL_dfeature, \
+                      dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolors, dL_dfeat)
   if (feat) {
     if (dcol) { if (geom) LSR_BWD(true, true, true); else LSR_BWD(true, true, false); }
     else      { if (geom) LSR_BWD(true, false, true); else LSR_BWD(true, false, false); }

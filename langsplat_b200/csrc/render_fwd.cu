@@ -1,10 +1,12 @@
 // render_fwd.cu — K6': 16x16-tile front-to-back alpha blend of RGB + the 3-channel language feature.
 // Replaces FORWARD::render / renderCUDA (RAST/cuda_rasterizer/forward.cu:262-426).
 //
-// One CTA per tile, one thread per pixel.  Per 256-instance batch the CTA gathers one 48-byte GeomRec per instance
-// (position, conic, opacity, colour AND feature — the reference re-reads colour/feature from global memory for every
-// contributing pair, forward.cu:359-366), drops instances that provably cannot contribute anywhere in the tile and
-// compacts the rest into shared memory (render_common.cuh); then every pixel walks the survivors.
+// One single-warp CTA per 8x8-pixel quadrant of a tile, two pixels per thread (rows r and r+4), so the shared-memory
+// broadcasts, the x half of the quadratic form and the loop overhead are paid once per 64 pixels, and no CTA barrier
+// exists.  Per 32-instance batch the warp gathers one 48-byte GeomRec per instance (position, conic, opacity, colour
+// AND feature — the reference re-reads colour/feature from global memory for every contributing pair,
+// forward.cu:359-366); instances that provably cannot contribute anywhere in the quadrant are dropped at staging
+// (render_common.cuh).  The next batch's records are fetched into registers before the current one is blended.
 // The per-pair arithmetic is written with explicit round-to-nearest intrinsics in the exact order of the reference's
 // SASS so that the skip / stop decisions, hence n_contrib, are bit-identical:
 //   power = fma(fma(dx, cx*dx, (cz*dy)*dy), -0.5, -((cy*dx)*dy));  alpha = min(0.99, o*expf(power)).
@@ -16,74 +18,110 @@ namespace lsr {
 
 namespace {
 
+constexpr int FWD_SLOTS = BLEND_SLOTS;
+
 template <bool FEAT>
-__global__ void __launch_bounds__(TILE_PIX)
-render_fwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t* __restrict__ list,
+__global__ void __launch_bounds__(32)
+render_fwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, const uint32_t* __restrict__ list,
                   const GeomRec* __restrict__ rec, const float* __restrict__ bg, float* __restrict__ final_T,
                   uint32_t* __restrict__ n_contrib, float* __restrict__ out_color, float* __restrict__ out_feature) {
-  __shared__ BatchSmem sm;
+  __shared__ WarpBatch sm;
 
-  const int tid = threadIdx.x;
-  // warp w owns an 8x4-pixel footprint (compact, instead of the reference's 16x2 strips)
-  const int tx = ((tid >> 5) & 1) * 8 + (tid & 7), ty = (tid >> 6) * 4 + ((tid & 31) >> 3);
-  const int tiles_x = (W + TILE_X - 1) / TILE_X;
-  const uint32_t px = blockIdx.x * TILE_X + tx, py = blockIdx.y * TILE_Y + ty;
-  const bool inside = px < (uint32_t)W && py < (uint32_t)H;
-  const float pxf = (float)px, pyf = (float)py;
-  const float X0 = (float)(blockIdx.x * TILE_X), Y0 = (float)(blockIdx.y * TILE_Y);
-  const uint2 range = ranges[blockIdx.y * tiles_x + blockIdx.x];
+  const int lane = threadIdx.x;
+  const uint32_t tile = blockIdx.x / QUADS, quad = blockIdx.x % QUADS;
+  const uint32_t qx0 = (tile % tiles_x) * TILE_X + (quad % QUADS_X) * QUAD_X;
+  const uint32_t qy0 = (tile / tiles_x) * TILE_Y + (quad / QUADS_X) * QUAD_Y;
+  const uint32_t px = qx0 + (lane & 7), py0 = qy0 + (lane >> 3);  // slot s adds 4*s rows
+  const float pxf = (float)px;
+  const float X0 = (float)qx0, Y0 = (float)qy0;
+  const uint2 range = ranges[tile];
   const int len = (int)(range.y - range.x);
-  const int rounds = (len + TILE_PIX - 1) / TILE_PIX;
 
-  bool done = !inside;
-  float T = 1.0f;
-  uint32_t last_contributor = 0;
-  float C0 = 0.f, C1 = 0.f, C2 = 0.f, F0 = 0.f, F1 = 0.f, F2 = 0.f;
+  // lim[s] is the bound of the reference's `power > 0` skip (forward.cu:343); once pixel s has finished it drops to
+  // -inf, which retires the pixel inside the same compare (a NaN power still gets through and is caught below).
+  float pyf[FWD_SLOTS], T[FWD_SLOTS], lim[FWD_SLOTS], C[FWD_SLOTS][3], F[FWD_SLOTS][3];
+  bool inside[FWD_SLOTS];
+  uint32_t last_contributor[FWD_SLOTS];
+  const float kDone = __int_as_float(0xff800000);
+#pragma unroll
+  for (int s = 0; s < FWD_SLOTS; s++) {
+    const uint32_t py = py0 + 4 * s;
+    pyf[s] = (float)py;
+    inside[s] = px < (uint32_t)W && py < (uint32_t)H;
+    lim[s] = inside[s] ? 0.0f : kDone;
+    T[s] = 1.0f;
+    last_contributor[s] = 0;
+#pragma unroll
+    for (int ch = 0; ch < 3; ch++) { C[s][ch] = 0.f; F[s][ch] = 0.f; }
+  }
 
-  for (int i = 0; i < rounds; i++) {
-    if (__syncthreads_count(done) == TILE_PIX) break;
-    const int li = i * TILE_PIX + tid;
-    const int nb = stage_batch<TILE_PIX>(sm, list, rec, range.x, li < len ? li : -1, X0, Y0);
-    for (int j = 0; !done && j < nb; j++) {
-      const float4 a = sm.A[j];
-      const float4 b = sm.B[j];
-      const float dx = __fadd_rn(a.x, -pxf), dy = __fadd_rn(a.y, -pyf);
-      const float q = __fmaf_rn(dx, __fmul_rn(a.z, dx), __fmul_rn(__fmul_rn(b.x, dy), dy));
-      const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(__fmul_rn(a.w, dx), dy));
-      if (power > 0.0f || power < b.y) continue;  // b.y = thr_m: below it alpha < 1/255 for certain
-      const float alpha = fminf(0.99f, __fmul_rn(b.z, expf(power)));
-      if (alpha < kAlphaMin) continue;
-      const float test_T = __fmul_rn(T, __fadd_rn(1.0f, -alpha));
-      if (test_T < 0.0001f) {
-        done = true;
-        continue;
+  const uint32_t smA = smem_u32(&sm.A[0]);
+  Fetched nxt = fetch_instance(list, rec, range.x, lane < len ? lane : -1);
+  for (int base = 0; base < len; base += 32) {
+    // stop when no pixel of the quadrant is still blending; also ends everyone's reads of the previous batch
+    if (__all_sync(0xffffffffu, lim[0] < 0.0f && lim[1] < 0.0f)) break;
+    const int nb = commit_batch(sm, nxt, X0, Y0);
+    {
+      const int li = base + 32 + lane;
+      nxt = fetch_instance(list, rec, range.x, li < len ? li : -1);
+    }
+    for (int j = 0; j < nb; j++) {
+      const uint32_t ad = smA + (uint32_t)j * (uint32_t)sizeof(float4);
+      const float4 a = lds128(ad);
+      const float4 b = lds128(ad + SM_B);
+      const float dx = __fadd_rn(a.x, -pxf);
+      const float qx = __fmul_rn(a.z, dx), hx = __fmul_rn(a.w, dx);
+      float power[FWD_SLOTS];
+      bool ok[FWD_SLOTS];
+#pragma unroll
+      for (int s = 0; s < FWD_SLOTS; s++) {
+        const float dy = __fadd_rn(a.y, -pyf[s]);
+        const float q = __fmaf_rn(dx, qx, __fmul_rn(__fmul_rn(b.x, dy), dy));
+        power[s] = __fmaf_rn(q, -0.5f, -__fmul_rn(hx, dy));
+        // b.y = thr_m: below it alpha < 1/255 for certain (a NaN power blends, as in the reference)
+        ok[s] = !(power[s] > lim[s]) && !(power[s] < b.y);
       }
-      const float4 c = sm.C[j];
-      C0 = __fmaf_rn(T, __fmul_rn(c.x, alpha), C0);
-      C1 = __fmaf_rn(T, __fmul_rn(c.y, alpha), C1);
-      C2 = __fmaf_rn(T, __fmul_rn(c.z, alpha), C2);
-      if (FEAT) {
-        const float4 d = sm.D[j];
-        F0 = __fmaf_rn(T, __fmul_rn(c.w, alpha), F0);
-        F1 = __fmaf_rn(T, __fmul_rn(d.x, alpha), F1);
-        F2 = __fmaf_rn(T, __fmul_rn(d.y, alpha), F2);
+      if (!(ok[0] || ok[1])) continue;
+      const float4 c = lds128(ad + SM_C);
+      float4 d = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (FEAT) d = lds128(ad + SM_D);
+#pragma unroll
+      for (int s = 0; s < FWD_SLOTS; s++) {
+        if (!ok[s] || lim[s] < 0.0f) continue;
+        const float alpha = fminf(0.99f, __fmul_rn(b.z, expf(power[s])));
+        if (alpha < kAlphaMin) continue;
+        const float test_T = __fmul_rn(T[s], __fadd_rn(1.0f, -alpha));
+        if (test_T < 0.0001f) {
+          lim[s] = kDone;  // done (forward.cu:353-357)
+          continue;
+        }
+        C[s][0] = __fmaf_rn(T[s], __fmul_rn(c.x, alpha), C[s][0]);
+        C[s][1] = __fmaf_rn(T[s], __fmul_rn(c.y, alpha), C[s][1]);
+        C[s][2] = __fmaf_rn(T[s], __fmul_rn(c.z, alpha), C[s][2]);
+        if (FEAT) {
+          F[s][0] = __fmaf_rn(T[s], __fmul_rn(c.w, alpha), F[s][0]);
+          F[s][1] = __fmaf_rn(T[s], __fmul_rn(d.x, alpha), F[s][1]);
+          F[s][2] = __fmaf_rn(T[s], __fmul_rn(d.y, alpha), F[s][2]);
+        }
+        T[s] = test_T;
+        last_contributor[s] = __float_as_uint(b.w) + 1u;  // 1-based position in the tile's list (forward.cu:372)
       }
-      T = test_T;
-      last_contributor = __float_as_uint(b.w) + 1u;  // 1-based position in the tile's list (forward.cu:372)
     }
   }
-  if (inside) {
-    const size_t N = (size_t)W * H;
-    const size_t pix = (size_t)py * W + px;
-    final_T[pix] = T;
-    n_contrib[pix] = last_contributor;
-    out_color[pix] = __fmaf_rn(T, __ldg(bg), C0);
-    out_color[N + pix] = __fmaf_rn(T, __ldg(bg + 1), C1);
-    out_color[2 * N + pix] = __fmaf_rn(T, __ldg(bg + 2), C2);
+  const size_t N = (size_t)W * H;
+#pragma unroll
+  for (int s = 0; s < FWD_SLOTS; s++) {
+    if (!inside[s]) continue;
+    const size_t pix = (size_t)(py0 + 4 * s) * W + px;
+    final_T[pix] = T[s];
+    n_contrib[pix] = last_contributor[s];
+    out_color[pix] = __fmaf_rn(T[s], __ldg(bg), C[s][0]);
+    out_color[N + pix] = __fmaf_rn(T[s], __ldg(bg + 1), C[s][1]);
+    out_color[2 * N + pix] = __fmaf_rn(T[s], __ldg(bg + 2), C[s][2]);
     if (FEAT) {
-      out_feature[pix] = F0;  // no background term for the feature image (forward.cu:388)
-      out_feature[N + pix] = F1;
-      out_feature[2 * N + pix] = F2;
+      out_feature[pix] = F[s][0];  // no background term for the feature image (forward.cu:388)
+      out_feature[N + pix] = F[s][1];
+      out_feature[2 * N + pix] = F[s][2];
     }
   }
 }
@@ -93,14 +131,15 @@ render_fwd_kernel(int W, int H, const uint2* __restrict__ ranges, const uint32_t
 void launch_render_fwd(int W, int H, const uint2* ranges, const uint32_t* list, const GeomRec* rec, const float* bg,
                        bool include_feature, float* final_T, uint32_t* n_contrib, float* out_color,
                        float* out_feature, cudaStream_t s) {
-  dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y);
-  if (grid.x == 0 || grid.y == 0) return;
+  const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
+  if (tiles_x == 0 || tiles_y == 0) return;
+  const unsigned grid = (unsigned)tiles_x * (unsigned)tiles_y * QUADS;
   if (include_feature)
-    render_fwd_kernel<true><<<grid, TILE_PIX, 0, s>>>(W, H, ranges, list, rec, bg, final_T, n_contrib, out_color,
-                                                      out_feature);
+    render_fwd_kernel<true><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, list, rec, bg, final_T, n_contrib, out_color,
+                                                out_feature);
   else
-    render_fwd_kernel<false><<<grid, TILE_PIX, 0, s>>>(W, H, ranges, list, rec, bg, final_T, n_contrib, out_color,
-                                                       out_feature);
+    render_fwd_kernel<false><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, list, rec, bg, final_T, n_contrib, out_color,
+                                                 out_feature);
   count_launch();
 }
 
