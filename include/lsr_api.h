@@ -139,6 +139,16 @@ int lsr_backward(const lsr_frame* frame, const lsr_inputs* in, const int32_t* ra
 int lsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, void* stream);
 
+/* Fused (masked) L1 loss on the rendered images — the consumer right after the rasterizer in the training step
+ * (SURVEY.md 8(f) row 1).  Replaces l1_loss(pred * mask, gt * mask) = torch.abs(pred*mask - gt*mask).mean()
+ * (utils/loss_utils.py:17-18 as called from train.py:96-99).  pred, gt: [C,N] (N = H*W); mask: [N] broadcast over
+ * the channels, or null (= ones, the RGB call of train.py:102).  *loss (DEVICE scalar) receives the mean. */
+int lsr_l1_loss_forward(const float* pred, const float* gt, const float* mask, int32_t C, int64_t N, float* loss,
+                        void* stream);
+/* dL_dpred[C,N] = (*grad_out) * sign(pred*mask - gt*mask) * mask / (C*N); grad_out is a DEVICE scalar. */
+int lsr_l1_loss_backward(const float* pred, const float* gt, const float* mask, int32_t C, int64_t N,
+                         const float* grad_out, float* dL_dpred, void* stream);
+
 /* Stable ascending radix sort of (uint64 key, uint32 value) pairs on bits [0, end_bit) — the sort the forward uses
  * in place of cub::DeviceRadixSort::SortPairs (rasterizer_impl.cu:306-311); exported for unit tests.
  * keys_tmp / vals_tmp are n-sized ping-pong buffers; result lands in keys_out / vals_out.

@@ -144,6 +144,22 @@ int lsr_profile_read(float* ms, int n) {
   return ST_COUNT;
 }
 
+int lsr_l1_loss_forward(const float* pred, const float* gt, const float* mask, int32_t C, int64_t N, float* loss,
+                        void* stream) {
+  if (C < 0 || N < 0) return fail(LSR_ERR_INVALID, "C < 0 or N < 0");
+  if (!loss || ((int64_t)C * N > 0 && (!pred || !gt))) return fail(LSR_ERR_INVALID, "null pointer");
+  LSR_CUDA(launch_l1_forward(pred, gt, mask, C, N, loss, (cudaStream_t)stream));
+  return LSR_OK;
+}
+
+int lsr_l1_loss_backward(const float* pred, const float* gt, const float* mask, int32_t C, int64_t N,
+                         const float* grad_out, float* dL_dpred, void* stream) {
+  if (C < 0 || N < 0) return fail(LSR_ERR_INVALID, "C < 0 or N < 0");
+  if ((int64_t)C * N > 0 && (!pred || !gt || !grad_out || !dL_dpred)) return fail(LSR_ERR_INVALID, "null pointer");
+  LSR_CUDA(launch_l1_backward(pred, gt, mask, C, N, grad_out, dL_dpred, (cudaStream_t)stream));
+  return LSR_OK;
+}
+
 int lsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, void* stream) {
   (void)projmatrix;  // the reference's in_frustum computes p_proj but only tests p_view.z (auxiliary.h:139-164)

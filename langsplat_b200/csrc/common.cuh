@@ -173,6 +173,12 @@ void launch_preprocess_bwd(const lsr_frame& f, const lsr_inputs& in, float focal
                            const int32_t* radii, GeomView g, uint32_t need_mask, const lsr_grads& gr, cudaStream_t s);
 void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, uint8_t* present, cudaStream_t s);
 
+// loss.cu: fused (masked) L1 loss forward / backward on [C,N] images
+cudaError_t launch_l1_forward(const float* pred, const float* gt, const float* mask, int C, int64_t N, float* loss,
+                              cudaStream_t s);
+cudaError_t launch_l1_backward(const float* pred, const float* gt, const float* mask, int C, int64_t N,
+                               const float* grad_out, float* dL_dpred, cudaStream_t s);
+
 void count_launch(int n = 1);
 
 }  // namespace lsr

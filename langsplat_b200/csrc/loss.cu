@@ -1,0 +1,135 @@
+// loss.cu — fused (masked) L1 loss on the rendered images: the step right after the rasterizer in LangSplat's
+// training loop.  Replaces, for pred/gt [C,N] and an optional mask [N] broadcast over C,
+//     l1_loss(pred * mask, gt * mask) = torch.abs(pred * mask - gt * mask).mean()
+// (utils/loss_utils.py:17-18 as called from train.py:96-99), which PyTorch runs as five elementwise / reduction
+// kernels forward and four backward, each streaming a [C,H,W] temporary through HBM.  Here the forward is one pass
+// (reads pred, gt, mask; one pre-scaled atomicAdd per CTA) and the backward one pass (reads pred, gt, mask and the
+// upstream scalar; writes dL_dpred = g * sign(pred*m - gt*m) * m / (C*N)).  HBM-bound: 8 B/element forward,
+// 12 B/element backward (+ 4/C B for the mask).
+// Arithmetic follows PyTorch's: the two products are rounded separately before the subtraction.
+#include "common.cuh"
+
+namespace lsr {
+
+namespace {
+
+constexpr int LOSS_THREADS = 256;
+constexpr int LOSS_VEC_PER_THREAD = 4;  // float4 per thread
+
+__device__ __forceinline__ float diff_masked(float p, float g, float m) {
+  return __fsub_rn(__fmul_rn(p, m), __fmul_rn(g, m));
+}
+
+template <bool MASK>
+__global__ void __launch_bounds__(LOSS_THREADS)
+l1_forward_kernel(const float* __restrict__ pred, const float* __restrict__ gt, const float* __restrict__ mask,
+                  int64_t N, int64_t total, float inv_count, float* __restrict__ loss) {
+  __shared__ float s_part[LOSS_THREADS / 32];
+  const int64_t nvec = total / 4;
+  float acc = 0.f;
+  const bool vec_ok = (N % 4) == 0;  // a float4 never straddles two channels, so the mask index is (i % N)
+  if (vec_ok) {
+    const float4* p4 = reinterpret_cast<const float4*>(pred);
+    const float4* g4 = reinterpret_cast<const float4*>(gt);
+    const int64_t nv_per_ch = N / 4;
+    for (int64_t v = (int64_t)blockIdx.x * LOSS_THREADS * LOSS_VEC_PER_THREAD + threadIdx.x, it = 0;
+         it < LOSS_VEC_PER_THREAD; it++, v += LOSS_THREADS) {
+      if (v >= nvec) break;
+      const float4 p = __ldg(p4 + v), g = __ldg(g4 + v);
+      float4 m = make_float4(1.f, 1.f, 1.f, 1.f);
+      if (MASK) m = __ldg(reinterpret_cast<const float4*>(mask) + (v % nv_per_ch));
+      acc += fabsf(diff_masked(p.x, g.x, m.x)) + fabsf(diff_masked(p.y, g.y, m.y)) +
+             fabsf(diff_masked(p.z, g.z, m.z)) + fabsf(diff_masked(p.w, g.w, m.w));
+    }
+  } else {
+    for (int64_t i = (int64_t)blockIdx.x * LOSS_THREADS * LOSS_VEC_PER_THREAD * 4 + threadIdx.x, it = 0;
+         it < LOSS_VEC_PER_THREAD * 4; it++, i += LOSS_THREADS) {
+      if (i >= total) break;
+      const float m = MASK ? __ldg(mask + (i % N)) : 1.f;
+      acc += fabsf(diff_masked(__ldg(pred + i), __ldg(gt + i), m));
+    }
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+  if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < LOSS_THREADS / 32; w++) t += s_part[w];
+    atomicAdd(loss, t * inv_count);
+  }
+}
+
+template <bool MASK>
+__global__ void __launch_bounds__(LOSS_THREADS)
+l1_backward_kernel(const float* __restrict__ pred, const float* __restrict__ gt, const float* __restrict__ mask,
+                   int64_t N, int64_t total, float inv_count, const float* __restrict__ grad_out,
+                   float* __restrict__ dL_dpred) {
+  const float gscale = __ldg(grad_out) * inv_count;
+  // d|x|/dx = sign(x) with sign(0) = 0, as torch.abs' backward
+  auto grad1 = [&](float p, float g, float m) {
+    const float d = diff_masked(p, g, m);
+    const float sg = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f);
+    return gscale * sg * m;
+  };
+  const int64_t nvec = total / 4;
+  if ((N % 4) == 0) {
+    const float4* p4 = reinterpret_cast<const float4*>(pred);
+    const float4* g4 = reinterpret_cast<const float4*>(gt);
+    float4* o4 = reinterpret_cast<float4*>(dL_dpred);
+    const int64_t nv_per_ch = N / 4;
+    for (int64_t v = (int64_t)blockIdx.x * LOSS_THREADS * LOSS_VEC_PER_THREAD + threadIdx.x, it = 0;
+         it < LOSS_VEC_PER_THREAD; it++, v += LOSS_THREADS) {
+      if (v >= nvec) break;
+      const float4 p = __ldg(p4 + v), g = __ldg(g4 + v);
+      float4 m = make_float4(1.f, 1.f, 1.f, 1.f);
+      if (MASK) m = __ldg(reinterpret_cast<const float4*>(mask) + (v % nv_per_ch));
+      o4[v] = make_float4(grad1(p.x, g.x, m.x), grad1(p.y, g.y, m.y), grad1(p.z, g.z, m.z), grad1(p.w, g.w, m.w));
+    }
+  } else {
+    for (int64_t i = (int64_t)blockIdx.x * LOSS_THREADS * LOSS_VEC_PER_THREAD * 4 + threadIdx.x, it = 0;
+         it < LOSS_VEC_PER_THREAD * 4; it++, i += LOSS_THREADS) {
+      if (i >= total) break;
+      const float m = MASK ? __ldg(mask + (i % N)) : 1.f;
+      dL_dpred[i] = grad1(__ldg(pred + i), __ldg(gt + i), m);
+    }
+  }
+}
+
+inline unsigned loss_blocks(int64_t total) {
+  const int64_t per = (int64_t)LOSS_THREADS * LOSS_VEC_PER_THREAD * 4;
+  return (unsigned)((total + per - 1) / per);
+}
+
+}  // namespace
+
+cudaError_t launch_l1_forward(const float* pred, const float* gt, const float* mask, int C, int64_t N, float* loss,
+                              cudaStream_t s) {
+  cudaError_t e = cudaMemsetAsync(loss, 0, sizeof(float), s);
+  if (e != cudaSuccess) return e;
+  const int64_t total = (int64_t)C * N;
+  if (total == 0) return cudaSuccess;
+  const float inv = (float)(1.0 / (double)total);
+  if (mask) l1_forward_kernel<true><<<loss_blocks(total), LOSS_THREADS, 0, s>>>(pred, gt, mask, N, total, inv, loss);
+  else l1_forward_kernel<false><<<loss_blocks(total), LOSS_THREADS, 0, s>>>(pred, gt, mask, N, total, inv, loss);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_l1_backward(const float* pred, const float* gt, const float* mask, int C, int64_t N,
+                               const float* grad_out, float* dL_dpred, cudaStream_t s) {
+  const int64_t total = (int64_t)C * N;
+  if (total == 0) return cudaSuccess;
+  const float inv = (float)(1.0 / (double)total);
+  if (mask)
+    l1_backward_kernel<true><<<loss_blocks(total), LOSS_THREADS, 0, s>>>(pred, gt, mask, N, total, inv, grad_out,
+                                                                         dL_dpred);
+  else
+    l1_backward_kernel<false><<<loss_blocks(total), LOSS_THREADS, 0, s>>>(pred, gt, mask, N, total, inv, grad_out,
+                                                                          dL_dpred);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace lsr

@@ -99,7 +99,14 @@ render_bwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
   constexpr int I_FEAT = I_COL + (DCOL ? 3 : 0);
   constexpr int NV = I_FEAT + (FEAT ? 3 : 0);
 
+  // warp reduction through shared memory for wide value sets: lane l stores its NV partials as column l of a
+  // [NV][36]-float array (rows padded to 36 so the 128-bit row reads below are conflict-free), then lane (k, h) =
+  // (l & 15, l >> 4) sums the 16 partials of half h of row k, one shuffle joins the halves and lane k issues the RED.
+  // 12 STS + 4 LDS.128 + 16 FADD + 1 SHFL instead of the butterfly's 13 SHFL + 24 FSEL + 13 FADD.
+  constexpr bool SMEM_REDUCE = NV > 6;
+  constexpr int RED_ROW = 36;
   __shared__ WarpBatch sm;
+  __shared__ __align__(16) float s_red[SMEM_REDUCE ? NV * RED_ROW : 4];
 
   const int lane = threadIdx.x;
   const uint32_t tile = blockIdx.x / QUADS, quad = blockIdx.x % QUADS;
@@ -143,7 +150,7 @@ render_bwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
   const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
 
   // which reduced value this lane ends up holding, and where it goes
-  const int held = held_index<NV, 16>(lane);
+  const int held = SMEM_REDUCE ? (((lane & 15) < NV && lane < 16) ? (lane & 15) : -1) : held_index<NV, 16>(lane);
   float* out_base = nullptr;
   int out_stride = 0;
   if (held >= 0) {
@@ -270,8 +277,22 @@ render_bwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
           }
         }
       } else {
-        multi_reduce<NV, 16>(v, lane);
-        if (out_base != nullptr) atomicAdd(out_base + (size_t)gid * out_stride, v[0]);
+        if constexpr (SMEM_REDUCE) {
+#pragma unroll
+          for (int k = 0; k < NV; k++) s_red[k * RED_ROW + lane] = v[k];
+          __syncwarp();
+          const int row = min(lane & 15, NV - 1);
+          const float4* rp = reinterpret_cast<const float4*>(s_red + row * RED_ROW + (lane >> 4) * 16);
+          const float4 r0 = rp[0], r1 = rp[1], r2 = rp[2], r3 = rp[3];
+          float t = ((r0.x + r0.y) + (r0.z + r0.w)) + ((r1.x + r1.y) + (r1.z + r1.w)) +
+                    (((r2.x + r2.y) + (r2.z + r2.w)) + ((r3.x + r3.y) + (r3.z + r3.w)));
+          t += __shfl_xor_sync(0xffffffffu, t, 16);
+          if (out_base != nullptr) atomicAdd(out_base + (size_t)gid * out_stride, t);
+          __syncwarp();  // the rows are rewritten by the next working instance
+        } else {
+          multi_reduce<NV, 16>(v, lane);
+          if (out_base != nullptr) atomicAdd(out_base + (size_t)gid * out_stride, v[0]);
+        }
       }
     }
   }

@@ -182,3 +182,27 @@ def mark_visible(means3D, viewmatrix, dtype=np.float32) -> np.ndarray:
     getattr(lib(), "orc_mark_visible_" + ("f32" if dtype == np.float32 else "f64"))(
         ctypes.c_int(means3D.shape[0]), _p(means3D), _p(viewmatrix), _p(out))
     return out.astype(bool)
+
+
+# ---- L1 loss on the rendered images -------------------------------------------------------------
+def l1_loss(network_output, gt, mask=None) -> np.float32:
+    """utils/loss_utils.py:17-18 `torch.abs((network_output - gt)).mean()`, with train.py:96-99's masking
+    (`l1_loss(x * mask, gt * mask)`, mask broadcast over the channel dimension) when `mask` is given.
+    float32 products and difference as PyTorch computes them; the mean is accumulated in float64."""
+    x = np.asarray(network_output, np.float32)
+    g = np.asarray(gt, np.float32)
+    if mask is not None:
+        m = np.broadcast_to(np.asarray(mask, np.float32), x.shape)
+        x, g = x * m, g * m
+    d = (x - g).astype(np.float32)
+    return np.float32(np.abs(d).astype(np.float64).mean()) if d.size else np.float32("nan")
+
+
+def l1_loss_grad(network_output, gt, mask=None, grad_out: float = 1.0) -> np.ndarray:
+    """Gradient of `l1_loss` w.r.t. network_output: grad_out * sign(x*m - gt*m) * m / numel (sign(0) = 0)."""
+    x = np.asarray(network_output, np.float32)
+    g = np.asarray(gt, np.float32)
+    m = np.ones_like(x) if mask is None else np.broadcast_to(np.asarray(mask, np.float32), x.shape)
+    d = (x * m - g * m).astype(np.float32)
+    scale = np.float32(np.float32(grad_out) * np.float32(1.0 / max(d.size, 1)))
+    return (scale * np.sign(d) * m).astype(np.float32)
