@@ -104,15 +104,16 @@ enum {
   LSR_ARR_GEOM_REC = 0,      /* float[P][12]: x, y, conic.x, conic.y, conic.z, opacity, r, g, b, f0, f1, f2 */
   LSR_ARR_GEOM_DEPTH = 1,    /* float[P] */
   LSR_ARR_GEOM_TILES = 2,    /* uint32[P] tiles_touched */
-  LSR_ARR_GEOM_OFFSETS = 3,  /* uint32[P] inclusive scan of tiles_touched */
+  LSR_ARR_GEOM_OFFSETS = 3,  /* uint32[P] inclusive scan of tiles_touched taken in DEPTH ORDER (LSR_ARR_SCR_DEPTH_ORDER):
+                                offsets[i] = end of the instances of Gaussian depth_order[i] in the unsorted list */
   LSR_ARR_GEOM_COV3D = 4,    /* float[P][6] */
   LSR_ARR_GEOM_CLAMPED = 5,  /* uint8[P] bit ch set when colour channel ch was clamped */
   LSR_ARR_IMG_FINAL_T = 10,  /* float[H*W] */
   LSR_ARR_IMG_NCONTRIB = 11, /* uint32[H*W] */
   LSR_ARR_IMG_RANGES = 12,   /* uint32[T][2] */
-  LSR_ARR_SCR_KEYS_UNSORTED = 20, /* uint64[capacity] */
-  LSR_ARR_SCR_VALS_UNSORTED = 21, /* uint32[capacity] */
-  LSR_ARR_SCR_KEYS_SORTED = 22    /* uint64[capacity] sorted words as the forward keeps them (packed: use
+  LSR_ARR_SCR_KEYS_UNSORTED = 20, /* uint64[capacity] instance words (tile << id_bits | index), sort ping-pong */
+  LSR_ARR_SCR_DEPTH_ORDER = 21,   /* uint32[P] Gaussian indices in ascending depth order (stable) */
+  LSR_ARR_SCR_KEYS_SORTED = 22    /* uint64[capacity] sorted instance words as the forward keeps them (use
                                      lsr_debug_sorted_keys for the reference's key format) */
 };
 size_t lsr_array_offset(int which, int32_t P, int32_t width, int32_t height, int64_t capacity);
@@ -160,10 +161,11 @@ int lsr_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* k
 
 /* Tests / debugging: writes the sorted instance keys of the most recent lsr_forward issued from this thread, in the
  * reference's format (tile_id << 32 | float bits of depth; point_list_keys of rasterizer_impl.cu:181-194), into
- * keys_out[num_rendered].  The forward sorts a packed form of the same keys (compacted key | Gaussian id in one
- * 64-bit word); this is its exact inverse.  `scratch` is the buffer that forward was given. */
-int lsr_debug_sorted_keys(const void* scratch, int32_t P, int64_t capacity, int64_t num_rendered, uint64_t* keys_out,
-                          void* stream);
+ * keys_out[num_rendered].  The forward orders the Gaussians by depth first and then sorts instance words
+ * (tile_id << id_bits | Gaussian index) on the tile bits only; the reference key of an instance is its tile id with
+ * the depth bits of its Gaussian.  `scratch` / `geom` are the buffers that forward was given. */
+int lsr_debug_sorted_keys(const void* scratch, const void* geom, int32_t P, int64_t capacity, int64_t num_rendered,
+                          uint64_t* keys_out, void* stream);
 
 /* Per-stage device timing (CUDA events on `stream`), used by bench.py for the live roofline figures.
  * lsr_profile_enable(1) makes forward/backward record events; lsr_profile_read() synchronises the events of the

@@ -24,7 +24,7 @@ NEED_GEOMETRY, NEED_COLOR, NEED_FEATURE, NEED_MEANS2D, NEED_ALL = 1, 2, 4, 8, 15
 # lsr_array_offset ids
 ARR_GEOM_REC, ARR_GEOM_DEPTH, ARR_GEOM_TILES, ARR_GEOM_OFFSETS, ARR_GEOM_COV3D, ARR_GEOM_CLAMPED = 0, 1, 2, 3, 4, 5
 ARR_IMG_FINAL_T, ARR_IMG_NCONTRIB, ARR_IMG_RANGES = 10, 11, 12
-ARR_SCR_KEYS_UNSORTED, ARR_SCR_VALS_UNSORTED, ARR_SCR_KEYS_SORTED = 20, 21, 22
+ARR_SCR_KEYS_UNSORTED, ARR_SCR_DEPTH_ORDER, ARR_SCR_KEYS_SORTED = 20, 21, 22
 
 
 class Frame(Structure):
@@ -61,7 +61,7 @@ EXPORTS = {
     "lsr_sort_work_bytes": (c_size_t, [c_int64]),
     "lsr_sort_pairs": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p,
                                c_size_t, c_void_p]),
-    "lsr_debug_sorted_keys": (c_int, [c_void_p, c_int32, c_int64, c_int64, c_void_p, c_void_p]),
+    "lsr_debug_sorted_keys": (c_int, [c_void_p, c_void_p, c_int32, c_int64, c_int64, c_void_p, c_void_p]),
     "lsr_profile_enable": (None, [c_int]),
     "lsr_profile_read": (c_int, [POINTER(c_float), c_int]),
     "lsr_profile_stage_name": (c_char_p, [c_int]),

@@ -54,12 +54,14 @@ static uint32_t higher_msb(uint32_t n) {
 }
 
 // ---- per-stage profiling with CUDA events on the caller's stream ----
-enum { ST_PRE = 0, ST_SCAN, ST_SYNC, ST_DUP, ST_SORT, ST_RANGES, ST_RENDER, ST_BZERO, ST_BRENDER, ST_BPRE, ST_COUNT };
-static const char* kStageNames[ST_COUNT] = {"preprocess_fwd", "scan", "host_sync_gap", "duplicate", "sort",
-                                            "tile_ranges",    "render_fwd", "bwd_zero_fill", "render_bwd",
+enum { ST_PRE = 0, ST_SYNC, ST_DEPTH, ST_SCAN, ST_DUP, ST_SORT, ST_RANGES, ST_RENDER, ST_BZERO, ST_BRENDER, ST_BPRE,
+       ST_COUNT };
+static const char* kStageNames[ST_COUNT] = {"preprocess_fwd", "host_sync_gap", "depth_order", "scan", "duplicate",
+                                            "sort", "tile_ranges", "render_fwd", "bwd_zero_fill", "render_bwd",
                                             "preprocess_bwd"};
 static bool g_profile = false;
-static cudaEvent_t g_ev_f[8], g_ev_b[4];
+constexpr int N_EV_F = ST_RENDER - ST_PRE + 2;  // one event before each forward stage and one after the last
+static cudaEvent_t g_ev_f[N_EV_F], g_ev_b[4];
 static bool g_ev_init = false, g_have_f = false, g_have_b = false;
 static void prof_init() {
   if (g_ev_init) return;
@@ -71,8 +73,8 @@ static inline void prof(cudaEvent_t* arr, int i, cudaStream_t s) {
   if (g_profile) cudaEventRecord(arr[i], s);
 }
 
-// plan of the most recent forward on this thread (lsr_debug_sorted_keys decodes the packed words with it)
-static thread_local SortPlan g_last_plan = {0u, 32, 0, 32, 4, 0, false};
+// index width of the most recent forward on this thread (lsr_debug_sorted_keys decodes the instance words with it)
+static thread_local int g_last_id_bits = 0;
 
 static uint32_t* pinned_ctrl() {
   static thread_local uint32_t* p = nullptr;
@@ -112,7 +114,7 @@ size_t lsr_array_offset(int which, int32_t P, int32_t width, int32_t height, int
     case LSR_ARR_IMG_NCONTRIB: return (char*)im.n_contrib - base;
     case LSR_ARR_IMG_RANGES: return (char*)im.ranges - base;
     case LSR_ARR_SCR_KEYS_UNSORTED: return (char*)sc.keys_a - base;
-    case LSR_ARR_SCR_VALS_UNSORTED: return (char*)sc.vals_a - base;
+    case LSR_ARR_SCR_DEPTH_ORDER: return (char*)sc.perm - base;
     case LSR_ARR_SCR_KEYS_SORTED: return (char*)sc.keys_b - base;
     default: return (size_t)-1;
   }
@@ -133,8 +135,8 @@ int lsr_profile_read(float* ms, int n) {
   float v[ST_COUNT];
   for (int i = 0; i < ST_COUNT; i++) v[i] = 0.f;
   if (g_have_f) {
-    cudaEventSynchronize(g_ev_f[7]);
-    for (int i = 0; i < 7; i++) cudaEventElapsedTime(&v[ST_PRE + i], g_ev_f[i], g_ev_f[i + 1]);
+    cudaEventSynchronize(g_ev_f[N_EV_F - 1]);
+    for (int i = 0; i < N_EV_F - 1; i++) cudaEventElapsedTime(&v[ST_PRE + i], g_ev_f[i], g_ev_f[i + 1]);
   }
   if (g_have_b) {
     cudaEventSynchronize(g_ev_b[3]);
@@ -171,18 +173,15 @@ int lsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, c
   return LSR_OK;
 }
 
-int lsr_debug_sorted_keys(const void* scratch, int32_t P, int64_t capacity, int64_t num_rendered, uint64_t* keys_out,
-                          void* stream) {
+int lsr_debug_sorted_keys(const void* scratch, const void* geom, int32_t P, int64_t capacity, int64_t num_rendered,
+                          uint64_t* keys_out, void* stream) {
   if (num_rendered == 0) return LSR_OK;
-  if (!scratch || !keys_out || num_rendered < 0 || num_rendered > capacity) return fail(LSR_ERR_INVALID, "bad argument");
+  if (!scratch || !geom || !keys_out || num_rendered < 0 || num_rendered > capacity || g_last_id_bits <= 0)
+    return fail(LSR_ERR_INVALID, "bad argument");
   ScratchView sc = scratch_view(const_cast<void*>(scratch), P, capacity);
-  if (g_last_plan.packed) {
-    launch_unpack_keys(num_rendered, sc.keys_b, keys_out, g_last_plan, (cudaStream_t)stream);
-    LSR_CUDA(cudaGetLastError());
-  } else {
-    LSR_CUDA(cudaMemcpyAsync(keys_out, sc.keys_b, (size_t)num_rendered * 8, cudaMemcpyDeviceToDevice,
-                             (cudaStream_t)stream));
-  }
+  GeomView g = geom_view(const_cast<void*>(geom), P);
+  launch_unpack_keys(num_rendered, sc.keys_b, g.depth, keys_out, g_last_id_bits, (cudaStream_t)stream);
+  LSR_CUDA(cudaGetLastError());
   return LSR_OK;
 }
 
@@ -254,11 +253,9 @@ int lsr_forward(const lsr_frame* frame, const lsr_inputs* in, float* out_color, 
     launch_preprocess_fwd(*frame, *in, focal_x, focal_y, radii, g, sc.ctrl, s);
     LSR_STAGE("preprocess_fwd");
     prof(g_ev_f, 1, s);
-    launch_scan_tiles(P, g.tiles, g.offsets, sc.scan_status, sc.ctrl, s);
-    LSR_STAGE("scan");
-    prof(g_ev_f, 2, s);
-    // R decides the launch geometry of the sort; read it back like the reference does (rasterizer_impl.cu:284),
-    // together with the range of the depth word, which decides how many digits the sort needs
+    // R (accumulated by the preprocess kernel) decides the launch geometry of the instance sort; read it back like
+    // the reference does (rasterizer_impl.cu:284), together with the range of the depth word, which decides how many
+    // digits the depth ordering needs
     uint32_t* h = pinned_ctrl();
     LSR_CUDA(cudaMemcpyAsync(h, sc.ctrl, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
     LSR_CUDA(cudaStreamSynchronize(s));
@@ -269,37 +266,50 @@ int lsr_forward(const lsr_frame* frame, const lsr_inputs* in, float* out_color, 
     if (R > list_capacity) return fail(LSR_ERR_CAPACITY, "num_rendered %lld exceeds list capacity %lld",
                                        (long long)R, (long long)list_capacity);
     if (R > 0 && !list) return fail(LSR_ERR_INVALID, "null list buffer");
-    prof(g_ev_f, 3, s);
-    // the reference sorts bits [0, 32 + getHigherMsb(T)) (rasterizer_impl.cu:303,311); the depth word only spans
-    // [min, max], so the same order is obtained from hi_bits + bitlength(max - min) bits
+    prof(g_ev_f, 2, s);
+    // The reference sorts R keys on bits [0, 32 + getHigherMsb(T)) (rasterizer_impl.cu:303,311).  Same order, less
+    // traffic (binning.cu): (1) stable sort of the P Gaussians by depth — the depth word only spans [min, max], so
+    // bitlength(max - min) bits suffice; (2) instances emitted in that order; (3) stable sort of the R instance words
+    // on the tile bits only.
     int id_bits = 1;
     while (id_bits < 32 && (((uint32_t)P - 1u) >> id_bits) != 0) id_bits++;
-    const SortPlan plan =
-        make_sort_plan(~h[CTRL_DEPTH_NEGMIN], h[CTRL_DEPTH_MAX], (int)higher_msb((uint32_t)T), id_bits);
-    g_last_plan = plan;
-    // the sorted keys always end up in keys_b: the unsorted ones start in keys_a (odd pass count) or keys_b (even)
-    uint64_t* kin = (plan.passes & 1) ? sc.keys_a : sc.keys_b;
-    uint64_t* ktmp = sc.keys_a;
+    const SortPlan dplan = make_sort_plan(~h[CTRL_DEPTH_NEGMIN], h[CTRL_DEPTH_MAX], 0, id_bits);
+    const SortPlan plan = make_sort_plan_packed((int)higher_msb((uint32_t)T), id_bits);
+    g_last_id_bits = id_bits;
     if (R > 0) {
-      sort_prepare(sc.sort_work, R, plan, s);
-      launch_duplicate(P, gx, gy, radii, g, kin, sc.vals_a, list_capacity, plan,
-                       sort_work_view(sc.sort_work, R).hist, s);
-      LSR_STAGE("duplicate");
+      uint64_t* din = (dplan.passes & 1) ? sc.dwords_a : sc.dwords_b;  // sorted words always end up in dwords_b
+      sort_prepare(sc.sort_work_p, P, dplan, s);
+      launch_depth_words(P, g.depth, g.tiles, dplan, din, sort_work_view(sc.sort_work_p, P).hist, s);
+      sort_pairs(din, nullptr, sc.dwords_b, sc.perm, sc.dwords_a, nullptr, P, dplan, true, sc.sort_work_p, s);
+      LSR_STAGE("depth_order");
+    }
+    prof(g_ev_f, 3, s);
+    if (R > 0) {
+      launch_scan_tiles(P, g.tiles, sc.perm, g.offsets, sc.scan_status, sc.ctrl, s);
+      LSR_STAGE("scan");
     }
     prof(g_ev_f, 4, s);
+    // the sorted words always end up in keys_b: the unsorted ones start in keys_a (odd pass count) or keys_b (even)
+    uint64_t* kin = (plan.passes & 1) ? sc.keys_a : sc.keys_b;
     if (R > 0) {
-      sort_pairs(kin, sc.vals_a, sc.keys_b, (uint32_t*)list, ktmp, sc.vals_b, R, plan, true, sc.sort_work, s);
-      keys_sorted = sc.keys_b;
-      LSR_STAGE("sort");
+      sort_prepare(sc.sort_work, R, plan, s);
+      launch_duplicate(P, gx, gy, sc.perm, radii, g, kin, list_capacity, plan, sort_work_view(sc.sort_work, R).hist, s);
+      LSR_STAGE("duplicate");
     }
     prof(g_ev_f, 5, s);
     if (R > 0) {
-      launch_tile_ranges(R, keys_sorted, plan.packed ? plan.id_bits + plan.lo_bits : 32, img.ranges, s);
-      LSR_STAGE("tile_ranges");
+      sort_pairs(kin, nullptr, sc.keys_b, (uint32_t*)list, sc.keys_a, nullptr, R, plan, true, sc.sort_work, s);
+      keys_sorted = sc.keys_b;
+      LSR_STAGE("sort");
     }
     prof(g_ev_f, 6, s);
+    if (R > 0) {
+      launch_tile_ranges(R, keys_sorted, id_bits, img.ranges, s);
+      LSR_STAGE("tile_ranges");
+    }
+    prof(g_ev_f, 7, s);
   } else if (g_profile) {
-    for (int i = 0; i <= 6; i++) prof(g_ev_f, i, s);
+    for (int i = 0; i <= 7; i++) prof(g_ev_f, i, s);
   }
   // P == 0 (rasterize_points.cu:91): the reference returns zero-filled images; blending empty ranges gives
   // colour = bg, which differs, so reproduce the zero fill.
@@ -312,7 +322,7 @@ int lsr_forward(const lsr_frame* frame, const lsr_inputs* in, float* out_color, 
                       img.final_T, img.n_contrib, out_color, out_feature, s);
     LSR_STAGE("render_fwd");
   }
-  prof(g_ev_f, 7, s);
+  prof(g_ev_f, 8, s);
   if (g_profile) g_have_f = true;
   return LSR_OK;
 }

@@ -1,6 +1,12 @@
-// binning.cu — K2' tile-count scan, K3' key/value duplication, K5' tile ranges.
+// binning.cu — K2' tile-count scan, K3' instance duplication, K5' tile ranges.
 // Replaces cub::DeviceScan::InclusiveSum (RAST/cuda_rasterizer/rasterizer_impl.cu:280), duplicateWithKeys
 // (:70-111) and identifyTileRanges (:116-138).  All HBM-bound integer work.
+//
+// Depth-first binning.  The reference sorts R (tile | depth) keys, one per Gaussian/tile instance (:306-311).  The
+// same order is obtained with far less traffic by ordering the P Gaussians by depth first (a stable sort of P packed
+// words, api.cu) and emitting the instances in that order: a stable sort of the instances on the TILE bits alone then
+// leaves every tile's run in depth order, ties in Gaussian-index order — exactly the reference's stable result.
+// The R-sized sort shrinks from ceil((tile_bits + depth_bits) / 8) passes to ceil(tile_bits / 8) (C2: 5 -> 2).
 #include "common.cuh"
 #include "gs_math.cuh"
 
@@ -8,14 +14,51 @@ namespace lsr {
 
 namespace {
 
+// One packed word per Gaussian for the depth ordering: ((depth bits - lo_min) << id_bits) | index.  Gaussians that
+// touch no tile get depth field 0: where they land is irrelevant (they emit no instance).  The same pass counts the
+// digits of every pass of the depth sort (shared-memory histograms, one flush per CTA).  The low digits of a float's
+// bit pattern are close to uniform, so plain shared atomics rarely collide; the top digit takes few distinct values,
+// so there the lanes holding the same digit are merged first (MATCH.ANY) and one of them adds the group's count.
+constexpr int DW_THREADS = 256;
+__global__ void __launch_bounds__(DW_THREADS)
+depth_words_kernel(int P, const float* __restrict__ depths, const uint32_t* __restrict__ tiles, uint32_t lo_min,
+                   int id_bits, int passes, int total_bits, uint64_t* __restrict__ words,
+                   uint32_t* __restrict__ ghist) {
+  __shared__ uint32_t s_hist[SORT_MAX_PASSES * SORT_BINS];
+  const int tid = threadIdx.x, lane = tid & 31;
+  for (int j = tid; j < passes * SORT_BINS; j += DW_THREADS) s_hist[j] = 0;
+  __syncthreads();
+  const int n_round = (P + 31) & ~31;  // keep warps converged for match.any
+  for (int idx = blockIdx.x * DW_THREADS + tid; idx < n_round; idx += gridDim.x * DW_THREADS) {
+    const bool ok = idx < P;
+    uint32_t d = 0;
+    if (ok && tiles[idx] != 0u) d = __float_as_uint(depths[idx]) - lo_min;
+    if (ok) words[idx] = ((uint64_t)d << id_bits) | (uint64_t)(uint32_t)idx;
+    for (int p = 0; p < passes; p++) {
+      const int shift = p * SORT_RADIX_BITS;
+      const int bits = min(SORT_RADIX_BITS, total_bits - shift);
+      const uint32_t dg = (d >> shift) & ((1u << bits) - 1);
+      if (p + 1 < passes) {
+        if (ok) atomicAdd(&s_hist[p * SORT_BINS + dg], 1u);
+      } else {
+        const uint32_t peers = __match_any_sync(0xffffffffu, ok ? dg : 0xffffffffu);
+        if (ok && (peers & ((1u << lane) - 1)) == 0) atomicAdd(&s_hist[p * SORT_BINS + dg], (uint32_t)__popc(peers));
+      }
+    }
+  }
+  __syncthreads();
+  for (int j = tid; j < passes * SORT_BINS; j += DW_THREADS)
+    if (s_hist[j]) atomicAdd(&ghist[j], s_hist[j]);
+}
+
 // ------------------------------------------------------------------------------------------------------------
 // K2': single-pass inclusive scan with decoupled look-back.  status word: [63:62] flag, [31:0] value.
 // ------------------------------------------------------------------------------------------------------------
 constexpr uint64_t FLAG_AGG = 1ull << 62, FLAG_INC = 2ull << 62, FLAG_MASK = 3ull << 62;
 
 __global__ void __launch_bounds__(SCAN_THREADS)
-scan_tiles_kernel(int P, const uint32_t* __restrict__ in, uint32_t* __restrict__ out,
-                  volatile uint64_t* __restrict__ status, uint32_t* __restrict__ ctrl) {
+scan_tiles_kernel(int P, const uint32_t* __restrict__ in, const uint32_t* __restrict__ perm,
+                  uint32_t* __restrict__ out, volatile uint64_t* __restrict__ status, uint32_t* __restrict__ ctrl) {
   __shared__ uint32_t s_warp[SCAN_THREADS / 32];
   __shared__ uint32_t s_bid, s_prefix;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -24,7 +67,17 @@ scan_tiles_kernel(int P, const uint32_t* __restrict__ in, uint32_t* __restrict__
   const uint32_t bid = s_bid;
   const int base = bid * SCAN_TILE + tid * SCAN_ITEMS;
   uint32_t v[SCAN_ITEMS];
-  if (base + SCAN_ITEMS <= P) {
+  if (perm != nullptr) {  // scan in[perm[i]] (the depth order)
+    if (base + SCAN_ITEMS <= P) {
+      const uint4 a = __ldg(reinterpret_cast<const uint4*>(perm + base));
+      const uint4 b = __ldg(reinterpret_cast<const uint4*>(perm + base) + 1);
+      v[0] = __ldg(in + a.x); v[1] = __ldg(in + a.y); v[2] = __ldg(in + a.z); v[3] = __ldg(in + a.w);
+      v[4] = __ldg(in + b.x); v[5] = __ldg(in + b.y); v[6] = __ldg(in + b.z); v[7] = __ldg(in + b.w);
+    } else {
+#pragma unroll
+      for (int i = 0; i < SCAN_ITEMS; i++) v[i] = (base + i < P) ? in[perm[base + i]] : 0u;
+    }
+  } else if (base + SCAN_ITEMS <= P) {
     const uint4 a = __ldg(reinterpret_cast<const uint4*>(in + base));
     const uint4 b = __ldg(reinterpret_cast<const uint4*>(in + base) + 1);
     v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
@@ -83,7 +136,7 @@ scan_tiles_kernel(int P, const uint32_t* __restrict__ in, uint32_t* __restrict__
     }
     if (lane == 0) {
       s_prefix = prefix;
-      if ((int)(bid + 1) * SCAN_TILE >= P) ctrl[CTRL_NUM_RENDERED] = prefix + block_sum;
+      if (perm == nullptr && (int)(bid + 1) * SCAN_TILE >= P) ctrl[CTRL_NUM_RENDERED] = prefix + block_sum;
     }
   }
   __syncthreads();
@@ -101,45 +154,45 @@ scan_tiles_kernel(int P, const uint32_t* __restrict__ in, uint32_t* __restrict__
 }
 
 // ------------------------------------------------------------------------------------------------------------
-// K3': one (key, value) pair per Gaussian/tile overlap; key = tile_id << 32 | float_bits(depth); rect walked y-major
-// then x, pairs written consecutively from offsets[idx-1]  (rasterizer_impl.cu:85-109).
+// K3': one word per Gaussian/tile overlap, word = (tile_id << id_bits) | Gaussian index; rect walked y-major then x
+// (rasterizer_impl.cu:85-109), Gaussians taken in depth order (perm), instances of Gaussian perm[i] written
+// consecutively from offsets[i-1].  The reference's key tile_id << 32 | float_bits(depth) is implied: the depth
+// ordering is already in the emission order, and the depth bits are depths[index] (lsr_debug_sorted_keys).
 //
-// Load-balanced: a warp owns 32 consecutive Gaussians, whose instances occupy one contiguous output range; the 32
-// lanes walk that range together (lane = consecutive output slot), finding the owning Gaussian of each slot with a
-// 5-step binary search over the lanes' start offsets (shuffles).  Every store instruction therefore writes 32
-// consecutive keys (256 B) / values (128 B) — the reference's one-thread-per-Gaussian loop scatters them.
+// Load-balanced: a warp owns 32 consecutive Gaussians (of the depth order), whose instances occupy one contiguous
+// output range; the 32 lanes walk that range together (lane = consecutive output slot), finding the owning Gaussian
+// of each slot with a 5-step binary search over the lanes' start offsets (shuffles).  Every store instruction
+// therefore writes 32 consecutive words (256 B) — the reference's one-thread-per-Gaussian loop scatters them.
 // The division by the rect width uses a per-Gaussian magic reciprocal (exact for slot, width < 2^16).
 //
-// The kernel also accumulates the radix sort's digit histograms for every pass (in shared memory, flushed once per
-// CTA), so the sort never reads the keys just to count them.  Passes whose digit lies entirely inside the depth word
-// are counted once per Gaussian with weight tiles_touched; the others per instance, with runs of equal digits in a
-// warp collapsed into one shared-memory atomic (a full-warp shared atomic costs ~34 SM-cycles on B200, so only run
-// heads issue one).
+// The kernel also accumulates the tile sort's digit histograms for every pass (in shared memory, flushed once per
+// CTA), so the sort never reads the words just to count them; runs of equal digits in a warp are collapsed into one
+// shared-memory atomic (a full-warp shared atomic costs ~34 SM-cycles on B200, so only run heads issue one).
 // ------------------------------------------------------------------------------------------------------------
 constexpr int DUP_THREADS = 256;
 
 __global__ void __launch_bounds__(DUP_THREADS)
-duplicate_kernel(int P, int gx, int gy, const int32_t* __restrict__ radii, const GeomRec* __restrict__ rec,
-                 const float* __restrict__ depths, const uint32_t* __restrict__ offsets, uint64_t* __restrict__ keys,
-                 uint32_t* __restrict__ vals, uint32_t capacity, SortPlan plan, uint32_t* __restrict__ ghist) {
+duplicate_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const int32_t* __restrict__ radii,
+                 const GeomRec* __restrict__ rec, const uint32_t* __restrict__ offsets, uint64_t* __restrict__ words,
+                 uint32_t capacity, SortPlan plan, uint32_t* __restrict__ ghist) {
   __shared__ uint32_t s_hist[SORT_MAX_PASSES * SORT_BINS];
   const int tid = threadIdx.x, lane = tid & 31;
   const int passes = plan.passes;
   for (int j = tid; j < passes * SORT_BINS; j += DUP_THREADS) s_hist[j] = 0;
   __syncthreads();
-  // passes [0, per_gaussian) take their digit from the depth word only
-  const int per_gaussian = min(passes, plan.lo_bits / SORT_RADIX_BITS);
   const int nblocks = (P + DUP_THREADS - 1) / DUP_THREADS;
   for (int blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
-    const int idx = blk * DUP_THREADS + tid;
-    uint32_t x0 = 0, y0 = 0, x1 = 0, y1 = 0, incl = 0, dbits = 0;
+    const int i = blk * DUP_THREADS + tid;
+    uint32_t x0 = 0, y0 = 0, x1 = 0, y1 = 0, incl = 0, gid = 0;
     int radius = 0;
-    if (idx < P) radius = radii[idx];
-    incl = offsets[min(idx, P - 1)];  // lanes past the end sit at the end of the output range with zero instances
+    if (i < P) {
+      gid = perm[i];
+      radius = radii[gid];
+    }
+    incl = offsets[min(i, P - 1)];  // lanes past the end sit at the end of the output range with zero instances
     if (radius > 0) {
-      const float2 xy = *reinterpret_cast<const float2*>(rec + idx);
+      const float2 xy = *reinterpret_cast<const float2*>(rec + gid);
       get_rect(xy.x, xy.y, radius, gx, gy, x0, y0, x1, y1);
-      dbits = __float_as_uint(depths[idx]);
     }
     const uint32_t w = x1 - x0;
     const uint32_t cnt = w * (y1 - y0);
@@ -149,13 +202,7 @@ duplicate_kernel(int P, int gx, int gy, const int32_t* __restrict__ radii, const
     const uint32_t rel = start - wstart;
     const uint32_t magic = w > 1 ? 0xffffffffu / w + 1u : 0u;  // ceil(2^32 / w)
     const uint32_t origin = (y0 << 16) | x0;
-    const uint32_t lo = dbits - plan.lo_min;
-    if (cnt > 0) {
-      for (int p = 0; p < per_gaussian; p++)
-        atomicAdd(&s_hist[p * SORT_BINS + ((lo >> (p * SORT_RADIX_BITS)) & (SORT_BINS - 1))], cnt);
-    }
     const uint32_t total = wend - wstart;
-    const int wbase_idx = blk * DUP_THREADS + (tid & ~31);
     for (uint32_t k0 = 0; k0 < total; k0 += 32) {
       const uint32_t k = k0 + lane;
       // last lane j with rel_j <= k (zero-count lanes share their successor's start, so they are never picked)
@@ -169,28 +216,19 @@ duplicate_kernel(int P, int gx, int gy, const int32_t* __restrict__ radii, const
       const uint32_t jw = __shfl_sync(0xffffffffu, w, j);
       const uint32_t jmagic = __shfl_sync(0xffffffffu, magic, j);
       const uint32_t jorigin = __shfl_sync(0xffffffffu, origin, j);
-      const uint32_t jd = __shfl_sync(0xffffffffu, dbits, j);
+      const uint32_t jgid = __shfl_sync(0xffffffffu, gid, j);
       const bool ok = k < total;
       const uint32_t r = k - jrel;
       const uint32_t q = jw > 1 ? __umulhi(r, jmagic) : r;  // r / jw
       const uint32_t y = (jorigin >> 16) + q, x = (jorigin & 0xffffu) + (r - q * jw);
       const uint32_t tile = y * (uint32_t)gx + x;
       const uint32_t o = wstart + k;
-      // compacted key (radix_sort.cu): tile above the depth word's offset from its minimum
-      const uint64_t c = ((uint64_t)tile << plan.lo_bits) | (uint64_t)(jd - plan.lo_min);
-      if (ok && o < capacity) {
-        if (plan.packed) {
-          keys[o] = (c << plan.id_bits) | (uint64_t)(uint32_t)(wbase_idx + j);  // id rides in the low bits
-        } else {
-          keys[o] = ((uint64_t)tile << 32) | jd;
-          vals[o] = (uint32_t)(wbase_idx + j);
-        }
-      }
-      // digits that involve tile bits: one shared atomic per run of equal digits
-      for (int p = per_gaussian; p < passes; p++) {
+      if (ok && o < capacity) words[o] = ((uint64_t)tile << plan.id_bits) | (uint64_t)jgid;
+      // digits of the tile id: one shared atomic per run of equal digits
+      for (int p = 0; p < passes; p++) {
         const int shift = p * SORT_RADIX_BITS;
         const int bits = min(SORT_RADIX_BITS, plan.total_bits - shift);
-        const uint32_t d = ok ? ((uint32_t)(c >> shift) & ((1u << bits) - 1)) : 0xffffffffu;
+        const uint32_t d = ok ? ((tile >> shift) & ((1u << bits) - 1)) : 0xffffffffu;
         const uint32_t prev = __shfl_up_sync(0xffffffffu, d, 1);
         const bool head = (lane == 0) || (prev != d);
         const uint32_t heads = __ballot_sync(0xffffffffu, head);
@@ -239,32 +277,43 @@ tile_ranges_kernel(uint32_t L, const uint64_t* __restrict__ keys, int tile_shift
   }
 }
 
-// packed sorted word -> the reference's key format (tile << 32 | depth bits); exact inverse of the packing above
+// sorted word (tile << id_bits | index) -> the reference's key format (tile << 32 | depth bits of that Gaussian)
 __global__ void __launch_bounds__(256)
-unpack_keys_kernel(uint32_t L, const uint64_t* __restrict__ words, uint64_t* __restrict__ keys, SortPlan plan) {
+unpack_keys_kernel(uint32_t L, const uint64_t* __restrict__ words, const float* __restrict__ depths,
+                   uint64_t* __restrict__ keys, int id_bits) {
   const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= L) return;
-  const uint64_t c = words[idx] >> plan.id_bits;
-  const uint32_t lo = (uint32_t)(c & ((1ull << plan.lo_bits) - 1)) + plan.lo_min;
-  keys[idx] = ((c >> plan.lo_bits) << 32) | lo;
+  const uint64_t w = words[idx];
+  const uint32_t gid = (uint32_t)(w & ((1ull << id_bits) - 1));
+  keys[idx] = ((w >> id_bits) << 32) | (uint64_t)__float_as_uint(depths[gid]);
 }
 
 }  // namespace
 
-void launch_scan_tiles(int P, const uint32_t* tiles, uint32_t* offsets, uint64_t* status, uint32_t* ctrl,
-                       cudaStream_t s) {
+void launch_depth_words(int P, const float* depths, const uint32_t* tiles, const SortPlan& plan, uint64_t* words,
+                        uint32_t* ghist, cudaStream_t s) {
   if (P <= 0) return;
-  const int blocks = (P + SCAN_TILE - 1) / SCAN_TILE;
-  scan_tiles_kernel<<<blocks, SCAN_THREADS, 0, s>>>(P, tiles, offsets, status, ctrl);
+  const int nblocks = (P + DW_THREADS * 4 - 1) / (DW_THREADS * 4);
+  const int grid = nblocks < 148 * 2 ? nblocks : 148 * 2;  // few persistent CTAs: each flushes passes*256 global atomics
+  depth_words_kernel<<<grid, DW_THREADS, 0, s>>>(P, depths, tiles, plan.lo_min, plan.id_bits, plan.passes,
+                                                 plan.total_bits, words, ghist);
   count_launch();
 }
 
-void launch_duplicate(int P, int grid_x, int grid_y, const int32_t* radii, GeomView g, uint64_t* keys, uint32_t* vals,
-                      int64_t capacity, const SortPlan& plan, uint32_t* ghist, cudaStream_t s) {
+void launch_scan_tiles(int P, const uint32_t* tiles, const uint32_t* perm, uint32_t* offsets, uint64_t* status,
+                       uint32_t* ctrl, cudaStream_t s) {
+  if (P <= 0) return;
+  const int blocks = (P + SCAN_TILE - 1) / SCAN_TILE;
+  scan_tiles_kernel<<<blocks, SCAN_THREADS, 0, s>>>(P, tiles, perm, offsets, status, ctrl);
+  count_launch();
+}
+
+void launch_duplicate(int P, int grid_x, int grid_y, const uint32_t* perm, const int32_t* radii, GeomView g,
+                      uint64_t* words, int64_t capacity, const SortPlan& plan, uint32_t* ghist, cudaStream_t s) {
   if (P <= 0) return;
   const int nblocks = (P + DUP_THREADS - 1) / DUP_THREADS;
   const int grid = nblocks < 148 * 8 ? nblocks : 148 * 8;  // persistent CTAs: one histogram flush each
-  duplicate_kernel<<<grid, DUP_THREADS, 0, s>>>(P, grid_x, grid_y, radii, g.rec, g.depth, g.offsets, keys, vals,
+  duplicate_kernel<<<grid, DUP_THREADS, 0, s>>>(P, grid_x, grid_y, perm, radii, g.rec, g.offsets, words,
                                                    (uint32_t)capacity, plan, ghist);
   count_launch();
 }
@@ -275,9 +324,10 @@ void launch_tile_ranges(int64_t R, const uint64_t* keys, int tile_shift, uint2* 
   count_launch();
 }
 
-void launch_unpack_keys(int64_t R, const uint64_t* words, uint64_t* keys, const SortPlan& plan, cudaStream_t s) {
+void launch_unpack_keys(int64_t R, const uint64_t* words, const float* depths, uint64_t* keys, int id_bits,
+                        cudaStream_t s) {
   if (R <= 0) return;
-  unpack_keys_kernel<<<(unsigned)((R + 255) / 256), 256, 0, s>>>((uint32_t)R, words, keys, plan);
+  unpack_keys_kernel<<<(unsigned)((R + 255) / 256), 256, 0, s>>>((uint32_t)R, words, depths, keys, id_bits);
   count_launch();
 }
 

@@ -10,6 +10,12 @@ namespace lsr {
 constexpr int TILE_X = 16, TILE_Y = 16;  // reference: BLOCK_X/BLOCK_Y, RAST/cuda_rasterizer/config.h:17-18
 constexpr int TILE_PIX = TILE_X * TILE_Y;
 
+// render_bwd accumulates pair-weighted moments instead of the six geometric gradient sums, preprocess_bwd applies the
+// per-Gaussian coefficients (see render_bwd.cu).  0 restores the direct sums (A/B measurements).
+#ifndef LSR_MOMENTS
+#define LSR_MOMENTS 1
+#endif
+
 // One 48-byte record per Gaussian holds everything the blend kernels gather per instance, so a gather touches
 // two 32-B sectors instead of the reference's four to six (means2D, conic_opacity, rgb, feature are separate
 // arrays there: rasterizer_impl.cu:155-170).
@@ -74,6 +80,7 @@ constexpr int SORT_BINS = 1 << SORT_RADIX_BITS;
 constexpr int SORT_THREADS = 256;
 constexpr int SORT_ITEMS = 16;
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // keys per CTA per pass
+inline int sort_items_for(int64_t) { return SORT_ITEMS; }  // keys per thread (the kernel is templated on it)
 constexpr int SORT_MAX_PASSES = 8;
 
 struct SortWork {  // carved from the `work` buffer
@@ -106,30 +113,37 @@ inline size_t scan_nblocks(int P) { return (size_t)((P + SCAN_TILE - 1) / SCAN_T
 struct ScratchView {
   uint32_t* ctrl;  // [64] control words: [0] num_rendered, [1] scan ticket, [2] error flags
   uint64_t* scan_status;  // [scan_nblocks]
-  uint64_t* keys_a;
-  uint64_t* keys_b;
-  uint32_t* vals_a;
-  uint32_t* vals_b;
-  void* sort_work;
+  uint64_t* dwords_a;     // [P] depth-order sort of the Gaussians: packed (depth | index) words, ping
+  uint64_t* dwords_b;     // [P] pong (sorted result)
+  uint32_t* perm;         // [P] Gaussian indices in depth order
+  void* sort_work_p;      // sort workspace for P elements
+  uint64_t* keys_a;       // [cap] instance words (tile | index), ping-pong
+  uint64_t* keys_b;       // [cap] sorted instance words end up here
+  void* sort_work;        // sort workspace for cap elements
   size_t head_zero_bytes;  // ctrl + scan_status must be zero at the start of every forward
 };
 inline ScratchView scratch_view(void* base, int P, int64_t cap) {
   char* p = (char*)base;
   ScratchView s;
   size_t c = (size_t)(cap > 0 ? cap : 0);
+  size_t n = (size_t)(P > 0 ? P : 0);
   s.ctrl = (uint32_t*)p;          p += 256;
   s.scan_status = (uint64_t*)p;   p += align_up(scan_nblocks(P) * 8);
   s.head_zero_bytes = (size_t)(p - (char*)base);
+  s.dwords_a = (uint64_t*)p;      p += align_up(n * 8);
+  s.dwords_b = (uint64_t*)p;      p += align_up(n * 8);
+  s.perm = (uint32_t*)p;          p += align_up(n * 4);
+  s.sort_work_p = (void*)p;       p += sort_work_bytes((int64_t)n);
   s.keys_a = (uint64_t*)p;        p += align_up(c * 8);
   s.keys_b = (uint64_t*)p;        p += align_up(c * 8);
-  s.vals_a = (uint32_t*)p;        p += align_up(c * 4);
-  s.vals_b = (uint32_t*)p;        p += align_up(c * 4);
   s.sort_work = (void*)p;
   return s;
 }
 inline size_t scratch_bytes(int P, int64_t cap) {
   size_t c = (size_t)(cap > 0 ? cap : 0);
-  return 256 + align_up(scan_nblocks(P) * 8) + 2 * align_up(c * 8) + 2 * align_up(c * 4) + sort_work_bytes(cap) + 256;
+  size_t n = (size_t)(P > 0 ? P : 0);
+  return 256 + align_up(scan_nblocks(P) * 8) + 2 * align_up(n * 8) + align_up(n * 4) + sort_work_bytes((int64_t)n) +
+         2 * align_up(c * 8) + sort_work_bytes(cap) + 256;
 }
 
 // ctrl words (zeroed at the start of every forward).  DEPTH_NEGMIN holds max(~bits) so that zero-init works.
@@ -145,18 +159,26 @@ struct SortPlan {
 };
 SortPlan make_sort_plan(uint32_t lo_min, uint32_t lo_max, int hi_bits, int id_bits);
 SortPlan make_sort_plan_bits(int end_bit);
+// packed plan whose compacted key is `key_bits` wide (digits from bits [id_bits, id_bits + key_bits) of the word)
+SortPlan make_sort_plan_packed(int key_bits, int id_bits);
 
 // ---- launchers implemented in the .cu files ----
 void launch_preprocess_fwd(const lsr_frame& f, const lsr_inputs& in, float focal_x, float focal_y, int32_t* radii,
                            GeomView g, uint32_t* ctrl, cudaStream_t s);
-void launch_scan_tiles(int P, const uint32_t* tiles, uint32_t* offsets, uint64_t* status, uint32_t* ctrl,
-                       cudaStream_t s);
-void launch_duplicate(int P, int grid_x, int grid_y, const int32_t* radii, GeomView g, uint64_t* keys, uint32_t* vals,
-                      int64_t capacity, const SortPlan& plan, uint32_t* ghist, cudaStream_t s);
+// packed (depth - lo_min | index) words of the P Gaussians, input of the depth-order sort, and that sort's digit
+// histograms (ghist must be zero: sort_prepare)
+void launch_depth_words(int P, const float* depths, const uint32_t* tiles, const SortPlan& plan, uint64_t* words,
+                        uint32_t* ghist, cudaStream_t s);
+// inclusive scan of tiles[perm[i]] (perm == nullptr: of tiles[i], which also publishes the total in ctrl)
+void launch_scan_tiles(int P, const uint32_t* tiles, const uint32_t* perm, uint32_t* offsets, uint64_t* status,
+                       uint32_t* ctrl, cudaStream_t s);
+void launch_duplicate(int P, int grid_x, int grid_y, const uint32_t* perm, const int32_t* radii, GeomView g,
+                      uint64_t* words, int64_t capacity, const SortPlan& plan, uint32_t* ghist, cudaStream_t s);
 // tile id of a sorted word = word >> tile_shift (32 for reference-format keys)
 void launch_tile_ranges(int64_t R, const uint64_t* keys, int tile_shift, uint2* ranges, cudaStream_t s);
-// reference-format keys (tile << 32 | depth bits) from the packed sorted words (tests / debugging)
-void launch_unpack_keys(int64_t R, const uint64_t* words, uint64_t* keys, const SortPlan& plan, cudaStream_t s);
+// reference-format keys (tile << 32 | depth bits) from the sorted instance words (tests / debugging)
+void launch_unpack_keys(int64_t R, const uint64_t* words, const float* depths, uint64_t* keys, int id_bits,
+                        cudaStream_t s);
 // hist_ready: the per-pass digit histograms are already in the work buffer (sort_prepare + duplication kernel)
 void sort_prepare(void* work, int64_t n, const SortPlan& pl, cudaStream_t s);
 int sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,

@@ -403,7 +403,7 @@ void launch_preprocess_bwd(const lsr_frame& f, const lsr_inputs& in, float focal
                            const int32_t* radii, GeomView g, uint32_t need_mask, const lsr_grads& gr, cudaStream_t s) {
   if (f.P <= 0) return;
   // the blend kernel leaves moments instead of gradients exactly when it ran in its GEOM mode (render_bwd.cu)
-  const int moments = (need_mask & LSR_NEED_GEOMETRY) ? 1 : 0;
+  const int moments = (LSR_MOMENTS && (need_mask & LSR_NEED_GEOMETRY)) ? 1 : 0;
   const float* cov3Ds = in.cov3D_precomp ? in.cov3D_precomp : g.cov3D;
   const bool sh16 = in.shs != nullptr && gr.dL_dsh != nullptr && f.M == 16 && (((uintptr_t)in.shs) & 15) == 0 &&
                     (((uintptr_t)gr.dL_dsh) & 15) == 0;

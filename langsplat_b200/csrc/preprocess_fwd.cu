@@ -65,7 +65,7 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   __shared__ __align__(16) float s_scl[PRE_THREADS * 3];
   __shared__ __align__(16) float s_lng[PRE_THREADS * 3];
   __shared__ float s_view[16], s_proj[16], s_cam[3];
-  __shared__ uint32_t s_negmin, s_max;
+  __shared__ uint32_t s_negmin, s_max, s_tiles;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int first = blockIdx.x * PRE_THREADS;
   const int count = min(PRE_THREADS, P - first);
@@ -74,7 +74,7 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
     s_proj[tid] = projmatrix[tid];
   }
   if (tid < 3) s_cam[tid] = campos[tid];
-  if (tid == 0) { s_negmin = 0u; s_max = 0u; }
+  if (tid == 0) { s_negmin = 0u; s_max = 0u; s_tiles = 0u; }
   stage_flat_async<PRE_THREADS>(means3D, s_xyz, (size_t)first * 3, count * 3, tid);
   if (scales) stage_flat_async<PRE_THREADS>(scales, s_scl, (size_t)first * 3, count * 3, tid);
   if (lang) stage_flat_async<PRE_THREADS>(lang, s_lng, (size_t)first * 3, count * 3, tid);
@@ -227,12 +227,16 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
     const uint32_t bits = __float_as_uint(viewz);
     const uint32_t wmax = __reduce_max_sync(0xffffffffu, vis ? bits : 0u);
     const uint32_t wneg = __reduce_max_sync(0xffffffffu, vis ? ~bits : 0u);
-    if (lane == 0) { atomicMax(&s_max, wmax); atomicMax(&s_negmin, wneg); }
+    const uint32_t wtiles = __reduce_add_sync(0xffffffffu, tiles_out);
+    if (lane == 0) { atomicMax(&s_max, wmax); atomicMax(&s_negmin, wneg); atomicAdd(&s_tiles, wtiles); }
   }
   __syncthreads();
   if (tid == 0 && s_max != 0u) {
     atomicMax(&ctrl[CTRL_DEPTH_MAX], s_max);
     atomicMax(&ctrl[CTRL_DEPTH_NEGMIN], s_negmin);
+    // num_rendered = sum of tiles_touched (the reference reads it off the end of its prefix sum,
+    // rasterizer_impl.cu:280-284); the host needs it before the instance list is laid out in depth order
+    if (s_tiles) atomicAdd(&ctrl[CTRL_NUM_RENDERED], s_tiles);
   }
 }
 

@@ -33,7 +33,9 @@ constexpr int BITS = SORT_RADIX_BITS;
 constexpr int BINS = SORT_BINS;
 static_assert(BINS == SORT_THREADS, "one bin per thread in the look-back");
 // keys (8 B) staged first, the same region is reused for the values; per-warp histograms; bin starts; global offsets
-constexpr size_t SORT_SMEM = (size_t)SORT_TILE * 8 + (size_t)WARPS * BINS * 4 + BINS * 4 + SORT_TILE;
+constexpr size_t sort_smem(int items) {
+  return (size_t)SORT_THREADS * items * 8 + (size_t)WARPS * BINS * 4 + BINS * 4 + (size_t)SORT_THREADS * items;
+}
 
 struct DigitMap {  // compacted key = (hi << lo_bits) | (lo - lo_min)
   uint32_t lo_min;
@@ -45,11 +47,13 @@ __device__ __forceinline__ uint32_t digit_of(uint64_t key, const DigitMap m, int
   return (uint32_t)(c >> shift) & mask;
 }
 
-// Stand-alone histogram of all passes (lsr_sort_pairs only; the forward fuses this into the duplication kernel).
+// Stand-alone histogram of all passes (lsr_sort_pairs and the forward's depth-order sort of the Gaussians; the
+// instance sort's histograms come from the duplication kernel).  packed_shift >= 0: the words are packed
+// (compacted key << id_bits | id) and packed_shift = id_bits.
 // Warp-private shared histograms, one plain read-modify-write per group of equal digits (no shared atomics).
 __global__ void __launch_bounds__(256)
 sort_hist_kernel(const uint64_t* __restrict__ keys, uint32_t n, int passes, int total_bits, DigitMap dm,
-                 uint32_t* __restrict__ ghist) {
+                 int packed_shift, uint32_t* __restrict__ ghist) {
   extern __shared__ uint32_t sh_hist[];  // [8 warps][passes][BINS]
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   for (int j = tid; j < 8 * passes * BINS; j += 256) sh_hist[j] = 0;
@@ -63,7 +67,10 @@ sort_hist_kernel(const uint64_t* __restrict__ keys, uint32_t n, int passes, int 
     for (int p = 0; p < passes; p++) {
       const int shift = p * BITS;
       const int bits = min(BITS, total_bits - shift);
-      const uint32_t d = ok ? digit_of(key, dm, shift, (1u << bits) - 1) : 0xffffffffu;
+      const uint32_t mask = (1u << bits) - 1;
+      const uint32_t d = !ok ? 0xffffffffu
+                             : (packed_shift >= 0 ? ((uint32_t)(key >> (packed_shift + shift)) & mask)
+                                                  : digit_of(key, dm, shift, mask));
       const uint32_t peers = __match_any_sync(0xffffffffu, d);
       if (ok && (peers & ((1u << lane) - 1)) == 0) wh[p * BINS + d] += __popc(peers);
       __syncwarp();
@@ -128,7 +135,7 @@ __device__ __forceinline__ uint32_t sw(uint32_t p) { return p ^ ((p >> 4) & 15u)
 // PAIRS = false: the value rides in the low bits of the 64-bit word (binning.cu packs compacted key | Gaussian id), so
 // a pass moves 8 instead of 12 bytes per element and the whole value phase disappears; the last pass additionally
 // writes the ids out as the u32 point list (`ids_out`).
-template <int NB, bool PAIRS>
+template <int NB, bool PAIRS, int ITEMS>
 __global__ void __launch_bounds__(SORT_THREADS, 4)
 onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, const uint32_t* __restrict__ vin,
                 uint32_t* __restrict__ vout, uint32_t n, uint32_t* __restrict__ ticket,
@@ -137,7 +144,7 @@ onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, c
   extern __shared__ __align__(16) unsigned char smem[];
   uint64_t* s_keys = reinterpret_cast<uint64_t*>(smem);
   uint32_t* s_vals = reinterpret_cast<uint32_t*>(smem);  // reuses the key region after the keys are written out
-  uint32_t* s_whist = reinterpret_cast<uint32_t*>(smem + (size_t)SORT_TILE * 8);  // [WARPS][BINS]
+  uint32_t* s_whist = reinterpret_cast<uint32_t*>(smem + (size_t)(SORT_THREADS * ITEMS) * 8);  // [WARPS][BINS]
   uint32_t* s_gofs = s_whist + WARPS * BINS;
   uint8_t* s_dig = reinterpret_cast<uint8_t*>(s_gofs + BINS);  // digit of the element at CTA-sorted position p
   __shared__ uint32_t s_tile;
@@ -149,21 +156,21 @@ onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, c
   for (int j = tid; j < WARPS * BINS; j += SORT_THREADS) s_whist[j] = 0;
   __syncthreads();
   const uint32_t tile = s_tile;
-  const uint32_t tile_base = tile * SORT_TILE;
+  const uint32_t tile_base = tile * (SORT_THREADS * ITEMS);
   if (tile_base >= n) return;
-  const uint32_t valid = min((uint32_t)SORT_TILE, n - tile_base);
-  const bool full = valid == SORT_TILE;
+  const uint32_t valid = min((uint32_t)(SORT_THREADS * ITEMS), n - tile_base);
+  const bool full = valid == (SORT_THREADS * ITEMS);
 
   // ---- load (warp-striped: warp w owns a contiguous 32*ITEMS chunk; item i of lane l is element i*32+l) ----
-  const uint32_t wofs = warp * (32 * SORT_ITEMS) + lane;  // + i*32 = position inside the tile
+  const uint32_t wofs = warp * (32 * ITEMS) + lane;  // + i*32 = position inside the tile
   const uint64_t* kp = kin + tile_base + wofs;
-  uint64_t key[SORT_ITEMS];
+  uint64_t key[ITEMS];
   if (full) {
 #pragma unroll
-    for (int i = 0; i < SORT_ITEMS; i++) key[i] = __ldg(kp + i * 32);
+    for (int i = 0; i < ITEMS; i++) key[i] = __ldg(kp + i * 32);
   } else {
 #pragma unroll
-    for (int i = 0; i < SORT_ITEMS; i++) key[i] = (wofs + i * 32 < valid) ? __ldg(kp + i * 32) : 0ull;
+    for (int i = 0; i < ITEMS; i++) key[i] = (wofs + i * 32 < valid) ? __ldg(kp + i * 32) : 0ull;
   }
   // exclusive bin bases of this pass from the raw global histogram (every CTA redoes this 256-element scan)
   uint32_t gbase;
@@ -185,19 +192,19 @@ onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, c
   }
   // ---- digits (once), packed four to a register ----
   // padding items of a partial last tile take the highest digit and, being the last elements, rank last inside it
-  uint32_t dig[SORT_ITEMS / 4];
+  uint32_t dig[ITEMS / 4];
 #pragma unroll
-  for (int i = 0; i < SORT_ITEMS; i++) {
+  for (int i = 0; i < ITEMS; i++) {
     uint32_t d = pass_digit(key[i], pd);
     if (!full && !(wofs + i * 32 < valid)) d = BINS - 1;
     if ((i & 3) == 0) dig[i >> 2] = d; else dig[i >> 2] |= d << (8 * (i & 3));
   }
   // ---- warp-level multi-split ranking (stable: items in ascending i, lanes in ascending order) ----
-  uint16_t rank[SORT_ITEMS];
+  uint16_t rank[ITEMS];
   uint32_t* wh = s_whist + warp * BINS;
   const uint32_t lt = (1u << lane) - 1;
 #pragma unroll
-  for (int i = 0; i < SORT_ITEMS; i++) {
+  for (int i = 0; i < ITEMS; i++) {
     const uint32_t d = (dig[i >> 2] >> (8 * (i & 3))) & 0xffu;
     // (padding digits of a partial last tile may exceed NB bits, so that tile matches on all 8)
     const uint32_t peers = NB == 0 ? __match_any_sync(0xffffffffu, d) : (full ? match_digit<NB>(d) : match_digit<BITS>(d));
@@ -222,7 +229,7 @@ onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, c
       cnt += s_whist[w * BINS + t];
     }
     vcnt = cnt;
-    if (t == BINS - 1) vcnt -= (SORT_TILE - valid);
+    if (t == BINS - 1) vcnt -= ((SORT_THREADS * ITEMS) - valid);
     volatile uint32_t* mine = lookback + (size_t)tile * BINS + t;
     *mine = (tile == 0 ? LB_INC : LB_AGG) | vcnt;  // publish before the CTA-wide scan
     uint32_t inc = cnt;
@@ -245,9 +252,9 @@ onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, c
   __syncthreads();
 
   // ---- stage keys in CTA-sorted order, write them out as coalesced runs ----
-  // (rank[] now holds the CTA-sorted position, < SORT_TILE <= 65536)
+  // (rank[] now holds the CTA-sorted position, < (SORT_THREADS * ITEMS) <= 65536)
 #pragma unroll
-  for (int i = 0; i < SORT_ITEMS; i++) {
+  for (int i = 0; i < ITEMS; i++) {
     const uint32_t d = (dig[i >> 2] >> (8 * (i & 3))) & 0xffu;
     const uint32_t pos = wh[d] + rank[i];
     rank[i] = (uint16_t)pos;
@@ -255,15 +262,15 @@ onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, c
     s_dig[sw(pos)] = (uint8_t)d;
   }
   // the values are fetched now: their latency overlaps the key write-out
-  uint32_t val[PAIRS ? SORT_ITEMS : 1];
+  uint32_t val[PAIRS ? ITEMS : 1];
   if (PAIRS) {
     const uint32_t* vp = vin + tile_base + wofs;
     if (full) {
 #pragma unroll
-      for (int i = 0; i < SORT_ITEMS; i++) val[i] = __ldg(vp + i * 32);
+      for (int i = 0; i < ITEMS; i++) val[i] = __ldg(vp + i * 32);
     } else {
 #pragma unroll
-      for (int i = 0; i < SORT_ITEMS; i++) val[i] = (wofs + i * 32 < valid) ? __ldg(vp + i * 32) : 0u;
+      for (int i = 0; i < ITEMS; i++) val[i] = (wofs + i * 32 < valid) ? __ldg(vp + i * 32) : 0u;
     }
   }
   // ---- decoupled look-back (thread t == bin t); the staged keys and the value loads are already in flight ----
@@ -296,7 +303,7 @@ onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, c
   __syncthreads();
   if (full) {
 #pragma unroll
-    for (int i = 0; i < SORT_ITEMS; i++) {
+    for (int i = 0; i < ITEMS; i++) {
       const uint32_t p = tid + i * SORT_THREADS;
       const uint64_t k = s_keys[sw(p)];
       const uint32_t g = s_gofs[s_dig[sw(p)]] + p;
@@ -305,7 +312,7 @@ onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, c
     }
   } else {
 #pragma unroll
-    for (int i = 0; i < SORT_ITEMS; i++) {
+    for (int i = 0; i < ITEMS; i++) {
       const uint32_t p = tid + i * SORT_THREADS;
       if (p < valid) {
         const uint64_t k = s_keys[sw(p)];
@@ -318,17 +325,17 @@ onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, c
   if (!PAIRS) return;
   __syncthreads();
 #pragma unroll
-  for (int i = 0; i < SORT_ITEMS; i++) s_vals[sw(rank[i])] = val[PAIRS ? i : 0];
+  for (int i = 0; i < ITEMS; i++) s_vals[sw(rank[i])] = val[PAIRS ? i : 0];
   __syncthreads();
   if (full) {
 #pragma unroll
-    for (int i = 0; i < SORT_ITEMS; i++) {
+    for (int i = 0; i < ITEMS; i++) {
       const uint32_t p = tid + i * SORT_THREADS;
       vout[s_gofs[s_dig[sw(p)]] + p] = s_vals[sw(p)];
     }
   } else {
 #pragma unroll
-    for (int i = 0; i < SORT_ITEMS; i++) {
+    for (int i = 0; i < ITEMS; i++) {
       const uint32_t p = tid + i * SORT_THREADS;
       if (p < valid) vout[s_gofs[s_dig[sw(p)]] + p] = s_vals[sw(p)];
     }
@@ -337,22 +344,25 @@ onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, c
 
 using OnesweepFn = void (*)(const uint64_t*, uint64_t*, const uint32_t*, uint32_t*, uint32_t, uint32_t*,
                             volatile uint32_t*, const uint32_t*, PassDigit, uint32_t*, uint32_t);
-template <bool PAIRS>
+template <bool PAIRS, int ITEMS>
 OnesweepFn onesweep_for_bits_t(int nb) {
   switch (nb) {
-    case 0: return onesweep_kernel<0, PAIRS>;
-    case 1: return onesweep_kernel<1, PAIRS>;
-    case 2: return onesweep_kernel<2, PAIRS>;
-    case 3: return onesweep_kernel<3, PAIRS>;
-    case 4: return onesweep_kernel<4, PAIRS>;
-    case 5: return onesweep_kernel<5, PAIRS>;
-    case 6: return onesweep_kernel<6, PAIRS>;
-    case 7: return onesweep_kernel<7, PAIRS>;
-    default: return onesweep_kernel<8, PAIRS>;
+    case 0: return onesweep_kernel<0, PAIRS, ITEMS>;
+    case 1: return onesweep_kernel<1, PAIRS, ITEMS>;
+    case 2: return onesweep_kernel<2, PAIRS, ITEMS>;
+    case 3: return onesweep_kernel<3, PAIRS, ITEMS>;
+    case 4: return onesweep_kernel<4, PAIRS, ITEMS>;
+    case 5: return onesweep_kernel<5, PAIRS, ITEMS>;
+    case 6: return onesweep_kernel<6, PAIRS, ITEMS>;
+    case 7: return onesweep_kernel<7, PAIRS, ITEMS>;
+    default: return onesweep_kernel<8, PAIRS, ITEMS>;
   }
 }
-OnesweepFn onesweep_for_bits(int nb, bool pairs) {
-  return pairs ? onesweep_for_bits_t<true>(nb) : onesweep_for_bits_t<false>(nb);
+// (1024-key tiles for small inputs were measured and rejected: the depth ordering of 1 M Gaussians went from 20 to
+// 24 us per pass — the single-wave passes are bound by the look-back chain, which more tiles only lengthen)
+OnesweepFn onesweep_for_bits(int nb, bool pairs, int items) {
+  (void)items;
+  return pairs ? onesweep_for_bits_t<true, SORT_ITEMS>(nb) : onesweep_for_bits_t<false, SORT_ITEMS>(nb);
 }
 
 }  // namespace
@@ -387,6 +397,19 @@ SortPlan make_sort_plan_bits(int end_bit) {
   return pl;
 }
 
+SortPlan make_sort_plan_packed(int key_bits, int id_bits) {
+  if (key_bits < 1) key_bits = 1;
+  SortPlan pl;
+  pl.lo_min = 0;
+  pl.lo_bits = 0;
+  pl.hi_bits = key_bits;
+  pl.total_bits = key_bits;
+  pl.passes = (key_bits + BITS - 1) / BITS;
+  pl.id_bits = id_bits;
+  pl.packed = true;
+  return pl;
+}
+
 void sort_prepare(void* work, int64_t n, const SortPlan& pl, cudaStream_t s) {
   // histograms + tickets + the look-back words of the passes that will run must be zero
   SortWork w = sort_work_view(work, n);
@@ -399,12 +422,17 @@ int sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_
                cudaStream_t s) {
   if (n <= 0) return 0;
   SortWork w = sort_work_view(work, n);
-  const uint32_t nblocks = (uint32_t)((n + SORT_TILE - 1) / SORT_TILE);
+  const int items = sort_items_for(n);
+  const uint32_t nblocks = (uint32_t)((n + SORT_THREADS * items - 1) / (SORT_THREADS * items));
   static bool attr_done = false;
   if (!attr_done) {
     for (int nb = 0; nb <= BITS; nb++) {
-      cudaFuncSetAttribute(onesweep_for_bits(nb, true), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM);
-      cudaFuncSetAttribute(onesweep_for_bits(nb, false), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM);
+      for (int it : {SORT_ITEMS}) {
+        cudaFuncSetAttribute(onesweep_for_bits(nb, true, it), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)sort_smem(it));
+        cudaFuncSetAttribute(onesweep_for_bits(nb, false, it), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)sort_smem(it));
+      }
     }
     attr_done = true;
   }
@@ -414,7 +442,8 @@ int sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_
     const uint32_t hist_blocks = (uint32_t)std::min<int64_t>((n + 2047) / 2048, (int64_t)148 * 8);
     const size_t hist_smem = (size_t)8 * pl.passes * BINS * 4;
     cudaFuncSetAttribute(sort_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_smem);
-    sort_hist_kernel<<<hist_blocks, 256, hist_smem, s>>>(keys_in, (uint32_t)n, pl.passes, pl.total_bits, dm, w.hist);
+    sort_hist_kernel<<<hist_blocks, 256, hist_smem, s>>>(keys_in, (uint32_t)n, pl.passes, pl.total_bits, dm,
+                                                         pl.packed ? pl.id_bits : -1, w.hist);
     count_launch();
   }
   const uint64_t* ksrc = keys_in;
@@ -443,7 +472,7 @@ int sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_
     }
     const bool last = p == pl.passes - 1;
     const bool depth_only = shift + bits <= pl.lo_bits && bits == BITS;  // digit inside the depth word: MATCH.ANY
-    onesweep_for_bits(depth_only ? 0 : bits, !pl.packed)<<<nblocks, SORT_THREADS, SORT_SMEM, s>>>(
+    onesweep_for_bits(depth_only ? 0 : bits, !pl.packed, items)<<<nblocks, SORT_THREADS, sort_smem(items), s>>>(
         ksrc, kdst, vsrc, vdst, (uint32_t)n, w.tickets + p, w.lookback + (size_t)p * sort_nblocks(n) * BINS,
         w.hist + p * BINS, pd, (pl.packed && last) ? vals_out : nullptr,
         pl.id_bits >= 32 ? 0xffffffffu : ((1u << pl.id_bits) - 1));

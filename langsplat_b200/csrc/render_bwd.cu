@@ -235,7 +235,7 @@ render_bwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
           alpha_last[s] = alpha[s];
           float dL_dalpha = (cd - accA[s]) * T[s];
           if (DCOL) dL_dalpha += bgT[s] * rcp;  // background term (backward.cu:545-550)
-          if (GEOM) {
+          if (GEOM && LSR_MOMENTS) {
             // moments of the pixel offset about the Gaussian centre, weighted by s = G * dL_dalpha
             const float sw = G[s] * dL_dalpha;
             const float sx = sw * dx, sy = sw * dy[s];
@@ -252,6 +252,12 @@ render_bwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
             const float dG_ddely = -gdy * bb.x - gdx * a.w;
             v[I_MEAN + 0] += dL_dG * dG_ddelx * ddelx_dx;
             v[I_MEAN + 1] += dL_dG * dG_ddely * ddely_dy;
+            if (GEOM) {
+              v[I_CONIC + 0] += -0.5f * gdx * dx * dL_dG;
+              v[I_CONIC + 1] += -0.5f * gdx * dy[s] * dL_dG;
+              v[I_CONIC + 2] += -0.5f * gdy * dy[s] * dL_dG;
+              v[I_OPAC] += G[s] * dL_dalpha;
+            }
           }
         }
       }

@@ -362,7 +362,8 @@ def debug_arrays(state) -> Dict[str, torch.Tensor]:
         sc = state["scratch"]
         # (the unsorted keys are overwritten by the sort's ping-pong; the sorted keys are the same multiset)
         keys = torch.empty((R,), dtype=torch.int64, device=sc.device)
-        rc = lib.lsr_debug_sorted_keys(_ptr(sc), P, cap, R, _ptr(keys),
+        out["depth_order"] = view(sc, L.ARR_SCR_DEPTH_ORDER, torch.int32, P)
+        rc = lib.lsr_debug_sorted_keys(_ptr(sc), _ptr(geom), P, cap, R, _ptr(keys),
                                        ctypes.c_void_p(torch.cuda.current_stream(sc.device).cuda_stream))
         _check(rc, "lsr_debug_sorted_keys")
         out["keys"] = keys
