@@ -217,6 +217,8 @@ render_bwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
         if (cmask[s] == 0u) continue;  // warp-uniform
         if (contrib[s]) {
           const float one_m_alpha = __fadd_rn(1.f, -alpha[s]);
+          // (an IEEE division here, as the reference's T = T / (1 - alpha), was measured: the gradients' distance to
+          // the reference does not change — it is set by the reference's own run-to-run atomic-order noise)
           const float rcp = __fdividef(1.f, one_m_alpha);
           T[s] *= rcp;
           const float w = alpha[s] * T[s];  // d(channel)/d(colour)
