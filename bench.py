@@ -499,7 +499,7 @@ def main():
         try:
             tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
             if args.config == 2 and args.P is None:
-                names_k = {"sort": "onesweep_kernel"}
+                names_k = {"sort": "onesweep_kernel_instances", "depth_order": "onesweep_kernel_depth_order"}
                 traffic = {k: tj.get(names_k.get(k, k + "_kernel"), {}).get("dram_bytes_per_launch") for k in table}
                 for k, e in table.items():
                     if traffic.get(k):
