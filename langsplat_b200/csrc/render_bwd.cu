@@ -164,6 +164,9 @@ render_bwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
   // back to front: the batch starting at `top` covers forward indices top-lane, top = eff_len-1 downwards
   // (backward.cu:486-498)
   const uint32_t smA = smem_u32(&sm.A[0]);
+  // reduction scratch: lane l stores into column l, then reads 16 floats of row min(l & 15, NV-1), half l >> 4
+  const uint32_t red_st = smem_u32(s_red) + (uint32_t)lane * 4u;
+  const uint32_t red_ld = smem_u32(s_red) + (uint32_t)((min(lane & 15, NV - 1) * RED_ROW + (lane >> 4) * 16) * 4);
   Fetched nxt = fetch_instance(list, rec, range.x, eff_len - 1 - lane);
   for (int top = eff_len - 1; top >= 0; top -= 32) {
     __syncwarp();  // everyone has left the previous batch
@@ -219,7 +222,7 @@ render_bwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
           const float one_m_alpha = __fadd_rn(1.f, -alpha[s]);
           // (an IEEE division here, as the reference's T = T / (1 - alpha), was measured: the gradients' distance to
           // the reference does not change — it is set by the reference's own run-to-run atomic-order noise)
-          const float rcp = __fdividef(1.f, one_m_alpha);
+          const float rcp = rcp_ftz(one_m_alpha);  // 1 - alpha is in [0.01, 1]
           T[s] *= rcp;
           const float w = alpha[s] * T[s];  // d(channel)/d(colour)
           float cd = 0.f;                   // colour . dL_dpixel over all blended channels
@@ -287,11 +290,9 @@ render_bwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
       } else {
         if constexpr (SMEM_REDUCE) {
 #pragma unroll
-          for (int k = 0; k < NV; k++) s_red[k * RED_ROW + lane] = v[k];
+          for (int k = 0; k < NV; k++) sts32(red_st + (uint32_t)(k * RED_ROW * 4), v[k]);
           __syncwarp();
-          const int row = min(lane & 15, NV - 1);
-          const float4* rp = reinterpret_cast<const float4*>(s_red + row * RED_ROW + (lane >> 4) * 16);
-          const float4 r0 = rp[0], r1 = rp[1], r2 = rp[2], r3 = rp[3];
+          const float4 r0 = lds128(red_ld), r1 = lds128(red_ld + 16), r2 = lds128(red_ld + 32), r3 = lds128(red_ld + 48);
           float t = ((r0.x + r0.y) + (r0.z + r0.w)) + ((r1.x + r1.y) + (r1.z + r1.w)) +
                     (((r2.x + r2.y) + (r2.z + r2.w)) + ((r3.x + r3.y) + (r3.z + r3.w)));
           t += __shfl_xor_sync(0xffffffffu, t, 16);
