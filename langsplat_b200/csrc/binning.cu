@@ -28,21 +28,34 @@ depth_words_kernel(int P, const float* __restrict__ depths, const uint32_t* __re
   const int tid = threadIdx.x, lane = tid & 31;
   for (int j = tid; j < passes * SORT_BINS; j += DW_THREADS) s_hist[j] = 0;
   __syncthreads();
-  const int n_round = (P + 31) & ~31;  // keep warps converged for match.any
-  for (int idx = blockIdx.x * DW_THREADS + tid; idx < n_round; idx += gridDim.x * DW_THREADS) {
-    const bool ok = idx < P;
-    uint32_t d = 0;
-    if (ok && tiles[idx] != 0u) d = __float_as_uint(depths[idx]) - lo_min;
-    if (ok) words[idx] = ((uint64_t)d << id_bits) | (uint64_t)(uint32_t)idx;
-    for (int p = 0; p < passes; p++) {
-      const int shift = p * SORT_RADIX_BITS;
-      const int bits = min(SORT_RADIX_BITS, total_bits - shift);
-      const uint32_t dg = (d >> shift) & ((1u << bits) - 1);
-      if (p + 1 < passes) {
-        if (ok) atomicAdd(&s_hist[p * SORT_BINS + dg], 1u);
-      } else {
-        const uint32_t peers = __match_any_sync(0xffffffffu, ok ? dg : 0xffffffffu);
-        if (ok && (peers & ((1u << lane) - 1)) == 0) atomicAdd(&s_hist[p * SORT_BINS + dg], (uint32_t)__popc(peers));
+  // four elements per thread and iteration, all eight loads issued before the first use
+  constexpr int DW_ITEMS = 4;
+  const int stride = gridDim.x * DW_THREADS * DW_ITEMS;
+  for (int base = blockIdx.x * DW_THREADS * DW_ITEMS; base < P; base += stride) {  // CTA-uniform trip count
+    uint32_t t[DW_ITEMS], db[DW_ITEMS];
+#pragma unroll
+    for (int i = 0; i < DW_ITEMS; i++) {
+      const int idx = base + i * DW_THREADS + tid;
+      t[i] = idx < P ? __ldg(tiles + idx) : 0u;
+      db[i] = idx < P ? __float_as_uint(__ldg(depths + idx)) : 0u;  // stale for culled Gaussians: masked by t == 0
+    }
+#pragma unroll
+    for (int i = 0; i < DW_ITEMS; i++) {
+      const int idx = base + i * DW_THREADS + tid;
+      const bool ok = idx < P;
+      const uint32_t d = t[i] != 0u ? db[i] - lo_min : 0u;
+      if (ok) words[idx] = ((uint64_t)d << id_bits) | (uint64_t)(uint32_t)idx;
+      for (int p = 0; p < passes; p++) {
+        const int shift = p * SORT_RADIX_BITS;
+        const int bits = min(SORT_RADIX_BITS, total_bits - shift);
+        const uint32_t dg = (d >> shift) & ((1u << bits) - 1);
+        if (p + 1 < passes) {
+          if (ok) atomicAdd(&s_hist[p * SORT_BINS + dg], 1u);
+        } else {
+          const uint32_t peers = __match_any_sync(0xffffffffu, ok ? dg : 0xffffffffu);
+          if (ok && (peers & ((1u << lane) - 1)) == 0)
+            atomicAdd(&s_hist[p * SORT_BINS + dg], (uint32_t)__popc(peers));
+        }
       }
     }
   }
@@ -294,7 +307,7 @@ void launch_depth_words(int P, const float* depths, const uint32_t* tiles, const
                         uint32_t* ghist, cudaStream_t s) {
   if (P <= 0) return;
   const int nblocks = (P + DW_THREADS * 4 - 1) / (DW_THREADS * 4);
-  const int grid = nblocks < 148 * 2 ? nblocks : 148 * 2;  // few persistent CTAs: each flushes passes*256 global atomics
+  const int grid = nblocks < 148 * 4 ? nblocks : 148 * 4;  // persistent CTAs: each flushes passes*256 global atomics
   depth_words_kernel<<<grid, DW_THREADS, 0, s>>>(P, depths, tiles, plan.lo_min, plan.id_bits, plan.passes,
                                                  plan.total_bits, words, ghist);
   count_launch();
