@@ -116,27 +116,6 @@ __device__ __forceinline__ float3 sh_dir_backward(int deg, const float* sh, floa
   return sh_backward_t<false>(deg, 16, sh, dir_orig, make_float3(g[0], g[1], g[2]), nullptr);
 }
 
-// SH basis values b[k] with dRGB/dsh[k][ch] = b[k] * dL_dRGB[ch]; zero above the active degree (backward.cu:36-129).
-__device__ __forceinline__ void sh_basis(int deg, float x, float y, float z, float (&b)[16]) {
-#pragma unroll
-  for (int k = 0; k < 16; k++) b[k] = 0.f;
-  b[0] = LSR_SH_C0;
-  if (deg > 0) {
-    b[1] = -LSR_SH_C1 * y; b[2] = LSR_SH_C1 * z; b[3] = -LSR_SH_C1 * x;
-    if (deg > 1) {
-      const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
-      b[4] = LSR_SH_C2_0 * xy; b[5] = LSR_SH_C2_1 * yz; b[6] = LSR_SH_C2_2 * (2.f * zz - xx - yy);
-      b[7] = LSR_SH_C2_3 * xz; b[8] = LSR_SH_C2_4 * (xx - yy);
-      if (deg > 2) {
-        b[9] = LSR_SH_C3_0 * y * (3.f * xx - yy); b[10] = LSR_SH_C3_1 * xy * z;
-        b[11] = LSR_SH_C3_2 * y * (4.f * zz - xx - yy); b[12] = LSR_SH_C3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy);
-        b[13] = LSR_SH_C3_4 * x * (4.f * zz - xx - yy); b[14] = LSR_SH_C3_5 * z * (xx - yy);
-        b[15] = LSR_SH_C3_6 * x * (xx - 3.f * yy);
-      }
-    }
-  }
-}
-
 constexpr int BPRE_THREADS = 256;
 constexpr int SH_ROW = 12;
 constexpr int BPRE_WARP_F4 = 32 * (SH_ROW + 1) + 48;  // per warp: 32 padded SH rows + 32 cov3D rows (24 B each)

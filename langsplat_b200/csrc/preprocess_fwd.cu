@@ -49,8 +49,16 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, const float* __restrict__ s
 constexpr int SH_ROW = 12;  // float4 chunks per [16,3] SH row
 constexpr size_t PRE_SH_SMEM = (size_t)(PRE_THREADS / 32) * 32 * (SH_ROW + 1) * sizeof(float4);
 
+// LSR_PRE_STAGE_ALL = 1 also stages scales / language features through shared memory (6 KB more per CTA: 3 CTAs per
+// SM); 0 reads those two 12-byte triplets directly (a warp's 384 contiguous bytes) and fits 4 CTAs per SM.
+#ifndef LSR_PRE_STAGE_ALL
+#define LSR_PRE_STAGE_ALL 0
+#endif
+#ifndef LSR_PRE_MINB
+#define LSR_PRE_MINB 4
+#endif
 template <bool SH16>
-__global__ void __launch_bounds__(PRE_THREADS)
+__global__ void __launch_bounds__(PRE_THREADS, LSR_PRE_MINB)
 preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, const float* __restrict__ scales,
                       float scale_modifier, const float* __restrict__ rotations, const float* __restrict__ opacities,
                       const float* __restrict__ shs, const float* __restrict__ cov3D_precomp,
@@ -62,8 +70,10 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
                       uint8_t* __restrict__ clamped, uint32_t* __restrict__ ctrl) {
   extern __shared__ __align__(16) float4 s_dyn[];  // per warp: 32 padded SH rows; reused to stage rec / cov3D
   __shared__ __align__(16) float s_xyz[PRE_THREADS * 3];
+#if LSR_PRE_STAGE_ALL
   __shared__ __align__(16) float s_scl[PRE_THREADS * 3];
   __shared__ __align__(16) float s_lng[PRE_THREADS * 3];
+#endif
   __shared__ float s_view[16], s_proj[16], s_cam[3];
   __shared__ uint32_t s_negmin, s_max, s_tiles;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -76,8 +86,10 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   if (tid < 3) s_cam[tid] = campos[tid];
   if (tid == 0) { s_negmin = 0u; s_max = 0u; s_tiles = 0u; }
   stage_flat_async<PRE_THREADS>(means3D, s_xyz, (size_t)first * 3, count * 3, tid);
+#if LSR_PRE_STAGE_ALL
   if (scales) stage_flat_async<PRE_THREADS>(scales, s_scl, (size_t)first * 3, count * 3, tid);
   if (lang) stage_flat_async<PRE_THREADS>(lang, s_lng, (size_t)first * 3, count * 3, tid);
+#endif
   cp_async_commit();
   cp_async_wait<0>();
   __syncthreads();
@@ -85,6 +97,12 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   const int idx = first + tid;
   const float mx = valid ? s_xyz[3 * tid] : 0.f, my = valid ? s_xyz[3 * tid + 1] : 0.f,
               mz = valid ? s_xyz[3 * tid + 2] : 0.f;
+#if !LSR_PRE_STAGE_ALL
+  float sc0 = 0.f, sc1 = 0.f, sc2 = 0.f;  // requested now, used after the projection arithmetic
+  if (valid && scales) {
+    sc0 = __ldg(scales + 3 * (size_t)idx); sc1 = __ldg(scales + 3 * (size_t)idx + 1); sc2 = __ldg(scales + 3 * (size_t)idx + 2);
+  }
+#endif
   float4* wsm = s_dyn + (size_t)warp * 32 * (SH_ROW + 1);
   // Speculative prefetch of the SH rows (cp.async), so that they fly during the projection arithmetic below: a
   // Gaussian in front of the camera whose centre projects inside the image (plus a 16-pixel band) is almost surely
@@ -127,8 +145,12 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
       for (int i = 0; i < 6; i++) cov3D[i] = __ldg(cov3D_precomp + (size_t)idx * 6 + i);
     } else {
       const float4 q = __ldg(reinterpret_cast<const float4*>(rotations) + idx);
+#if LSR_PRE_STAGE_ALL
       compute_cov3D(s_scl[3 * tid], s_scl[3 * tid + 1], s_scl[3 * tid + 2], scale_modifier, q.x, q.y, q.z, q.w,
                     cov3D);
+#else
+      compute_cov3D(sc0, sc1, sc2, scale_modifier, q.x, q.y, q.z, q.w, cov3D);
+#endif
     }
     Cov2D c2;
     compute_cov2D(mx, my, mz, focal_x, focal_y, tan_fovx, tan_fovy, cov3D, s_view, c2);
@@ -168,13 +190,23 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
       const float len = sqrtf(dx * dx + dy * dy + dz * dz);
       dx = dx / len; dy = dy / len; dz = dz / len;
       if (SH16) {
-        float v[48];
+        // RGB[ch] = sum_k basis[k] * sh[k][ch] + 0.5, coefficients consumed straight from the staged row (the terms of
+        // each channel in the reference's order, forward.cu:31-68), so the 48 floats never sit in registers
+        float bs[16];
+        sh_basis(D, dx, dy, dz, bs);
+        const int nfl = 3 * (D + 1) * (D + 1);  // floats of the row that belong to active coefficients
+        float acc[3] = {0.f, 0.f, 0.f};
 #pragma unroll
         for (int i = 0; i < SH_ROW; i++) {
           const float4 t = wsm[row_slot<SH_ROW>(lane, i)];
-          v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+          const float e[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+          for (int j = 0; j < 4; j++) {
+            const int f = 4 * i + j;
+            if (f < nfl) acc[f % 3] = f < 3 ? bs[0] * e[j] : acc[f % 3] + bs[f / 3] * e[j];
+          }
         }
-        col = sh_to_rgb(D, v, dx, dy, dz, 3);
+        col = make_float3(acc[0] + 0.5f, acc[1] + 0.5f, acc[2] + 0.5f);
       } else {
         col = sh_to_rgb(D, shs + (size_t)idx * M * 3, dx, dy, dz, 3);
       }
@@ -191,7 +223,11 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   // ---- outputs: the 48-byte records and cov3D go out through shared memory as coalesced 16-byte chunks ----
   if (vis) {
     float f0 = 0.f, f1 = 0.f, f2 = 0.f;
+#if LSR_PRE_STAGE_ALL
     if (lang) { f0 = s_lng[3 * tid]; f1 = s_lng[3 * tid + 1]; f2 = s_lng[3 * tid + 2]; }
+#else
+    if (lang) { f0 = __ldg(lang + 3 * (size_t)idx); f1 = __ldg(lang + 3 * (size_t)idx + 1); f2 = __ldg(lang + 3 * (size_t)idx + 2); }
+#endif
     wsm[row_slot<3>(lane, 0)] = make_float4(px, py, conx, cony);
     wsm[row_slot<3>(lane, 1)] = make_float4(conz, __ldg(opacities + idx), col.x, col.y);
     wsm[row_slot<3>(lane, 2)] = make_float4(col.z, f0, f1, f2);
