@@ -224,7 +224,10 @@ def main():
     W, H = cam.image_width, cam.image_height
     P = scene["means3D"].shape[0]
     metric = METRICS.get(cfg, METRIC)
-    what = ("language-feature-only fwd+bwd" if feature_only else "forward only, 3 feature levels" if fwd_only
+    what = ("language-feature-only fwd+bwd" if feature_only else
+            ("forward only, 3 feature levels" + (" (ours: one preprocess + binning shared by the levels, "
+                                                 "forward_feature_levels)" if args.impl == "ours" else ""))
+            if fwd_only
             else "fwd+bwd")
     workload = (f"config{cfg}: {P} Gaussians, {W}x{H}, SH deg 3 + 3-ch language feature, {what}, "
                 + (f"8 camera views per step over {world} GPU(s)" if cfg == 4 else "one camera view per GPU per step")
@@ -269,8 +272,13 @@ def main():
     def step():
         if fwd_only:
             with torch.no_grad():
-                for lang in levels:
-                    forward(lang=lang)
+                if args.impl == "ours":  # the three levels share the geometry: preprocess + binning once
+                    rast.forward_feature_levels(means3D=params["means3D"], opacities=params["opacities"],
+                                                language_features=levels, shs=params["shs"], scales=params["scales"],
+                                                rotations=params["rotations"])
+                else:
+                    for lang in levels:
+                        forward(lang=lang)
             return
         for p in params.values():
             p.grad = None
@@ -329,9 +337,16 @@ def main():
         if fwd_only:
             with torch.no_grad():
                 acc = None
-                for lang in levels:
-                    color, feat, radii = forward(GR(raster_settings=rs2), lang)
-                    acc = feat.mean() if acc is None else acc + feat.mean()
+                if args.impl == "ours":
+                    color, feats, radii = GR(raster_settings=rs2).forward_feature_levels(
+                        means3D=params["means3D"], opacities=params["opacities"], language_features=levels,
+                        shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
+                    for feat in feats:
+                        acc = feat.mean() if acc is None else acc + feat.mean()
+                else:
+                    for lang in levels:
+                        color, feat, radii = forward(GR(raster_settings=rs2), lang)
+                        acc = feat.mean() if acc is None else acc + feat.mean()
             main.wait_event(gt_ready)
             return float((acc + (feat - gt_f).abs().mean()).item())
         color, feat, radii = GR(raster_settings=rs2)(

@@ -127,6 +127,16 @@ int lsr_forward(const lsr_frame* frame, const lsr_inputs* in, float* out_color, 
                 void* geom, void* image, void* list, int64_t list_capacity, void* scratch, size_t scratch_bytes,
                 int64_t* num_rendered, void* stream);
 
+/* Another feature level on the same geometry (LangSplat's three SAM levels share every Gaussian
+ * attribute except language_feature, and render.py renders them back to back).  Takes the saved state of an
+ * lsr_forward made with include_feature, replaces the language feature held in its per-Gaussian records by
+ * `language_feature` [P,3] and re-blends the feature image only — no preprocess, no binning, no RGB.
+ * out_feature [3,H,W] is fully written and equals what a full lsr_forward with that feature tensor would produce.
+ * Afterwards the state describes the new level. */
+int lsr_forward_feature_level(int32_t P, int32_t width, int32_t height, const int32_t* radii, void* geom,
+                              const void* image, const void* list, const float* language_feature, float* out_feature,
+                              void* stream);
+
 /* Backward.  Replaces _C.rasterize_gaussians_backward -> RasterizeGaussiansBackwardCUDA
  * (RAST/rasterize_points.cu:129-224) -> Rasterizer::backward (rasterizer_impl.cu:359-463).
  * dL_dcolor / dL_dfeature are [3,H,W]; dL_dcolor may be null (treated as zero, as in feature-only training);

@@ -53,6 +53,8 @@ EXPORTS = {
     "lsr_array_offset": (c_size_t, [c_int, c_int32, c_int32, c_int32, c_int64]),
     "lsr_forward": (c_int, [POINTER(Frame), POINTER(Inputs), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                             c_void_p, c_int64, c_void_p, c_size_t, POINTER(c_int64), c_void_p]),
+    "lsr_forward_feature_level": (c_int, [c_int32, c_int32, c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                          c_void_p, c_void_p]),
     "lsr_backward": (c_int, [POINTER(Frame), POINTER(Inputs), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                              c_void_p, c_uint32, POINTER(Grads), c_void_p]),
     "lsr_mark_visible": (c_int, [c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -327,6 +327,25 @@ int lsr_forward(const lsr_frame* frame, const lsr_inputs* in, float* out_color, 
   return LSR_OK;
 }
 
+int lsr_forward_feature_level(int32_t P, int32_t width, int32_t height, const int32_t* radii, void* geom,
+                              const void* image, const void* list, const float* language_feature, float* out_feature,
+                              void* stream) {
+  if (P < 0 || width < 0 || height < 0) return fail(LSR_ERR_INVALID, "negative size");
+  if (!image || !out_feature) return fail(LSR_ERR_INVALID, "null image / out_feature");
+  if (P > 0 && (!radii || !geom || !language_feature)) return fail(LSR_ERR_INVALID, "null radii / geom / feature");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (P == 0) {  // as lsr_forward: an empty scene gives zero images (rasterize_points.cu:91)
+    LSR_CUDA(cudaMemsetAsync(out_feature, 0, 3 * (size_t)width * height * sizeof(float), s));
+    return LSR_OK;
+  }
+  GeomView g = geom_view(geom, P);
+  ImageView img = image_view(const_cast<void*>(image), width, height);
+  launch_refeature_render(P, width, height, radii, language_feature, g.rec, img.ranges, (const uint32_t*)list,
+                          out_feature, s);
+  LSR_CUDA(cudaGetLastError());
+  return LSR_OK;
+}
+
 int lsr_backward(const lsr_frame* frame, const lsr_inputs* in, const int32_t* radii, const void* geom,
                  const void* image, const void* list, const float* dL_dcolor, const float* dL_dfeature,
                  uint32_t need_mask, const lsr_grads* grads, void* stream) {

@@ -187,6 +187,9 @@ int sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_
 void launch_render_fwd(int W, int H, const uint2* ranges, const uint32_t* list, const GeomRec* rec, const float* bg,
                        bool include_feature, float* final_T, uint32_t* n_contrib, float* out_color,
                        float* out_feature, cudaStream_t s);
+// feature-only re-blend of an already binned frame with another [P,3] language feature (records updated in place)
+void launch_refeature_render(int P, int W, int H, const int32_t* radii, const float* lang, GeomRec* rec,
+                             const uint2* ranges, const uint32_t* list, float* out_feature, cudaStream_t s);
 void launch_render_bwd(int W, int H, const uint2* ranges, const uint32_t* list, const GeomRec* rec, const float* bg,
                        bool include_feature, const float* final_T, const uint32_t* n_contrib, const float* dL_dcolor,
                        const float* dL_dfeature, uint32_t need_mask, float* dL_dmean2D, float* dL_dconic,

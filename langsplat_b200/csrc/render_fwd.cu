@@ -20,7 +20,9 @@ namespace {
 
 constexpr int FWD_SLOTS = BLEND_SLOTS;
 
-template <bool FEAT>
+// COLOR = false: feature-only re-blend of a frame whose geometry is already binned (lsr_forward_feature_level): the
+// same walk and the same decisions, but no RGB accumulation and no colour / final_T / n_contrib stores.
+template <bool FEAT, bool COLOR>
 __global__ void __launch_bounds__(32)
 render_fwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, const uint32_t* __restrict__ list,
                   const GeomRec* __restrict__ rec, const float* __restrict__ bg, float* __restrict__ final_T,
@@ -95,9 +97,11 @@ render_fwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
           lim[s] = kDone;  // done (forward.cu:353-357)
           continue;
         }
-        C[s][0] = __fmaf_rn(T[s], __fmul_rn(c.x, alpha), C[s][0]);
-        C[s][1] = __fmaf_rn(T[s], __fmul_rn(c.y, alpha), C[s][1]);
-        C[s][2] = __fmaf_rn(T[s], __fmul_rn(c.z, alpha), C[s][2]);
+        if (COLOR) {
+          C[s][0] = __fmaf_rn(T[s], __fmul_rn(c.x, alpha), C[s][0]);
+          C[s][1] = __fmaf_rn(T[s], __fmul_rn(c.y, alpha), C[s][1]);
+          C[s][2] = __fmaf_rn(T[s], __fmul_rn(c.z, alpha), C[s][2]);
+        }
         if (FEAT) {
           F[s][0] = __fmaf_rn(T[s], __fmul_rn(c.w, alpha), F[s][0]);
           F[s][1] = __fmaf_rn(T[s], __fmul_rn(d.x, alpha), F[s][1]);
@@ -113,17 +117,30 @@ render_fwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
   for (int s = 0; s < FWD_SLOTS; s++) {
     if (!inside[s]) continue;
     const size_t pix = (size_t)(py0 + 4 * s) * W + px;
-    final_T[pix] = T[s];
-    n_contrib[pix] = last_contributor[s];
-    out_color[pix] = __fmaf_rn(T[s], __ldg(bg), C[s][0]);
-    out_color[N + pix] = __fmaf_rn(T[s], __ldg(bg + 1), C[s][1]);
-    out_color[2 * N + pix] = __fmaf_rn(T[s], __ldg(bg + 2), C[s][2]);
+    if (COLOR) {
+      final_T[pix] = T[s];
+      n_contrib[pix] = last_contributor[s];
+      out_color[pix] = __fmaf_rn(T[s], __ldg(bg), C[s][0]);
+      out_color[N + pix] = __fmaf_rn(T[s], __ldg(bg + 1), C[s][1]);
+      out_color[2 * N + pix] = __fmaf_rn(T[s], __ldg(bg + 2), C[s][2]);
+    }
     if (FEAT) {
       out_feature[pix] = F[s][0];  // no background term for the feature image (forward.cu:388)
       out_feature[N + pix] = F[s][1];
       out_feature[2 * N + pix] = F[s][2];
     }
   }
+}
+
+
+// language feature of every visible Gaussian's record replaced by `lang` [P,3]
+__global__ void __launch_bounds__(256)
+refeature_kernel(int P, const int32_t* __restrict__ radii, const float* __restrict__ lang, GeomRec* __restrict__ rec) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P || radii[idx] <= 0) return;
+  rec[idx].f0 = __ldg(lang + 3 * (size_t)idx);
+  rec[idx].f1 = __ldg(lang + 3 * (size_t)idx + 1);
+  rec[idx].f2 = __ldg(lang + 3 * (size_t)idx + 2);
 }
 
 }  // namespace
@@ -135,11 +152,25 @@ void launch_render_fwd(int W, int H, const uint2* ranges, const uint32_t* list, 
   if (tiles_x == 0 || tiles_y == 0) return;
   const unsigned grid = (unsigned)tiles_x * (unsigned)tiles_y * QUADS;
   if (include_feature)
-    render_fwd_kernel<true><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, list, rec, bg, final_T, n_contrib, out_color,
-                                                out_feature);
+    render_fwd_kernel<true, true><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, list, rec, bg, final_T, n_contrib,
+                                                      out_color, out_feature);
   else
-    render_fwd_kernel<false><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, list, rec, bg, final_T, n_contrib, out_color,
-                                                 out_feature);
+    render_fwd_kernel<false, true><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, list, rec, bg, final_T, n_contrib,
+                                                       out_color, out_feature);
+  count_launch();
+}
+
+void launch_refeature_render(int P, int W, int H, const int32_t* radii, const float* lang, GeomRec* rec,
+                             const uint2* ranges, const uint32_t* list, float* out_feature, cudaStream_t s) {
+  const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
+  if (P > 0) {
+    refeature_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, radii, lang, rec);
+    count_launch();
+  }
+  if (tiles_x == 0 || tiles_y == 0) return;
+  const unsigned grid = (unsigned)tiles_x * (unsigned)tiles_y * QUADS;
+  render_fwd_kernel<true, false><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, list, rec, nullptr, nullptr, nullptr,
+                                                     nullptr, out_feature);
   count_launch();
 }
 

@@ -333,6 +333,45 @@ class GaussianRasterizer(nn.Module):  # RAST/diff_gaussian_rasterization/__init_
                                    rotations, cov3D_precomp, raster_settings)
 
 
+    def forward_feature_levels(self, means3D, opacities, language_features, shs=None, colors_precomp=None,
+                               scales=None, rotations=None, cov3D_precomp=None):
+        """Render several language-feature levels of the SAME geometry in one go (inference only, no autograd):
+        `language_features` is a sequence of [P,3] tensors.  LangSplat trains its three SAM levels on frozen geometry,
+        and render.py / process.sh render them back to back (render.py:35-52, process.sh:19-32); here the preprocess
+        and the binning run once and every further level costs one feature-only blend (lsr_forward_feature_level).
+        Returns (color, [feature image per level], radii); each feature image equals what a separate `forward` call
+        with that level would return.  Extension over the reference surface."""
+        rs = self.raster_settings
+        if not rs.include_feature:
+            raise LsrError("forward_feature_levels needs raster_settings.include_feature=True")
+        levels = list(language_features)
+        if not levels:
+            raise LsrError("forward_feature_levels needs at least one language feature tensor")
+        if (shs is None) == (colors_precomp is None):
+            raise Exception(_MSG_COLORS)
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or (
+                (scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception(_MSG_COV)
+        lib = L.load()
+        with torch.no_grad():
+            color, feat0, radii, state = _forward_impl(rs, means3D, shs, colors_precomp, levels[0], opacities, scales,
+                                                       rotations, cov3D_precomp)
+            feats = [feat0]
+            device, P, W, H = state["device"], state["P"], state["W"], state["H"]
+            stream = ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+            for lang in levels[1:]:
+                lang = _prep(lang, device)
+                if lang is None or lang.numel() != P * 3:
+                    raise LsrError("every language feature level must have shape (num_points, 3)")
+                out = torch.empty((3, H, W), dtype=torch.float32, device=device)
+                with torch.cuda.device(device):
+                    rc = lib.lsr_forward_feature_level(P, W, H, _ptr(radii), _ptr(state["geom"]), _ptr(state["image"]),
+                                                       _ptr(state["point_list"]), _ptr(lang), _ptr(out), stream)
+                _check(rc, "lsr_forward_feature_level")
+                feats.append(out)
+        return color, feats, radii
+
+
 # ---- test / bench helpers (not part of the reference surface) ----
 def debug_arrays(state) -> Dict[str, torch.Tensor]:
     """Typed views of the arrays inside a forward's geom / image / scratch buffers (include/lsr_api.h LSR_ARR_*)."""
