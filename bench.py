@@ -307,19 +307,20 @@ def main():
         def l1_loss(x, gt):
             return torch.abs(x - gt).mean()
 
-    # Ground-truth prefetch, as a data loader does it: every step copies ONE view's ground truth (49.8 MB) from pinned
-    # host memory on a side stream; the copy issued in step k is consumed by step k+1, so it overlaps step k's
-    # backward as well as its forward.  The copy of step k's own camera matrices stays in line.  All inside the timed
-    # region, same code for both arms.
+    # View prefetch, as a data loader does it: every step copies ONE view (camera matrices + 49.8 MB of ground truth)
+    # from pinned host memory on a side stream; the copy issued in step k is consumed by step k+1, so it overlaps
+    # step k's forward and backward.  All inside the timed region, same code for both arms.
     pending = {}
 
     def issue_gt_copy():
         # fresh buffers from the caching allocator (stream-aware: a block is reused only after its recorded uses end)
         with torch.cuda.stream(copy_stream):
             gt_c, gt_f = gt_c_h.to(dev, non_blocking=True), gt_f_h.to(dev, non_blocking=True)
+            cam_d = (view_h.to(dev, non_blocking=True), proj_h.to(dev, non_blocking=True),
+                     cam_h.to(dev, non_blocking=True))  # the view's camera travels with its ground truth
             ev = torch.cuda.Event()
             ev.record(copy_stream)
-        pending["gt"] = (gt_c, gt_f, ev)
+        pending["gt"] = (gt_c, gt_f, cam_d, ev)
 
     def e2e_step():
         for p in params.values():
@@ -328,12 +329,12 @@ def main():
         main = torch.cuda.current_stream(dev)
         if "gt" not in pending:
             issue_gt_copy()  # first step only: nothing was prefetched yet
-        gt_c, gt_f, gt_ready = pending.pop("gt")
-        gt_c.record_stream(main)
-        gt_f.record_stream(main)
-        issue_gt_copy()  # next step's ground truth: overlaps this step's forward and backward
-        rs2 = rs._replace(viewmatrix=view_h.to(dev, non_blocking=True), projmatrix=proj_h.to(dev, non_blocking=True),
-                          campos=cam_h.to(dev, non_blocking=True))
+        gt_c, gt_f, cam_d, gt_ready = pending.pop("gt")
+        for t in (gt_c, gt_f) + cam_d:
+            t.record_stream(main)
+        issue_gt_copy()  # next step's view (camera + ground truth): overlaps this step's forward and backward
+        main.wait_event(gt_ready)  # this step's view was copied during the previous step
+        rs2 = rs._replace(viewmatrix=cam_d[0], projmatrix=cam_d[1], campos=cam_d[2])
         if fwd_only:
             with torch.no_grad():
                 acc = None
@@ -347,13 +348,11 @@ def main():
                     for lang in levels:
                         color, feat, radii = forward(GR(raster_settings=rs2), lang)
                         acc = feat.mean() if acc is None else acc + feat.mean()
-            main.wait_event(gt_ready)
             return float((acc + (feat - gt_f).abs().mean()).item())
         color, feat, radii = GR(raster_settings=rs2)(
             means3D=params["means3D"], means2D=means2D, shs=params["shs"],
             language_feature_precomp=params["language_feature"], opacities=params["opacities"],
             scales=params["scales"], rotations=params["rotations"])
-        main.wait_event(gt_ready)
         if feature_only:
             loss = l1_loss(feat, gt_f)
         else:
@@ -439,9 +438,9 @@ def main():
             "e2e": {"value": (world * (len(levels) if fwd_only else 1)) * args.steps / (e2e_ms_total / 1000.0),
                     "unit": "frames/s",
                     "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4,
-                    "what": "per step: camera matrices + one view's GT colour/feature images (49.8 MB) copied from "
-                            "pinned host memory (GT on a side stream, prefetched one step ahead like a data "
-                            "loader), L1 loss (ours: fused langsplat_b200.l1_loss; reference: torch.abs(x-gt).mean()"
+                    "what": "per step: one view (camera matrices + GT colour/feature images, 49.8 MB) copied from "
+                            "pinned host memory on a side stream, prefetched one step ahead like a data "
+                            "loader, L1 loss (ours: fused langsplat_b200.l1_loss; reference: torch.abs(x-gt).mean()"
                             "), backward, loss.item()"},
             "gpu_launches": launches}
     if args.impl == "reference":
