@@ -59,6 +59,8 @@ def parse_args():
     ap.add_argument("--width", type=int, default=None)
     ap.add_argument("--height", type=int, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--dense-sh-exchange", action="store_true",
+                    help="multi-view / multi-GPU: all-reduce dL_dsh itself instead of its per-view factors (A/B)")
     ap.add_argument("--cpu-frames", type=int, default=3)
     return ap.parse_args()
 
@@ -264,6 +266,24 @@ def main():
                            language_feature_precomp=params["language_feature"] if lang is None else lang,
                            opacities=params["opacities"], scales=params["scales"], rotations=params["rotations"])
 
+    # Our arm, when a step sums several views (config 4) or several ranks: the SH gradient travels and accumulates as
+    # its per-view rank-1 factor (12 B per Gaussian and view) and is formed once per step (langsplat_b200.dist).
+    factored = (args.impl == "ours" and not fwd_only and not feature_only and not args.dense_sh_exchange
+                and (world > 1 or len(my_views) > 1))
+    if factored:
+        from langsplat_b200.dist import factored_sh_gradients, finish_sh_gradients
+
+    def backward_and_reduce(run_views):
+        """run_views() runs forward+backward of this rank's views; afterwards every rank holds the summed gradients."""
+        if not factored:
+            run_views()
+            reduce_grads()
+            return
+        with factored_sh_gradients() as factors:
+            run_views()
+        reduce_grads()  # everything but the SH gradient (absent from .grad in this mode)
+        params["shs"].grad = finish_sh_gradients(factors, params["means3D"], params["shs"].shape[1])
+
     def reduce_grads():
         if world > 1:
             from langsplat_b200.dist import allreduce_gradients
@@ -283,13 +303,15 @@ def main():
         for p in params.values():
             p.grad = None
         means2D.grad = None
-        for r in rasts:  # gradients of this rank's views accumulate in .grad
-            color, feat, radii = forward(r)
-            if feature_only:
-                torch.autograd.backward([feat], [dfeat])
-            else:
-                torch.autograd.backward([color, feat], [dcol, dfeat])
-        reduce_grads()
+
+        def run_views():
+            for r in rasts:  # gradients of this rank's views accumulate in .grad
+                color, feat, radii = forward(r)
+                if feature_only:
+                    torch.autograd.backward([feat], [dfeat])
+                else:
+                    torch.autograd.backward([color, feat], [dcol, dfeat])
+        backward_and_reduce(run_views)
 
     # ---- host-buffer (end-to-end) step: camera + ground truth come from pinned host memory, loss goes back ----
     g = torch.Generator().manual_seed(77 + rank)
@@ -349,17 +371,21 @@ def main():
                         color, feat, radii = forward(GR(raster_settings=rs2), lang)
                         acc = feat.mean() if acc is None else acc + feat.mean()
             return float((acc + (feat - gt_f).abs().mean()).item())
-        color, feat, radii = GR(raster_settings=rs2)(
-            means3D=params["means3D"], means2D=means2D, shs=params["shs"],
-            language_feature_precomp=params["language_feature"], opacities=params["opacities"],
-            scales=params["scales"], rotations=params["rotations"])
-        if feature_only:
-            loss = l1_loss(feat, gt_f)
-        else:
-            loss = l1_loss(color, gt_c) + l1_loss(feat, gt_f)
-        loss.backward()
-        reduce_grads()
-        return float(loss.item())  # device -> host read of the step's result
+        out = {}
+
+        def run_view():
+            color, feat, radii = GR(raster_settings=rs2)(
+                means3D=params["means3D"], means2D=means2D, shs=params["shs"],
+                language_feature_precomp=params["language_feature"], opacities=params["opacities"],
+                scales=params["scales"], rotations=params["rotations"])
+            if feature_only:
+                loss = l1_loss(feat, gt_f)
+            else:
+                loss = l1_loss(color, gt_c) + l1_loss(feat, gt_f)
+            loss.backward()
+            out["loss"] = loss
+        backward_and_reduce(run_view)
+        return float(out["loss"].item())  # device -> host read of the step's result
 
     lib = None
     if args.impl == "ours":

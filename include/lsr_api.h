@@ -77,6 +77,9 @@ typedef struct lsr_grads {
   float* dL_drotations;         /* [P,4] */
   float* dL_dcov3D;             /* [P,6] */
   float* dL_dconic;             /* [P,4] (internal in the reference; exposed for tests) */
+  float* dL_dcolors_masked;     /* [P,3] optional: the SH gradient's per-view factor (dL_dcolor with the clamp mask of
+                                   backward.cu:31-34 applied, zero for culled Gaussians).  Given instead of dL_dsh it
+                                   makes lsr_backward skip the 16x larger dL_dsh; see lsr_sh_gradient_from_views */
 } lsr_grads;
 
 /* need_mask bits for lsr_backward: which groups of gradients the caller will read
@@ -145,6 +148,14 @@ int lsr_forward_feature_level(int32_t P, int32_t width, int32_t height, const in
 int lsr_backward(const lsr_frame* frame, const lsr_inputs* in, const int32_t* radii, const void* geom,
                  const void* image, const void* list, const float* dL_dcolor, const float* dL_dfeature,
                  uint32_t need_mask, const lsr_grads* grads, void* stream);
+
+/* dL_dsh from per-view factors (data-parallel / multi-view steps).  One view's SH gradient is rank-1 per Gaussian:
+ * dL_dsh[k][ch] = basis_k(normalize(mean - campos)) * g[ch] (RAST/cuda_rasterizer/backward.cu:36-129), with g that
+ * view's dL_dcolors_masked.  This sums V views: means3D [P,3], campos [V,3], g [V,P,3] -> dL_dsh [P,M,3] (fully
+ * written; rows above the active degree D are zero).  A view-sharded step exchanges the 12-byte factors (all-gather)
+ * instead of all-reducing the 192-byte products. */
+int lsr_sh_gradient_from_views(int32_t P, int32_t M, int32_t D, int32_t n_views, const float* means3D,
+                               const float* campos, const float* g, float* dL_dsh, void* stream);
 
 /* Replaces _C.mark_visible -> markVisible (rasterize_points.cu:226-245) -> checkFrustum (rasterizer_impl.cu:54-66). */
 int lsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,

@@ -42,7 +42,7 @@ class Inputs(Structure):
 class Grads(Structure):
     _fields_ = [(n, c_void_p) for n in ("dL_dmeans3D", "dL_dmeans2D", "dL_dsh", "dL_dcolors",
                                          "dL_dlanguage_feature", "dL_dopacity", "dL_dscales", "dL_drotations",
-                                         "dL_dcov3D", "dL_dconic")]
+                                         "dL_dcov3D", "dL_dconic", "dL_dcolors_masked")]
 
 
 EXPORTS = {
@@ -57,6 +57,8 @@ EXPORTS = {
                                           c_void_p, c_void_p]),
     "lsr_backward": (c_int, [POINTER(Frame), POINTER(Inputs), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                              c_void_p, c_uint32, POINTER(Grads), c_void_p]),
+    "lsr_sh_gradient_from_views": (c_int, [c_int32, c_int32, c_int32, c_int32, c_void_p, c_void_p, c_void_p, c_void_p,
+                                           c_void_p]),
     "lsr_mark_visible": (c_int, [c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "lsr_l1_loss_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_int32, c_int64, c_void_p, c_void_p]),
     "lsr_l1_loss_backward": (c_int, [c_void_p, c_void_p, c_void_p, c_int32, c_int64, c_void_p, c_void_p, c_void_p]),

@@ -162,6 +162,18 @@ int lsr_l1_loss_backward(const float* pred, const float* gt, const float* mask, 
   return LSR_OK;
 }
 
+int lsr_sh_gradient_from_views(int32_t P, int32_t M, int32_t D, int32_t n_views, const float* means3D,
+                               const float* campos, const float* g, float* dL_dsh, void* stream) {
+  if (P < 0 || M < 0 || n_views < 0 || D < 0 || D > 3) return fail(LSR_ERR_INVALID, "bad size / degree");
+  if (M < (D + 1) * (D + 1)) return fail(LSR_ERR_INVALID, "sh_degree %d needs at least %d SH coefficients, got %d", D,
+                                         (D + 1) * (D + 1), M);
+  if (P > 0 && M > 0 && (!means3D || !dL_dsh || (n_views > 0 && (!campos || !g))))
+    return fail(LSR_ERR_INVALID, "null pointer");
+  launch_sh_grad_views(P, D, M, n_views, means3D, campos, g, dL_dsh, (cudaStream_t)stream);
+  LSR_CUDA(cudaGetLastError());
+  return LSR_OK;
+}
+
 int lsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, void* stream) {
   (void)projmatrix;  // the reference's in_frustum computes p_proj but only tests p_view.z (auxiliary.h:139-164)
@@ -377,7 +389,7 @@ int lsr_backward(const lsr_frame* frame, const lsr_inputs* in, const int32_t* ra
     add(gr.dL_dcolors, 3);
     add(gr.dL_dlanguage_feature, 3);
     // outputs the per-Gaussian kernel will not write in this configuration
-    const bool run_pre = geom_need || (in->shs && gr.dL_dsh && dcol);
+    const bool run_pre = geom_need || (in->shs && (gr.dL_dsh || gr.dL_dcolors_masked) && dcol);
     if (!run_pre) { add(gr.dL_dmeans3D, 3); add(gr.dL_dcov3D, 6); add(gr.dL_dscales, 3); add(gr.dL_drotations, 4); }
     if (!run_pre || !in->shs || !gr.dL_dcolors) { if (gr.dL_dsh && frame->M > 0) add(gr.dL_dsh, (size_t)frame->M * 3); }
     if (run_pre && !in->scales) { add(gr.dL_dscales, 3); add(gr.dL_drotations, 4); }
@@ -400,7 +412,7 @@ int lsr_backward(const lsr_frame* frame, const lsr_inputs* in, const int32_t* ra
                     gr.dL_dopacity, gr.dL_dcolors, gr.dL_dlanguage_feature, s);
   LSR_STAGE("render_bwd");
   prof(g_ev_b, 2, s);
-  if (geom_need || (in->shs && gr.dL_dsh && dcol)) {
+  if (geom_need || (in->shs && (gr.dL_dsh || gr.dL_dcolors_masked) && dcol)) {
     if (!gr.dL_dconic) return fail(LSR_ERR_INVALID, "dL_dconic required for the per-Gaussian backward");
     const float focal_y = H / (2.0f * frame->tanfovy);
     const float focal_x = W / (2.0f * frame->tanfovx);

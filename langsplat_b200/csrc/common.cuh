@@ -196,6 +196,9 @@ void launch_render_bwd(int W, int H, const uint2* ranges, const uint32_t* list, 
                        float* dL_dopacity, float* dL_dcolors, float* dL_dfeat, cudaStream_t s);
 void launch_preprocess_bwd(const lsr_frame& f, const lsr_inputs& in, float focal_x, float focal_y,
                            const int32_t* radii, GeomView g, uint32_t need_mask, const lsr_grads& gr, cudaStream_t s);
+// dL_dsh [P,M,3] = sum over V views of basis(normalize(mean - campos_v)) (x) g_v, g: [V,P,3] clamp-masked dL_dcolor
+void launch_sh_grad_views(int P, int D, int M, int V, const float* means3D, const float* campos, const float* g,
+                          float* dL_dsh, cudaStream_t s);
 void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, uint8_t* present, cudaStream_t s);
 
 // loss.cu: fused (masked) L1 loss forward / backward on [C,N] images

@@ -133,7 +133,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
                       float ddely_dy, float* __restrict__ dL_dmean2D,
                       const float* __restrict__ dL_dconic, const float* __restrict__ dL_dcolor,
                       float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
-                      float* __restrict__ dL_dscale, float* __restrict__ dL_drot) {
+                      float* __restrict__ dL_dscale, float* __restrict__ dL_drot, float* __restrict__ dL_dcolor_masked) {
   extern __shared__ __align__(16) float4 s_dyn[];
   __shared__ __align__(16) float s_xyz[BPRE_THREADS * 3];   // means3D in, dL_dmean3D out
   __shared__ __align__(16) float s_scl[BPRE_THREADS * 3];   // scales in, dL_dscale out
@@ -148,7 +148,10 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
     s_proj[tid] = projmatrix[tid];
   }
   if (tid < 3) s_cam[tid] = campos[tid];
-  const bool do_sh = shs != nullptr && dL_dsh != nullptr && dL_dcolor != nullptr;
+  // factored SH gradient: dL_dsh[k][ch] = basis_k(dir) * g[ch] with g = dL_dcolor masked by the clamp (backward.cu:31-34)
+  // — a caller that wants the factor g instead of the 16x larger product passes dL_dcolor_masked and no dL_dsh
+  const bool write_sh = dL_dsh != nullptr;
+  const bool do_sh = shs != nullptr && (write_sh || dL_dcolor_masked != nullptr) && dL_dcolor != nullptr;
   const bool do_scale = scales != nullptr && dL_dscale != nullptr;
   const bool valid = tid < count;
   const int idx = first + tid;
@@ -295,11 +298,12 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
         }
         const float3 dm = sh_dir_backward(D, v, dir, g);
         dmean.x += dm.x; dmean.y += dm.y; dmean.z += dm.z;
+        if (dL_dcolor_masked) { s_dcol[3 * tid] = g[0]; s_dcol[3 * tid + 1] = g[1]; s_dcol[3 * tid + 2] = g[2]; }
         const float len = sqrtf(dir.x * dir.x + dir.y * dir.y + dir.z * dir.z);
         float bs[16];
-        sh_basis(D, dir.x / len, dir.y / len, dir.z / len, bs);
+        if (write_sh) sh_basis(D, dir.x / len, dir.y / len, dir.z / len, bs);
 #pragma unroll
-        for (int i = 0; i < SH_ROW; i++) {
+        for (int i = 0; write_sh && i < SH_ROW; i++) {
           float4 o;
           o.x = bs[(4 * i) / 3] * g[(4 * i) % 3];
           o.y = bs[(4 * i + 1) / 3] * g[(4 * i + 1) % 3];
@@ -309,11 +313,12 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
         }
       }
       __syncwarp();
-      warp_store_rows<SH_ROW>(reinterpret_cast<float4*>(dL_dsh) + wfirst * SH_ROW, wsm, vis_mask, valid_mask, true,
-                              lane);
+      if (write_sh)
+        warp_store_rows<SH_ROW>(reinterpret_cast<float4*>(dL_dsh) + wfirst * SH_ROW, wsm, vis_mask, valid_mask, true,
+                                lane);
       __syncwarp();
     } else if (valid) {
-      float* dsh = dL_dsh + (size_t)idx * M * 3;
+      float* dsh = write_sh ? dL_dsh + (size_t)idx * M * 3 : nullptr;
       if (vis) {
         const uint8_t cl = clamped[idx];
         float3 g;
@@ -321,9 +326,11 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
         g.y = (cl & 2) ? 0.f : s_dcol[3 * tid + 1];
         g.z = (cl & 4) ? 0.f : s_dcol[3 * tid + 2];
         const float3 dir = make_float3(mx - s_cam[0], my - s_cam[1], mz - s_cam[2]);
-        const float3 dm = sh_backward(D, M, shs + (size_t)idx * M * 3, dir, g, dsh);
+        if (dL_dcolor_masked) { s_dcol[3 * tid] = g.x; s_dcol[3 * tid + 1] = g.y; s_dcol[3 * tid + 2] = g.z; }
+        const float3 dm = write_sh ? sh_backward(D, M, shs + (size_t)idx * M * 3, dir, g, dsh)
+                                   : sh_backward_t<false>(D, M, shs + (size_t)idx * M * 3, dir, g, nullptr);
         dmean.x += dm.x; dmean.y += dm.y; dmean.z += dm.z;
-      } else {
+      } else if (write_sh) {
         for (int i = 0; i < M * 3; i++) dsh[i] = 0.f;
       }
     }
@@ -365,6 +372,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
     dq.w = 2 * r * (dMt.m[0][1] - dMt.m[1][0]) + 2 * x * (dMt.m[2][0] + dMt.m[0][2]) + 2 * y * (dMt.m[1][2] + dMt.m[2][1]) -
            4 * z * (dMt.m[1][1] + dMt.m[0][0]);
   }
+  if (do_sh && dL_dcolor_masked && !vis) { s_dcol[3 * tid] = 0.f; s_dcol[3 * tid + 1] = 0.f; s_dcol[3 * tid + 2] = 0.f; }
   if (do_scale && valid) reinterpret_cast<float4*>(dL_drot)[idx] = dq;
   // dL_dmean3D / dL_dscale leave through the arrays their inputs came in by (each thread owns its triplet)
   __syncthreads();
@@ -373,7 +381,64 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   __syncthreads();
   if (dL_dmean3D) unstage_flat<BPRE_THREADS>(dL_dmean3D, s_xyz, (size_t)first * 3, count * 3, tid);
   if (moments) unstage_flat<BPRE_THREADS>(dL_dmean2D, s_m2d, (size_t)first * 3, count * 3, tid);
+  if (do_sh && dL_dcolor_masked) unstage_flat<BPRE_THREADS>(dL_dcolor_masked, s_dcol, (size_t)first * 3, count * 3, tid);
   if (do_scale) unstage_flat<BPRE_THREADS>(dL_dscale, s_scl, (size_t)first * 3, count * 3, tid);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// dL_dsh from per-view factors.  For one view, dL_dsh[k][ch] = basis_k(normalize(mean - campos)) * g[ch]
+// (backward.cu:36-129), a rank-1 matrix per Gaussian, g = that view's clamp-masked dL_dcolor (zero if culled).  Given
+// the factors g_v of V views (the local ones or those all-gathered from the other ranks: 12 B per Gaussian and view
+// instead of 192), this kernel forms sum_v basis(dir_v) (x) g_v and writes the [P,M,3] gradient once, rows staged
+// through shared memory for coalesced 16-byte stores when M == 16.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int SHV_THREADS = 128;
+constexpr size_t SHV_SMEM = (size_t)(SHV_THREADS / 32) * 32 * (SH_ROW + 1) * sizeof(float4);
+
+template <bool SH16>
+__global__ void __launch_bounds__(SHV_THREADS)
+sh_grad_views_kernel(int P, int D, int M, int V, const float* __restrict__ means3D, const float* __restrict__ campos,
+                     const float* __restrict__ g, float* __restrict__ dL_dsh) {
+  extern __shared__ __align__(16) float4 s_rows[];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int idx = blockIdx.x * SHV_THREADS + tid;
+  const bool valid = idx < P;
+  float acc[48];
+#pragma unroll
+  for (int i = 0; i < 48; i++) acc[i] = 0.f;
+  float mx = 0.f, my = 0.f, mz = 0.f;
+  if (valid) { mx = __ldg(means3D + 3 * (size_t)idx); my = __ldg(means3D + 3 * (size_t)idx + 1); mz = __ldg(means3D + 3 * (size_t)idx + 2); }
+  for (int v = 0; v < V; v++) {
+    float g0 = 0.f, g1 = 0.f, g2 = 0.f;
+    if (valid) {
+      const float* gp = g + ((size_t)v * P + idx) * 3;
+      g0 = __ldg(gp); g1 = __ldg(gp + 1); g2 = __ldg(gp + 2);
+    }
+    if (g0 == 0.f && g1 == 0.f && g2 == 0.f) continue;  // culled in this view (or no gradient): contributes nothing
+    const float dx = mx - __ldg(campos + 3 * v), dy = my - __ldg(campos + 3 * v + 1), dz = mz - __ldg(campos + 3 * v + 2);
+    const float len = sqrtf(dx * dx + dy * dy + dz * dz);
+    float bs[16];
+    sh_basis(D, dx / len, dy / len, dz / len, bs);
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+      acc[3 * k] += bs[k] * g0;
+      acc[3 * k + 1] += bs[k] * g1;
+      acc[3 * k + 2] += bs[k] * g2;
+    }
+  }
+  if (SH16) {
+    float4* wsm = s_rows + (size_t)warp * 32 * (SH_ROW + 1);
+#pragma unroll
+    for (int i = 0; i < SH_ROW; i++)
+      wsm[row_slot<SH_ROW>(lane, i)] = make_float4(acc[4 * i], acc[4 * i + 1], acc[4 * i + 2], acc[4 * i + 3]);
+    __syncwarp();
+    const uint32_t valid_mask = __ballot_sync(0xffffffffu, valid);
+    warp_store_rows<SH_ROW>(reinterpret_cast<float4*>(dL_dsh) + (size_t)(blockIdx.x * SHV_THREADS + warp * 32) * SH_ROW,
+                            wsm, valid_mask, valid_mask, false, lane);
+  } else if (valid) {
+    float* o = dL_dsh + (size_t)idx * M * 3;
+    for (int i = 0; i < M * 3; i++) o[i] = i < 48 ? acc[i] : 0.f;
+  }
 }
 
 }  // namespace
@@ -384,8 +449,8 @@ void launch_preprocess_bwd(const lsr_frame& f, const lsr_inputs& in, float focal
   // the blend kernel leaves moments instead of gradients exactly when it ran in its GEOM mode (render_bwd.cu)
   const int moments = (LSR_MOMENTS && (need_mask & LSR_NEED_GEOMETRY)) ? 1 : 0;
   const float* cov3Ds = in.cov3D_precomp ? in.cov3D_precomp : g.cov3D;
-  const bool sh16 = in.shs != nullptr && gr.dL_dsh != nullptr && f.M == 16 && (((uintptr_t)in.shs) & 15) == 0 &&
-                    (((uintptr_t)gr.dL_dsh) & 15) == 0;
+  const bool sh16 = in.shs != nullptr && (gr.dL_dsh != nullptr || gr.dL_dcolors_masked != nullptr) && f.M == 16 &&
+                    (((uintptr_t)in.shs) & 15) == 0 && (((uintptr_t)gr.dL_dsh) & 15) == 0;
   static bool attr_done = false;
   if (!attr_done) {
     cudaFuncSetAttribute(preprocess_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BPRE_SH_SMEM);
@@ -398,10 +463,21 @@ void launch_preprocess_bwd(const lsr_frame& f, const lsr_inputs& in, float focal
       f.viewmatrix, f.projmatrix, focal_x, focal_y, f.tanfovx, f.tanfovy, f.campos, in.opacities, moments,       \
       0.5f * f.width,                                                                                              \
       0.5f * f.height, gr.dL_dmeans2D, gr.dL_dconic,                                                               \
-      gr.dL_dcolors, gr.dL_dmeans3D, gr.dL_dcov3D, gr.dL_dsh, gr.dL_dscales, gr.dL_drotations
+      gr.dL_dcolors, gr.dL_dmeans3D, gr.dL_dcov3D, gr.dL_dsh, gr.dL_dscales, gr.dL_drotations,                      \
+      gr.dL_dcolors_masked
   if (sh16) preprocess_bwd_kernel<true><<<blocks, BPRE_THREADS, BPRE_SH_SMEM, s>>>(LSR_BPRE_ARGS);
   else preprocess_bwd_kernel<false><<<blocks, BPRE_THREADS, BPRE_SH_SMEM, s>>>(LSR_BPRE_ARGS);
 #undef LSR_BPRE_ARGS
+  count_launch();
+}
+
+void launch_sh_grad_views(int P, int D, int M, int V, const float* means3D, const float* campos, const float* g,
+                          float* dL_dsh, cudaStream_t s) {
+  if (P <= 0 || M <= 0) return;
+  const bool sh16 = M == 16 && (((uintptr_t)dL_dsh) & 15) == 0;
+  const int blocks = (P + SHV_THREADS - 1) / SHV_THREADS;
+  if (sh16) sh_grad_views_kernel<true><<<blocks, SHV_THREADS, SHV_SMEM, s>>>(P, D, M, V, means3D, campos, g, dL_dsh);
+  else sh_grad_views_kernel<false><<<blocks, SHV_THREADS, SHV_SMEM, s>>>(P, D, M, V, means3D, campos, g, dL_dsh);
   count_launch();
 }
 

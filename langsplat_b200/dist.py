@@ -7,6 +7,8 @@ in the CPU tests).  No collective touches the rasterizer's data path itself.
 """
 from __future__ import annotations
 
+import contextlib
+import ctypes
 from typing import Dict, Iterable, List, Optional, Sequence
 
 import torch
@@ -82,3 +84,70 @@ def reduce_view_statistics(stat_sum: torch.Tensor, stat_count: torch.Tensor, max
     dist.all_reduce(stat_sum, op=dist.ReduceOp.SUM, group=group)
     dist.all_reduce(stat_count, op=dist.ReduceOp.SUM, group=group)
     dist.all_reduce(max_radii, op=dist.ReduceOp.MAX, group=group)
+
+
+# ---- factored SH gradients --------------------------------------------------------------------------------------
+# 81 % of the parameter-gradient bytes of an RGB step are dL_dsh (192 of 236 B per Gaussian), yet one view's dL_dsh is
+# rank-1 per Gaussian: basis(normalize(mean - campos)) (x) g with g = the clamp-masked dL_dcolor (RAST backward.cu:
+# 31-129).  Inside `factored_sh_gradients()` the rasterizer's backward hands out the 12-byte factor g instead of the
+# product; `finish_sh_gradients` all-gathers the factors of every rank's views (12 B per Gaussian and view instead of
+# an all-reduce of 192 B) and forms sum_v basis(dir_v) (x) g_v once with lsr_sh_gradient_from_views.  The result equals
+# the all-reduced dL_dsh up to float summation order.  On one GPU it still pays for multi-view steps: no per-view
+# [P,16,3] gradient is written and re-accumulated.
+
+@contextlib.contextmanager
+def factored_sh_gradients():
+    """Context in which GaussianRasterizer backward passes collect per-view SH-gradient factors (yields the list)."""
+    from . import rasterizer as R
+    sink: List = []
+    prev = R._sh_factor_sink
+    R._sh_factor_sink = sink
+    try:
+        yield sink
+    finally:
+        R._sh_factor_sink = prev
+
+
+def gather_sh_factors(factors, P: int, device, group=None):
+    """(g [V_all, P, 3], campos [V_all, 3], sh_degree) over the views of all ranks, rank-major (all_gather order).
+    Every rank must contribute the same number of views.  Two collectives: 12 B per Gaussian and view, and the
+    camera positions."""
+    g_local = (torch.stack([f[0] for f in factors]) if factors
+               else torch.zeros((0, P, 3), dtype=torch.float32, device=device))
+    c_local = (torch.stack([f[1].reshape(3).to(device, torch.float32) for f in factors]) if factors
+               else torch.zeros((0, 3), dtype=torch.float32, device=device))
+    degree = int(factors[0][2]) if factors else 0
+    if not (dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1):
+        return g_local.contiguous(), c_local.contiguous(), degree
+    world = dist.get_world_size(group)
+    g_all = torch.empty((world * g_local.shape[0], P, 3), dtype=torch.float32, device=device)
+    c_all = torch.empty((world * c_local.shape[0], 3), dtype=torch.float32, device=device)
+    dist.all_gather_into_tensor(g_all, g_local.contiguous(), group=group)
+    dist.all_gather_into_tensor(c_all, c_local.contiguous(), group=group)
+    return g_all, c_all, degree
+
+
+def finish_sh_gradients(factors, means3D: torch.Tensor, n_coeffs: int, group=None) -> Optional[torch.Tensor]:
+    """dL_dsh [P, n_coeffs, 3] summed over the views of ALL ranks from the factors collected on this rank
+    (lsr_sh_gradient_from_views).  Returns None if there is no process group and no view produced a factor."""
+    from . import _lib as L
+    from .rasterizer import LsrError
+    distributed = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+    if not factors and not distributed:
+        return None
+    P = means3D.shape[0]
+    dev = means3D.device
+    if not means3D.is_cuda:
+        raise LsrError("finish_sh_gradients: langsplat_b200 has no CPU path")
+    g_all, c_all, degree = gather_sh_factors(factors, P, dev, group)
+    lib = L.load()
+    out = torch.empty((P, n_coeffs, 3), dtype=torch.float32, device=dev)
+    m3 = means3D.detach().contiguous()
+    with torch.cuda.device(dev):
+        rc = lib.lsr_sh_gradient_from_views(P, n_coeffs, degree, g_all.shape[0], ctypes.c_void_p(m3.data_ptr()),
+                                            ctypes.c_void_p(c_all.data_ptr()), ctypes.c_void_p(g_all.data_ptr()),
+                                            ctypes.c_void_p(out.data_ptr()),
+                                            ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
+    if rc != L.LSR_OK:
+        raise LsrError(L.last_error())
+    return out

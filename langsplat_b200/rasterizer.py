@@ -161,7 +161,15 @@ def _forward_impl(rs: GaussianRasterizationSettings, means3D, sh, colors, lang, 
     return color, feature, radii, state
 
 
-def _backward_impl(state, grad_color, grad_feature, need_mask: int, want_sh: bool):
+# When a list is installed here (langsplat_b200.dist.factored_sh_gradients), a backward that owes an SH gradient does
+# not materialise dL_dsh [P,16,3]; it appends that view's factor — (clamp-masked dL_dcolor [P,3], campos [3],
+# sh_degree) — and returns no gradient for `shs`.  dL_dsh of a view is the rank-1 product basis(dir) (x) factor, so a
+# multi-view / data-parallel step can exchange and accumulate 12-byte factors instead of 192-byte products and form
+# the sum once (lsr_sh_gradient_from_views).
+_sh_factor_sink = None
+
+
+def _backward_impl(state, grad_color, grad_feature, need_mask: int, want_sh: bool, sh_factor_out=None):
     lib = L.load()
     P, M, W, H, device = state["P"], state["M"], state["W"], state["H"], state["device"]
     (means3D, sh, colors, lang, opac, scales, rots, cov3D, *_rest) = state["keep"]
@@ -176,7 +184,8 @@ def _backward_impl(state, grad_color, grad_feature, need_mask: int, want_sh: boo
     # for any P), so a data-parallel caller can all-reduce them as ONE flat message (langsplat_b200.dist.coalesce);
     # the internal accumulators (conic, means2D, colours, cov3D) follow from the next 16-byte boundary.  The library
     # zero-fills what the blend kernel accumulates into (adjacent ranges merge into one memset).
-    n_sh = M * 3 if (run_pre and sh is not None) else 0
+    factored = sh_factor_out is not None and run_pre and sh is not None and gc is not None
+    n_sh = M * 3 if (run_pre and sh is not None and not factored) else 0
     sizes = [("rots", 4 if run_pre else 0), ("sh", n_sh), ("means3D", 3 if run_pre else 0),
              ("scales", 3 if run_pre else 0), ("feat", 3), ("opac", 1), ("|", 0), ("conic", 4), ("means2D", 3),
              ("colors", 3), ("cov3D", 6 if run_pre else 0)]
@@ -201,9 +210,13 @@ def _backward_impl(state, grad_color, grad_feature, need_mask: int, want_sh: boo
         d_means3D = part["means3D"].view(P, 3)
         d_cov3D = part["cov3D"].view(P, 6)
         g.dL_dmeans3D, g.dL_dcov3D = d_means3D.data_ptr(), d_cov3D.data_ptr()
-        if sh is not None:
+        if sh is not None and not factored:
             d_sh = part["sh"].view(P, M, 3)
             g.dL_dsh = d_sh.data_ptr()
+        if factored:
+            masked = torch.empty((P, 3), **f32)
+            g.dL_dcolors_masked = masked.data_ptr()
+            sh_factor_out.append((masked, state["keep"][11], int(state["frame"].D)))
         d_scales = part["scales"].view(P, 3)
         d_rots = part["rots"].view(P, 4)
         g.dL_dscales, g.dL_drotations = d_scales.data_ptr(), d_rots.data_ptr()
@@ -265,7 +278,8 @@ class _RasterizeGaussians(torch.autograd.Function):
                 print("\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
                 raise ex
         else:
-            g = _backward_impl(state, grad_out_color, grad_out_language_feature, mask, want_sh)
+            g = _backward_impl(state, grad_out_color, grad_out_language_feature, mask, want_sh,
+                               _sh_factor_sink if need[2] else None)
         lang_grad = None
         if need[4]:
             lang_grad = g["language_feature"] if include_feature else torch.zeros(
