@@ -59,6 +59,9 @@ def parse_args():
     ap.add_argument("--width", type=int, default=None)
     ap.add_argument("--height", type=int, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--allgather-sh-exchange", action="store_true",
+                    help="multi-GPU: NCCL all-gather of the SH-gradient factors instead of reading them from peer "
+                         "memory inside the SH-gradient kernel (A/B)")
     ap.add_argument("--dense-sh-exchange", action="store_true",
                     help="multi-view / multi-GPU: all-reduce dL_dsh itself instead of its per-view factors (A/B)")
     ap.add_argument("--cpu-frames", type=int, default=3)
@@ -270,8 +273,20 @@ def main():
     # its per-view rank-1 factor (12 B per Gaussian and view) and is formed once per step (langsplat_b200.dist).
     factored = (args.impl == "ours" and not fwd_only and not feature_only and not args.dense_sh_exchange
                 and (world > 1 or len(my_views) > 1))
+    peer = None
     if factored:
-        from langsplat_b200.dist import factored_sh_gradients, finish_sh_gradients
+        from langsplat_b200.dist import factored_sh_gradients, finish_sh_gradients, make_peer_exchange
+        if world > 1 and not args.allgather_sh_exchange:  # factors read in place over NVLink by the SH-gradient kernel
+            peer = make_peer_exchange(P, len(my_views), dev)
+
+    exchange = ("none (one view, one GPU)" if world == 1 and len(my_views) == 1 else
+                "dL_dsh summed by autograd" + (" + NCCL all-reduce of all gradients" if world > 1 else ""))
+    if factored:
+        exchange = ("SH gradient as per-view 12-byte factors: "
+                    + ("read from peer memory over NVLink inside the SH-gradient kernel (one barrier kernel), "
+                       "concurrently NCCL all-reduce of the other 56 B/Gaussian" if peer else
+                       ("NCCL all-gather of factors + all-reduce of the other 56 B/Gaussian" if world > 1 else
+                        "summed over the step's views by one kernel")))
 
     def backward_and_reduce(run_views):
         """run_views() runs forward+backward of this rank's views; afterwards every rank holds the summed gradients."""
@@ -279,15 +294,22 @@ def main():
             run_views()
             reduce_grads()
             return
-        with factored_sh_gradients() as factors:
+        with factored_sh_gradients(peer.begin_step() if peer else None) as factors:
             run_views()
-        reduce_grads()  # everything but the SH gradient (absent from .grad in this mode)
-        params["shs"].grad = finish_sh_gradients(factors, params["means3D"], params["shs"].shape[1])
+        # everything but the SH gradient (absent from .grad in this mode): NCCL, on its own stream, while ...
+        handles = reduce_grads(async_op=True)
+        if peer:  # ... this rank's kernel pulls the other ranks' factors over NVLink and forms dL_dsh
+            params["shs"].grad = peer.finish(params["means3D"], params["shs"].shape[1])
+        else:
+            params["shs"].grad = finish_sh_gradients(factors, params["means3D"], params["shs"].shape[1])
+        for h in handles:
+            h.wait()
 
-    def reduce_grads():
+    def reduce_grads(async_op=False):
         if world > 1:
             from langsplat_b200.dist import allreduce_gradients
-            allreduce_gradients([p.grad for p in params.values() if p.grad is not None])
+            return allreduce_gradients([p.grad for p in params.values() if p.grad is not None], async_op=async_op)
+        return []
 
     def step():
         if fwd_only:
@@ -447,6 +469,9 @@ def main():
         stage_ms = acc[:n_st] / args.steps
         stages = {lib.lsr_profile_stage_name(i).decode(): float(stage_ms[i]) for i in range(n_st)}
 
+    if peer is not None:
+        peer.check()  # a barrier that timed out would have produced garbage gradients: fail the run
+        peer.close()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -459,7 +484,7 @@ def main():
             "scaling": "strong" if cfg == 4 else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload, "P": P, "width": W, "height": H, "cameras_per_step": views_per_step,
                        "l2_policy": "inputs larger than L2 (Gaussian tensors ~250 MB), no explicit flush",
-                       "impl": impl_name},
+                       "impl": impl_name, "exchange": exchange},
             "fwd_only_ms_per_frame": fwd_ms, "clocks": clocks,
             "e2e": {"value": (world * (len(levels) if fwd_only else 1)) * args.steps / (e2e_ms_total / 1000.0),
                     "unit": "frames/s",

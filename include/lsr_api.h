@@ -157,6 +157,35 @@ int lsr_backward(const lsr_frame* frame, const lsr_inputs* in, const int32_t* ra
 int lsr_sh_gradient_from_views(int32_t P, int32_t M, int32_t D, int32_t n_views, const float* means3D,
                                const float* campos, const float* g, float* dL_dsh, void* stream);
 
+/* The same sum with every view's factor and camera position given by its own device pointer: g_views[v] -> [P,3],
+ * campos_views[v] -> 3 floats (both arrays live on the host, n_views entries).  The pointers may be peer memory mapped
+ * with lsr_peer_open: the kernel then reads the other ranks' factors in place over NVLink and no all-gather is needed.
+ * More than LSR_MAX_VIEWS views are processed in chunks. */
+#define LSR_MAX_VIEWS 64
+int lsr_sh_gradient_from_view_ptrs(int32_t P, int32_t M, int32_t D, int32_t n_views, const float* means3D,
+                                   const float* const* g_views, const float* const* campos_views, float* dL_dsh,
+                                   void* stream);
+
+/* ---- peer memory for the view-sharded step (one process per GPU of one node; no reference counterpart: the
+ * reference is single-GPU, train.py:84-92) ----
+ * lsr_peer_alloc: device buffer of `bytes` (zero-filled) that other processes can map, and its 64-byte handle (a CUDA
+ *   IPC handle) to hand to them by any channel (torch.distributed all_gather in langsplat_b200.dist).
+ * lsr_peer_open / lsr_peer_close: map / unmap another process's buffer; lsr_peer_free: release an own buffer.
+ * The first LSR_PEER_HEADER_BYTES of every buffer belong to the library (barrier words); payload starts after them.
+ * lsr_peer_barrier: stream-ordered barrier across `world` ranks; headers[r] = rank r's buffer as seen from this
+ *   process (own pointer at headers[rank]).  `epoch` must grow by one per call on every rank.  Work enqueued after it
+ *   sees everything the peers enqueued before theirs.  A peer that does not arrive within 4 s is reported by
+ *   lsr_peer_status (returns LSR_ERR_CUDA, "peer barrier timed out") instead of hanging the device. */
+#define LSR_PEER_HANDLE_BYTES 64
+#define LSR_PEER_HEADER_BYTES 256
+#define LSR_MAX_PEERS 16
+int lsr_peer_alloc(size_t bytes, void** ptr, uint8_t* handle);
+int lsr_peer_open(const uint8_t* handle, void** ptr);
+int lsr_peer_close(void* ptr);
+int lsr_peer_free(void* ptr);
+int lsr_peer_barrier(int32_t rank, int32_t world, void* const* headers, uint32_t epoch, void* stream);
+int lsr_peer_status(const void* own_buffer, void* stream);
+
 /* Replaces _C.mark_visible -> markVisible (rasterize_points.cu:226-245) -> checkFrustum (rasterizer_impl.cu:54-66). */
 int lsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, void* stream);

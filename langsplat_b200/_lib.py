@@ -45,6 +45,8 @@ class Grads(Structure):
                                          "dL_dcov3D", "dL_dconic", "dL_dcolors_masked")]
 
 
+PEER_HANDLE_BYTES, PEER_HEADER_BYTES, MAX_PEERS, MAX_VIEWS = 64, 256, 16, 64  # include/lsr_api.h
+
 EXPORTS = {
     "lsr_geom_bytes": (c_size_t, [c_int32]),
     "lsr_image_bytes": (c_size_t, [c_int32, c_int32]),
@@ -59,6 +61,14 @@ EXPORTS = {
                              c_void_p, c_uint32, POINTER(Grads), c_void_p]),
     "lsr_sh_gradient_from_views": (c_int, [c_int32, c_int32, c_int32, c_int32, c_void_p, c_void_p, c_void_p, c_void_p,
                                            c_void_p]),
+    "lsr_sh_gradient_from_view_ptrs": (c_int, [c_int32, c_int32, c_int32, c_int32, c_void_p, POINTER(c_void_p),
+                                               POINTER(c_void_p), c_void_p, c_void_p]),
+    "lsr_peer_alloc": (c_int, [c_size_t, POINTER(c_void_p), c_void_p]),
+    "lsr_peer_open": (c_int, [c_void_p, POINTER(c_void_p)]),
+    "lsr_peer_close": (c_int, [c_void_p]),
+    "lsr_peer_free": (c_int, [c_void_p]),
+    "lsr_peer_barrier": (c_int, [c_int32, c_int32, POINTER(c_void_p), c_uint32, c_void_p]),
+    "lsr_peer_status": (c_int, [c_void_p, c_void_p]),
     "lsr_mark_visible": (c_int, [c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "lsr_l1_loss_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_int32, c_int64, c_void_p, c_void_p]),
     "lsr_l1_loss_backward": (c_int, [c_void_p, c_void_p, c_void_p, c_int32, c_int64, c_void_p, c_void_p, c_void_p]),

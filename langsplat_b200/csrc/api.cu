@@ -174,6 +174,79 @@ int lsr_sh_gradient_from_views(int32_t P, int32_t M, int32_t D, int32_t n_views,
   return LSR_OK;
 }
 
+int lsr_sh_gradient_from_view_ptrs(int32_t P, int32_t M, int32_t D, int32_t n_views, const float* means3D,
+                                   const float* const* g_views, const float* const* campos_views, float* dL_dsh,
+                                   void* stream) {
+  if (P < 0 || M < 0 || n_views < 0 || D < 0 || D > 3) return fail(LSR_ERR_INVALID, "bad size / degree");
+  if (M < (D + 1) * (D + 1)) return fail(LSR_ERR_INVALID, "sh_degree %d needs at least %d SH coefficients, got %d", D,
+                                         (D + 1) * (D + 1), M);
+  if (P > 0 && M > 0 && (!means3D || !dL_dsh || (n_views > 0 && (!g_views || !campos_views))))
+    return fail(LSR_ERR_INVALID, "null pointer");
+  for (int v = 0; v < n_views && P > 0 && M > 0; v++)
+    if (!g_views[v] || !campos_views[v]) return fail(LSR_ERR_INVALID, "null pointer for view %d", v);
+  launch_sh_grad_view_ptrs(P, D, M, n_views, means3D, g_views, campos_views, dL_dsh, (cudaStream_t)stream);
+  LSR_CUDA(cudaGetLastError());
+  return LSR_OK;
+}
+
+// ---- peer memory (CUDA IPC) ----
+static_assert(sizeof(cudaIpcMemHandle_t) == LSR_PEER_HANDLE_BYTES, "IPC handle size");
+
+int lsr_peer_alloc(size_t bytes, void** ptr, uint8_t* handle) {
+  if (!ptr || !handle || bytes < LSR_PEER_HEADER_BYTES) return fail(LSR_ERR_INVALID, "bad argument");
+  void* p = nullptr;
+  LSR_CUDA(cudaMalloc(&p, bytes));
+  cudaError_t e = cudaMemset(p, 0, bytes);
+  cudaIpcMemHandle_t h;
+  if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, p);
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    return fail(LSR_ERR_CUDA, "lsr_peer_alloc: %s", cudaGetErrorString(e));
+  }
+  memcpy(handle, &h, sizeof(h));
+  *ptr = p;
+  return LSR_OK;
+}
+
+int lsr_peer_open(const uint8_t* handle, void** ptr) {
+  if (!handle || !ptr) return fail(LSR_ERR_INVALID, "null pointer");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof(h));
+  LSR_CUDA(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return LSR_OK;
+}
+
+int lsr_peer_close(void* ptr) {
+  if (ptr) LSR_CUDA(cudaIpcCloseMemHandle(ptr));
+  return LSR_OK;
+}
+
+int lsr_peer_free(void* ptr) {
+  if (ptr) LSR_CUDA(cudaFree(ptr));
+  return LSR_OK;
+}
+
+int lsr_peer_barrier(int32_t rank, int32_t world, void* const* headers, uint32_t epoch, void* stream) {
+  if (world < 1 || world > LSR_MAX_PEERS || rank < 0 || rank >= world || !headers)
+    return fail(LSR_ERR_INVALID, "bad rank / world (at most %d peers)", LSR_MAX_PEERS);
+  for (int r = 0; r < world; r++)
+    if (!headers[r]) return fail(LSR_ERR_INVALID, "null header for rank %d", r);
+  launch_peer_barrier(rank, world, headers, epoch, (cudaStream_t)stream);
+  LSR_CUDA(cudaGetLastError());
+  return LSR_OK;
+}
+
+int lsr_peer_status(const void* own_buffer, void* stream) {
+  if (!own_buffer) return fail(LSR_ERR_INVALID, "null pointer");
+  uint32_t flag = 0;
+  LSR_CUDA(cudaMemcpyAsync(&flag, static_cast<const uint8_t*>(own_buffer) + LSR_MAX_PEERS * sizeof(uint32_t),
+                           sizeof(flag), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  LSR_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  if (flag) return fail(LSR_ERR_CUDA, "peer barrier timed out (a rank did not arrive within 4 s)");
+  return LSR_OK;
+}
+
 int lsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, void* stream) {
   (void)projmatrix;  // the reference's in_frustum computes p_proj but only tests p_view.z (auxiliary.h:139-164)

@@ -199,6 +199,11 @@ void launch_preprocess_bwd(const lsr_frame& f, const lsr_inputs& in, float focal
 // dL_dsh [P,M,3] = sum over V views of basis(normalize(mean - campos_v)) (x) g_v, g: [V,P,3] clamp-masked dL_dcolor
 void launch_sh_grad_views(int P, int D, int M, int V, const float* means3D, const float* campos, const float* g,
                           float* dL_dsh, cudaStream_t s);
+// same, each view's factor / campos given by its own pointer (peer memory allowed); any V (chunks of LSR_MAX_VIEWS)
+void launch_sh_grad_view_ptrs(int P, int D, int M, int V, const float* means3D, const float* const* g_views,
+                              const float* const* campos_views, float* dL_dsh, cudaStream_t s);
+// cross-GPU barrier on the stream (peer.cu): signals `epoch` into every peer's header, waits for all of them
+void launch_peer_barrier(int rank, int world, void* const* headers, uint32_t epoch, cudaStream_t s);
 void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, uint8_t* present, cudaStream_t s);
 
 // loss.cu: fused (masked) L1 loss forward / backward on [C,N] images

@@ -8,6 +8,9 @@
 // With `moments` set, the blend kernel (render_bwd.cu) left the pair-weighted moments M0, (Mx, My), (Mxx, Mxy, Myy) of the
 // pixel offsets in dL_dopacity / dL_dmean2D / dL_dconic instead of the reference's sums (backward.cu:552-582); the
 // per-Gaussian coefficients are applied here, and dL_dmean2D is rewritten in place with the actual gradient.
+#include <algorithm>
+#include <vector>
+
 #include "common.cuh"
 #include "gs_math.cuh"
 #include "stage.cuh"
@@ -393,37 +396,58 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
 // through shared memory for coalesced 16-byte stores when M == 16.
 // ---------------------------------------------------------------------------------------------------------------
 constexpr int SHV_THREADS = 128;
+constexpr int SHV_BATCH = 8;  // views whose factors are loaded together (independent loads in flight: NVLink latency)
 constexpr size_t SHV_SMEM = (size_t)(SHV_THREADS / 32) * 32 * (SH_ROW + 1) * sizeof(float4);
+
+// Per-view base pointers: g[v] -> that view's [P,3] factor, campos[v] -> its 3 floats.  The pointers may be peer
+// memory (another GPU's buffer mapped over NVLink, lsr_peer_open): the kernel then IS the exchange — every rank reads
+// the other ranks' factors in place, no all-gather staging copy.
+struct ShViewPtrs {
+  const float* g[LSR_MAX_VIEWS];
+  const float* campos[LSR_MAX_VIEWS];
+};
 
 template <bool SH16>
 __global__ void __launch_bounds__(SHV_THREADS)
-sh_grad_views_kernel(int P, int D, int M, int V, const float* __restrict__ means3D, const float* __restrict__ campos,
-                     const float* __restrict__ g, float* __restrict__ dL_dsh) {
+sh_grad_views_kernel(int P, int D, int M, int V, const float* __restrict__ means3D, const ShViewPtrs vp,
+                     float* __restrict__ dL_dsh, int accumulate) {
   extern __shared__ __align__(16) float4 s_rows[];
+  __shared__ float s_cam[LSR_MAX_VIEWS * 3];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int idx = blockIdx.x * SHV_THREADS + tid;
   const bool valid = idx < P;
+  for (int i = tid; i < V * 3; i += SHV_THREADS) s_cam[i] = vp.campos[i / 3][i % 3];
   float acc[48];
 #pragma unroll
   for (int i = 0; i < 48; i++) acc[i] = 0.f;
   float mx = 0.f, my = 0.f, mz = 0.f;
   if (valid) { mx = __ldg(means3D + 3 * (size_t)idx); my = __ldg(means3D + 3 * (size_t)idx + 1); mz = __ldg(means3D + 3 * (size_t)idx + 2); }
-  for (int v = 0; v < V; v++) {
-    float g0 = 0.f, g1 = 0.f, g2 = 0.f;
-    if (valid) {
-      const float* gp = g + ((size_t)v * P + idx) * 3;
-      g0 = __ldg(gp); g1 = __ldg(gp + 1); g2 = __ldg(gp + 2);
-    }
-    if (g0 == 0.f && g1 == 0.f && g2 == 0.f) continue;  // culled in this view (or no gradient): contributes nothing
-    const float dx = mx - __ldg(campos + 3 * v), dy = my - __ldg(campos + 3 * v + 1), dz = mz - __ldg(campos + 3 * v + 2);
-    const float len = sqrtf(dx * dx + dy * dy + dz * dz);
-    float bs[16];
-    sh_basis(D, dx / len, dy / len, dz / len, bs);
+  __syncthreads();
+  for (int v0 = 0; v0 < V; v0 += SHV_BATCH) {
+    float gv[SHV_BATCH][3];
 #pragma unroll
-    for (int k = 0; k < 16; k++) {
-      acc[3 * k] += bs[k] * g0;
-      acc[3 * k + 1] += bs[k] * g1;
-      acc[3 * k + 2] += bs[k] * g2;
+    for (int j = 0; j < SHV_BATCH; j++) {
+      gv[j][0] = gv[j][1] = gv[j][2] = 0.f;
+      if (valid && v0 + j < V) {
+        const float* gp = vp.g[v0 + j] + (size_t)idx * 3;
+        gv[j][0] = gp[0]; gv[j][1] = gp[1]; gv[j][2] = gp[2];
+      }
+    }
+#pragma unroll 1
+    for (int j = 0; j < SHV_BATCH; j++) {
+      const float g0 = gv[j][0], g1 = gv[j][1], g2 = gv[j][2];
+      if (g0 == 0.f && g1 == 0.f && g2 == 0.f) continue;  // culled in this view (or no gradient): contributes nothing
+      const int v = v0 + j;
+      const float dx = mx - s_cam[3 * v], dy = my - s_cam[3 * v + 1], dz = mz - s_cam[3 * v + 2];
+      const float len = sqrtf(dx * dx + dy * dy + dz * dz);
+      float bs[16];
+      sh_basis(D, dx / len, dy / len, dz / len, bs);
+#pragma unroll
+      for (int k = 0; k < 16; k++) {
+        acc[3 * k] += bs[k] * g0;
+        acc[3 * k + 1] += bs[k] * g1;
+        acc[3 * k + 2] += bs[k] * g2;
+      }
     }
   }
   if (SH16) {
@@ -437,7 +461,8 @@ sh_grad_views_kernel(int P, int D, int M, int V, const float* __restrict__ means
                             wsm, valid_mask, valid_mask, false, lane);
   } else if (valid) {
     float* o = dL_dsh + (size_t)idx * M * 3;
-    for (int i = 0; i < M * 3; i++) o[i] = i < 48 ? acc[i] : 0.f;
+    if (accumulate) { for (int i = 0; i < M * 3 && i < 48; i++) o[i] += acc[i]; }
+    else { for (int i = 0; i < M * 3; i++) o[i] = i < 48 ? acc[i] : 0.f; }
   }
 }
 
@@ -471,14 +496,30 @@ void launch_preprocess_bwd(const lsr_frame& f, const lsr_inputs& in, float focal
   count_launch();
 }
 
+void launch_sh_grad_view_ptrs(int P, int D, int M, int V, const float* means3D, const float* const* g_views,
+                              const float* const* campos_views, float* dL_dsh, cudaStream_t s) {
+  if (P <= 0 || M <= 0) return;
+  const int blocks = (P + SHV_THREADS - 1) / SHV_THREADS;
+  // LSR_MAX_VIEWS views per launch; later chunks add to what the first one wrote (scalar path)
+  for (int v0 = 0; v0 == 0 || v0 < V; v0 += LSR_MAX_VIEWS) {
+    const int n = std::min(V - v0, (int)LSR_MAX_VIEWS);
+    ShViewPtrs vp;
+    for (int i = 0; i < LSR_MAX_VIEWS; i++) {
+      vp.g[i] = i < n ? g_views[v0 + i] : nullptr;
+      vp.campos[i] = i < n ? campos_views[v0 + i] : nullptr;
+    }
+    const bool sh16 = v0 == 0 && M == 16 && (((uintptr_t)dL_dsh) & 15) == 0;
+    if (sh16) sh_grad_views_kernel<true><<<blocks, SHV_THREADS, SHV_SMEM, s>>>(P, D, M, n, means3D, vp, dL_dsh, 0);
+    else sh_grad_views_kernel<false><<<blocks, SHV_THREADS, SHV_SMEM, s>>>(P, D, M, n, means3D, vp, dL_dsh, v0 > 0);
+    count_launch();
+  }
+}
+
 void launch_sh_grad_views(int P, int D, int M, int V, const float* means3D, const float* campos, const float* g,
                           float* dL_dsh, cudaStream_t s) {
-  if (P <= 0 || M <= 0) return;
-  const bool sh16 = M == 16 && (((uintptr_t)dL_dsh) & 15) == 0;
-  const int blocks = (P + SHV_THREADS - 1) / SHV_THREADS;
-  if (sh16) sh_grad_views_kernel<true><<<blocks, SHV_THREADS, SHV_SMEM, s>>>(P, D, M, V, means3D, campos, g, dL_dsh);
-  else sh_grad_views_kernel<false><<<blocks, SHV_THREADS, SHV_SMEM, s>>>(P, D, M, V, means3D, campos, g, dL_dsh);
-  count_launch();
+  std::vector<const float*> gp((size_t)std::max(V, 0)), cp((size_t)std::max(V, 0));
+  for (int v = 0; v < V; v++) { gp[v] = g + (size_t)v * P * 3; cp[v] = campos + 3 * (size_t)v; }
+  launch_sh_grad_view_ptrs(P, D, M, V, means3D, gp.data(), cp.data(), dL_dsh, s);
 }
 
 }  // namespace lsr

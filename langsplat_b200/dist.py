@@ -96,10 +96,13 @@ def reduce_view_statistics(stat_sum: torch.Tensor, stat_count: torch.Tensor, max
 # [P,16,3] gradient is written and re-accumulated.
 
 @contextlib.contextmanager
-def factored_sh_gradients():
-    """Context in which GaussianRasterizer backward passes collect per-view SH-gradient factors (yields the list)."""
+def factored_sh_gradients(sink=None):
+    """Context in which GaussianRasterizer backward passes hand out per-view SH-gradient factors instead of dL_dsh.
+    Yields the sink: by default a list of (factor [P,3], campos, sh_degree), one entry per backward; pass
+    `PeerFactorExchange.begin_step()` to have the factors written straight into peer-visible memory."""
     from . import rasterizer as R
-    sink: List = []
+    if sink is None:
+        sink = R.ShFactorList()
     prev = R._sh_factor_sink
     R._sh_factor_sink = sink
     try:
@@ -151,3 +154,150 @@ def finish_sh_gradients(factors, means3D: torch.Tensor, n_coeffs: int, group=Non
     if rc != L.LSR_OK:
         raise LsrError(L.last_error())
     return out
+
+
+# ---- the exchange fused into the kernel: factors read in place over NVLink ------------------------------------------
+class _DevicePtr:
+    """Lets torch wrap device memory it did not allocate (the peer buffer) as a tensor."""
+
+    def __init__(self, ptr: int, n_floats: int):
+        self.__cuda_array_interface__ = {"shape": (n_floats,), "typestr": "<f4", "data": (ptr, False), "version": 2}
+
+
+class PeerFactorExchange:
+    """NVLink exchange of the SH-gradient factors without a collective: every rank's backward writes its views'
+    factors into a buffer the other ranks have mapped (lsr_peer_alloc / lsr_peer_open, CUDA IPC); after one
+    stream-ordered barrier kernel (lsr_peer_barrier) the SH-gradient kernel reads all world x views_per_rank factors in
+    place — its loads of the other ranks' factors ARE the transfer, overlapped tile by tile with the accumulation and
+    the dL_dsh stores (lsr_sh_gradient_from_view_ptrs).  No all-gather, no staging copy, and NCCL stays free to
+    all-reduce the remaining gradients at the same time.
+
+    Two slots alternate by step parity: a rank can only get two steps ahead of a peer by passing the barrier in
+    between, which that peer enqueues after the kernel that read the slot, so no slot is overwritten while in use.
+    Every rank must run the same number of views per step, on the same stream from step to step."""
+
+    def __init__(self, P: int, views_per_rank: int, device, group=None):
+        from . import _lib as L
+        from .rasterizer import LsrError
+        self._L, self._lib, self._err = L, L.load(), LsrError
+        self.P, self.V, self.device, self.group = int(P), int(views_per_rank), torch.device(device), group
+        on = dist.is_available() and dist.is_initialized()
+        self.rank = dist.get_rank(group) if on else 0
+        self.world = dist.get_world_size(group) if on else 1
+        if self.world > L.MAX_PEERS:
+            raise LsrError(f"PeerFactorExchange: at most {L.MAX_PEERS} ranks")
+        self.cam_off = self.V * self.P * 3  # floats: factors first, then 4 floats of camera position per view
+        slot_floats = (self.cam_off + 4 * self.V + 63) // 64 * 64
+        self.slot_bytes = slot_floats * 4
+        total = L.PEER_HEADER_BYTES + 2 * self.slot_bytes
+        own, handle = ctypes.c_void_p(), (ctypes.c_uint8 * L.PEER_HANDLE_BYTES)()
+        with torch.cuda.device(self.device):
+            rc = self._lib.lsr_peer_alloc(total, ctypes.byref(own), handle)
+        self.own = own.value if rc == L.LSR_OK else None
+        self.bases: List[Optional[int]] = [None] * self.world
+        self.bases[self.rank] = self.own
+        self._opened: List[int] = []
+        if self.world > 1:  # a rank whose allocation failed still takes part, so that nobody waits for it
+            handles: List = [None] * self.world
+            dist.all_gather_object(handles, bytes(handle) if rc == L.LSR_OK else None, group=group)
+            if any(h is None for h in handles):
+                if self.own is not None:
+                    self._lib.lsr_peer_free(ctypes.c_void_p(self.own))
+                    self.own = None
+                raise LsrError("PeerFactorExchange: lsr_peer_alloc failed on a rank: " + L.last_error())
+            with torch.cuda.device(self.device):
+                for r in range(self.world):
+                    if r != self.rank:
+                        h = (ctypes.c_uint8 * L.PEER_HANDLE_BYTES).from_buffer_copy(handles[r])
+                        p = ctypes.c_void_p()
+                        self._check(self._lib.lsr_peer_open(h, ctypes.byref(p)))
+                        self.bases[r] = p.value
+                        self._opened.append(p.value)
+        self._check(rc)
+        self._payload = torch.as_tensor(_DevicePtr(self.own + L.PEER_HEADER_BYTES, 2 * slot_floats),
+                                        device=self.device).view(2, slot_floats)
+        self._headers = (ctypes.c_void_p * self.world)(*self.bases)
+        self.epoch, self._count, self._degree = 0, 0, 0
+
+    def _check(self, rc: int) -> None:
+        if rc != self._L.LSR_OK:
+            raise self._err(self._L.last_error())
+
+    # -- sink protocol (rasterizer._backward_impl) --
+    def begin_step(self) -> "PeerFactorExchange":
+        """Starts a step: the next `views_per_rank` backward passes write into this step's slot.  Returns the sink."""
+        self.epoch += 1
+        self._count = 0
+        return self
+
+    def new_factor(self, P: int, device, campos: torch.Tensor, degree: int) -> torch.Tensor:
+        if P != self.P or self._count >= self.V:
+            raise self._err(f"PeerFactorExchange: built for {self.V} view(s) of {self.P} Gaussians per step")
+        i, slot = self._count, self._payload[self.epoch & 1]
+        self._count += 1
+        self._degree = int(degree)
+        slot[self.cam_off + 4 * i: self.cam_off + 4 * i + 3].copy_(campos.reshape(3), non_blocking=True)
+        return slot[i * P * 3:(i + 1) * P * 3].view(P, 3)
+
+    def finish(self, means3D: torch.Tensor, n_coeffs: int) -> torch.Tensor:
+        """dL_dsh [P, n_coeffs, 3] summed over the views of all ranks; call once per step, after the backward passes.
+        Every rank must have run the same number (1..views_per_rank) of backward passes since begin_step()."""
+        if self._count == 0:
+            raise self._err("PeerFactorExchange: no view ran a backward this step")
+        L, P, V = self._L, self.P, self._count
+        stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        n = self.world * V
+        g_ptrs, c_ptrs = (ctypes.c_void_p * n)(), (ctypes.c_void_p * n)()
+        off = L.PEER_HEADER_BYTES + (self.epoch & 1) * self.slot_bytes
+        for r in range(self.world):  # rank-major, the order an all-gather would produce
+            for i in range(V):
+                g_ptrs[r * V + i] = self.bases[r] + off + i * P * 12
+                c_ptrs[r * V + i] = self.bases[r] + off + (self.cam_off + 4 * i) * 4
+        out = torch.empty((P, n_coeffs, 3), dtype=torch.float32, device=self.device)
+        m3 = means3D.detach().contiguous()
+        with torch.cuda.device(self.device):
+            self._check(self._lib.lsr_peer_barrier(self.rank, self.world, self._headers, self.epoch & 0xFFFFFFFF,
+                                                   stream))
+            self._check(self._lib.lsr_sh_gradient_from_view_ptrs(P, n_coeffs, self._degree, n,
+                                                                 ctypes.c_void_p(m3.data_ptr()), g_ptrs, c_ptrs,
+                                                                 ctypes.c_void_p(out.data_ptr()), stream))
+        return out
+
+    def check(self) -> None:
+        """Synchronises and raises if a barrier of this rank ever timed out (a peer was missing)."""
+        with torch.cuda.device(self.device):
+            self._check(self._lib.lsr_peer_status(ctypes.c_void_p(self.own), ctypes.c_void_p(
+                torch.cuda.current_stream(self.device).cuda_stream)))
+
+    def close(self) -> None:
+        """Collective: every rank unmaps its peers, then (after a host barrier) frees its own buffer."""
+        if self.own is None:
+            return
+        with torch.cuda.device(self.device):
+            torch.cuda.synchronize(self.device)
+            for p in self._opened:
+                self._lib.lsr_peer_close(ctypes.c_void_p(p))
+            self._opened = []
+            if self.world > 1:
+                dist.barrier(group=self.group)
+            self._payload = None
+            self._lib.lsr_peer_free(ctypes.c_void_p(self.own))
+        self.own = None
+
+
+def make_peer_exchange(P: int, views_per_rank: int, device, group=None) -> Optional[PeerFactorExchange]:
+    """PeerFactorExchange if every rank could map every other rank's buffer, else None on all ranks (no NVLink /
+    IPC between the processes): the caller then uses the all-gather path (`finish_sh_gradients`)."""
+    ex, ok = None, 1
+    try:
+        ex = PeerFactorExchange(P, views_per_rank, device, group)
+    except Exception as e:  # noqa: BLE001 — whatever failed, the decision must be collective
+        ok, ex = 0, None
+        print(f"[langsplat_b200.dist] peer exchange unavailable on this rank: {e}")
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        flag = torch.tensor([ok], dtype=torch.int32, device=device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        if int(flag.item()) == 0 and ex is not None:
+            ex.own and ex._lib.lsr_peer_free(ctypes.c_void_p(ex.own))
+            ex = None
+    return ex

@@ -169,6 +169,16 @@ def _forward_impl(rs: GaussianRasterizationSettings, means3D, sh, colors, lang, 
 _sh_factor_sink = None
 
 
+class ShFactorList(list):
+    """Default sink: one fresh [P,3] tensor per view; entries are (factor, campos, sh_degree).  Any object with this
+    `new_factor` method can serve as a sink (langsplat_b200.dist.PeerFactorExchange hands out peer-visible memory)."""
+
+    def new_factor(self, P: int, device, campos: torch.Tensor, degree: int) -> torch.Tensor:
+        t = torch.empty((P, 3), dtype=torch.float32, device=device)
+        self.append((t, campos, degree))
+        return t
+
+
 def _backward_impl(state, grad_color, grad_feature, need_mask: int, want_sh: bool, sh_factor_out=None):
     lib = L.load()
     P, M, W, H, device = state["P"], state["M"], state["W"], state["H"], state["device"]
@@ -214,9 +224,8 @@ def _backward_impl(state, grad_color, grad_feature, need_mask: int, want_sh: boo
             d_sh = part["sh"].view(P, M, 3)
             g.dL_dsh = d_sh.data_ptr()
         if factored:
-            masked = torch.empty((P, 3), **f32)
+            masked = sh_factor_out.new_factor(P, device, state["keep"][11], int(state["frame"].D))
             g.dL_dcolors_masked = masked.data_ptr()
-            sh_factor_out.append((masked, state["keep"][11], int(state["frame"].D)))
         d_scales = part["scales"].view(P, 3)
         d_rots = part["rots"].view(P, 4)
         g.dL_dscales, g.dL_drotations = d_scales.data_ptr(), d_rots.data_ptr()

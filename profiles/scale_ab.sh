@@ -1,5 +1,6 @@
 #!/usr/bin/env bash
-# Multi-GPU A/B on the box: bench at N ranks with the factored SH-gradient exchange and with the dense all-reduce.
+# Multi-GPU A/B on the box: the 2+-rank peer-exchange check, then bench at N ranks with the three SH-gradient exchanges
+# (factors read from peer memory / NCCL all-gather of factors / dense all-reduce).
 # Usage: bash profiles/scale_ab.sh TAG N [config]
 set -uo pipefail
 TAG="$1"; N="$2"; CFG="${3:-2}"; OUT=gpurun_out/$TAG; mkdir -p "$OUT"
@@ -14,5 +15,11 @@ j = json.load(open(sys.argv[1]))
 print("  %s %.1f  ms/step %.3f  e2e %.1f  launches %s" % (j["unit"], j["value"], j["ms_per_step"], j["e2e"]["value"], j["gpu_launches"]))
 PY
 }
-run factored ""
+if [ "$CFG" = 2 ]; then
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node "$N" --master-addr 127.0.0.1 --master-port 29534 \
+    tests/peer_exchange_check.py > "$OUT/peer_check_n${N}.log" 2>&1
+  echo "peer check rc=$?"; grep -h "PEER_EXCHANGE_OK\|Error\|unavailable" "$OUT/peer_check_n${N}.log" | head -5
+fi
+run peer ""
+run allgather "--allgather-sh-exchange"
 run dense "--dense-sh-exchange"

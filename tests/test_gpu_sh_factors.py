@@ -88,3 +88,117 @@ def test_no_views_and_bad_arguments():
     assert rc == L.LSR_OK
     torch.cuda.synchronize()
     assert float(out.abs().max()) == 0.0
+
+
+# ---- per-view pointers and the peer buffer / barrier (single process; the 2-rank run is tests/peer_exchange_check.py,
+# launched under torchrun by profiles/scale_ab.sh on a multi-GPU box) ----
+def _ptr_array(ptrs):
+    import ctypes
+    return (ctypes.c_void_p * len(ptrs))(*ptrs)
+
+
+def test_view_pointers_equal_contiguous_and_chunking():
+    import ctypes
+    from langsplat_b200 import _lib as L
+    lib = L.load()
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(5)
+    P, V = 3000, 70  # more than LSR_MAX_VIEWS: second chunk accumulates
+    means = torch.randn(P, 3, generator=g).to(dev)
+    cams = (4.0 * torch.randn(V, 3, generator=g)).to(dev)
+    fac = torch.randn(V, P, 3, generator=g)
+    fac[torch.rand(V, P, generator=g) < 0.4] = 0.0  # culled in that view
+    fac = fac.to(dev)
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def contiguous(v0, v1, M=16, D=3):
+        out = torch.empty(P, M, 3, device=dev)
+        rc = lib.lsr_sh_gradient_from_views(P, M, D, v1 - v0, ctypes.c_void_p(means.data_ptr()),
+                                            ctypes.c_void_p(cams[v0:v1].contiguous().data_ptr()),
+                                            ctypes.c_void_p(fac[v0:v1].contiguous().data_ptr()),
+                                            ctypes.c_void_p(out.data_ptr()), stream)
+        assert rc == L.LSR_OK, L.last_error()
+        return out
+
+    def by_pointers(views, M=16, D=3):
+        out = torch.empty(P, M, 3, device=dev)
+        gp = _ptr_array([fac[v].data_ptr() for v in views])
+        cp = _ptr_array([cams[v].data_ptr() for v in views])
+        rc = lib.lsr_sh_gradient_from_view_ptrs(P, M, D, len(views), ctypes.c_void_p(means.data_ptr()), gp, cp,
+                                                ctypes.c_void_p(out.data_ptr()), stream)
+        assert rc == L.LSR_OK, L.last_error()
+        return out
+
+    assert torch.equal(by_pointers(list(range(8))), contiguous(0, 8))  # same kernel, same order
+    assert torch.equal(by_pointers(list(range(8)), M=9, D=2), contiguous(0, 8, M=9, D=2))
+    whole = by_pointers(list(range(V)))
+    parts = contiguous(0, 64) + contiguous(64, V)
+    assert rel_err(whole, parts) <= 1e-6
+    # float64 restatement of basis(dir) (x) g for a handful of Gaussians
+    from test_dist_gloo import _sh_basis
+    idx = torch.arange(0, P, 97)
+    want = np.zeros((len(idx), 16, 3))
+    for v in range(V):
+        d = (means[idx] - cams[v]).double().cpu().numpy()
+        d /= np.linalg.norm(d, axis=1, keepdims=True)
+        want += _sh_basis(d)[:, :, None] * fac[v, idx].double().cpu().numpy()[:, None, :]
+    assert rel_err(whole[idx], want) <= 1e-5
+    bad = _ptr_array([fac[0].data_ptr(), 0])
+    rc = lib.lsr_sh_gradient_from_view_ptrs(P, 16, 3, 2, ctypes.c_void_p(means.data_ptr()), bad, bad,
+                                            ctypes.c_void_p(whole.data_ptr()), stream)
+    assert rc != L.LSR_OK and "view 1" in L.last_error()
+
+
+def test_peer_barrier_two_ranks_on_two_streams_and_timeout():
+    import ctypes
+    from langsplat_b200 import _lib as L
+    lib = L.load()
+    bufs, hnd = [], (ctypes.c_uint8 * L.PEER_HANDLE_BYTES)()
+    for _ in range(2):
+        p = ctypes.c_void_p()
+        assert lib.lsr_peer_alloc(4096, ctypes.byref(p), hnd) == L.LSR_OK, L.last_error()
+        bufs.append(p.value)
+    assert any(hnd)  # a real IPC handle came back
+    headers = _ptr_array(bufs)
+    s0, s1 = torch.cuda.Stream(), torch.cuda.Stream()
+    for epoch in (1, 2, 3):  # both "ranks" arrive (two streams of one device): the barrier completes
+        assert lib.lsr_peer_barrier(0, 2, headers, epoch, ctypes.c_void_p(s0.cuda_stream)) == L.LSR_OK
+        assert lib.lsr_peer_barrier(1, 2, headers, epoch, ctypes.c_void_p(s1.cuda_stream)) == L.LSR_OK
+    torch.cuda.synchronize()
+    for r in (0, 1):
+        assert lib.lsr_peer_status(ctypes.c_void_p(bufs[r]), None) == L.LSR_OK
+    # rank 1 never arrives at epoch 4: rank 0 gives up after the time-out instead of hanging the device
+    assert lib.lsr_peer_barrier(0, 2, headers, 4, ctypes.c_void_p(s0.cuda_stream)) == L.LSR_OK
+    torch.cuda.synchronize()
+    assert lib.lsr_peer_status(ctypes.c_void_p(bufs[0]), None) != L.LSR_OK and "timed out" in L.last_error()
+    assert lib.lsr_peer_barrier(0, 17, headers, 5, None) != L.LSR_OK
+    assert lib.lsr_peer_barrier(2, 2, headers, 5, None) != L.LSR_OK
+    for b in bufs:
+        assert lib.lsr_peer_free(ctypes.c_void_p(b)) == L.LSR_OK
+
+
+def test_peer_exchange_single_rank_equals_list_sink():
+    dev = torch.device("cuda:0")
+    scene, cams = syn.make_config(4, P=8000, W=160, H=120, n_cameras=2)
+    listed = _step(scene, cams, dev, 3, factored=True)
+    ex = D.PeerFactorExchange(8000, 2, dev)
+    try:
+        for _ in range(3):  # slots alternate; every step must give the same answer
+            params = {k: scene[k].to(dev).requires_grad_(True) for k in NAMES}
+            means2D = torch.zeros_like(params["means3D"], requires_grad=True)
+            with D.factored_sh_gradients(ex.begin_step()):
+                for i, cam in enumerate(cams):
+                    dcol, dfeat = [t.to(dev) for t in syn.make_grads(cam.image_width, cam.image_height, 300 + i)]
+                    rast = R.GaussianRasterizer(settings_for(cam, dev, sh_degree=3))
+                    color, feat, radii = rast(means3D=params["means3D"], means2D=means2D, shs=params["shs"],
+                                              language_feature_precomp=params["language_feature"],
+                                              opacities=params["opacities"], scales=params["scales"],
+                                              rotations=params["rotations"])
+                    torch.autograd.backward([color, feat], [dcol, dfeat])
+            got = ex.finish(params["means3D"], 16)
+            assert rel_err(got, listed["shs"]) <= 1e-5
+        ex.check()
+        with pytest.raises(R.LsrError):
+            ex.begin_step().finish(params["means3D"], 16)  # no backward ran
+    finally:
+        ex.close()
