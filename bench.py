@@ -589,9 +589,84 @@ def main():
                                     "peak_source": src}
     elif stages:
         line["stages"] = {k: {"ms": v} for k, v in stages.items()}
+    if world == 1 and not fwd_only:
+        line["adjacent"] = adjacent_ops(P, W, H, dev, hbm)
     emit(line)
     if world > 1:
         dist.destroy_process_group()
+
+
+def adjacent_ops(P, W, H, dev, hbm_peak):
+    """The fused steps on either side of the path, each timed fwd+bwd with CUDA events next to the
+    PyTorch expressions LangSplat runs today (scene/gaussian_model.py:134-155, gaussian_renderer/__init__.py:86-88,
+    train.py:96-99).  Not part of `value` / `e2e`; HBM-bound, so the fraction is algorithmic bytes / time / peak."""
+    from langsplat_b200 import activate, l1_loss
+    g = torch.Generator().manual_seed(5)
+    raw = [t.to(dev).requires_grad_(True) for t in (torch.randn(P, 3, generator=g) - 3.0, torch.randn(P, 4, generator=g),
+                                                     torch.randn(P, 1, generator=g), torch.randn(P, 3, generator=g))]
+    ups = [torch.randn(t.shape, device=dev) for t in raw]
+    pred = torch.rand(3, H, W, device=dev, requires_grad=True)
+    gt, mask = torch.rand(3, H, W, device=dev), (torch.rand(1, H, W, device=dev) > 0.3).float()
+
+    def act_ours():
+        torch.autograd.backward(list(activate(*raw)), ups)
+
+    def act_torch():
+        f = raw[3]
+        outs = [torch.exp(raw[0]), torch.nn.functional.normalize(raw[1]), torch.sigmoid(raw[2]),
+                f / (f.norm(dim=-1, keepdim=True) + 1e-9)]
+        torch.autograd.backward(outs, ups)
+
+    def loss_ours():
+        l1_loss(pred, gt, mask).backward()
+
+    def loss_torch():
+        torch.abs(pred * mask - gt * mask).mean().backward()
+
+    def timed(fn, n=20):
+        for _ in range(3):
+            fn()
+        for t in raw + [pred]:
+            t.grad = None
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(n):
+            fn()
+            for t in raw + [pred]:
+                t.grad = None
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n * 1e3
+
+    # the kernels alone, back to back through the C ABI (the host enqueues faster than they run)
+    from langsplat_b200 import _lib
+    lib = _lib.load()
+    vp = lambda t: ctypes.c_void_p(t.data_ptr())  # noqa: E731
+    st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    d_raw = [t.detach() for t in raw]
+    outs, grads = [torch.empty_like(t) for t in d_raw], [torch.empty_like(t) for t in d_raw]
+    loss, one, d_pred = torch.empty((), device=dev), torch.ones((), device=dev), torch.empty(3, H, W, device=dev)
+    p0, N = pred.detach(), W * H
+
+    def act_kernels():
+        lib.lsr_activate_forward(P, *[vp(t) for t in d_raw], *[vp(t) for t in outs], st)
+        lib.lsr_activate_backward(P, *[vp(t) for t in d_raw], *[vp(t) for t in ups], *[vp(t) for t in grads], st)
+
+    def loss_kernels():
+        lib.lsr_l1_loss_forward(vp(p0), vp(gt), vp(mask), 3, N, vp(loss), st)
+        lib.lsr_l1_loss_backward(vp(p0), vp(gt), vp(mask), 3, N, vp(one), vp(d_pred), st)
+
+    act_bytes = P * (44 + 44) + P * (44 + 44 + 44)  # fwd: raw in, activated out; bwd: raw + upstream in, grads out
+    loss_bytes = W * H * (3 * 8 + 4) + W * H * (3 * 12 + 4)
+    a, at, l, lt = timed(act_ours), timed(act_torch), timed(loss_ours), timed(loss_torch)
+    ak, lk = timed(act_kernels, 50), timed(loss_kernels, 50)
+    return {"activate_fwd_bwd": {"kernels_us": ak, "autograd_us": a, "torch_us": at, "bytes": act_bytes,
+                                 "hbm_frac": act_bytes / (ak * 1e-6) / 1e9 / hbm_peak},
+            "masked_l1_fwd_bwd": {"kernels_us": lk, "autograd_us": l, "torch_us": lt, "bytes": loss_bytes,
+                                  "hbm_frac": loss_bytes / (lk * 1e-6) / 1e9 / hbm_peak},
+            "note": "kernels_us: the two kernels back to back through the C ABI; autograd_us / torch_us: the Python "
+                    "call sequence on one stream (host-bound at this size), CUDA events"}
 
 
 if __name__ == "__main__":

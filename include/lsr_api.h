@@ -200,6 +200,22 @@ int lsr_l1_loss_forward(const float* pred, const float* gt, const float* mask, i
 int lsr_l1_loss_backward(const float* pred, const float* gt, const float* mask, int32_t C, int64_t N,
                          const float* grad_out, float* dL_dpred, void* stream);
 
+/* Fused per-Gaussian activations in front of the rasterizer: scales = exp(scaling)
+ * (scene/gaussian_model.py:33,134-136), rotations = normalize(rotation) = q / max(||q||, 1e-12) (:40,138-140),
+ * opacities = sigmoid(opacity) (:37,153-155), language feature f / (||f|| + 1e-9)
+ * (gaussian_renderer/__init__.py:86-88).  scaling [P,3], rotation [P,4] (16-byte aligned), opacity [P,1],
+ * feature [P,3]; an input given as null is skipped together with its output. */
+int lsr_activate_forward(int32_t P, const float* scaling, const float* rotation, const float* opacity,
+                         const float* feature, float* scales_out, float* rotations_out, float* opacities_out,
+                         float* feature_out, void* stream);
+/* Gradients w.r.t. the raw parameters from the gradients w.r.t. the activated ones (recomputed from the raw inputs,
+ * nothing saved by the forward).  A quantity is processed when its d_* output is non-null; its raw input and its
+ * upstream gradient g_* must then be given. */
+int lsr_activate_backward(int32_t P, const float* scaling, const float* rotation, const float* opacity,
+                          const float* feature, const float* g_scales, const float* g_rotations,
+                          const float* g_opacities, const float* g_feature, float* d_scaling, float* d_rotation,
+                          float* d_opacity, float* d_feature, void* stream);
+
 /* Stable ascending radix sort of (uint64 key, uint32 value) pairs on bits [0, end_bit) — the sort the forward uses
  * in place of cub::DeviceRadixSort::SortPairs (rasterizer_impl.cu:306-311); exported for unit tests.
  * keys_tmp / vals_tmp are n-sized ping-pong buffers; result lands in keys_out / vals_out.

@@ -8,6 +8,7 @@ liblsr.so is missing (there is no CPU fallback).
 from .rasterizer import (GaussianRasterizationSettings, GaussianRasterizer, LsrError, rasterize_gaussians,
                          cpu_deep_copy_tuple)
 from .loss import l1_loss
+from .activations import activate
 
 __all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians", "LsrError",
-           "cpu_deep_copy_tuple", "l1_loss"]
+           "cpu_deep_copy_tuple", "l1_loss", "activate"]

@@ -69,6 +69,8 @@ EXPORTS = {
     "lsr_peer_free": (c_int, [c_void_p]),
     "lsr_peer_barrier": (c_int, [c_int32, c_int32, POINTER(c_void_p), c_uint32, c_void_p]),
     "lsr_peer_status": (c_int, [c_void_p, c_void_p]),
+    "lsr_activate_forward": (c_int, [c_int32] + [c_void_p] * 9),
+    "lsr_activate_backward": (c_int, [c_int32] + [c_void_p] * 13),
     "lsr_mark_visible": (c_int, [c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "lsr_l1_loss_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_int32, c_int64, c_void_p, c_void_p]),
     "lsr_l1_loss_backward": (c_int, [c_void_p, c_void_p, c_void_p, c_int32, c_int64, c_void_p, c_void_p, c_void_p]),

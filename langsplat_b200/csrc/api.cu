@@ -247,6 +247,39 @@ int lsr_peer_status(const void* own_buffer, void* stream) {
   return LSR_OK;
 }
 
+int lsr_activate_forward(int32_t P, const float* scaling, const float* rotation, const float* opacity,
+                         const float* feature, float* scales_out, float* rotations_out, float* opacities_out,
+                         float* feature_out, void* stream) {
+  if (P < 0) return fail(LSR_ERR_INVALID, "P < 0");
+  if (P == 0) return LSR_OK;
+  if ((scaling && !scales_out) || (rotation && !rotations_out) || (opacity && !opacities_out) ||
+      (feature && !feature_out))
+    return fail(LSR_ERR_INVALID, "an input is given without its output");
+  if (rotation && ((((uintptr_t)rotation) | ((uintptr_t)rotations_out)) & 15))
+    return fail(LSR_ERR_INVALID, "rotation tensors must be 16-byte aligned");
+  launch_activate_forward(P, scaling, rotation, opacity, feature, scales_out, rotations_out, opacities_out,
+                          feature_out, (cudaStream_t)stream);
+  LSR_CUDA(cudaGetLastError());
+  return LSR_OK;
+}
+
+int lsr_activate_backward(int32_t P, const float* scaling, const float* rotation, const float* opacity,
+                          const float* feature, const float* g_scales, const float* g_rotations,
+                          const float* g_opacities, const float* g_feature, float* d_scaling, float* d_rotation,
+                          float* d_opacity, float* d_feature, void* stream) {
+  if (P < 0) return fail(LSR_ERR_INVALID, "P < 0");
+  if (P == 0) return LSR_OK;
+  if ((d_scaling && (!scaling || !g_scales)) || (d_rotation && (!rotation || !g_rotations)) ||
+      (d_opacity && (!opacity || !g_opacities)) || (d_feature && (!feature || !g_feature)))
+    return fail(LSR_ERR_INVALID, "a gradient is requested without its raw input or upstream gradient");
+  if (d_rotation && ((((uintptr_t)rotation) | ((uintptr_t)g_rotations) | ((uintptr_t)d_rotation)) & 15))
+    return fail(LSR_ERR_INVALID, "rotation tensors must be 16-byte aligned");
+  launch_activate_backward(P, scaling, rotation, opacity, feature, g_scales, g_rotations, g_opacities, g_feature,
+                           d_scaling, d_rotation, d_opacity, d_feature, (cudaStream_t)stream);
+  LSR_CUDA(cudaGetLastError());
+  return LSR_OK;
+}
+
 int lsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, void* stream) {
   (void)projmatrix;  // the reference's in_frustum computes p_proj but only tests p_view.z (auxiliary.h:139-164)

@@ -204,6 +204,13 @@ void launch_sh_grad_view_ptrs(int P, int D, int M, int V, const float* means3D, 
                               const float* const* campos_views, float* dL_dsh, cudaStream_t s);
 // cross-GPU barrier on the stream (peer.cu): signals `epoch` into every peer's header, waits for all of them
 void launch_peer_barrier(int rank, int world, void* const* headers, uint32_t epoch, cudaStream_t s);
+void launch_activate_forward(int P, const float* scaling, const float* rotation, const float* opacity,
+                             const float* feature, float* scales_out, float* rotations_out, float* opacities_out,
+                             float* feature_out, cudaStream_t s);
+void launch_activate_backward(int P, const float* scaling, const float* rotation, const float* opacity,
+                              const float* feature, const float* g_scales, const float* g_rotations,
+                              const float* g_opacities, const float* g_feature, float* d_scaling, float* d_rotation,
+                              float* d_opacity, float* d_feature, cudaStream_t s);
 void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, uint8_t* present, cudaStream_t s);
 
 // loss.cu: fused (masked) L1 loss forward / backward on [C,N] images

@@ -206,3 +206,52 @@ def l1_loss_grad(network_output, gt, mask=None, grad_out: float = 1.0) -> np.nda
     d = (x * m - g * m).astype(np.float32)
     scale = np.float32(np.float32(grad_out) * np.float32(1.0 / max(d.size, 1)))
     return (scale * np.sign(d) * m).astype(np.float32)
+
+
+# ---- activations in front of the rasterizer -----------------------------------------------------
+def activate(scaling=None, rotation=None, opacity=None, language_feature=None):
+    """(exp(scaling), normalize(rotation), sigmoid(opacity), f / (||f|| + 1e-9)) in float32:
+    scene/gaussian_model.py:33,37,40 (torch.exp, torch.sigmoid, F.normalize with eps 1e-12) as read by
+    get_scaling / get_rotation / get_opacity (:134-155), and gaussian_renderer/__init__.py:86-88.  None -> None."""
+    f32 = np.float32
+    out = [None, None, None, None]
+    if scaling is not None:
+        out[0] = np.exp(np.asarray(scaling, f32)).astype(f32)
+    if rotation is not None:
+        q = np.asarray(rotation, f32)
+        n = np.sqrt((q * q).sum(axis=1, keepdims=True, dtype=f32)).astype(f32)
+        out[1] = (q / np.maximum(n, f32(1e-12))).astype(f32)
+    if opacity is not None:
+        x = np.asarray(opacity, f32)
+        with np.errstate(over="ignore"):  # exp(-x) -> inf for very negative x, sigmoid -> 0 as in PyTorch
+            out[2] = (f32(1) / (f32(1) + np.exp(-x).astype(f32))).astype(f32)
+    if language_feature is not None:
+        f = np.asarray(language_feature, f32)
+        n = np.sqrt((f * f).sum(axis=1, keepdims=True, dtype=f32)).astype(f32)
+        out[3] = (f / (n + f32(1e-9))).astype(f32)
+    return tuple(out)
+
+
+def activate_grad(scaling=None, rotation=None, opacity=None, language_feature=None, g_scales=None, g_rotations=None,
+                  g_opacities=None, g_feature=None):
+    """Gradients of `activate` w.r.t. the raw parameters (float64 inside, float32 out), as autograd derives them from
+    the reference expressions: clamp_min passes the gradient where ||q|| >= eps; norm's backward is 0 at ||f|| = 0."""
+    out = [None, None, None, None]
+    if scaling is not None and g_scales is not None:
+        out[0] = (np.asarray(g_scales, np.float64) * np.exp(np.asarray(scaling, np.float64))).astype(np.float32)
+    if rotation is not None and g_rotations is not None:
+        q, g = np.asarray(rotation, np.float64), np.asarray(g_rotations, np.float64)
+        n = np.sqrt((q * q).sum(axis=1, keepdims=True))
+        d = np.maximum(n, 1e-12)
+        k = np.where(n >= 1e-12, (g * q).sum(axis=1, keepdims=True) / (d * d * np.where(n > 0, n, 1.0)), 0.0)
+        out[1] = (g / d - q * k).astype(np.float32)
+    if opacity is not None and g_opacities is not None:
+        y = 1.0 / (1.0 + np.exp(-np.asarray(opacity, np.float64)))
+        out[2] = (np.asarray(g_opacities, np.float64) * y * (1.0 - y)).astype(np.float32)
+    if language_feature is not None and g_feature is not None:
+        f, g = np.asarray(language_feature, np.float64), np.asarray(g_feature, np.float64)
+        n = np.sqrt((f * f).sum(axis=1, keepdims=True))
+        d = n + 1e-9
+        k = np.where(n > 0, (g * f).sum(axis=1, keepdims=True) / (d * d * np.where(n > 0, n, 1.0)), 0.0)
+        out[3] = (g / d - f * k).astype(np.float32)
+    return tuple(out)
