@@ -657,11 +657,53 @@ def adjacent_ops(P, W, H, dev, hbm_peak):
         lib.lsr_l1_loss_forward(vp(p0), vp(gt), vp(mask), 3, N, vp(loss), st)
         lib.lsr_l1_loss_backward(vp(p0), vp(gt), vp(mask), 3, N, vp(one), vp(d_pred), st)
 
+    # Adam over the six RGB-mode groups (59 floats per Gaussian), fused vs torch.optim.Adam as the reference builds it
+    from langsplat_b200.optim import FusedAdam
+    shapes = [(P, 3), (P, 1, 3), (P, 15, 3), (P, 1), (P, 3), (P, 4)]
+
+    def make_opt(cls):
+        ps = [torch.nn.Parameter(torch.randn(s_, device=dev)) for s_ in shapes]
+        for q in ps:
+            q.grad = torch.randn_like(q) * 0.01
+        return cls([{"params": [q], "lr": 1e-3} for q in ps], lr=0.0, eps=1e-15)
+
+    o_ours, o_torch = make_opt(FusedAdam), make_opt(torch.optim.Adam)
+    adam_bytes = 59 * P * 28
+    # ground-truth feature map of one camera: gather on the GPU vs the reference's CPU gather + upload
+    from langsplat_b200.gt_features import language_feature_map
+    K = 300
+    seg_h = torch.randint(-1, K, (4, H, W), generator=g).float()
+    table_h = torch.randn(K, 3, generator=g)
+    seg_d, table_d = seg_h.to(dev), table_h.to(dev)
+
+    def gt_ours():
+        language_feature_map(seg_d, table_d, 1, H, W, validate=False)
+
+    def gt_reference_cpu():  # scene/cameras.py:58-92 restated with the same torch calls, on the host, then .cuda()
+        y, x = torch.meshgrid(torch.arange(0, H), torch.arange(0, W), indexing="ij")
+        seg = seg_h[:, y.reshape(-1, 1), x.reshape(-1, 1)].squeeze(-1).long()
+        mask = (seg != -1)[1:2].reshape(1, H, W)
+        pf = table_h[seg[1:2]].squeeze(0).reshape(H, W, -1).permute(2, 0, 1)
+        return pf.to(dev), mask.to(dev)
+
+    import time as _time
+    torch.cuda.synchronize()
+    t0 = _time.perf_counter()
+    gt_reference_cpu()
+    torch.cuda.synchronize()
+    gt_ref_ms = (_time.perf_counter() - t0) * 1e3
+    gt_bytes = W * H * (4 + 12 + 1)
+
     act_bytes = P * (44 + 44) + P * (44 + 44 + 44)  # fwd: raw in, activated out; bwd: raw + upstream in, grads out
     loss_bytes = W * H * (3 * 8 + 4) + W * H * (3 * 12 + 4)
     a, at, l, lt = timed(act_ours), timed(act_torch), timed(loss_ours), timed(loss_torch)
     ak, lk = timed(act_kernels, 50), timed(loss_kernels, 50)
-    return {"activate_fwd_bwd": {"kernels_us": ak, "autograd_us": a, "torch_us": at, "bytes": act_bytes,
+    ad, adt, gtk = timed(o_ours.step), timed(o_torch.step), timed(gt_ours, 50)
+    return {"adam_step": {"us": ad, "torch_us": adt, "bytes": adam_bytes,
+                          "hbm_frac": adam_bytes / (ad * 1e-6) / 1e9 / hbm_peak},
+            "gt_feature_map": {"us": gtk, "reference_cpu_ms": gt_ref_ms, "bytes": gt_bytes,
+                               "hbm_frac": gt_bytes / (gtk * 1e-6) / 1e9 / hbm_peak},
+            "activate_fwd_bwd": {"kernels_us": ak, "autograd_us": a, "torch_us": at, "bytes": act_bytes,
                                  "hbm_frac": act_bytes / (ak * 1e-6) / 1e9 / hbm_peak},
             "masked_l1_fwd_bwd": {"kernels_us": lk, "autograd_us": l, "torch_us": lt, "bytes": loss_bytes,
                                   "hbm_frac": loss_bytes / (lk * 1e-6) / 1e9 / hbm_peak},

@@ -216,6 +216,36 @@ int lsr_activate_backward(int32_t P, const float* scaling, const float* rotation
                           const float* g_opacities, const float* g_feature, float* d_scaling, float* d_rotation,
                           float* d_opacity, float* d_feature, void* stream);
 
+/* Ground-truth language-feature map of one camera and level (replaces the CPU gather of
+ * Camera.get_language_feature, scene/cameras.py:58-92).  seg: one level of the seg map, H rows of W values
+ * (float32 as preprocess.py:120,173 saves it, or int32), consecutive rows seg_row_stride elements apart (a larger map
+ * is cropped to its top-left H x W like the reference's meshgrid does); table: feature_map [K,C].
+ * out [C,H,W] = table[seg] (index -1 selects the last row, as the reference's negative index does),
+ * mask_u8 / mask_f [H,W] = (seg != -1), either may be null.  *bad (device int, may be null; caller zeroes it) counts
+ * indices outside [-K, K), for which PyTorch would raise; those pixels get zeros. */
+int lsr_language_feature_map(const void* seg, int32_t seg_is_float, int64_t seg_row_stride, int32_t width,
+                             int32_t height, const float* table, int32_t K, int32_t C, float* out, uint8_t* mask_u8,
+                             float* mask_f, int32_t* bad, void* stream);
+
+/* Fused Adam step over all parameter groups in one launch (replaces optimizer.step() of
+ * torch.optim.Adam(l, lr=0.0, eps=1e-15), scene/gaussian_model.py:198-227, train.py:136-138).  PyTorch's single-tensor
+ * Adam arithmetic (amsgrad off, no weight decay); `step` is the 1-based step count AFTER the increment (PyTorch's
+ * state['step']).  Each tensor: param / exp_avg / exp_avg_sq updated in place from grad, `numel` floats, its own lr;
+ * row_width = floats per Gaussian (used only with `visible`).  visible [P] uint8 or null: when given, only rows of
+ * visible Gaussians are updated, moments included ("sparse Adam"); null = the reference's dense step. */
+#define LSR_ADAM_MAX_TENSORS 8
+typedef struct lsr_adam_tensor {
+  float* param;
+  const float* grad;
+  float* exp_avg;
+  float* exp_avg_sq;
+  int64_t numel;
+  int32_t row_width;
+  float lr;
+} lsr_adam_tensor;
+int lsr_adam_step(int32_t n_tensors, const lsr_adam_tensor* tensors, int64_t step, double beta1, double beta2,
+                  double eps, const uint8_t* visible, void* stream);
+
 /* Stable ascending radix sort of (uint64 key, uint32 value) pairs on bits [0, end_bit) — the sort the forward uses
  * in place of cub::DeviceRadixSort::SortPairs (rasterizer_impl.cu:306-311); exported for unit tests.
  * keys_tmp / vals_tmp are n-sized ping-pong buffers; result lands in keys_out / vals_out.

@@ -8,7 +8,8 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_int32, c_int64, c_size_t, c_uint32, c_uint64, c_void_p
+from ctypes import (POINTER, Structure, c_char_p, c_double, c_float, c_int, c_int32, c_int64, c_size_t, c_uint32,
+                    c_uint64, c_void_p)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "liblsr.so")
@@ -47,6 +48,13 @@ class Grads(Structure):
 
 PEER_HANDLE_BYTES, PEER_HEADER_BYTES, MAX_PEERS, MAX_VIEWS = 64, 256, 16, 64  # include/lsr_api.h
 
+class AdamTensor(ctypes.Structure):  # lsr_adam_tensor
+    _fields_ = [("param", c_void_p), ("grad", c_void_p), ("exp_avg", c_void_p), ("exp_avg_sq", c_void_p),
+                ("numel", c_int64), ("row_width", c_int32), ("lr", ctypes.c_float)]
+
+
+ADAM_MAX_TENSORS = 8
+
 EXPORTS = {
     "lsr_geom_bytes": (c_size_t, [c_int32]),
     "lsr_image_bytes": (c_size_t, [c_int32, c_int32]),
@@ -71,6 +79,9 @@ EXPORTS = {
     "lsr_peer_status": (c_int, [c_void_p, c_void_p]),
     "lsr_activate_forward": (c_int, [c_int32] + [c_void_p] * 9),
     "lsr_activate_backward": (c_int, [c_int32] + [c_void_p] * 13),
+    "lsr_language_feature_map": (c_int, [c_void_p, c_int32, c_int64, c_int32, c_int32, c_void_p, c_int32, c_int32,
+                                         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "lsr_adam_step": (c_int, [c_int32, c_void_p, c_int64, c_double, c_double, c_double, c_void_p, c_void_p]),
     "lsr_mark_visible": (c_int, [c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "lsr_l1_loss_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_int32, c_int64, c_void_p, c_void_p]),
     "lsr_l1_loss_backward": (c_int, [c_void_p, c_void_p, c_void_p, c_int32, c_int64, c_void_p, c_void_p, c_void_p]),

@@ -280,6 +280,40 @@ int lsr_activate_backward(int32_t P, const float* scaling, const float* rotation
   return LSR_OK;
 }
 
+int lsr_language_feature_map(const void* seg, int32_t seg_is_float, int64_t seg_row_stride, int32_t width,
+                             int32_t height, const float* table, int32_t K, int32_t C, float* out, uint8_t* mask_u8,
+                             float* mask_f, int32_t* bad, void* stream) {
+  if (width < 0 || height < 0 || K < 1 || C < 1 || seg_row_stride < width)
+    return fail(LSR_ERR_INVALID, "bad size (K and C must be >= 1, seg_row_stride >= width)");
+  if ((int64_t)width * height == 0) return LSR_OK;
+  if (!seg || !table || !out) return fail(LSR_ERR_INVALID, "null pointer");
+  launch_feature_map(seg, seg_is_float, seg_row_stride, width, height, table, K, C, out, mask_u8, mask_f, bad,
+                     (cudaStream_t)stream);
+  LSR_CUDA(cudaGetLastError());
+  return LSR_OK;
+}
+
+int lsr_adam_step(int32_t n_tensors, const lsr_adam_tensor* tensors, int64_t step, double beta1, double beta2,
+                  double eps, const uint8_t* visible, void* stream) {
+  if (n_tensors < 0 || n_tensors > LSR_ADAM_MAX_TENSORS)
+    return fail(LSR_ERR_INVALID, "at most %d tensors per call", LSR_ADAM_MAX_TENSORS);
+  if (step < 1) return fail(LSR_ERR_INVALID, "step must be >= 1 (the count after this step)");
+  if (!(beta1 >= 0.0 && beta1 < 1.0) || !(beta2 >= 0.0 && beta2 < 1.0) || !(eps >= 0.0))
+    return fail(LSR_ERR_INVALID, "bad betas / eps");
+  if (n_tensors > 0 && !tensors) return fail(LSR_ERR_INVALID, "null pointer");
+  for (int i = 0; i < n_tensors; i++) {
+    const lsr_adam_tensor& t = tensors[i];
+    if (t.numel < 0) return fail(LSR_ERR_INVALID, "tensor %d: numel < 0", i);
+    if (t.numel > 0 && (!t.param || !t.grad || !t.exp_avg || !t.exp_avg_sq))
+      return fail(LSR_ERR_INVALID, "tensor %d: null pointer", i);
+    if (visible && t.numel > 0 && (t.row_width < 1 || t.numel % t.row_width))
+      return fail(LSR_ERR_INVALID, "tensor %d: numel is not a multiple of row_width", i);
+  }
+  launch_adam(n_tensors, tensors, step, beta1, beta2, eps, visible, (cudaStream_t)stream);
+  LSR_CUDA(cudaGetLastError());
+  return LSR_OK;
+}
+
 int lsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, void* stream) {
   (void)projmatrix;  // the reference's in_frustum computes p_proj but only tests p_view.z (auxiliary.h:139-164)

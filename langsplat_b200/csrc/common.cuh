@@ -211,6 +211,10 @@ void launch_activate_backward(int P, const float* scaling, const float* rotation
                               const float* feature, const float* g_scales, const float* g_rotations,
                               const float* g_opacities, const float* g_feature, float* d_scaling, float* d_rotation,
                               float* d_opacity, float* d_feature, cudaStream_t s);
+void launch_feature_map(const void* seg, int seg_is_float, int64_t seg_row_stride, int W, int H, const float* table,
+                        int K, int C, float* out, uint8_t* mask_u8, float* mask_f, int* bad, cudaStream_t s);
+void launch_adam(int n, const lsr_adam_tensor* ts, int64_t step, double beta1, double beta2, double eps,
+                 const uint8_t* visible, cudaStream_t s);
 void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, uint8_t* present, cudaStream_t s);
 
 // loss.cu: fused (masked) L1 loss forward / backward on [C,N] images

@@ -255,3 +255,36 @@ def activate_grad(scaling=None, rotation=None, opacity=None, language_feature=No
         k = np.where(n > 0, (g * f).sum(axis=1, keepdims=True) / (d * d * np.where(n > 0, n, 1.0)), 0.0)
         out[3] = (g / d - f * k).astype(np.float32)
     return tuple(out)
+
+
+# ---- ground-truth language-feature map ----------------------------------------------------------
+def language_feature_map(seg_map, feature_map, feature_level, image_height, image_width):
+    """scene/cameras.py:58-92: seg = seg_map[:, y, x].long() over the image's meshgrid (the top-left H x W of the map),
+    mask = seg != -1, point_feature = feature_map[seg[level]] as [C,H,W] (numpy's negative index wraps like torch's:
+    -1 selects the last row).  Returns (point_feature float32 [C,H,W], mask bool [1,H,W])."""
+    if feature_level not in (0, 1, 2, 3):
+        raise ValueError("feature_level=", feature_level)
+    seg = np.asarray(seg_map)[feature_level, :image_height, :image_width]
+    seg = np.trunc(seg).astype(np.int64)  # .long() truncates toward zero
+    mask = (seg != -1)[None]
+    feat = np.asarray(feature_map, np.float32)[seg]  # [H,W,C]; raises IndexError outside [-K, K)
+    return np.ascontiguousarray(feat.transpose(2, 0, 1)), mask
+
+
+# ---- Adam step (SURVEY 8(f) row 3) ----------------------------------------------------------------------------------
+def adam_step(param, grad, exp_avg, exp_avg_sq, step, lr, beta1=0.9, beta2=0.999, eps=1e-15, visible=None):
+    """One torch.optim.Adam step (torch/optim/adam.py _single_tensor_adam: amsgrad off, no weight decay) as the
+    reference configures it (scene/gaussian_model.py:227: Adam(l, lr=0.0, eps=1e-15), per-group lr), in float64.
+    `step` is the count after the increment.  visible [P] bool: rows not visible keep param and moments.
+    Returns (param, exp_avg, exp_avg_sq) as float64 arrays."""
+    p, g = np.asarray(param, np.float64), np.asarray(grad, np.float64)
+    m0, v0 = np.asarray(exp_avg, np.float64), np.asarray(exp_avg_sq, np.float64)
+    m = m0 + (g - m0) * (1.0 - beta1)
+    v = v0 * beta2 + (1.0 - beta2) * g * g
+    bc1, bc2 = 1.0 - beta1 ** step, 1.0 - beta2 ** step
+    denom = np.sqrt(v) / np.sqrt(bc2) + eps
+    new = p - (lr / bc1) * (m / denom)
+    if visible is not None:
+        on = np.asarray(visible, bool).reshape((-1,) + (1,) * (p.ndim - 1))
+        new, m, v = np.where(on, new, p), np.where(on, m, m0), np.where(on, v, v0)
+    return new, m, v
