@@ -12,6 +12,9 @@ constexpr int TILE_PIX = TILE_X * TILE_Y;
 
 // render_bwd accumulates pair-weighted moments instead of the six geometric gradient sums, preprocess_bwd applies the
 // per-Gaussian coefficients (see render_bwd.cu).  0 restores the direct sums (A/B measurements).
+#ifndef LSR_FWD_PK
+#define LSR_FWD_PK 1  // forward blend: both pixels of a thread through packed fp32 (FFMA2) instructions
+#endif
 #ifndef LSR_MOMENTS
 #define LSR_MOMENTS 1
 #endif

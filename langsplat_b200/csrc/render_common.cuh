@@ -23,6 +23,8 @@
 // batch in shared memory instead of 13 registers was measured: 64 registers and 32 warps per SM, but render_bwd went
 // from 852 to 875 us — the extra wait + LDS round trip per batch costs more than the occupancy buys.)
 #pragma once
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace lsr {
@@ -39,6 +41,42 @@ struct WarpBatch {
   float4 C[32];  // r, g, b, f0
   float4 D[32];  // f1, f2, gaussian id (uint bits), unused
 };
+
+// Packed layout for the forward blend: sm_100 issues two independent IEEE fp32 FMAs as one instruction
+// (fma.rn.f32x2 -> FFMA2).  A thread's two pixels share x and every per-Gaussian constant, so the constants are stored
+// already duplicated: each 64-bit half of a float4 is directly a packed operand and no broadcast MOVs are needed.
+struct WarpBatchPk {
+  float4 A[32];  // x, x, y, y
+  float4 Q[32];  // conic.x, conic.x, -conic.y, -conic.y
+  float4 B[32];  // conic.z, conic.z, thr_m, opacity
+  float4 C[32];  // r, g, b, f0
+  float4 D[32];  // f1, f2, position in the tile list (uint bits), gaussian id (uint bits)
+};
+
+typedef unsigned long long f32x2;  // two floats in one 64-bit register pair: lo = slot 0, hi = slot 1
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void upk2(f32x2 v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
 
 constexpr float kAlphaMin = 1.0f / 255.0f;
 
@@ -122,7 +160,8 @@ __device__ __forceinline__ Fetched fetch_instance(const uint32_t* __restrict__ l
 // Tests the warp's 32 fetched instances against the quadrant whose first pixel is (X0, Y0) and writes the survivors
 // to shared memory in lane order.  Returns their number (identical in all lanes).  All 32 lanes must call it, after a
 // __syncwarp() that ends the reads of the previous batch; it ends with a __syncwarp().
-__device__ __forceinline__ int commit_batch(WarpBatch& sm, const Fetched& f, float X0, float Y0) {
+template <typename Batch>
+__device__ __forceinline__ int commit_batch(Batch& sm, const Fetched& f, float X0, float Y0) {
   const int lane = threadIdx.x & 31;
   bool keep = false;
   float thr_m = 0.f;
@@ -140,10 +179,18 @@ __device__ __forceinline__ int commit_batch(WarpBatch& sm, const Fetched& f, flo
   const uint32_t m = __ballot_sync(0xffffffffu, keep);
   if (keep) {
     const int slot = __popc(m & ((1u << lane) - 1u));
-    sm.A[slot] = f.a;                                                                // x, y, cx, cy
-    sm.B[slot] = make_float4(f.b.x, thr_m, f.b.y, __uint_as_float((uint32_t)f.pos));  // cz, thr_m, o, pos
-    sm.C[slot] = make_float4(f.b.z, f.b.w, f.c.x, f.c.y);                            // r, g, b, f0
-    sm.D[slot] = make_float4(f.c.z, f.c.w, __uint_as_float(f.id), 0.f);              // f1, f2, id
+    if constexpr (std::is_same<Batch, WarpBatchPk>::value) {
+      sm.A[slot] = make_float4(f.a.x, f.a.x, f.a.y, f.a.y);
+      sm.Q[slot] = make_float4(f.a.z, f.a.z, -f.a.w, -f.a.w);
+      sm.B[slot] = make_float4(f.b.x, f.b.x, thr_m, f.b.y);
+      sm.C[slot] = make_float4(f.b.z, f.b.w, f.c.x, f.c.y);
+      sm.D[slot] = make_float4(f.c.z, f.c.w, __uint_as_float((uint32_t)f.pos), __uint_as_float(f.id));
+    } else {
+      sm.A[slot] = f.a;                                                                // x, y, cx, cy
+      sm.B[slot] = make_float4(f.b.x, thr_m, f.b.y, __uint_as_float((uint32_t)f.pos));  // cz, thr_m, o, pos
+      sm.C[slot] = make_float4(f.b.z, f.b.w, f.c.x, f.c.y);                            // r, g, b, f0
+      sm.D[slot] = make_float4(f.c.z, f.c.w, __uint_as_float(f.id), 0.f);              // f1, f2, id
+    }
   }
   __syncwarp();
   return __popc(m);

@@ -27,7 +27,11 @@ __global__ void __launch_bounds__(32)
 render_fwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, const uint32_t* __restrict__ list,
                   const GeomRec* __restrict__ rec, const float* __restrict__ bg, float* __restrict__ final_T,
                   uint32_t* __restrict__ n_contrib, float* __restrict__ out_color, float* __restrict__ out_feature) {
+#if LSR_FWD_PK
+  __shared__ WarpBatchPk sm;
+#else
   __shared__ WarpBatch sm;
+#endif
 
   const int lane = threadIdx.x;
   const uint32_t tile = blockIdx.x / QUADS, quad = blockIdx.x % QUADS;
@@ -58,6 +62,9 @@ render_fwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
   }
 
   const uint32_t smA = smem_u32(&sm.A[0]);
+#if LSR_FWD_PK
+  const f32x2 npx2 = pk2(-pxf, -pxf), npy2 = pk2(-pyf[0], -pyf[1]);
+#endif
   Fetched nxt = fetch_instance(list, rec, range.x, lane < len ? lane : -1);
   for (int base = 0; base < len; base += 32) {
     // stop when no pixel of the quadrant is still blending; also ends everyone's reads of the previous batch
@@ -69,12 +76,32 @@ render_fwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
     }
     for (int j = 0; j < nb; j++) {
       const uint32_t ad = smA + (uint32_t)j * (uint32_t)sizeof(float4);
+      float power[FWD_SLOTS];
+      bool ok[FWD_SLOTS];
+#if LSR_FWD_PK
+      // both pixels of the thread at once; every packed op is the scalar path's op on each half (same roundings)
+      const float4 a = lds128(ad);            // x, x, y, y
+      const float4 q4 = lds128(ad + SM_B);    // cx, cx, -cy, -cy
+      const float4 b4 = lds128(ad + 2 * SM_B);  // cz, cz, thr_m, o
+      const f32x2 dxp = add2(pk2(a.x, a.y), npx2);
+      const f32x2 dyp = add2(pk2(a.z, a.w), npy2);
+      const f32x2 qxp = mul2(pk2(q4.x, q4.y), dxp);
+      const f32x2 nhxp = mul2(pk2(q4.z, q4.w), dxp);  // -(cy*dx)
+      const f32x2 qq = fma2(dxp, qxp, mul2(mul2(pk2(b4.x, b4.y), dyp), dyp));
+      const f32x2 pw = fma2(qq, pk2(-0.5f, -0.5f), mul2(nhxp, dyp));
+      upk2(pw, power[0], power[1]);
+      const float thr_m = b4.z, opac = b4.w;
+#pragma unroll
+      for (int s = 0; s < FWD_SLOTS; s++) ok[s] = !(power[s] > lim[s]) && !(power[s] < thr_m);
+      if (!(ok[0] || ok[1])) continue;
+      const float4 c = lds128(ad + 3 * SM_B);
+      const float4 d = lds128(ad + 4 * SM_B);  // f1, f2, pos, id
+      const float pos_bits = d.z;
+#else
       const float4 a = lds128(ad);
       const float4 b = lds128(ad + SM_B);
       const float dx = __fadd_rn(a.x, -pxf);
       const float qx = __fmul_rn(a.z, dx), hx = __fmul_rn(a.w, dx);
-      float power[FWD_SLOTS];
-      bool ok[FWD_SLOTS];
 #pragma unroll
       for (int s = 0; s < FWD_SLOTS; s++) {
         const float dy = __fadd_rn(a.y, -pyf[s]);
@@ -84,13 +111,15 @@ render_fwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
         ok[s] = !(power[s] > lim[s]) && !(power[s] < b.y);
       }
       if (!(ok[0] || ok[1])) continue;
+      const float opac = b.z, pos_bits = b.w;
       const float4 c = lds128(ad + SM_C);
       float4 d = make_float4(0.f, 0.f, 0.f, 0.f);
       if (FEAT) d = lds128(ad + SM_D);
+#endif
 #pragma unroll
       for (int s = 0; s < FWD_SLOTS; s++) {
         if (!ok[s] || lim[s] < 0.0f) continue;
-        const float alpha = fminf(0.99f, __fmul_rn(b.z, expf(power[s])));
+        const float alpha = fminf(0.99f, __fmul_rn(opac, expf(power[s])));
         if (alpha < kAlphaMin) continue;
         const float test_T = __fmul_rn(T[s], __fadd_rn(1.0f, -alpha));
         if (test_T < 0.0001f) {
@@ -108,7 +137,7 @@ render_fwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
           F[s][2] = __fmaf_rn(T[s], __fmul_rn(d.y, alpha), F[s][2]);
         }
         T[s] = test_T;
-        last_contributor[s] = __float_as_uint(b.w) + 1u;  // 1-based position in the tile's list (forward.cu:372)
+        last_contributor[s] = __float_as_uint(pos_bits) + 1u;  // 1-based position in the tile's list (forward.cu:372)
       }
     }
   }

@@ -60,6 +60,10 @@ def _present(t: Optional[torch.Tensor]) -> bool:
 def _prep(t: Optional[torch.Tensor], device) -> Optional[torch.Tensor]:
     """`.contiguous()` as rasterize_points.cu:103-122 does (required: Camera.world_view_transform is a transposed
     view, scene/cameras.py:54); absent -> None."""
+    if t is None:
+        return None
+    if t.dtype is torch.float32 and t.device == device and t.is_contiguous():  # the common case, kept cheap: this
+        return t if t.numel() != 0 else None                                   # runs a dozen times per frame
     if not _present(t):
         return None
     if t.device != device or t.dtype != torch.float32:
@@ -99,6 +103,39 @@ def _get_scratch(device, stream_ptr: int, nbytes: int) -> torch.Tensor:
     return buf
 
 
+_size_cache: Dict[tuple, int] = {}
+
+
+def _sized(fn, *args) -> int:
+    """Memoised size queries (lsr_geom_bytes & co. are pure functions of their arguments)."""
+    key = (fn.__name__,) + args
+    v = _size_cache.get(key)
+    if v is None:
+        if len(_size_cache) > 256:
+            _size_cache.clear()
+        v = _size_cache[key] = int(fn(*args))
+    return v
+
+
+class _NoContext:
+    def __enter__(self):
+        return None
+
+    def __exit__(self, *a):
+        return False
+
+
+_NO_CONTEXT = _NoContext()
+
+
+def _on_device(device):
+    """`with torch.cuda.device(device)` only when the current device differs (the guard costs ~10 us per use)."""
+    idx = device.index
+    if idx is None or idx == torch.cuda.current_device():
+        return _NO_CONTEXT
+    return torch.cuda.device(device)
+
+
 def _check(rc: int, what: str):
     if rc != L.LSR_OK:
         raise LsrError(f"{what}: {L.last_error()} (status {rc})")
@@ -130,17 +167,18 @@ def _forward_impl(rs: GaussianRasterizationSettings, means3D, sh, colors, lang, 
     feature = (torch.empty((3, H, W), dtype=torch.float32, device=device) if include_feature else torch.zeros(
         (1,), dtype=torch.float32, device=device))
     radii = torch.empty((P,), dtype=torch.int32, device=device)
-    geom = torch.empty((lib.lsr_geom_bytes(P),), dtype=torch.uint8, device=device)
-    image = torch.empty((lib.lsr_image_bytes(W, H),), dtype=torch.uint8, device=device)
+    geom = torch.empty((_sized(lib.lsr_geom_bytes, P),), dtype=torch.uint8, device=device)
+    image = torch.empty((_sized(lib.lsr_image_bytes, W, H),), dtype=torch.uint8, device=device)
     stream = torch.cuda.current_stream(device).cuda_stream
     dev_idx = device.index if device.index is not None else torch.cuda.current_device()
     global _capacity_retries
     capacity = max(int(_last_R.get(dev_idx, 0) * 1.25), _CAPACITY_PER_GAUSSIAN * P, _INITIAL_CAPACITY_FLOOR)
+    capacity = (capacity + 0xFFFF) & ~0xFFFF  # 64 Ki steps: stable buffer sizes from frame to frame
     nr = ctypes.c_int64(0)
-    with torch.cuda.device(device):
+    with _on_device(device):
         while True:
-            point_list = torch.empty((lib.lsr_list_bytes(capacity),), dtype=torch.uint8, device=device)
-            need = lib.lsr_scratch_bytes(P, W, H, capacity)
+            point_list = torch.empty((_sized(lib.lsr_list_bytes, capacity),), dtype=torch.uint8, device=device)
+            need = _sized(lib.lsr_scratch_bytes, P, W, H, capacity)
             scratch = (torch.empty((need,), dtype=torch.uint8, device=device) if keep_scratch else _get_scratch(
                 device, stream, need))
             rc = lib.lsr_forward(ctypes.byref(frame), ctypes.byref(inputs), _ptr(color), _ptr(feature), _ptr(radii),
@@ -230,7 +268,7 @@ def _backward_impl(state, grad_color, grad_feature, need_mask: int, want_sh: boo
         d_rots = part["rots"].view(P, 4)
         g.dL_dscales, g.dL_drotations = d_scales.data_ptr(), d_rots.data_ptr()
     stream = torch.cuda.current_stream(device).cuda_stream
-    with torch.cuda.device(device):
+    with _on_device(device):
         rc = lib.lsr_backward(ctypes.byref(state["frame"]), ctypes.byref(state["inputs"]), _ptr(state["radii"]),
                               _ptr(state["geom"]), _ptr(state["image"]), _ptr(state["point_list"]), _ptr(gc), _ptr(gf),
                               need_mask | (L.NEED_GEOMETRY if run_pre else 0), ctypes.byref(g),
