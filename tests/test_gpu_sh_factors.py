@@ -179,9 +179,9 @@ def test_peer_barrier_two_ranks_on_two_streams_and_timeout():
 
 def test_peer_exchange_single_rank_equals_list_sink():
     dev = torch.device("cuda:0")
-    scene, cams = syn.make_config(4, P=8000, W=160, H=120, n_cameras=2)
+    scene, cams = syn.make_config(4, P=8001, W=160, H=120, n_cameras=2)  # odd P: unaligned second slot
     listed = _step(scene, cams, dev, 3, factored=True)
-    ex = D.PeerFactorExchange(8000, 2, dev)
+    ex = D.PeerFactorExchange(8001, 2, dev)
     try:
         for _ in range(3):  # slots alternate; every step must give the same answer
             params = {k: scene[k].to(dev).requires_grad_(True) for k in NAMES}
