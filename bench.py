@@ -62,6 +62,9 @@ def parse_args():
     ap.add_argument("--allgather-sh-exchange", action="store_true",
                     help="multi-GPU: NCCL all-gather of the SH-gradient factors instead of reading them from peer "
                          "memory inside the SH-gradient kernel (A/B)")
+    ap.add_argument("--peer-allreduce", action="store_true",
+                    help="multi-GPU: sum the non-SH gradients with the two-shot peer-memory kernel instead of NCCL "
+                         "(A/B; measured slower overall because it serialises with the SH-gradient kernel)")
     ap.add_argument("--dense-sh-exchange", action="store_true",
                     help="multi-view / multi-GPU: all-reduce dL_dsh itself instead of its per-view factors (A/B)")
     ap.add_argument("--cpu-frames", type=int, default=3)
@@ -277,14 +280,16 @@ def main():
     if factored:
         from langsplat_b200.dist import factored_sh_gradients, finish_sh_gradients, make_peer_exchange
         if world > 1 and not args.allgather_sh_exchange:  # factors read in place over NVLink by the SH-gradient kernel
-            peer = make_peer_exchange(P, len(my_views), dev)
+            peer = make_peer_exchange(P, len(my_views), dev, grad_floats_per_gaussian=14 if args.peer_allreduce else 0)
 
     exchange = ("none (one view, one GPU)" if world == 1 and len(my_views) == 1 else
                 "dL_dsh summed by autograd" + (" + NCCL all-reduce of all gradients" if world > 1 else ""))
     if factored:
         exchange = ("SH gradient as per-view 12-byte factors: "
-                    + ("read from peer memory over NVLink inside the SH-gradient kernel (one barrier kernel), "
-                       "concurrently NCCL all-reduce of the other 56 B/Gaussian" if peer else
+                    + (("read from peer memory over NVLink inside the SH-gradient kernel, "
+                        + ("concurrently NCCL all-reduce of the other 56 B/Gaussian" if not args.peer_allreduce else
+                           "the other 56 B/Gaussian by a two-shot all-reduce kernel over peer memory; no NCCL on "
+                           "the data path")) if peer else
                        ("NCCL all-gather of factors + all-reduce of the other 56 B/Gaussian" if world > 1 else
                         "summed over the step's views by one kernel")))
 
@@ -296,6 +301,17 @@ def main():
             return
         with factored_sh_gradients(peer.begin_step() if peer else None) as factors:
             run_views()
+        if peer and args.peer_allreduce:
+            # the whole exchange over peer memory: two-shot all-reduce of the other 56 B/Gaussian + the SH-gradient
+            # kernel pulling the factors, ordered by barrier kernels on this stream; NCCL is not involved
+            others = [k for k in params if k != "shs"]
+            sh_grad, reduced = peer.exchange(params["means3D"], params["shs"].shape[1],
+                                             [params[k].grad for k in others])
+            for k, g_ in zip(others, reduced):
+                if g_ is not None:
+                    params[k].grad = g_
+            params["shs"].grad = sh_grad
+            return
         # everything but the SH gradient (absent from .grad in this mode): NCCL, on its own stream, while ...
         handles = reduce_grads(async_op=True)
         if peer:  # ... this rank's kernel pulls the other ranks' factors over NVLink and forms dL_dsh

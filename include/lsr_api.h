@@ -175,7 +175,14 @@ int lsr_sh_gradient_from_view_ptrs(int32_t P, int32_t M, int32_t D, int32_t n_vi
  * lsr_peer_barrier: stream-ordered barrier across `world` ranks; headers[r] = rank r's buffer as seen from this
  *   process (own pointer at headers[rank]).  `epoch` must grow by one per call on every rank.  Work enqueued after it
  *   sees everything the peers enqueued before theirs.  A peer that does not arrive within 4 s is reported by
- *   lsr_peer_status (returns LSR_ERR_CUDA, "peer barrier timed out") instead of hanging the device. */
+ *   lsr_peer_status (returns LSR_ERR_CUDA, "peer barrier timed out") instead of hanging the device.
+ * lsr_peer_signal / lsr_peer_wait: the two halves of the barrier, for a rank that has local work to run between
+ *   "my remote writes are done" and "everybody's are".
+ * lsr_peer_allreduce: two-shot sum over the ranks through peer memory.  in[r] / out[r] = rank r's input / output
+ *   vector of n_floats floats (16-byte aligned, n_floats % 4 == 0) as mapped in this process.  This rank reduces its
+ *   own 1/world chunk from all inputs (fixed rank order: every rank ends with the same bits) and stores it into every
+ *   rank's output.  Order it with the barrier: inputs complete on all ranks before it (lsr_peer_barrier), outputs
+ *   complete once every rank has signalled after it (lsr_peer_signal ... lsr_peer_wait). */
 #define LSR_PEER_HANDLE_BYTES 64
 #define LSR_PEER_HEADER_BYTES 256
 #define LSR_MAX_PEERS 16
@@ -184,6 +191,10 @@ int lsr_peer_open(const uint8_t* handle, void** ptr);
 int lsr_peer_close(void* ptr);
 int lsr_peer_free(void* ptr);
 int lsr_peer_barrier(int32_t rank, int32_t world, void* const* headers, uint32_t epoch, void* stream);
+int lsr_peer_signal(int32_t rank, int32_t world, void* const* headers, uint32_t epoch, void* stream);
+int lsr_peer_wait(int32_t rank, int32_t world, void* const* headers, uint32_t epoch, void* stream);
+int lsr_peer_allreduce(int32_t rank, int32_t world, const float* const* in, float* const* out, int64_t n_floats,
+                       void* stream);
 int lsr_peer_status(const void* own_buffer, void* stream);
 
 /* Replaces _C.mark_visible -> markVisible (rasterize_points.cu:226-245) -> checkFrustum (rasterizer_impl.cu:54-66). */

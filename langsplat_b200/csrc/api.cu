@@ -227,12 +227,35 @@ int lsr_peer_free(void* ptr) {
   return LSR_OK;
 }
 
-int lsr_peer_barrier(int32_t rank, int32_t world, void* const* headers, uint32_t epoch, void* stream) {
+static int peer_sync(int32_t rank, int32_t world, void* const* headers, uint32_t epoch, int mode, void* stream) {
   if (world < 1 || world > LSR_MAX_PEERS || rank < 0 || rank >= world || !headers)
     return fail(LSR_ERR_INVALID, "bad rank / world (at most %d peers)", LSR_MAX_PEERS);
   for (int r = 0; r < world; r++)
     if (!headers[r]) return fail(LSR_ERR_INVALID, "null header for rank %d", r);
-  launch_peer_barrier(rank, world, headers, epoch, (cudaStream_t)stream);
+  launch_peer_barrier(rank, world, headers, epoch, mode, (cudaStream_t)stream);
+  LSR_CUDA(cudaGetLastError());
+  return LSR_OK;
+}
+
+int lsr_peer_barrier(int32_t rank, int32_t world, void* const* headers, uint32_t epoch, void* stream) {
+  return peer_sync(rank, world, headers, epoch, 3, stream);
+}
+int lsr_peer_signal(int32_t rank, int32_t world, void* const* headers, uint32_t epoch, void* stream) {
+  return peer_sync(rank, world, headers, epoch, 1, stream);
+}
+int lsr_peer_wait(int32_t rank, int32_t world, void* const* headers, uint32_t epoch, void* stream) {
+  return peer_sync(rank, world, headers, epoch, 2, stream);
+}
+
+int lsr_peer_allreduce(int32_t rank, int32_t world, const float* const* in, float* const* out, int64_t n_floats,
+                       void* stream) {
+  if (world < 1 || world > LSR_MAX_PEERS || rank < 0 || rank >= world || !in || !out)
+    return fail(LSR_ERR_INVALID, "bad rank / world (at most %d peers)", LSR_MAX_PEERS);
+  if (n_floats < 0 || (n_floats & 3)) return fail(LSR_ERR_INVALID, "n_floats must be a non-negative multiple of 4");
+  for (int r = 0; r < world; r++)
+    if (!in[r] || !out[r] || ((((uintptr_t)in[r]) | ((uintptr_t)out[r])) & 15))
+      return fail(LSR_ERR_INVALID, "buffer of rank %d is null or not 16-byte aligned", r);
+  launch_peer_allreduce(rank, world, in, out, n_floats, (cudaStream_t)stream);
   LSR_CUDA(cudaGetLastError());
   return LSR_OK;
 }

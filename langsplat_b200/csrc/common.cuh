@@ -206,7 +206,11 @@ void launch_sh_grad_views(int P, int D, int M, int V, const float* means3D, cons
 void launch_sh_grad_view_ptrs(int P, int D, int M, int V, const float* means3D, const float* const* g_views,
                               const float* const* campos_views, float* dL_dsh, cudaStream_t s);
 // cross-GPU barrier on the stream (peer.cu): signals `epoch` into every peer's header, waits for all of them
-void launch_peer_barrier(int rank, int world, void* const* headers, uint32_t epoch, cudaStream_t s);
+// mode: 1 = signal, 2 = wait, 3 = both
+void launch_peer_barrier(int rank, int world, void* const* headers, uint32_t epoch, int mode, cudaStream_t s);
+// out[r][i] = sum over ranks of in[.][i] for this rank's chunk of the n_floats-long vectors, for every rank r
+void launch_peer_allreduce(int rank, int world, const float* const* in, float* const* out, int64_t n_floats,
+                           cudaStream_t s);
 void launch_activate_forward(int P, const float* scaling, const float* rotation, const float* opacity,
                              const float* feature, float* scales_out, float* rotations_out, float* opacities_out,
                              float* feature_out, cudaStream_t s);

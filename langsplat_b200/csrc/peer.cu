@@ -3,6 +3,8 @@
 // ranks' buffers mapped (lsr_peer_open, CUDA IPC over NVLink / NVSwitch).  The barrier is the only ordering the
 // exchange needs: after it, every rank's factors of this step are complete and visible, so the SH-gradient kernel
 // (preprocess_bwd.cu: sh_grad_views_kernel) can read them straight out of peer memory.
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace lsr {
@@ -29,12 +31,17 @@ __device__ __forceinline__ uint64_t globaltimer_ns() {
 // timed_out in the own header (lsr_peer_status), the gradients of that step are then garbage and the caller aborts.
 constexpr uint64_t LSR_PEER_TIMEOUT_NS = 4000000000ull;
 
-__global__ void __launch_bounds__(32) peer_barrier_kernel(PeerHeaders hs, int rank, int world, uint32_t epoch) {
+// mode bit 0: signal, bit 1: wait.  Splitting the two lets a rank publish "my remote writes are done", run local work
+// that does not depend on the peers, and only then wait for them.
+__global__ void __launch_bounds__(32) peer_barrier_kernel(PeerHeaders hs, int rank, int world, uint32_t epoch,
+                                                          int mode) {
   const int r = threadIdx.x;
   __threadfence_system();
-  if (r < world) {
+  if (r < world && (mode & 1)) {
     uint32_t* theirs = &hs.h[r]->arrived[rank];
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(theirs), "r"(epoch) : "memory");
+  }
+  if (r < world && (mode & 2)) {
     const uint32_t* mine = &hs.h[rank]->arrived[r];
     const uint64_t t0 = globaltimer_ns();
     for (;;) {
@@ -52,12 +59,65 @@ __global__ void __launch_bounds__(32) peer_barrier_kernel(PeerHeaders hs, int ra
   __threadfence_system();
 }
 
+// Two-shot sum over the ranks through peer memory.  Rank r owns the r-th chunk of the vector: it loads that chunk from
+// every rank's input buffer (its own included, fixed rank order, so the sum is the same bits whoever computes it),
+// adds, and stores the result into EVERY rank's output buffer — the reduce-scatter reads and the all-gather writes of
+// an all-reduce, fused into one pass over NVLink with 16-byte accesses.  Callers order it with the barrier: inputs
+// complete on all ranks before (signal+wait), outputs complete on all ranks after (signal, ..., wait).
+struct PeerBufs {
+  const float4* in[LSR_MAX_PEERS];
+  float4* out[LSR_MAX_PEERS];
+};
+
+constexpr int PAR_THREADS = 256;
+
+template <int WORLD>
+__global__ void __launch_bounds__(PAR_THREADS)
+peer_allreduce_kernel(PeerBufs b, int world, int64_t first, int64_t end) {
+  const int64_t stride = (int64_t)gridDim.x * PAR_THREADS;
+  for (int64_t i = first + (int64_t)blockIdx.x * PAR_THREADS + threadIdx.x; i < end; i += stride) {
+    const int n = WORLD > 0 ? WORLD : world;
+    float4 v[WORLD > 0 ? WORLD : LSR_MAX_PEERS];
+#pragma unroll
+    for (int r = 0; r < (WORLD > 0 ? WORLD : LSR_MAX_PEERS); r++)
+      if (r < n) v[r] = b.in[r][i];  // all loads in flight before the first add
+    float4 acc = v[0];
+#pragma unroll
+    for (int r = 1; r < (WORLD > 0 ? WORLD : LSR_MAX_PEERS); r++)
+      if (r < n) { acc.x += v[r].x; acc.y += v[r].y; acc.z += v[r].z; acc.w += v[r].w; }
+#pragma unroll
+    for (int r = 0; r < (WORLD > 0 ? WORLD : LSR_MAX_PEERS); r++)
+      if (r < n) b.out[r][i] = acc;
+  }
+}
+
 }  // namespace
 
-void launch_peer_barrier(int rank, int world, void* const* headers, uint32_t epoch, cudaStream_t s) {
+void launch_peer_barrier(int rank, int world, void* const* headers, uint32_t epoch, int mode, cudaStream_t s) {
   PeerHeaders hs;
   for (int i = 0; i < LSR_MAX_PEERS; i++) hs.h[i] = i < world ? reinterpret_cast<PeerHeader*>(headers[i]) : nullptr;
-  peer_barrier_kernel<<<1, 32, 0, s>>>(hs, rank, world, epoch);
+  peer_barrier_kernel<<<1, 32, 0, s>>>(hs, rank, world, epoch, mode);
+  count_launch();
+}
+
+void launch_peer_allreduce(int rank, int world, const float* const* in, float* const* out, int64_t n_floats,
+                           cudaStream_t s) {
+  const int64_t n4 = n_floats / 4;
+  const int64_t chunk = (n4 + world - 1) / world;
+  const int64_t first = std::min(n4, (int64_t)rank * chunk), end = std::min(n4, first + chunk);
+  if (end <= first) return;
+  PeerBufs b;
+  for (int i = 0; i < LSR_MAX_PEERS; i++) {
+    b.in[i] = i < world ? reinterpret_cast<const float4*>(in[i]) : nullptr;
+    b.out[i] = i < world ? reinterpret_cast<float4*>(out[i]) : nullptr;
+  }
+  const int blocks = (int)std::min<int64_t>((end - first + PAR_THREADS - 1) / PAR_THREADS, 148 * 8);
+  switch (world) {
+    case 2: peer_allreduce_kernel<2><<<blocks, PAR_THREADS, 0, s>>>(b, world, first, end); break;
+    case 4: peer_allreduce_kernel<4><<<blocks, PAR_THREADS, 0, s>>>(b, world, first, end); break;
+    case 8: peer_allreduce_kernel<8><<<blocks, PAR_THREADS, 0, s>>>(b, world, first, end); break;
+    default: peer_allreduce_kernel<0><<<blocks, PAR_THREADS, 0, s>>>(b, world, first, end); break;
+  }
   count_launch();
 }
 

@@ -172,11 +172,17 @@ class PeerFactorExchange:
     the dL_dsh stores (lsr_sh_gradient_from_view_ptrs).  No all-gather, no staging copy, and NCCL stays free to
     all-reduce the remaining gradients at the same time.
 
+    Optionally (grad_floats_per_gaussian > 0, `exchange`) the remaining gradients are summed over peer memory as well,
+    by a two-shot all-reduce kernel.  Measured at N=2, 56 MB: that kernel alone 85 us against NCCL's 127 us, but it
+    and the SH-gradient kernel contend for the same links and SMs and end up back to back (185 us for the whole
+    exchange), whereas NCCL's copy-engine-like traffic overlaps the SH-gradient kernel (136 us) — so `finish` + NCCL
+    is the default and `exchange` the alternative (profiles/tools/exchange_times.py, bench.py --peer-allreduce).
+
     Two slots alternate by step parity: a rank can only get two steps ahead of a peer by passing the barrier in
     between, which that peer enqueues after the kernel that read the slot, so no slot is overwritten while in use.
     Every rank must run the same number of views per step, on the same stream from step to step."""
 
-    def __init__(self, P: int, views_per_rank: int, device, group=None):
+    def __init__(self, P: int, views_per_rank: int, device, group=None, grad_floats_per_gaussian: int = 0):
         from . import _lib as L
         from .rasterizer import LsrError
         self._L, self._lib, self._err = L, L.load(), LsrError
@@ -186,8 +192,13 @@ class PeerFactorExchange:
         self.world = dist.get_world_size(group) if on else 1
         if self.world > L.MAX_PEERS:
             raise LsrError(f"PeerFactorExchange: at most {L.MAX_PEERS} ranks")
-        self.cam_off = self.V * self.P * 3  # floats: factors first, then 4 floats of camera position per view
-        slot_floats = (self.cam_off + 4 * self.V + 63) // 64 * 64
+        # one slot, in floats: the views' factors | 4 floats of camera position per view | (64-float aligned) this
+        # rank's other gradients, input of the two-shot all-reduce | its output, written by all ranks
+        self.cam_off = self.V * self.P * 3
+        self.grad_cap = (int(grad_floats_per_gaussian) * self.P + 63) // 64 * 64
+        self.in_off = (self.cam_off + 4 * self.V + 63) // 64 * 64
+        self.out_off = self.in_off + self.grad_cap
+        slot_floats = self.out_off + self.grad_cap
         self.slot_bytes = slot_floats * 4
         total = L.PEER_HEADER_BYTES + 2 * self.slot_bytes
         own, handle = ctypes.c_void_p(), (ctypes.c_uint8 * L.PEER_HANDLE_BYTES)()
@@ -217,7 +228,8 @@ class PeerFactorExchange:
         self._payload = torch.as_tensor(_DevicePtr(self.own + L.PEER_HEADER_BYTES, 2 * slot_floats),
                                         device=self.device).view(2, slot_floats)
         self._headers = (ctypes.c_void_p * self.world)(*self.bases)
-        self.epoch, self._count, self._degree = 0, 0, 0
+        self.epoch, self._count, self._degree, self._barriers = 0, 0, 0, 0
+        self._side = torch.cuda.Stream(device=self.device)
 
     def _check(self, rc: int) -> None:
         if rc != self._L.LSR_OK:
@@ -239,16 +251,64 @@ class PeerFactorExchange:
         slot[self.cam_off + 4 * i: self.cam_off + 4 * i + 3].copy_(campos.reshape(3), non_blocking=True)
         return slot[i * P * 3:(i + 1) * P * 3].view(P, 3)
 
+    def new_flat(self, n_floats: int, device) -> Optional[torch.Tensor]:
+        """Memory for the parameter gradients of the step's FIRST backward: the head of this step's staging area, so
+        that `exchange` finds them in place (autograd hands the slices to .grad and later views accumulate into them).
+        None (caller allocates) for further views or when it does not fit."""
+        if self.world == 1 or self._count != 0 or n_floats > self.grad_cap:  # asked before the view's new_factor;
+            # grad_cap is 0 unless the exchange was built with grad_floats_per_gaussian (the all-reduce option)
+            return None
+        return self._payload[self.epoch & 1][self.in_off:self.in_off + n_floats]
+
     def finish(self, means3D: torch.Tensor, n_coeffs: int) -> torch.Tensor:
         """dL_dsh [P, n_coeffs, 3] summed over the views of all ranks; call once per step, after the backward passes.
         Every rank must have run the same number (1..views_per_rank) of backward passes since begin_step()."""
+        return self.exchange(means3D, n_coeffs, [])[0]
+
+    def exchange(self, means3D: torch.Tensor, n_coeffs: int, grads: Sequence[Optional[torch.Tensor]]):
+        """The whole exchange of a step, all of it over peer memory: returns (dL_dsh summed over the views of all
+        ranks, the other gradients summed over the ranks, in the order given; None stays None).
+        The other gradients take a two-shot all-reduce (lsr_peer_allreduce): every rank reduces its 1/world chunk out
+        of all ranks' staging areas and stores the sums into every rank's result area; the tensors returned are views
+        of that area — valid until the step after next, i.e. consume them (optimizer step) within the step, as a
+        training loop does.  Per rank: (gradients already sit in the staging area when the backward got its memory from
+        new_flat, else one copy), barrier, then the all-reduce kernel + signal on the caller's stream while the
+        SH-gradient kernel pulls the factors on a second stream, join, wait."""
         if self._count == 0:
             raise self._err("PeerFactorExchange: no view ran a backward this step")
         L, P, V = self._L, self.P, self._count
         stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        parity = self.epoch & 1
+        slot = self._payload[parity]
+        off = L.PEER_HEADER_BYTES + parity * self.slot_bytes
+        # ---- stage the other gradients (adjacent slices travel as one copy) ----
+        live = [g for g in grads if g is not None]
+        places, total = {}, 0
+        if live and self.world > 1:
+            for g in live:
+                if g.dtype != torch.float32 or not g.is_cuda:
+                    raise self._err("PeerFactorExchange: gradients must be CUDA float32 tensors")
+            fixed = [g if g.is_contiguous() else g.contiguous() for g in live]
+            pieces = coalesce(fixed)
+            stage0 = slot[self.in_off:self.in_off + 1].data_ptr()
+            in_place = len(pieces) == 1 and pieces[0].data_ptr() == stage0  # new_flat's memory, handed back by autograd
+            if not in_place:  # anything that happens to live in the staging area must move out of the way first
+                lo, hi = stage0, stage0 + self.grad_cap * 4
+                pieces = [p_.clone() if lo <= p_.data_ptr() < hi else p_ for p_ in pieces]
+            for piece, orig in zip(pieces, coalesce(fixed)):
+                n = piece.numel()
+                if total + n > self.grad_cap:
+                    raise self._err(f"PeerFactorExchange: more than {self.grad_cap} gradient floats per rank; raise "
+                                    "grad_floats_per_gaussian")
+                if not in_place:
+                    slot[self.in_off + total: self.in_off + total + n].copy_(piece.reshape(-1), non_blocking=True)
+                for g, f in zip(live, fixed):
+                    d = f.data_ptr() - orig.data_ptr()
+                    if 0 <= d < n * 4 and id(g) not in places:
+                        places[id(g)] = total + d // 4
+                total += (n + 3) // 4 * 4
         n = self.world * V
         g_ptrs, c_ptrs = (ctypes.c_void_p * n)(), (ctypes.c_void_p * n)()
-        off = L.PEER_HEADER_BYTES + (self.epoch & 1) * self.slot_bytes
         for r in range(self.world):  # rank-major, the order an all-gather would produce
             for i in range(V):
                 g_ptrs[r * V + i] = self.bases[r] + off + i * P * 12
@@ -256,12 +316,38 @@ class PeerFactorExchange:
         out = torch.empty((P, n_coeffs, 3), dtype=torch.float32, device=self.device)
         m3 = means3D.detach().contiguous()
         with torch.cuda.device(self.device):
-            self._check(self._lib.lsr_peer_barrier(self.rank, self.world, self._headers, self.epoch & 0xFFFFFFFF,
-                                                   stream))
+            self._barriers += 1
+            self._check(self._lib.lsr_peer_barrier(self.rank, self.world, self._headers,
+                                                   self._barriers & 0xFFFFFFFF, stream))
+            sh_stream = stream
+            if total:  # the SH-gradient kernel runs beside the all-reduce kernel, on a second stream
+                main = torch.cuda.current_stream(self.device)
+                self._side.wait_stream(main)
+                out.record_stream(self._side)
+                sh_stream = ctypes.c_void_p(self._side.cuda_stream)
             self._check(self._lib.lsr_sh_gradient_from_view_ptrs(P, n_coeffs, self._degree, n,
                                                                  ctypes.c_void_p(m3.data_ptr()), g_ptrs, c_ptrs,
-                                                                 ctypes.c_void_p(out.data_ptr()), stream))
-        return out
+                                                                 ctypes.c_void_p(out.data_ptr()), sh_stream))
+            if total:
+                ins = (ctypes.c_void_p * self.world)(*[b + off + self.in_off * 4 for b in self.bases])
+                outs = (ctypes.c_void_p * self.world)(*[b + off + self.out_off * 4 for b in self.bases])
+                self._check(self._lib.lsr_peer_allreduce(self.rank, self.world, ins, outs, total, stream))
+                self._barriers += 1
+                self._check(self._lib.lsr_peer_signal(self.rank, self.world, self._headers,
+                                                      self._barriers & 0xFFFFFFFF, stream))
+                main.wait_stream(self._side)
+                self._check(self._lib.lsr_peer_wait(self.rank, self.world, self._headers,
+                                                    self._barriers & 0xFFFFFFFF, stream))
+        if not total:
+            return out, list(grads)
+        reduced = []
+        for g in grads:
+            if g is None:
+                reduced.append(None)
+            else:
+                o = self.out_off + places[id(g)]
+                reduced.append(slot[o:o + g.numel()].view(g.shape))
+        return out, reduced
 
     def check(self) -> None:
         """Synchronises and raises if a barrier of this rank ever timed out (a peer was missing)."""
@@ -285,12 +371,13 @@ class PeerFactorExchange:
         self.own = None
 
 
-def make_peer_exchange(P: int, views_per_rank: int, device, group=None) -> Optional[PeerFactorExchange]:
+def make_peer_exchange(P: int, views_per_rank: int, device, group=None,
+                       grad_floats_per_gaussian: int = 0) -> Optional[PeerFactorExchange]:
     """PeerFactorExchange if every rank could map every other rank's buffer, else None on all ranks (no NVLink /
     IPC between the processes): the caller then uses the all-gather path (`finish_sh_gradients`)."""
     ex, ok = None, 1
     try:
-        ex = PeerFactorExchange(P, views_per_rank, device, group)
+        ex = PeerFactorExchange(P, views_per_rank, device, group, grad_floats_per_gaussian)
     except Exception as e:  # noqa: BLE001 — whatever failed, the decision must be collective
         ok, ex = 0, None
         print(f"[langsplat_b200.dist] peer exchange unavailable on this rank: {e}")

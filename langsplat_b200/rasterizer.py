@@ -237,13 +237,23 @@ def _backward_impl(state, grad_color, grad_feature, need_mask: int, want_sh: boo
     sizes = [("rots", 4 if run_pre else 0), ("sh", n_sh), ("means3D", 3 if run_pre else 0),
              ("scales", 3 if run_pre else 0), ("feat", 3), ("opac", 1), ("|", 0), ("conic", 4), ("means2D", 3),
              ("colors", 3), ("cov3D", 6 if run_pre else 0)]
-    flat = torch.empty((sum(n for _, n in sizes) * P + 4,), **f32)
-    part, off = {}, 0
+    # A sink may provide the memory of the parameter gradients (PeerFactorExchange: peer-visible staging memory, so
+    # that the all-reduce reads them in place); the internal accumulators then come from their own allocation.
+    n_params = sum(n for _, n in sizes[:sizes.index(("|", 0))]) * P
+    lead = sh_factor_out.new_flat(n_params, device) if factored and hasattr(sh_factor_out, "new_flat") else None
+    if lead is None:
+        flat = torch.empty((sum(n for _, n in sizes) * P + 4,), **f32)
+    else:
+        flat = torch.empty((sum(n for _, n in sizes) * P + 4 - n_params,), **f32)
+    part, off, buf = {}, 0, (flat if lead is None else lead)
     for name, n in sizes:
         if name == "|":
-            off = (off + 3) // 4 * 4
+            if lead is None:
+                off = (off + 3) // 4 * 4
+            else:
+                buf, off = flat, 0
             continue
-        part[name] = flat[off:off + n * P] if n else None
+        part[name] = buf[off:off + n * P] if n else None
         off += n * P
     d_conic = part["conic"].view(P, 4)
     d_means2D = part["means2D"].view(P, 3)

@@ -1,6 +1,7 @@
 #!/usr/bin/env bash
 # Multi-GPU A/B on the box: the 2+-rank peer-exchange check, then bench at N ranks with the three SH-gradient exchanges
-# (factors read from peer memory / NCCL all-gather of factors / dense all-reduce).
+# (default: factors read from peer memory + NCCL for the rest; FULL=1 adds: everything over peer memory / NCCL
+# all-gather of factors / dense all-reduce).
 # Usage: bash profiles/scale_ab.sh TAG N [config]
 set -uo pipefail
 TAG="$1"; N="$2"; CFG="${3:-2}"; OUT=gpurun_out/$TAG; mkdir -p "$OUT"
@@ -21,5 +22,8 @@ if [ "$CFG" = 2 ]; then
   echo "peer check rc=$?"; grep -h "PEER_EXCHANGE_OK\|Error\|unavailable" "$OUT/peer_check_n${N}.log" | head -5
 fi
 run peer ""
-run allgather "--allgather-sh-exchange"
-run dense "--dense-sh-exchange"
+if [ "${FULL:-0}" = 1 ]; then
+  run peer_allreduce "--peer-allreduce"
+  run allgather "--allgather-sh-exchange"
+  run dense "--dense-sh-exchange"
+fi

@@ -2,7 +2,8 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 tests/peer_exchange_check.py
 Each rank renders its own views of a small scene; the SH gradient formed (a) from factors read out of peer memory
 (PeerFactorExchange), (b) from NCCL-all-gathered factors (finish_sh_gradients) and (c) by all-reducing the dense dL_dsh
-must agree on every rank, for several steps (the two slots alternate).  Prints PEER_EXCHANGE_OK on rank 0."""
+must agree on every rank, for several steps (the two slots alternate); the other gradients summed by the two-shot
+peer-memory all-reduce must match NCCL's and be bit-identical on all ranks.  Prints PEER_EXCHANGE_OK on rank 0."""
 import os
 import sys
 
@@ -40,25 +41,36 @@ def main():
                                           opacities=params["opacities"], scales=params["scales"],
                                           rotations=params["rotations"])
                 torch.autograd.backward([color, feat], [dcol, dfeat])
+        others = [k for k in NAMES if k != "shs"]
         if sink == "dense":
             views()
-            D.allreduce_gradients([params["shs"].grad])
-            return params["shs"].grad
+            D.allreduce_gradients([params[k].grad for k in NAMES])
+            return params["shs"].grad, [params[k].grad for k in others]
         with D.factored_sh_gradients(sink.begin_step() if sink else None) as factors:
             views()
         if sink:
-            return sink.finish(params["means3D"], 16)
-        return D.finish_sh_gradients(factors, params["means3D"], 16)
+            sh, red = sink.exchange(params["means3D"], 16, [params[k].grad for k in others] + [None])
+            assert red[-1] is None
+            return sh, [t.clone() for t in red[:-1]]
+        D.allreduce_gradients([params[k].grad for k in others])
+        return D.finish_sh_gradients(factors, params["means3D"], 16), [params[k].grad for k in others]
 
-    dense = run("dense")
-    gathered = run(None)
+    dense, dense_others = run("dense")
+    gathered, _ = run(None)
     assert rel_err(gathered, dense) <= 1e-5, rel_err(gathered, dense)
-    ex = D.make_peer_exchange(P, per_rank, dev)
+    ex = D.make_peer_exchange(P, per_rank, dev, grad_floats_per_gaussian=14)
     assert ex is not None, "peer memory could not be mapped between the ranks"
     for step in range(4):
-        got = run(ex)
+        got, others = run(ex)
         assert rel_err(got, dense) <= 1e-5, (step, rel_err(got, dense))
         assert torch.equal(got, gathered) or rel_err(got, gathered) <= 1e-6
+        for a, b in zip(others, dense_others):  # two-shot all-reduce over peer memory vs NCCL (+ atomics noise)
+            assert a.shape == b.shape and rel_err(a, b) <= 2e-5, (step, rel_err(a, b))
+        # every rank must hold the same bits: each chunk is reduced by one rank and broadcast
+        flat = torch.cat([t.reshape(-1) for t in others])
+        ref = flat.clone()
+        dist.broadcast(ref, src=0)
+        assert torch.equal(flat, ref), "ranks disagree on the reduced gradients"
     ex.check()
     ex.close()
     dist.barrier()

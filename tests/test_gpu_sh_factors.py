@@ -202,3 +202,36 @@ def test_peer_exchange_single_rank_equals_list_sink():
             ex.begin_step().finish(params["means3D"], 16)  # no backward ran
     finally:
         ex.close()
+
+
+def test_peer_allreduce_two_ranks_in_one_process():
+    """lsr_peer_allreduce with both 'ranks' on one device: each call reduces its own chunk from both inputs and stores
+    it into both outputs; together they leave the full sum everywhere (odd length in float4s, tail chunk shorter)."""
+    import ctypes
+    from langsplat_b200 import _lib as L
+    lib = L.load()
+    dev = torch.device("cuda:0")
+    n = 4 * 100003
+    g = torch.Generator().manual_seed(3)
+    ins = [torch.randn(n, generator=g).to(dev) for _ in range(2)]
+    outs = [torch.full((n,), float("nan"), device=dev) for _ in range(2)]
+    ip, op = _ptr_array([t.data_ptr() for t in ins]), _ptr_array([t.data_ptr() for t in outs])
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for rank in (0, 1):
+        assert lib.lsr_peer_allreduce(rank, 2, ip, op, n, stream) == L.LSR_OK, L.last_error()
+    torch.cuda.synchronize()
+    want = ins[0] + ins[1]
+    assert torch.equal(outs[0], want) and torch.equal(outs[1], want)
+    # generic world size (not one of the unrolled 2 / 4 / 8): three ranks
+    ins3 = ins + [torch.randn(n, generator=g).to(dev)]
+    outs3 = [torch.zeros(n, device=dev) for _ in range(3)]
+    ip3, op3 = _ptr_array([t.data_ptr() for t in ins3]), _ptr_array([t.data_ptr() for t in outs3])
+    for rank in range(3):
+        assert lib.lsr_peer_allreduce(rank, 3, ip3, op3, n, stream) == L.LSR_OK
+    torch.cuda.synchronize()
+    want3 = (ins3[0] + ins3[1]) + ins3[2]
+    assert all(torch.equal(o, want3) for o in outs3)
+    assert lib.lsr_peer_allreduce(0, 2, ip, op, n + 2, stream) != L.LSR_OK  # not a multiple of 4
+    bad = _ptr_array([ins[0].data_ptr() + 4, ins[1].data_ptr()])
+    assert lib.lsr_peer_allreduce(0, 2, bad, op, n, stream) != L.LSR_OK and "aligned" in L.last_error()
+    assert lib.lsr_peer_allreduce(0, 1, ip, op, 0, stream) == L.LSR_OK  # nothing to do
