@@ -9,6 +9,7 @@ from __future__ import annotations
 
 import contextlib
 import ctypes
+import sys
 from typing import Dict, Iterable, List, Optional, Sequence
 
 import torch
@@ -380,7 +381,7 @@ def make_peer_exchange(P: int, views_per_rank: int, device, group=None,
         ex = PeerFactorExchange(P, views_per_rank, device, group, grad_floats_per_gaussian)
     except Exception as e:  # noqa: BLE001 — whatever failed, the decision must be collective
         ok, ex = 0, None
-        print(f"[langsplat_b200.dist] peer exchange unavailable on this rank: {e}")
+        print(f"[langsplat_b200.dist] peer exchange unavailable on this rank: {e}", file=sys.stderr)
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         flag = torch.tensor([ok], dtype=torch.int32, device=device)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
