@@ -69,15 +69,18 @@ def test_config2_full_size_gradients_against_reference():
     cam = cams[0]
     dcol, dfeat = syn.make_grads(cam.image_width, cam.image_height, 2002)
     ours = run_module(R.GaussianRasterizer, R.GaussianRasterizationSettings, scene, cam, grads=(dcol, dfeat))
-    ref = run_module(REF.GaussianRasterizer, REF.GaussianRasterizationSettings, scene, cam, grads=(dcol, dfeat))
-    ref2 = run_module(REF.GaussianRasterizer, REF.GaussianRasterizationSettings, scene, cam, grads=(dcol, dfeat))
+    refs = [run_module(REF.GaussianRasterizer, REF.GaussianRasterizationSettings, scene, cam, grads=(dcol, dfeat))
+            for _ in range(3)]
     for k in ("means3D", "means2D", "shs", "language_feature", "opacities", "scales", "rotations"):
-        err = rel_err(ours["grads"][k], ref["grads"][k])
         # The bar is the north star's 1e-4 (max-abs error / max-abs value).  At this size the reference's unordered
-        # float atomics make its OWN two runs differ by 3e-5 ... 1e-4 on dL_dscales (profiles/tools/grad_noise.py;
-        # every other tensor stays below 5e-6), so where that self-noise is the larger quantity it sets the bar.
-        noise = rel_err(ref2["grads"][k], ref["grads"][k])
-        assert err < max(1e-4, 2.0 * noise), f"{k}: rel err {err:.3e} (reference vs itself: {noise:.3e})"
+        # float atomics make its OWN runs differ by 3e-5 ... 1.2e-4 on dL_dscales (profiles/tools/grad_noise.py; every
+        # other tensor stays below 5e-6; ours vs ours: < 2e-5), so a single reference run is not a fixed point to
+        # measure against.  Compare with the mean of three reference runs and, where the reference's scatter about
+        # that mean is the larger quantity, let three times that scatter set the bar.
+        mean = sum(r["grads"][k].double() for r in refs) / len(refs)
+        noise = max(rel_err(r["grads"][k], mean) for r in refs)
+        err = rel_err(ours["grads"][k], mean)
+        assert err < max(1e-4, 3.0 * noise), f"{k}: rel err {err:.3e} (reference runs about their mean: {noise:.3e})"
 
 
 def test_config5_forward_structure_and_reference():
