@@ -482,6 +482,7 @@ int lsr_forward(const lsr_frame* frame, const lsr_inputs* in, float* out_color, 
       launch_tile_ranges(R, keys_sorted, id_bits, img.ranges, s);
       LSR_STAGE("tile_ranges");
     }
+    if (LSR_TILE_ORDER) launch_tile_order(T, img.ranges, img.tile_order, s);
     prof(g_ev_f, 7, s);
   } else if (g_profile) {
     for (int i = 0; i <= 7; i++) prof(g_ev_f, i, s);
@@ -493,7 +494,7 @@ int lsr_forward(const lsr_frame* frame, const lsr_inputs* in, float* out_color, 
     LSR_CUDA(cudaMemsetAsync(out_color, 0, 3 * N * sizeof(float), s));
     if (frame->include_feature) LSR_CUDA(cudaMemsetAsync(out_feature, 0, 3 * N * sizeof(float), s));
   } else {
-    launch_render_fwd(W, H, img.ranges, (const uint32_t*)list, g.rec, frame->bg, frame->include_feature != 0,
+    launch_render_fwd(W, H, img.ranges, LSR_TILE_ORDER ? img.tile_order : nullptr, (const uint32_t*)list, g.rec, frame->bg, frame->include_feature != 0,
                       img.final_T, img.n_contrib, out_color, out_feature, s);
     LSR_STAGE("render_fwd");
   }
@@ -515,7 +516,8 @@ int lsr_forward_feature_level(int32_t P, int32_t width, int32_t height, const in
   }
   GeomView g = geom_view(geom, P);
   ImageView img = image_view(const_cast<void*>(image), width, height);
-  launch_refeature_render(P, width, height, radii, language_feature, g.rec, img.ranges, (const uint32_t*)list,
+  launch_refeature_render(P, width, height, radii, language_feature, g.rec, img.ranges,
+                          LSR_TILE_ORDER ? img.tile_order : nullptr, (const uint32_t*)list,
                           out_feature, s);
   LSR_CUDA(cudaGetLastError());
   return LSR_OK;
@@ -570,7 +572,7 @@ int lsr_backward(const lsr_frame* frame, const lsr_inputs* in, const int32_t* ra
   prof(g_ev_b, 1, s);
   GeomView g = geom_view(const_cast<void*>(geom), P);
   ImageView img = image_view(const_cast<void*>(image), W, H);
-  launch_render_bwd(W, H, img.ranges, (const uint32_t*)list, g.rec, frame->bg, frame->include_feature != 0,
+  launch_render_bwd(W, H, img.ranges, LSR_TILE_ORDER ? img.tile_order : nullptr, (const uint32_t*)list, g.rec, frame->bg, frame->include_feature != 0,
                     img.final_T, img.n_contrib, dL_dcolor, dL_dfeature, need_mask, gr.dL_dmeans2D, gr.dL_dconic,
                     gr.dL_dopacity, gr.dL_dcolors, gr.dL_dlanguage_feature, s);
   LSR_STAGE("render_bwd");

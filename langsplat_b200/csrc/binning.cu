@@ -290,6 +290,41 @@ tile_ranges_kernel(uint32_t L, const uint64_t* __restrict__ keys, int tile_shift
   }
 }
 
+// The blend kernels' CTA -> tile map: tiles by descending list length, so that the long-running quadrants start first
+// and the last wave of the grid consists of short ones (the hardware hands out CTAs in index order).  Counting sort on
+// min(len / 8, 255), one CTA; the order inside a bucket is irrelevant (it only schedules; results do not depend on it).
+__global__ void __launch_bounds__(1024)
+tile_order_kernel(int T, const uint2* __restrict__ ranges, uint32_t* __restrict__ order) {
+  __shared__ uint32_t s_cnt[256];
+  const int tid = threadIdx.x;
+  if (tid < 256) s_cnt[tid] = 0;
+  __syncthreads();
+  for (int t = tid; t < T; t += 1024) {
+    const uint2 r = ranges[t];
+    atomicAdd(&s_cnt[255u - min((r.y - r.x) >> 3, 255u)], 1u);
+  }
+  __syncthreads();
+  if (tid < 32) {  // exclusive scan of the 256 counts by one warp (8 per lane)
+    uint32_t v[8], sum = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) { v[i] = s_cnt[tid * 8 + i]; sum += v[i]; }
+    uint32_t inc = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+      if (tid >= d) inc += o;
+    }
+    uint32_t run = inc - sum;
+#pragma unroll
+    for (int i = 0; i < 8; i++) { s_cnt[tid * 8 + i] = run; run += v[i]; }
+  }
+  __syncthreads();
+  for (int t = tid; t < T; t += 1024) {
+    const uint2 r = ranges[t];
+    order[atomicAdd(&s_cnt[255u - min((r.y - r.x) >> 3, 255u)], 1u)] = (uint32_t)t;
+  }
+}
+
 // sorted word (tile << id_bits | index) -> the reference's key format (tile << 32 | depth bits of that Gaussian)
 __global__ void __launch_bounds__(256)
 unpack_keys_kernel(uint32_t L, const uint64_t* __restrict__ words, const float* __restrict__ depths,
@@ -334,6 +369,12 @@ void launch_duplicate(int P, int grid_x, int grid_y, const uint32_t* perm, const
 void launch_tile_ranges(int64_t R, const uint64_t* keys, int tile_shift, uint2* ranges, cudaStream_t s) {
   if (R <= 0) return;
   tile_ranges_kernel<<<(unsigned)((R + 1023) / 1024), 256, 0, s>>>((uint32_t)R, keys, tile_shift, ranges);
+  count_launch();
+}
+
+void launch_tile_order(int T, const uint2* ranges, uint32_t* order, cudaStream_t s) {
+  if (T <= 0) return;
+  tile_order_kernel<<<1, 1024, 0, s>>>(T, ranges, order);
   count_launch();
 }
 

@@ -12,6 +12,9 @@ constexpr int TILE_PIX = TILE_X * TILE_Y;
 
 // render_bwd accumulates pair-weighted moments instead of the six geometric gradient sums, preprocess_bwd applies the
 // per-Gaussian coefficients (see render_bwd.cu).  0 restores the direct sums (A/B measurements).
+#ifndef LSR_TILE_ORDER
+#define LSR_TILE_ORDER 1  // blend kernels take the tiles heaviest first (shorter tail of the last wave)
+#endif
 #ifndef LSR_FWD_PK
 #define LSR_FWD_PK 1  // forward blend: both pixels of a thread through packed fp32 (FFMA2) instructions
 #endif
@@ -41,6 +44,7 @@ struct ImageView {
   float* final_T;
   uint32_t* n_contrib;
   uint2* ranges;
+  uint32_t* tile_order;  // tiles by descending list length: the blend kernels' CTA -> tile map (heaviest first)
 };
 
 __host__ __device__ inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
@@ -69,12 +73,13 @@ inline ImageView image_view(void* base, int W, int H) {
   v.final_T = (float*)p;       p += align_up(N * 4);
   v.n_contrib = (uint32_t*)p;  p += align_up(N * 4);
   v.ranges = (uint2*)p;        p += align_up(T * 8);
+  v.tile_order = (uint32_t*)p; p += align_up(T * 4);
   return v;
 }
 inline size_t image_bytes(int W, int H) {
   size_t N = (size_t)W * H;
   size_t T = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
-  return 2 * align_up(N * 4) + align_up(T * 8) + 256;
+  return 2 * align_up(N * 4) + align_up(T * 8) + align_up(T * 4) + 256;
 }
 
 // ---- radix sort geometry (radix_sort.cu) ----
@@ -179,6 +184,8 @@ void launch_duplicate(int P, int grid_x, int grid_y, const uint32_t* perm, const
                       uint64_t* words, int64_t capacity, const SortPlan& plan, uint32_t* ghist, cudaStream_t s);
 // tile id of a sorted word = word >> tile_shift (32 for reference-format keys)
 void launch_tile_ranges(int64_t R, const uint64_t* keys, int tile_shift, uint2* ranges, cudaStream_t s);
+// order[] = the T tiles by descending list length (counting sort, one CTA); any R, also 0
+void launch_tile_order(int T, const uint2* ranges, uint32_t* order, cudaStream_t s);
 // reference-format keys (tile << 32 | depth bits) from the sorted instance words (tests / debugging)
 void launch_unpack_keys(int64_t R, const uint64_t* words, const float* depths, uint64_t* keys, int id_bits,
                         cudaStream_t s);
@@ -187,13 +194,14 @@ void sort_prepare(void* work, int64_t n, const SortPlan& pl, cudaStream_t s);
 int sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
                uint64_t* keys_tmp, uint32_t* vals_tmp, int64_t n, const SortPlan& pl, bool hist_ready, void* work,
                cudaStream_t s);
-void launch_render_fwd(int W, int H, const uint2* ranges, const uint32_t* list, const GeomRec* rec, const float* bg,
+void launch_render_fwd(int W, int H, const uint2* ranges, const uint32_t* order, const uint32_t* list, const GeomRec* rec, const float* bg,
                        bool include_feature, float* final_T, uint32_t* n_contrib, float* out_color,
                        float* out_feature, cudaStream_t s);
 // feature-only re-blend of an already binned frame with another [P,3] language feature (records updated in place)
 void launch_refeature_render(int P, int W, int H, const int32_t* radii, const float* lang, GeomRec* rec,
-                             const uint2* ranges, const uint32_t* list, float* out_feature, cudaStream_t s);
-void launch_render_bwd(int W, int H, const uint2* ranges, const uint32_t* list, const GeomRec* rec, const float* bg,
+                             const uint2* ranges, const uint32_t* order, const uint32_t* list, float* out_feature,
+                             cudaStream_t s);
+void launch_render_bwd(int W, int H, const uint2* ranges, const uint32_t* order, const uint32_t* list, const GeomRec* rec, const float* bg,
                        bool include_feature, const float* final_T, const uint32_t* n_contrib, const float* dL_dcolor,
                        const float* dL_dfeature, uint32_t need_mask, float* dL_dmean2D, float* dL_dconic,
                        float* dL_dopacity, float* dL_dcolors, float* dL_dfeat, cudaStream_t s);

@@ -86,7 +86,8 @@ constexpr int BWD_SLOTS = BLEND_SLOTS;  // pixels per thread (rows r, r+4)
 #endif
 template <bool FEAT, bool DCOL, bool GEOM>
 __global__ void __launch_bounds__(32, LSR_BWD_MINB)
-render_bwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, const uint32_t* __restrict__ list,
+render_bwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, const uint32_t* __restrict__ order,
+                  const uint32_t* __restrict__ list,
                   const GeomRec* __restrict__ rec, const float* __restrict__ bg, const float* __restrict__ final_Ts,
                   const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
                   const float* __restrict__ dL_dpixels_F, float* __restrict__ dL_dmean2D,
@@ -109,7 +110,8 @@ render_bwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
   __shared__ __align__(16) float s_red[SMEM_REDUCE ? NV * RED_ROW : 4];
 
   const int lane = threadIdx.x;
-  const uint32_t tile = blockIdx.x / QUADS, quad = blockIdx.x % QUADS;
+  const uint32_t quad = blockIdx.x % QUADS;
+  const uint32_t tile = order ? __ldg(order + blockIdx.x / QUADS) : blockIdx.x / QUADS;
   const uint32_t qx0 = (tile % tiles_x) * TILE_X + (quad % QUADS_X) * QUAD_X;
   const uint32_t qy0 = (tile / tiles_x) * TILE_Y + (quad / QUADS_X) * QUAD_Y;
   const uint32_t px = qx0 + (lane & 7), py0 = qy0 + (lane >> 3);  // slot s adds 4*s rows
@@ -308,19 +310,19 @@ render_bwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
 }
 
 template <bool FEAT, bool DCOL, bool GEOM>
-void launch_one(unsigned grid, cudaStream_t s, int W, int H, int tiles_x, const uint2* ranges, const uint32_t* list,
-                const GeomRec* rec, const float* bg, const float* final_T, const uint32_t* n_contrib,
+void launch_one(unsigned grid, cudaStream_t s, int W, int H, int tiles_x, const uint2* ranges, const uint32_t* order,
+                const uint32_t* list, const GeomRec* rec, const float* bg, const float* final_T, const uint32_t* n_contrib,
                 const float* dL_dcolor, const float* dL_dfeature, float* dL_dmean2D, float* dL_dconic,
                 float* dL_dopacity, float* dL_dcolors, float* dL_dfeat) {
-  render_bwd_kernel<FEAT, DCOL, GEOM><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, list, rec, bg, final_T, n_contrib,
-                                                        dL_dcolor, dL_dfeature, dL_dmean2D, dL_dconic, dL_dopacity,
+  render_bwd_kernel<FEAT, DCOL, GEOM><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, order, list, rec, bg, final_T,
+                                                        n_contrib, dL_dcolor, dL_dfeature, dL_dmean2D, dL_dconic, dL_dopacity,
                                                         dL_dcolors, dL_dfeat);
 }
 
 }  // namespace
 
-void launch_render_bwd(int W, int H, const uint2* ranges, const uint32_t* list, const GeomRec* rec, const float* bg,
-                       bool include_feature, const float* final_T, const uint32_t* n_contrib, const float* dL_dcolor,
+void launch_render_bwd(int W, int H, const uint2* ranges, const uint32_t* order, const uint32_t* list,
+                       const GeomRec* rec, const float* bg, bool include_feature, const float* final_T, const uint32_t* n_contrib, const float* dL_dcolor,
                        const float* dL_dfeature, uint32_t need_mask, float* dL_dmean2D, float* dL_dconic,
                        float* dL_dopacity, float* dL_dcolors, float* dL_dfeat, cudaStream_t s) {
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
@@ -331,8 +333,8 @@ void launch_render_bwd(int W, int H, const uint2* ranges, const uint32_t* list, 
   const bool geom = (need_mask & LSR_NEED_GEOMETRY) != 0;
   if (!feat && !dcol) return;  // no upstream gradient at all: everything stays zero
 #define LSR_BWD(F, D, G)                                                                                      \
-  launch_one<F, D, G>(grid, s, W, H, tiles_x, ranges, list, rec, bg, final_T, n_contrib, dL_dcolor, dL_dfeature, \
-                      dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolors, dL_dfeat)
+  launch_one<F, D, G>(grid, s, W, H, tiles_x, ranges, order, list, rec, bg, final_T, n_contrib, dL_dcolor,   \
+                      dL_dfeature, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolors, dL_dfeat)
   if (feat) {
     if (dcol) { if (geom) LSR_BWD(true, true, true); else LSR_BWD(true, true, false); }
     else      { if (geom) LSR_BWD(true, false, true); else LSR_BWD(true, false, false); }

@@ -24,7 +24,8 @@ constexpr int FWD_SLOTS = BLEND_SLOTS;
 // same walk and the same decisions, but no RGB accumulation and no colour / final_T / n_contrib stores.
 template <bool FEAT, bool COLOR>
 __global__ void __launch_bounds__(32)
-render_fwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, const uint32_t* __restrict__ list,
+render_fwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, const uint32_t* __restrict__ order,
+                  const uint32_t* __restrict__ list,
                   const GeomRec* __restrict__ rec, const float* __restrict__ bg, float* __restrict__ final_T,
                   uint32_t* __restrict__ n_contrib, float* __restrict__ out_color, float* __restrict__ out_feature) {
 #if LSR_FWD_PK
@@ -34,7 +35,8 @@ render_fwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
 #endif
 
   const int lane = threadIdx.x;
-  const uint32_t tile = blockIdx.x / QUADS, quad = blockIdx.x % QUADS;
+  const uint32_t quad = blockIdx.x % QUADS;
+  const uint32_t tile = order ? __ldg(order + blockIdx.x / QUADS) : blockIdx.x / QUADS;
   const uint32_t qx0 = (tile % tiles_x) * TILE_X + (quad % QUADS_X) * QUAD_X;
   const uint32_t qy0 = (tile / tiles_x) * TILE_Y + (quad / QUADS_X) * QUAD_Y;
   const uint32_t px = qx0 + (lane & 7), py0 = qy0 + (lane >> 3);  // slot s adds 4*s rows
@@ -174,23 +176,24 @@ refeature_kernel(int P, const int32_t* __restrict__ radii, const float* __restri
 
 }  // namespace
 
-void launch_render_fwd(int W, int H, const uint2* ranges, const uint32_t* list, const GeomRec* rec, const float* bg,
+void launch_render_fwd(int W, int H, const uint2* ranges, const uint32_t* order, const uint32_t* list, const GeomRec* rec, const float* bg,
                        bool include_feature, float* final_T, uint32_t* n_contrib, float* out_color,
                        float* out_feature, cudaStream_t s) {
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
   if (tiles_x == 0 || tiles_y == 0) return;
   const unsigned grid = (unsigned)tiles_x * (unsigned)tiles_y * QUADS;
   if (include_feature)
-    render_fwd_kernel<true, true><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, list, rec, bg, final_T, n_contrib,
+    render_fwd_kernel<true, true><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, order, list, rec, bg, final_T, n_contrib,
                                                       out_color, out_feature);
   else
-    render_fwd_kernel<false, true><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, list, rec, bg, final_T, n_contrib,
+    render_fwd_kernel<false, true><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, order, list, rec, bg, final_T, n_contrib,
                                                        out_color, out_feature);
   count_launch();
 }
 
 void launch_refeature_render(int P, int W, int H, const int32_t* radii, const float* lang, GeomRec* rec,
-                             const uint2* ranges, const uint32_t* list, float* out_feature, cudaStream_t s) {
+                             const uint2* ranges, const uint32_t* order, const uint32_t* list, float* out_feature,
+                             cudaStream_t s) {
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
   if (P > 0) {
     refeature_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, radii, lang, rec);
@@ -198,7 +201,7 @@ void launch_refeature_render(int P, int W, int H, const int32_t* radii, const fl
   }
   if (tiles_x == 0 || tiles_y == 0) return;
   const unsigned grid = (unsigned)tiles_x * (unsigned)tiles_y * QUADS;
-  render_fwd_kernel<true, false><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, list, rec, nullptr, nullptr, nullptr,
+  render_fwd_kernel<true, false><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, order, list, rec, nullptr, nullptr, nullptr,
                                                      nullptr, out_feature);
   count_launch();
 }
