@@ -555,7 +555,8 @@ def main():
         d_passes = (d_bits + 7) // 8
         byt = {"preprocess_fwd": 20 * P + 291 * V, "depth_order": 16 * P + 16 * P * d_passes + 4 * P,
                "scan": 12 * P, "duplicate": 8 * P + 12 * V + 8 * Rn,
-               "sort": Rn * (16 * t_passes + 4), "tile_ranges": 8 * Rn + 8 * T, "render_fwd": 52 * Rn + 32 * N,
+               "sort": Rn * (16 * t_passes + 4), "tile_ranges": 8 * Rn + 8 * T + 12 * T,  # + tile ordering: ranges -> CTA map
+               "render_fwd": 52 * Rn + 32 * N,
                "bwd_zero_fill": 56 * P, "render_bwd": 52 * Rn + 32 * N + 48 * V, "preprocess_bwd": 236 * P + 303 * V}
         ins = {"render_fwd": 20 * Kx + 15 * Kc, "render_bwd": 20 * Kx + 54 * Kc}
         table = {}

@@ -482,7 +482,7 @@ int lsr_forward(const lsr_frame* frame, const lsr_inputs* in, float* out_color, 
       launch_tile_ranges(R, keys_sorted, id_bits, img.ranges, s);
       LSR_STAGE("tile_ranges");
     }
-    if (LSR_TILE_ORDER) launch_tile_order(T, img.ranges, img.tile_order, s);
+    if (LSR_TILE_ORDER) launch_tile_order(T, img.ranges, img.tile_order, s);  // also when nothing was rendered
     prof(g_ev_f, 7, s);
   } else if (g_profile) {
     for (int i = 0; i <= 7; i++) prof(g_ev_f, i, s);

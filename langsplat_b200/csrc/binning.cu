@@ -261,11 +261,67 @@ duplicate_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const
 // ------------------------------------------------------------------------------------------------------------
 // K5': identifyTileRanges (rasterizer_impl.cu:116-138).  ranges must be zero on entry (cudaMemset, :313).
 // ------------------------------------------------------------------------------------------------------------
+// The blend kernels' CTA -> tile map: tiles by descending list length, so that the long-running quadrants start first
+// and the last wave of the grid consists of short ones (the hardware hands out CTAs in index order).  Counting sort on
+// min(len / 8, 255) by ONE CTA of 1024 threads; the order inside a bucket is irrelevant (it only schedules; results do
+// not depend on it).
+__device__ __forceinline__ void order_tiles(int T, const uint2* __restrict__ ranges, uint32_t* __restrict__ order,
+                                            uint32_t* s_cnt) {
+  const int tid = threadIdx.x;
+  if (tid < 256) s_cnt[tid] = 0;
+  __syncthreads();
+  constexpr int KEEP = 8;  // a thread's first tiles stay in registers (all of them up to 8192 tiles)
+  uint32_t bucket[KEEP];
+#pragma unroll
+  for (int k = 0; k < KEEP; k++) {
+    const int t = tid + k * 1024;
+    bucket[k] = 0;
+    if (t < T) {
+      const uint2 r = __ldg(ranges + t);
+      bucket[k] = 255u - min((r.y - r.x) >> 3, 255u);
+      atomicAdd(&s_cnt[bucket[k]], 1u);
+    }
+  }
+  for (int t = tid + KEEP * 1024; t < T; t += 1024) {
+    const uint2 r = __ldg(ranges + t);
+    atomicAdd(&s_cnt[255u - min((r.y - r.x) >> 3, 255u)], 1u);
+  }
+  __syncthreads();
+  if (tid < 32) {  // exclusive scan of the 256 counts by one warp (8 per lane)
+    uint32_t v[8], sum = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) { v[i] = s_cnt[tid * 8 + i]; sum += v[i]; }
+    uint32_t inc = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+      if (tid >= d) inc += o;
+    }
+    uint32_t run = inc - sum;
+#pragma unroll
+    for (int i = 0; i < 8; i++) { s_cnt[tid * 8 + i] = run; run += v[i]; }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < KEEP; k++) {
+    const int t = tid + k * 1024;
+    if (t < T) order[atomicAdd(&s_cnt[bucket[k]], 1u)] = (uint32_t)t;
+  }
+  for (int t = tid + KEEP * 1024; t < T; t += 1024) {
+    const uint2 r = __ldg(ranges + t);
+    order[atomicAdd(&s_cnt[255u - min((r.y - r.x) >> 3, 255u)], 1u)] = (uint32_t)t;
+  }
+}
+
+__global__ void __launch_bounds__(1024)
+tile_order_kernel(int T, const uint2* __restrict__ ranges, uint32_t* __restrict__ order) {
+  __shared__ uint32_t s_cnt[256];
+  order_tiles(T, ranges, order, s_cnt);
+}
+
 // Four consecutive words per thread (two 128-bit loads), one extra load for the predecessor of the first.
-__global__ void __launch_bounds__(256)
-tile_ranges_kernel(uint32_t L, const uint64_t* __restrict__ keys, int tile_shift, uint2* __restrict__ ranges) {
-  const uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4u;
-  if (i0 >= L) return;
+__device__ __forceinline__ void mark_ranges(uint32_t i0, uint32_t L, const uint64_t* __restrict__ keys, int tile_shift,
+                                            uint2* __restrict__ ranges) {
   uint64_t k[4];
   if (i0 + 4 <= L) {
     const ulonglong2 a = __ldg(reinterpret_cast<const ulonglong2*>(keys + i0));
@@ -290,39 +346,12 @@ tile_ranges_kernel(uint32_t L, const uint64_t* __restrict__ keys, int tile_shift
   }
 }
 
-// The blend kernels' CTA -> tile map: tiles by descending list length, so that the long-running quadrants start first
-// and the last wave of the grid consists of short ones (the hardware hands out CTAs in index order).  Counting sort on
-// min(len / 8, 255), one CTA; the order inside a bucket is irrelevant (it only schedules; results do not depend on it).
-__global__ void __launch_bounds__(1024)
-tile_order_kernel(int T, const uint2* __restrict__ ranges, uint32_t* __restrict__ order) {
-  __shared__ uint32_t s_cnt[256];
-  const int tid = threadIdx.x;
-  if (tid < 256) s_cnt[tid] = 0;
-  __syncthreads();
-  for (int t = tid; t < T; t += 1024) {
-    const uint2 r = ranges[t];
-    atomicAdd(&s_cnt[255u - min((r.y - r.x) >> 3, 255u)], 1u);
-  }
-  __syncthreads();
-  if (tid < 32) {  // exclusive scan of the 256 counts by one warp (8 per lane)
-    uint32_t v[8], sum = 0;
-#pragma unroll
-    for (int i = 0; i < 8; i++) { v[i] = s_cnt[tid * 8 + i]; sum += v[i]; }
-    uint32_t inc = sum;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
-      if (tid >= d) inc += o;
-    }
-    uint32_t run = inc - sum;
-#pragma unroll
-    for (int i = 0; i < 8; i++) { s_cnt[tid * 8 + i] = run; run += v[i]; }
-  }
-  __syncthreads();
-  for (int t = tid; t < T; t += 1024) {
-    const uint2 r = ranges[t];
-    order[atomicAdd(&s_cnt[255u - min((r.y - r.x) >> 3, 255u)], 1u)] = (uint32_t)t;
-  }
+// (Ordering the tiles inside this kernel — the CTA that finishes last does it — was measured: the ticket and the fence
+// cost every CTA more than the extra launch saves, 32.6 vs 25.5 us for the stage.)
+__global__ void __launch_bounds__(256)
+tile_ranges_kernel(uint32_t L, const uint64_t* __restrict__ keys, int tile_shift, uint2* __restrict__ ranges) {
+  const uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4u;
+  if (i0 < L) mark_ranges(i0, L, keys, tile_shift, ranges);
 }
 
 // sorted word (tile << id_bits | index) -> the reference's key format (tile << 32 | depth bits of that Gaussian)
