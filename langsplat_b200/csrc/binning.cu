@@ -263,28 +263,35 @@ duplicate_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const
 // ------------------------------------------------------------------------------------------------------------
 // The blend kernels' CTA -> tile map: tiles by descending list length, so that the long-running quadrants start first
 // and the last wave of the grid consists of short ones (the hardware hands out CTAs in index order).  Counting sort on
-// min(len / 8, 255) by ONE CTA of 1024 threads; the order inside a bucket is irrelevant (it only schedules; results do
+// a 256-level logarithmic length scale by ONE CTA of 1024 threads; the order inside a bucket is irrelevant (it only schedules; results do
 // not depend on it).
+// 256 buckets on a logarithmic scale (4 fractional bits: ~6 % resolution at any list length), longest lists first
+__device__ __forceinline__ uint32_t order_bucket(uint2 r) {
+  const uint32_t len = r.y - r.x;
+  uint32_t key = len;
+  if (len >= 16u) {
+    const uint32_t e = 31u - (uint32_t)__clz((int)len);  // >= 4
+    key = min((e - 3u) * 16u + ((len >> (e - 4u)) & 15u), 255u);
+  }
+  return 255u - key;
+}
+
 __device__ __forceinline__ void order_tiles(int T, const uint2* __restrict__ ranges, uint32_t* __restrict__ order,
                                             uint32_t* s_cnt) {
   const int tid = threadIdx.x;
   if (tid < 256) s_cnt[tid] = 0;
   __syncthreads();
-  constexpr int KEEP = 8;  // a thread's first tiles stay in registers (all of them up to 8192 tiles)
-  uint32_t bucket[KEEP];
+  constexpr int CH = 8;  // tiles per thread and chunk: the 8 loads of a chunk are in flight together
+  for (int base = 0; base < T; base += CH * 1024) {
+    uint32_t bucket[CH];
 #pragma unroll
-  for (int k = 0; k < KEEP; k++) {
-    const int t = tid + k * 1024;
-    bucket[k] = 0;
-    if (t < T) {
-      const uint2 r = __ldg(ranges + t);
-      bucket[k] = 255u - min((r.y - r.x) >> 3, 255u);
-      atomicAdd(&s_cnt[bucket[k]], 1u);
+    for (int k = 0; k < CH; k++) {
+      const int t = base + tid + k * 1024;
+      bucket[k] = t < T ? order_bucket(__ldg(ranges + t)) : 256u;
     }
-  }
-  for (int t = tid + KEEP * 1024; t < T; t += 1024) {
-    const uint2 r = __ldg(ranges + t);
-    atomicAdd(&s_cnt[255u - min((r.y - r.x) >> 3, 255u)], 1u);
+#pragma unroll
+    for (int k = 0; k < CH; k++)  // (warp-aggregating these with MATCH.ANY was measured slower)
+      if (bucket[k] < 256u) atomicAdd(&s_cnt[bucket[k]], 1u);
   }
   __syncthreads();
   if (tid < 32) {  // exclusive scan of the 256 counts by one warp (8 per lane)
@@ -302,14 +309,16 @@ __device__ __forceinline__ void order_tiles(int T, const uint2* __restrict__ ran
     for (int i = 0; i < 8; i++) { s_cnt[tid * 8 + i] = run; run += v[i]; }
   }
   __syncthreads();
+  for (int base = 0; base < T; base += CH * 1024) {
+    uint32_t bucket[CH];
 #pragma unroll
-  for (int k = 0; k < KEEP; k++) {
-    const int t = tid + k * 1024;
-    if (t < T) order[atomicAdd(&s_cnt[bucket[k]], 1u)] = (uint32_t)t;
-  }
-  for (int t = tid + KEEP * 1024; t < T; t += 1024) {
-    const uint2 r = __ldg(ranges + t);
-    order[atomicAdd(&s_cnt[255u - min((r.y - r.x) >> 3, 255u)], 1u)] = (uint32_t)t;
+    for (int k = 0; k < CH; k++) {
+      const int t = base + tid + k * 1024;
+      bucket[k] = t < T ? order_bucket(__ldg(ranges + t)) : 256u;
+    }
+#pragma unroll
+    for (int k = 0; k < CH; k++)
+      if (bucket[k] < 256u) order[atomicAdd(&s_cnt[bucket[k]], 1u)] = (uint32_t)(base + tid + k * 1024);
   }
 }
 
