@@ -337,6 +337,54 @@ int lsr_adam_step(int32_t n_tensors, const lsr_adam_tensor* tensors, int64_t ste
   return LSR_OK;
 }
 
+static int decoder_check(const lsr_decoder* d) {
+  if (!d) return fail(LSR_ERR_INVALID, "null decoder");
+  if (d->n_layers < 1 || d->n_layers > LSR_DECODER_MAX_LAYERS)
+    return fail(LSR_ERR_INVALID, "decoder needs 1..%d layers", LSR_DECODER_MAX_LAYERS);
+  for (int l = 0; l <= d->n_layers; l++)
+    if (d->dims[l] < 1 || d->dims[l] > 512) return fail(LSR_ERR_INVALID, "decoder widths must be in 1..512");
+  for (int l = 0; l < d->n_layers; l++)
+    if (!d->weight[l] || !d->bias[l]) return fail(LSR_ERR_INVALID, "layer %d: null pointer", l);
+  return LSR_OK;
+}
+
+size_t lsr_decoder_packed_bytes(const lsr_decoder* dec) {
+  if (decoder_check(dec) != LSR_OK) return 0;
+  return decoder_packed_bytes(dec);
+}
+
+int lsr_decoder_pack(const lsr_decoder* dec, float* packed, void* stream) {
+  if (int rc = decoder_check(dec)) return rc;
+  if (!packed || ((uintptr_t)packed & 15)) return fail(LSR_ERR_INVALID, "packed must be a 16-byte aligned device pointer");
+  launch_decoder_pack(dec, packed, (cudaStream_t)stream);
+  LSR_CUDA(cudaGetLastError());
+  return LSR_OK;
+}
+
+int lsr_decode(const lsr_decoder* dec, const float* in, int64_t n, int32_t precision, float* out, const float* phrases,
+               int32_t n_pos, int32_t n_neg, float* relevancy, void* stream) {
+  if (int rc = decoder_check(dec)) return rc;
+  if (n < 0) return fail(LSR_ERR_INVALID, "n < 0");
+  if (precision != LSR_DECODE_FP32 && precision != LSR_DECODE_TF32) return fail(LSR_ERR_INVALID, "unknown precision");
+  if (relevancy) {
+    if (!phrases) return fail(LSR_ERR_INVALID, "relevancy needs phrase embeddings");
+    if (n_pos < 1 || n_neg < 1 || n_pos + n_neg > LSR_DECODER_MAX_PHRASES)
+      return fail(LSR_ERR_INVALID, "need n_pos >= 1, n_neg >= 1, n_pos + n_neg <= %d", LSR_DECODER_MAX_PHRASES);
+  } else {
+    phrases = nullptr;
+    n_pos = n_neg = 0;
+  }
+  if (!out && !relevancy) return fail(LSR_ERR_INVALID, "nothing to compute (out and relevancy are both null)");
+  if (n == 0) return LSR_OK;
+  if (!in) return fail(LSR_ERR_INVALID, "null pointer");
+  if (precision == LSR_DECODE_TF32) {
+    if (const char* why = decoder_tc_unsupported(dec)) return fail(LSR_ERR_INVALID, "tensor-core decode: %s", why);
+    if (out && ((uintptr_t)out & 15)) return fail(LSR_ERR_INVALID, "out must be 16-byte aligned");
+  }
+  LSR_CUDA(launch_decode(dec, in, n, precision, out, phrases, n_pos, n_neg, relevancy, (cudaStream_t)stream));
+  return LSR_OK;
+}
+
 int lsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, void* stream) {
   (void)projmatrix;  // the reference's in_frustum computes p_proj but only tests p_view.z (auxiliary.h:139-164)

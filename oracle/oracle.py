@@ -288,3 +288,33 @@ def adam_step(param, grad, exp_avg, exp_avg_sq, step, lr, beta1=0.9, beta2=0.999
         on = np.asarray(visible, bool).reshape((-1,) + (1,) * (p.ndim - 1))
         new, m, v = np.where(on, new, p), np.where(on, m, m0), np.where(on, v, v0)
     return new, m, v
+
+
+def decode_features(x, weights, biases, dtype=np.float64):
+    """Autoencoder.decode (autoencoder/model.py:42-46, decoder built at :18-25): Linear, then (ReLU, Linear) for every
+    further layer, then x / x.norm(dim=-1, keepdim=True).  weights[l] is nn.Linear's [out, in] matrix.  float64 by
+    default (the checker); dtype=np.float32 for the timed CPU baseline."""
+    h = _np(x, dtype)
+    for l, (w, b) in enumerate(zip(weights, biases)):
+        if l > 0:
+            h = np.maximum(h, 0)
+        h = h @ _np(w, dtype).T + _np(b, dtype)
+    return h / np.sqrt((h * h).sum(-1, keepdims=True))
+
+
+def relevancy(embed, phrases, n_pos, dtype=np.float64):
+    """OpenCLIPNetwork.get_relevancy for every positive phrase (eval/openclip_encoder.py:42-56): sims = embed @ p.T,
+    softmax over the pair (10 * positive, 10 * negative_j) for every negative j, the pair whose positive probability is
+    lowest is returned.  Returns [n_pos, N, 2] (column 0 is what get_max_across keeps, :96-111)."""
+    e, p = _np(embed, dtype), _np(phrases, dtype)
+    sims = e @ p.T
+    neg = sims[:, n_pos:]
+    out = np.empty((n_pos, e.shape[0], 2), dtype)
+    for j in range(n_pos):
+        pos = np.repeat(sims[:, j:j + 1], neg.shape[1], 1)
+        pair = 10 * np.stack((pos, neg), -1)
+        pair = np.exp(pair - pair.max(-1, keepdims=True))
+        sm = pair / pair.sum(-1, keepdims=True)
+        best = sm[..., 0].argmin(1)
+        out[j] = sm[np.arange(e.shape[0]), best]
+    return out

@@ -1,0 +1,127 @@
+"""Eval-side decode: decoder MLP + phrase relevancy.  The oracle's float64 restatement is pinned
+on vectors produced by the reference's own Autoencoder.decode and OpenCLIPNetwork.get_relevancy
+(tests/golden/make_golden_decoder.py); on the GPU langsplat_b200.decode.FeatureDecoder (lsr_decode through the C ABI)
+is held to the same vectors and to the oracle at ragged sizes.
+Tolerances (outputs are unit 512-vectors, components ~0.04, and probabilities):
+  fp32 variant: 1e-5 on features, 2e-5 on relevancy (summation order only);
+  tf32 variant (tcgen05, TF32 operands, fp32 accumulate): 5e-4 on features, 1e-3 on relevancy — TF32 operand rounding
+  emulated on the CPU for the golden case gives 1.1e-4 / 2.4e-4 with truncation, 3.5e-5 / 6e-5 with rounding."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import orc
+
+GOLD = np.load(os.path.join(os.path.dirname(__file__), "golden", "decoder.npz"))
+NL = int(GOLD["n_layers"])
+WS = [GOLD[f"w{i}"] for i in range(NL)]
+BS = [GOLD[f"b{i}"] for i in range(NL)]
+N_POS = int(GOLD["n_pos"])
+TOL = {"fp32": (1e-5, 2e-5), "tf32": (5e-4, 1e-3)}
+
+
+def test_oracle_matches_reference_vectors():
+    y = orc.decode_features(GOLD["x"], WS, BS)
+    assert np.abs(y - GOLD["y"]).max() < 5e-7
+    r = orc.relevancy(GOLD["y"], GOLD["phrases"], N_POS)
+    assert np.abs(r - GOLD["relevancy"]).max() < 1e-6
+    assert np.abs(r.sum(-1) - 1).max() < 1e-12
+
+
+def test_oracle_decode_is_scale_free_after_first_relu_free_layer():
+    # property used at full size on the GPU: outputs are unit vectors
+    y = orc.decode_features(np.random.default_rng(0).normal(size=(64, 3)), WS, BS)
+    assert np.abs(np.sqrt((y * y).sum(-1)) - 1).max() < 1e-12
+
+
+def _decoder(precision):
+    from langsplat_b200.decode import FeatureDecoder
+    dev = torch.device("cuda:0")
+    dec = FeatureDecoder([torch.from_numpy(w).to(dev) for w in WS], [torch.from_numpy(b).to(dev) for b in BS], precision)
+    ph = torch.from_numpy(GOLD["phrases"]).to(dev)
+    dec.set_phrases(ph[:N_POS], ph[N_POS:])
+    return dec, dev
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+def test_gpu_matches_reference_vectors(precision):
+    from langsplat_b200 import _lib
+    dec, dev = _decoder(precision)
+    x = torch.from_numpy(GOLD["x"]).to(dev)
+    before = _lib.load().lsr_launch_count()
+    y = dec.decode(x)
+    rel = dec.relevancy_maps(x)
+    torch.cuda.synchronize()
+    assert _lib.load().lsr_launch_count() > before
+    tf, tr = TOL[precision]
+    assert np.abs(y.cpu().numpy() - GOLD["y"]).max() < tf
+    assert np.abs(rel.cpu().numpy() - GOLD["relevancy"][..., 0]).max() < tr
+    pair = dec.get_relevancy(x, 1).cpu().numpy()
+    assert np.abs(pair - GOLD["relevancy"][1]).max() < tr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+@pytest.mark.parametrize("n", [1, 31, 127, 128, 129, 1000, 148 * 128 * 2 + 77])
+def test_gpu_matches_oracle_ragged(precision, n):
+    dec, dev = _decoder(precision)
+    rng = np.random.default_rng(100 + n)
+    x = rng.normal(size=(n, 3)).astype(np.float32)
+    x /= np.linalg.norm(x, axis=-1, keepdims=True)
+    y0 = orc.decode_features(x, WS, BS)
+    r0 = orc.relevancy(y0, GOLD["phrases"], N_POS)[..., 0]
+    xt = torch.from_numpy(x).to(dev)
+    tf, tr = TOL[precision]
+    assert np.abs(dec.decode(xt).cpu().numpy() - y0).max() < tf
+    assert np.abs(dec.relevancy_maps(xt).cpu().numpy() - r0).max() < tr
+
+
+@pytest.mark.gpu
+def test_gpu_empty_and_errors():
+    from langsplat_b200.decode import FeatureDecoder
+    from langsplat_b200 import LsrError
+    dec, dev = _decoder("tf32")
+    assert dec.decode(torch.empty((0, 3), device=dev)).shape == (0, 512)
+    assert dec.relevancy_maps(torch.empty((0, 3), device=dev)).shape == (N_POS, 0)
+    with pytest.raises(LsrError):
+        dec.decode(torch.zeros((4, 5), device=dev))
+    with pytest.raises(LsrError):
+        dec.decode(torch.zeros((4, 3)))
+    odd = FeatureDecoder([torch.randn(10, 3, device=dev), torch.randn(7, 10, device=dev)],
+                         [torch.randn(10, device=dev), torch.randn(7, device=dev)], "tf32")
+    x = torch.randn(50, 3, device=dev)
+    with pytest.raises(LsrError, match="multiples of 16"):
+        odd.decode(x)
+    y = odd.decode(x, precision="fp32")  # the fp32 variant takes any widths
+    w = [t.cpu().numpy() for t in odd.weights]
+    b = [t.cpu().numpy() for t in odd.biases]
+    assert np.abs(y.cpu().numpy() - orc.decode_features(x.cpu().numpy(), w, b)).max() < 1e-5
+    with pytest.raises(LsrError):
+        odd.relevancy_maps(x)  # no phrases set
+
+
+@pytest.mark.gpu
+def test_gpu_full_size_properties():
+    """A 1440x1080 eval image, three levels (the shape of eval/evaluate_iou_loc.py:256-259): unit outputs, both
+    variants agree, get_max_across has the reference's layout, many tiles per CTA."""
+    dec, dev = _decoder("tf32")
+    g = torch.Generator(device="cpu").manual_seed(5)
+    sem = torch.randn(3, 270, 360, 3, generator=g)
+    sem = (sem / sem.norm(dim=-1, keepdim=True)).to(dev)
+    y = dec.decode(sem)
+    assert y.shape == (3, 270, 360, 512)
+    assert float((y.norm(dim=-1) - 1).abs().max()) < 1e-5
+    y32 = dec.decode(sem, precision="fp32")
+    assert float((y - y32).abs().max()) < TOL["tf32"][0]
+    rel = dec.get_max_across(sem)
+    assert rel.shape == (3, N_POS, 270, 360)
+    rel32 = dec.get_max_across(sem, precision="fp32")
+    assert float((rel - rel32).abs().max()) < TOL["tf32"][1]
+    assert float(rel.min()) >= 0.0 and float(rel.max()) <= 1.0
+    big = torch.randn(1080 * 1440, 3, generator=g).to(dev)
+    r1 = dec.relevancy_maps(big)
+    r2 = dec.relevancy_maps(big[: 1080 * 720])
+    assert torch.equal(r1[:, : 1080 * 720], r2)  # pixels are independent: a prefix gives the same values
