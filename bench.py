@@ -721,7 +721,9 @@ def adjacent_ops(P, W, H, dev, hbm_peak):
     a, at, l, lt = timed(act_ours), timed(act_torch), timed(loss_ours), timed(loss_torch)
     ak, lk = timed(act_kernels, 50), timed(loss_kernels, 50)
     ad, adt, gtk = timed(o_ours.step), timed(o_torch.step), timed(gt_ours, 50)
-    return {"adam_step": {"us": ad, "torch_us": adt, "bytes": adam_bytes,
+    decode = decode_ops(dev)
+    return {"decode_relevancy": decode,
+            "adam_step": {"us": ad, "torch_us": adt, "bytes": adam_bytes,
                           "hbm_frac": adam_bytes / (ad * 1e-6) / 1e9 / hbm_peak},
             "gt_feature_map": {"us": gtk, "reference_cpu_ms": gt_ref_ms, "bytes": gt_bytes,
                                "hbm_frac": gt_bytes / (gtk * 1e-6) / 1e9 / hbm_peak},
@@ -731,6 +733,66 @@ def adjacent_ops(P, W, H, dev, hbm_peak):
                                   "hbm_frac": loss_bytes / (lk * 1e-6) / 1e9 / hbm_peak},
             "note": "kernels_us: the two kernels back to back through the C ABI; autograd_us / torch_us: the Python "
                     "call sequence on one stream (host-bound at this size), CUDA events"}
+
+
+def decode_ops(dev):
+    """Eval-side decode on one 1440x1080 feature map: 3-d features -> decoder MLP -> relevancy
+    against 3 positive + 4 negative phrases, our fused kernel (tcgen05 TF32 and IEEE-fp32 variants) next to the
+    reference's PyTorch call sequence (nn.Linear chain, mm, softmax; eval/openclip_encoder.py:42-56) on the same GPU.
+    Random-init weights of the reference's architecture.  Tensor-bound: achieved TFLOP/s = 2 * MACs / time; the peak
+    quoted is half the measured dense bf16 figure (TF32 runs at half the bf16 rate).  Not part of `value` / `e2e`."""
+    try:
+        from langsplat_b200.decode import FeatureDecoder
+        dims = [3, 16, 32, 64, 128, 256, 256, 512]
+        g = torch.Generator().manual_seed(9)
+        ws = [(torch.randn(dims[i + 1], dims[i], generator=g) / dims[i] ** 0.5).to(dev) for i in range(7)]
+        bs = [(0.1 * torch.randn(dims[i + 1], generator=g)).to(dev) for i in range(7)]
+        ph = torch.randn(7, 512, generator=g)
+        ph = (ph / ph.norm(dim=-1, keepdim=True)).to(dev)
+        n = 1440 * 1080
+        x = torch.randn(n, 3, generator=g)
+        x = (x / x.norm(dim=-1, keepdim=True)).to(dev)
+        dec = FeatureDecoder(ws, bs, "tf32")
+        dec.set_phrases(ph[:3], ph[3:])
+
+        def torch_way():
+            with torch.no_grad():
+                h = x
+                for i in range(7):
+                    h = torch.nn.functional.linear(torch.relu(h) if i else h, ws[i], bs[i])
+                h = h / h.norm(dim=-1, keepdim=True)
+                out = torch.mm(h, ph.T)
+                res = []
+                for j in range(3):
+                    sm = torch.softmax(10 * torch.stack((out[:, j:j + 1].repeat(1, 4), out[:, 3:]), -1), -1)
+                    best = sm[..., 0].argmin(1)
+                    res.append(torch.gather(sm, 1, best[..., None, None].expand(n, 4, 2))[:, 0, 0])
+                return torch.stack(res)
+
+        def timed(fn, k):
+            fn()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(k):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1) / k
+
+        t_tc = timed(lambda: dec.relevancy_maps(x), 10)
+        t_32 = timed(lambda: dec.relevancy_maps(x, precision="fp32"), 3)
+        t_ref = timed(torch_way, 3)
+        err = float((dec.relevancy_maps(x) - torch_way()).abs().max())
+        macs = sum(dims[i] * dims[i + 1] for i in range(7)) + 7 * 512
+        peaks = measured_peaks() if "measured_peaks" in globals() else {}
+        tf32_peak = 0.5 * float(peaks.get("bf16_tflops", 1667.1)) if isinstance(peaks, dict) else 833.5
+        tfs = 2.0 * macs * n / (t_tc * 1e-3) / 1e12
+        return {"pixels": n, "tf32_ms": t_tc, "fp32_ms": t_32, "torch_ms": t_ref, "max_abs_diff_vs_torch": err,
+                "roofline": {"bound": "tensor", "achieved": tfs, "peak": tf32_peak, "unit": "TFLOP/s",
+                             "frac": tfs / tf32_peak, "peak_source": "0.5 x measured dense bf16 (TF32 rate)"}}
+    except Exception as e:  # noqa: BLE001 — a side measurement must not cost the headline line
+        return {"error": repr(e)}
 
 
 if __name__ == "__main__":

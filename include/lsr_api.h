@@ -263,8 +263,9 @@ int lsr_adam_step(int32_t n_tensors, const lsr_adam_tensor* tensors, int64_t ste
  * (eval/openclip_encoder.py:42-56, 96-111) with one fused kernel.
  * lsr_decoder: n_layers Linear layers, layer l maps dims[l] -> dims[l+1] with nn.Linear's weight [dims[l+1], dims[l]]
  * (row-major) and bias [dims[l+1]]; ReLU between layers, none after the last; the result is divided by its L2 norm.
- * `packed` (device, lsr_decoder_packed_bytes bytes, 16-byte aligned) is the weight blob lsr_decoder_pack writes for the
- * tensor-core variant (pack once per checkpoint); it may be null when only LSR_DECODE_FP32 is used.
+ * packed_tf32 / packed_f16 (device, lsr_decoder_packed_bytes(dec, precision) bytes, 16-byte aligned) are the weight
+ * blobs lsr_decoder_pack writes for the tensor-core variants (pack once per checkpoint); each may be null when its
+ * variant is not used.
  * lsr_decode: in [n, dims[0]] (a flattened [H,W,3] feature image) ->
  *   out [n, dims[L]] unit vectors (may be null), and/or
  *   relevancy [n_pos, n]: for positive phrase j the first column of get_relevancy(embed, j), i.e.
@@ -272,23 +273,31 @@ int lsr_adam_step(int32_t n_tensors, const lsr_adam_tensor* tensors, int64_t ste
  * phrases [n_pos + n_neg, dims[L]]: unit phrase embeddings, positives first (pos_embeds then neg_embeds);
  * n_pos + n_neg <= LSR_DECODER_MAX_PHRASES, n_neg >= 1 when relevancy is requested.
  * precision: LSR_DECODE_FP32 = IEEE fp32 on the FP32 pipe (the reference's arithmetic up to summation order);
- * LSR_DECODE_TF32 = tcgen05 tensor cores, TF32 operands with fp32 accumulation in TMEM (needs `packed`; layer widths
- * multiples of 16, at most 512, inputs at most 256 wide; otherwise LSR_ERR_INVALID). */
+ * LSR_DECODE_TF32 / LSR_DECODE_F16 = tcgen05 tensor cores with fp32 accumulation in TMEM, operands as TF32 (fp32
+ * truncated to 10 mantissa bits) or fp16 (rounded to nearest, clamped to +-65504); both need their packed blob,
+ * layer widths that are multiples of 16 and at most 512 (256 for all but the last), inputs at most 256 wide;
+ * otherwise LSR_ERR_INVALID. */
 #define LSR_DECODER_MAX_LAYERS 8
 #define LSR_DECODER_MAX_PHRASES 16
 #define LSR_DECODE_FP32 0
 #define LSR_DECODE_TF32 1
+#define LSR_DECODE_F16 2
 typedef struct lsr_decoder {
   int32_t n_layers;
   int32_t dims[LSR_DECODER_MAX_LAYERS + 1];
   const float* weight[LSR_DECODER_MAX_LAYERS];
   const float* bias[LSR_DECODER_MAX_LAYERS];
-  const float* packed;
+  const void* packed_tf32;
+  const void* packed_f16;
 } lsr_decoder;
-size_t lsr_decoder_packed_bytes(const lsr_decoder* dec);
-int lsr_decoder_pack(const lsr_decoder* dec, float* packed, void* stream);
+size_t lsr_decoder_packed_bytes(const lsr_decoder* dec, int32_t precision);
+int lsr_decoder_pack(const lsr_decoder* dec, int32_t precision, void* packed, void* stream);
 int lsr_decode(const lsr_decoder* dec, const float* in, int64_t n, int32_t precision, float* out, const float* phrases,
                int32_t n_pos, int32_t n_neg, float* relevancy, void* stream);
+/* Profiling aid: later tensor-core lsr_decode launches make CTA 0 write clock64() stamps of its second tile into
+ * device_buffer (>= 64 int64: tile start, then per pass "MMAs issued", "accumulator complete", "epilogue done");
+ * null switches it off. */
+int lsr_debug_decode_trace(void* device_buffer);
 
 /* Stable ascending radix sort of (uint64 key, uint32 value) pairs on bits [0, end_bit) — the sort the forward uses
  * in place of cub::DeviceRadixSort::SortPairs (rasterizer_impl.cu:306-311); exported for unit tests.

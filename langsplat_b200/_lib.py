@@ -54,13 +54,13 @@ class AdamTensor(ctypes.Structure):  # lsr_adam_tensor
 
 
 ADAM_MAX_TENSORS = 8
-DECODER_MAX_LAYERS, DECODER_MAX_PHRASES, DECODE_FP32, DECODE_TF32 = 8, 16, 0, 1
+DECODER_MAX_LAYERS, DECODER_MAX_PHRASES, DECODE_FP32, DECODE_TF32, DECODE_F16 = 8, 16, 0, 1, 2
 
 
 class Decoder(ctypes.Structure):  # lsr_decoder
     _fields_ = [("n_layers", c_int32), ("dims", c_int32 * (DECODER_MAX_LAYERS + 1)),
                 ("weight", c_void_p * DECODER_MAX_LAYERS), ("bias", c_void_p * DECODER_MAX_LAYERS),
-                ("packed", c_void_p)]
+                ("packed_tf32", c_void_p), ("packed_f16", c_void_p)]
 
 
 EXPORTS = {
@@ -93,10 +93,11 @@ EXPORTS = {
     "lsr_language_feature_map": (c_int, [c_void_p, c_int32, c_int64, c_int32, c_int32, c_void_p, c_int32, c_int32,
                                          c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "lsr_adam_step": (c_int, [c_int32, c_void_p, c_int64, c_double, c_double, c_double, c_void_p, c_void_p]),
-    "lsr_decoder_packed_bytes": (c_size_t, [POINTER(Decoder)]),
-    "lsr_decoder_pack": (c_int, [POINTER(Decoder), c_void_p, c_void_p]),
+    "lsr_decoder_packed_bytes": (c_size_t, [POINTER(Decoder), c_int32]),
+    "lsr_decoder_pack": (c_int, [POINTER(Decoder), c_int32, c_void_p, c_void_p]),
     "lsr_decode": (c_int, [POINTER(Decoder), c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_int32, c_int32, c_void_p,
                            c_void_p]),
+    "lsr_debug_decode_trace": (c_int, [c_void_p]),
     "lsr_mark_visible": (c_int, [c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "lsr_l1_loss_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_int32, c_int64, c_void_p, c_void_p]),
     "lsr_l1_loss_backward": (c_int, [c_void_p, c_void_p, c_void_p, c_int32, c_int64, c_void_p, c_void_p, c_void_p]),

@@ -348,15 +348,26 @@ static int decoder_check(const lsr_decoder* d) {
   return LSR_OK;
 }
 
-size_t lsr_decoder_packed_bytes(const lsr_decoder* dec) {
-  if (decoder_check(dec) != LSR_OK) return 0;
-  return decoder_packed_bytes(dec);
+int lsr_debug_decode_trace(void* device_buffer) {
+  decoder_set_trace(device_buffer);
+  return LSR_OK;
 }
 
-int lsr_decoder_pack(const lsr_decoder* dec, float* packed, void* stream) {
+static bool decoder_tc_precision(int32_t precision) {
+  return precision == LSR_DECODE_TF32 || precision == LSR_DECODE_F16;
+}
+
+size_t lsr_decoder_packed_bytes(const lsr_decoder* dec, int32_t precision) {
+  if (decoder_check(dec) != LSR_OK) return 0;
+  if (!decoder_tc_precision(precision)) { fail(LSR_ERR_INVALID, "only the tensor-core variants use packed weights"); return 0; }
+  return decoder_packed_bytes(dec, precision);
+}
+
+int lsr_decoder_pack(const lsr_decoder* dec, int32_t precision, void* packed, void* stream) {
   if (int rc = decoder_check(dec)) return rc;
+  if (!decoder_tc_precision(precision)) return fail(LSR_ERR_INVALID, "only the tensor-core variants use packed weights");
   if (!packed || ((uintptr_t)packed & 15)) return fail(LSR_ERR_INVALID, "packed must be a 16-byte aligned device pointer");
-  launch_decoder_pack(dec, packed, (cudaStream_t)stream);
+  launch_decoder_pack(dec, precision, packed, (cudaStream_t)stream);
   LSR_CUDA(cudaGetLastError());
   return LSR_OK;
 }
@@ -365,7 +376,7 @@ int lsr_decode(const lsr_decoder* dec, const float* in, int64_t n, int32_t preci
                int32_t n_pos, int32_t n_neg, float* relevancy, void* stream) {
   if (int rc = decoder_check(dec)) return rc;
   if (n < 0) return fail(LSR_ERR_INVALID, "n < 0");
-  if (precision != LSR_DECODE_FP32 && precision != LSR_DECODE_TF32) return fail(LSR_ERR_INVALID, "unknown precision");
+  if (precision != LSR_DECODE_FP32 && !decoder_tc_precision(precision)) return fail(LSR_ERR_INVALID, "unknown precision");
   if (relevancy) {
     if (!phrases) return fail(LSR_ERR_INVALID, "relevancy needs phrase embeddings");
     if (n_pos < 1 || n_neg < 1 || n_pos + n_neg > LSR_DECODER_MAX_PHRASES)
@@ -377,9 +388,13 @@ int lsr_decode(const lsr_decoder* dec, const float* in, int64_t n, int32_t preci
   if (!out && !relevancy) return fail(LSR_ERR_INVALID, "nothing to compute (out and relevancy are both null)");
   if (n == 0) return LSR_OK;
   if (!in) return fail(LSR_ERR_INVALID, "null pointer");
-  if (precision == LSR_DECODE_TF32) {
-    if (const char* why = decoder_tc_unsupported(dec)) return fail(LSR_ERR_INVALID, "tensor-core decode: %s", why);
+  if (decoder_tc_precision(precision)) {
+    if (const char* why = decoder_tc_unsupported(dec, precision)) return fail(LSR_ERR_INVALID, "tensor-core decode: %s", why);
     if (out && ((uintptr_t)out & 15)) return fail(LSR_ERR_INVALID, "out must be 16-byte aligned");
+    const int64_t ph_floats = (int64_t)(n_pos + n_neg) * dec->dims[dec->n_layers];
+    if (relevancy && ph_floats > (precision == LSR_DECODE_F16 ? 4096 : 8192))
+      return fail(LSR_ERR_INVALID, "tensor-core decode: phrase table too large for shared memory (%s)",
+                  precision == LSR_DECODE_F16 ? "f16: 8 phrases of 512" : "tf32: 16 phrases of 512");
   }
   LSR_CUDA(launch_decode(dec, in, n, precision, out, phrases, n_pos, n_neg, relevancy, (cudaStream_t)stream));
   return LSR_OK;

@@ -228,9 +228,10 @@ void launch_activate_backward(int P, const float* scaling, const float* rotation
                               float* d_opacity, float* d_feature, cudaStream_t s);
 void launch_feature_map(const void* seg, int seg_is_float, int64_t seg_row_stride, int W, int H, const float* table,
                         int K, int C, float* out, uint8_t* mask_u8, float* mask_f, int* bad, cudaStream_t s);
-size_t decoder_packed_bytes(const lsr_decoder* d);
-void launch_decoder_pack(const lsr_decoder* d, float* packed, cudaStream_t s);
-const char* decoder_tc_unsupported(const lsr_decoder* d);
+void decoder_set_trace(void* dev_buf);
+size_t decoder_packed_bytes(const lsr_decoder* d, int precision);
+void launch_decoder_pack(const lsr_decoder* d, int precision, void* packed, cudaStream_t s);
+const char* decoder_tc_unsupported(const lsr_decoder* d, int precision);
 cudaError_t launch_decode(const lsr_decoder* d, const float* in, int64_t n, int precision, float* out,
                           const float* phrases, int n_pos, int n_neg, float* relev, cudaStream_t s);
 void launch_adam(int n, const lsr_adam_tensor* ts, int64_t step, double beta1, double beta2, double eps,

@@ -6,16 +6,22 @@
 // and then an [N,512] x [512,n] mm per level; here ONE kernel keeps a tile of pixels on chip from the 3-d input to
 // the relevancy value: 12 B read and 4*n_pos B written per pixel (plus 2 KB if the restored feature is wanted).
 //
-// Two kernels behind lsr_decode:
-//   * decode_tc_kernel (precision = LSR_DECODE_TF32): 128 pixels per CTA = the 128 TMEM lanes.  Every layer is a
-//     tcgen05.mma.kind::tf32 chain (M = 128, N = layer width, K = 8 per instruction) issued by one thread; the A operand
-//     (activations, fp32 in the canonical no-swizzle K-major core-matrix layout: [K/4][128 rows][4 floats]) stays in
-//     shared memory, the B operand (weights, pre-packed once by lsr_decoder_pack into the same [K/4][N][4] layout)
-//     streams from L2 through a 4-stage ring of 16 KB slices filled by cp.async.bulk (TMA 1-D) on mbarriers, the
-//     accumulator lives in TMEM (up to 512 columns).  Epilogue per layer: tcgen05.ld, + bias, ReLU, back into the A
-//     buffer; last layer: norm, phrase dot products and the softmax pair on the CUDA cores straight out of TMEM.
-//   * decode_fp32_kernel (precision = LSR_DECODE_FP32): the same fusion on the FP32 pipe (32 pixels per CTA,
-//     activations ping-pong in shared memory), IEEE fp32 like the reference's SGEMM — the exact-arithmetic variant.
+// Kernels behind lsr_decode:
+//   * decode_tc_kernel<F16> (LSR_DECODE_TF32 / LSR_DECODE_F16): 128 pixels per CTA = the 128 TMEM lanes.  Every layer
+//     is a tcgen05.mma chain (kind::tf32, K = 8 per instruction, or kind::f16, K = 16; M = 128, N = layer width) issued
+//     by one thread; the A operand (activations, in the canonical no-swizzle K-major core-matrix layout:
+//     [K chunks of 16 B][128 rows]) stays in shared memory, the B operand (weights, pre-packed once by lsr_decoder_pack
+//     into the same layout) streams from L2 through a ring of 16 KB slices filled by cp.async.bulk (TMA 1-D) on
+//     mbarriers, the accumulator lives in TMEM (256 columns; a 512-wide last layer is two passes).  Epilogue per layer:
+//     tcgen05.ld, + bias, ReLU, back into the A buffer; last layer: norm, phrase dot products and the softmax pair on
+//     the CUDA cores straight out of TMEM.  TF32: fp32 activations (128 KB), one CTA per SM, operands truncated to 10
+//     mantissa bits by the tensor core.  F16: activations and weights rounded to nearest fp16 (same 10 mantissa bits,
+//     values clamped to +-65504), 64 KB of activations, two CTAs per SM so one CTA's epilogue overlaps the other's
+//     MMAs, half the weight bytes per tile and twice the MMA rate.  fp32 accumulation, bias, norm and relevancy in both.
+//   * decode_fp32_kernel (LSR_DECODE_FP32): the same fusion on the FP32 pipe (32 pixels per CTA, activations ping-pong
+//     in shared memory), IEEE fp32 like the reference's SGEMM — the exact-arithmetic variant.
+#include <cuda_fp16.h>
+
 #include <cmath>
 #include <cstdlib>
 
@@ -146,50 +152,71 @@ decode_fp32_kernel(const DecArgs a, const float* __restrict__ in, int64_t n, flo
     __syncthreads();
   }
 }
-
 // ------------------------------------------------------------------------------------------------------------------
-// weight packing for the tensor-core variant: layer l -> [Kp/4][N][4] floats (Kp = K rounded up to 8, zero padded):
-// the canonical no-swizzle K-major UMMA layout (8-row x 16-byte core matrices, 128 B apart along N, N*16 B along K).
-__global__ void pack_weights_kernel(const float* __restrict__ W, int K, int N, int Kp, float4* __restrict__ dst) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= (Kp / 4) * N) return;
-  const int kc = i / N, o = i - kc * N;
-  float v[4];
-#pragma unroll
-  for (int j = 0; j < 4; j++) {
-    const int k = kc * 4 + j;
-    v[j] = k < K ? __ldg(W + (size_t)o * K + k) : 0.0f;
-  }
-  dst[i] = make_float4(v[0], v[1], v[2], v[3]);
-}
-
-// ------------------------------------------------------------------------------------------------------------------
-// tcgen05 variant
+// Tensor-core variants.  A "pass" is one accumulator's worth of a layer: rows [n0, n0 + Np) of its weight matrix,
+// Np <= 256 TMEM columns.  Every layer but the last is one pass (widths <= 256); a last layer wider than 256 is two
+// passes of half the width, run one after the other (norm and phrase dot products accumulate across them).
+// Packed weights of a pass: [Kp/E][Np][E] elements, E = elements per 16 bytes (4 tf32 / 8 f16), Kp = K rounded up to
+// 2E and zero padded: the canonical no-swizzle K-major UMMA layout (8-row x 16-byte core matrices, 128 B apart along
+// N, Np*16 B apart along K).
 constexpr int TC_M = 128;
-constexpr int TC_STAGES = 4;
 constexpr int TC_STAGE_BYTES = 16384;
 constexpr int TC_MAXK = 256;
-constexpr int TC_A_BYTES = TC_M * TC_MAXK * 4;                         // 128 KB
-constexpr int TC_PH_BYTES = DEC_MAXPH * DEC_MAXW * 4;                  // 32 KB
-constexpr int TC_BAR_OFF = TC_A_BYTES + TC_STAGES * TC_STAGE_BYTES + TC_PH_BYTES;
-constexpr int TC_SMEM = TC_BAR_OFF + 128;
 constexpr int TC_MAX_SLICES = 96;
-constexpr int TC_TMEM_COLS = 512;
+constexpr int TC_MAX_PASSES = DEC_MAXL + 1;
+constexpr int TC_TMEM_COLS = 256;
+
+template <bool F16>
+struct TcCfg {
+  static constexpr int E = F16 ? 8 : 4;                       // elements per 16-byte K chunk
+  static constexpr int A_BYTES = TC_M * TC_MAXK * (F16 ? 2 : 4);
+  static constexpr int STAGES = F16 ? 2 : 4;                  // f16: 112 KB per CTA -> two CTAs per SM
+  static constexpr int PH_BYTES = F16 ? 16384 : 32768;        // phrase embeddings (fp32) for the last epilogue
+  static constexpr int BAR_OFF = A_BYTES + STAGES * TC_STAGE_BYTES + PH_BYTES;
+  static constexpr int SMEM = BAR_OFF + 128;
+  static constexpr int CTAS_PER_SM = F16 ? 2 : 1;
+};
+
+__global__ void pack_weights_kernel(const float* __restrict__ W, int K, int Np, int Kp, int f16, uint4* __restrict__ dst) {
+  const int E = f16 ? 8 : 4;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (Kp / E) * Np) return;
+  const int kc = i / Np, o = i - kc * Np;
+  float v[8];
+#pragma unroll
+  for (int j = 0; j < 8; j++) {
+    const int k = kc * E + j;
+    v[j] = (j < E && k < K) ? __ldg(W + (size_t)o * K + k) : 0.0f;
+  }
+  uint4 r;
+  if (f16) {
+    __half2 h0 = __floats2half2_rn(v[0], v[1]), h1 = __floats2half2_rn(v[2], v[3]);
+    __half2 h2 = __floats2half2_rn(v[4], v[5]), h3 = __floats2half2_rn(v[6], v[7]);
+    r = make_uint4(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1),
+                   *reinterpret_cast<uint32_t*>(&h2), *reinterpret_cast<uint32_t*>(&h3));
+  } else {
+    r = make_uint4(__float_as_uint(v[0]), __float_as_uint(v[1]), __float_as_uint(v[2]), __float_as_uint(v[3]));
+  }
+  dst[i] = r;
+}
 
 struct TcSlice {
   uint32_t off16;  // offset of the slice in the packed blob, 16-byte units
   uint16_t nch;    // 16-byte K chunks in the slice (even)
-  uint8_t c0;      // first chunk index within the layer
-  uint8_t layer;
+  uint8_t c0;      // first chunk index within the pass
+  uint8_t pass;
 };
 struct TcArgs {
   int n_layers;
   int dims[DEC_MAXL + 1];
   const float* bias[DEC_MAXL];
-  const float* packed;
+  const void* packed;
+  uint32_t replica_stride16, replicas;
+  int exp_no_loads;  // experiment (LSR_DEC_EXP=2): arrive on the full barriers without copying (pure MMA + control timing)  // the blob is stored `replicas` times; CTA b reads copy b % replicas
+  int n_passes;
+  int pass_layer[TC_MAX_PASSES], pass_n0[TC_MAX_PASSES], pass_np[TC_MAX_PASSES];
+  int pass_slice_end[TC_MAX_PASSES];  // one past the last slice of each pass
   int n_slices;
-  int slice_end[DEC_MAXL];  // one past the last slice of each layer
-  int variant;              // debug: bit 0 swaps the LBO / SBO fields of the shared-memory descriptors
   TcSlice sl[TC_MAX_SLICES];
 };
 
@@ -226,14 +253,24 @@ __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.a
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
-                                            uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-      : "memory");
+template <bool F16>
+__device__ __forceinline__ void tc_mma(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                       uint32_t accumulate) {
+  if constexpr (F16) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  }
 }
 // K-major, no swizzle: start address, LBO = byte distance of the two 16-byte K chunks of one instruction,
 // SBO = byte distance of consecutive 8-row groups, descriptor version 1 (sm_100).
@@ -255,24 +292,34 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
 #pragma unroll
   for (int i = 0; i < 16; i++) v[i] = __uint_as_float(r[i]);
 }
+__device__ __forceinline__ uint32_t pack_h2(float a, float b) {
+  __half2 h = __floats2half2_rn(fminf(a, 65504.0f), fminf(b, 65504.0f));
+  return *reinterpret_cast<uint32_t*>(&h);
+}
 
-__global__ void __launch_bounds__(TC_M, 1)
+template <bool F16, int PHB>  // PHB: rows of the (zero padded) phrase table in shared memory, 8 or 16
+__global__ void __launch_bounds__(TC_M, TcCfg<F16>::CTAS_PER_SM)
 decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in, int64_t n, float* __restrict__ out,
-                 const float* __restrict__ phrases, int n_pos, int n_neg, float* __restrict__ relev) {
+                 const float* __restrict__ phrases, int n_pos, int n_neg, float* __restrict__ relev,
+                 long long* __restrict__ trace) {
+  using C = TcCfg<F16>;
+  constexpr int E = C::E;
   extern __shared__ __align__(1024) uint8_t tsm[];
-  float4* A = reinterpret_cast<float4*>(tsm);
-  uint8_t* stages = tsm + TC_A_BYTES;
-  float* ph = reinterpret_cast<float*>(stages + TC_STAGES * TC_STAGE_BYTES);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(tsm + TC_BAR_OFF);  // full[4], empty[4], done
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * TC_STAGES + 1);
+  uint4* A = reinterpret_cast<uint4*>(tsm);  // [K/E][128 rows] 16-byte chunks
+  uint8_t* stages = tsm + C::A_BYTES;
+  float* ph = reinterpret_cast<float*>(stages + C::STAGES * TC_STAGE_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(tsm + C::BAR_OFF);  // full[STAGES], empty[STAGES], done
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * C::STAGES + 1);
   const int tid = threadIdx.x, warp = tid >> 5;
-  const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + TC_STAGES), done = smem_u32(bars + 2 * TC_STAGES);
+  const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + C::STAGES), done = smem_u32(bars + 2 * C::STAGES);
   const uint32_t a_base = smem_u32(A), st_base = smem_u32(stages);
+  const uint8_t* packed = reinterpret_cast<const uint8_t*>(a.packed) +
+                          (size_t)(blockIdx.x % a.replicas) * a.replica_stride16 * 16;
   const int NL = a.dims[a.n_layers];
   const int n_ph = phrases ? n_pos + n_neg : 0;
 
   if (tid == 0) {
-    for (int i = 0; i < TC_STAGES; i++) { mbar_init(full0 + 8 * i, 1); mbar_init(empty0 + 8 * i, 1); }
+    for (int i = 0; i < C::STAGES; i++) { mbar_init(full0 + 8 * i, 1); mbar_init(empty0 + 8 * i, 1); }
     mbar_init(done, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -282,29 +329,38 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  for (int i = tid; i < n_ph * NL; i += TC_M) ph[i] = __ldg(phrases + i);
+  for (int i = tid; i < PHB * NL; i += TC_M) ph[i] = i < n_ph * NL ? __ldg(phrases + i) : 0.0f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   const uint32_t t_lane = tmem + ((uint32_t)(warp * 32) << 16);  // this warp's quarter of the 128 lanes
 
-  uint32_t it_load = 0, it_mma = 0;  // thread 0: slices loaded / multiplied so far (ring position and phase)
+  uint32_t it_load = 0, it_mma = 0;  // thread 32 / thread 0: slices requested / multiplied so far (ring position, phase)
   uint32_t done_phase = 0;
   const int64_t ntiles = (n + TC_M - 1) / TC_M;
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int64_t pix = tile * TC_M + tid;
     const bool live = pix < n;
-    {  // input row -> A, K padded to 8 with zeros
-      const int d0 = a.dims[0], kc_n = ((d0 + 7) & ~7) >> 2;
+    {  // input row -> A, K padded to 2E with zeros
+      const int d0 = a.dims[0], kc_n = ((d0 + 2 * E - 1) & ~(2 * E - 1)) / E;
       for (int kc = 0; kc < kc_n; kc++) {
-        float v[4];
+        float v[E];
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-          const int k = kc * 4 + j;
+        for (int j = 0; j < E; j++) {
+          const int k = kc * E + j;
           v[j] = (live && k < d0) ? __ldg(in + pix * d0 + k) : 0.0f;
         }
-        A[kc * TC_M + tid] = make_float4(v[0], v[1], v[2], v[3]);
+        if constexpr (F16) {
+          auto cv = [](float x, float y) {
+            __half2 h = __floats2half2_rn(fminf(fmaxf(x, -65504.0f), 65504.0f), fminf(fmaxf(y, -65504.0f), 65504.0f));
+            return *reinterpret_cast<uint32_t*>(&h);
+          };
+          A[kc * TC_M + tid] = make_uint4(cv(v[0], v[1]), cv(v[2], v[3]), cv(v[4 % E], v[5 % E]), cv(v[6 % E], v[7 % E]));
+        } else {
+          A[kc * TC_M + tid] = make_uint4(__float_as_uint(v[0]), __float_as_uint(v[1]), __float_as_uint(v[2]),
+                                          __float_as_uint(v[3]));
+        }
       }
     }
     fence_async_smem();
@@ -312,86 +368,116 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
     __syncthreads();
     tc_fence_after();
 
-    int next_load = 0;  // thread 0: next slice of this tile to request
-    for (int l = 0; l < a.n_layers; l++) {
-      const int N = a.dims[l + 1];
-      if (tid == 0) {
-        const int s_begin = l ? a.slice_end[l - 1] : 0, s_end = a.slice_end[l];
-        const int n_mma = N > 256 ? 2 : 1, Nm = N / n_mma;
-        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(Nm >> 3) << 17) | ((TC_M >> 4) << 24);
-        const uint32_t a_lbo = TC_M * 16, b_lbo = (uint32_t)N * 16, sbo = 128;
-        for (int s = s_begin; s < s_end; s++) {
-          while (next_load < a.n_slices && next_load <= s + 2) {  // keep up to three slices in flight
-            const TcSlice& q = a.sl[next_load];
-            const uint32_t st = it_load % TC_STAGES, use = it_load / TC_STAGES;
-            mbar_wait(empty0 + 8 * st, (use & 1) ^ 1);
-            const uint32_t bytes = (uint32_t)q.nch * (uint32_t)a.dims[q.layer + 1] * 16u;
+    const bool tr = trace && blockIdx.x == 0 && tid == 0 && tile == (int64_t)gridDim.x;  // CTA 0's second tile
+    int ti = 0;
+    if (tr) trace[ti++] = clock64();
+    int next_load = 0;  // thread 32: next slice of this tile to request
+    float ssp[4] = {0.0f, 0.0f, 0.0f, 0.0f}, sim[PHB];
+#pragma unroll
+    for (int j = 0; j < PHB; j++) sim[j] = 0.0f;
+
+    for (int p = 0; p < a.n_passes; p++) {
+      const int l = a.pass_layer[p], n0 = a.pass_n0[p], Np = a.pass_np[p];
+      const int s_begin = p ? a.pass_slice_end[p - 1] : 0, s_end = a.pass_slice_end[p];
+      if (tid == 32) {
+        // producer: weight slices of this pass, and up to STAGES - 1 slices of the next ones while this pass's epilogue
+        // runs (a stage is reused once the MMAs that read it have completed: empty barrier)
+        const int target = min(a.n_slices, s_end + C::STAGES - 1);
+        while (next_load < target) {
+          const TcSlice q = a.sl[next_load];
+          const uint32_t st = it_load % C::STAGES, use = it_load / C::STAGES;
+          mbar_wait(empty0 + 8 * st, (use & 1) ^ 1);
+          const uint32_t bytes = (uint32_t)q.nch * (uint32_t)a.pass_np[q.pass] * 16u;
+          if (a.exp_no_loads) {
+            mbar_expect_tx(full0 + 8 * st, 0);
+          } else {
             mbar_expect_tx(full0 + 8 * st, bytes);
-            bulk_g2s(st_base + st * TC_STAGE_BYTES, reinterpret_cast<const uint8_t*>(a.packed) + (size_t)q.off16 * 16,
-                     bytes, full0 + 8 * st);
-            it_load++;
-            next_load++;
+            bulk_g2s(st_base + st * TC_STAGE_BYTES, packed + (size_t)q.off16 * 16, bytes, full0 + 8 * st);
           }
-          const TcSlice& q = a.sl[s];
-          const uint32_t st = it_mma % TC_STAGES, use = it_mma / TC_STAGES;
+          it_load++;
+          next_load++;
+        }
+      } else if (tid == 0) {
+        // MMA issuer
+        const uint32_t fmt = F16 ? 0u : 2u;
+        const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(Np >> 3) << 17) | ((TC_M >> 4) << 24);
+        const uint32_t a_lbo = TC_M * 16, b_lbo = (uint32_t)Np * 16, sbo = 128;
+        const uint64_t a_step = (uint64_t)((2 * a_lbo) >> 4), b_step = (uint64_t)((2 * b_lbo) >> 4);
+        for (int s = s_begin; s < s_end; s++) {
+          const TcSlice q = a.sl[s];
+          const uint32_t st = it_mma % C::STAGES, use = it_mma / C::STAGES;
+          uint64_t ad = smem_desc(a_base + (uint32_t)q.c0 * a_lbo, a_lbo, sbo);
+          uint64_t bd = smem_desc(st_base + st * TC_STAGE_BYTES, b_lbo, sbo);
+          uint32_t acc = q.c0 > 0 ? 1u : 0u;
+          const int steps = q.nch >> 1;
           mbar_wait(full0 + 8 * st, use & 1);
           tc_fence_after();
-          const uint32_t b_base = st_base + st * TC_STAGE_BYTES;
-          for (int j = 0; j < q.nch / 2; j++) {
-            const uint32_t a_addr = a_base + (uint32_t)(q.c0 + 2 * j) * a_lbo;
-            const uint64_t ad = (a.variant & 1) ? smem_desc(a_addr, sbo, a_lbo) : smem_desc(a_addr, a_lbo, sbo);
-            for (int h = 0; h < n_mma; h++) {
-              const uint32_t b_addr = b_base + (uint32_t)(2 * j) * b_lbo + (uint32_t)(h * Nm) * 16;
-              const uint64_t bd = (a.variant & 1) ? smem_desc(b_addr, sbo, b_lbo) : smem_desc(b_addr, b_lbo, sbo);
-              tc_mma_tf32(tmem + (uint32_t)(h * Nm), ad, bd, idesc, (q.c0 + j) > 0 ? 1u : 0u);
-            }
+#pragma unroll 4
+          for (int j = 0; j < steps; j++) {
+            tc_mma<F16>(tmem, ad, bd, idesc, acc);
+            acc = 1u;
+            ad += a_step;
+            bd += b_step;
           }
           tc_commit(empty0 + 8 * st);  // the slice's stage is free once these MMAs have read it
           it_mma++;
         }
-        tc_commit(done);  // accumulator of this layer complete
+        tc_commit(done);  // accumulator of this pass complete
       }
+      if (tr) trace[ti++] = clock64();  // MMAs of the pass issued
       __syncwarp();
       mbar_wait(done, done_phase);
       done_phase ^= 1;
       __syncwarp();
       tc_fence_after();
+      if (tr) trace[ti++] = clock64();  // accumulator complete
 
-      const float* __restrict__ B = a.bias[l];
+      const float* __restrict__ B = a.bias[l] + n0;
       if (l + 1 < a.n_layers) {
-        for (int c = 0; c < N; c += 16) {
+        for (int c = 0; c < Np; c += 16) {
           float v[16];
           tmem_ld16(t_lane + c, v);
 #pragma unroll
           for (int q4 = 0; q4 < 4; q4++) {
-            float4 o;
-            o.x = fmaxf(v[q4 * 4 + 0] + __ldg(B + c + q4 * 4 + 0), 0.0f);
-            o.y = fmaxf(v[q4 * 4 + 1] + __ldg(B + c + q4 * 4 + 1), 0.0f);
-            o.z = fmaxf(v[q4 * 4 + 2] + __ldg(B + c + q4 * 4 + 2), 0.0f);
-            o.w = fmaxf(v[q4 * 4 + 3] + __ldg(B + c + q4 * 4 + 3), 0.0f);
-            A[((c >> 2) + q4) * TC_M + tid] = o;
+            const float4 b4 = __ldg(reinterpret_cast<const float4*>(B + c) + q4);
+            v[q4 * 4 + 0] = fmaxf(v[q4 * 4 + 0] + b4.x, 0.0f);
+            v[q4 * 4 + 1] = fmaxf(v[q4 * 4 + 1] + b4.y, 0.0f);
+            v[q4 * 4 + 2] = fmaxf(v[q4 * 4 + 2] + b4.z, 0.0f);
+            v[q4 * 4 + 3] = fmaxf(v[q4 * 4 + 3] + b4.w, 0.0f);
+          }
+          if constexpr (F16) {
+            A[((c >> 3) + 0) * TC_M + tid] =
+                make_uint4(pack_h2(v[0], v[1]), pack_h2(v[2], v[3]), pack_h2(v[4], v[5]), pack_h2(v[6], v[7]));
+            A[((c >> 3) + 1) * TC_M + tid] =
+                make_uint4(pack_h2(v[8], v[9]), pack_h2(v[10], v[11]), pack_h2(v[12], v[13]), pack_h2(v[14], v[15]));
+          } else {
+#pragma unroll
+            for (int q4 = 0; q4 < 4; q4++)
+              A[((c >> 2) + q4) * TC_M + tid] =
+                  make_uint4(__float_as_uint(v[q4 * 4 + 0]), __float_as_uint(v[q4 * 4 + 1]),
+                             __float_as_uint(v[q4 * 4 + 2]), __float_as_uint(v[q4 * 4 + 3]));
           }
         }
         fence_async_smem();
       } else {
-        float ss = 0.0f, sim[DEC_MAXPH];
-#pragma unroll
-        for (int j = 0; j < DEC_MAXPH; j++) sim[j] = 0.0f;
-        for (int c = 0; c < N; c += 16) {
+        // last layer: norm and phrase dot products accumulate over its passes; the unnormalised values are parked in
+        // `out` and scaled by this same thread once the norm is known
+        for (int c = 0; c < Np; c += 16) {
           float v[16];
           tmem_ld16(t_lane + c, v);
 #pragma unroll
-          for (int i = 0; i < 16; i++) {
-            v[i] += __ldg(B + c + i);
-            ss = fmaf(v[i], v[i], ss);
+          for (int q4 = 0; q4 < 4; q4++) {
+            const float4 b4 = __ldg(reinterpret_cast<const float4*>(B + c) + q4);
+            v[q4 * 4 + 0] += b4.x; v[q4 * 4 + 1] += b4.y; v[q4 * 4 + 2] += b4.z; v[q4 * 4 + 3] += b4.w;
           }
 #pragma unroll
-          for (int j = 0; j < DEC_MAXPH; j++) {
-            if (j < n_ph) {
-              const float4* pj = reinterpret_cast<const float4*>(ph + j * NL + c);
+          for (int i = 0; i < 16; i++) ssp[i & 3] = fmaf(v[i], v[i], ssp[i & 3]);
+          if (n_ph) {
 #pragma unroll
-              for (int q4 = 0; q4 < 4; q4++) {
-                const float4 w = pj[q4];
+            for (int q4 = 0; q4 < 4; q4++) {
+#pragma unroll
+              for (int j = 0; j < PHB; j++) {  // rows past n_ph are zeros: no branches, PHB independent chains
+                const float4 w = *reinterpret_cast<const float4*>(ph + j * NL + n0 + c + q4 * 4);
                 sim[j] = fmaf(v[q4 * 4 + 0], w.x, sim[j]);
                 sim[j] = fmaf(v[q4 * 4 + 1], w.y, sim[j]);
                 sim[j] = fmaf(v[q4 * 4 + 2], w.z, sim[j]);
@@ -399,30 +485,36 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
               }
             }
           }
+          if (out && live) {
+#pragma unroll
+            for (int q4 = 0; q4 < 4; q4++)
+              *reinterpret_cast<float4*>(out + pix * NL + n0 + c + q4 * 4) =
+                  make_float4(v[q4 * 4 + 0], v[q4 * 4 + 1], v[q4 * 4 + 2], v[q4 * 4 + 3]);
+          }
         }
-        const float norm = sqrtf(ss);
-        if (n_ph && live) {
-          float max_neg = -INFINITY;
+        if (p + 1 == a.n_passes) {
+          const float norm = sqrtf((ssp[0] + ssp[1]) + (ssp[2] + ssp[3]));
+          if (n_ph && live) {
+            float max_neg = -INFINITY;
 #pragma unroll
-          for (int j = 0; j < DEC_MAXPH; j++)
-            if (j >= n_pos && j < n_ph) max_neg = fmaxf(max_neg, sim[j] / norm);
+            for (int j = 0; j < PHB; j++)
+              if (j >= n_pos && j < n_ph) max_neg = fmaxf(max_neg, sim[j] / norm);
 #pragma unroll
-          for (int j = 0; j < DEC_MAXPH; j++)
-            if (j < n_pos) relev[(size_t)j * n + pix] = pair_softmax_pos(sim[j] / norm, max_neg);
-        }
-        if (out) {
-          for (int c = 0; c < N; c += 16) {
-            float v[16];
-            tmem_ld16(t_lane + c, v);  // whole warp takes part (.sync.aligned); only live rows store
-            if (live) {
-#pragma unroll
-              for (int q4 = 0; q4 < 4; q4++) {
-                float4 o;
-                o.x = (v[q4 * 4 + 0] + __ldg(B + c + q4 * 4 + 0)) / norm;
-                o.y = (v[q4 * 4 + 1] + __ldg(B + c + q4 * 4 + 1)) / norm;
-                o.z = (v[q4 * 4 + 2] + __ldg(B + c + q4 * 4 + 2)) / norm;
-                o.w = (v[q4 * 4 + 3] + __ldg(B + c + q4 * 4 + 3)) / norm;
-                *reinterpret_cast<float4*>(out + pix * N + c + q4 * 4) = o;
+            for (int j = 0; j < PHB; j++)
+              if (j < n_pos) relev[(size_t)j * n + pix] = pair_softmax_pos(sim[j] / norm, max_neg);
+          }
+          if (out) {  // each warp scales its own 32 rows, a row per instruction (coalesced, L2-resident)
+            __syncwarp();
+            const int lane = tid & 31;
+            for (int r = 0; r < 32; r++) {
+              const float nr = __shfl_sync(0xffffffffu, norm, r);
+              const int64_t prow = tile * TC_M + warp * 32 + r;
+              if (prow >= n) break;
+              float4* row = reinterpret_cast<float4*>(out + prow * NL);
+              for (int c = lane; c < NL / 4; c += 32) {
+                float4 v = row[c];
+                v.x /= nr; v.y /= nr; v.z /= nr; v.w /= nr;
+                row[c] = v;
               }
             }
           }
@@ -431,12 +523,29 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
       tc_fence_before();
       __syncthreads();
       tc_fence_after();
+      if (tr) trace[ti++] = clock64();  // epilogue done
     }
   }
   __syncthreads();
   if (warp == 0)
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TC_TMEM_COLS) : "memory");
 }
+
+// Copies of the packed weights in global memory (all CTAs stream the same bytes at about the same time; copies spread
+// the requests over more L2 lines).  LSR_DEC_REPLICAS overrides for experiments.
+int tc_replicas() {
+  static int r = 0;
+  if (!r) {
+    const char* e = getenv("LSR_DEC_REPLICAS");
+    r = e ? atoi(e) : 1;
+    if (r < 1) r = 1;
+    if (r > 64) r = 64;
+  }
+  return r;
+}
+size_t replica_stride16(const struct PassPlan& pl);
+
+long long* g_dec_trace = nullptr;  // debug: device buffer of clock64 stamps (lsr_debug_decode_trace)
 
 int g_sm_count = 0;
 int sm_count() {
@@ -449,98 +558,136 @@ int sm_count() {
   return g_sm_count;
 }
 
-size_t packed_floats(const lsr_decoder* d, size_t* layer_off) {
+// passes of a decoder and the element offset of each in the packed blob (in 16-byte units)
+struct PassPlan {
+  int n;
+  int layer[TC_MAX_PASSES], n0[TC_MAX_PASSES], np[TC_MAX_PASSES], kp[TC_MAX_PASSES];
+  size_t off16[TC_MAX_PASSES];
+  size_t total16;
+};
+PassPlan plan_passes(const lsr_decoder* d, bool f16) {
+  PassPlan pl{};
+  const int E = f16 ? 8 : 4;
   size_t off = 0;
   for (int l = 0; l < d->n_layers; l++) {
-    if (layer_off) layer_off[l] = off;
-    off += (size_t)((d->dims[l] + 7) & ~7) * d->dims[l + 1];
+    const int K = d->dims[l], N = d->dims[l + 1], Kp = (K + 2 * E - 1) & ~(2 * E - 1);
+    const int parts = N > 256 ? 2 : 1;
+    for (int h = 0; h < parts; h++) {
+      const int i = pl.n++;
+      pl.layer[i] = l; pl.np[i] = N / parts; pl.n0[i] = h * (N / parts); pl.kp[i] = Kp; pl.off16[i] = off;
+      off += (size_t)(Kp / E) * (N / parts);
+    }
   }
-  return off;
+  pl.total16 = off;
+  return pl;
+}
+
+size_t replica_stride16(const PassPlan& pl) { return (pl.total16 + 15) & ~(size_t)15; }
+
+template <bool F16, int PHB>
+cudaError_t launch_tc(const lsr_decoder* d, const float* in, int64_t n, float* out, const float* phrases, int n_pos,
+                      int n_neg, float* relev, cudaStream_t s) {
+  using C = TcCfg<F16>;
+  TcArgs a{};
+  a.n_layers = d->n_layers;
+  for (int l = 0; l <= d->n_layers; l++) a.dims[l] = d->dims[l];
+  for (int l = 0; l < d->n_layers; l++) a.bias[l] = d->bias[l];
+  a.packed = F16 ? d->packed_f16 : d->packed_tf32;
+  const PassPlan pl = plan_passes(d, F16);
+  a.replicas = (uint32_t)tc_replicas();
+  {
+    const char* e = getenv("LSR_DEC_EXP");
+    a.exp_no_loads = e && atoi(e) == 2;
+  }
+  a.replica_stride16 = (uint32_t)replica_stride16(pl);
+  a.n_passes = pl.n;
+  int ns = 0;
+  for (int p = 0; p < pl.n; p++) {
+    a.pass_layer[p] = pl.layer[p]; a.pass_n0[p] = pl.n0[p]; a.pass_np[p] = pl.np[p];
+    const int Np = pl.np[p], chunks = pl.kp[p] / C::E;
+    int per = (TC_STAGE_BYTES / (Np * 16)) & ~1;
+    if (per < 2) per = 2;
+    for (int c = 0; c < chunks; c += per) {
+      if (ns >= TC_MAX_SLICES) return cudaErrorInvalidValue;
+      TcSlice& q = a.sl[ns++];
+      q.off16 = (uint32_t)(pl.off16[p] + (size_t)c * Np);
+      q.nch = (uint16_t)(chunks - c < per ? chunks - c : per);
+      q.c0 = (uint8_t)c;
+      q.pass = (uint8_t)p;
+    }
+    a.pass_slice_end[p] = ns;
+  }
+  a.n_slices = ns;
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e =
+        cudaFuncSetAttribute(decode_tc_kernel<F16, PHB>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+    if (e != cudaSuccess) return e;
+    attr = true;
+  }
+  const int64_t tiles = (n + TC_M - 1) / TC_M, slots = (int64_t)sm_count() * C::CTAS_PER_SM;
+  const int grid = (int)(tiles < slots ? tiles : slots);
+  decode_tc_kernel<F16, PHB><<<grid, TC_M, C::SMEM, s>>>(a, in, n, out, phrases, n_pos, n_neg, relev, g_dec_trace);
+  count_launch();
+  return cudaGetLastError();
 }
 
 }  // namespace
 
-size_t decoder_packed_bytes(const lsr_decoder* d) { return packed_floats(d, nullptr) * 4; }
+void decoder_set_trace(void* dev_buf) { g_dec_trace = reinterpret_cast<long long*>(dev_buf); }
 
-void launch_decoder_pack(const lsr_decoder* d, float* packed, cudaStream_t s) {
-  size_t off[DEC_MAXL];
-  packed_floats(d, off);
-  for (int l = 0; l < d->n_layers; l++) {
-    const int K = d->dims[l], N = d->dims[l + 1], Kp = (K + 7) & ~7;
-    const int items = (Kp / 4) * N;
-    pack_weights_kernel<<<(items + 255) / 256, 256, 0, s>>>(d->weight[l], K, N, Kp,
-                                                            reinterpret_cast<float4*>(packed + off[l]));
-    count_launch();
-  }
+size_t decoder_packed_bytes(const lsr_decoder* d, int precision) {
+  return replica_stride16(plan_passes(d, precision == LSR_DECODE_F16)) * 16 * tc_replicas();
 }
 
-// Why the tensor-core variant cannot take this decoder (null if it can).
-const char* decoder_tc_unsupported(const lsr_decoder* d) {
-  if (!d->packed) return "lsr_decoder.packed is null (call lsr_decoder_pack first)";
-  if ((uintptr_t)d->packed & 15) return "lsr_decoder.packed must be 16-byte aligned";
+void launch_decoder_pack(const lsr_decoder* d, int precision, void* packed, cudaStream_t s) {
+  const bool f16 = precision == LSR_DECODE_F16;
+  const PassPlan pl = plan_passes(d, f16);
+  for (int r = 0; r < tc_replicas(); r++)
+    for (int p = 0; p < pl.n; p++) {
+      const int l = pl.layer[p], K = d->dims[l];
+      const int items = (pl.kp[p] / (f16 ? 8 : 4)) * pl.np[p];
+      pack_weights_kernel<<<(items + 255) / 256, 256, 0, s>>>(
+          d->weight[l] + (size_t)pl.n0[p] * K, K, pl.np[p], pl.kp[p], f16 ? 1 : 0,
+          reinterpret_cast<uint4*>(packed) + r * replica_stride16(pl) + pl.off16[p]);
+      count_launch();
+    }
+}
+
+// Why a tensor-core variant cannot take this decoder (null if it can).
+const char* decoder_tc_unsupported(const lsr_decoder* d, int precision) {
+  const void* packed = precision == LSR_DECODE_F16 ? d->packed_f16 : d->packed_tf32;
+  if (!packed) return "the packed weights of this precision are null (call lsr_decoder_pack first)";
+  if ((uintptr_t)packed & 15) return "packed weights must be 16-byte aligned";
   for (int l = 0; l < d->n_layers; l++) {
     const int K = d->dims[l], N = d->dims[l + 1];
     if (K > TC_MAXK) return "a layer input wider than 256";
     if (N % 16 || (N > 256 && N % 32)) return "layer widths must be multiples of 16 (of 32 above 256)";
-    if (2 * N * 16 > TC_STAGE_BYTES) return "layer wider than 512";
+    if ((uintptr_t)d->bias[l] & 15) return "bias pointers must be 16-byte aligned";
   }
   return nullptr;
 }
 
 cudaError_t launch_decode(const lsr_decoder* d, const float* in, int64_t n, int precision, float* out,
                           const float* phrases, int n_pos, int n_neg, float* relev, cudaStream_t s) {
-  if (precision == LSR_DECODE_FP32) {
-    DecArgs a{};
-    a.n_layers = d->n_layers;
-    for (int l = 0; l <= d->n_layers; l++) a.dims[l] = d->dims[l];
-    for (int l = 0; l < d->n_layers; l++) { a.weight[l] = d->weight[l]; a.bias[l] = d->bias[l]; }
-    const int smem = 2 * F_TP * F_LD * 4;
-    static bool attr = false;
-    if (!attr) {
-      cudaError_t e = cudaFuncSetAttribute(decode_fp32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-      if (e != cudaSuccess) return e;
-      attr = true;
-    }
-    const int64_t tiles = (n + F_TP - 1) / F_TP;
-    const int grid = (int)(tiles < (int64_t)sm_count() * 4 ? tiles : (int64_t)sm_count() * 4);
-    decode_fp32_kernel<<<grid, F_THREADS, smem, s>>>(a, in, n, out, phrases, n_pos, n_neg, relev);
-    count_launch();
-    return cudaGetLastError();
-  }
-  TcArgs a{};
+  if (precision == LSR_DECODE_TF32)
+    return (phrases && n_pos + n_neg > 8) ? launch_tc<false, 16>(d, in, n, out, phrases, n_pos, n_neg, relev, s)
+                                          : launch_tc<false, 8>(d, in, n, out, phrases, n_pos, n_neg, relev, s);
+  if (precision == LSR_DECODE_F16) return launch_tc<true, 8>(d, in, n, out, phrases, n_pos, n_neg, relev, s);
+  DecArgs a{};
   a.n_layers = d->n_layers;
   for (int l = 0; l <= d->n_layers; l++) a.dims[l] = d->dims[l];
-  for (int l = 0; l < d->n_layers; l++) a.bias[l] = d->bias[l];
-  a.packed = d->packed;
-  const char* v = getenv("LSR_TC_VARIANT");
-  a.variant = v ? atoi(v) : 0;
-  size_t off[DEC_MAXL];
-  packed_floats(d, off);
-  int ns = 0;
-  for (int l = 0; l < d->n_layers; l++) {
-    const int Kp = (d->dims[l] + 7) & ~7, N = d->dims[l + 1], chunks = Kp / 4;
-    int per = (TC_STAGE_BYTES / (N * 16)) & ~1;
-    if (per < 2) per = 2;
-    for (int c = 0; c < chunks; c += per) {
-      if (ns >= TC_MAX_SLICES) return cudaErrorInvalidValue;
-      TcSlice& q = a.sl[ns++];
-      q.off16 = (uint32_t)((off[l] * 4 + (size_t)c * N * 16) / 16);
-      q.nch = (uint16_t)(chunks - c < per ? chunks - c : per);
-      q.c0 = (uint8_t)c;
-      q.layer = (uint8_t)l;
-    }
-    a.slice_end[l] = ns;
-  }
-  a.n_slices = ns;
+  for (int l = 0; l < d->n_layers; l++) { a.weight[l] = d->weight[l]; a.bias[l] = d->bias[l]; }
+  const int smem = 2 * F_TP * F_LD * 4;
   static bool attr = false;
   if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(decode_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(decode_fp32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     attr = true;
   }
-  const int64_t tiles = (n + TC_M - 1) / TC_M;
-  const int grid = (int)(tiles < (int64_t)sm_count() ? tiles : (int64_t)sm_count());
-  decode_tc_kernel<<<grid, TC_M, TC_SMEM, s>>>(a, in, n, out, phrases, n_pos, n_neg, relev);
+  const int64_t tiles = (n + F_TP - 1) / F_TP;
+  const int grid = (int)(tiles < (int64_t)sm_count() * 4 ? tiles : (int64_t)sm_count() * 4);
+  decode_fp32_kernel<<<grid, F_THREADS, smem, s>>>(a, in, n, out, phrases, n_pos, n_neg, relev);
   count_launch();
   return cudaGetLastError();
 }

@@ -4,8 +4,9 @@ on vectors produced by the reference's own Autoencoder.decode and OpenCLIPNetwor
 is held to the same vectors and to the oracle at ragged sizes.
 Tolerances (outputs are unit 512-vectors, components ~0.04, and probabilities):
   fp32 variant: 1e-5 on features, 2e-5 on relevancy (summation order only);
-  tf32 variant (tcgen05, TF32 operands, fp32 accumulate): 5e-4 on features, 1e-3 on relevancy — TF32 operand rounding
-  emulated on the CPU for the golden case gives 1.1e-4 / 2.4e-4 with truncation, 3.5e-5 / 6e-5 with rounding."""
+  tf32 variant (tcgen05, TF32 operands, fp32 accumulate): 5e-4 on features, 1e-3 on relevancy — TF32 operand truncation
+  emulated on the CPU for the golden case gives 1.1e-4 / 2.4e-4, and the B200 reproduces exactly that;
+  f16 variant (operands rounded to nearest fp16, same 10 mantissa bits): same bars (emulation: 3.5e-5 / 6e-5)."""
 import os
 
 import numpy as np
@@ -19,7 +20,7 @@ NL = int(GOLD["n_layers"])
 WS = [GOLD[f"w{i}"] for i in range(NL)]
 BS = [GOLD[f"b{i}"] for i in range(NL)]
 N_POS = int(GOLD["n_pos"])
-TOL = {"fp32": (1e-5, 2e-5), "tf32": (5e-4, 1e-3)}
+TOL = {"fp32": (1e-5, 2e-5), "tf32": (5e-4, 1e-3), "f16": (5e-4, 1e-3)}
 
 
 def test_oracle_matches_reference_vectors():
@@ -46,7 +47,7 @@ def _decoder(precision):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+@pytest.mark.parametrize("precision", ["fp32", "tf32", "f16"])
 def test_gpu_matches_reference_vectors(precision):
     from langsplat_b200 import _lib
     dec, dev = _decoder(precision)
@@ -64,7 +65,7 @@ def test_gpu_matches_reference_vectors(precision):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+@pytest.mark.parametrize("precision", ["fp32", "tf32", "f16"])
 @pytest.mark.parametrize("n", [1, 31, 127, 128, 129, 1000, 148 * 128 * 2 + 77])
 def test_gpu_matches_oracle_ragged(precision, n):
     dec, dev = _decoder(precision)
@@ -115,13 +116,16 @@ def test_gpu_full_size_properties():
     assert y.shape == (3, 270, 360, 512)
     assert float((y.norm(dim=-1) - 1).abs().max()) < 1e-5
     y32 = dec.decode(sem, precision="fp32")
-    assert float((y - y32).abs().max()) < TOL["tf32"][0]
-    rel = dec.get_max_across(sem)
-    assert rel.shape == (3, N_POS, 270, 360)
     rel32 = dec.get_max_across(sem, precision="fp32")
-    assert float((rel - rel32).abs().max()) < TOL["tf32"][1]
-    assert float(rel.min()) >= 0.0 and float(rel.max()) <= 1.0
     big = torch.randn(1080 * 1440, 3, generator=g).to(dev)
-    r1 = dec.relevancy_maps(big)
-    r2 = dec.relevancy_maps(big[: 1080 * 720])
-    assert torch.equal(r1[:, : 1080 * 720], r2)  # pixels are independent: a prefix gives the same values
+    for prec in ("tf32", "f16"):
+        y = dec.decode(sem, precision=prec)
+        assert float((y.norm(dim=-1) - 1).abs().max()) < 1e-5
+        assert float((y - y32).abs().max()) < TOL[prec][0]
+        rel = dec.get_max_across(sem, precision=prec)
+        assert rel.shape == (3, N_POS, 270, 360)
+        assert float((rel - rel32).abs().max()) < TOL[prec][1]
+        assert float(rel.min()) >= 0.0 and float(rel.max()) <= 1.0
+        r1 = dec.relevancy_maps(big, precision=prec)
+        r2 = dec.relevancy_maps(big[: 1080 * 720], precision=prec)
+        assert torch.equal(r1[:, : 1080 * 720], r2)  # pixels are independent: a prefix gives the same values
