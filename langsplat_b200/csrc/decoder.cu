@@ -23,7 +23,6 @@
 #include <cuda_fp16.h>
 
 #include <cmath>
-#include <cstdlib>
 
 #include "common.cuh"
 
@@ -160,7 +159,9 @@ decode_fp32_kernel(const DecArgs a, const float* __restrict__ in, int64_t n, flo
 // 2E and zero padded: the canonical no-swizzle K-major UMMA layout (8-row x 16-byte core matrices, 128 B apart along
 // N, Np*16 B apart along K).
 constexpr int TC_M = 128;
-constexpr int TC_STAGE_BYTES = 16384;
+#ifndef TC_TF32_STAGE_BYTES
+#define TC_TF32_STAGE_BYTES 32768  // measured: 16 KB slices 3.30 ms, 32 KB slices 2.61 ms (per-slice latency amortised)
+#endif
 constexpr int TC_MAXK = 256;
 constexpr int TC_MAX_SLICES = 96;
 constexpr int TC_MAX_PASSES = DEC_MAXL + 1;
@@ -170,9 +171,10 @@ template <bool F16>
 struct TcCfg {
   static constexpr int E = F16 ? 8 : 4;                       // elements per 16-byte K chunk
   static constexpr int A_BYTES = TC_M * TC_MAXK * (F16 ? 2 : 4);
-  static constexpr int STAGES = F16 ? 2 : 4;                  // f16: 112 KB per CTA -> two CTAs per SM
+  static constexpr int STAGE_BYTES = F16 ? 16384 : TC_TF32_STAGE_BYTES;
+  static constexpr int STAGES = F16 ? 2 : 65536 / STAGE_BYTES;  // f16: 112 KB per CTA -> two CTAs per SM
   static constexpr int PH_BYTES = F16 ? 16384 : 32768;        // phrase embeddings (fp32) for the last epilogue
-  static constexpr int BAR_OFF = A_BYTES + STAGES * TC_STAGE_BYTES + PH_BYTES;
+  static constexpr int BAR_OFF = A_BYTES + STAGES * STAGE_BYTES + PH_BYTES;
   static constexpr int SMEM = BAR_OFF + 128;
   static constexpr int CTAS_PER_SM = F16 ? 2 : 1;
 };
@@ -211,8 +213,6 @@ struct TcArgs {
   int dims[DEC_MAXL + 1];
   const float* bias[DEC_MAXL];
   const void* packed;
-  uint32_t replica_stride16, replicas;
-  int exp_no_loads;  // experiment (LSR_DEC_EXP=2): arrive on the full barriers without copying (pure MMA + control timing)  // the blob is stored `replicas` times; CTA b reads copy b % replicas
   int n_passes;
   int pass_layer[TC_MAX_PASSES], pass_n0[TC_MAX_PASSES], pass_np[TC_MAX_PASSES];
   int pass_slice_end[TC_MAX_PASSES];  // one past the last slice of each pass
@@ -307,14 +307,13 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
   extern __shared__ __align__(1024) uint8_t tsm[];
   uint4* A = reinterpret_cast<uint4*>(tsm);  // [K/E][128 rows] 16-byte chunks
   uint8_t* stages = tsm + C::A_BYTES;
-  float* ph = reinterpret_cast<float*>(stages + C::STAGES * TC_STAGE_BYTES);
+  float* ph = reinterpret_cast<float*>(stages + C::STAGES * C::STAGE_BYTES);
   uint64_t* bars = reinterpret_cast<uint64_t*>(tsm + C::BAR_OFF);  // full[STAGES], empty[STAGES], done
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * C::STAGES + 1);
   const int tid = threadIdx.x, warp = tid >> 5;
   const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + C::STAGES), done = smem_u32(bars + 2 * C::STAGES);
   const uint32_t a_base = smem_u32(A), st_base = smem_u32(stages);
-  const uint8_t* packed = reinterpret_cast<const uint8_t*>(a.packed) +
-                          (size_t)(blockIdx.x % a.replicas) * a.replica_stride16 * 16;
+  const uint8_t* packed = reinterpret_cast<const uint8_t*>(a.packed);
   const int NL = a.dims[a.n_layers];
   const int n_ph = phrases ? n_pos + n_neg : 0;
 
@@ -388,12 +387,8 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
           const uint32_t st = it_load % C::STAGES, use = it_load / C::STAGES;
           mbar_wait(empty0 + 8 * st, (use & 1) ^ 1);
           const uint32_t bytes = (uint32_t)q.nch * (uint32_t)a.pass_np[q.pass] * 16u;
-          if (a.exp_no_loads) {
-            mbar_expect_tx(full0 + 8 * st, 0);
-          } else {
-            mbar_expect_tx(full0 + 8 * st, bytes);
-            bulk_g2s(st_base + st * TC_STAGE_BYTES, packed + (size_t)q.off16 * 16, bytes, full0 + 8 * st);
-          }
+          mbar_expect_tx(full0 + 8 * st, bytes);
+          bulk_g2s(st_base + st * C::STAGE_BYTES, packed + (size_t)q.off16 * 16, bytes, full0 + 8 * st);
           it_load++;
           next_load++;
         }
@@ -407,7 +402,7 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
           const TcSlice q = a.sl[s];
           const uint32_t st = it_mma % C::STAGES, use = it_mma / C::STAGES;
           uint64_t ad = smem_desc(a_base + (uint32_t)q.c0 * a_lbo, a_lbo, sbo);
-          uint64_t bd = smem_desc(st_base + st * TC_STAGE_BYTES, b_lbo, sbo);
+          uint64_t bd = smem_desc(st_base + st * C::STAGE_BYTES, b_lbo, sbo);
           uint32_t acc = q.c0 > 0 ? 1u : 0u;
           const int steps = q.nch >> 1;
           mbar_wait(full0 + 8 * st, use & 1);
@@ -531,20 +526,6 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TC_TMEM_COLS) : "memory");
 }
 
-// Copies of the packed weights in global memory (all CTAs stream the same bytes at about the same time; copies spread
-// the requests over more L2 lines).  LSR_DEC_REPLICAS overrides for experiments.
-int tc_replicas() {
-  static int r = 0;
-  if (!r) {
-    const char* e = getenv("LSR_DEC_REPLICAS");
-    r = e ? atoi(e) : 1;
-    if (r < 1) r = 1;
-    if (r > 64) r = 64;
-  }
-  return r;
-}
-size_t replica_stride16(const struct PassPlan& pl);
-
 long long* g_dec_trace = nullptr;  // debug: device buffer of clock64 stamps (lsr_debug_decode_trace)
 
 int g_sm_count = 0;
@@ -582,8 +563,6 @@ PassPlan plan_passes(const lsr_decoder* d, bool f16) {
   return pl;
 }
 
-size_t replica_stride16(const PassPlan& pl) { return (pl.total16 + 15) & ~(size_t)15; }
-
 template <bool F16, int PHB>
 cudaError_t launch_tc(const lsr_decoder* d, const float* in, int64_t n, float* out, const float* phrases, int n_pos,
                       int n_neg, float* relev, cudaStream_t s) {
@@ -594,18 +573,12 @@ cudaError_t launch_tc(const lsr_decoder* d, const float* in, int64_t n, float* o
   for (int l = 0; l < d->n_layers; l++) a.bias[l] = d->bias[l];
   a.packed = F16 ? d->packed_f16 : d->packed_tf32;
   const PassPlan pl = plan_passes(d, F16);
-  a.replicas = (uint32_t)tc_replicas();
-  {
-    const char* e = getenv("LSR_DEC_EXP");
-    a.exp_no_loads = e && atoi(e) == 2;
-  }
-  a.replica_stride16 = (uint32_t)replica_stride16(pl);
   a.n_passes = pl.n;
   int ns = 0;
   for (int p = 0; p < pl.n; p++) {
     a.pass_layer[p] = pl.layer[p]; a.pass_n0[p] = pl.n0[p]; a.pass_np[p] = pl.np[p];
     const int Np = pl.np[p], chunks = pl.kp[p] / C::E;
-    int per = (TC_STAGE_BYTES / (Np * 16)) & ~1;
+    int per = (C::STAGE_BYTES / (Np * 16)) & ~1;
     if (per < 2) per = 2;
     for (int c = 0; c < chunks; c += per) {
       if (ns >= TC_MAX_SLICES) return cudaErrorInvalidValue;
@@ -637,21 +610,19 @@ cudaError_t launch_tc(const lsr_decoder* d, const float* in, int64_t n, float* o
 void decoder_set_trace(void* dev_buf) { g_dec_trace = reinterpret_cast<long long*>(dev_buf); }
 
 size_t decoder_packed_bytes(const lsr_decoder* d, int precision) {
-  return replica_stride16(plan_passes(d, precision == LSR_DECODE_F16)) * 16 * tc_replicas();
+  return plan_passes(d, precision == LSR_DECODE_F16).total16 * 16;
 }
 
 void launch_decoder_pack(const lsr_decoder* d, int precision, void* packed, cudaStream_t s) {
   const bool f16 = precision == LSR_DECODE_F16;
   const PassPlan pl = plan_passes(d, f16);
-  for (int r = 0; r < tc_replicas(); r++)
-    for (int p = 0; p < pl.n; p++) {
-      const int l = pl.layer[p], K = d->dims[l];
-      const int items = (pl.kp[p] / (f16 ? 8 : 4)) * pl.np[p];
-      pack_weights_kernel<<<(items + 255) / 256, 256, 0, s>>>(
-          d->weight[l] + (size_t)pl.n0[p] * K, K, pl.np[p], pl.kp[p], f16 ? 1 : 0,
-          reinterpret_cast<uint4*>(packed) + r * replica_stride16(pl) + pl.off16[p]);
-      count_launch();
-    }
+  for (int p = 0; p < pl.n; p++) {
+    const int l = pl.layer[p], K = d->dims[l];
+    const int items = (pl.kp[p] / (f16 ? 8 : 4)) * pl.np[p];
+    pack_weights_kernel<<<(items + 255) / 256, 256, 0, s>>>(d->weight[l] + (size_t)pl.n0[p] * K, K, pl.np[p], pl.kp[p],
+                                                            f16 ? 1 : 0, reinterpret_cast<uint4*>(packed) + pl.off16[p]);
+    count_launch();
+  }
 }
 
 // Why a tensor-core variant cannot take this decoder (null if it can).

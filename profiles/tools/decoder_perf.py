@@ -31,7 +31,7 @@ for prec in (sys.argv[1:] or ["tf32", "f16"]):
             fn()
         e1.record()
         torch.cuda.synchronize()
-        print(f"replicas={os.environ.get('LSR_DEC_REPLICAS', 'default')} {prec} {what}: {e0.elapsed_time(e1) / 10:.3f} ms", flush=True)
+        print(f"{prec} {what}: {e0.elapsed_time(e1) / 10:.3f} ms", flush=True)
     print(prec, "max diff vs fp32 variant", float((dec.relevancy_maps(x, precision=prec) - ref).abs().max()), flush=True)
 
 # per-phase clock stamps of CTA 0's second tile (cycles)
