@@ -803,8 +803,8 @@ def decode_ops(dev):
                 "roofline_tf32": {"kernel": "decode_tc_kernel<tf32>", "bound": "tensor", "achieved": tf_tc,
                                   "peak": 0.5 * bf16_peak, "unit": "TFLOP/s", "frac": tf_tc / (0.5 * bf16_peak),
                                   "peak_source": "0.5 x measured dense bf16 (TF32 rate)"},
-                "note": "algorithmic flops = 2 x 240176 MACs per pixel (the seven Linear layers); the phrase dot "
-                        "products (7 x 512 per pixel) run on the FP32 pipe and are not counted"}
+                "note": "algorithmic flops = 2 x 240176 MACs per pixel (the seven Linear layers); the phrase "
+                        "similarities (one more N=16 pass against P W7) are not counted"}
     except Exception as e:  # noqa: BLE001 — a side measurement must not cost the headline line
         return {"error": repr(e)}
 

@@ -276,7 +276,9 @@ int lsr_adam_step(int32_t n_tensors, const lsr_adam_tensor* tensors, int64_t ste
  * LSR_DECODE_TF32 / LSR_DECODE_F16 = tcgen05 tensor cores with fp32 accumulation in TMEM, operands as TF32 (fp32
  * truncated to 10 mantissa bits) or fp16 (rounded to nearest, clamped to +-65504); both need their packed blob,
  * layer widths that are multiples of 16 and at most 512 (256 for all but the last), inputs at most 256 wide;
- * otherwise LSR_ERR_INVALID. */
+ * otherwise LSR_ERR_INVALID.  work: device scratch of lsr_decode_work_bytes() bytes, 16-byte aligned, private to the
+ * call until it has finished on `stream` (the tensor-core variants fold the phrases into the last layer there:
+ * sim_j = h . (P W)_j + P_j . b, one more N = 16 MMA pass); may be null without relevancy or with LSR_DECODE_FP32. */
 #define LSR_DECODER_MAX_LAYERS 8
 #define LSR_DECODER_MAX_PHRASES 16
 #define LSR_DECODE_FP32 0
@@ -292,8 +294,9 @@ typedef struct lsr_decoder {
 } lsr_decoder;
 size_t lsr_decoder_packed_bytes(const lsr_decoder* dec, int32_t precision);
 int lsr_decoder_pack(const lsr_decoder* dec, int32_t precision, void* packed, void* stream);
+size_t lsr_decode_work_bytes(void);
 int lsr_decode(const lsr_decoder* dec, const float* in, int64_t n, int32_t precision, float* out, const float* phrases,
-               int32_t n_pos, int32_t n_neg, float* relevancy, void* stream);
+               int32_t n_pos, int32_t n_neg, float* relevancy, void* work, size_t work_bytes, void* stream);
 /* Profiling aid: later tensor-core lsr_decode launches make CTA 0 write clock64() stamps of its second tile into
  * device_buffer (>= 64 int64: tile start, then per pass "MMAs issued", "accumulator complete", "epilogue done");
  * null switches it off. */

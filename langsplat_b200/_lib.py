@@ -95,8 +95,9 @@ EXPORTS = {
     "lsr_adam_step": (c_int, [c_int32, c_void_p, c_int64, c_double, c_double, c_double, c_void_p, c_void_p]),
     "lsr_decoder_packed_bytes": (c_size_t, [POINTER(Decoder), c_int32]),
     "lsr_decoder_pack": (c_int, [POINTER(Decoder), c_int32, c_void_p, c_void_p]),
+    "lsr_decode_work_bytes": (c_size_t, []),
     "lsr_decode": (c_int, [POINTER(Decoder), c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_int32, c_int32, c_void_p,
-                           c_void_p]),
+                           c_void_p, c_size_t, c_void_p]),
     "lsr_debug_decode_trace": (c_int, [c_void_p]),
     "lsr_mark_visible": (c_int, [c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "lsr_l1_loss_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_int32, c_int64, c_void_p, c_void_p]),

@@ -372,8 +372,10 @@ int lsr_decoder_pack(const lsr_decoder* dec, int32_t precision, void* packed, vo
   return LSR_OK;
 }
 
+size_t lsr_decode_work_bytes(void) { return 32768; }
+
 int lsr_decode(const lsr_decoder* dec, const float* in, int64_t n, int32_t precision, float* out, const float* phrases,
-               int32_t n_pos, int32_t n_neg, float* relevancy, void* stream) {
+               int32_t n_pos, int32_t n_neg, float* relevancy, void* work, size_t work_bytes, void* stream) {
   if (int rc = decoder_check(dec)) return rc;
   if (n < 0) return fail(LSR_ERR_INVALID, "n < 0");
   if (precision != LSR_DECODE_FP32 && !decoder_tc_precision(precision)) return fail(LSR_ERR_INVALID, "unknown precision");
@@ -391,12 +393,10 @@ int lsr_decode(const lsr_decoder* dec, const float* in, int64_t n, int32_t preci
   if (decoder_tc_precision(precision)) {
     if (const char* why = decoder_tc_unsupported(dec, precision)) return fail(LSR_ERR_INVALID, "tensor-core decode: %s", why);
     if (out && ((uintptr_t)out & 15)) return fail(LSR_ERR_INVALID, "out must be 16-byte aligned");
-    const int64_t ph_floats = (int64_t)(n_pos + n_neg) * dec->dims[dec->n_layers];
-    if (relevancy && ph_floats > (precision == LSR_DECODE_F16 ? 4096 : 8192))
-      return fail(LSR_ERR_INVALID, "tensor-core decode: phrase table too large for shared memory (%s)",
-                  precision == LSR_DECODE_F16 ? "f16: 8 phrases of 512" : "tf32: 16 phrases of 512");
+    if (relevancy && (!work || ((uintptr_t)work & 15) || work_bytes < lsr_decode_work_bytes()))
+      return fail(LSR_ERR_INVALID, "tensor-core relevancy needs a 16-byte aligned work buffer of lsr_decode_work_bytes()");
   }
-  LSR_CUDA(launch_decode(dec, in, n, precision, out, phrases, n_pos, n_neg, relevancy, (cudaStream_t)stream));
+  LSR_CUDA(launch_decode(dec, in, n, precision, out, phrases, n_pos, n_neg, relevancy, work, (cudaStream_t)stream));
   return LSR_OK;
 }
 

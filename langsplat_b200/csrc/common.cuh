@@ -233,7 +233,7 @@ size_t decoder_packed_bytes(const lsr_decoder* d, int precision);
 void launch_decoder_pack(const lsr_decoder* d, int precision, void* packed, cudaStream_t s);
 const char* decoder_tc_unsupported(const lsr_decoder* d, int precision);
 cudaError_t launch_decode(const lsr_decoder* d, const float* in, int64_t n, int precision, float* out,
-                          const float* phrases, int n_pos, int n_neg, float* relev, cudaStream_t s);
+                          const float* phrases, int n_pos, int n_neg, float* relev, void* work, cudaStream_t s);
 void launch_adam(int n, const lsr_adam_tensor* ts, int64_t step, double beta1, double beta2, double eps,
                  const uint8_t* visible, cudaStream_t s);
 void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, uint8_t* present, cudaStream_t s);

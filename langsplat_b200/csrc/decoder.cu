@@ -13,9 +13,9 @@
 //     [K chunks of 16 B][128 rows]) stays in shared memory, the B operand (weights, pre-packed once by lsr_decoder_pack
 //     into the same layout) streams from L2 through a ring of 16 KB slices filled by cp.async.bulk (TMA 1-D) on
 //     mbarriers, the accumulator lives in TMEM (256 columns; a 512-wide last layer is two passes).  Epilogue per layer:
-//     tcgen05.ld, + bias, ReLU, back into the A buffer; last layer: norm, phrase dot products and the softmax pair on
-//     the CUDA cores straight out of TMEM.  TF32: fp32 activations (128 KB), one CTA per SM, operands truncated to 10
-//     mantissa bits by the tensor core.  F16: activations and weights rounded to nearest fp16 (same 10 mantissa bits,
+//     tcgen05.ld, + bias, ReLU, back into the A buffer; last layer: norm straight out of TMEM; the phrase similarities
+//     are one more N = 16 pass against P W (fold_phrases_kernel), then the softmax pair on the CUDA cores.  TF32: fp32 activations (128 KB), one CTA per SM, operands rounded to the
+//     nearest TF32 value (the tensor core then truncates exactly).  F16: activations and weights rounded to nearest fp16 (same 10 mantissa bits,
 //     values clamped to +-65504), 64 KB of activations, two CTAs per SM so one CTA's epilogue overlaps the other's
 //     MMAs, half the weight bytes per tile and twice the MMA rate.  fp32 accumulation, bias, norm and relevancy in both.
 //   * decode_fp32_kernel (LSR_DECODE_FP32): the same fusion on the FP32 pipe (32 pixels per CTA, activations ping-pong
@@ -164,7 +164,7 @@ constexpr int TC_M = 128;
 #endif
 constexpr int TC_MAXK = 256;
 constexpr int TC_MAX_SLICES = 96;
-constexpr int TC_MAX_PASSES = DEC_MAXL + 1;
+constexpr int TC_MAX_PASSES = DEC_MAXL + 2;
 constexpr int TC_TMEM_COLS = 256;
 
 template <bool F16>
@@ -172,12 +172,14 @@ struct TcCfg {
   static constexpr int E = F16 ? 8 : 4;                       // elements per 16-byte K chunk
   static constexpr int A_BYTES = TC_M * TC_MAXK * (F16 ? 2 : 4);
   static constexpr int STAGE_BYTES = F16 ? 16384 : TC_TF32_STAGE_BYTES;
-  static constexpr int STAGES = F16 ? 2 : 65536 / STAGE_BYTES;  // f16: 112 KB per CTA -> two CTAs per SM
-  static constexpr int PH_BYTES = F16 ? 16384 : 32768;        // phrase embeddings (fp32) for the last epilogue
-  static constexpr int BAR_OFF = A_BYTES + STAGES * STAGE_BYTES + PH_BYTES;
+  static constexpr int STAGES = 3;                            // f16: 64 + 48 = 112 KB per CTA -> two CTAs per SM
+  static constexpr int BAR_OFF = A_BYTES + STAGES * STAGE_BYTES;
   static constexpr int SMEM = BAR_OFF + 128;
   static constexpr int CTAS_PER_SM = F16 ? 2 : 1;
 };
+
+// fp32 -> nearest TF32 (10 mantissa bits), so the tensor core's truncation of the operands is exact
+__device__ __forceinline__ uint32_t tf32_rn(float x) { return (__float_as_uint(x) + 0x1000u) & 0xFFFFE000u; }
 
 __global__ void pack_weights_kernel(const float* __restrict__ W, int K, int Np, int Kp, int f16, uint4* __restrict__ dst) {
   const int E = f16 ? 8 : 4;
@@ -197,9 +199,51 @@ __global__ void pack_weights_kernel(const float* __restrict__ W, int K, int Np, 
     r = make_uint4(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1),
                    *reinterpret_cast<uint32_t*>(&h2), *reinterpret_cast<uint32_t*>(&h3));
   } else {
-    r = make_uint4(__float_as_uint(v[0]), __float_as_uint(v[1]), __float_as_uint(v[2]), __float_as_uint(v[3]));
+    r = make_uint4(tf32_rn(v[0]), tf32_rn(v[1]), tf32_rn(v[2]), tf32_rn(v[3]));
   }
   dst[i] = r;
+}
+
+// Phrase similarities folded into the last layer: sim_j = x . p_j = h . (P W)_j + P_j . b for the last Linear (W, b)
+// and its input h, so the similarities of a tile are one more N = 16 MMA pass against PW = P W  [16, K] instead of
+// n_ph x NL FMAs per pixel on the FP32 pipe.  Writes PW in the packed operand layout [Kp/E][16][E] (rows past n_ph are
+// zeros) and pb[16] = P b.
+__global__ void fold_phrases_kernel(const float* __restrict__ P, int n_ph, const float* __restrict__ W,
+                                    const float* __restrict__ b, int NL, int K, int Kp, int f16,
+                                    uint4* __restrict__ dst, float* __restrict__ pb) {
+  const int E = f16 ? 8 : 4;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int items = (Kp / E) * 16;
+  if (i < items) {
+    const int kc = i >> 4, j = i & 15;
+    float acc[8] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};
+    if (j < n_ph) {
+      const float* pj = P + (size_t)j * NL;
+      for (int o = 0; o < NL; o++) {
+        const float pv = __ldg(pj + o);
+        const float* w = W + (size_t)o * K + kc * E;
+#pragma unroll
+        for (int e = 0; e < 8; e++)
+          if (e < E && kc * E + e < K) acc[e] = fmaf(pv, __ldg(w + e), acc[e]);
+      }
+    }
+    uint4 r;
+    if (f16) {
+      __half2 h0 = __floats2half2_rn(acc[0], acc[1]), h1 = __floats2half2_rn(acc[2], acc[3]);
+      __half2 h2 = __floats2half2_rn(acc[4], acc[5]), h3 = __floats2half2_rn(acc[6], acc[7]);
+      r = make_uint4(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1),
+                     *reinterpret_cast<uint32_t*>(&h2), *reinterpret_cast<uint32_t*>(&h3));
+    } else {
+      r = make_uint4(tf32_rn(acc[0]), tf32_rn(acc[1]), tf32_rn(acc[2]), tf32_rn(acc[3]));
+    }
+    dst[i] = r;
+  } else if (i < items + 16) {
+    const int j = i - items;
+    float acc = 0.0f;
+    if (j < n_ph)
+      for (int o = 0; o < NL; o++) acc = fmaf(__ldg(P + (size_t)j * NL + o), __ldg(b + o), acc);
+    pb[j] = acc;
+  }
 }
 
 struct TcSlice {
@@ -213,6 +257,8 @@ struct TcArgs {
   int dims[DEC_MAXL + 1];
   const float* bias[DEC_MAXL];
   const void* packed;
+  const void* fold;    // PW operand of the similarity pass (pass_layer == n_layers), null without phrases
+  const float* fold_b; // P b  [16]
   int n_passes;
   int pass_layer[TC_MAX_PASSES], pass_n0[TC_MAX_PASSES], pass_np[TC_MAX_PASSES];
   int pass_slice_end[TC_MAX_PASSES];  // one past the last slice of each pass
@@ -297,7 +343,7 @@ __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
   return *reinterpret_cast<uint32_t*>(&h);
 }
 
-template <bool F16, int PHB>  // PHB: rows of the (zero padded) phrase table in shared memory, 8 or 16
+template <bool F16>
 __global__ void __launch_bounds__(TC_M, TcCfg<F16>::CTAS_PER_SM)
 decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in, int64_t n, float* __restrict__ out,
                  const float* __restrict__ phrases, int n_pos, int n_neg, float* __restrict__ relev,
@@ -307,7 +353,6 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
   extern __shared__ __align__(1024) uint8_t tsm[];
   uint4* A = reinterpret_cast<uint4*>(tsm);  // [K/E][128 rows] 16-byte chunks
   uint8_t* stages = tsm + C::A_BYTES;
-  float* ph = reinterpret_cast<float*>(stages + C::STAGES * C::STAGE_BYTES);
   uint64_t* bars = reinterpret_cast<uint64_t*>(tsm + C::BAR_OFF);  // full[STAGES], empty[STAGES], done
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * C::STAGES + 1);
   const int tid = threadIdx.x, warp = tid >> 5;
@@ -328,7 +373,6 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  for (int i = tid; i < PHB * NL; i += TC_M) ph[i] = i < n_ph * NL ? __ldg(phrases + i) : 0.0f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -357,8 +401,7 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
           };
           A[kc * TC_M + tid] = make_uint4(cv(v[0], v[1]), cv(v[2], v[3]), cv(v[4 % E], v[5 % E]), cv(v[6 % E], v[7 % E]));
         } else {
-          A[kc * TC_M + tid] = make_uint4(__float_as_uint(v[0]), __float_as_uint(v[1]), __float_as_uint(v[2]),
-                                          __float_as_uint(v[3]));
+          A[kc * TC_M + tid] = make_uint4(tf32_rn(v[0]), tf32_rn(v[1]), tf32_rn(v[2]), tf32_rn(v[3]));
         }
       }
     }
@@ -371,9 +414,9 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
     int ti = 0;
     if (tr) trace[ti++] = clock64();
     int next_load = 0;  // thread 32: next slice of this tile to request
-    float ssp[4] = {0.0f, 0.0f, 0.0f, 0.0f}, sim[PHB];
+    float ssp[4] = {0.0f, 0.0f, 0.0f, 0.0f}, sim[16];
 #pragma unroll
-    for (int j = 0; j < PHB; j++) sim[j] = 0.0f;
+    for (int j = 0; j < 16; j++) sim[j] = 0.0f;
 
     for (int p = 0; p < a.n_passes; p++) {
       const int l = a.pass_layer[p], n0 = a.pass_n0[p], Np = a.pass_np[p];
@@ -388,7 +431,8 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
           mbar_wait(empty0 + 8 * st, (use & 1) ^ 1);
           const uint32_t bytes = (uint32_t)q.nch * (uint32_t)a.pass_np[q.pass] * 16u;
           mbar_expect_tx(full0 + 8 * st, bytes);
-          bulk_g2s(st_base + st * C::STAGE_BYTES, packed + (size_t)q.off16 * 16, bytes, full0 + 8 * st);
+          const uint8_t* src = a.pass_layer[q.pass] == a.n_layers ? reinterpret_cast<const uint8_t*>(a.fold) : packed;
+          bulk_g2s(st_base + st * C::STAGE_BYTES, src + (size_t)q.off16 * 16, bytes, full0 + 8 * st);
           it_load++;
           next_load++;
         }
@@ -427,6 +471,18 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
       tc_fence_after();
       if (tr) trace[ti++] = clock64();  // accumulator complete
 
+      if (l == a.n_layers) {
+        // similarity pass: 16 columns = h . (P W)_j; + P_j . b
+        float v[16];
+        tmem_ld16(t_lane, v);
+#pragma unroll
+        for (int j = 0; j < 16; j++) sim[j] = v[j] + __ldg(a.fold_b + j);
+        tc_fence_before();
+        __syncthreads();
+        tc_fence_after();
+        if (tr) trace[ti++] = clock64();
+        continue;
+      }
       const float* __restrict__ B = a.bias[l] + n0;
       if (l + 1 < a.n_layers) {
         for (int c = 0; c < Np; c += 16) {
@@ -449,8 +505,7 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
 #pragma unroll
             for (int q4 = 0; q4 < 4; q4++)
               A[((c >> 2) + q4) * TC_M + tid] =
-                  make_uint4(__float_as_uint(v[q4 * 4 + 0]), __float_as_uint(v[q4 * 4 + 1]),
-                             __float_as_uint(v[q4 * 4 + 2]), __float_as_uint(v[q4 * 4 + 3]));
+                  make_uint4(tf32_rn(v[q4 * 4 + 0]), tf32_rn(v[q4 * 4 + 1]), tf32_rn(v[q4 * 4 + 2]), tf32_rn(v[q4 * 4 + 3]));
           }
         }
         fence_async_smem();
@@ -467,19 +522,6 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
           }
 #pragma unroll
           for (int i = 0; i < 16; i++) ssp[i & 3] = fmaf(v[i], v[i], ssp[i & 3]);
-          if (n_ph) {
-#pragma unroll
-            for (int q4 = 0; q4 < 4; q4++) {
-#pragma unroll
-              for (int j = 0; j < PHB; j++) {  // rows past n_ph are zeros: no branches, PHB independent chains
-                const float4 w = *reinterpret_cast<const float4*>(ph + j * NL + n0 + c + q4 * 4);
-                sim[j] = fmaf(v[q4 * 4 + 0], w.x, sim[j]);
-                sim[j] = fmaf(v[q4 * 4 + 1], w.y, sim[j]);
-                sim[j] = fmaf(v[q4 * 4 + 2], w.z, sim[j]);
-                sim[j] = fmaf(v[q4 * 4 + 3], w.w, sim[j]);
-              }
-            }
-          }
           if (out && live) {
 #pragma unroll
             for (int q4 = 0; q4 < 4; q4++)
@@ -492,10 +534,10 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
           if (n_ph && live) {
             float max_neg = -INFINITY;
 #pragma unroll
-            for (int j = 0; j < PHB; j++)
+            for (int j = 0; j < 16; j++)
               if (j >= n_pos && j < n_ph) max_neg = fmaxf(max_neg, sim[j] / norm);
 #pragma unroll
-            for (int j = 0; j < PHB; j++)
+            for (int j = 0; j < 16; j++)
               if (j < n_pos) relev[(size_t)j * n + pix] = pair_softmax_pos(sim[j] / norm, max_neg);
           }
           if (out) {  // each warp scales its own 32 rows, a row per instruction (coalesced, L2-resident)
@@ -563,9 +605,9 @@ PassPlan plan_passes(const lsr_decoder* d, bool f16) {
   return pl;
 }
 
-template <bool F16, int PHB>
+template <bool F16>
 cudaError_t launch_tc(const lsr_decoder* d, const float* in, int64_t n, float* out, const float* phrases, int n_pos,
-                      int n_neg, float* relev, cudaStream_t s) {
+                      int n_neg, float* relev, void* work, cudaStream_t s) {
   using C = TcCfg<F16>;
   TcArgs a{};
   a.n_layers = d->n_layers;
@@ -573,34 +615,53 @@ cudaError_t launch_tc(const lsr_decoder* d, const float* in, int64_t n, float* o
   for (int l = 0; l < d->n_layers; l++) a.bias[l] = d->bias[l];
   a.packed = F16 ? d->packed_f16 : d->packed_tf32;
   const PassPlan pl = plan_passes(d, F16);
-  a.n_passes = pl.n;
-  int ns = 0;
-  for (int p = 0; p < pl.n; p++) {
-    a.pass_layer[p] = pl.layer[p]; a.pass_n0[p] = pl.n0[p]; a.pass_np[p] = pl.np[p];
-    const int Np = pl.np[p], chunks = pl.kp[p] / C::E;
+  const int last = d->n_layers - 1, K7 = d->dims[last], K7p = (K7 + 2 * C::E - 1) & ~(2 * C::E - 1);
+  if (phrases) {  // PW and P b into the work buffer: [K7p/E][16] 16-byte chunks, then 16 floats
+    uint4* pw = reinterpret_cast<uint4*>(work);
+    float* pb = reinterpret_cast<float*>(pw + (size_t)(K7p / C::E) * 16);
+    const int items = (K7p / C::E) * 16 + 16;
+    fold_phrases_kernel<<<(items + 63) / 64, 64, 0, s>>>(phrases, n_pos + n_neg, d->weight[last], d->bias[last],
+                                                        d->dims[d->n_layers], K7, K7p, F16 ? 1 : 0, pw, pb);
+    count_launch();
+    a.fold = pw;
+    a.fold_b = pb;
+  }
+  int ns = 0, np = 0;
+  auto add_pass = [&](int layer, int n0, int Np, int Kp, size_t off16) -> bool {
+    a.pass_layer[np] = layer; a.pass_n0[np] = n0; a.pass_np[np] = Np;
+    const int chunks = Kp / C::E;
     int per = (C::STAGE_BYTES / (Np * 16)) & ~1;
     if (per < 2) per = 2;
     for (int c = 0; c < chunks; c += per) {
-      if (ns >= TC_MAX_SLICES) return cudaErrorInvalidValue;
+      if (ns >= TC_MAX_SLICES) return false;
       TcSlice& q = a.sl[ns++];
-      q.off16 = (uint32_t)(pl.off16[p] + (size_t)c * Np);
+      q.off16 = (uint32_t)(off16 + (size_t)c * Np);
       q.nch = (uint16_t)(chunks - c < per ? chunks - c : per);
       q.c0 = (uint8_t)c;
-      q.pass = (uint8_t)p;
+      q.pass = (uint8_t)np;
     }
-    a.pass_slice_end[p] = ns;
+    a.pass_slice_end[np++] = ns;
+    return true;
+  };
+  bool sim_done = !phrases;
+  for (int p = 0; p < pl.n; p++) {
+    if (!sim_done && pl.layer[p] == last) {  // the similarity pass reads the last layer's input: right before it
+      if (!add_pass(d->n_layers, 0, 16, K7p, 0)) return cudaErrorInvalidValue;
+      sim_done = true;
+    }
+    if (!add_pass(pl.layer[p], pl.n0[p], pl.np[p], pl.kp[p], pl.off16[p])) return cudaErrorInvalidValue;
   }
+  a.n_passes = np;
   a.n_slices = ns;
   static bool attr = false;
   if (!attr) {
-    cudaError_t e =
-        cudaFuncSetAttribute(decode_tc_kernel<F16, PHB>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+    cudaError_t e = cudaFuncSetAttribute(decode_tc_kernel<F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
     if (e != cudaSuccess) return e;
     attr = true;
   }
   const int64_t tiles = (n + TC_M - 1) / TC_M, slots = (int64_t)sm_count() * C::CTAS_PER_SM;
   const int grid = (int)(tiles < slots ? tiles : slots);
-  decode_tc_kernel<F16, PHB><<<grid, TC_M, C::SMEM, s>>>(a, in, n, out, phrases, n_pos, n_neg, relev, g_dec_trace);
+  decode_tc_kernel<F16><<<grid, TC_M, C::SMEM, s>>>(a, in, n, out, phrases, n_pos, n_neg, relev, g_dec_trace);
   count_launch();
   return cudaGetLastError();
 }
@@ -640,11 +701,9 @@ const char* decoder_tc_unsupported(const lsr_decoder* d, int precision) {
 }
 
 cudaError_t launch_decode(const lsr_decoder* d, const float* in, int64_t n, int precision, float* out,
-                          const float* phrases, int n_pos, int n_neg, float* relev, cudaStream_t s) {
-  if (precision == LSR_DECODE_TF32)
-    return (phrases && n_pos + n_neg > 8) ? launch_tc<false, 16>(d, in, n, out, phrases, n_pos, n_neg, relev, s)
-                                          : launch_tc<false, 8>(d, in, n, out, phrases, n_pos, n_neg, relev, s);
-  if (precision == LSR_DECODE_F16) return launch_tc<true, 8>(d, in, n, out, phrases, n_pos, n_neg, relev, s);
+                          const float* phrases, int n_pos, int n_neg, float* relev, void* work, cudaStream_t s) {
+  if (precision == LSR_DECODE_TF32) return launch_tc<false>(d, in, n, out, phrases, n_pos, n_neg, relev, work, s);
+  if (precision == LSR_DECODE_F16) return launch_tc<true>(d, in, n, out, phrases, n_pos, n_neg, relev, work, s);
   DecArgs a{};
   a.n_layers = d->n_layers;
   for (int l = 0; l <= d->n_layers; l++) a.dims[l] = d->dims[l];

@@ -114,8 +114,11 @@ class FeatureDecoder:
         with torch.cuda.device(self.device):
             if prec != L.DECODE_FP32:
                 self._ensure_packed(lib, prec)
+            work = None
+            if want_relevancy and prec != L.DECODE_FP32:  # per call: safe with several streams in flight
+                work = torch.empty(lib.lsr_decode_work_bytes() // 4, dtype=torch.float32, device=self.device)
             rc = lib.lsr_decode(ctypes.byref(self._desc), _ptr(x2), n, prec, _ptr(out), _ptr(self._phrases), n_pos,
-                                n_neg, _ptr(rel), self._stream())
+                                n_neg, _ptr(rel), _ptr(work), 0 if work is None else work.numel() * 4, self._stream())
         if rc != L.LSR_OK:
             raise LsrError(L.last_error())
         return out, rel
