@@ -382,7 +382,10 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
   uint32_t it_load = 0, it_mma = 0;  // thread 32 / thread 0: slices requested / multiplied so far (ring position, phase)
   uint32_t done_phase = 0;
   const int64_t ntiles = (n + TC_M - 1) / TC_M;
-  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+  const uint32_t total_loads = (uint32_t)((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x) * (uint32_t)a.n_slices;
+  int next_load = 0;         // thread 32: table index of the next slice to request (wraps at the end of a tile)
+  uint32_t tile_iter = 0;
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, tile_iter++) {
     const int64_t pix = tile * TC_M + tid;
     const bool live = pix < n;
     {  // input row -> A, K padded to 2E with zeros
@@ -413,7 +416,6 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
     const bool tr = trace && blockIdx.x == 0 && tid == 0 && tile == (int64_t)gridDim.x;  // CTA 0's second tile
     int ti = 0;
     if (tr) trace[ti++] = clock64();
-    int next_load = 0;  // thread 32: next slice of this tile to request
     float ssp[4] = {0.0f, 0.0f, 0.0f, 0.0f}, sim[16];
 #pragma unroll
     for (int j = 0; j < 16; j++) sim[j] = 0.0f;
@@ -424,8 +426,8 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
       if (tid == 32) {
         // producer: weight slices of this pass, and up to STAGES - 1 slices of the next ones while this pass's epilogue
         // runs (a stage is reused once the MMAs that read it have completed: empty barrier)
-        const int target = min(a.n_slices, s_end + C::STAGES - 1);
-        while (next_load < target) {
+        const uint32_t target = min(total_loads, tile_iter * (uint32_t)a.n_slices + (uint32_t)(s_end + C::STAGES - 1));
+        while (it_load < target) {  // runs into the next tile's first slices at the end of this one
           const TcSlice q = a.sl[next_load];
           const uint32_t st = it_load % C::STAGES, use = it_load / C::STAGES;
           mbar_wait(empty0 + 8 * st, (use & 1) ^ 1);
@@ -434,7 +436,7 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
           const uint8_t* src = a.pass_layer[q.pass] == a.n_layers ? reinterpret_cast<const uint8_t*>(a.fold) : packed;
           bulk_g2s(st_base + st * C::STAGE_BYTES, src + (size_t)q.off16 * 16, bytes, full0 + 8 * st);
           it_load++;
-          next_load++;
+          if (++next_load == a.n_slices) next_load = 0;
         }
       } else if (tid == 0) {
         // MMA issuer
@@ -534,11 +536,13 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
           if (n_ph && live) {
             float max_neg = -INFINITY;
 #pragma unroll
-            for (int j = 0; j < 16; j++)
-              if (j >= n_pos && j < n_ph) max_neg = fmaxf(max_neg, sim[j] / norm);
+            const float inv = 1.0f / norm;
 #pragma unroll
             for (int j = 0; j < 16; j++)
-              if (j < n_pos) relev[(size_t)j * n + pix] = pair_softmax_pos(sim[j] / norm, max_neg);
+              if (j >= n_pos && j < n_ph) max_neg = fmaxf(max_neg, sim[j] * inv);
+#pragma unroll
+            for (int j = 0; j < 16; j++)
+              if (j < n_pos) relev[(size_t)j * n + pix] = pair_softmax_pos(sim[j] * inv, max_neg);
           }
           if (out) {  // each warp scales its own 32 rows, a row per instruction (coalesced, L2-resident)
             __syncwarp();

@@ -81,6 +81,30 @@ def test_gpu_matches_oracle_ragged(precision, n):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("precision", ["fp32", "tf32", "f16"])
+@pytest.mark.parametrize("n_pos,n_neg", [(1, 1), (12, 4), (2, 14)])
+def test_gpu_phrase_counts(precision, n_pos, n_neg):
+    """Fewest and most phrases the C ABI takes (LSR_DECODER_MAX_PHRASES = 16), against the oracle."""
+    dec, dev = _decoder(precision)
+    rng = np.random.default_rng(7 + n_pos)
+    ph = rng.normal(size=(n_pos + n_neg, 512)).astype(np.float32)
+    ph /= np.linalg.norm(ph, axis=-1, keepdims=True)
+    x = rng.normal(size=(333, 3)).astype(np.float32)
+    y0 = orc.decode_features(x, WS, BS)
+    ph[0] = (0.5 * ph[0] + y0[:40].mean(0) * 10).astype(np.float32)
+    ph[0] /= np.linalg.norm(ph[0])
+    r0 = orc.relevancy(y0, ph, n_pos)[..., 0]
+    pt = torch.from_numpy(ph).to(dev)
+    dec.set_phrases(pt[:n_pos], pt[n_pos:])
+    got = dec.relevancy_maps(torch.from_numpy(x).to(dev)).cpu().numpy()
+    assert got.shape == (n_pos, 333)
+    assert np.abs(got - r0).max() < TOL[precision][1]
+    from langsplat_b200 import LsrError
+    with pytest.raises(LsrError):
+        dec.set_phrases(pt[:1].repeat(13, 1), pt[:1].repeat(4, 1))  # 17 phrases
+
+
+@pytest.mark.gpu
 def test_gpu_empty_and_errors():
     from langsplat_b200.decode import FeatureDecoder
     from langsplat_b200 import LsrError
