@@ -547,15 +547,26 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
           if (out) {  // each warp scales its own 32 rows, a row per instruction (coalesced, L2-resident)
             __syncwarp();
             const int lane = tid & 31;
-            for (int r = 0; r < 32; r++) {
-              const float nr = __shfl_sync(0xffffffffu, norm, r);
-              const int64_t prow = tile * TC_M + warp * 32 + r;
-              if (prow >= n) break;
-              float4* row = reinterpret_cast<float4*>(out + prow * NL);
-              for (int c = lane; c < NL / 4; c += 32) {
-                float4 v = row[c];
-                v.x /= nr; v.y /= nr; v.z /= nr; v.w /= nr;
-                row[c] = v;
+            const int per_row = NL >> 2;             // float4 per row
+            const int total = 32 * per_row;          // this warp's 32 rows are contiguous in `out`
+            float4* base = reinterpret_cast<float4*>(out + (tile * TC_M + warp * 32) * NL);
+            const int64_t rows_left = n - (tile * TC_M + warp * 32);
+            const int limit = rows_left >= 32 ? total : (rows_left > 0 ? (int)rows_left * per_row : 0);
+            for (int i0 = 0; i0 < limit; i0 += 32 * 8) {  // eight independent 512-byte accesses in flight per lane
+              float4 v[8];
+#pragma unroll
+              for (int u = 0; u < 8; u++) {
+                const int i = i0 + u * 32 + lane;
+                if (i < limit) v[u] = base[i];
+              }
+#pragma unroll
+              for (int u = 0; u < 8; u++) {
+                const int i = i0 + u * 32 + lane;
+                const float nr = __shfl_sync(0xffffffffu, norm, (i < limit ? i : 0) / per_row);
+                if (i < limit) {
+                  v[u].x /= nr; v[u].y /= nr; v[u].z /= nr; v[u].w /= nr;
+                  base[i] = v[u];
+                }
               }
             }
           }
