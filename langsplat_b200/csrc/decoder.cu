@@ -164,7 +164,8 @@ constexpr int TC_M = 128;
 #endif
 constexpr int TC_MAXK = 256;
 constexpr int TC_MAX_SLICES = 96;
-constexpr int TC_MAX_PASSES = DEC_MAXL + 2;
+constexpr int TC_MAX_PASSES = DEC_MAXL + 4;
+enum { PASS_HIDDEN = 0, PASS_SIM = 1, PASS_NORM = 2, PASS_STORE = 3 };
 constexpr int TC_TMEM_COLS = 256;
 
 template <bool F16>
@@ -261,6 +262,8 @@ struct TcArgs {
   const float* fold_b; // P b  [16]
   int n_passes;
   int pass_layer[TC_MAX_PASSES], pass_n0[TC_MAX_PASSES], pass_np[TC_MAX_PASSES];
+  int pass_mode[TC_MAX_PASSES];  // PASS_HIDDEN / PASS_SIM / PASS_NORM (last layer: sum of squares) / PASS_STORE
+  int last_norm_pass;            // the norm (and the relevancy) is final after this pass
   int pass_slice_end[TC_MAX_PASSES];  // one past the last slice of each pass
   int n_slices;
   TcSlice sl[TC_MAX_SLICES];
@@ -416,7 +419,7 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
     const bool tr = trace && blockIdx.x == 0 && tid == 0 && tile == (int64_t)gridDim.x;  // CTA 0's second tile
     int ti = 0;
     if (tr) trace[ti++] = clock64();
-    float ssp[4] = {0.0f, 0.0f, 0.0f, 0.0f}, sim[16];
+    float ssp[4] = {0.0f, 0.0f, 0.0f, 0.0f}, sim[16], norm = 1.0f;
 #pragma unroll
     for (int j = 0; j < 16; j++) sim[j] = 0.0f;
 
@@ -473,7 +476,8 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
       tc_fence_after();
       if (tr) trace[ti++] = clock64();  // accumulator complete
 
-      if (l == a.n_layers) {
+      const int mode = a.pass_mode[p];
+      if (mode == PASS_SIM) {
         // similarity pass: 16 columns = h . (P W)_j; + P_j . b
         float v[16];
         tmem_ld16(t_lane, v);
@@ -486,7 +490,7 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
         continue;
       }
       const float* __restrict__ B = a.bias[l] + n0;
-      if (l + 1 < a.n_layers) {
+      if (mode == PASS_HIDDEN) {
         for (int c = 0; c < Np; c += 16) {
           float v[16];
           tmem_ld16(t_lane + c, v);
@@ -511,9 +515,8 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
           }
         }
         fence_async_smem();
-      } else {
-        // last layer: norm and phrase dot products accumulate over its passes; the unnormalised values are parked in
-        // `out` and scaled by this same thread once the norm is known
+      } else if (mode == PASS_NORM) {
+        // last layer, first time round: only the sum of squares (nothing can be written before the norm is known)
         for (int c = 0; c < Np; c += 16) {
           float v[16];
           tmem_ld16(t_lane + c, v);
@@ -524,18 +527,11 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
           }
 #pragma unroll
           for (int i = 0; i < 16; i++) ssp[i & 3] = fmaf(v[i], v[i], ssp[i & 3]);
-          if (out && live) {
-#pragma unroll
-            for (int q4 = 0; q4 < 4; q4++)
-              *reinterpret_cast<float4*>(out + pix * NL + n0 + c + q4 * 4) =
-                  make_float4(v[q4 * 4 + 0], v[q4 * 4 + 1], v[q4 * 4 + 2], v[q4 * 4 + 3]);
-          }
         }
-        if (p + 1 == a.n_passes) {
-          const float norm = sqrtf((ssp[0] + ssp[1]) + (ssp[2] + ssp[3]));
+        if (p == a.last_norm_pass) {
+          norm = sqrtf((ssp[0] + ssp[1]) + (ssp[2] + ssp[3]));
           if (n_ph && live) {
             float max_neg = -INFINITY;
-#pragma unroll
             const float inv = 1.0f / norm;
 #pragma unroll
             for (int j = 0; j < 16; j++)
@@ -544,30 +540,20 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
             for (int j = 0; j < 16; j++)
               if (j < n_pos) relev[(size_t)j * n + pix] = pair_softmax_pos(sim[j] * inv, max_neg);
           }
-          if (out) {  // each warp scales its own 32 rows, a row per instruction (coalesced, L2-resident)
-            __syncwarp();
-            const int lane = tid & 31;
-            const int per_row = NL >> 2;             // float4 per row
-            const int total = 32 * per_row;          // this warp's 32 rows are contiguous in `out`
-            float4* base = reinterpret_cast<float4*>(out + (tile * TC_M + warp * 32) * NL);
-            const int64_t rows_left = n - (tile * TC_M + warp * 32);
-            const int limit = rows_left >= 32 ? total : (rows_left > 0 ? (int)rows_left * per_row : 0);
-            for (int i0 = 0; i0 < limit; i0 += 32 * 8) {  // eight independent 512-byte accesses in flight per lane
-              float4 v[8];
+        }
+      } else {
+        // PASS_STORE: the last layer's MMAs once more (cheaper than parking 2 KB per pixel in L2 and rescaling it:
+        // measured 22.9 GB of L2 traffic for 3.2 GB of output that way), normalised rows straight to `out`
+        for (int c = 0; c < Np; c += 16) {
+          float v[16];
+          tmem_ld16(t_lane + c, v);
+          if (live) {
 #pragma unroll
-              for (int u = 0; u < 8; u++) {
-                const int i = i0 + u * 32 + lane;
-                if (i < limit) v[u] = base[i];
-              }
-#pragma unroll
-              for (int u = 0; u < 8; u++) {
-                const int i = i0 + u * 32 + lane;
-                const float nr = __shfl_sync(0xffffffffu, norm, (i < limit ? i : 0) / per_row);
-                if (i < limit) {
-                  v[u].x /= nr; v[u].y /= nr; v[u].z /= nr; v[u].w /= nr;
-                  base[i] = v[u];
-                }
-              }
+            for (int q4 = 0; q4 < 4; q4++) {
+              const float4 b4 = __ldg(reinterpret_cast<const float4*>(B + c) + q4);
+              *reinterpret_cast<float4*>(out + pix * NL + n0 + c + q4 * 4) =
+                  make_float4((v[q4 * 4 + 0] + b4.x) / norm, (v[q4 * 4 + 1] + b4.y) / norm,
+                              (v[q4 * 4 + 2] + b4.z) / norm, (v[q4 * 4 + 3] + b4.w) / norm);
             }
           }
         }
@@ -642,8 +628,9 @@ cudaError_t launch_tc(const lsr_decoder* d, const float* in, int64_t n, float* o
     a.fold_b = pb;
   }
   int ns = 0, np = 0;
-  auto add_pass = [&](int layer, int n0, int Np, int Kp, size_t off16) -> bool {
-    a.pass_layer[np] = layer; a.pass_n0[np] = n0; a.pass_np[np] = Np;
+  auto add_pass = [&](int layer, int n0, int Np, int Kp, size_t off16, int mode) -> bool {
+    if (np >= TC_MAX_PASSES) return false;
+    a.pass_layer[np] = layer; a.pass_n0[np] = n0; a.pass_np[np] = Np; a.pass_mode[np] = mode;
     const int chunks = Kp / C::E;
     int per = (C::STAGE_BYTES / (Np * 16)) & ~1;
     if (per < 2) per = 2;
@@ -661,11 +648,17 @@ cudaError_t launch_tc(const lsr_decoder* d, const float* in, int64_t n, float* o
   bool sim_done = !phrases;
   for (int p = 0; p < pl.n; p++) {
     if (!sim_done && pl.layer[p] == last) {  // the similarity pass reads the last layer's input: right before it
-      if (!add_pass(d->n_layers, 0, 16, K7p, 0)) return cudaErrorInvalidValue;
+      if (!add_pass(d->n_layers, 0, 16, K7p, 0, PASS_SIM)) return cudaErrorInvalidValue;
       sim_done = true;
     }
-    if (!add_pass(pl.layer[p], pl.n0[p], pl.np[p], pl.kp[p], pl.off16[p])) return cudaErrorInvalidValue;
+    if (!add_pass(pl.layer[p], pl.n0[p], pl.np[p], pl.kp[p], pl.off16[p], pl.layer[p] == last ? PASS_NORM : PASS_HIDDEN))
+      return cudaErrorInvalidValue;
   }
+  a.last_norm_pass = np - 1;
+  if (out)
+    for (int p = 0; p < pl.n; p++)
+      if (pl.layer[p] == last && !add_pass(last, pl.n0[p], pl.np[p], pl.kp[p], pl.off16[p], PASS_STORE))
+        return cudaErrorInvalidValue;
   a.n_passes = np;
   a.n_slices = ns;
   static bool attr = false;
