@@ -273,8 +273,8 @@ int lsr_adam_step(int32_t n_tensors, const lsr_adam_tensor* tensors, int64_t ste
  * phrases [n_pos + n_neg, dims[L]]: unit phrase embeddings, positives first (pos_embeds then neg_embeds);
  * n_pos + n_neg <= LSR_DECODER_MAX_PHRASES, n_neg >= 1 when relevancy is requested.
  * precision: LSR_DECODE_FP32 = IEEE fp32 on the FP32 pipe (the reference's arithmetic up to summation order);
- * LSR_DECODE_TF32 / LSR_DECODE_F16 = tcgen05 tensor cores with fp32 accumulation in TMEM, operands as TF32 (fp32
- * truncated to 10 mantissa bits) or fp16 (rounded to nearest, clamped to +-65504); both need their packed blob,
+ * LSR_DECODE_TF32 / LSR_DECODE_F16 = tcgen05 tensor cores with fp32 accumulation in TMEM, operands rounded to the
+ * nearest TF32 (10 mantissa bits) or fp16 (10 mantissa bits, clamped to +-65504) value; both need their packed blob,
  * layer widths that are multiples of 16 and at most 512 (256 for all but the last), inputs at most 256 wide;
  * otherwise LSR_ERR_INVALID.  work: device scratch of lsr_decode_work_bytes() bytes, 16-byte aligned, private to the
  * call until it has finished on `stream` (the tensor-core variants fold the phrases into the last layer there:
