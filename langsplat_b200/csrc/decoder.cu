@@ -341,6 +341,12 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
 #pragma unroll
   for (int i = 0; i < 16; i++) v[i] = __uint_as_float(r[i]);
 }
+// One lane of a converged warp (the same one every time: tcgen05.commit tracks the MMAs of the thread that issued them)
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
   __half2 h = __floats2half2_rn(fminf(a, 65504.0f), fminf(b, 65504.0f));
   return *reinterpret_cast<uint32_t*>(&h);
@@ -359,6 +365,10 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
   uint64_t* bars = reinterpret_cast<uint64_t*>(tsm + C::BAR_OFF);  // full[STAGES], empty[STAGES], done
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * C::STAGES + 1);
   const int tid = threadIdx.x, warp = tid >> 5;
+  // warp index as a value the compiler knows to be warp-uniform: the producer and the issuer run as whole warps with
+  // uniform descriptors (in uniform registers) and elect one lane per instruction; under `if (tid == 0)` every
+  // tcgen05.mma was wrapped in an ELECT / R2UR.BROADCAST waterfall (~140 cycles per instruction, measured)
+  const int warp_u = __shfl_sync(0xffffffffu, warp, 0);
   const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + C::STAGES), done = smem_u32(bars + 2 * C::STAGES);
   const uint32_t a_base = smem_u32(A), st_base = smem_u32(stages);
   const uint8_t* packed = reinterpret_cast<const uint8_t*>(a.packed);
@@ -382,11 +392,11 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
   const uint32_t tmem = *tmem_slot;
   const uint32_t t_lane = tmem + ((uint32_t)(warp * 32) << 16);  // this warp's quarter of the 128 lanes
 
-  uint32_t it_load = 0, it_mma = 0;  // thread 32 / thread 0: slices requested / multiplied so far (ring position, phase)
+  uint32_t it_load = 0, it_mma = 0;  // warp 1 / warp 0: slices requested / multiplied so far (ring position, phase)
   uint32_t done_phase = 0;
   const int64_t ntiles = (n + TC_M - 1) / TC_M;
   const uint32_t total_loads = (uint32_t)((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x) * (uint32_t)a.n_slices;
-  int next_load = 0;         // thread 32: table index of the next slice to request (wraps at the end of a tile)
+  int next_load = 0;         // warp 1: table index of the next slice to request (wraps at the end of a tile)
   uint32_t tile_iter = 0;
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, tile_iter++) {
     const int64_t pix = tile * TC_M + tid;
@@ -426,23 +436,26 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
     for (int p = 0; p < a.n_passes; p++) {
       const int l = a.pass_layer[p], n0 = a.pass_n0[p], Np = a.pass_np[p];
       const int s_begin = p ? a.pass_slice_end[p - 1] : 0, s_end = a.pass_slice_end[p];
-      if (tid == 32) {
-        // producer: weight slices of this pass, and up to STAGES - 1 slices of the next ones while this pass's epilogue
-        // runs (a stage is reused once the MMAs that read it have completed: empty barrier)
+      if (warp_u == 1) {
+        // producer warp: weight slices of this pass, and up to STAGES - 1 slices of the next ones while this pass's
+        // epilogue runs (a stage is reused once the MMAs that read it have completed: empty barrier)
         const uint32_t target = min(total_loads, tile_iter * (uint32_t)a.n_slices + (uint32_t)(s_end + C::STAGES - 1));
         while (it_load < target) {  // runs into the next tile's first slices at the end of this one
           const TcSlice q = a.sl[next_load];
           const uint32_t st = it_load % C::STAGES, use = it_load / C::STAGES;
           mbar_wait(empty0 + 8 * st, (use & 1) ^ 1);
           const uint32_t bytes = (uint32_t)q.nch * (uint32_t)a.pass_np[q.pass] * 16u;
-          mbar_expect_tx(full0 + 8 * st, bytes);
           const uint8_t* src = a.pass_layer[q.pass] == a.n_layers ? reinterpret_cast<const uint8_t*>(a.fold) : packed;
-          bulk_g2s(st_base + st * C::STAGE_BYTES, src + (size_t)q.off16 * 16, bytes, full0 + 8 * st);
+          if (elect_one()) {
+            mbar_expect_tx(full0 + 8 * st, bytes);
+            bulk_g2s(st_base + st * C::STAGE_BYTES, src + (size_t)q.off16 * 16, bytes, full0 + 8 * st);
+          }
+          __syncwarp();
           it_load++;
           if (++next_load == a.n_slices) next_load = 0;
         }
-      } else if (tid == 0) {
-        // MMA issuer
+      } else if (warp_u == 0) {
+        // MMA issuer warp
         const uint32_t fmt = F16 ? 0u : 2u;
         const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(Np >> 3) << 17) | ((TC_M >> 4) << 24);
         const uint32_t a_lbo = TC_M * 16, b_lbo = (uint32_t)Np * 16, sbo = 128;
@@ -456,17 +469,21 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
           const int steps = q.nch >> 1;
           mbar_wait(full0 + 8 * st, use & 1);
           tc_fence_after();
+          if (elect_one()) {
 #pragma unroll 4
-          for (int j = 0; j < steps; j++) {
-            tc_mma<F16>(tmem, ad, bd, idesc, acc);
-            acc = 1u;
-            ad += a_step;
-            bd += b_step;
+            for (int j = 0; j < steps; j++) {
+              tc_mma<F16>(tmem, ad, bd, idesc, acc);
+              acc = 1u;
+              ad += a_step;
+              bd += b_step;
+            }
+            tc_commit(empty0 + 8 * st);  // the slice's stage is free once these MMAs have read it
           }
-          tc_commit(empty0 + 8 * st);  // the slice's stage is free once these MMAs have read it
+          __syncwarp();
           it_mma++;
         }
-        tc_commit(done);  // accumulator of this pass complete
+        if (elect_one()) tc_commit(done);  // accumulator of this pass complete
+        __syncwarp();
       }
       if (tr) trace[ti++] = clock64();  // MMAs of the pass issued
       __syncwarp();
