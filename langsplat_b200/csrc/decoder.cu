@@ -9,7 +9,7 @@
 // Kernels behind lsr_decode:
 //   * decode_tc_kernel<F16> (LSR_DECODE_TF32 / LSR_DECODE_F16): 128 pixels per CTA = the 128 TMEM lanes.  Every layer
 //     is a tcgen05.mma chain (kind::tf32, K = 8 per instruction, or kind::f16, K = 16; M = 128, N = layer width) issued
-//     by one thread; the A operand (activations, in the canonical no-swizzle K-major core-matrix layout:
+//     by one elected lane of warp 0; the A operand (activations, in the canonical no-swizzle K-major core-matrix layout:
 //     [K chunks of 16 B][128 rows]) stays in shared memory, the B operand (weights, pre-packed once by lsr_decoder_pack
 //     into the same layout) streams from L2 through a ring of 16 KB slices filled by cp.async.bulk (TMA 1-D) on
 //     mbarriers, the accumulator lives in TMEM (256 columns; a 512-wide last layer is two passes).  Epilogue per layer:
