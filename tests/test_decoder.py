@@ -37,6 +37,36 @@ def test_oracle_decode_is_scale_free_after_first_relu_free_layer():
     assert np.abs(np.sqrt((y * y).sum(-1)) - 1).max() < 1e-12
 
 
+def test_host_validation_without_gpu():
+    """FeatureDecoder refuses CPU tensors (no CPU path) and malformed layer lists before touching the library."""
+    from langsplat_b200 import LsrError
+    from langsplat_b200.decode import FeatureDecoder
+    ws = [torch.from_numpy(w) for w in WS]
+    bs = [torch.from_numpy(b) for b in BS]
+    with pytest.raises(LsrError, match="CUDA tensors required"):
+        FeatureDecoder(ws, bs)
+    with pytest.raises(LsrError):
+        FeatureDecoder(ws, bs[:-1])
+    with pytest.raises(LsrError):
+        FeatureDecoder([], [])
+    with pytest.raises(ValueError):
+        FeatureDecoder(ws, bs, precision="bf16")
+    with pytest.raises(LsrError, match="no decoder"):
+        FeatureDecoder.from_state_dict({"encoder.0.weight": ws[0]}, device="cpu")
+
+
+def test_abi_decoder_struct_matches_header():
+    """ctypes mirror of lsr_decoder: field order / sizes as include/lsr_api.h declares them."""
+    import ctypes
+    from langsplat_b200 import _lib as L
+    assert [f[0] for f in L.Decoder._fields_] == ["n_layers", "dims", "weight", "bias", "packed_tf32", "packed_f16"]
+    assert ctypes.sizeof(L.Decoder) == 4 + 4 * 9 + 8 * 8 + 8 * 8 + 8 + 8
+    hdr = open(os.path.join(os.path.dirname(__file__), "..", "include", "lsr_api.h")).read()
+    for sym in ("lsr_decoder_packed_bytes", "lsr_decoder_pack", "lsr_decode_work_bytes", "lsr_decode",
+                "lsr_debug_decode_trace"):
+        assert sym + "(" in hdr and sym in L.EXPORTS
+
+
 def _decoder(precision):
     from langsplat_b200.decode import FeatureDecoder
     dev = torch.device("cuda:0")
