@@ -23,6 +23,7 @@
 #include <cuda_fp16.h>
 
 #include <cmath>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -167,6 +168,9 @@ constexpr int TC_MAX_SLICES = 96;
 constexpr int TC_MAX_PASSES = DEC_MAXL + 4;
 enum { PASS_HIDDEN = 0, PASS_SIM = 1, PASS_NORM = 2, PASS_STORE = 3 };
 constexpr int TC_TMEM_COLS = 256;
+#ifndef TC_F16_STAGGER
+#define TC_F16_STAGGER 12000  // measured (f16, 1440x1080): 0 -> 1.083 ms, 6000 -> 1.070, 12000 -> 1.003, 20000 -> 1.027
+#endif
 
 template <bool F16>
 struct TcCfg {
@@ -264,6 +268,7 @@ struct TcArgs {
   int pass_layer[TC_MAX_PASSES], pass_n0[TC_MAX_PASSES], pass_np[TC_MAX_PASSES];
   int pass_mode[TC_MAX_PASSES];  // PASS_HIDDEN / PASS_SIM / PASS_NORM (last layer: sum of squares) / PASS_STORE
   int last_norm_pass;            // the norm (and the relevancy) is final after this pass
+  int stagger;                   // cycles the second CTA of an SM waits before its first tile (see launch_tc)
   int pass_slice_end[TC_MAX_PASSES];  // one past the last slice of each pass
   int n_slices;
   TcSlice sl[TC_MAX_SLICES];
@@ -392,6 +397,10 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
   const uint32_t tmem = *tmem_slot;
   const uint32_t t_lane = tmem + ((uint32_t)(warp * 32) << 16);  // this warp's quarter of the 128 lanes
 
+  if (a.stagger > 0 && blockIdx.x >= (gridDim.x + 1) / 2) {
+    const long long t0 = clock64();
+    while (clock64() - t0 < a.stagger) {}
+  }
   uint32_t it_load = 0, it_mma = 0;  // warp 1 / warp 0: slices requested / multiplied so far (ring position, phase)
   uint32_t done_phase = 0;
   const int64_t ntiles = (n + TC_M - 1) / TC_M;
@@ -678,6 +687,18 @@ cudaError_t launch_tc(const lsr_decoder* d, const float* in, int64_t n, float* o
         return cudaErrorInvalidValue;
   a.n_passes = np;
   a.n_slices = ns;
+  // Two co-resident CTAs that start together stay in phase (both in their MMA phase, then both in their epilogue) and
+  // share the tensor pipe and the TMEM read port; a one-off delay of the second wave of CTAs puts one CTA's epilogues
+  // under the other's MMAs.  LSR_DEC_STAGGER (cycles) overrides for experiments.
+  if (C::CTAS_PER_SM > 1) {
+    static int stagger = -1;
+    if (stagger < 0) {
+      const char* e = getenv("LSR_DEC_STAGGER");
+      stagger = e ? atoi(e) : TC_F16_STAGGER;
+      if (stagger < 0) stagger = 0;
+    }
+    a.stagger = stagger;
+  }
   static bool attr = false;
   if (!attr) {
     cudaError_t e = cudaFuncSetAttribute(decode_tc_kernel<F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
