@@ -597,15 +597,12 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
 
 long long* g_dec_trace = nullptr;  // debug: device buffer of clock64 stamps (lsr_debug_decode_trace)
 
-int g_sm_count = 0;
-int sm_count() {
-  if (!g_sm_count) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
-    if (g_sm_count <= 0) g_sm_count = 148;
-  }
-  return g_sm_count;
+int sm_count() {  // of the current device
+  int dev = 0, n = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
+      n <= 0)
+    n = 148;
+  return n;
 }
 
 // passes of a decoder and the element offset of each in the packed blob (in 16-byte units)
@@ -699,11 +696,9 @@ cudaError_t launch_tc(const lsr_decoder* d, const float* in, int64_t n, float* o
     }
     a.stagger = stagger;
   }
-  static bool attr = false;
-  if (!attr) {
+  {  // per launch: the attribute is per device, and a process may use several
     cudaError_t e = cudaFuncSetAttribute(decode_tc_kernel<F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
     if (e != cudaSuccess) return e;
-    attr = true;
   }
   const int64_t tiles = (n + TC_M - 1) / TC_M, slots = (int64_t)sm_count() * C::CTAS_PER_SM;
   const int grid = (int)(tiles < slots ? tiles : slots);
@@ -755,11 +750,9 @@ cudaError_t launch_decode(const lsr_decoder* d, const float* in, int64_t n, int 
   for (int l = 0; l <= d->n_layers; l++) a.dims[l] = d->dims[l];
   for (int l = 0; l < d->n_layers; l++) { a.weight[l] = d->weight[l]; a.bias[l] = d->bias[l]; }
   const int smem = 2 * F_TP * F_LD * 4;
-  static bool attr = false;
-  if (!attr) {
+  {
     cudaError_t e = cudaFuncSetAttribute(decode_fp32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
-    attr = true;
   }
   const int64_t tiles = (n + F_TP - 1) / F_TP;
   const int grid = (int)(tiles < (int64_t)sm_count() * 4 ? tiles : (int64_t)sm_count() * 4);
