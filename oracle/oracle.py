@@ -290,15 +290,40 @@ def adam_step(param, grad, exp_avg, exp_avg_sq, step, lr, beta1=0.9, beta2=0.999
     return new, m, v
 
 
-def decode_features(x, weights, biases, dtype=np.float64):
+def _round_operand(a, operand):
+    """Operand rounding of the tensor-core variants of the CUDA decode kernel: None = none; "tf32" = fp32 rounded to the
+    nearest value with 10 mantissa bits (what csrc/decoder.cu's tf32_rn does before the tensor core truncates);
+    "tf32_trunc" = plain truncation (raw fp32 operands fed to kind::tf32); "f16" = round to nearest fp16, clamped."""
+    if operand is None:
+        return a
+    a32 = np.asarray(a, np.float32)
+    if operand == "f16":
+        return np.clip(a32, -65504.0, 65504.0).astype(np.float16).astype(np.float64)
+    u = a32.view(np.uint32)
+    if operand == "tf32":
+        u = (u + np.uint32(0x1000)) & np.uint32(0xFFFFE000)
+    elif operand == "tf32_trunc":
+        u = u & np.uint32(0xFFFFE000)
+    else:
+        raise ValueError(operand)
+    return u.view(np.float32).astype(np.float64)
+
+
+def decode_features(x, weights, biases, dtype=np.float64, operand=None):
     """Autoencoder.decode (autoencoder/model.py:42-46, decoder built at :18-25): Linear, then (ReLU, Linear) for every
     further layer, then x / x.norm(dim=-1, keepdim=True).  weights[l] is nn.Linear's [out, in] matrix.  float64 by
-    default (the checker); dtype=np.float32 for the timed CPU baseline."""
+    default (the checker); dtype=np.float32 for the timed CPU baseline.  `operand` models the operand rounding of the
+    CUDA kernel's tensor-core variants (activations and weights rounded before every product, fp32 accumulator stored
+    between layers), which is where their tolerance comes from."""
     h = _np(x, dtype)
     for l, (w, b) in enumerate(zip(weights, biases)):
         if l > 0:
             h = np.maximum(h, 0)
-        h = h @ _np(w, dtype).T + _np(b, dtype)
+        if operand is None:
+            h = h @ _np(w, dtype).T + _np(b, dtype)
+        else:
+            h = (_round_operand(h, operand) @ _round_operand(w, operand).T).astype(np.float32).astype(np.float64)
+            h = (h.astype(np.float32) + _np(b, np.float32)).astype(np.float64)
     return h / np.sqrt((h * h).sum(-1, keepdims=True))
 
 

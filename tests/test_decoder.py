@@ -37,6 +37,21 @@ def test_oracle_decode_is_scale_free_after_first_relu_free_layer():
     assert np.abs(np.sqrt((y * y).sum(-1)) - 1).max() < 1e-12
 
 
+def test_operand_rounding_explains_the_tensor_core_tolerance():
+    """Where the 5e-4 / 1e-3 bars come from: rounding activations and weights to 10 mantissa bits before every
+    product, emulated on the CPU, against the reference's vectors.  The B200 measured 1.09e-4 / 2.44e-4 with raw fp32
+    operands (tensor-core truncation) and 3.46e-5 / 5.8e-5 with fp16 operands — the figures this emulation gives."""
+    got = {}
+    for operand in ("tf32_trunc", "tf32", "f16"):
+        y = orc.decode_features(GOLD["x"], WS, BS, operand=operand)
+        r = orc.relevancy(y, GOLD["phrases"], N_POS)[..., 0]
+        got[operand] = (np.abs(y - GOLD["y"]).max(), np.abs(r - GOLD["relevancy"][..., 0]).max())
+        assert got[operand][0] < TOL["tf32"][0] / 2 and got[operand][1] < TOL["tf32"][1] / 2
+    assert 0.9e-4 < got["tf32_trunc"][0] < 1.3e-4 and 2.0e-4 < got["tf32_trunc"][1] < 2.9e-4
+    assert 3.0e-5 < got["f16"][0] < 4.0e-5
+    assert got["tf32"][0] < got["tf32_trunc"][0]  # rounding to nearest first is why the kernel does it
+
+
 def test_host_validation_without_gpu():
     """FeatureDecoder refuses CPU tensors (no CPU path) and malformed layer lists before touching the library."""
     from langsplat_b200 import LsrError
