@@ -174,7 +174,7 @@ int lsr_sh_gradient_from_view_ptrs(int32_t P, int32_t M, int32_t D, int32_t n_vi
  * The first LSR_PEER_HEADER_BYTES of every buffer belong to the library (barrier words); payload starts after them.
  * lsr_peer_barrier: stream-ordered barrier across `world` ranks; headers[r] = rank r's buffer as seen from this
  *   process (own pointer at headers[rank]).  `epoch` must grow by one per call on every rank.  Work enqueued after it
- *   sees everything the peers enqueued before theirs.  A peer that does not arrive within 4 s is reported by
+ *   sees everything the peers enqueued before theirs.  A peer that does not arrive within the time-out (lsr_peer_set_timeout_ms) is reported by
  *   lsr_peer_status (returns LSR_ERR_CUDA, "peer barrier timed out") instead of hanging the device.
  * lsr_peer_signal / lsr_peer_wait: the two halves of the barrier, for a rank that has local work to run between
  *   "my remote writes are done" and "everybody's are".
@@ -196,6 +196,12 @@ int lsr_peer_wait(int32_t rank, int32_t world, void* const* headers, uint32_t ep
 int lsr_peer_allreduce(int32_t rank, int32_t world, const float* const* in, float* const* out, int64_t n_floats,
                        void* stream);
 int lsr_peer_status(const void* own_buffer, void* stream);
+/* Time-out of the barrier's wait (default 120 000 ms; process-wide).  A rank that does not arrive in time raises a
+ * sticky flag in the waiting rank's header: lsr_peer_status then fails, and lsr_peer_poison_on_timeout — to be
+ * enqueued behind every kernel that consumed peer data — overwrites `data` with NaN so that an incomplete sum can
+ * never pass for a gradient (one word read per thread when no time-out happened). */
+int lsr_peer_set_timeout_ms(uint64_t ms);
+int lsr_peer_poison_on_timeout(const void* own_buffer, float* data, int64_t n_floats, void* stream);
 
 /* Replaces _C.mark_visible -> markVisible (rasterize_points.cu:226-245) -> checkFrustum (rasterizer_impl.cu:54-66). */
 int lsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,

@@ -88,6 +88,8 @@ EXPORTS = {
     "lsr_peer_wait": (c_int, [c_int32, c_int32, POINTER(c_void_p), c_uint32, c_void_p]),
     "lsr_peer_allreduce": (c_int, [c_int32, c_int32, POINTER(c_void_p), POINTER(c_void_p), c_int64, c_void_p]),
     "lsr_peer_status": (c_int, [c_void_p, c_void_p]),
+    "lsr_peer_set_timeout_ms": (c_int, [c_uint64]),
+    "lsr_peer_poison_on_timeout": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "lsr_activate_forward": (c_int, [c_int32] + [c_void_p] * 9),
     "lsr_activate_backward": (c_int, [c_int32] + [c_void_p] * 13),
     "lsr_language_feature_map": (c_int, [c_void_p, c_int32, c_int64, c_int32, c_int32, c_void_p, c_int32, c_int32,

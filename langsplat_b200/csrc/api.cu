@@ -260,13 +260,27 @@ int lsr_peer_allreduce(int32_t rank, int32_t world, const float* const* in, floa
   return LSR_OK;
 }
 
+int lsr_peer_set_timeout_ms(uint64_t ms) {
+  if (ms == 0) return fail(LSR_ERR_INVALID, "time-out must be at least 1 ms");
+  peer_set_timeout_ms(ms);
+  return LSR_OK;
+}
+
+int lsr_peer_poison_on_timeout(const void* own_buffer, float* data, int64_t n_floats, void* stream) {
+  if (!own_buffer || (n_floats > 0 && !data) || n_floats < 0) return fail(LSR_ERR_INVALID, "bad argument");
+  launch_peer_poison(own_buffer, data, n_floats, (cudaStream_t)stream);
+  LSR_CUDA(cudaGetLastError());
+  return LSR_OK;
+}
+
 int lsr_peer_status(const void* own_buffer, void* stream) {
   if (!own_buffer) return fail(LSR_ERR_INVALID, "null pointer");
   uint32_t flag = 0;
   LSR_CUDA(cudaMemcpyAsync(&flag, static_cast<const uint8_t*>(own_buffer) + LSR_MAX_PEERS * sizeof(uint32_t),
                            sizeof(flag), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
   LSR_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
-  if (flag) return fail(LSR_ERR_CUDA, "peer barrier timed out (a rank did not arrive within 4 s)");
+  if (flag) return fail(LSR_ERR_CUDA, "peer barrier timed out (a rank did not arrive within %llu ms)",
+                        (unsigned long long)peer_timeout_ms());
   return LSR_OK;
 }
 
@@ -456,6 +470,10 @@ static int check_frame(const lsr_frame* f, const lsr_inputs* in) {
                 (f->D + 1) * (f->D + 1), f->M);
   if (f->include_feature && !in->language_feature)
     return fail(LSR_ERR_INVALID, "include_feature is set but language_feature_precomp is missing");
+  // the kernels read quaternions as one 128-bit load per Gaussian: a contiguous view that starts at an odd element
+  // of its storage (x[1:]) would fault, so say so here instead (the Python layer re-packs such tensors)
+  if (in->rotations && (((uintptr_t)in->rotations) & 15))
+    return fail(LSR_ERR_INVALID, "rotations must be 16-byte aligned");
   return LSR_OK;
 }
 
@@ -604,6 +622,8 @@ int lsr_backward(const lsr_frame* frame, const lsr_inputs* in, const int32_t* ra
   if (geom_need && (!gr.dL_dconic || !gr.dL_dopacity)) return fail(LSR_ERR_INVALID, "dL_dconic / dL_dopacity required");
   if (dcol && !gr.dL_dcolors) return fail(LSR_ERR_INVALID, "dL_dcolors buffer required when dL_dcolor is given");
   if (feat && !gr.dL_dlanguage_feature) return fail(LSR_ERR_INVALID, "dL_dlanguage_feature buffer required");
+  if (((((uintptr_t)gr.dL_dconic) | ((uintptr_t)gr.dL_drotations)) & 15) != 0)
+    return fail(LSR_ERR_INVALID, "dL_dconic and dL_drotations must be 16-byte aligned (read / written as float4)");
   if (g_profile) g_have_b = false;
   prof(g_ev_b, 0, s);
   // zero what the blend kernel accumulates into; adjacent buffers are merged into one memset

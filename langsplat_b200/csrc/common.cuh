@@ -3,6 +3,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
+
 #include "../../include/lsr_api.h"
 
 namespace lsr {
@@ -48,6 +50,22 @@ struct ImageView {
 };
 
 __host__ __device__ inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
+
+// Function attributes (MaxDynamicSharedMemorySize) are per DEVICE: a process that drives several GPUs must set them
+// on each one.  run(f) calls f() the first time it is reached with a given current device (idempotent work only:
+// two threads racing here both run f, which is harmless).
+struct DeviceOnce {
+  std::atomic<uint64_t> seen{0};
+  template <class F>
+  void run(F&& f) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const uint64_t bit = 1ull << (dev & 63);
+    if (seen.load(std::memory_order_acquire) & bit) return;
+    f();
+    seen.fetch_or(bit, std::memory_order_release);
+  }
+};
 
 inline GeomView geom_view(void* base, int P) {
   char* p = (char*)base;
@@ -216,6 +234,10 @@ void launch_sh_grad_view_ptrs(int P, int D, int M, int V, const float* means3D, 
 // cross-GPU barrier on the stream (peer.cu): signals `epoch` into every peer's header, waits for all of them
 // mode: 1 = signal, 2 = wait, 3 = both
 void launch_peer_barrier(int rank, int world, void* const* headers, uint32_t epoch, int mode, cudaStream_t s);
+void peer_set_timeout_ms(uint64_t ms);
+uint64_t peer_timeout_ms();
+// data[0..n) = NaN if a barrier of the owner of `own_buffer` ever timed out (sticky flag in its header)
+void launch_peer_poison(const void* own_buffer, float* data, int64_t n, cudaStream_t s);
 // out[r][i] = sum over ranks of in[.][i] for this rank's chunk of the n_floats-long vectors, for every rank r
 void launch_peer_allreduce(int rank, int world, const float* const* in, float* const* out, int64_t n_floats,
                            cudaStream_t s);

@@ -23,11 +23,12 @@ __device__ __forceinline__ float diff_masked(float p, float g, float m) {
 template <bool MASK>
 __global__ void __launch_bounds__(LOSS_THREADS)
 l1_forward_kernel(const float* __restrict__ pred, const float* __restrict__ gt, const float* __restrict__ mask,
-                  int64_t N, int64_t total, float inv_count, float* __restrict__ loss) {
+                  int64_t N, int64_t total, float inv_count, bool vec_ok, float* __restrict__ loss) {
   __shared__ float s_part[LOSS_THREADS / 32];
   const int64_t nvec = total / 4;
   float acc = 0.f;
-  const bool vec_ok = (N % 4) == 0;  // a float4 never straddles two channels, so the mask index is (i % N)
+  // vec_ok (host): N % 4 == 0 — a float4 never straddles two channels, so the mask index is (i % N) — and every
+  // pointer is 16-byte aligned (a contiguous view may start at any element of its storage)
   if (vec_ok) {
     const float4* p4 = reinterpret_cast<const float4*>(pred);
     const float4* g4 = reinterpret_cast<const float4*>(gt);
@@ -64,7 +65,7 @@ l1_forward_kernel(const float* __restrict__ pred, const float* __restrict__ gt, 
 template <bool MASK>
 __global__ void __launch_bounds__(LOSS_THREADS)
 l1_backward_kernel(const float* __restrict__ pred, const float* __restrict__ gt, const float* __restrict__ mask,
-                   int64_t N, int64_t total, float inv_count, const float* __restrict__ grad_out,
+                   int64_t N, int64_t total, float inv_count, bool vec_ok, const float* __restrict__ grad_out,
                    float* __restrict__ dL_dpred) {
   const float gscale = __ldg(grad_out) * inv_count;
   // d|x|/dx = sign(x) with sign(0) = 0, as torch.abs' backward
@@ -74,7 +75,7 @@ l1_backward_kernel(const float* __restrict__ pred, const float* __restrict__ gt,
     return gscale * sg * m;
   };
   const int64_t nvec = total / 4;
-  if ((N % 4) == 0) {
+  if (vec_ok) {
     const float4* p4 = reinterpret_cast<const float4*>(pred);
     const float4* g4 = reinterpret_cast<const float4*>(gt);
     float4* o4 = reinterpret_cast<float4*>(dL_dpred);
@@ -97,6 +98,10 @@ l1_backward_kernel(const float* __restrict__ pred, const float* __restrict__ gt,
   }
 }
 
+inline bool aligned16(const void* a, const void* b, const void* c, const void* d = nullptr) {
+  return ((((uintptr_t)a) | ((uintptr_t)b) | ((uintptr_t)c) | ((uintptr_t)d)) & 15) == 0;
+}
+
 inline unsigned loss_blocks(int64_t total) {
   const int64_t per = (int64_t)LOSS_THREADS * LOSS_VEC_PER_THREAD * 4;
   return (unsigned)((total + per - 1) / per);
@@ -111,8 +116,9 @@ cudaError_t launch_l1_forward(const float* pred, const float* gt, const float* m
   const int64_t total = (int64_t)C * N;
   if (total == 0) return cudaSuccess;
   const float inv = (float)(1.0 / (double)total);
-  if (mask) l1_forward_kernel<true><<<loss_blocks(total), LOSS_THREADS, 0, s>>>(pred, gt, mask, N, total, inv, loss);
-  else l1_forward_kernel<false><<<loss_blocks(total), LOSS_THREADS, 0, s>>>(pred, gt, mask, N, total, inv, loss);
+  const bool vec = (N % 4) == 0 && aligned16(pred, gt, mask);
+  if (mask) l1_forward_kernel<true><<<loss_blocks(total), LOSS_THREADS, 0, s>>>(pred, gt, mask, N, total, inv, vec, loss);
+  else l1_forward_kernel<false><<<loss_blocks(total), LOSS_THREADS, 0, s>>>(pred, gt, mask, N, total, inv, vec, loss);
   count_launch();
   return cudaGetLastError();
 }
@@ -122,11 +128,12 @@ cudaError_t launch_l1_backward(const float* pred, const float* gt, const float* 
   const int64_t total = (int64_t)C * N;
   if (total == 0) return cudaSuccess;
   const float inv = (float)(1.0 / (double)total);
+  const bool vec = (N % 4) == 0 && aligned16(pred, gt, mask, dL_dpred);
   if (mask)
-    l1_backward_kernel<true><<<loss_blocks(total), LOSS_THREADS, 0, s>>>(pred, gt, mask, N, total, inv, grad_out,
+    l1_backward_kernel<true><<<loss_blocks(total), LOSS_THREADS, 0, s>>>(pred, gt, mask, N, total, inv, vec, grad_out,
                                                                          dL_dpred);
   else
-    l1_backward_kernel<false><<<loss_blocks(total), LOSS_THREADS, 0, s>>>(pred, gt, mask, N, total, inv, grad_out,
+    l1_backward_kernel<false><<<loss_blocks(total), LOSS_THREADS, 0, s>>>(pred, gt, mask, N, total, inv, vec, grad_out,
                                                                           dL_dpred);
   count_launch();
   return cudaGetLastError();

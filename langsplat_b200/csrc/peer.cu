@@ -27,14 +27,16 @@ __device__ __forceinline__ uint64_t globaltimer_ns() {
 // One warp.  Lane r < world: publish this rank's epoch in rank r's header (release at system scope, after a system
 // fence that orders every earlier write of this stream — the factors — before it), then wait until rank r's epoch
 // shows up in our own header (acquire).  Epochs only grow, compared as a signed difference so that wrap-around is
-// harmless.  A peer that never arrives must not hang the GPU: after LSR_PEER_TIMEOUT_NS the wait gives up and raises
-// timed_out in the own header (lsr_peer_status), the gradients of that step are then garbage and the caller aborts.
-constexpr uint64_t LSR_PEER_TIMEOUT_NS = 4000000000ull;
+// harmless.  A peer that never arrives must not hang the GPU: after the time-out (lsr_peer_set_timeout_ms, default
+// 120 s — long enough for a rank that checkpoints, evaluates or loads data before its step) the wait gives up and
+// raises the sticky timed_out word in the own header.  Nothing downstream may then pass for a result: the consumers'
+// outputs are overwritten with NaN (peer_poison_kernel, enqueued behind them by the exchange), lsr_peer_status
+// reports it, and the Python exchange raises at its next begin_step().
 
 // mode bit 0: signal, bit 1: wait.  Splitting the two lets a rank publish "my remote writes are done", run local work
 // that does not depend on the peers, and only then wait for them.
 __global__ void __launch_bounds__(32) peer_barrier_kernel(PeerHeaders hs, int rank, int world, uint32_t epoch,
-                                                          int mode) {
+                                                          int mode, uint64_t timeout_ns) {
   const int r = threadIdx.x;
   __threadfence_system();
   if (r < world && (mode & 1)) {
@@ -48,7 +50,7 @@ __global__ void __launch_bounds__(32) peer_barrier_kernel(PeerHeaders hs, int ra
       uint32_t seen;
       asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(mine) : "memory");
       if ((int32_t)(seen - epoch) >= 0) break;
-      if (globaltimer_ns() - t0 > LSR_PEER_TIMEOUT_NS) {
+      if (globaltimer_ns() - t0 > timeout_ns) {
         hs.h[rank]->timed_out = 1u;
         break;
       }
@@ -57,6 +59,14 @@ __global__ void __launch_bounds__(32) peer_barrier_kernel(PeerHeaders hs, int ra
   }
   __syncwarp();
   __threadfence_system();
+}
+
+// After a time-out the step's sums are incomplete: overwrite `data` with NaN so that no consumer mistakes them for
+// gradients.  One word read per thread in the normal case.
+__global__ void __launch_bounds__(256) peer_poison_kernel(const PeerHeader* own, float* __restrict__ data, int64_t n) {
+  if (own->timed_out == 0u) return;
+  const float nan = __int_as_float(0x7fc00000);
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) data[i] = nan;
 }
 
 // Two-shot sum over the ranks through peer memory.  Rank r owns the r-th chunk of the vector: it loads that chunk from
@@ -91,12 +101,24 @@ peer_allreduce_kernel(PeerBufs b, int world, int64_t first, int64_t end) {
   }
 }
 
+std::atomic<uint64_t> g_timeout_ms{120000};
+
 }  // namespace
+
+void peer_set_timeout_ms(uint64_t ms) { g_timeout_ms.store(ms ? ms : 1, std::memory_order_relaxed); }
+uint64_t peer_timeout_ms() { return g_timeout_ms.load(std::memory_order_relaxed); }
 
 void launch_peer_barrier(int rank, int world, void* const* headers, uint32_t epoch, int mode, cudaStream_t s) {
   PeerHeaders hs;
   for (int i = 0; i < LSR_MAX_PEERS; i++) hs.h[i] = i < world ? reinterpret_cast<PeerHeader*>(headers[i]) : nullptr;
-  peer_barrier_kernel<<<1, 32, 0, s>>>(hs, rank, world, epoch, mode);
+  peer_barrier_kernel<<<1, 32, 0, s>>>(hs, rank, world, epoch, mode, peer_timeout_ms() * 1000000ull);
+  count_launch();
+}
+
+void launch_peer_poison(const void* own_buffer, float* data, int64_t n, cudaStream_t s) {
+  if (n <= 0) return;
+  const int blocks = (int)std::min<int64_t>((n + 255) / 256, 148 * 8);
+  peer_poison_kernel<<<blocks, 256, 0, s>>>(reinterpret_cast<const PeerHeader*>(own_buffer), data, n);
   count_launch();
 }
 

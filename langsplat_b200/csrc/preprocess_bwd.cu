@@ -476,12 +476,11 @@ void launch_preprocess_bwd(const lsr_frame& f, const lsr_inputs& in, float focal
   const float* cov3Ds = in.cov3D_precomp ? in.cov3D_precomp : g.cov3D;
   const bool sh16 = in.shs != nullptr && (gr.dL_dsh != nullptr || gr.dL_dcolors_masked != nullptr) && f.M == 16 &&
                     (((uintptr_t)in.shs) & 15) == 0 && (((uintptr_t)gr.dL_dsh) & 15) == 0;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static DeviceOnce attr;  // per device: a process may drive several GPUs
+  attr.run([] {
     cudaFuncSetAttribute(preprocess_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BPRE_SH_SMEM);
     cudaFuncSetAttribute(preprocess_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BPRE_SH_SMEM);
-    attr_done = true;
-  }
+  });
   const int blocks = (f.P + BPRE_THREADS - 1) / BPRE_THREADS;
 #define LSR_BPRE_ARGS                                                                                              \
   f.P, f.D, f.M, in.means3D, radii, in.shs, g.clamped, in.scales, in.rotations, f.scale_modifier, cov3Ds,          \

@@ -294,12 +294,11 @@ void launch_preprocess_fwd(const lsr_frame& f, const lsr_inputs& in, float focal
   if (blocks == 0) return;
   // fast path: the usual [P,16,3] SH tensor, 16-byte aligned -> rows staged through shared memory
   const bool sh16 = in.shs != nullptr && f.M == 16 && (((uintptr_t)in.shs) & 15) == 0;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static DeviceOnce attr;  // per device: a process may drive several GPUs
+  attr.run([] {
     cudaFuncSetAttribute(preprocess_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PRE_SH_SMEM);
     cudaFuncSetAttribute(preprocess_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PRE_SH_SMEM);
-    attr_done = true;
-  }
+  });
 #define LSR_PRE_ARGS                                                                                                  \
   f.P, f.D, f.M, in.means3D, in.scales, f.scale_modifier, in.rotations, in.opacities, in.shs, in.cov3D_precomp,       \
       in.colors_precomp, f.include_feature ? in.language_feature : nullptr, f.viewmatrix, f.projmatrix, f.campos,     \

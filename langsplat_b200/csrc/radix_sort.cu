@@ -424,8 +424,8 @@ int sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_
   SortWork w = sort_work_view(work, n);
   const int items = sort_items_for(n);
   const uint32_t nblocks = (uint32_t)((n + SORT_THREADS * items - 1) / (SORT_THREADS * items));
-  static bool attr_done = false;
-  if (!attr_done) {
+  static DeviceOnce attr;  // per device: a process may drive several GPUs
+  attr.run([] {
     for (int nb = 0; nb <= BITS; nb++) {
       for (int it : {SORT_ITEMS}) {
         cudaFuncSetAttribute(onesweep_for_bits(nb, true, it), cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -434,8 +434,7 @@ int sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_
                              (int)sort_smem(it));
       }
     }
-    attr_done = true;
-  }
+  });
   const DigitMap dm{pl.lo_min, pl.lo_bits};
   if (!hist_ready) {
     sort_prepare(work, n, pl, s);

@@ -9,6 +9,7 @@ from __future__ import annotations
 
 import contextlib
 import ctypes
+import os
 import sys
 from typing import Dict, Iterable, List, Optional, Sequence
 
@@ -231,6 +232,14 @@ class PeerFactorExchange:
         self._headers = (ctypes.c_void_p * self.world)(*self.bases)
         self.epoch, self._count, self._degree, self._barriers = 0, 0, 0, 0
         self._side = torch.cuda.Stream(device=self.device)
+        # the sticky timed-out word of the own header, mirrored into pinned host memory behind every exchange and
+        # looked at (without synchronising) when the next step begins
+        self._flag_dev = torch.as_tensor(_DevicePtr(self.own, L.PEER_HEADER_BYTES // 4), device=self.device)[
+            L.MAX_PEERS:L.MAX_PEERS + 1]
+        self._flag_host = torch.zeros(1, dtype=torch.float32).pin_memory()
+        ms = os.environ.get("LSR_PEER_TIMEOUT_MS")
+        if ms:
+            self._check(self._lib.lsr_peer_set_timeout_ms(int(ms)))
 
     def _check(self, rc: int) -> None:
         if rc != self._L.LSR_OK:
@@ -238,7 +247,13 @@ class PeerFactorExchange:
 
     # -- sink protocol (rasterizer._backward_impl) --
     def begin_step(self) -> "PeerFactorExchange":
-        """Starts a step: the next `views_per_rank` backward passes write into this step's slot.  Returns the sink."""
+        """Starts a step: the next `views_per_rank` backward passes write into this step's slot.  Returns the sink.
+        Raises if a barrier of an earlier step timed out (a peer did not arrive within the time-out, LSR_PEER_TIMEOUT_MS
+        / lsr_peer_set_timeout_ms, default 120 s): that step's sums were overwritten with NaN, never returned as
+        gradients."""
+        if self._flag_host.view(torch.int32)[0].item() != 0:
+            raise self._err("PeerFactorExchange: a peer barrier timed out in an earlier step (a rank did not arrive); "
+                            "that step's gradients were poisoned with NaN")
         self.epoch += 1
         self._count = 0
         return self
@@ -339,6 +354,14 @@ class PeerFactorExchange:
                 main.wait_stream(self._side)
                 self._check(self._lib.lsr_peer_wait(self.rank, self.world, self._headers,
                                                     self._barriers & 0xFFFFFFFF, stream))
+            # a barrier that gave up leaves incomplete sums behind: never let them pass for gradients
+            own = ctypes.c_void_p(self.own)
+            self._check(self._lib.lsr_peer_poison_on_timeout(own, ctypes.c_void_p(out.data_ptr()), out.numel(),
+                                                             stream))
+            if total:
+                self._check(self._lib.lsr_peer_poison_on_timeout(
+                    own, ctypes.c_void_p(self.bases[self.rank] + off + self.out_off * 4), total, stream))
+            self._flag_host.copy_(self._flag_dev, non_blocking=True)
         if not total:
             return out, list(grads)
         reduced = []

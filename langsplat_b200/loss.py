@@ -31,6 +31,10 @@ def _mask_rows(mask: Optional[torch.Tensor], pred: torch.Tensor) -> Optional[tor
     scene/cameras.py:58-92 returns it) or has pred's full shape (then it is applied as one [1, C*N] row)."""
     if mask is None:
         return None
+    if mask.is_cuda and mask.dtype in (torch.bool, torch.uint8):
+        # Camera.get_language_feature returns `seg != -1`, a bool mask (scene/cameras.py:70), and train.py:96-99
+        # multiplies it in as it is; the kernels read a float mask
+        mask = mask.to(torch.float32)
     mask = _check(mask, "mask")
     if mask.numel() == pred.numel():
         return mask

@@ -63,12 +63,16 @@ def _prep(t: Optional[torch.Tensor], device) -> Optional[torch.Tensor]:
     if t is None:
         return None
     if t.dtype is torch.float32 and t.device == device and t.is_contiguous():  # the common case, kept cheap: this
-        return t if t.numel() != 0 else None                                   # runs a dozen times per frame
+        if t.numel() == 0:                                                     # runs a dozen times per frame
+            return None
+        # the kernels use 128-bit accesses: a contiguous view may start anywhere in its storage (x[1:]) -> re-pack
+        return t if (t.data_ptr() & 15) == 0 else t.clone(memory_format=torch.contiguous_format)
     if not _present(t):
         return None
     if t.device != device or t.dtype != torch.float32:
         t = t.to(device=device, dtype=torch.float32)
-    return t.contiguous()
+    t = t.contiguous()
+    return t if (t.data_ptr() & 15) == 0 else t.clone(memory_format=torch.contiguous_format)
 
 
 def _ptr(t: Optional[torch.Tensor]):
@@ -306,6 +310,11 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.raster_settings = raster_settings
         ctx.num_rendered = state["num_rendered"]
         ctx.state = state
+        # The kernels' view of the inputs travels in `state` (device pointers of the contiguous tensors); the tensors
+        # themselves go through save_for_backward like the reference's (RAST/diff_gaussian_rasterization/
+        # __init__.py:102), so that autograd's version counters catch an in-place update between forward and backward
+        # (the backward combines the forward's geometry records with these inputs) and saved-tensor hooks see them.
+        ctx.save_for_backward(*args)
         ctx.set_materialize_grads(False)
         ctx.mark_non_differentiable(radii)
         return color, feature, radii
@@ -313,6 +322,7 @@ class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def backward(ctx, grad_out_color, grad_out_language_feature, _):
         state = ctx.state
+        ctx.saved_tensors  # raises if an input was modified in place since the forward (version counters)
         need = ctx.needs_input_grad  # (means3D, means2D, sh, colors, lang, opac, scales, rots, cov3D, settings)
         mask = 0
         if need[0] or need[5] or need[6] or need[7] or need[8]:

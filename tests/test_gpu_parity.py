@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 import torch
 
-from helpers import (R, cuda_forward_state, oracle_forward, orc, rel_err, run_module, syn)
+from helpers import (R, cuda_forward_state, oracle_forward, orc, rel_err, run_module, settings_for, syn)
 
 pytestmark = pytest.mark.gpu
 
@@ -230,3 +230,57 @@ def test_non_contiguous_camera_matrices():
     assert not cam2.viewmatrix.is_contiguous()
     alt = run_module(R.GaussianRasterizer, R.GaussianRasterizationSettings, scene, cam2)
     assert torch.equal(base["color"], alt["color"]) and torch.equal(base["radii"], alt["radii"])
+
+
+def test_misaligned_input_views_are_repacked():
+    """Contiguous views that start at an odd element of their storage (x[1:]): the kernels' 128-bit accesses need
+    16-byte alignment, so the host layer re-packs such tensors instead of faulting; results are unchanged."""
+    scene, cams = syn.make_config(1, P=3001, W=96, H=96)
+    cam = cams[0]
+    dcol, dfeat = syn.make_grads(cam.image_width, cam.image_height, 31)
+    cut = {k: v[1:].contiguous() for k, v in scene.items()}
+    base = run_module(R.GaussianRasterizer, R.GaussianRasterizationSettings, cut, cam, grads=(dcol, dfeat))
+    rs = settings_for(cam, "cuda")
+    dev = {k: v.cuda() for k, v in scene.items()}
+    t = {k: v[1:].requires_grad_(True) for k, v in dev.items()}  # views: storage offset of one row
+    assert t["rotations"].data_ptr() % 16 == 0 and t["means3D"].data_ptr() % 16 != 0
+    rot_odd = torch.cat([torch.zeros(1, device="cuda"), dev["rotations"][1:].reshape(-1)])[1:].view(-1, 4)
+    assert rot_odd.data_ptr() % 16 == 4 and rot_odd.is_contiguous()
+    rot_odd.requires_grad_(True)
+    means2D = torch.zeros_like(t["means3D"], requires_grad=True)
+    color, feat, radii = R.GaussianRasterizer(rs)(
+        means3D=t["means3D"], means2D=means2D, shs=t["shs"], language_feature_precomp=t["language_feature"],
+        opacities=t["opacities"], scales=t["scales"], rotations=rot_odd)
+    ((color * dcol.cuda()).sum() + (feat * dfeat.cuda()).sum()).backward()
+    torch.cuda.synchronize()
+    assert torch.equal(color, base["color"]) and torch.equal(radii, base["radii"])
+    assert rel_err(rot_odd.grad, base["grads"]["rotations"]) < 1e-5
+
+
+def test_in_place_update_between_forward_and_backward_is_detected():
+    """The reference saves its inputs with ctx.save_for_backward (RAST/diff_gaussian_rasterization/__init__.py:102), so
+    autograd raises when one of them is modified in place before backward; same here."""
+    scene, cams = syn.make_config(1, P=2000, W=64, H=64)
+    cam = cams[0]
+    t = {k: v.cuda().requires_grad_(True) for k, v in scene.items()}
+    means2D = torch.zeros_like(t["means3D"], requires_grad=True)
+    color, feat, radii = R.GaussianRasterizer(settings_for(cam, "cuda"))(
+        means3D=t["means3D"], means2D=means2D, shs=t["shs"], language_feature_precomp=t["language_feature"],
+        opacities=t["opacities"], scales=t["scales"], rotations=t["rotations"])
+    with torch.no_grad():
+        t["scales"].mul_(1.01)  # e.g. an optimizer step between the forwards and backwards of a multi-view step
+    with pytest.raises(RuntimeError, match="modified by an inplace operation"):
+        (color.sum() + feat.sum()).backward()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_second_device_in_the_same_process():
+    """Function attributes (dynamic shared memory > 48 KB) are per device: forward + backward on cuda:1 after cuda:0."""
+    scene, cams = syn.make_config(1, P=5000, W=128, H=128)
+    cam = cams[0]
+    dcol, dfeat = syn.make_grads(cam.image_width, cam.image_height, 32)
+    a = run_module(R.GaussianRasterizer, R.GaussianRasterizationSettings, scene, cam, device="cuda:0", grads=(dcol, dfeat))
+    b = run_module(R.GaussianRasterizer, R.GaussianRasterizationSettings, scene, cam, device="cuda:1", grads=(dcol, dfeat))
+    assert torch.equal(a["color"].cpu(), b["color"].cpu()) and torch.equal(a["radii"].cpu(), b["radii"].cpu())
+    for k in ("means3D", "shs", "scales", "rotations", "opacities", "language_feature"):
+        assert rel_err(a["grads"][k].cpu(), b["grads"][k].cpu()) < 1e-5

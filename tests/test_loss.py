@@ -85,3 +85,49 @@ def test_cuda_l1_loss_errors_and_empty():
     with pytest.raises(LsrError):
         l1_loss(torch.zeros(3, 4, 4, device=dev), torch.zeros(3, 4, 4, device=dev), torch.zeros(5, device=dev))
     assert torch.isnan(l1_loss(torch.zeros(3, 0, 4, device=dev), torch.zeros(3, 0, 4, device=dev)))
+
+
+@pytest.mark.gpu
+def test_cuda_l1_loss_takes_the_bool_mask_train_py_passes():
+    """scene/cameras.py:70 returns `seg != -1` (bool) and train.py:96-99 multiplies it in as it is; so does this
+    repo's drop-in get_language_feature.  The mask goes straight into l1_loss."""
+    from langsplat_b200 import l1_loss
+    from langsplat_b200.gt_features import language_feature_map
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(11)
+    H, W, K = 37, 52, 9
+    seg = torch.randint(-1, K, (4, H, W), generator=g).float().to(dev)
+    table = torch.randn(K, 3, generator=g).to(dev)
+    gt, mask = language_feature_map(seg, table, 1, H, W)
+    assert mask.dtype == torch.bool
+    x = torch.rand(3, H, W, generator=g).to(dev).requires_grad_(True)
+    ours = l1_loss(x, gt, mask)
+    ours.backward()
+    g_ours = x.grad.clone()
+    x.grad = None
+    ref = torch.abs(x * mask - gt * mask).mean()
+    ref.backward()
+    assert abs(ours.item() - ref.item()) <= 2e-6 * abs(ref.item())
+    np.testing.assert_allclose(g_ours.cpu().numpy(), x.grad.cpu().numpy(), rtol=2e-7, atol=0)
+    assert abs(l1_loss(x, gt, mask.to(torch.uint8)).item() - ref.item()) <= 2e-6 * abs(ref.item())
+
+
+@pytest.mark.gpu
+def test_cuda_l1_loss_misaligned_views():
+    """Contiguous views that do not start on a 16-byte boundary (storage offset 1) must take the scalar path, not
+    fault: the float4 fast path checks pointer alignment, not only the shape."""
+    from langsplat_b200 import l1_loss
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(12)
+    n = 3 * 16 * 16
+    base_x, base_gt = torch.rand(n + 1, generator=g).to(dev), torch.rand(n + 1, generator=g).to(dev)
+    base_m = (torch.rand(16 * 16 + 1, generator=g) > 0.3).float().to(dev)
+    x = base_x[1:].view(3, 16, 16).requires_grad_(True)
+    gt, m = base_gt[1:].view(3, 16, 16), base_m[1:].view(1, 16, 16)
+    assert x.data_ptr() % 16 == 4 and x.is_contiguous()
+    ours = l1_loss(x, gt, m)
+    ours.backward()
+    ref = torch.abs(x.detach() * m - gt * m).mean()
+    assert abs(ours.item() - ref.item()) <= 2e-6 * abs(ref.item())
+    want = torch.sign(x.detach() * m - gt * m) * m / n
+    np.testing.assert_allclose(x.grad.cpu().numpy(), want.cpu().numpy(), rtol=2e-7, atol=0)
