@@ -68,6 +68,12 @@ def parse_args():
     ap.add_argument("--dense-sh-exchange", action="store_true",
                     help="multi-view / multi-GPU: all-reduce dL_dsh itself instead of its per-view factors (A/B)")
     ap.add_argument("--cpu-frames", type=int, default=3)
+    ap.add_argument("--sync-forward", action="store_true",
+                    help="ours: keep the reference's per-frame host read-back of the instance count (lsr_forward) "
+                         "instead of the asynchronous forward (langsplat_b200.set_async_forward; A/B)")
+    ap.add_argument("--separate-levels", action="store_true",
+                    help="config 5, ours: three independent forward calls (the reference's call sequence, "
+                         "render.py:35-52) instead of forward_feature_levels (A/B)")
     return ap.parse_args()
 
 
@@ -220,6 +226,12 @@ def main():
     os.dup2(2, 1)  # anything else written to stdout (NCCL's version banner, warnings) goes to stderr
     rank, world, dev = init_dist(args.gpus)
     GR, GS, impl_name = load_impl(args.impl)
+    async_fwd = args.impl == "ours" and not args.sync_forward
+    if async_fwd:
+        # the package's public switch: no host read-back inside the forward (the first frame on a device still runs
+        # synchronously and teaches it the instance count)
+        import langsplat_b200
+        langsplat_b200.set_async_forward(True)
     scene, cams = syn.make_config(args.config, P=args.P, W=args.width, H=args.height, n_cameras=8)
     cfg = args.config
     feature_only = cfg == 3   # train.py --include_feature: only language_feature (and means2D) carry gradients
@@ -234,7 +246,9 @@ def main():
     metric = METRICS.get(cfg, METRIC)
     what = ("language-feature-only fwd+bwd" if feature_only else
             ("forward only, 3 feature levels" + (" (ours: one preprocess + binning shared by the levels, "
-                                                 "forward_feature_levels)" if args.impl == "ours" else ""))
+                                                 "forward_feature_levels)"
+                                                 if args.impl == "ours" and not args.separate_levels else
+                                                 " (three independent forward calls)"))
             if fwd_only
             else "fwd+bwd")
     workload = (f"config{cfg}: {P} Gaussians, {W}x{H}, SH deg 3 + 3-ch language feature, {what}, "
@@ -330,7 +344,7 @@ def main():
     def step():
         if fwd_only:
             with torch.no_grad():
-                if args.impl == "ours":  # the three levels share the geometry: preprocess + binning once
+                if args.impl == "ours" and not args.separate_levels:  # the levels share the geometry: preprocess + binning once
                     rast.forward_feature_levels(means3D=params["means3D"], opacities=params["opacities"],
                                                 language_features=levels, shs=params["shs"], scales=params["scales"],
                                                 rotations=params["rotations"])
@@ -398,7 +412,7 @@ def main():
         if fwd_only:
             with torch.no_grad():
                 acc = None
-                if args.impl == "ours":
+                if args.impl == "ours" and not args.separate_levels:
                     color, feats, radii = GR(raster_settings=rs2).forward_feature_levels(
                         means3D=params["means3D"], opacities=params["opacities"], language_features=levels,
                         shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
@@ -489,7 +503,10 @@ def main():
         lib.lsr_profile_enable(0)
         stage_ms = acc[:n_st] / args.steps
         stages = {lib.lsr_profile_stage_name(i).decode(): float(stage_ms[i]) for i in range(n_st)}
+        stages_us = {k: round(v * 1e3, 2) for k, v in stages.items()}
 
+    if async_fwd:
+        langsplat_b200.check_async_status()  # an instance list that overflowed would have NaN-filled a frame: fail
     if peer is not None:
         peer.check()  # a barrier that timed out would have produced garbage gradients: fail the run
         peer.close()
@@ -504,16 +521,21 @@ def main():
             "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
             "scaling": "strong" if cfg == 4 else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload, "P": P, "width": W, "height": H, "cameras_per_step": views_per_step,
-                       "l2_policy": "inputs larger than L2 (Gaussian tensors ~250 MB), no explicit flush",
-                       "impl": impl_name, "exchange": exchange},
+                       "l2_policy": "inputs larger than L2 (Gaussian tensors ~250 MB), no explicit flush"},
+            "implementation": impl_name, "exchange": exchange,
+            "forward_mode": ("asynchronous (lsr_forward_nosync: no host read-back, langsplat_b200.set_async_forward)"
+                             if async_fwd else "one host read-back of the instance count per frame, like the reference "
+                                               "(rasterizer_impl.cu:284)"),
             "fwd_only_ms_per_frame": fwd_ms, "clocks": clocks,
             "e2e": {"value": (world * (len(levels) if fwd_only else 1)) * args.steps / (e2e_ms_total / 1000.0),
                     "unit": "frames/s",
                     "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4,
                     "what": "per step: one view (camera matrices + GT colour/feature images, 49.8 MB) copied from "
                             "pinned host memory on a side stream, prefetched one step ahead like a data "
-                            "loader, L1 loss (ours: fused langsplat_b200.l1_loss; reference: torch.abs(x-gt).mean()"
-                            "), backward, loss.item()"},
+                            "loader, L1 loss, backward, loss.item()",
+                    "loss": ("fused langsplat_b200.l1_loss kernels (SURVEY 8(f) row 1)" if args.impl == "ours" else
+                             "LangSplat's own l1_loss, torch.abs(x - gt).mean() (utils/loss_utils.py:17-18)") +
+                            " - the two arms differ here: each runs its own public API"},
             "gpu_launches": launches}
     if args.impl == "reference":
         line["impl"] = "reference"
@@ -537,6 +559,8 @@ def main():
     hbm, sm_mhz, src = measured_peaks()
     n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
     fp32_peak = n_sm * 128 * sm_mhz * 1e6  # FP32-pipe instructions / s (FMA = 1)
+    if stages:
+        line["stages_us"] = stages_us  # every stage as timed by CUDA events inside liblsr.so, host_sync_gap included
     if stats and stage_ms is not None:
         V, Rn, Kx, Kc = stats["V"], stats["R"], stats["K_exam"], stats["K_contrib"]
         N, T = W * H, ((W + 15) // 16) * ((H + 15) // 16)
@@ -596,6 +620,7 @@ def main():
         if "fp32_instr" in d:
             line["roofline"] = {"kernel": dom, "bound": "fp32", "achieved": d["Tinstr_s"], "peak": fp32_peak / 1e12,
                                 "unit": "TInstr/s", "frac": d["fp32_frac"], "traffic": traffic.get(dom),
+                                "traffic_source": tj.get("_source") if traffic else None,
                                 "peak_source": f"{n_sm} SMs x 128 lanes x {sm_mhz:.0f} MHz ({src} clock)",
                                 "note": "blend kernels are FP32-pipe bound (no dense contraction, SURVEY 8d); "
                                         "roofline_frac in `stages` adds the HBM term"}

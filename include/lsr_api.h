@@ -130,6 +130,35 @@ int lsr_forward(const lsr_frame* frame, const lsr_inputs* in, float* out_color, 
                 void* geom, void* image, void* list, int64_t list_capacity, void* scratch, size_t scratch_bytes,
                 int64_t* num_rendered, void* stream);
 
+/* Forward without any host synchronisation (the reference reads the instance count back in the
+ * middle of every frame, rasterizer_impl.cu:284).  Same device work and same results as lsr_forward, but the instance
+ * count stays on the device: launch geometry comes from `list_capacity`, the kernels read the count (and the range of
+ * the depth word) from device memory, and nothing is returned to the host before the call ends — so the call can be
+ * captured in a CUDA graph and the host runs ahead of the GPU.
+ * What the device found out is kept in the call's `image` state as LSR_STATUS_WORDS 32-bit words (lsr_forward_status
+ * reads them, synchronising) and, if `status_host` is given (PINNED host memory, LSR_STATUS_WORDS words), also copied
+ * there asynchronously on `stream`: the copy is complete once status_host[LSR_STATUS_STAMP] == stamp (the caller
+ * picks `stamp` != 0 and clears the word first).
+ * If the instance count exceeds list_capacity the frame cannot be rendered: LSR_STATUS_FLAG_OVERFLOW is raised and
+ * out_color / out_feature are filled with NaN, so that an incomplete image can never pass for a result; the caller
+ * repeats the frame with the capacity the status reports.  prefiltered=1 violations are reported the same way
+ * (LSR_STATUS_FLAG_PREFILTERED) instead of LSR_ERR_PREFILTERED. */
+enum {
+  LSR_STATUS_NUM_RENDERED = 0, /* R, the number of Gaussian/tile instances of the frame (may exceed the capacity) */
+  LSR_STATUS_FLAGS = 1,        /* LSR_STATUS_FLAG_* */
+  LSR_STATUS_DEPTH_MIN = 2,    /* float bits of the smallest / largest view depth among the visible Gaussians */
+  LSR_STATUS_DEPTH_MAX = 3,
+  LSR_STATUS_CAPACITY = 4,     /* the list_capacity the frame ran with */
+  LSR_STATUS_STAMP = 5,        /* the caller's stamp, written last */
+  LSR_STATUS_WORDS = 8
+};
+enum { LSR_STATUS_FLAG_PREFILTERED = 1, LSR_STATUS_FLAG_OVERFLOW = 2 };
+int lsr_forward_nosync(const lsr_frame* frame, const lsr_inputs* in, float* out_color, float* out_feature,
+                       int32_t* radii, void* geom, void* image, void* list, int64_t list_capacity, void* scratch,
+                       size_t scratch_bytes, uint32_t stamp, uint32_t* status_host, void* stream);
+/* Status words of a forward (either kind) from its `image` state; synchronises `stream`.  status: HOST, 8 words. */
+int lsr_forward_status(int32_t width, int32_t height, const void* image, uint32_t* status, void* stream);
+
 /* Another feature level on the same geometry (LangSplat's three SAM levels share every Gaussian
  * attribute except language_feature, and render.py renders them back to back).  Takes the saved state of an
  * lsr_forward made with include_feature, replaces the language feature held in its per-Gaussian records by

@@ -6,9 +6,11 @@ Importing this package does not load the CUDA library; the first rasterizer call
 liblsr.so is missing (there is no CPU fallback).
 """
 from .rasterizer import (GaussianRasterizationSettings, GaussianRasterizer, LsrError, rasterize_gaussians,
-                         cpu_deep_copy_tuple)
+                         cpu_deep_copy_tuple, set_async_forward, async_forward, check_async_status,
+                         reserve_instances)
 from .loss import l1_loss
 from .activations import activate
 
 __all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians", "LsrError",
-           "cpu_deep_copy_tuple", "l1_loss", "activate"]
+           "cpu_deep_copy_tuple", "l1_loss", "activate", "set_async_forward", "async_forward",
+           "check_async_status", "reserve_instances"]

@@ -20,6 +20,11 @@ LSR_ERR_CAPACITY = -2
 LSR_ERR_CUDA = -3
 LSR_ERR_PREFILTERED = -4
 
+# status words of a forward (include/lsr_api.h LSR_STATUS_*)
+STATUS_NUM_RENDERED, STATUS_FLAGS, STATUS_DEPTH_MIN, STATUS_DEPTH_MAX, STATUS_CAPACITY, STATUS_STAMP, STATUS_WORDS = (
+    0, 1, 2, 3, 4, 5, 8)
+STATUS_FLAG_PREFILTERED, STATUS_FLAG_OVERFLOW = 1, 2
+
 NEED_GEOMETRY, NEED_COLOR, NEED_FEATURE, NEED_MEANS2D, NEED_ALL = 1, 2, 4, 8, 15
 
 # lsr_array_offset ids
@@ -71,6 +76,9 @@ EXPORTS = {
     "lsr_array_offset": (c_size_t, [c_int, c_int32, c_int32, c_int32, c_int64]),
     "lsr_forward": (c_int, [POINTER(Frame), POINTER(Inputs), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                             c_void_p, c_int64, c_void_p, c_size_t, POINTER(c_int64), c_void_p]),
+    "lsr_forward_nosync": (c_int, [POINTER(Frame), POINTER(Inputs), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                   c_void_p, c_int64, c_void_p, c_size_t, c_uint32, c_void_p, c_void_p]),
+    "lsr_forward_status": (c_int, [c_int32, c_int32, c_void_p, c_void_p, c_void_p]),
     "lsr_forward_feature_level": (c_int, [c_int32, c_int32, c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                           c_void_p, c_void_p]),
     "lsr_backward": (c_int, [POINTER(Frame), POINTER(Inputs), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,

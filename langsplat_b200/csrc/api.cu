@@ -4,6 +4,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <algorithm>
 #include <utility>
@@ -477,110 +478,170 @@ static int check_frame(const lsr_frame* f, const lsr_inputs* in) {
   return LSR_OK;
 }
 
-int lsr_forward(const lsr_frame* frame, const lsr_inputs* in, float* out_color, float* out_feature, int32_t* radii,
-                void* geom, void* image, void* list, int64_t list_capacity, void* scratch, size_t scratch_nbytes,
-                int64_t* num_rendered, void* stream) {
-  cudaStream_t s = (cudaStream_t)stream;
+// One device pipeline serves both entry points.  Nothing after the preprocess kernel needs the instance count R or
+// the depth range on the host: the kernels read them from the control words (binning.cu, radix_sort.cu), launch
+// geometry comes from a bound on R.  lsr_forward reads R back once after the preprocess kernel, like the reference
+// (rasterizer_impl.cu:284), because its contract is to report R and to refuse a list that is too small BEFORE anything
+// is blended; its bound is then R itself.  lsr_forward_nosync skips that read: the bound is the list capacity, an
+// overflow is flagged on the device and the images are NaN-filled.
+static int forward_impl(const lsr_frame* frame, const lsr_inputs* in, float* out_color, float* out_feature,
+                        int32_t* radii, void* geom, void* image, void* list, int64_t list_capacity, void* scratch,
+                        size_t scratch_nbytes, int64_t* num_rendered, bool sync, uint32_t stamp,
+                        uint32_t* status_host, cudaStream_t s) {
   int rc = check_frame(frame, in);
   if (rc != LSR_OK) return rc;
-  if (!out_color || !image || !num_rendered || (frame->include_feature && !out_feature))
+  if (!out_color || !image || (sync && !num_rendered) || (frame->include_feature && !out_feature))
     return fail(LSR_ERR_INVALID, "null output pointer");
   const int P = frame->P, W = frame->width, H = frame->height;
   const int gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
   const int T = gx * gy;
+  const size_t N = (size_t)W * H;
   ImageView img = image_view(image, W, H);
-  *num_rendered = 0;
+  if (num_rendered) *num_rendered = 0;
   if (g_profile) g_have_f = false;
-  LSR_CUDA(cudaMemsetAsync(img.ranges, 0, (size_t)T * sizeof(uint2), s));  // rasterizer_impl.cu:313
-  int64_t R = 0;
+  if (P == 0) {
+    // rasterize_points.cu:91: the reference returns zero-filled images for an empty scene (blending empty ranges
+    // would give colour = bg, which differs), so reproduce the zero fill
+    LSR_CUDA(cudaMemsetAsync(img.ranges, 0, (size_t)T * sizeof(uint2), s));
+    LSR_CUDA(cudaMemsetAsync(img.status, 0, LSR_STATUS_WORDS * sizeof(uint32_t), s));
+    LSR_CUDA(cudaMemsetAsync(out_color, 0, 3 * N * sizeof(float), s));
+    if (frame->include_feature) LSR_CUDA(cudaMemsetAsync(out_feature, 0, 3 * N * sizeof(float), s));
+    if (g_profile) {
+      for (int i = 0; i <= 8; i++) prof(g_ev_f, i, s);
+      g_have_f = true;
+    }
+    if (status_host) {
+      // (the stamp travels through a staging word of the image state so that the copy stays stream-ordered)
+      LSR_CUDA(cudaMemcpyAsync(img.status + LSR_STATUS_STAMP, &stamp, sizeof(stamp), cudaMemcpyHostToDevice, s));
+      LSR_CUDA(cudaMemcpyAsync(status_host, img.status, LSR_STATUS_WORDS * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    }
+    return LSR_OK;
+  }
+  if (!radii || !geom || !scratch) return fail(LSR_ERR_INVALID, "null radii / geom / scratch");
+  if (list_capacity < 0 || list_capacity >= (1ll << 30)) return fail(LSR_ERR_INVALID, "list_capacity out of range");
+  if (list_capacity > 0 && !list) return fail(LSR_ERR_INVALID, "null list buffer");
+  if (scratch_nbytes < scratch_bytes(P, list_capacity))
+    return fail(LSR_ERR_INVALID, "scratch buffer smaller than lsr_scratch_bytes(P, capacity)");
   GeomView g = geom_view(geom, P);
   ScratchView sc = scratch_view(scratch, P, list_capacity);
-  const uint64_t* keys_sorted = nullptr;
-  if (P > 0) {
-    if (!radii || !geom || !scratch) return fail(LSR_ERR_INVALID, "null radii / geom / scratch");
-    if (list_capacity < 0 || list_capacity >= (1ll << 30)) return fail(LSR_ERR_INVALID, "list_capacity out of range");
-    if (scratch_nbytes < scratch_bytes(P, list_capacity))
-      return fail(LSR_ERR_INVALID, "scratch buffer smaller than lsr_scratch_bytes(P, capacity)");
-    // focal lengths exactly as the reference computes them on the host in f32 (rasterizer_impl.cu:225-226)
-    const float focal_y = H / (2.0f * frame->tanfovy);
-    const float focal_x = W / (2.0f * frame->tanfovx);
-    LSR_CUDA(cudaMemsetAsync(scratch, 0, sc.head_zero_bytes, s));
-    prof(g_ev_f, 0, s);
-    launch_preprocess_fwd(*frame, *in, focal_x, focal_y, radii, g, sc.ctrl, s);
-    LSR_STAGE("preprocess_fwd");
-    prof(g_ev_f, 1, s);
-    // R (accumulated by the preprocess kernel) decides the launch geometry of the instance sort; read it back like
-    // the reference does (rasterizer_impl.cu:284), together with the range of the depth word, which decides how many
-    // digits the depth ordering needs
+  // focal lengths exactly as the reference computes them on the host in f32 (rasterizer_impl.cu:225-226)
+  const float focal_y = H / (2.0f * frame->tanfovy);
+  const float focal_x = W / (2.0f * frame->tanfovx);
+  int id_bits = 1;
+  while (id_bits < 32 && (((uint32_t)P - 1u) >> id_bits) != 0) id_bits++;
+  // The reference sorts R keys on bits [0, 32 + getHigherMsb(T)) (rasterizer_impl.cu:303,311).  Same order, less
+  // traffic (binning.cu): (1) stable sort of the P Gaussians by depth — the depth word only spans [min, max], so
+  // bitlength(max - min) bits suffice, a width only the device knows; (2) instances emitted in that order;
+  // (3) stable sort of the R instance words on the tile bits only.
+  const SortPlan dplan = make_sort_plan_packed(32, id_bits);  // worst case: DEPTH_MAX_PASSES, the device skips the rest
+  const SortPlan plan = make_sort_plan_packed((int)higher_msb((uint32_t)T), id_bits);
+  g_last_id_bits = id_bits;
+
+  LSR_CUDA(cudaMemsetAsync(scratch, 0, sc.head_zero_bytes, s));
+  LSR_CUDA(cudaMemsetAsync(img.ranges, 0xFF, (size_t)T * sizeof(uint2), s));  // (start, ~end) under min-operations
+  prof(g_ev_f, 0, s);
+  launch_preprocess_fwd(*frame, *in, focal_x, focal_y, radii, g, sc.ctrl, s);
+  LSR_STAGE("preprocess_fwd");
+  prof(g_ev_f, 1, s);
+  int64_t bound = list_capacity;  // what the launch geometry of the R-sized kernels is sized for
+  if (sync) {
     uint32_t* h = pinned_ctrl();
     LSR_CUDA(cudaMemcpyAsync(h, sc.ctrl, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
     LSR_CUDA(cudaStreamSynchronize(s));
-    R = (int64_t)h[CTRL_NUM_RENDERED];
+    const int64_t R = (int64_t)h[CTRL_NUM_RENDERED];
     *num_rendered = R;
-    if (h[CTRL_ERROR] & 1u)
+    if (h[CTRL_ERROR] & ERR_PREFILTERED)
       return fail(LSR_ERR_PREFILTERED, "Point is filtered although prefiltered is set. This shouldn't happen!");
     if (R > list_capacity) return fail(LSR_ERR_CAPACITY, "num_rendered %lld exceeds list capacity %lld",
                                        (long long)R, (long long)list_capacity);
-    if (R > 0 && !list) return fail(LSR_ERR_INVALID, "null list buffer");
-    prof(g_ev_f, 2, s);
-    // The reference sorts R keys on bits [0, 32 + getHigherMsb(T)) (rasterizer_impl.cu:303,311).  Same order, less
-    // traffic (binning.cu): (1) stable sort of the P Gaussians by depth — the depth word only spans [min, max], so
-    // bitlength(max - min) bits suffice; (2) instances emitted in that order; (3) stable sort of the R instance words
-    // on the tile bits only.
-    int id_bits = 1;
-    while (id_bits < 32 && (((uint32_t)P - 1u) >> id_bits) != 0) id_bits++;
-    const SortPlan dplan = make_sort_plan(~h[CTRL_DEPTH_NEGMIN], h[CTRL_DEPTH_MAX], 0, id_bits);
-    const SortPlan plan = make_sort_plan_packed((int)higher_msb((uint32_t)T), id_bits);
-    g_last_id_bits = id_bits;
-    if (R > 0) {
-      uint64_t* din = (dplan.passes & 1) ? sc.dwords_a : sc.dwords_b;  // sorted words always end up in dwords_b
-      sort_prepare(sc.sort_work_p, P, dplan, s);
-      launch_depth_words(P, g.depth, g.tiles, dplan, din, sort_work_view(sc.sort_work_p, P).hist, s);
-      sort_pairs(din, nullptr, sc.dwords_b, sc.perm, sc.dwords_a, nullptr, P, dplan, true, sc.sort_work_p, s);
-      LSR_STAGE("depth_order");
-    }
-    prof(g_ev_f, 3, s);
-    if (R > 0) {
-      launch_scan_tiles(P, g.tiles, sc.perm, g.offsets, sc.scan_status, sc.ctrl, s);
-      LSR_STAGE("scan");
-    }
+    bound = R;
+  }
+  prof(g_ev_f, 2, s);
+  {
+    sort_prepare(sc.sort_work_p, P, dplan, s);
+    launch_depth_words(P, g.depth, g.tiles, sc.ctrl, id_bits, sc.dwords_a, sort_work_view(sc.sort_work_p, P).hist, s);
+    SortDyn dd;
+    dd.bits_dev = sc.ctrl + CTRL_DEPTH_BITS;
+    dd.max_passes = DEPTH_MAX_PASSES;
+    sort_pairs(sc.dwords_a, nullptr, sc.dwords_b, sc.perm, sc.dwords_a, nullptr, P, dplan, true, sc.sort_work_p, s, &dd);
+    LSR_STAGE("depth_order");
+  }
+  prof(g_ev_f, 3, s);
+  // the sorted words always end up in keys_b: the unsorted ones start in keys_a (odd pass count) or keys_b (even)
+  uint64_t* kin = (plan.passes & 1) ? sc.keys_a : sc.keys_b;
+  // LSR_LEGACY_BINNING=1 (synchronous forward only): the round-1 kernels — stand-alone scan, slot-walking duplication,
+  // separate range kernel — kept selectable for A/B measurements and for bisecting a parity failure.
+  static const bool legacy_env = getenv("LSR_LEGACY_BINNING") != nullptr;
+  if (legacy_env && sync) {
+    const int64_t R = bound;
+    LSR_CUDA(cudaMemsetAsync(img.ranges, 0, (size_t)T * sizeof(uint2), s));  // rasterizer_impl.cu:313
+    if (R > 0) launch_scan_tiles(P, g.tiles, sc.perm, g.offsets, sc.scan_status, sc.ctrl, s);
     prof(g_ev_f, 4, s);
-    // the sorted words always end up in keys_b: the unsorted ones start in keys_a (odd pass count) or keys_b (even)
-    uint64_t* kin = (plan.passes & 1) ? sc.keys_a : sc.keys_b;
     if (R > 0) {
       sort_prepare(sc.sort_work, R, plan, s);
       launch_duplicate(P, gx, gy, sc.perm, radii, g, kin, list_capacity, plan, sort_work_view(sc.sort_work, R).hist, s);
-      LSR_STAGE("duplicate");
     }
     prof(g_ev_f, 5, s);
-    if (R > 0) {
-      sort_pairs(kin, nullptr, sc.keys_b, (uint32_t*)list, sc.keys_a, nullptr, R, plan, true, sc.sort_work, s);
-      keys_sorted = sc.keys_b;
+    if (R > 0) sort_pairs(kin, nullptr, sc.keys_b, (uint32_t*)list, sc.keys_a, nullptr, R, plan, true, sc.sort_work, s);
+    prof(g_ev_f, 6, s);
+    if (R > 0) launch_tile_ranges(R, sc.keys_b, id_bits, img.ranges, s);
+    launch_finalize_tiles(T, img.ranges, img.tile_order, false, sc.ctrl, list_capacity, stamp, img.status, s);
+    LSR_STAGE("legacy binning");
+  } else {
+    prof(g_ev_f, 4, s);  // (the scan of the tile counts is part of the duplication kernel)
+    if (bound > 0) sort_prepare(sc.sort_work, bound, plan, s);
+    launch_dup_scan(P, gx, gy, sc.perm, radii, g, kin, list_capacity, plan, sc.scan_status, sc.ctrl,
+                    sort_work_view(sc.sort_work, bound).hist, s);
+    LSR_STAGE("duplicate");
+    prof(g_ev_f, 5, s);
+    if (bound > 0) {
+      SortDyn sd;
+      sd.n_dev = sc.ctrl + CTRL_NUM_RENDERED;
+      sd.ranges = img.ranges;
+      sd.tile_shift = id_bits;
+      sort_pairs(kin, nullptr, sc.keys_b, (uint32_t*)list, sc.keys_a, nullptr, bound, plan, true, sc.sort_work, s, &sd);
       LSR_STAGE("sort");
     }
     prof(g_ev_f, 6, s);
-    if (R > 0) {
-      launch_tile_ranges(R, keys_sorted, id_bits, img.ranges, s);
-      LSR_STAGE("tile_ranges");
-    }
-    if (LSR_TILE_ORDER) launch_tile_order(T, img.ranges, img.tile_order, s);  // also when nothing was rendered
-    prof(g_ev_f, 7, s);
-  } else if (g_profile) {
-    for (int i = 0; i <= 7; i++) prof(g_ev_f, i, s);
+    launch_finalize_tiles(T, img.ranges, img.tile_order, true, sc.ctrl, list_capacity, stamp, img.status, s);
+    LSR_STAGE("tile_ranges");
   }
-  // P == 0 (rasterize_points.cu:91): the reference returns zero-filled images; blending empty ranges gives
-  // colour = bg, which differs, so reproduce the zero fill.
-  if (P == 0) {
-    const size_t N = (size_t)W * H;
-    LSR_CUDA(cudaMemsetAsync(out_color, 0, 3 * N * sizeof(float), s));
-    if (frame->include_feature) LSR_CUDA(cudaMemsetAsync(out_feature, 0, 3 * N * sizeof(float), s));
-  } else {
-    launch_render_fwd(W, H, img.ranges, LSR_TILE_ORDER ? img.tile_order : nullptr, (const uint32_t*)list, g.rec, frame->bg, frame->include_feature != 0,
-                      img.final_T, img.n_contrib, out_color, out_feature, s);
-    LSR_STAGE("render_fwd");
-  }
+  prof(g_ev_f, 7, s);
+  launch_render_fwd(W, H, img.ranges, img.tile_order, (const uint32_t*)list, g.rec, frame->bg,
+                    frame->include_feature != 0, img.final_T, img.n_contrib, out_color, out_feature, s);
+  LSR_STAGE("render_fwd");
   prof(g_ev_f, 8, s);
+  if (!sync) {
+    launch_poison_outputs(img.status, out_color, 3 * N, frame->include_feature ? out_feature : nullptr, 3 * N, s);
+    if (status_host)
+      LSR_CUDA(cudaMemcpyAsync(status_host, img.status, LSR_STATUS_WORDS * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    LSR_STAGE("status");
+  }
   if (g_profile) g_have_f = true;
+  return LSR_OK;
+}
+
+int lsr_forward(const lsr_frame* frame, const lsr_inputs* in, float* out_color, float* out_feature, int32_t* radii,
+                void* geom, void* image, void* list, int64_t list_capacity, void* scratch, size_t scratch_nbytes,
+                int64_t* num_rendered, void* stream) {
+  return forward_impl(frame, in, out_color, out_feature, radii, geom, image, list, list_capacity, scratch,
+                      scratch_nbytes, num_rendered, true, 0u, nullptr, (cudaStream_t)stream);
+}
+
+int lsr_forward_nosync(const lsr_frame* frame, const lsr_inputs* in, float* out_color, float* out_feature,
+                       int32_t* radii, void* geom, void* image, void* list, int64_t list_capacity, void* scratch,
+                       size_t scratch_nbytes, uint32_t stamp, uint32_t* status_host, void* stream) {
+  if (frame && frame->debug) return fail(LSR_ERR_INVALID, "debug=1 synchronises after every stage: use lsr_forward");
+  return forward_impl(frame, in, out_color, out_feature, radii, geom, image, list, list_capacity, scratch,
+                      scratch_nbytes, nullptr, false, stamp, status_host, (cudaStream_t)stream);
+}
+
+int lsr_forward_status(int32_t width, int32_t height, const void* image, uint32_t* status, void* stream) {
+  if (!image || !status || width <= 0 || height <= 0) return fail(LSR_ERR_INVALID, "bad argument");
+  ImageView img = image_view(const_cast<void*>(image), width, height);
+  LSR_CUDA(cudaMemcpyAsync(status, img.status, LSR_STATUS_WORDS * sizeof(uint32_t), cudaMemcpyDeviceToHost,
+                           (cudaStream_t)stream));
+  LSR_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
   return LSR_OK;
 }
 
@@ -598,7 +659,7 @@ int lsr_forward_feature_level(int32_t P, int32_t width, int32_t height, const in
   GeomView g = geom_view(geom, P);
   ImageView img = image_view(const_cast<void*>(image), width, height);
   launch_refeature_render(P, width, height, radii, language_feature, g.rec, img.ranges,
-                          LSR_TILE_ORDER ? img.tile_order : nullptr, (const uint32_t*)list,
+                          img.tile_order, (const uint32_t*)list,
                           out_feature, s);
   LSR_CUDA(cudaGetLastError());
   return LSR_OK;
@@ -655,7 +716,7 @@ int lsr_backward(const lsr_frame* frame, const lsr_inputs* in, const int32_t* ra
   prof(g_ev_b, 1, s);
   GeomView g = geom_view(const_cast<void*>(geom), P);
   ImageView img = image_view(const_cast<void*>(image), W, H);
-  launch_render_bwd(W, H, img.ranges, LSR_TILE_ORDER ? img.tile_order : nullptr, (const uint32_t*)list, g.rec, frame->bg, frame->include_feature != 0,
+  launch_render_bwd(W, H, img.ranges, img.tile_order, (const uint32_t*)list, g.rec, frame->bg, frame->include_feature != 0,
                     img.final_T, img.n_contrib, dL_dcolor, dL_dfeature, need_mask, gr.dL_dmeans2D, gr.dL_dconic,
                     gr.dL_dopacity, gr.dL_dcolors, gr.dL_dlanguage_feature, s);
   LSR_STAGE("render_bwd");

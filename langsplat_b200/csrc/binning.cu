@@ -20,12 +20,20 @@ namespace {
 // bit pattern are close to uniform, so plain shared atomics rarely collide; the top digit takes few distinct values,
 // so there the lanes holding the same digit are merged first (MATCH.ANY) and one of them adds the group's count.
 constexpr int DW_THREADS = 256;
+// The range of the depth word is only known on the device (ctrl, reduced by the preprocess kernel): every CTA derives
+// lo_min and the width of the span from it, so the host never has to read it back; CTA 0 publishes the width for the
+// sort passes (ctrl[CTRL_DEPTH_BITS]), which skip themselves when their digit lies above it.
 __global__ void __launch_bounds__(DW_THREADS)
-depth_words_kernel(int P, const float* __restrict__ depths, const uint32_t* __restrict__ tiles, uint32_t lo_min,
-                   int id_bits, int passes, int total_bits, uint64_t* __restrict__ words,
+depth_words_kernel(int P, const float* __restrict__ depths, const uint32_t* __restrict__ tiles,
+                   uint32_t* __restrict__ ctrl, int id_bits, uint64_t* __restrict__ words,
                    uint32_t* __restrict__ ghist) {
-  __shared__ uint32_t s_hist[SORT_MAX_PASSES * SORT_BINS];
+  __shared__ uint32_t s_hist[DEPTH_MAX_PASSES * SORT_BINS];
   const int tid = threadIdx.x, lane = tid & 31;
+  const uint32_t lo_min = ~ctrl[CTRL_DEPTH_NEGMIN], lo_max = ctrl[CTRL_DEPTH_MAX];
+  const uint32_t span = lo_max >= lo_min ? lo_max - lo_min : 0u;
+  const int total_bits = max(1, 32 - __clz((int)span));
+  const int passes = (total_bits + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
+  if (blockIdx.x == 0 && tid == 0) ctrl[CTRL_DEPTH_BITS] = (uint32_t)total_bits;
   for (int j = tid; j < passes * SORT_BINS; j += DW_THREADS) s_hist[j] = 0;
   __syncthreads();
   // four elements per thread and iteration, all eight loads issued before the first use
@@ -47,8 +55,7 @@ depth_words_kernel(int P, const float* __restrict__ depths, const uint32_t* __re
       if (ok) words[idx] = ((uint64_t)d << id_bits) | (uint64_t)(uint32_t)idx;
       for (int p = 0; p < passes; p++) {
         const int shift = p * SORT_RADIX_BITS;
-        const int bits = min(SORT_RADIX_BITS, total_bits - shift);
-        const uint32_t dg = (d >> shift) & ((1u << bits) - 1);
+        const uint32_t dg = (d >> shift) & (SORT_BINS - 1);  // bits above the span are zero
         if (p + 1 < passes) {
           if (ok) atomicAdd(&s_hist[p * SORT_BINS + dg], 1u);
         } else {
@@ -259,6 +266,162 @@ duplicate_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// K2'+K3' fused: duplication that computes its own offsets.  A block takes 256 consecutive Gaussians of the depth
+// order (dynamic ticket, so blocks start in order), scans their tile counts, obtains its base from the blocks before
+// it by decoupled look-back (one warp, 32 predecessors per poll), and emits its instances: no scan kernel, no
+// offsets round trip through HBM, no binary search per slot.
+//
+// Emission goes through shared memory in chunks of DUP_CHUNK slots: every thread writes the words of ITS Gaussian that
+// fall into the chunk (row-major walk of the rect with two counters: no division in the loop), then the block copies
+// the chunk out with fully coalesced 8-byte stores and counts the tile sort's digits on the way.  Gaussians with more
+// than DUP_BIG instances would make one lane loop alone, so the block emits those cooperatively (slot -> row, column
+// by one division per slot).
+//
+// Nothing here needs the instance count on the host: stores are clipped at `capacity`, and an overflow raises
+// ERR_OVERFLOW in ctrl (the forward then poisons its outputs, api.cu).
+// ------------------------------------------------------------------------------------------------------------
+constexpr int DUP_CHUNK = 2048;  // staged words per chunk (16 KB)
+constexpr uint32_t DUP_BIG = 512;
+
+__global__ void __launch_bounds__(DUP_BLOCK)
+dup_scan_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const int32_t* __restrict__ radii,
+                const GeomRec* __restrict__ rec, uint32_t* __restrict__ offsets, uint64_t* __restrict__ words,
+                uint32_t capacity, int id_bits, int passes, volatile uint64_t* __restrict__ status,
+                uint32_t* __restrict__ ctrl, uint32_t* __restrict__ ghist) {
+  __shared__ __align__(16) uint64_t s_words[DUP_CHUNK];
+  __shared__ uint32_t s_hist[SORT_MAX_PASSES * SORT_BINS];
+  __shared__ uint32_t s_warp[DUP_BLOCK / 32];
+  __shared__ uint32_t s_blk, s_base, s_nbig;
+  __shared__ uint4 s_bigrec[DUP_BLOCK];  // Gaussians emitted cooperatively: block-local start, count, width, y0<<16|x0
+  __shared__ uint32_t s_biggid[DUP_BLOCK];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int j = tid; j < passes * SORT_BINS; j += DUP_BLOCK) s_hist[j] = 0;
+  if (blockIdx.x == 0 && tid == 0 && ctrl[CTRL_NUM_RENDERED] > capacity) atomicOr(&ctrl[CTRL_ERROR], ERR_OVERFLOW);
+  const int nblocks = (P + DUP_BLOCK - 1) / DUP_BLOCK;
+  for (;;) {
+    __syncthreads();  // previous block's shared state is no longer read
+    if (tid == 0) { s_blk = atomicAdd(&ctrl[CTRL_DUP_TICKET], 1u); s_nbig = 0; }
+    __syncthreads();
+    const uint32_t blk = s_blk;
+    if (blk >= (uint32_t)nblocks) break;
+    const int i = (int)blk * DUP_BLOCK + tid;
+    uint32_t x0 = 0, y0 = 0, x1 = 0, y1 = 0, gid = 0;
+    int radius = 0;
+    if (i < P) {
+      gid = __ldg(perm + i);
+      radius = __ldg(radii + gid);
+    }
+    if (radius > 0) {
+      const float2 xy = __ldg(reinterpret_cast<const float2*>(rec + gid));
+      get_rect(xy.x, xy.y, radius, gx, gy, x0, y0, x1, y1);
+    }
+    const uint32_t w = x1 - x0;
+    const uint32_t cnt = w * (y1 - y0);  // == tiles_touched of this Gaussian
+    // ---- block scan of the counts ----
+    uint32_t inc = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t n = __shfl_up_sync(0xffffffffu, inc, d);
+      if (lane >= d) inc += n;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    uint32_t warp_prefix = 0, block_sum = 0;
+#pragma unroll
+    for (int k = 0; k < DUP_BLOCK / 32; k++) {
+      const uint32_t x = s_warp[k];
+      if (k < warp) warp_prefix += x;
+      block_sum += x;
+    }
+    // ---- base of the block: decoupled look-back by warp 0 (status word: [63:62] flag, [31:0] value) ----
+    if (warp == 0) {
+      if (lane == 0) status[blk] = (blk == 0 ? FLAG_INC : FLAG_AGG) | block_sum;
+      uint32_t prefix = 0;
+      if (blk > 0) {
+        int look = (int)blk - 1;
+        while (true) {
+          const int j = look - lane;
+          uint64_t st = FLAG_INC;  // virtual zero prefix before block 0
+          if (j >= 0) {
+            do { st = status[j]; } while ((st & FLAG_MASK) == 0);
+          }
+          const uint32_t inc_mask = __ballot_sync(0xffffffffu, (st & FLAG_MASK) == FLAG_INC);
+          const int first_inc = inc_mask ? __ffs(inc_mask) - 1 : 31;
+          uint32_t val = (lane <= first_inc) ? (uint32_t)st : 0u;
+#pragma unroll
+          for (int d = 16; d > 0; d >>= 1) val += __shfl_xor_sync(0xffffffffu, val, d);
+          prefix += val;
+          if (inc_mask) break;
+          look -= 32;
+        }
+        if (lane == 0) status[blk] = FLAG_INC | (uint64_t)(prefix + block_sum);
+      }
+      if (lane == 0) s_base = prefix;
+    }
+    const uint32_t lend = warp_prefix + inc;  // block-local [lstart, lend) of this thread's instances
+    const uint32_t lstart = lend - cnt;
+    const uint32_t origin = (y0 << 16) | x0;
+    if (cnt > DUP_BIG) {
+      const uint32_t k = atomicAdd(&s_nbig, 1u);
+      s_bigrec[k] = make_uint4(lstart, cnt, w, origin);
+      s_biggid[k] = gid;
+    }
+    __syncthreads();
+    const uint32_t base = s_base, nbig = s_nbig;
+    if (i < P) offsets[i] = base + lend;  // inclusive, as the stand-alone scan wrote it
+    // ---- emission, DUP_CHUNK slots at a time ----
+    for (uint32_t c0 = 0; c0 < block_sum; c0 += DUP_CHUNK) {
+      const uint32_t c1 = min(c0 + (uint32_t)DUP_CHUNK, block_sum);
+      if (cnt != 0u && cnt <= DUP_BIG && lstart < c1 && lend > c0) {
+        const uint32_t a = max(lstart, c0), b = min(lend, c1);
+        uint32_t r = a - lstart;
+        uint32_t row = 0, col = r;
+        if (r != 0u) { row = r / w; col = r - row * w; }  // only for a Gaussian cut by the chunk boundary
+        uint32_t tile = (y0 + row) * (uint32_t)gx + x0 + col;
+        for (uint32_t sl = a; sl < b; sl++) {
+          s_words[sl - c0] = ((uint64_t)tile << id_bits) | (uint64_t)gid;
+          col++; tile++;
+          if (col == w) { col = 0; tile += (uint32_t)gx - w; }
+        }
+      }
+      for (uint32_t bi = 0; bi < nbig; bi++) {  // the block's big Gaussians, all threads together
+        const uint4 br = s_bigrec[bi];
+        const uint32_t a = max(br.x, c0), b = min(br.x + br.y, c1);
+        const uint32_t bgid = s_biggid[bi];
+        for (uint32_t sl = a + tid; sl < b; sl += DUP_BLOCK) {
+          const uint32_t r = sl - br.x, row = r / br.z, col = r - row * br.z;
+          const uint32_t tile = ((br.w >> 16) + row) * (uint32_t)gx + (br.w & 0xffffu) + col;
+          s_words[sl - c0] = ((uint64_t)tile << id_bits) | (uint64_t)bgid;
+        }
+      }
+      __syncthreads();
+      const uint32_t n = c1 - c0;
+      for (uint32_t k0 = 0; k0 < n; k0 += DUP_BLOCK) {  // CTA-uniform trip count (warp-wide votes below)
+        const uint32_t k = k0 + tid;
+        const uint32_t o = base + c0 + k;
+        const bool ok = k < n && o < capacity;  // clipped instances are neither stored nor counted
+        const uint64_t word = ok ? s_words[k] : 0ull;
+        if (ok) words[o] = word;
+        const uint32_t tile = (uint32_t)(word >> id_bits);
+        // digits of the tile id for every pass of the tile sort.  Lowest digit: consecutive slots hold consecutive
+        // tiles, so plain shared atomics rarely collide.  Higher digits: a warp's slots mostly share one value, so the
+        // lanes holding the same digit are merged first and one of them adds the group's count.
+        if (ok) atomicAdd(&s_hist[tile & (SORT_BINS - 1)], 1u);
+        for (int p = 1; p < passes; p++) {
+          const uint32_t d = ok ? ((tile >> (p * SORT_RADIX_BITS)) & (SORT_BINS - 1)) : 0xffffffffu;
+          const uint32_t peers = __match_any_sync(0xffffffffu, d);
+          if (ok && (peers & ((1u << lane) - 1)) == 0) atomicAdd(&s_hist[p * SORT_BINS + d], (uint32_t)__popc(peers));
+        }
+      }
+      __syncthreads();
+    }
+  }
+  // (all threads left the loop together after the barrier that published s_blk)
+  for (int j = tid; j < passes * SORT_BINS; j += DUP_BLOCK)
+    if (s_hist[j]) atomicAdd(&ghist[j], s_hist[j]);
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // K5': identifyTileRanges (rasterizer_impl.cu:116-138).  ranges must be zero on entry (cudaMemset, :313).
 // ------------------------------------------------------------------------------------------------------------
 // The blend kernels' CTA -> tile map: tiles by descending list length, so that the long-running quadrants start first
@@ -276,7 +439,11 @@ __device__ __forceinline__ uint32_t order_bucket(uint2 r) {
   return 255u - key;
 }
 
-__device__ __forceinline__ void order_tiles(int T, const uint2* __restrict__ ranges, uint32_t* __restrict__ order,
+// ENC: the ranges come straight out of the last sort pass (radix_sort.cu), which marks them with min-operations on
+// (start, ~end) over a 0xFF-filled array; they are decoded in place here — (0, 0) for a tile nobody touched, as the
+// reference's zero-initialised ranges read (rasterizer_impl.cu:313) — by the thread that then buckets them.
+template <bool ENC>
+__device__ __forceinline__ void order_tiles(int T, uint2* __restrict__ ranges, uint32_t* __restrict__ order,
                                             uint32_t* s_cnt) {
   const int tid = threadIdx.x;
   if (tid < 256) s_cnt[tid] = 0;
@@ -287,7 +454,15 @@ __device__ __forceinline__ void order_tiles(int T, const uint2* __restrict__ ran
 #pragma unroll
     for (int k = 0; k < CH; k++) {
       const int t = base + tid + k * 1024;
-      bucket[k] = t < T ? order_bucket(__ldg(ranges + t)) : 256u;
+      bucket[k] = 256u;
+      if (t < T) {
+        uint2 r = ranges[t];
+        if (ENC) {
+          r = r.x == 0xffffffffu ? make_uint2(0u, 0u) : make_uint2(r.x, ~r.y);
+          ranges[t] = r;
+        }
+        bucket[k] = order_bucket(r);
+      }
     }
 #pragma unroll
     for (int k = 0; k < CH; k++)  // (warp-aggregating these with MATCH.ANY was measured slower)
@@ -314,7 +489,7 @@ __device__ __forceinline__ void order_tiles(int T, const uint2* __restrict__ ran
 #pragma unroll
     for (int k = 0; k < CH; k++) {
       const int t = base + tid + k * 1024;
-      bucket[k] = t < T ? order_bucket(__ldg(ranges + t)) : 256u;
+      bucket[k] = t < T ? order_bucket(ranges[t]) : 256u;  // (written above by this same thread when ENC)
     }
 #pragma unroll
     for (int k = 0; k < CH; k++)
@@ -323,9 +498,41 @@ __device__ __forceinline__ void order_tiles(int T, const uint2* __restrict__ ran
 }
 
 __global__ void __launch_bounds__(1024)
-tile_order_kernel(int T, const uint2* __restrict__ ranges, uint32_t* __restrict__ order) {
+tile_order_kernel(int T, uint2* __restrict__ ranges, uint32_t* __restrict__ order) {
   __shared__ uint32_t s_cnt[256];
-  order_tiles(T, ranges, order, s_cnt);
+  order_tiles<false>(T, ranges, order, s_cnt);
+}
+
+// Last binning step of a forward: decode the ranges, order the tiles, and keep what the device found out about this
+// frame (instance count, error flags, depth range) with the call's own state, where lsr_forward_status / the
+// asynchronous host copy pick it up.
+__global__ void __launch_bounds__(1024)
+finalize_tiles_kernel(int T, uint2* __restrict__ ranges, uint32_t* __restrict__ order, bool encoded,
+                      const uint32_t* __restrict__ ctrl, uint32_t capacity, uint32_t stamp,
+                      uint32_t* __restrict__ status) {
+  __shared__ uint32_t s_cnt[256];
+  if (threadIdx.x == 0) {
+    status[LSR_STATUS_NUM_RENDERED] = ctrl[CTRL_NUM_RENDERED];
+    status[LSR_STATUS_FLAGS] = ctrl[CTRL_ERROR];
+    status[LSR_STATUS_DEPTH_MIN] = ~ctrl[CTRL_DEPTH_NEGMIN];
+    status[LSR_STATUS_DEPTH_MAX] = ctrl[CTRL_DEPTH_MAX];
+    status[LSR_STATUS_CAPACITY] = capacity;
+    status[LSR_STATUS_STAMP] = stamp;
+  }
+  if (encoded) order_tiles<true>(T, ranges, order, s_cnt);
+  else order_tiles<false>(T, ranges, order, s_cnt);
+}
+
+// An instance list that did not fit leaves incomplete images behind: overwrite them with NaN so that they can never
+// pass for a render (asynchronous forward only; the synchronous one returns LSR_ERR_CAPACITY before blending).
+__global__ void __launch_bounds__(256)
+poison_outputs_kernel(const uint32_t* __restrict__ status, float* __restrict__ a, size_t na, float* __restrict__ b,
+                      size_t nb) {
+  if ((status[LSR_STATUS_FLAGS] & ERR_OVERFLOW) == 0u) return;
+  const float nan = __int_as_float(0x7fc00000);
+  const size_t stride = (size_t)gridDim.x * 256;
+  for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < na; i += stride) a[i] = nan;
+  for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < nb; i += stride) b[i] = nan;
 }
 
 // Four consecutive words per thread (two 128-bit loads), one extra load for the predecessor of the first.
@@ -376,13 +583,23 @@ unpack_keys_kernel(uint32_t L, const uint64_t* __restrict__ words, const float* 
 
 }  // namespace
 
-void launch_depth_words(int P, const float* depths, const uint32_t* tiles, const SortPlan& plan, uint64_t* words,
+void launch_depth_words(int P, const float* depths, const uint32_t* tiles, uint32_t* ctrl, int id_bits, uint64_t* words,
                         uint32_t* ghist, cudaStream_t s) {
   if (P <= 0) return;
   const int nblocks = (P + DW_THREADS * 4 - 1) / (DW_THREADS * 4);
   const int grid = nblocks < 148 * 4 ? nblocks : 148 * 4;  // persistent CTAs: each flushes passes*256 global atomics
-  depth_words_kernel<<<grid, DW_THREADS, 0, s>>>(P, depths, tiles, plan.lo_min, plan.id_bits, plan.passes,
-                                                 plan.total_bits, words, ghist);
+  depth_words_kernel<<<grid, DW_THREADS, 0, s>>>(P, depths, tiles, ctrl, id_bits, words, ghist);
+  count_launch();
+}
+
+void launch_dup_scan(int P, int grid_x, int grid_y, const uint32_t* perm, const int32_t* radii, GeomView g,
+                     uint64_t* words, int64_t capacity, const SortPlan& plan, uint64_t* status, uint32_t* ctrl,
+                     uint32_t* ghist, cudaStream_t s) {
+  if (P <= 0) return;
+  const int nblocks = (P + DUP_BLOCK - 1) / DUP_BLOCK;
+  const int grid = nblocks < 148 * 6 ? nblocks : 148 * 6;  // persistent CTAs (29 KB of shared memory each)
+  dup_scan_kernel<<<grid, DUP_BLOCK, 0, s>>>(P, grid_x, grid_y, perm, radii, g.rec, g.offsets, words,
+                                               (uint32_t)capacity, plan.id_bits, plan.passes, status, ctrl, ghist);
   count_launch();
 }
 
@@ -410,9 +627,20 @@ void launch_tile_ranges(int64_t R, const uint64_t* keys, int tile_shift, uint2* 
   count_launch();
 }
 
-void launch_tile_order(int T, const uint2* ranges, uint32_t* order, cudaStream_t s) {
+void launch_tile_order(int T, uint2* ranges, uint32_t* order, cudaStream_t s) {
   if (T <= 0) return;
   tile_order_kernel<<<1, 1024, 0, s>>>(T, ranges, order);
+  count_launch();
+}
+
+void launch_finalize_tiles(int T, uint2* ranges, uint32_t* order, bool encoded, const uint32_t* ctrl,
+                           int64_t capacity, uint32_t stamp, uint32_t* status, cudaStream_t s) {
+  finalize_tiles_kernel<<<1, 1024, 0, s>>>(T, ranges, order, encoded, ctrl, (uint32_t)capacity, stamp, status);
+  count_launch();
+}
+
+void launch_poison_outputs(const uint32_t* status, float* a, size_t na, float* b, size_t nb, cudaStream_t s) {
+  poison_outputs_kernel<<<148 * 2, 256, 0, s>>>(status, a, a ? na : 0, b, b ? nb : 0);
   count_launch();
 }
 

@@ -47,6 +47,7 @@ struct ImageView {
   uint32_t* n_contrib;
   uint2* ranges;
   uint32_t* tile_order;  // tiles by descending list length: the blend kernels' CTA -> tile map (heaviest first)
+  uint32_t* status;      // [LSR_STATUS_WORDS] what the forward found out on the device (lsr_api.h), kept per call
 };
 
 __host__ __device__ inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
@@ -92,12 +93,13 @@ inline ImageView image_view(void* base, int W, int H) {
   v.n_contrib = (uint32_t*)p;  p += align_up(N * 4);
   v.ranges = (uint2*)p;        p += align_up(T * 8);
   v.tile_order = (uint32_t*)p; p += align_up(T * 4);
+  v.status = (uint32_t*)p;     p += 256;
   return v;
 }
 inline size_t image_bytes(int W, int H) {
   size_t N = (size_t)W * H;
   size_t T = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
-  return 2 * align_up(N * 4) + align_up(T * 8) + align_up(T * 4) + 256;
+  return 2 * align_up(N * 4) + align_up(T * 8) + align_up(T * 4) + 256 + 256;
 }
 
 // ---- radix sort geometry (radix_sort.cu) ----
@@ -136,9 +138,12 @@ constexpr int SCAN_ITEMS = 8;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 inline size_t scan_nblocks(int P) { return (size_t)((P + SCAN_TILE - 1) / SCAN_TILE) + 1; }
 
+constexpr int DUP_BLOCK = 256;  // Gaussians per block of the duplication kernel (binning.cu)
+inline size_t dup_nblocks(int P) { return (size_t)((P + DUP_BLOCK - 1) / DUP_BLOCK) + 1; }
+
 struct ScratchView {
   uint32_t* ctrl;  // [64] control words: [0] num_rendered, [1] scan ticket, [2] error flags
-  uint64_t* scan_status;  // [scan_nblocks]
+  uint64_t* scan_status;  // [max(scan_nblocks, dup_nblocks)] look-back words of the offset scan
   uint64_t* dwords_a;     // [P] depth-order sort of the Gaussians: packed (depth | index) words, ping
   uint64_t* dwords_b;     // [P] pong (sorted result)
   uint32_t* perm;         // [P] Gaussian indices in depth order
@@ -154,7 +159,7 @@ inline ScratchView scratch_view(void* base, int P, int64_t cap) {
   size_t c = (size_t)(cap > 0 ? cap : 0);
   size_t n = (size_t)(P > 0 ? P : 0);
   s.ctrl = (uint32_t*)p;          p += 256;
-  s.scan_status = (uint64_t*)p;   p += align_up(scan_nblocks(P) * 8);
+  s.scan_status = (uint64_t*)p;   p += align_up(dup_nblocks(P) * 8);
   s.head_zero_bytes = (size_t)(p - (char*)base);
   s.dwords_a = (uint64_t*)p;      p += align_up(n * 8);
   s.dwords_b = (uint64_t*)p;      p += align_up(n * 8);
@@ -168,12 +173,16 @@ inline ScratchView scratch_view(void* base, int P, int64_t cap) {
 inline size_t scratch_bytes(int P, int64_t cap) {
   size_t c = (size_t)(cap > 0 ? cap : 0);
   size_t n = (size_t)(P > 0 ? P : 0);
-  return 256 + align_up(scan_nblocks(P) * 8) + 2 * align_up(n * 8) + align_up(n * 4) + sort_work_bytes((int64_t)n) +
+  return 256 + align_up(dup_nblocks(P) * 8) + 2 * align_up(n * 8) + align_up(n * 4) + sort_work_bytes((int64_t)n) +
          2 * align_up(c * 8) + sort_work_bytes(cap) + 256;
 }
 
 // ctrl words (zeroed at the start of every forward).  DEPTH_NEGMIN holds max(~bits) so that zero-init works.
-enum CtrlWord { CTRL_NUM_RENDERED = 0, CTRL_SCAN_TICKET = 1, CTRL_ERROR = 2, CTRL_DEPTH_NEGMIN = 3, CTRL_DEPTH_MAX = 4 };
+// CTRL_DEPTH_BITS: width of the depth word's span, published by depth_words_kernel for the depth-sort passes.
+enum CtrlWord { CTRL_NUM_RENDERED = 0, CTRL_SCAN_TICKET = 1, CTRL_ERROR = 2, CTRL_DEPTH_NEGMIN = 3, CTRL_DEPTH_MAX = 4,
+                CTRL_DEPTH_BITS = 5, CTRL_DUP_TICKET = 6 };
+constexpr uint32_t ERR_PREFILTERED = 1u, ERR_OVERFLOW = 2u;  // bits of ctrl[CTRL_ERROR] (= LSR_STATUS_FLAG_*)
+constexpr int DEPTH_MAX_PASSES = 4;  // a 32-bit depth word in 8-bit digits
 
 // Which bits the sort has to look at: digits are taken from (hi << lo_bits) | (lo - lo_min)  (radix_sort.cu).
 // packed: the Gaussian id (id_bits) rides in the low bits of the 64-bit word, above it the compacted key; the sort
@@ -193,8 +202,18 @@ void launch_preprocess_fwd(const lsr_frame& f, const lsr_inputs& in, float focal
                            GeomView g, uint32_t* ctrl, cudaStream_t s);
 // packed (depth - lo_min | index) words of the P Gaussians, input of the depth-order sort, and that sort's digit
 // histograms (ghist must be zero: sort_prepare)
-void launch_depth_words(int P, const float* depths, const uint32_t* tiles, const SortPlan& plan, uint64_t* words,
+// (the range of the depth word is read from ctrl on the device; its width is published in ctrl[CTRL_DEPTH_BITS])
+void launch_depth_words(int P, const float* depths, const uint32_t* tiles, uint32_t* ctrl, int id_bits, uint64_t* words,
                         uint32_t* ghist, cudaStream_t s);
+// duplication fused with the scan of the tile counts (look-back words in `status`, zero on entry; ticket in ctrl)
+void launch_dup_scan(int P, int grid_x, int grid_y, const uint32_t* perm, const int32_t* radii, GeomView g,
+                     uint64_t* words, int64_t capacity, const SortPlan& plan, uint64_t* status, uint32_t* ctrl,
+                     uint32_t* ghist, cudaStream_t s);
+// decodes the ranges marked by the last sort pass (encoded), orders the tiles, stores the frame's status words
+void launch_finalize_tiles(int T, uint2* ranges, uint32_t* order, bool encoded, const uint32_t* ctrl,
+                           int64_t capacity, uint32_t stamp, uint32_t* status, cudaStream_t s);
+// NaN-fills a[0..na) and b[0..nb) if the status words report an instance-list overflow
+void launch_poison_outputs(const uint32_t* status, float* a, size_t na, float* b, size_t nb, cudaStream_t s);
 // inclusive scan of tiles[perm[i]] (perm == nullptr: of tiles[i], which also publishes the total in ctrl)
 void launch_scan_tiles(int P, const uint32_t* tiles, const uint32_t* perm, uint32_t* offsets, uint64_t* status,
                        uint32_t* ctrl, cudaStream_t s);
@@ -203,15 +222,28 @@ void launch_duplicate(int P, int grid_x, int grid_y, const uint32_t* perm, const
 // tile id of a sorted word = word >> tile_shift (32 for reference-format keys)
 void launch_tile_ranges(int64_t R, const uint64_t* keys, int tile_shift, uint2* ranges, cudaStream_t s);
 // order[] = the T tiles by descending list length (counting sort, one CTA); any R, also 0
-void launch_tile_order(int T, const uint2* ranges, uint32_t* order, cudaStream_t s);
+void launch_tile_order(int T, uint2* ranges, uint32_t* order, cudaStream_t s);
 // reference-format keys (tile << 32 | depth bits) from the sorted instance words (tests / debugging)
 void launch_unpack_keys(int64_t R, const uint64_t* words, const float* depths, uint64_t* keys, int id_bits,
                         cudaStream_t s);
 // hist_ready: the per-pass digit histograms are already in the work buffer (sort_prepare + duplication kernel)
 void sort_prepare(void* work, int64_t n, const SortPlan& pl, cudaStream_t s);
+// What only the device knows when the forward does not read anything back (all optional):
+//  n_dev     element count (the `n` argument is then the bound the launch geometry and the workspace are sized for);
+//  bits_dev  width of the packed key: max_passes passes are launched, those above the width return at once, the last
+//            one below it writes the ids (the sorted words end up in keys_out OR keys_tmp: consume the ids only);
+//  ranges    instance sort: the last pass marks the tile ranges (0xFF-filled on entry, decoded by finalize_tiles),
+//            tile id = word >> tile_shift.
+struct SortDyn {
+  const uint32_t* n_dev = nullptr;
+  const uint32_t* bits_dev = nullptr;
+  int max_passes = 0;
+  uint2* ranges = nullptr;
+  int tile_shift = 0;
+};
 int sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
                uint64_t* keys_tmp, uint32_t* vals_tmp, int64_t n, const SortPlan& pl, bool hist_ready, void* work,
-               cudaStream_t s);
+               cudaStream_t s, const SortDyn* dyn = nullptr);
 void launch_render_fwd(int W, int H, const uint2* ranges, const uint32_t* order, const uint32_t* list, const GeomRec* rec, const float* bg,
                        bool include_feature, float* final_T, uint32_t* n_contrib, float* out_color,
                        float* out_feature, cudaStream_t s);

@@ -27,6 +27,10 @@ namespace lsr {
 
 namespace {
 
+#ifndef LSR_SORT_LB_WIN
+#define LSR_SORT_LB_WIN 16
+#endif
+constexpr int LB_WIN = LSR_SORT_LB_WIN;
 constexpr uint32_t LB_AGG = 1u << 30, LB_INC = 2u << 30, LB_FLAG = 3u << 30, LB_VAL = ~LB_FLAG;
 constexpr int WARPS = SORT_THREADS / 32;
 constexpr int BITS = SORT_RADIX_BITS;
@@ -105,6 +109,14 @@ __device__ __forceinline__ uint32_t pass_digit(uint64_t key, const PassDigit& pd
   return (shr32(lo, pd.s1) | shl32(hi, pd.s2) | shr32(hi, pd.s3)) & pd.mask;
 }
 
+struct SortDynArgs {  // per-launch view of SortDyn (common.cuh)
+  const uint32_t* n_dev;
+  const uint32_t* bits_dev;
+  uint32_t shift;
+  uint2* ranges;
+  int tile_shift;
+};
+
 // Lanes of the warp holding the same digit, from NB ballots.  MATCH.ANY would be one instruction, but on B200 its cost
 // grows with the number of DISTINCT values in the warp (profiles/tools/ubench_rank.cu: 5 SM-cycles per warp
 // instruction when all lanes agree, 66 when all differ — and radix digits mostly differ); 8 ballots cost ~14.
@@ -138,9 +150,18 @@ __device__ __forceinline__ uint32_t sw(uint32_t p) { return p ^ ((p >> 4) & 15u)
 template <int NB, bool PAIRS, int ITEMS>
 __global__ void __launch_bounds__(SORT_THREADS, 4)
 onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, const uint32_t* __restrict__ vin,
-                uint32_t* __restrict__ vout, uint32_t n, uint32_t* __restrict__ ticket,
+                uint32_t* __restrict__ vout, uint32_t n_bound, uint32_t* __restrict__ ticket,
                 volatile uint32_t* __restrict__ lookback, const uint32_t* __restrict__ ghist, PassDigit pd,
-                uint32_t* __restrict__ ids_out, uint32_t id_mask) {
+                uint32_t* __restrict__ ids_out, uint32_t id_mask, SortDynArgs dyn) {
+  // Sizes that only the device knows (the forward never reads them back): the element count, and for the depth
+  // ordering the width of the key — a pass whose digit lies above it has nothing to do, and the last pass that has
+  // emits the ids.
+  if (dyn.bits_dev != nullptr) {
+    const uint32_t width = __ldg(dyn.bits_dev);
+    if (dyn.shift >= width) return;
+    if (dyn.shift + BITS < width) ids_out = nullptr;
+  }
+  const uint32_t n = dyn.n_dev != nullptr ? min(__ldg(dyn.n_dev), n_bound) : n_bound;
   extern __shared__ __align__(16) unsigned char smem[];
   uint64_t* s_keys = reinterpret_cast<uint64_t*>(smem);
   uint32_t* s_vals = reinterpret_cast<uint32_t*>(smem);  // reuses the key region after the keys are written out
@@ -279,21 +300,24 @@ onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, c
     volatile uint32_t* mine = lookback + (size_t)tile * BINS + t;
     uint32_t prefix = 0;
     if (tile != 0) {
-      // look back four tiles at a time (independent loads in flight), consume them nearest first
+      // look back LB_WIN tiles at a time (independent loads in flight), consume them nearest first.  A sort that fits
+      // one wave (the depth ordering: 245 tiles at C2) publishes all its aggregates at about the same moment, so a
+      // tile far down the chain sums hundreds of them: the window keeps that from being one L2 round trip each.
       int k = (int)tile - 1;
       bool done = false;
       while (!done) {
-        uint32_t v[4];
+        uint32_t v[LB_WIN];
 #pragma unroll
-        for (int j = 0; j < 4; j++) v[j] = (k - j >= 0) ? lookback[(size_t)(k - j) * BINS + t] : (uint32_t)(2u << 30);
+        for (int j = 0; j < LB_WIN; j++)
+          v[j] = (k - j >= 0) ? lookback[(size_t)(k - j) * BINS + t] : (uint32_t)(2u << 30);
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
+        for (int j = 0; j < LB_WIN; j++) {
           if (done) break;
           while ((v[j] & LB_FLAG) == 0) v[j] = lookback[(size_t)(k - j) * BINS + t];
           prefix += v[j] & LB_VAL;
           if ((v[j] & LB_FLAG) == LB_INC) done = true;
         }
-        k -= 4;
+        k -= LB_WIN;
       }
       *mine = LB_INC | (prefix + vcnt);
     }
@@ -301,14 +325,40 @@ onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, c
   }
 
   __syncthreads();
+  // Tile ranges straight out of the last pass of the instance sort (replaces identifyTileRanges,
+  // rasterizer_impl.cu:116-138, and its extra sweep over the sorted list).  Neighbours in the CTA-sorted order that
+  // share the digit are neighbours in the output, so a change of tile between them IS a range boundary: plain stores of
+  // (start, ~end).  The first / last element of the CTA's chunk of a bin cannot see its neighbour in another CTA's
+  // chunk; it offers its own position with atomicMin, and the true boundary — the smallest start, the smallest ~end —
+  // wins whichever order the writes land in.  `ranges` is 0xFF-filled on entry and decoded by finalize_tiles_kernel.
+  auto mark_range = [&](uint32_t p, uint64_t k, uint32_t dg, uint32_t g) {
+    const uint32_t tile = (uint32_t)(k >> dyn.tile_shift);
+    if (p == 0) {
+      atomicMin(&dyn.ranges[tile].x, g);
+    } else {
+      const uint32_t ptile = (uint32_t)(s_keys[sw(p - 1)] >> dyn.tile_shift);
+      const uint32_t pdg = s_dig[sw(p - 1)];
+      if (pdg != dg) {
+        atomicMin(&dyn.ranges[tile].x, g);
+        atomicMin(&dyn.ranges[ptile].y, ~(s_gofs[pdg] + p));  // one past the predecessor's output position
+      } else if (ptile != tile) {
+        dyn.ranges[tile].x = g;
+        dyn.ranges[ptile].y = ~g;
+      }
+    }
+    if (p == valid - 1) atomicMin(&dyn.ranges[tile].y, ~(g + 1u));
+  };
+  const bool marking = !PAIRS && dyn.ranges != nullptr;
   if (full) {
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
       const uint32_t p = tid + i * SORT_THREADS;
       const uint64_t k = s_keys[sw(p)];
-      const uint32_t g = s_gofs[s_dig[sw(p)]] + p;
+      const uint32_t dg = s_dig[sw(p)];
+      const uint32_t g = s_gofs[dg] + p;
       kout[g] = k;
       if (!PAIRS && ids_out != nullptr) ids_out[g] = (uint32_t)k & id_mask;
+      if (marking) mark_range(p, k, dg, g);
     }
   } else {
 #pragma unroll
@@ -316,9 +366,11 @@ onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, c
       const uint32_t p = tid + i * SORT_THREADS;
       if (p < valid) {
         const uint64_t k = s_keys[sw(p)];
-        const uint32_t g = s_gofs[s_dig[sw(p)]] + p;
+        const uint32_t dg = s_dig[sw(p)];
+        const uint32_t g = s_gofs[dg] + p;
         kout[g] = k;
         if (!PAIRS && ids_out != nullptr) ids_out[g] = (uint32_t)k & id_mask;
+        if (marking) mark_range(p, k, dg, g);
       }
     }
   }
@@ -343,7 +395,7 @@ onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, c
 }
 
 using OnesweepFn = void (*)(const uint64_t*, uint64_t*, const uint32_t*, uint32_t*, uint32_t, uint32_t*,
-                            volatile uint32_t*, const uint32_t*, PassDigit, uint32_t*, uint32_t);
+                            volatile uint32_t*, const uint32_t*, PassDigit, uint32_t*, uint32_t, SortDynArgs);
 template <bool PAIRS, int ITEMS>
 OnesweepFn onesweep_for_bits_t(int nb) {
   switch (nb) {
@@ -419,7 +471,7 @@ void sort_prepare(void* work, int64_t n, const SortPlan& pl, cudaStream_t s) {
 
 int sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
                uint64_t* keys_tmp, uint32_t* vals_tmp, int64_t n, const SortPlan& pl, bool hist_ready, void* work,
-               cudaStream_t s) {
+               cudaStream_t s, const SortDyn* dyn) {
   if (n <= 0) return 0;
   SortWork w = sort_work_view(work, n);
   const int items = sort_items_for(n);
@@ -445,14 +497,19 @@ int sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_
                                                          pl.packed ? pl.id_bits : -1, w.hist);
     count_launch();
   }
+  // Key width known on the device only (dyn->bits_dev, packed words): launch the worst-case number of passes; those
+  // above the width return at once, the last one below it emits the ids.  The words then end up in keys_out or
+  // keys_tmp depending on that width — such callers consume the ids only.
+  const bool dyn_width = dyn != nullptr && dyn->bits_dev != nullptr;
+  const int passes = dyn_width ? dyn->max_passes : pl.passes;
   const uint64_t* ksrc = keys_in;
   const uint32_t* vsrc = vals_in;
-  for (int p = 0; p < pl.passes; p++) {
-    const bool to_out = ((pl.passes - 1 - p) & 1) == 0;
+  for (int p = 0; p < passes; p++) {
+    const bool to_out = dyn_width ? (p & 1) == 0 : ((passes - 1 - p) & 1) == 0;
     uint64_t* kdst = to_out ? keys_out : keys_tmp;
     uint32_t* vdst = to_out ? vals_out : vals_tmp;
     const int shift = p * BITS;
-    const int bits = std::min(BITS, pl.total_bits - shift);
+    const int bits = dyn_width ? BITS : std::min(BITS, pl.total_bits - shift);
     // d = (((lo - lo_min) >> s1) | (hi << s2) | (hi >> s3)) & mask of the compacted key (hi << lo_bits) | (lo - lo_min)
     PassDigit pd;
     pd.lo_min = pl.lo_min;
@@ -469,17 +526,24 @@ int sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_
       pd.s2 = (shift < pl.lo_bits && pl.lo_bits - shift < 32) ? (uint32_t)(pl.lo_bits - shift) : 32u;
       pd.s3 = shift >= pl.lo_bits ? (uint32_t)std::min(shift - pl.lo_bits, 32) : 32u;
     }
-    const bool last = p == pl.passes - 1;
-    const bool depth_only = shift + bits <= pl.lo_bits && bits == BITS;  // digit inside the depth word: MATCH.ANY
+    const bool last = p == passes - 1;
+    const bool depth_only = dyn_width || (shift + bits <= pl.lo_bits && bits == BITS);  // digit inside the depth word: MATCH.ANY
+    SortDynArgs da{};
+    da.shift = (uint32_t)shift;
+    if (dyn != nullptr) {
+      da.n_dev = dyn->n_dev;
+      da.bits_dev = dyn->bits_dev;
+      if (last && pl.packed) { da.ranges = dyn->ranges; da.tile_shift = dyn->tile_shift; }
+    }
+    uint32_t* ids = pl.packed && (last || dyn_width) ? vals_out : nullptr;
     onesweep_for_bits(depth_only ? 0 : bits, !pl.packed, items)<<<nblocks, SORT_THREADS, sort_smem(items), s>>>(
         ksrc, kdst, vsrc, vdst, (uint32_t)n, w.tickets + p, w.lookback + (size_t)p * sort_nblocks(n) * BINS,
-        w.hist + p * BINS, pd, (pl.packed && last) ? vals_out : nullptr,
-        pl.id_bits >= 32 ? 0xffffffffu : ((1u << pl.id_bits) - 1));
+        w.hist + p * BINS, pd, ids, pl.id_bits >= 32 ? 0xffffffffu : ((1u << pl.id_bits) - 1), da);
     count_launch();
     ksrc = kdst;
     vsrc = vdst;
   }
-  return pl.passes;
+  return passes;
 }
 
 }  // namespace lsr

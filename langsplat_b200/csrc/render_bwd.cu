@@ -81,6 +81,9 @@ __device__ __forceinline__ int held_index(int lane) {
 
 constexpr int BWD_SLOTS = BLEND_SLOTS;  // pixels per thread (rows r, r+4)
 
+#ifndef LSR_BWD_IEEE_DIV
+#define LSR_BWD_IEEE_DIV 0  // 1: walk T back with IEEE divisions like the reference (A/B of the gradient error)
+#endif
 #ifndef LSR_BWD_MINB
 #define LSR_BWD_MINB 25  // caps ptxas at 80 registers: 25 instead of 23 warps per SM (measured: 958 -> 905 us)
 #endif
@@ -224,8 +227,13 @@ render_bwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
           const float one_m_alpha = __fadd_rn(1.f, -alpha[s]);
           // (an IEEE division here, as the reference's T = T / (1 - alpha), was measured: the gradients' distance to
           // the reference does not change — it is set by the reference's own run-to-run atomic-order noise)
+#if LSR_BWD_IEEE_DIV
+          const float rcp = __fdiv_rn(1.f, one_m_alpha);
+          T[s] = __fdiv_rn(T[s], one_m_alpha);  // the reference's T = T / (1 - alpha) (backward.cu:521)
+#else
           const float rcp = rcp_ftz(one_m_alpha);  // 1 - alpha is in [0.01, 1]
           T[s] *= rcp;
+#endif
           const float w = alpha[s] * T[s];  // d(channel)/d(colour)
           float cd = 0.f;                   // colour . dL_dpixel over all blended channels
           if (DCOL) {

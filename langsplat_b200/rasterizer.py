@@ -8,7 +8,10 @@ lives in liblsr.so.  There is no CPU path: tensors must be CUDA float32.
 """
 from __future__ import annotations
 
+import collections
+import contextlib
 import ctypes
+import os
 from typing import Dict, NamedTuple, Optional, Tuple
 
 import torch
@@ -51,6 +54,122 @@ _last_R: Dict[int, int] = {}
 _CAPACITY_PER_GAUSSIAN = 4
 _INITIAL_CAPACITY_FLOOR = 1 << 16
 _capacity_retries = 0  # how often lsr_forward had to be repeated with a larger list (diagnostics / tests)
+
+
+# ---- forward without host synchronisation -----------------------------------------------------------------------------
+# The reference reads the instance count back in the middle of every forward (rasterizer_impl.cu:284), and so does the
+# default path here (lsr_forward: it has to report the count and to refuse a list that is too small before anything is
+# blended).  With `set_async_forward(True)` (or LSR_ASYNC_FORWARD=1) a forward whose device has seen a frame before
+# goes through lsr_forward_nosync instead: the instance list is sized from the recent frames' counts times
+# `capacity_margin`, nothing is read back, the host runs ahead of the GPU and the call can be captured in a CUDA graph.
+# What the device found out arrives later through pinned memory and is looked at — without waiting — at the next
+# forward / backward on that device (or, waiting, by `check_async_status()`): an instance list that turned out too
+# small raises LsrError there, and that frame's images were NaN-filled on the device, so an incomplete render can
+# never pass for a result.  Same kernels, same results as the synchronous path.
+class _AsyncConfig:
+    enabled = os.environ.get("LSR_ASYNC_FORWARD", "0") not in ("", "0")
+    capacity_margin = 1.5
+
+
+_recent_R: Dict[int, "collections.deque"] = {}  # per device: instance counts of the last frames
+_pending: Dict[int, list] = {}                  # per device: forwards whose status words have not been looked at
+_status_pool: list = []                         # free pinned status buffers: (tensor, numpy view)
+_stamp = [0]
+
+
+def set_async_forward(enabled: bool = True, capacity_margin: Optional[float] = None) -> None:
+    """Switches the forward between the reference's behaviour (one host read-back per frame) and the asynchronous
+    path described above.  `capacity_margin`: head room of the instance list over the largest recent frame."""
+    _AsyncConfig.enabled = bool(enabled)
+    if capacity_margin is not None:
+        if not capacity_margin >= 1.0:
+            raise ValueError("capacity_margin must be >= 1")
+        _AsyncConfig.capacity_margin = float(capacity_margin)
+
+
+@contextlib.contextmanager
+def async_forward(enabled: bool = True, capacity_margin: Optional[float] = None):
+    saved = (_AsyncConfig.enabled, _AsyncConfig.capacity_margin)
+    set_async_forward(enabled, capacity_margin)
+    try:
+        yield
+    finally:
+        _AsyncConfig.enabled, _AsyncConfig.capacity_margin = saved
+
+
+def reserve_instances(device, count: int) -> None:
+    """Tells the asynchronous path how many Gaussian/tile instances to expect on `device` (e.g. the maximum over the
+    training cameras, found with one synchronous forward each), so that no frame outgrows its list."""
+    dev = torch.device(device)
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    _recent_R.setdefault(idx, collections.deque(maxlen=16)).append(int(count))
+    _last_R[idx] = max(_last_R.get(idx, 0), int(count))
+
+
+def _note_R(dev_idx: int, R: int) -> None:
+    _recent_R.setdefault(dev_idx, collections.deque(maxlen=16)).append(R)
+    _last_R[dev_idx] = R
+
+
+_status_blocks: list = []  # the pinned allocations behind the pool; never freed (a captured CUDA graph may hold them)
+
+
+def _take_status():
+    if not _status_pool:  # a block of 32 at a time: no pinned allocation in the middle of a CUDA-graph capture
+        block = torch.zeros((32, L.STATUS_WORDS), dtype=torch.int32).pin_memory()
+        _status_blocks.append(block)
+        _status_pool.extend((row, row.numpy().view("uint32")) for row in block)
+    return _status_pool.pop()
+
+
+def _resolve(state, block: bool) -> bool:
+    """Looks at the status words of an asynchronous forward; True once they are known.  Raises on overflow."""
+    st = state.get("status")
+    if st is None:
+        return True
+    tensor, words = st
+    if int(words[L.STATUS_STAMP]) != state["stamp"]:
+        if not block:
+            return False
+        host = (ctypes.c_uint32 * L.STATUS_WORDS)()
+        with _on_device(state["device"]):
+            _check(L.load().lsr_forward_status(state["W"], state["H"], _ptr(state["image"]), host,
+                                               ctypes.c_void_p(state["stream"])), "lsr_forward_status")
+        vals = list(host)
+    else:
+        vals = [int(w) for w in words]
+    state["status"] = None
+    _status_pool.append(st)
+    pend = _pending.get(state["dev_idx"])
+    if pend is not None:
+        pend[:] = [x for x in pend if x is not state]
+    R, flags = vals[L.STATUS_NUM_RENDERED], vals[L.STATUS_FLAGS]
+    state["num_rendered"] = R
+    _note_R(state["dev_idx"], R)
+    if flags & L.STATUS_FLAG_PREFILTERED:  # auxiliary.h:156-160 traps; here the frame is reported
+        raise LsrError("Point is filtered although prefiltered is set. This shouldn't happen!")
+    if flags & L.STATUS_FLAG_OVERFLOW:
+        raise LsrError(f"asynchronous forward: the frame has {R} Gaussian/tile instances but its list was sized for "
+                       f"{state['capacity']}; its images were filled with NaN on the device.  Repeat the step (the next "
+                       "forward sizes its list from this count), raise capacity_margin, or call reserve_instances().")
+    return True
+
+
+def check_async_status(device=None) -> None:
+    """Waits for every outstanding asynchronous forward (of `device`, default all) and raises if one overflowed."""
+    for idx in list(_pending):
+        if device is not None:
+            d = torch.device(device)
+            if (d.index if d.index is not None else torch.cuda.current_device()) != idx:
+                continue
+        for state in list(_pending.get(idx, ())):
+            _resolve(state, block=True)
+
+
+def _poll_pending(dev_idx: int) -> None:
+    for state in list(_pending.get(dev_idx, ())):
+        if not _resolve(state, block=False):
+            break  # stream order: later frames cannot be done either
 
 
 def _present(t: Optional[torch.Tensor]) -> bool:
@@ -176,6 +295,35 @@ def _forward_impl(rs: GaussianRasterizationSettings, means3D, sh, colors, lang, 
     stream = torch.cuda.current_stream(device).cuda_stream
     dev_idx = device.index if device.index is not None else torch.cuda.current_device()
     global _capacity_retries
+    recent = _recent_R.get(dev_idx)
+    if _AsyncConfig.enabled and recent and not rs.debug:
+        _poll_pending(dev_idx)  # (raises if an earlier frame on this device outgrew its list)
+        capacity = max(int(max(recent) * _AsyncConfig.capacity_margin), _INITIAL_CAPACITY_FLOOR)
+        capacity = (capacity + 0xFFFF) & ~0xFFFF
+        status = _take_status()
+        status[1][L.STATUS_STAMP] = 0
+        _stamp[0] = _stamp[0] % 0xFFFFFFF0 + 1
+        with _on_device(device):
+            point_list = torch.empty((_sized(lib.lsr_list_bytes, capacity),), dtype=torch.uint8, device=device)
+            need = _sized(lib.lsr_scratch_bytes, P, W, H, capacity)
+            scratch = (torch.empty((need,), dtype=torch.uint8, device=device) if keep_scratch else _get_scratch(
+                device, stream, need))
+            rc = lib.lsr_forward_nosync(ctypes.byref(frame), ctypes.byref(inputs), _ptr(color), _ptr(feature),
+                                        _ptr(radii), _ptr(geom), _ptr(image), _ptr(point_list), capacity, _ptr(scratch),
+                                        scratch.numel(), _stamp[0], ctypes.c_void_p(status[0].data_ptr()),
+                                        ctypes.c_void_p(stream))
+        if rc != L.LSR_OK:
+            _status_pool.append(status)
+        _check(rc, "lsr_forward_nosync")
+        state = dict(frame=frame, inputs=inputs, geom=geom, image=image, point_list=point_list, num_rendered=None,
+                     capacity=capacity, keep=(means3D, sh, colors, lang, opac, scales, rots, cov3D, bg, view, proj,
+                                              campos),
+                     radii=radii, P=P, M=M, W=W, H=H, device=device, dev_idx=dev_idx, stream=stream, status=status,
+                     stamp=_stamp[0])
+        _pending.setdefault(dev_idx, []).append(state)
+        if keep_scratch:
+            state["scratch"] = scratch
+        return color, feature, radii, state
     capacity = max(int(_last_R.get(dev_idx, 0) * 1.25), _CAPACITY_PER_GAUSSIAN * P, _INITIAL_CAPACITY_FLOOR)
     capacity = (capacity + 0xFFFF) & ~0xFFFF  # 64 Ki steps: stable buffer sizes from frame to frame
     nr = ctypes.c_int64(0)
@@ -194,10 +342,10 @@ def _forward_impl(rs: GaussianRasterizationSettings, means3D, sh, colors, lang, 
                 continue
             break
     _check(rc, "lsr_forward")
-    _last_R[dev_idx] = int(nr.value)
+    _note_R(dev_idx, int(nr.value))
     state = dict(frame=frame, inputs=inputs, geom=geom, image=image, point_list=point_list, num_rendered=int(nr.value),
                  capacity=capacity, keep=(means3D, sh, colors, lang, opac, scales, rots, cov3D, bg, view, proj, campos),
-                 radii=radii, P=P, M=M, W=W, H=H, device=device)
+                 radii=radii, P=P, M=M, W=W, H=H, device=device, dev_idx=dev_idx, stream=stream)
     if keep_scratch:
         state["scratch"] = scratch
     return color, feature, radii, state
@@ -223,6 +371,7 @@ class ShFactorList(list):
 
 def _backward_impl(state, grad_color, grad_feature, need_mask: int, want_sh: bool, sh_factor_out=None):
     lib = L.load()
+    _resolve(state, block=False)  # asynchronous forward: raises if its instance list is known to have overflowed
     P, M, W, H, device = state["P"], state["M"], state["W"], state["H"], state["device"]
     (means3D, sh, colors, lang, opac, scales, rots, cov3D, *_rest) = state["keep"]
     f32 = dict(dtype=torch.float32, device=device)
@@ -308,7 +457,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         else:
             color, feature, radii, state = _forward_impl(raster_settings, *args)
         ctx.raster_settings = raster_settings
-        ctx.num_rendered = state["num_rendered"]
+        ctx.num_rendered = state["num_rendered"]  # None until known when the forward ran asynchronously
         ctx.state = state
         # The kernels' view of the inputs travels in `state` (device pointers of the contiguous tensors); the tensors
         # themselves go through save_for_backward like the reference's (RAST/diff_gaussian_rasterization/
@@ -457,6 +606,7 @@ class GaussianRasterizer(nn.Module):  # RAST/diff_gaussian_rasterization/__init_
 def debug_arrays(state) -> Dict[str, torch.Tensor]:
     """Typed views of the arrays inside a forward's geom / image / scratch buffers (include/lsr_api.h LSR_ARR_*)."""
     lib = L.load()
+    _resolve(state, block=True)  # an asynchronous forward learns its instance count here
     P, W, H, cap, R = state["P"], state["W"], state["H"], state["capacity"], state["num_rendered"]
     T = ((W + 15) // 16) * ((H + 15) // 16)
 

@@ -15,10 +15,10 @@ cat "$OUT/bench_ours.json" | head -c 3000; echo
 if [ "${NCU:-1}" = 1 ]; then
   CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline"
   $CMD > "$OUT/plain.log" 2>&1 &&
-  ncu --metrics gpu__time_duration.sum --clock-control none -k regex:'preprocess_fwd_kernel|preprocess_bwd_kernel|depth_words_kernel|scan_tiles_kernel|duplicate_kernel|onesweep_kernel|tile_ranges_kernel|tile_order_kernel|render_fwd_kernel|render_bwd_kernel' -s 42 -c 28 --csv \
+  ncu --metrics gpu__time_duration.sum --clock-control none -k regex:'preprocess_fwd_kernel|preprocess_bwd_kernel|depth_words_kernel|scan_tiles_kernel|duplicate_kernel|dup_scan_kernel|onesweep_kernel|tile_ranges_kernel|tile_order_kernel|finalize_tiles_kernel|render_fwd_kernel|render_bwd_kernel' -s 42 -c 28 --csv \
       --log-file "$OUT/launches.csv" $CMD > "$OUT/ncu_launches.log" 2>&1
   echo "ncu launches rc=$?"
-  ncu --set full --clock-control none --import-source on -k regex:'preprocess_fwd_kernel|preprocess_bwd_kernel|depth_words_kernel|scan_tiles_kernel|duplicate_kernel|onesweep_kernel|tile_ranges_kernel|tile_order_kernel|render_fwd_kernel|render_bwd_kernel' -s 42 -c 14 -f -o "$OUT/prof_step" $CMD \
+  ncu --set full --clock-control none --import-source on -k regex:'preprocess_fwd_kernel|preprocess_bwd_kernel|depth_words_kernel|scan_tiles_kernel|duplicate_kernel|dup_scan_kernel|onesweep_kernel|tile_ranges_kernel|tile_order_kernel|finalize_tiles_kernel|render_fwd_kernel|render_bwd_kernel' -s 42 -c 14 -f -o "$OUT/prof_step" $CMD \
       > "$OUT/ncu_full.log" 2>&1
   echo "ncu full rc=$?"
 fi
