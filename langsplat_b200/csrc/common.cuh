@@ -23,6 +23,9 @@ constexpr int TILE_PIX = TILE_X * TILE_Y;
 #ifndef LSR_MOMENTS
 #define LSR_MOMENTS 1
 #endif
+#ifndef LSR_BWD_IEEE_DIV
+#define LSR_BWD_IEEE_DIV 0  // 1: walk T back with IEEE divisions like the reference (A/B of the gradient error)
+#endif
 
 // One 48-byte record per Gaussian holds everything the blend kernels gather per instance, so a gather touches
 // two 32-B sectors instead of the reference's four to six (means2D, conic_opacity, rgb, feature are separate
@@ -255,6 +258,11 @@ void launch_render_bwd(int W, int H, const uint2* ranges, const uint32_t* order,
                        bool include_feature, const float* final_T, const uint32_t* n_contrib, const float* dL_dcolor,
                        const float* dL_dfeature, uint32_t need_mask, float* dL_dmean2D, float* dL_dconic,
                        float* dL_dopacity, float* dL_dcolors, float* dL_dfeat, cudaStream_t s);
+// the two-phase variant of the same kernel (render_bwd2.cu), same contract
+void launch_render_bwd2(int W, int H, const uint2* ranges, const uint32_t* order, const uint32_t* list, const GeomRec* rec, const float* bg,
+                        bool include_feature, const float* final_T, const uint32_t* n_contrib, const float* dL_dcolor,
+                        const float* dL_dfeature, uint32_t need_mask, float* dL_dmean2D, float* dL_dconic,
+                        float* dL_dopacity, float* dL_dcolors, float* dL_dfeat, cudaStream_t s);
 void launch_preprocess_bwd(const lsr_frame& f, const lsr_inputs& in, float focal_x, float focal_y,
                            const int32_t* radii, GeomView g, uint32_t need_mask, const lsr_grads& gr, cudaStream_t s);
 // dL_dsh [P,M,3] = sum over V views of basis(normalize(mean - campos_v)) (x) g_v, g: [V,P,3] clamp-masked dL_dcolor

@@ -31,6 +31,8 @@
 // Template switches specialise on what the caller needs (ctx.needs_input_grad): FEAT = language feature blended,
 // DCOL = a colour upstream gradient exists, GEOM = conic/opacity gradients wanted.  LangSplat's feature-only training
 // (train.py:96-99 with gaussian_model.py:212-217) runs <FEAT=1, DCOL=0, GEOM=0>: 5 values instead of 12.
+#include <cstdlib>
+
 #include "render_common.cuh"
 
 namespace lsr {
@@ -81,9 +83,6 @@ __device__ __forceinline__ int held_index(int lane) {
 
 constexpr int BWD_SLOTS = BLEND_SLOTS;  // pixels per thread (rows r, r+4)
 
-#ifndef LSR_BWD_IEEE_DIV
-#define LSR_BWD_IEEE_DIV 0  // 1: walk T back with IEEE divisions like the reference (A/B of the gradient error)
-#endif
 #ifndef LSR_BWD_MINB
 #define LSR_BWD_MINB 25  // caps ptxas at 80 registers: 25 instead of 23 warps per SM (measured: 958 -> 905 us)
 #endif
@@ -333,6 +332,15 @@ void launch_render_bwd(int W, int H, const uint2* ranges, const uint32_t* order,
                        const GeomRec* rec, const float* bg, bool include_feature, const float* final_T, const uint32_t* n_contrib, const float* dL_dcolor,
                        const float* dL_dfeature, uint32_t need_mask, float* dL_dmean2D, float* dL_dconic,
                        float* dL_dopacity, float* dL_dcolors, float* dL_dfeat, cudaStream_t s) {
+#if LSR_MOMENTS
+  // the two-phase kernel (render_bwd2.cu) is the default; LSR_BWD_V1=1 selects this file's one-phase kernel (A/B)
+  static const bool v1 = getenv("LSR_BWD_V1") != nullptr;
+  if (!v1) {
+    launch_render_bwd2(W, H, ranges, order, list, rec, bg, include_feature, final_T, n_contrib, dL_dcolor, dL_dfeature,
+                       need_mask, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolors, dL_dfeat, s);
+    return;
+  }
+#endif
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
   if (tiles_x == 0 || tiles_y == 0) return;
   const unsigned grid = (unsigned)tiles_x * (unsigned)tiles_y * QUADS;

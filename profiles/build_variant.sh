@@ -6,7 +6,7 @@ NAME="$1"; FLAGS="${2:-}"
 ROOT="$(cd "$(dirname "$0")/.." && pwd)"
 D="$ROOT/build/variants/$NAME.d"; mkdir -p "$D"
 cd "$ROOT/langsplat_b200/csrc"
-for f in api preprocess_fwd binning radix_sort render_fwd render_bwd preprocess_bwd loss peer activations gt_features adam decoder; do
+for f in api preprocess_fwd binning radix_sort render_fwd render_bwd render_bwd2 preprocess_bwd loss peer activations gt_features adam decoder; do
   /usr/local/cuda/bin/nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -lineinfo -Xcompiler -fPIC \
     -Xcompiler -fvisibility=hidden -Xptxas -v $FLAGS -c $f.cu -o "$D/$f.o" 2> "$D/$f.ptxas.log" &
 done

@@ -193,7 +193,7 @@ def test_reference_python_side_branches(pipe_kw):
 @needs
 def test_reference_render_at_half_hd():
     """A larger frame (200 k Gaussians, 960x540) through the same unmodified caller, feature mode."""
-    scene, cams = syn.make_config(2, P=200_000, W=960, H=540)
+    scene, cams = syn.make_config(2, P=200_000, W=960, H=540, n_cameras=2)
     ours = _iteration(_ours(), scene, cams[1], True)
     ref = _iteration(_Caller(REF), scene, cams[1], True)
     _compare(ours, ref, True)
