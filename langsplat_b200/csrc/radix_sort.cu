@@ -147,8 +147,14 @@ __device__ __forceinline__ uint32_t sw(uint32_t p) { return p ^ ((p >> 4) & 15u)
 // PAIRS = false: the value rides in the low bits of the 64-bit word (binning.cu packs compacted key | Gaussian id), so
 // a pass moves 8 instead of 12 bytes per element and the whole value phase disappears; the last pass additionally
 // writes the ids out as the u32 point list (`ids_out`).
+#ifndef LSR_SORT_MINB
+#define LSR_SORT_MINB 4  // CTAs per SM the register allocation aims at (4: 64 registers with ~100 B of spills)
+#endif
+#ifndef LSR_DEPTH_NB
+#define LSR_DEPTH_NB 0  // ranking of the depth-ordering passes: 0 = MATCH.ANY, 8 = eight ballots
+#endif
 template <int NB, bool PAIRS, int ITEMS>
-__global__ void __launch_bounds__(SORT_THREADS, 4)
+__global__ void __launch_bounds__(SORT_THREADS, LSR_SORT_MINB)
 onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, const uint32_t* __restrict__ vin,
                 uint32_t* __restrict__ vout, uint32_t n_bound, uint32_t* __restrict__ ticket,
                 volatile uint32_t* __restrict__ lookback, const uint32_t* __restrict__ ghist, PassDigit pd,
@@ -536,7 +542,7 @@ int sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_
       if (last && pl.packed) { da.ranges = dyn->ranges; da.tile_shift = dyn->tile_shift; }
     }
     uint32_t* ids = pl.packed && (last || dyn_width) ? vals_out : nullptr;
-    onesweep_for_bits(depth_only ? 0 : bits, !pl.packed, items)<<<nblocks, SORT_THREADS, sort_smem(items), s>>>(
+    onesweep_for_bits(depth_only ? LSR_DEPTH_NB : bits, !pl.packed, items)<<<nblocks, SORT_THREADS, sort_smem(items), s>>>(
         ksrc, kdst, vsrc, vdst, (uint32_t)n, w.tickets + p, w.lookback + (size_t)p * sort_nblocks(n) * BINS,
         w.hist + p * BINS, pd, ids, pl.id_bits >= 32 ? 0xffffffffu : ((1u << pl.id_bits) - 1), da);
     count_launch();

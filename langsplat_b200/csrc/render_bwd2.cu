@@ -27,7 +27,7 @@
 // path's 1e-4 relative tolerance; the forward decisions are untouched.
 #include "render_common.cuh"
 
-static_assert(LSR_MOMENTS == 1, "the two-phase backward hands moments to the per-Gaussian kernel");
+#if LSR_MOMENTS  // the two-phase backward hands moments to the per-Gaussian kernel (an LSR_MOMENTS=0 build uses render_bwd.cu)
 
 namespace lsr {
 
@@ -51,6 +51,9 @@ struct __align__(16) Bwd2Smem {
 
 #ifndef LSR_BWD2_MINB
 #define LSR_BWD2_MINB 24
+#endif
+#ifndef LSR_BWD2_PIPE
+#define LSR_BWD2_PIPE 1  // software-pipelined, branch-free walk (0: one instance at a time with early-outs; A/B)
 #endif
 
 template <bool FEAT, bool DCOL, bool GEOM>
@@ -225,6 +228,110 @@ render_bwd2_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, 
   const uint32_t stMeta = smem_u32(&sm.meta[0]), stConic = smem_u32(&sm.conic[0]);
   int ncol = 0;
   Fetched nxt = fetch_instance(list, rec, range.x, eff_len - 1 - lane);
+#if LSR_BWD2_PIPE
+  // Software-pipelined walk.  The one-instance-at-a-time loop is a single dependent chain per warp (position -> power
+  // -> exp -> alpha -> ballot -> reciprocal -> T -> recurrences -> stores; ncu r2c: 23 % of the stall samples are
+  // fixed-latency waits, 19 % MUFU / shared-memory scoreboard, issue slots only 70 % used), and its data-dependent
+  // branches keep the compiler from overlapping neighbouring iterations.  Here every iteration runs the FRONT half of
+  // instance j+1 (geometry, exp, alpha, contribution test: independent of everything before it) next to the BACK half
+  // of instance j (the sequential part: T, colour-behind, w and s), both branch-free — lanes that do not contribute
+  // compute and discard — so the two chains sit in one basic block and interleave.
+  struct Front {
+    float G[BLEND_SLOTS], alpha[BLEND_SLOTS];
+    bool contrib[BLEND_SLOTS];
+    bool any;
+  };
+  auto front = [&](int j) {
+    Front f;
+    const uint32_t ad = smA + (uint32_t)j * (uint32_t)sizeof(float4);
+    const float4 a = lds128(ad);
+    const float4 bb = lds128(ad + SM_B);  // cz, thr_m, opacity, position
+    const uint32_t fwd = __float_as_uint(bb.w);
+    const float dx = __fadd_rn(a.x, -pxf);
+    const float qx = __fmul_rn(a.z, dx), hx = __fmul_rn(a.w, dx);
+    bool any = false;
+#pragma unroll
+    for (int s = 0; s < BLEND_SLOTS; s++) {
+      const float dy = __fadd_rn(a.y, -pyf[s]);
+      const float q = __fmaf_rn(dx, qx, __fmul_rn(__fmul_rn(bb.x, dy), dy));
+      const float power = __fmaf_rn(q, -0.5f, -__fmul_rn(hx, dy));
+      // entries at or beyond n_contrib were never blended (backward.cu:504-506); power > 0 and the alpha threshold as
+      // in the forward
+      const bool maybe = (fwd < lastc[s]) && !(power > 0.0f);
+      f.G[s] = expf(power);
+      f.alpha[s] = fminf(0.99f, __fmul_rn(bb.z, f.G[s]));
+      f.contrib[s] = maybe && !(f.alpha[s] < kAlphaMin);
+      any |= f.contrib[s];
+    }
+    f.any = any;  // this lane's view; the warp-wide vote follows the back half (so that both halves share a block)
+    return f;
+  };
+  auto back = [&](int j, const Front& f) {
+    const uint32_t ad = smA + (uint32_t)j * (uint32_t)sizeof(float4);
+    const float4 c = lds128(ad + SM_C);  // r, g, b, f0
+    const float4 d = lds128(ad + SM_D);  // f1, f2, id
+    const uint32_t colofs = (uint32_t)(ncol * ROW * 4);
+#pragma unroll
+    for (int s = 0; s < BLEND_SLOTS; s++) {
+      const bool ct = f.contrib[s];
+      const float one_m_alpha = __fadd_rn(1.f, -f.alpha[s]);
+#if LSR_BWD_IEEE_DIV
+      const float rcp = __fdiv_rn(1.f, one_m_alpha);
+      const float Tn = __fdiv_rn(T[s], one_m_alpha);  // the reference's T = T / (1 - alpha) (backward.cu:521)
+#else
+      const float rcp = rcp_ftz(one_m_alpha);  // 1 - alpha is in [0.01, 1]
+      const float Tn = T[s] * rcp;
+#endif
+      float cd = 0.f;  // colour . dL_dpixel over all blended channels
+      if (DCOL) cd = c.x * dpix[s][0] + c.y * dpix[s][1] + c.z * dpix[s][2];
+      if (FEAT) cd += c.w * dpixF[s][0] + d.x * dpixF[s][1] + d.y * dpixF[s][2];
+      // "colour behind" recurrence on the dot product (backward.cu:527-538, per channel there)
+      const float accn = alpha_last[s] * cd_last[s] + (1.f - alpha_last[s]) * accA[s];
+      float dL_dalpha = (cd - accn) * Tn;
+      if (DCOL) dL_dalpha += bgT[s] * rcp;  // background term (backward.cu:545-550)
+      const float wv = ct ? f.alpha[s] * Tn : 0.f;  // d(channel)/d(colour)
+      const float sv = ct ? f.G[s] * dL_dalpha : 0.f;
+      T[s] = ct ? Tn : T[s];
+      accA[s] = ct ? accn : accA[s];
+      cd_last[s] = ct ? cd : cd_last[s];
+      alpha_last[s] = ct ? f.alpha[s] : alpha_last[s];
+      sts32(stW + colofs + (uint32_t)(s * 36 * 4), wv);
+      sts32(stS + colofs + (uint32_t)(s * 36 * 4), sv);
+    }
+    if (lane == 0) {
+      const float4 a = lds128(ad);
+      const float4 bb = lds128(ad + SM_B);
+      asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(stMeta + (uint32_t)ncol * 16u), "f"(a.x), "f"(a.y),
+                   "f"(d.z), "f"(bb.z)
+                   : "memory");
+      if (!GEOM)
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(stConic + (uint32_t)ncol * 16u), "f"(a.z),
+                     "f"(a.w), "f"(bb.x), "f"(0.f)
+                     : "memory");
+    }
+  };
+  for (int top = eff_len - 1; top >= 0; top -= 32) {
+    __syncwarp();  // everyone has left the previous batch
+    const int nb = commit_batch(sm.batch, nxt, X0, Y0);
+    nxt = fetch_instance(list, rec, range.x, top - 32 - lane);
+    if (nb == 0) continue;
+    Front cur = front(0);
+    cur.any = __any_sync(0xffffffffu, cur.any);
+    for (int j = 0; j < nb; j++) {
+      // (the last iteration evaluates the front of its own instance once more instead of branching around it)
+      Front nxtf = front(min(j + 1, nb - 1));
+      back(j, cur);  // a column nobody contributes to is written but not kept
+      nxtf.any = __any_sync(0xffffffffu, nxtf.any);
+      if (cur.any && ++ncol == NCOL) {
+        __syncwarp();  // the panel is complete
+        flush(NCOL);
+        ncol = 0;
+        __syncwarp();  // ... and free again
+      }
+      cur = nxtf;
+    }
+  }
+#else
   for (int top = eff_len - 1; top >= 0; top -= 32) {
     __syncwarp();  // everyone has left the previous batch
     const int nb = commit_batch(sm.batch, nxt, X0, Y0);
@@ -310,6 +417,7 @@ render_bwd2_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, 
       }
     }
   }
+#endif
   if (ncol > 0) {
     __syncwarp();
     flush(ncol);
@@ -354,3 +462,4 @@ void launch_render_bwd2(int W, int H, const uint2* ranges, const uint32_t* order
 }
 
 }  // namespace lsr
+#endif  // LSR_MOMENTS

@@ -200,26 +200,77 @@ def record_errors(case: str, table: dict) -> None:
         pass
 
 
-def compare_with_reference_runs(case: str, ours: dict, refs: list, keys, bar: float = 1e-4) -> None:
+def compare_with_reference_runs(case: str, ours: dict, refs: list, keys, bar: float = 1e-4, arbiter=None) -> None:
     """ours / refs[i]: {name: gradient tensor}.  The reference sums with unordered float atomics, so one reference run
     is not a fixed point: compare with the mean of the runs and let 3x the runs' own scatter about that mean widen the
     bar where it is the larger quantity.  Both metrics (max-abs ratio, relative L2) of ours-vs-mean and
-    of every reference run vs the mean go to the tracked error log."""
-    table, failures = {}, []
+    of every reference run vs the mean go to the tracked error log.
+
+    `arbiter` (optional): callable returning {name: float64 gradient} of the same step from the CPU oracle evaluated
+    in float64.  Some Gaussians are ill-conditioned in float32 (needles a fraction of a pixel thin: config 4's Gaussian
+    1772573 has dL_drotation = 11.43 in float64, 11.26 from the reference and 11.66 from this repo — both 2 % off, in
+    opposite directions, while each implementation repeats itself to 0.5 %), so run-to-run scatter does not bound the
+    distance between two correct float32 evaluations there.  Where an element misses the bar, float64 decides: this
+    repo's value must be no farther from it than twice the reference's (or the bar), such elements must be rare
+    (< 1e-5 of the tensor), and the relative-L2 bar must hold on the rest."""
+    table, failures, truth = {}, [], None
     for k in keys:
         mean = sum(r[k].double() for r in refs) / len(refs)
         noise = max(rel_err(r[k], mean) for r in refs)
         noise_l2 = max(rel_l2(r[k], mean) for r in refs)
         err, err_l2 = rel_err(ours[k], mean), rel_l2(ours[k], mean)
+        bar_max, bar_l2 = max(bar, 3.0 * noise), max(bar, 3.0 * noise_l2)
         table[k] = dict(ours_vs_mean_maxabs=err, ours_vs_mean_l2=err_l2, ref_vs_mean_maxabs=noise,
-                        ref_vs_mean_l2=noise_l2, bar_maxabs=max(bar, 3.0 * noise), bar_l2=max(bar, 3.0 * noise_l2),
+                        ref_vs_mean_l2=noise_l2, bar_maxabs=bar_max, bar_l2=bar_l2,
                         reference_runs=len(refs), max_abs_value=float(mean.abs().max()))
-        if not err < max(bar, 3.0 * noise):
-            failures.append(f"{k}: max-abs rel err {err:.3e} (reference runs about their mean: {noise:.3e})")
-        if not err_l2 < max(bar, 3.0 * noise_l2):
-            failures.append(f"{k}: rel L2 err {err_l2:.3e} (reference runs about their mean: {noise_l2:.3e})")
+        if err < bar_max and err_l2 < bar_l2:
+            continue
+        if arbiter is None:
+            if not err < bar_max:
+                failures.append(f"{k}: max-abs rel err {err:.3e} (reference runs about their mean: {noise:.3e})")
+            if not err_l2 < bar_l2:
+                failures.append(f"{k}: rel L2 err {err_l2:.3e} (reference runs about their mean: {noise_l2:.3e})")
+            continue
+        if truth is None:
+            truth = arbiter()
+        t = torch.as_tensor(truth[k]).to(mean.device).double().reshape(mean.shape)
+        o = ours[k].double()
+        scale = mean.abs().max().item()
+        out = (o - mean).abs() > bar_max * scale  # the elements that miss the bar
+        n_out = int(out.sum())
+        d_ours, d_ref = (o - t).abs()[out], (mean - t).abs()[out]
+        worst = float((d_ours / torch.clamp(torch.maximum(2.0 * d_ref, torch.full_like(d_ref, bar * scale)),
+                                            min=1e-300)).max()) if n_out else 0.0
+        rest = ~out
+        l2_rest = ((o - mean)[rest].norm() / mean[rest].norm()).item()
+        table[k].update(arbitrated_elements=n_out, arbitrated_fraction=n_out / out.numel(),
+                        worst_ours_over_2x_reference_distance_to_f64=worst, l2_without_arbitrated=l2_rest,
+                        ours_vs_f64_maxabs=rel_err(o, t), ref_mean_vs_f64_maxabs=rel_err(mean, t))
+        if n_out > max(8, 1e-5 * out.numel()):
+            failures.append(f"{k}: {n_out} elements miss the bar {bar_max:.2e} (too many to be conditioning outliers)")
+        if worst > 1.0:
+            failures.append(f"{k}: an element is {worst:.2f}x farther from the float64 value than allowed "
+                            f"(2x the reference's distance)")
+        if not l2_rest < bar_l2:
+            failures.append(f"{k}: rel L2 err {l2_rest:.3e} without the arbitrated elements")
     record_errors(case, table)
     assert not failures, "; ".join(failures)
+
+
+def oracle_step_f64(scene, cams, grad_seed0):
+    """The summed gradients of a multi-view step from the CPU oracle in float64 (upstream gradients
+    syn.make_grads(.., grad_seed0 + view)); keys as run_module's `grads`."""
+    total = {}
+    names = dict(means3D="means3D", means2D="means2D", shs="shs", language_feature="language_feature",
+                 opacities="opacities", scales="scales", rotations="rotations")
+    for i, cam in enumerate(cams):
+        dcol, dfeat = syn.make_grads(cam.image_width, cam.image_height, grad_seed0 + i)
+        fw = oracle_forward(scene, cam, dtype=np.float64)
+        g = orc.backward(fw, dcol.numpy(), dfeat.numpy())
+        for k, ok in names.items():
+            v = np.asarray(g[ok], np.float64)
+            total[k] = v if k not in total else total[k] + v
+    return total
 
 
 # ---- golden vectors (tests/golden/*.npz, produced by tests/golden/make_golden.py from the reference extension) ----

@@ -147,6 +147,6 @@ def test_forward_and_backward_replay_from_a_cuda_graph():
             assert torch.equal(radii, want[i]["radii"])
             got = dict(zip(names + ("means2D",), gs))
             for k in names + ("means2D",):
-                assert rel_err(got[k], want[i]["grads"][k]) < 2e-5, (i, k)
+                assert rel_err(got[k], want[i]["grads"][k]) < 1e-4, (i, k)  # the path's gradient bar (unordered atomics)
         for pend in R._pending.values():  # (the capture's status stamp cannot be matched to a replay)
             pend.clear()

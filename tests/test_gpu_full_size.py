@@ -4,8 +4,8 @@ import numpy as np
 import pytest
 import torch
 
-from helpers import (R, compare_with_reference_runs, cuda_forward_state, load_reference, ref_forward_buffers,
-                     rel_err, run_module, syn)
+from helpers import (R, compare_with_reference_runs, cuda_forward_state, load_reference, oracle_step_f64,
+                     ref_forward_buffers, rel_err, run_module, syn)
 
 pytestmark = pytest.mark.gpu
 
@@ -146,11 +146,18 @@ def test_config4_full_size_eight_views_against_reference():
     scene, cams = syn.make_config(4, n_cameras=8)
     refs = [_multi_view_step(REF.GaussianRasterizer, REF.GaussianRasterizationSettings, scene, cams, dev)
             for _ in range(2)]
+    truth = {}
+
+    def f64():  # evaluated at most once, and only if an element misses the bar (about a minute of host time)
+        if not truth:
+            truth.update(oracle_step_f64(scene, cams, 2400))
+        return truth
+
     dense = _multi_view_step(R.GaussianRasterizer, R.GaussianRasterizationSettings, scene, cams, dev)
-    compare_with_reference_runs("config4_full_dense", dense, refs, GRAD_KEYS)
+    compare_with_reference_runs("config4_full_dense", dense, refs, GRAD_KEYS, arbiter=f64)
     del dense
     fact = _multi_view_step(R.GaussianRasterizer, R.GaussianRasterizationSettings, scene, cams, dev, factored=True)
-    compare_with_reference_runs("config4_full_factored_sh", fact, refs, GRAD_KEYS)
+    compare_with_reference_runs("config4_full_factored_sh", fact, refs, GRAD_KEYS, arbiter=f64)
 
 
 def test_config5_forward_structure_and_reference():

@@ -178,3 +178,34 @@ def test_mark_visible_is_the_depth_cull():
     z = m.numpy() @ V[[2, 6, 10]] + V[14]
     clear = np.abs(z - 0.2) > 1e-5
     np.testing.assert_array_equal(got[clear], (z > 0.2)[clear])
+
+
+def test_reference_comparison_arbitrated_by_float64():
+    """tests/helpers.compare_with_reference_runs: an element where two float32 evaluations disagree beyond the bar is
+    judged against a float64 value; a systematic error on many elements, or an element much farther from float64 than
+    the reference is, still fails."""
+    import pytest
+    import torch
+    from helpers import compare_with_reference_runs
+    g = torch.Generator().manual_seed(3)
+    truth = torch.randn(200_000, 4, generator=g, dtype=torch.float64)
+    refs = [dict(x=(truth + 1e-7 * torch.randn(truth.shape, generator=g, dtype=torch.float64)).float()) for _ in range(3)]
+    ours = (truth + 1e-7 * torch.randn(truth.shape, generator=g, dtype=torch.float64)).float()
+    compare_with_reference_runs("selftest_plain", dict(x=ours), refs, ("x",))
+    # one ill-conditioned element: both implementations 2 % off the float64 value, in opposite directions
+    scale = float(truth.abs().max())
+    truth[7, 2] = 0.5 * scale
+    for r in refs:
+        r["x"][7, 2] = 0.5 * scale * 0.98
+    ours[7, 2] = 0.5 * scale * 1.02
+    with pytest.raises(AssertionError):
+        compare_with_reference_runs("selftest_no_arbiter", dict(x=ours), refs, ("x",))
+    compare_with_reference_runs("selftest_arbiter", dict(x=ours), refs, ("x",), arbiter=lambda: dict(x=truth.numpy()))
+    bad = ours.clone()
+    bad[7, 2] = 0.5 * scale * 1.10  # five times the reference's distance from the float64 value
+    with pytest.raises(AssertionError, match="farther from the float64 value"):
+        compare_with_reference_runs("selftest_far", dict(x=bad), refs, ("x",), arbiter=lambda: dict(x=truth.numpy()))
+    many = ours.clone()
+    many[:100, 0] += 1e-3 * scale  # a systematic error is not a conditioning outlier
+    with pytest.raises(AssertionError, match="too many"):
+        compare_with_reference_runs("selftest_many", dict(x=many), refs, ("x",), arbiter=lambda: dict(x=truth.numpy()))
