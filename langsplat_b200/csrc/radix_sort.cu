@@ -151,7 +151,8 @@ __device__ __forceinline__ uint32_t sw(uint32_t p) { return p ^ ((p >> 4) & 15u)
 #define LSR_SORT_MINB 4  // CTAs per SM the register allocation aims at (4: 64 registers with ~100 B of spills)
 #endif
 #ifndef LSR_DEPTH_NB
-#define LSR_DEPTH_NB 0  // ranking of the depth-ordering passes: 0 = MATCH.ANY, 8 = eight ballots
+#define LSR_DEPTH_NB 8  // ranking of the depth-ordering passes: eight ballots (0 = MATCH.ANY: 77 vs 65 us for the
+                       // three passes at C2, GPU call r2d: the low digits of a depth word mostly differ within a warp)
 #endif
 template <int NB, bool PAIRS, int ITEMS>
 __global__ void __launch_bounds__(SORT_THREADS, LSR_SORT_MINB)

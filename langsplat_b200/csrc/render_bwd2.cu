@@ -53,7 +53,12 @@ struct __align__(16) Bwd2Smem {
 #define LSR_BWD2_MINB 24
 #endif
 #ifndef LSR_BWD2_PIPE
-#define LSR_BWD2_PIPE 1  // software-pipelined, branch-free walk (0: one instance at a time with early-outs; A/B)
+// 0: one instance at a time, early-outs, per-slot branches (the default).
+// 1: software-pipelined, branch-free walk: front half of instance j+1 next to the back half of instance j.  Measured
+//    (GPU call r2d, C2): 945 us against 826 us — the extra work (exp for every examined pair, selects, the re-read
+//    records) and the registers cost more than the overlap returns; with a 96-register cap 868 us.
+// 2: as 0, but the back half of an instance is branch-free, so that the two pixel slots' chains share a basic block.
+#define LSR_BWD2_PIPE 0
 #endif
 
 template <bool FEAT, bool DCOL, bool GEOM>
@@ -229,7 +234,7 @@ render_bwd2_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, 
   int ncol = 0;
   Fetched nxt = fetch_instance(list, rec, range.x, eff_len - 1 - lane);
 #if LSR_BWD2_PIPE
-  // Software-pipelined walk.  The one-instance-at-a-time loop is a single dependent chain per warp (position -> power
+  // Software-pipelined walk (LSR_BWD2_PIPE == 1).  The one-instance-at-a-time loop is a single dependent chain per warp (position -> power
   // -> exp -> alpha -> ballot -> reciprocal -> T -> recurrences -> stores; ncu r2c: 23 % of the stall samples are
   // fixed-latency waits, 19 % MUFU / shared-memory scoreboard, issue slots only 70 % used), and its data-dependent
   // branches keep the compiler from overlapping neighbouring iterations.  Here every iteration runs the FRONT half of
@@ -310,6 +315,49 @@ render_bwd2_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, 
                      : "memory");
     }
   };
+#if LSR_BWD2_PIPE == 2
+  for (int top = eff_len - 1; top >= 0; top -= 32) {
+    __syncwarp();  // everyone has left the previous batch
+    const int nb = commit_batch(sm.batch, nxt, X0, Y0);
+    nxt = fetch_instance(list, rec, range.x, top - 32 - lane);
+    for (int j = 0; j < nb; j++) {
+      const uint32_t ad = smA + (uint32_t)j * (uint32_t)sizeof(float4);
+      const float4 a = lds128(ad);
+      const float4 bb = lds128(ad + SM_B);  // cz, thr_m, opacity, position
+      const uint32_t fwd = __float_as_uint(bb.w);
+      const float dx = __fadd_rn(a.x, -pxf);
+      const float qx = __fmul_rn(a.z, dx), hx = __fmul_rn(a.w, dx);
+      float power[BLEND_SLOTS];
+      bool maybe[BLEND_SLOTS], any_maybe = false;
+#pragma unroll
+      for (int s = 0; s < BLEND_SLOTS; s++) {
+        const float dy = __fadd_rn(a.y, -pyf[s]);
+        const float q = __fmaf_rn(dx, qx, __fmul_rn(__fmul_rn(bb.x, dy), dy));
+        power[s] = __fmaf_rn(q, -0.5f, -__fmul_rn(hx, dy));
+        maybe[s] = (fwd < lastc[s]) && !(power[s] > 0.0f) && !(power[s] < bb.y);
+        any_maybe |= maybe[s];
+      }
+      if (!__any_sync(0xffffffffu, any_maybe)) continue;
+      Front f;
+      bool any = false;
+#pragma unroll
+      for (int s = 0; s < BLEND_SLOTS; s++) {
+        f.G[s] = expf(power[s]);
+        f.alpha[s] = fminf(0.99f, __fmul_rn(bb.z, f.G[s]));
+        f.contrib[s] = maybe[s] && !(f.alpha[s] < kAlphaMin);
+        any |= f.contrib[s];
+      }
+      if (!__any_sync(0xffffffffu, any)) continue;
+      back(j, f);
+      if (++ncol == NCOL) {
+        __syncwarp();  // the panel is complete
+        flush(NCOL);
+        ncol = 0;
+        __syncwarp();  // ... and free again
+      }
+    }
+  }
+#else
   for (int top = eff_len - 1; top >= 0; top -= 32) {
     __syncwarp();  // everyone has left the previous batch
     const int nb = commit_batch(sm.batch, nxt, X0, Y0);
@@ -331,6 +379,7 @@ render_bwd2_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, 
       cur = nxtf;
     }
   }
+#endif
 #else
   for (int top = eff_len - 1; top >= 0; top -= 32) {
     __syncwarp();  // everyone has left the previous batch

@@ -114,11 +114,22 @@ def _note_R(dev_idx: int, R: int) -> None:
 _status_blocks: list = []  # the pinned allocations behind the pool; never freed (a captured CUDA graph may hold them)
 
 
-def _take_status():
-    if not _status_pool:  # a block of 32 at a time: no pinned allocation in the middle of a CUDA-graph capture
-        block = torch.zeros((32, L.STATUS_WORDS), dtype=torch.int32).pin_memory()
+def _take_status(dev_idx: int):
+    """A pinned status buffer.  The pool is allocated once (256 buffers, 8 KB): a pinned allocation synchronises the
+    device, so there must be none once frames are in flight (nor inside a CUDA-graph capture).  A host that runs
+    further ahead than the pool is deep waits for its oldest outstanding frame instead."""
+    if not _status_blocks:
+        block = torch.zeros((256, L.STATUS_WORDS), dtype=torch.int32).pin_memory()
         _status_blocks.append(block)
         _status_pool.extend((row, row.numpy().view("uint32")) for row in block)
+    while not _status_pool:
+        oldest = next((p[0] for p in ([_pending.get(dev_idx)] + list(_pending.values())) if p), None)
+        if oldest is None:  # every buffer is held by a captured graph: grow (outside any capture)
+            block = torch.zeros((256, L.STATUS_WORDS), dtype=torch.int32).pin_memory()
+            _status_blocks.append(block)
+            _status_pool.extend((row, row.numpy().view("uint32")) for row in block)
+            break
+        _resolve(oldest, block=True)
     return _status_pool.pop()
 
 
@@ -300,7 +311,7 @@ def _forward_impl(rs: GaussianRasterizationSettings, means3D, sh, colors, lang, 
         _poll_pending(dev_idx)  # (raises if an earlier frame on this device outgrew its list)
         capacity = max(int(max(recent) * _AsyncConfig.capacity_margin), _INITIAL_CAPACITY_FLOOR)
         capacity = (capacity + 0xFFFF) & ~0xFFFF
-        status = _take_status()
+        status = _take_status(dev_idx)
         status[1][L.STATUS_STAMP] = 0
         _stamp[0] = _stamp[0] % 0xFFFFFFF0 + 1
         with _on_device(device):

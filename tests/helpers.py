@@ -241,6 +241,13 @@ def compare_with_reference_runs(case: str, ours: dict, refs: list, keys, bar: fl
         d_ours, d_ref = (o - t).abs()[out], (mean - t).abs()[out]
         worst = float((d_ours / torch.clamp(torch.maximum(2.0 * d_ref, torch.full_like(d_ref, bar * scale)),
                                             min=1e-300)).max()) if n_out else 0.0
+        if n_out:  # the worst of them, for the log: flat index, this repo, reference mean, float64
+            ratio = d_ours / torch.clamp(torch.maximum(2.0 * d_ref, torch.full_like(d_ref, bar * scale)), min=1e-300)
+            top = ratio.topk(min(5, n_out))
+            flat_idx = out.flatten().nonzero().flatten()[top.indices]
+            table[k]["worst_elements"] = [dict(index=int(i), ours=float(o.flatten()[i]), reference=float(mean.flatten()[i]),
+                                               float64=float(t.flatten()[i]), ratio=float(r))
+                                          for i, r in zip(flat_idx.tolist(), top.values.tolist())]
         rest = ~out
         l2_rest = ((o - mean)[rest].norm() / mean[rest].norm()).item()
         table[k].update(arbitrated_elements=n_out, arbitrated_fraction=n_out / out.numel(),
