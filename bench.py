@@ -71,6 +71,14 @@ def parse_args():
     ap.add_argument("--sync-forward", action="store_true",
                     help="ours: keep the reference's per-frame host read-back of the instance count (lsr_forward) "
                          "instead of the asynchronous forward (langsplat_b200.set_async_forward; A/B)")
+    ap.add_argument("--gt", choices=["u8", "f32"], default="u8",
+                    help="ours, end-to-end step: what travels from the host per step.  u8 (default): the view's colour "
+                         "image as uint8 (6.2 MB at 1080p; images are 8-bit on disk) + camera matrices, the ground-truth "
+                         "feature map from the package's per-camera GPU cache (langsplat_b200.gt_features, SURVEY "
+                         "8(f) row 2).  f32: both ground-truth images as float32 (49.8 MB), as the reference arm does")
+    ap.add_argument("--no-graph", action="store_true",
+                    help="ours, 1 GPU: time the end-to-end step eagerly only (default: the headline e2e replays the "
+                         "step from a CUDA graph, langsplat_b200.graphs.GraphedStep; the eager figure is reported too)")
     ap.add_argument("--separate-levels", action="store_true",
                     help="config 5, ours: three independent forward calls (the reference's call sequence, "
                          "render.py:35-52) instead of forward_feature_levels (A/B)")
@@ -370,7 +378,26 @@ def main():
     gt_c_h = torch.rand(3, H, W, generator=g).pin_memory()
     gt_f_h = torch.rand(3, H, W, generator=g).pin_memory()
     view_h, proj_h, cam_h = cam.viewmatrix.pin_memory(), cam.projmatrix.pin_memory(), cam.campos.pin_memory()
-    h2d_bytes = sum(t.numel() * 4 for t in (gt_c_h, gt_f_h, view_h, proj_h, cam_h))
+    gt_u8 = args.impl == "ours" and args.gt == "u8"
+    if gt_u8:
+        # colour: 8-bit, as the images are stored; feature map: assembled once per camera on the GPU from its seg map
+        # and feature table and kept there (LanguageFeatureCache), so nothing of it travels per step
+        from langsplat_b200.gt_features import LanguageFeatureCache
+        gt_c_h = (gt_c_h * 255.0).round().to(torch.uint8).pin_memory()
+        lf_cache = LanguageFeatureCache(dev)
+        n_seg = 300
+        seg = torch.randint(0, n_seg, (4, H, W), generator=g).float()
+        table = torch.nn.functional.normalize(torch.randn(n_seg, 3, generator=g), dim=-1)
+        lf_cache._inputs["view%d" % my_views[0]] = (seg.to(dev), table.to(dev))
+        gt_f_h = None
+
+    def gt_images(gt_c, gt_f):
+        """The step's ground truth as float32 [3,H,W] tensors on the device."""
+        if not gt_u8:
+            return gt_c, gt_f
+        return gt_c.to(torch.float32).mul_(1.0 / 255.0), lf_cache.get("view%d" % my_views[0], 1, H, W)[0]
+
+    h2d_bytes = sum(t.numel() * t.element_size() for t in (gt_c_h, gt_f_h, view_h, proj_h, cam_h) if t is not None)
 
     copy_stream = torch.cuda.Stream(device=dev)
     # Our arm forms the loss with the package's fused L1 kernels (langsplat_b200.l1_loss, SURVEY 8(f) row 1); the
@@ -390,7 +417,8 @@ def main():
     def issue_gt_copy():
         # fresh buffers from the caching allocator (stream-aware: a block is reused only after its recorded uses end)
         with torch.cuda.stream(copy_stream):
-            gt_c, gt_f = gt_c_h.to(dev, non_blocking=True), gt_f_h.to(dev, non_blocking=True)
+            gt_c = gt_c_h.to(dev, non_blocking=True)
+            gt_f = gt_f_h.to(dev, non_blocking=True) if gt_f_h is not None else gt_c
             cam_d = (view_h.to(dev, non_blocking=True), proj_h.to(dev, non_blocking=True),
                      cam_h.to(dev, non_blocking=True))  # the view's camera travels with its ground truth
             ev = torch.cuda.Event()
@@ -408,6 +436,7 @@ def main():
         for t in (gt_c, gt_f) + cam_d:
             t.record_stream(main)
         main.wait_event(gt_ready)  # this step's view was copied during the previous step
+        gt_c, gt_f = gt_images(gt_c, gt_f)
         rs2 = rs._replace(viewmatrix=cam_d[0], projmatrix=cam_d[1], campos=cam_d[2])
         if fwd_only:
             with torch.no_grad():
@@ -487,6 +516,81 @@ def main():
     ev1.record()
     barrier(world)
     e2e_ms_total = max_over_ranks(ev0.elapsed_time(ev1), world, dev)
+    e2e_eager_ms_total, e2e_mode = e2e_ms_total, "eager"
+
+    # ---- the same end-to-end step replayed from a CUDA graph (ours, one GPU): the asynchronous forward makes no
+    # synchronising call, so forward + loss + backward are captured once and every step is: wait for the prefetched
+    # view, one replay, enqueue the next view's copy, loss.item().  Two captures with their own static view buffers
+    # alternate, so that step k+1's ground truth can be copied while step k still reads its own.  Same bytes copied,
+    # same kernels, same result read back.  (The reference cannot be captured: rasterizer_impl.cu:284 synchronises.)
+    use_graph = (args.impl == "ours" and async_fwd and world == 1 and not fwd_only and not factored
+                 and not args.no_graph)
+    if use_graph:
+        from langsplat_b200.graphs import GraphedStep
+        trainable_t = [params[k] for k in trainable] + [means2D]
+
+        class ViewSet:
+            pass
+
+        sets = []
+        for _i in range(2):
+            st = ViewSet()
+            st.gt_c = torch.empty_like(gt_c_h, device=dev)
+            st.gt_f = torch.empty_like(gt_f_h, device=dev) if gt_f_h is not None else None
+            st.view, st.proj, st.cam = (torch.empty_like(view_h, device=dev), torch.empty_like(proj_h, device=dev),
+                                        torch.empty_like(cam_h, device=dev))
+            st.ready = None
+            for dst, src in ((st.gt_c, gt_c_h), (st.gt_f, gt_f_h), (st.view, view_h), (st.proj, proj_h),
+                             (st.cam, cam_h)):
+                if dst is not None:
+                    dst.copy_(src)
+            r_st = GR(raster_settings=rs._replace(viewmatrix=st.view, projmatrix=st.proj, campos=st.cam))
+
+            def fn(st=st, r_st=r_st):
+                color, feat, radii = r_st(means3D=params["means3D"], means2D=means2D, shs=params["shs"],
+                                          language_feature_precomp=params["language_feature"],
+                                          opacities=params["opacities"], scales=params["scales"],
+                                          rotations=params["rotations"])
+                gt_c, gt_f = gt_images(st.gt_c, st.gt_f)
+                loss = l1_loss(feat, gt_f) if feature_only else l1_loss(color, gt_c) + l1_loss(feat, gt_f)
+                return loss, torch.autograd.grad(loss, trainable_t)
+
+            st.step = GraphedStep(fn)
+            sets.append(st)
+
+        def issue_set_copy(st):
+            with torch.cuda.stream(copy_stream):
+                for dst, src in ((st.gt_c, gt_c_h), (st.gt_f, gt_f_h), (st.view, view_h), (st.proj, proj_h),
+                                 (st.cam, cam_h)):
+                    if dst is not None:
+                        dst.copy_(src, non_blocking=True)
+                st.ready = torch.cuda.Event()
+                st.ready.record(copy_stream)
+
+        counter = [0]
+
+        def e2e_step_graph():
+            st = sets[counter[0] & 1]
+            if st.ready is None:
+                issue_set_copy(st)  # first step only: nothing was prefetched yet
+            torch.cuda.current_stream(dev).wait_event(st.ready)
+            loss, _grads = st.step.replay()
+            issue_set_copy(sets[(counter[0] + 1) & 1])  # next step's view (its set was last read two steps ago)
+            counter[0] += 1
+            return float(loss.item())
+
+        for _ in range(3):
+            e2e_step_graph()
+        barrier(world)
+        ev0.record()
+        for _ in range(args.steps):
+            e2e_step_graph()
+        ev1.record()
+        barrier(world)
+        e2e_ms_total = ev0.elapsed_time(ev1)
+        e2e_mode = "CUDA graph replay (langsplat_b200.graphs.GraphedStep)"
+        for st in sets:
+            st.step.check()
     clocks = sampler.stop() if rank == 0 else None
 
     # ---- per-stage device times (CUDA events inside liblsr.so, same stream), one profiled pass of K steps ----
@@ -530,9 +634,14 @@ def main():
             "e2e": {"value": (world * (len(levels) if fwd_only else 1)) * args.steps / (e2e_ms_total / 1000.0),
                     "unit": "frames/s",
                     "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4,
-                    "what": "per step: one view (camera matrices + GT colour/feature images, 49.8 MB) copied from "
-                            "pinned host memory on a side stream, prefetched one step ahead like a data "
-                            "loader, L1 loss, backward, loss.item()",
+                    "mode": e2e_mode,
+                    "eager_value": (world * (len(levels) if fwd_only else 1)) * args.steps / (e2e_eager_ms_total / 1000.0),
+                    "what": "per step: one view copied from pinned host memory on a side stream, prefetched one step "
+                            "ahead like a data loader ("
+                            + ("camera matrices + the colour image as uint8; the ground-truth feature map comes from "
+                               "the per-camera GPU cache of langsplat_b200.gt_features" if gt_u8 else
+                               "camera matrices + GT colour / feature images as float32")
+                            + "), L1 loss, backward, loss.item()",
                     "loss": ("fused langsplat_b200.l1_loss kernels (SURVEY 8(f) row 1)" if args.impl == "ours" else
                              "LangSplat's own l1_loss, torch.abs(x - gt).mean() (utils/loss_utils.py:17-18)") +
                             " - the two arms differ here: each runs its own public API"},

@@ -150,3 +150,42 @@ def test_forward_and_backward_replay_from_a_cuda_graph():
                 assert rel_err(got[k], want[i]["grads"][k]) < 1e-4, (i, k)  # the path's gradient bar (unordered atomics)
         for pend in R._pending.values():  # (the capture's status stamp cannot be matched to a replay)
             pend.clear()
+
+
+def test_graphed_step_helper():
+    """langsplat_b200.graphs.GraphedStep: capture forward + fused L1 loss + backward once, replay per view."""
+    from langsplat_b200.graphs import GraphedStep
+    scene, cams = syn.make_config(1, n_cameras=2)
+    dev = torch.device("cuda")
+    g = torch.Generator().manual_seed(9)
+    gts = [(torch.rand(3, c.image_height, c.image_width, generator=g).to(dev),
+            torch.rand(3, c.image_height, c.image_width, generator=g).to(dev)) for c in cams]
+    names = ("means3D", "shs", "language_feature", "opacities", "scales", "rotations")
+    params = {k: scene[k].to(dev).requires_grad_(True) for k in names}
+    means2D = torch.zeros_like(params["means3D"], requires_grad=True)
+
+    def iteration(rast, gt_c, gt_f):
+        color, feat, radii = rast(means3D=params["means3D"], means2D=means2D, shs=params["shs"],
+                                  language_feature_precomp=params["language_feature"], opacities=params["opacities"],
+                                  scales=params["scales"], rotations=params["rotations"])
+        loss = lsb.l1_loss(color, gt_c) + lsb.l1_loss(feat, gt_f)
+        return loss, torch.autograd.grad(loss, [params[k] for k in names])
+
+    want = []
+    for cam, (gt_c, gt_f) in zip(cams, gts):  # eager, synchronous
+        loss, grads = iteration(R.GaussianRasterizer(settings_for(cam, dev)), gt_c, gt_f)
+        want.append((loss.item(), [x.clone() for x in grads]))
+    view, proj, campos = (cams[0].viewmatrix.to(dev).clone(), cams[0].projmatrix.to(dev).clone(),
+                          cams[0].campos.to(dev).clone())
+    gt_c, gt_f = gts[0][0].clone(), gts[0][1].clone()
+    rast = R.GaussianRasterizer(settings_for(cams[0], dev)._replace(viewmatrix=view, projmatrix=proj, campos=campos))
+    step = GraphedStep(lambda: iteration(rast, gt_c, gt_f))
+    assert not lsb.rasterizer._AsyncConfig.enabled  # the switch is restored after the capture
+    for i in (1, 0, 1):
+        view.copy_(cams[i].viewmatrix.to(dev)); proj.copy_(cams[i].projmatrix.to(dev)); campos.copy_(cams[i].campos.to(dev))
+        gt_c.copy_(gts[i][0]); gt_f.copy_(gts[i][1])
+        loss, grads = step.replay()
+        step.check()
+        assert abs(loss.item() - want[i][0]) <= 1e-6 * abs(want[i][0])
+        for got, ref in zip(grads, want[i][1]):
+            assert rel_err(got, ref) < 1e-4
