@@ -517,6 +517,7 @@ def main():
     barrier(world)
     e2e_ms_total = max_over_ranks(ev0.elapsed_time(ev1), world, dev)
     e2e_eager_ms_total, e2e_mode = e2e_ms_total, "eager"
+    value_mode, value_eager_ms_total, fwd_eager_ms = "eager launches", ms_total, fwd_ms
 
     # ---- the same end-to-end step replayed from a CUDA graph (ours, one GPU): the asynchronous forward makes no
     # synchronising call, so forward + loss + backward are captured once and every step is: wait for the prefetched
@@ -527,7 +528,49 @@ def main():
                  and not args.no_graph)
     if use_graph:
         from langsplat_b200.graphs import GraphedStep
+        # fresh leaves: autograd nodes of the eager runs above belong to the default stream, a capture must not touch it
+        params = {k: v.detach().clone().requires_grad_(v.requires_grad) for k, v in params.items()}
+        means2D = torch.zeros((P, 3), device=dev, requires_grad=True)
         trainable_t = [params[k] for k in trainable] + [means2D]
+        torch.cuda.synchronize()
+
+        # `value` and the forward-only time as graph replays too: same kernels on the same resident inputs, but the
+        # device-timed figure no longer depends on how fast this host's Python enqueues ~30 launches per step (shared
+        # hosts: eager runs of the same build measured 1.77 ms and 3.02 ms per step minutes apart, kernels unchanged)
+        def value_fn():
+            color, feat, radii = rast(means3D=params["means3D"], means2D=means2D, shs=params["shs"],
+                                      language_feature_precomp=params["language_feature"],
+                                      opacities=params["opacities"], scales=params["scales"],
+                                      rotations=params["rotations"])
+            if feature_only:
+                return torch.autograd.grad([feat], trainable_t, [dfeat])
+            return torch.autograd.grad([color, feat], trainable_t, [dcol, dfeat])
+
+        def fwd_fn():
+            with torch.no_grad():
+                return rast(means3D=params["means3D"], means2D=means2D, shs=params["shs"],
+                            language_feature_precomp=params["language_feature"], opacities=params["opacities"],
+                            scales=params["scales"], rotations=params["rotations"])
+
+        n0 = lib.lsr_launch_count()
+        g_value = GraphedStep(value_fn, warmup=1)
+        launches_per_step = (lib.lsr_launch_count() - n0) // 2  # one warm-up run + the capture
+        g_fwd = GraphedStep(fwd_fn, warmup=1)
+        for g_, label in ((g_value, "value"), (g_fwd, "fwd")):
+            for _ in range(3):
+                g_.replay()
+            torch.cuda.synchronize()
+            ev0.record()
+            for _ in range(args.steps):
+                g_.replay()
+            ev1.record()
+            torch.cuda.synchronize()
+            g_.check()
+            if label == "value":
+                ms_total, launches = ev0.elapsed_time(ev1), launches_per_step * args.steps
+            else:
+                fwd_ms = ev0.elapsed_time(ev1) / args.steps
+        value_mode = "CUDA graph replay (langsplat_b200.graphs.GraphedStep)"
 
         class ViewSet:
             pass
@@ -631,6 +674,9 @@ def main():
                              if async_fwd else "one host read-back of the instance count per frame, like the reference "
                                                "(rasterizer_impl.cu:284)"),
             "fwd_only_ms_per_frame": fwd_ms, "clocks": clocks,
+            "value_mode": value_mode,
+            "value_eager": frames_per_step * args.steps / (value_eager_ms_total / 1000.0),
+            "fwd_only_ms_per_frame_eager": fwd_eager_ms,
             "e2e": {"value": (world * (len(levels) if fwd_only else 1)) * args.steps / (e2e_ms_total / 1000.0),
                     "unit": "frames/s",
                     "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4,

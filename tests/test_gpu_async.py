@@ -175,6 +175,12 @@ def test_graphed_step_helper():
     for cam, (gt_c, gt_f) in zip(cams, gts):  # eager, synchronous
         loss, grads = iteration(R.GaussianRasterizer(settings_for(cam, dev)), gt_c, gt_f)
         want.append((loss.item(), [x.clone() for x in grads]))
+    del loss, grads
+    # fresh leaves for the captured iteration: autograd nodes created by the eager runs above belong to the default
+    # stream, and a capture must not make the legacy stream depend on the capturing one
+    params = {k: v.detach().clone().requires_grad_(True) for k, v in params.items()}
+    means2D = torch.zeros_like(params["means3D"], requires_grad=True)
+    torch.cuda.synchronize()
     view, proj, campos = (cams[0].viewmatrix.to(dev).clone(), cams[0].projmatrix.to(dev).clone(),
                           cams[0].campos.to(dev).clone())
     gt_c, gt_f = gts[0][0].clone(), gts[0][1].clone()
