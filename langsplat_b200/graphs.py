@@ -63,14 +63,14 @@ class GraphedStep:
         """Waits for the device and raises if a replayed frame outgrew its instance list (its images were NaN-filled)
         or tripped the prefiltered trap."""
         torch.cuda.synchronize()
-        for st in self._frames:
-            words = st["status"][1] if st.get("status") is not None else None
+        for st in self._frames:  # rasterizer._AsyncFrame records; their pinned status words are rewritten by every replay
+            words = st.status[1] if st.status is not None else None
             if words is None:
                 continue
             flags, count = int(words[L.STATUS_FLAGS]), int(words[L.STATUS_NUM_RENDERED])
             if flags & L.STATUS_FLAG_OVERFLOW:
                 raise R.LsrError(f"graphed step: a frame has {count} Gaussian/tile instances but the captured instance "
-                                 f"list holds {st['capacity']}; its images were filled with NaN.  Capture again after "
+                                 f"list holds {st.capacity}; its images were filled with NaN.  Capture again after "
                                  "reserve_instances(device, count) or with a larger capacity_margin.")
             if flags & L.STATUS_FLAG_PREFILTERED:
                 raise R.LsrError("Point is filtered although prefiltered is set. This shouldn't happen!")

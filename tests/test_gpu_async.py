@@ -44,7 +44,7 @@ def test_async_forward_is_bit_identical(cfg, P, W, H):
     assert s0["num_rendered"] is not None
     with lsb.async_forward():
         c1, f1, r1, s1 = _forward_state(scene, cam)
-        assert s1["num_rendered"] is None and s1["status"] is not None  # nothing was read back
+        assert s1["num_rendered"] is None and s1["async"].status is not None  # nothing was read back
         a1 = R.debug_arrays(s1)  # (waits for the status words)
     assert s1["num_rendered"] == s0["num_rendered"]
     assert torch.equal(c0, c1) and torch.equal(f0, f1) and torch.equal(r0, r1)
