@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define LSR_VERSION 1
+#define LSR_VERSION 2
 
 typedef enum lsr_status {
   LSR_OK = 0,
@@ -319,6 +319,8 @@ int lsr_adam_step(int32_t n_tensors, const lsr_adam_tensor* tensors, int64_t ste
 #define LSR_DECODE_FP32 0
 #define LSR_DECODE_TF32 1
 #define LSR_DECODE_F16 2
+#define LSR_DECODE_BF16X2 3 /* tensor cores at the reference's arithmetic: every fp32 operand carried as two bf16 numbers
+                               (hi + lo, 16 mantissa bits), every product as three bf16 MMAs with fp32 accumulation */
 typedef struct lsr_decoder {
   int32_t n_layers;
   int32_t dims[LSR_DECODER_MAX_LAYERS + 1];
@@ -326,6 +328,7 @@ typedef struct lsr_decoder {
   const float* bias[LSR_DECODER_MAX_LAYERS];
   const void* packed_tf32;
   const void* packed_f16;
+  const void* packed_bf16x2;
 } lsr_decoder;
 size_t lsr_decoder_packed_bytes(const lsr_decoder* dec, int32_t precision);
 int lsr_decoder_pack(const lsr_decoder* dec, int32_t precision, void* packed, void* stream);

@@ -59,13 +59,13 @@ class AdamTensor(ctypes.Structure):  # lsr_adam_tensor
 
 
 ADAM_MAX_TENSORS = 8
-DECODER_MAX_LAYERS, DECODER_MAX_PHRASES, DECODE_FP32, DECODE_TF32, DECODE_F16 = 8, 16, 0, 1, 2
+DECODER_MAX_LAYERS, DECODER_MAX_PHRASES, DECODE_FP32, DECODE_TF32, DECODE_F16, DECODE_BF16X2 = 8, 16, 0, 1, 2, 3
 
 
 class Decoder(ctypes.Structure):  # lsr_decoder
     _fields_ = [("n_layers", c_int32), ("dims", c_int32 * (DECODER_MAX_LAYERS + 1)),
                 ("weight", c_void_p * DECODER_MAX_LAYERS), ("bias", c_void_p * DECODER_MAX_LAYERS),
-                ("packed_tf32", c_void_p), ("packed_f16", c_void_p)]
+                ("packed_tf32", c_void_p), ("packed_f16", c_void_p), ("packed_bf16x2", c_void_p)]
 
 
 EXPORTS = {

@@ -369,7 +369,7 @@ int lsr_debug_decode_trace(void* device_buffer) {
 }
 
 static bool decoder_tc_precision(int32_t precision) {
-  return precision == LSR_DECODE_TF32 || precision == LSR_DECODE_F16;
+  return precision == LSR_DECODE_TF32 || precision == LSR_DECODE_F16 || precision == LSR_DECODE_BF16X2;
 }
 
 size_t lsr_decoder_packed_bytes(const lsr_decoder* dec, int32_t precision) {

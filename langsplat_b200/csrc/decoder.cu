@@ -172,10 +172,18 @@ constexpr int TC_TMEM_COLS = 256;
 #define TC_F16_STAGGER 12000  // measured (f16, 1440x1080): 0 -> 1.083 ms, 6000 -> 1.070, 12000 -> 1.003, 20000 -> 1.027
 #endif
 
-template <bool F16>
+// Operand modes of the tensor-core kernel.  TC_BX2 ("split bf16"): every fp32 operand x is carried as two bf16 numbers,
+// hi = bf16(x) and lo = bf16(x - hi) (16 mantissa bits together), and every product as three bf16 MMAs with fp32
+// accumulation, hi*hi + lo*hi + hi*lo (the lo*lo term is 2^-18 relative) — fp32-class results (the reference runs fp32
+// SGEMMs) at tensor-core speed: the same operand bytes as TF32, 1.5x its MMA instructions.
+enum { TC_TF32 = 0, TC_F16 = 1, TC_BX2 = 2 };
+template <int MODE>
 struct TcCfg {
-  static constexpr int E = F16 ? 8 : 4;                       // elements per 16-byte K chunk
-  static constexpr int A_BYTES = TC_M * TC_MAXK * (F16 ? 2 : 4);
+  static constexpr bool F16 = MODE == TC_F16, BX2 = MODE == TC_BX2;
+  static constexpr int E = MODE == TC_TF32 ? 4 : 8;           // elements per 16-byte K chunk
+  static constexpr int PARTS = BX2 ? 2 : 1;                   // operand parts (hi, lo)
+  static constexpr int A_PART_BYTES = TC_M * TC_MAXK * (MODE == TC_TF32 ? 4 : 2);
+  static constexpr int A_BYTES = A_PART_BYTES * PARTS;
   static constexpr int STAGE_BYTES = F16 ? 16384 : TC_TF32_STAGE_BYTES;
   static constexpr int STAGES = 3;                            // f16: 64 + 48 = 112 KB per CTA -> two CTAs per SM
   static constexpr int BAR_OFF = A_BYTES + STAGES * STAGE_BYTES;
@@ -183,11 +191,31 @@ struct TcCfg {
   static constexpr int CTAS_PER_SM = F16 ? 2 : 1;
 };
 
+// fp32 -> (hi, lo) bf16 pair, round to nearest even; bf16 keeps fp32's exponent range, so nothing is clamped
+__device__ __forceinline__ uint32_t bf16_rn_bits(float x) {
+  const uint32_t u = __float_as_uint(x);
+  return (u + 0x7FFFu + ((u >> 16) & 1u)) >> 16;
+}
+__device__ __forceinline__ void bf16_split(float x, uint32_t& hi, uint32_t& lo) {
+  hi = bf16_rn_bits(x);
+  lo = bf16_rn_bits(x - __uint_as_float(hi << 16));
+}
+// eight floats -> one 16-byte chunk of hi parts and one of lo parts
+__device__ __forceinline__ void bf16_split8(const float* v, uint4& hi, uint4& lo) {
+  uint32_t h[8], l[8];
+#pragma unroll
+  for (int j = 0; j < 8; j++) bf16_split(v[j], h[j], l[j]);
+  hi = make_uint4(h[0] | (h[1] << 16), h[2] | (h[3] << 16), h[4] | (h[5] << 16), h[6] | (h[7] << 16));
+  lo = make_uint4(l[0] | (l[1] << 16), l[2] | (l[3] << 16), l[4] | (l[5] << 16), l[6] | (l[7] << 16));
+}
+
 // fp32 -> nearest TF32 (10 mantissa bits), so the tensor core's truncation of the operands is exact
 __device__ __forceinline__ uint32_t tf32_rn(float x) { return (__float_as_uint(x) + 0x1000u) & 0xFFFFE000u; }
 
-__global__ void pack_weights_kernel(const float* __restrict__ W, int K, int Np, int Kp, int f16, uint4* __restrict__ dst) {
-  const int E = f16 ? 8 : 4;
+// mode TC_BX2: the hi and lo chunks of K chunk kc sit next to each other, [Kp/8][2][Np] 16-byte chunks, so that a K
+// slice (hi and lo) is one contiguous run of bytes for the bulk copy
+__global__ void pack_weights_kernel(const float* __restrict__ W, int K, int Np, int Kp, int mode, uint4* __restrict__ dst) {
+  const int E = mode == TC_TF32 ? 4 : 8;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (Kp / E) * Np) return;
   const int kc = i / Np, o = i - kc * Np;
@@ -197,8 +225,15 @@ __global__ void pack_weights_kernel(const float* __restrict__ W, int K, int Np, 
     const int k = kc * E + j;
     v[j] = (j < E && k < K) ? __ldg(W + (size_t)o * K + k) : 0.0f;
   }
+  if (mode == TC_BX2) {
+    uint4 hi, lo;
+    bf16_split8(v, hi, lo);
+    dst[(size_t)(2 * kc) * Np + o] = hi;
+    dst[(size_t)(2 * kc + 1) * Np + o] = lo;
+    return;
+  }
   uint4 r;
-  if (f16) {
+  if (mode == TC_F16) {
     __half2 h0 = __floats2half2_rn(v[0], v[1]), h1 = __floats2half2_rn(v[2], v[3]);
     __half2 h2 = __floats2half2_rn(v[4], v[5]), h3 = __floats2half2_rn(v[6], v[7]);
     r = make_uint4(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1),
@@ -214,9 +249,9 @@ __global__ void pack_weights_kernel(const float* __restrict__ W, int K, int Np, 
 // n_ph x NL FMAs per pixel on the FP32 pipe.  Writes PW in the packed operand layout [Kp/E][16][E] (rows past n_ph are
 // zeros) and pb[16] = P b.
 __global__ void fold_phrases_kernel(const float* __restrict__ P, int n_ph, const float* __restrict__ W,
-                                    const float* __restrict__ b, int NL, int K, int Kp, int f16,
+                                    const float* __restrict__ b, int NL, int K, int Kp, int mode,
                                     uint4* __restrict__ dst, float* __restrict__ pb) {
-  const int E = f16 ? 8 : 4;
+  const int E = mode == TC_TF32 ? 4 : 8;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int items = (Kp / E) * 16;
   if (i < items) {
@@ -233,7 +268,14 @@ __global__ void fold_phrases_kernel(const float* __restrict__ P, int n_ph, const
       }
     }
     uint4 r;
-    if (f16) {
+    if (mode == TC_BX2) {  // [Kp/8][2][16] chunks, as pack_weights_kernel lays a pass out
+      uint4 hi, lo;
+      bf16_split8(acc, hi, lo);
+      dst[(2 * kc) * 16 + j] = hi;
+      dst[(2 * kc + 1) * 16 + j] = lo;
+      return;
+    }
+    if (mode == TC_F16) {
       __half2 h0 = __floats2half2_rn(acc[0], acc[1]), h1 = __floats2half2_rn(acc[2], acc[3]);
       __half2 h2 = __floats2half2_rn(acc[4], acc[5]), h3 = __floats2half2_rn(acc[6], acc[7]);
       r = make_uint4(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1),
@@ -307,10 +349,10 @@ __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.a
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
-template <bool F16>
+template <int MODE>
 __device__ __forceinline__ void tc_mma(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
                                        uint32_t accumulate) {
-  if constexpr (F16) {
+  if constexpr (MODE != TC_TF32) {  // fp16 and bf16 operands both run as kind::f16 (the formats are in idesc)
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "setp.ne.b32 p, %4, 0;\n\t"
@@ -357,15 +399,17 @@ __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
   return *reinterpret_cast<uint32_t*>(&h);
 }
 
-template <bool F16>
-__global__ void __launch_bounds__(TC_M, TcCfg<F16>::CTAS_PER_SM)
+template <int MODE>
+__global__ void __launch_bounds__(TC_M, TcCfg<MODE>::CTAS_PER_SM)
 decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in, int64_t n, float* __restrict__ out,
                  const float* __restrict__ phrases, int n_pos, int n_neg, float* __restrict__ relev,
                  long long* __restrict__ trace) {
-  using C = TcCfg<F16>;
+  using C = TcCfg<MODE>;
   constexpr int E = C::E;
+  constexpr bool F16 = C::F16, BX2 = C::BX2;
   extern __shared__ __align__(1024) uint8_t tsm[];
-  uint4* A = reinterpret_cast<uint4*>(tsm);  // [K/E][128 rows] 16-byte chunks
+  uint4* A = reinterpret_cast<uint4*>(tsm);  // [K/E][128 rows] 16-byte chunks (TC_BX2: the hi parts)
+  uint4* A_lo = reinterpret_cast<uint4*>(tsm + C::A_PART_BYTES);  // TC_BX2: the lo parts, same layout
   uint8_t* stages = tsm + C::A_BYTES;
   uint64_t* bars = reinterpret_cast<uint64_t*>(tsm + C::BAR_OFF);  // full[STAGES], empty[STAGES], done
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * C::STAGES + 1);
@@ -419,7 +463,15 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
           const int k = kc * E + j;
           v[j] = (live && k < d0) ? __ldg(in + pix * d0 + k) : 0.0f;
         }
-        if constexpr (F16) {
+        if constexpr (BX2) {
+          float v8[8];
+#pragma unroll
+          for (int j = 0; j < 8; j++) v8[j] = v[j % E];
+          uint4 hi, lo;
+          bf16_split8(v8, hi, lo);
+          A[kc * TC_M + tid] = hi;
+          A_lo[kc * TC_M + tid] = lo;
+        } else if constexpr (F16) {
           auto cv = [](float x, float y) {
             __half2 h = __floats2half2_rn(fminf(fmaxf(x, -65504.0f), 65504.0f), fminf(fmaxf(y, -65504.0f), 65504.0f));
             return *reinterpret_cast<uint32_t*>(&h);
@@ -453,7 +505,7 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
           const TcSlice q = a.sl[next_load];
           const uint32_t st = it_load % C::STAGES, use = it_load / C::STAGES;
           mbar_wait(empty0 + 8 * st, (use & 1) ^ 1);
-          const uint32_t bytes = (uint32_t)q.nch * (uint32_t)a.pass_np[q.pass] * 16u;
+          const uint32_t bytes = (uint32_t)q.nch * (uint32_t)a.pass_np[q.pass] * 16u * (uint32_t)C::PARTS;
           const uint8_t* src = a.pass_layer[q.pass] == a.n_layers ? reinterpret_cast<const uint8_t*>(a.fold) : packed;
           if (elect_one()) {
             mbar_expect_tx(full0 + 8 * st, bytes);
@@ -465,10 +517,14 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
         }
       } else if (warp_u == 0) {
         // MMA issuer warp
-        const uint32_t fmt = F16 ? 0u : 2u;
+        // operand formats: kind::tf32 -> 2 (TF32); kind::f16 -> 0 (F16) or 1 (BF16)
+        const uint32_t fmt = MODE == TC_TF32 ? 2u : (BX2 ? 1u : 0u);
         const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(Np >> 3) << 17) | ((TC_M >> 4) << 24);
-        const uint32_t a_lbo = TC_M * 16, b_lbo = (uint32_t)Np * 16, sbo = 128;
+        // byte distance of the two 16-byte K chunks of one instruction (TC_BX2: a weight chunk's hi and lo parts sit
+        // next to each other, so consecutive K chunks of one part are two rows of Np chunks apart)
+        const uint32_t a_lbo = TC_M * 16, b_lbo = (uint32_t)Np * 16 * (uint32_t)C::PARTS, sbo = 128;
         const uint64_t a_step = (uint64_t)((2 * a_lbo) >> 4), b_step = (uint64_t)((2 * b_lbo) >> 4);
+        const uint64_t a_lo_ofs = (uint64_t)(C::A_PART_BYTES >> 4), b_lo_ofs = (uint64_t)(((uint32_t)Np * 16) >> 4);
         for (int s = s_begin; s < s_end; s++) {
           const TcSlice q = a.sl[s];
           const uint32_t st = it_mma % C::STAGES, use = it_mma / C::STAGES;
@@ -481,8 +537,12 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
           if (elect_one()) {
 #pragma unroll 4
             for (int j = 0; j < steps; j++) {
-              tc_mma<F16>(tmem, ad, bd, idesc, acc);
+              tc_mma<MODE>(tmem, ad, bd, idesc, acc);  // (hi) x (hi)
               acc = 1u;
+              if constexpr (BX2) {
+                tc_mma<MODE>(tmem, ad + a_lo_ofs, bd, idesc, 1u);  // lo x hi
+                tc_mma<MODE>(tmem, ad, bd + b_lo_ofs, idesc, 1u);  // hi x lo
+              }
               ad += a_step;
               bd += b_step;
             }
@@ -528,7 +588,15 @@ decode_tc_kernel(const __grid_constant__ TcArgs a, const float* __restrict__ in,
             v[q4 * 4 + 2] = fmaxf(v[q4 * 4 + 2] + b4.z, 0.0f);
             v[q4 * 4 + 3] = fmaxf(v[q4 * 4 + 3] + b4.w, 0.0f);
           }
-          if constexpr (F16) {
+          if constexpr (BX2) {
+            uint4 hi, lo;
+            bf16_split8(v, hi, lo);
+            A[((c >> 3) + 0) * TC_M + tid] = hi;
+            A_lo[((c >> 3) + 0) * TC_M + tid] = lo;
+            bf16_split8(v + 8, hi, lo);
+            A[((c >> 3) + 1) * TC_M + tid] = hi;
+            A_lo[((c >> 3) + 1) * TC_M + tid] = lo;
+          } else if constexpr (F16) {
             A[((c >> 3) + 0) * TC_M + tid] =
                 make_uint4(pack_h2(v[0], v[1]), pack_h2(v[2], v[3]), pack_h2(v[4], v[5]), pack_h2(v[6], v[7]));
             A[((c >> 3) + 1) * TC_M + tid] =
@@ -612,40 +680,47 @@ struct PassPlan {
   size_t off16[TC_MAX_PASSES];
   size_t total16;
 };
-PassPlan plan_passes(const lsr_decoder* d, bool f16) {
+PassPlan plan_passes(const lsr_decoder* d, int mode) {
   PassPlan pl{};
-  const int E = f16 ? 8 : 4;
+  const int E = mode == TC_TF32 ? 4 : 8, parts = mode == TC_BX2 ? 2 : 1;
   size_t off = 0;
   for (int l = 0; l < d->n_layers; l++) {
     const int K = d->dims[l], N = d->dims[l + 1], Kp = (K + 2 * E - 1) & ~(2 * E - 1);
-    const int parts = N > 256 ? 2 : 1;
-    for (int h = 0; h < parts; h++) {
+    const int halves = N > 256 ? 2 : 1;
+    for (int h = 0; h < halves; h++) {
       const int i = pl.n++;
-      pl.layer[i] = l; pl.np[i] = N / parts; pl.n0[i] = h * (N / parts); pl.kp[i] = Kp; pl.off16[i] = off;
-      off += (size_t)(Kp / E) * (N / parts);
+      pl.layer[i] = l; pl.np[i] = N / halves; pl.n0[i] = h * (N / halves); pl.kp[i] = Kp; pl.off16[i] = off;
+      off += (size_t)(Kp / E) * (N / halves) * parts;
     }
   }
   pl.total16 = off;
   return pl;
 }
 
-template <bool F16>
+inline int tc_mode_of(int precision) {
+  return precision == LSR_DECODE_F16 ? TC_F16 : (precision == LSR_DECODE_BF16X2 ? TC_BX2 : TC_TF32);
+}
+inline const void* packed_of(const lsr_decoder* d, int precision) {
+  return precision == LSR_DECODE_F16 ? d->packed_f16 : (precision == LSR_DECODE_BF16X2 ? d->packed_bf16x2 : d->packed_tf32);
+}
+
+template <int MODE>
 cudaError_t launch_tc(const lsr_decoder* d, const float* in, int64_t n, float* out, const float* phrases, int n_pos,
                       int n_neg, float* relev, void* work, cudaStream_t s) {
-  using C = TcCfg<F16>;
+  using C = TcCfg<MODE>;
   TcArgs a{};
   a.n_layers = d->n_layers;
   for (int l = 0; l <= d->n_layers; l++) a.dims[l] = d->dims[l];
   for (int l = 0; l < d->n_layers; l++) a.bias[l] = d->bias[l];
-  a.packed = F16 ? d->packed_f16 : d->packed_tf32;
-  const PassPlan pl = plan_passes(d, F16);
+  a.packed = MODE == TC_F16 ? d->packed_f16 : (MODE == TC_BX2 ? d->packed_bf16x2 : d->packed_tf32);
+  const PassPlan pl = plan_passes(d, MODE);
   const int last = d->n_layers - 1, K7 = d->dims[last], K7p = (K7 + 2 * C::E - 1) & ~(2 * C::E - 1);
   if (phrases) {  // PW and P b into the work buffer: [K7p/E][16] 16-byte chunks, then 16 floats
     uint4* pw = reinterpret_cast<uint4*>(work);
-    float* pb = reinterpret_cast<float*>(pw + (size_t)(K7p / C::E) * 16);
+    float* pb = reinterpret_cast<float*>(pw + (size_t)(K7p / C::E) * 16 * C::PARTS);
     const int items = (K7p / C::E) * 16 + 16;
     fold_phrases_kernel<<<(items + 63) / 64, 64, 0, s>>>(phrases, n_pos + n_neg, d->weight[last], d->bias[last],
-                                                        d->dims[d->n_layers], K7, K7p, F16 ? 1 : 0, pw, pb);
+                                                        d->dims[d->n_layers], K7, K7p, MODE, pw, pb);
     count_launch();
     a.fold = pw;
     a.fold_b = pb;
@@ -655,12 +730,12 @@ cudaError_t launch_tc(const lsr_decoder* d, const float* in, int64_t n, float* o
     if (np >= TC_MAX_PASSES) return false;
     a.pass_layer[np] = layer; a.pass_n0[np] = n0; a.pass_np[np] = Np; a.pass_mode[np] = mode;
     const int chunks = Kp / C::E;
-    int per = (C::STAGE_BYTES / (Np * 16)) & ~1;
+    int per = (C::STAGE_BYTES / (Np * 16 * C::PARTS)) & ~1;
     if (per < 2) per = 2;
     for (int c = 0; c < chunks; c += per) {
       if (ns >= TC_MAX_SLICES) return false;
       TcSlice& q = a.sl[ns++];
-      q.off16 = (uint32_t)(off16 + (size_t)c * Np);
+      q.off16 = (uint32_t)(off16 + (size_t)c * Np * C::PARTS);
       q.nch = (uint16_t)(chunks - c < per ? chunks - c : per);
       q.c0 = (uint8_t)c;
       q.pass = (uint8_t)np;
@@ -697,12 +772,12 @@ cudaError_t launch_tc(const lsr_decoder* d, const float* in, int64_t n, float* o
     a.stagger = stagger;
   }
   {  // per launch: the attribute is per device, and a process may use several
-    cudaError_t e = cudaFuncSetAttribute(decode_tc_kernel<F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+    cudaError_t e = cudaFuncSetAttribute(decode_tc_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
     if (e != cudaSuccess) return e;
   }
   const int64_t tiles = (n + TC_M - 1) / TC_M, slots = (int64_t)sm_count() * C::CTAS_PER_SM;
   const int grid = (int)(tiles < slots ? tiles : slots);
-  decode_tc_kernel<F16><<<grid, TC_M, C::SMEM, s>>>(a, in, n, out, phrases, n_pos, n_neg, relev, g_dec_trace);
+  decode_tc_kernel<MODE><<<grid, TC_M, C::SMEM, s>>>(a, in, n, out, phrases, n_pos, n_neg, relev, g_dec_trace);
   count_launch();
   return cudaGetLastError();
 }
@@ -712,24 +787,24 @@ cudaError_t launch_tc(const lsr_decoder* d, const float* in, int64_t n, float* o
 void decoder_set_trace(void* dev_buf) { g_dec_trace = reinterpret_cast<long long*>(dev_buf); }
 
 size_t decoder_packed_bytes(const lsr_decoder* d, int precision) {
-  return plan_passes(d, precision == LSR_DECODE_F16).total16 * 16;
+  return plan_passes(d, tc_mode_of(precision)).total16 * 16;
 }
 
 void launch_decoder_pack(const lsr_decoder* d, int precision, void* packed, cudaStream_t s) {
-  const bool f16 = precision == LSR_DECODE_F16;
-  const PassPlan pl = plan_passes(d, f16);
+  const int mode = tc_mode_of(precision);
+  const PassPlan pl = plan_passes(d, mode);
   for (int p = 0; p < pl.n; p++) {
     const int l = pl.layer[p], K = d->dims[l];
-    const int items = (pl.kp[p] / (f16 ? 8 : 4)) * pl.np[p];
+    const int items = (pl.kp[p] / (mode == TC_TF32 ? 4 : 8)) * pl.np[p];
     pack_weights_kernel<<<(items + 255) / 256, 256, 0, s>>>(d->weight[l] + (size_t)pl.n0[p] * K, K, pl.np[p], pl.kp[p],
-                                                            f16 ? 1 : 0, reinterpret_cast<uint4*>(packed) + pl.off16[p]);
+                                                            mode, reinterpret_cast<uint4*>(packed) + pl.off16[p]);
     count_launch();
   }
 }
 
 // Why a tensor-core variant cannot take this decoder (null if it can).
 const char* decoder_tc_unsupported(const lsr_decoder* d, int precision) {
-  const void* packed = precision == LSR_DECODE_F16 ? d->packed_f16 : d->packed_tf32;
+  const void* packed = packed_of(d, precision);
   if (!packed) return "the packed weights of this precision are null (call lsr_decoder_pack first)";
   if ((uintptr_t)packed & 15) return "packed weights must be 16-byte aligned";
   for (int l = 0; l < d->n_layers; l++) {
@@ -743,8 +818,9 @@ const char* decoder_tc_unsupported(const lsr_decoder* d, int precision) {
 
 cudaError_t launch_decode(const lsr_decoder* d, const float* in, int64_t n, int precision, float* out,
                           const float* phrases, int n_pos, int n_neg, float* relev, void* work, cudaStream_t s) {
-  if (precision == LSR_DECODE_TF32) return launch_tc<false>(d, in, n, out, phrases, n_pos, n_neg, relev, work, s);
-  if (precision == LSR_DECODE_F16) return launch_tc<true>(d, in, n, out, phrases, n_pos, n_neg, relev, work, s);
+  if (precision == LSR_DECODE_TF32) return launch_tc<TC_TF32>(d, in, n, out, phrases, n_pos, n_neg, relev, work, s);
+  if (precision == LSR_DECODE_F16) return launch_tc<TC_F16>(d, in, n, out, phrases, n_pos, n_neg, relev, work, s);
+  if (precision == LSR_DECODE_BF16X2) return launch_tc<TC_BX2>(d, in, n, out, phrases, n_pos, n_neg, relev, work, s);
   DecArgs a{};
   a.n_layers = d->n_layers;
   for (int l = 0; l <= d->n_layers; l++) a.dims[l] = d->dims[l];

@@ -7,9 +7,13 @@ eval/openclip_encoder.py:42-56, 96-111).  `FeatureDecoder` mirrors those entry p
 (csrc/decoder.cu, `lsr_decode`): `decode(x)` returns the unit 512-d features, `get_max_across(sem_map3)` goes from the
 3-d maps straight to the relevancy maps without ever materialising the 512-d features in HBM.
 
-precision="tf32" (default) and "f16" run the layers on the tcgen05 tensor cores with fp32 accumulation in TMEM —
-operands as TF32 (fp32 truncated to 10 mantissa bits) or as fp16 (rounded to nearest, clamped to +-65504; faster:
-half the bytes, twice the MMA rate, two CTAs per SM); precision="fp32" is the IEEE-fp32 variant on the FP32 pipe.
+Precisions, all with fp32 accumulation (in TMEM for the tensor-core variants):
+  "bf16x2" (default) — tcgen05 tensor cores at the reference's arithmetic: the reference runs fp32 SGEMMs, so every fp32
+      operand is carried as two bf16 numbers (hi + lo, 16 mantissa bits) and every product as three bf16 MMAs; results
+      agree with the fp32 chain to ~1e-6 (the bars of the fp32 variant);
+  "tf32" / "f16" — one MMA per product, operands rounded to 10 mantissa bits (TF32, or fp16 clamped to +-65504: half the
+      bytes, twice the MMA rate, two CTAs per SM): faster, errors ~1e-4;
+  "fp32" — IEEE fp32 on the FP32 pipe.
 CUDA only; no CPU path.
 """
 from __future__ import annotations
@@ -22,7 +26,7 @@ import torch
 from . import _lib as L
 from .rasterizer import LsrError
 
-_PRECISIONS = {"fp32": L.DECODE_FP32, "tf32": L.DECODE_TF32, "f16": L.DECODE_F16}
+_PRECISIONS = {"fp32": L.DECODE_FP32, "tf32": L.DECODE_TF32, "f16": L.DECODE_F16, "bf16x2": L.DECODE_BF16X2}
 
 
 def _ptr(t: Optional[torch.Tensor]):
@@ -35,7 +39,7 @@ class FeatureDecoder:
     weights[l]: nn.Linear weight [out, in]; biases[l]: [out] (CUDA float32).  `from_state_dict` takes the checkpoint the
     reference saves (autoencoder/train.py: keys `decoder.<i>.weight/bias`, ReLU modules interleaved)."""
 
-    def __init__(self, weights: Sequence[torch.Tensor], biases: Sequence[torch.Tensor], precision: str = "tf32"):
+    def __init__(self, weights: Sequence[torch.Tensor], biases: Sequence[torch.Tensor], precision: str = "bf16x2"):
         if len(weights) != len(biases) or not 1 <= len(weights) <= L.DECODER_MAX_LAYERS:
             raise LsrError(f"FeatureDecoder: 1..{L.DECODER_MAX_LAYERS} (weight, bias) pairs expected")
         if precision not in _PRECISIONS:
@@ -60,13 +64,13 @@ class FeatureDecoder:
             d.dims[l + 1] = w.shape[0]
             d.weight[l] = w.data_ptr()
             d.bias[l] = b.data_ptr()
-        d.packed_tf32 = d.packed_f16 = None
+        d.packed_tf32 = d.packed_f16 = d.packed_bf16x2 = None
         self._desc = d
         self._packed = {}
         self.pos_embeds = self.neg_embeds = self._phrases = None
 
     @classmethod
-    def from_state_dict(cls, state_dict, device="cuda", precision: str = "tf32"):
+    def from_state_dict(cls, state_dict, device="cuda", precision: str = "bf16x2"):
         idx = sorted({int(k.split(".")[1]) for k in state_dict if k.startswith("decoder.") and k.endswith(".weight")})
         if not idx:
             raise LsrError("no decoder.<i>.weight entries in the state dict")
@@ -89,6 +93,8 @@ class FeatureDecoder:
             self._packed[prec] = packed
             if prec == L.DECODE_F16:
                 self._desc.packed_f16 = packed.data_ptr()
+            elif prec == L.DECODE_BF16X2:
+                self._desc.packed_bf16x2 = packed.data_ptr()
             else:
                 self._desc.packed_tf32 = packed.data_ptr()
 

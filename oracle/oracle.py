@@ -309,6 +309,18 @@ def _round_operand(a, operand):
     return u.view(np.float32).astype(np.float64)
 
 
+def _bf16_split(a):
+    """(hi, lo) of the CUDA kernel's split-bf16 operands: hi = bf16(x), lo = bf16(x - hi), round to nearest even."""
+    def rn(v32):
+        u = v32.view(np.uint32)
+        u = (u + np.uint32(0x7FFF) + ((u >> np.uint32(16)) & np.uint32(1))) & np.uint32(0xFFFF0000)
+        return u.view(np.float32)
+    a32 = np.ascontiguousarray(a, np.float32)
+    hi = rn(a32)
+    lo = rn((a32 - hi).astype(np.float32))
+    return hi.astype(np.float64), lo.astype(np.float64)
+
+
 def decode_features(x, weights, biases, dtype=np.float64, operand=None):
     """Autoencoder.decode (autoencoder/model.py:42-46, decoder built at :18-25): Linear, then (ReLU, Linear) for every
     further layer, then x / x.norm(dim=-1, keepdim=True).  weights[l] is nn.Linear's [out, in] matrix.  float64 by
@@ -321,6 +333,10 @@ def decode_features(x, weights, biases, dtype=np.float64, operand=None):
             h = np.maximum(h, 0)
         if operand is None:
             h = h @ _np(w, dtype).T + _np(b, dtype)
+        elif operand == "bf16x2":  # three bf16 MMAs per product: hi*hi + lo*hi + hi*lo, fp32 accumulator
+            (hh, hl), (wh, wl) = _bf16_split(h), _bf16_split(w)
+            h = (hh @ wh.T + hl @ wh.T + hh @ wl.T).astype(np.float32).astype(np.float64)
+            h = (h.astype(np.float32) + _np(b, np.float32)).astype(np.float64)
         else:
             h = (_round_operand(h, operand) @ _round_operand(w, operand).T).astype(np.float32).astype(np.float64)
             h = (h.astype(np.float32) + _np(b, np.float32)).astype(np.float64)

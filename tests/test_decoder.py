@@ -20,7 +20,10 @@ NL = int(GOLD["n_layers"])
 WS = [GOLD[f"w{i}"] for i in range(NL)]
 BS = [GOLD[f"b{i}"] for i in range(NL)]
 N_POS = int(GOLD["n_pos"])
-TOL = {"fp32": (1e-5, 2e-5), "tf32": (5e-4, 1e-3), "f16": (5e-4, 1e-3)}
+# (features, relevancy) max-abs bars.  "bf16x2" — the tensor-core variant at the reference's arithmetic (split-bf16
+# operands, three MMAs per product) — is held to the bars of the IEEE-fp32 variant; the single-MMA variants carry the
+# error of 10-bit operands.
+TOL = {"fp32": (1e-5, 2e-5), "bf16x2": (1e-5, 2e-5), "tf32": (5e-4, 1e-3), "f16": (5e-4, 1e-3)}
 
 
 def test_oracle_matches_reference_vectors():
@@ -50,6 +53,11 @@ def test_operand_rounding_explains_the_tensor_core_tolerance():
     assert 0.9e-4 < got["tf32_trunc"][0] < 1.3e-4 and 2.0e-4 < got["tf32_trunc"][1] < 2.9e-4
     assert 3.0e-5 < got["f16"][0] < 4.0e-5
     assert got["tf32"][0] < got["tf32_trunc"][0]  # rounding to nearest first is why the kernel does it
+    # split-bf16 operands (16 mantissa bits, three MMAs per product): inside the fp32 variant's bars with room to spare
+    y = orc.decode_features(GOLD["x"], WS, BS, operand="bf16x2")
+    r = orc.relevancy(y, GOLD["phrases"], N_POS)[..., 0]
+    e = (np.abs(y - GOLD["y"]).max(), np.abs(r - GOLD["relevancy"][..., 0]).max())
+    assert e[0] < TOL["bf16x2"][0] / 4 and e[1] < TOL["bf16x2"][1] / 4, e
 
 
 def test_host_validation_without_gpu():
@@ -65,7 +73,7 @@ def test_host_validation_without_gpu():
     with pytest.raises(LsrError):
         FeatureDecoder([], [])
     with pytest.raises(ValueError):
-        FeatureDecoder(ws, bs, precision="bf16")
+        FeatureDecoder(ws, bs, precision="bf16")  # (the split variant is "bf16x2")
     with pytest.raises(LsrError, match="no decoder"):
         FeatureDecoder.from_state_dict({"encoder.0.weight": ws[0]}, device="cpu")
 
@@ -74,8 +82,9 @@ def test_abi_decoder_struct_matches_header():
     """ctypes mirror of lsr_decoder: field order / sizes as include/lsr_api.h declares them."""
     import ctypes
     from langsplat_b200 import _lib as L
-    assert [f[0] for f in L.Decoder._fields_] == ["n_layers", "dims", "weight", "bias", "packed_tf32", "packed_f16"]
-    assert ctypes.sizeof(L.Decoder) == 4 + 4 * 9 + 8 * 8 + 8 * 8 + 8 + 8
+    assert [f[0] for f in L.Decoder._fields_] == ["n_layers", "dims", "weight", "bias", "packed_tf32", "packed_f16",
+                                                  "packed_bf16x2"]
+    assert ctypes.sizeof(L.Decoder) == 4 + 4 * 9 + 8 * 8 + 8 * 8 + 8 + 8 + 8
     hdr = open(os.path.join(os.path.dirname(__file__), "..", "include", "lsr_api.h")).read()
     for sym in ("lsr_decoder_packed_bytes", "lsr_decoder_pack", "lsr_decode_work_bytes", "lsr_decode",
                 "lsr_debug_decode_trace"):
@@ -92,7 +101,7 @@ def _decoder(precision):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("precision", ["fp32", "tf32", "f16"])
+@pytest.mark.parametrize("precision", ["fp32", "bf16x2", "tf32", "f16"])
 def test_gpu_matches_reference_vectors(precision):
     from langsplat_b200 import _lib
     dec, dev = _decoder(precision)
@@ -110,7 +119,7 @@ def test_gpu_matches_reference_vectors(precision):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("precision", ["fp32", "tf32", "f16"])
+@pytest.mark.parametrize("precision", ["fp32", "bf16x2", "tf32", "f16"])
 @pytest.mark.parametrize("n", [1, 31, 127, 128, 129, 1000, 148 * 128 * 2 + 77])
 def test_gpu_matches_oracle_ragged(precision, n):
     dec, dev = _decoder(precision)
@@ -126,7 +135,7 @@ def test_gpu_matches_oracle_ragged(precision, n):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("precision", ["fp32", "tf32", "f16"])
+@pytest.mark.parametrize("precision", ["fp32", "bf16x2", "tf32", "f16"])
 @pytest.mark.parametrize("n_pos,n_neg", [(1, 1), (12, 4), (2, 14)])
 def test_gpu_phrase_counts(precision, n_pos, n_neg):
     """Fewest and most phrases the C ABI takes (LSR_DECODER_MAX_PHRASES = 16), against the oracle."""
@@ -187,7 +196,7 @@ def test_gpu_full_size_properties():
     y32 = dec.decode(sem, precision="fp32")
     rel32 = dec.get_max_across(sem, precision="fp32")
     big = torch.randn(1080 * 1440, 3, generator=g).to(dev)
-    for prec in ("tf32", "f16"):
+    for prec in ("bf16x2", "tf32", "f16"):
         y = dec.decode(sem, precision=prec)
         assert float((y.norm(dim=-1) - 1).abs().max()) < 1e-5
         assert float((y - y32).abs().max()) < TOL[prec][0]
