@@ -725,16 +725,18 @@ def main():
         # R pairs: R*(8 + 24*passes)).  Our binning orders the P Gaussians by depth first and sorts the R instance
         # words on the tile bits only, so its own minimum traffic is what its kernels are held against:
         #   depth_order: 8*P read (depth, tiles) + 8*P written, then 16*P per pass (d_passes passes, 8-byte words);
-        #   scan: 4*P permutation + 4*P tiles read, 4*P written; duplicate: 4*P perm + 4*P offsets + 12*V (radius, xy)
-        #   + 8*R written; sort: 16*R per pass over the tile bits (+ 4*R for the point list in the last pass).
+        #   duplicate (with its own offset scan): 4*P permutation + 4*P radii read, 4*P offsets written, 12*V (xy of the
+        #   visible ones) + 8*R written; sort: 16*R per pass over the tile bits (+ 4*R for the point list in the last pass).
         # `sort_survey_equiv` keeps SURVEY's figure for the whole binning so the two algorithms can be compared.
         tile_bits = max(1, int(math.ceil(math.log2(T)))) if T > 1 else 1
         t_passes = (tile_bits + 7) // 8
         d_bits = stats.get("depth_bits", 24)
         d_passes = (d_bits + 7) // 8
         byt = {"preprocess_fwd": 20 * P + 291 * V, "depth_order": 16 * P + 16 * P * d_passes + 4 * P,
-               "scan": 12 * P, "duplicate": 8 * P + 12 * V + 8 * Rn,
-               "sort": Rn * (16 * t_passes + 4), "tile_ranges": 8 * Rn + 8 * T + 12 * T,  # + tile ordering: ranges -> CTA map
+               # the scan of the tile counts is part of the duplication kernel (its stage is empty), and the tile
+               # ranges are marked by the last sort pass; "tile_ranges" is what is left: decode + tile ordering
+               "duplicate": 12 * P + 12 * V + 8 * Rn,
+               "sort": Rn * (16 * t_passes + 4) + 16 * T, "tile_ranges": 20 * T,
                "render_fwd": 52 * Rn + 32 * N,
                "bwd_zero_fill": 56 * P, "render_bwd": 52 * Rn + 32 * N + 48 * V, "preprocess_bwd": 236 * P + 303 * V}
         ins = {"render_fwd": 20 * Kx + 15 * Kc, "render_bwd": 20 * Kx + 54 * Kc}
