@@ -280,41 +280,47 @@ duplicate_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const
 // Nothing here needs the instance count on the host: stores are clipped at `capacity`, and an overflow raises
 // ERR_OVERFLOW in ctrl (the forward then poisons its outputs, api.cu).
 // ------------------------------------------------------------------------------------------------------------
-constexpr int DUP_CHUNK = 2048;  // staged words per chunk (16 KB)
+constexpr int DUP_CHUNK = 3072;  // staged words per chunk (24 KB): most blocks (2 240 instances on average at C2) need one
 constexpr uint32_t DUP_BIG = 512;
+constexpr int DUP_HIST_PASSES = 4;
 
+// Barriers are what this kernel waits on (ncu, GPU call r2i, first version: 12 barrier-stall cycles per issued
+// instruction — every warp of a block sat behind warp 0's look-back before it could start filling).  So: the fill of
+// the first chunk does not need the block's base and runs BESIDE the look-back; the next block's ticket is taken one
+// block ahead and its (index, radius, centre) gathers — three dependent global loads — are issued while the current
+// block is still being emitted; a block that fits one chunk passes three barriers.
 __global__ void __launch_bounds__(DUP_BLOCK)
 dup_scan_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const int32_t* __restrict__ radii,
                 const GeomRec* __restrict__ rec, uint32_t* __restrict__ offsets, uint64_t* __restrict__ words,
                 uint32_t capacity, int id_bits, int passes, volatile uint64_t* __restrict__ status,
                 uint32_t* __restrict__ ctrl, uint32_t* __restrict__ ghist) {
   __shared__ __align__(16) uint64_t s_words[DUP_CHUNK];
-  __shared__ uint32_t s_hist[SORT_MAX_PASSES * SORT_BINS];
+  __shared__ uint32_t s_hist[DUP_HIST_PASSES * SORT_BINS];  // (tile ids are 32-bit: at most four 8-bit digits)
   __shared__ uint32_t s_warp[DUP_BLOCK / 32];
-  __shared__ uint32_t s_blk, s_base, s_nbig;
+  __shared__ uint32_t s_blk[2], s_base, s_nbig;
   __shared__ uint4 s_bigrec[DUP_BLOCK];  // Gaussians emitted cooperatively: block-local start, count, width, y0<<16|x0
   __shared__ uint32_t s_biggid[DUP_BLOCK];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   for (int j = tid; j < passes * SORT_BINS; j += DUP_BLOCK) s_hist[j] = 0;
   if (blockIdx.x == 0 && tid == 0 && ctrl[CTRL_NUM_RENDERED] > capacity) atomicOr(&ctrl[CTRL_ERROR], ERR_OVERFLOW);
-  const int nblocks = (P + DUP_BLOCK - 1) / DUP_BLOCK;
-  for (;;) {
-    __syncthreads();  // previous block's shared state is no longer read
-    if (tid == 0) { s_blk = atomicAdd(&ctrl[CTRL_DUP_TICKET], 1u); s_nbig = 0; }
-    __syncthreads();
-    const uint32_t blk = s_blk;
-    if (blk >= (uint32_t)nblocks) break;
+  const uint32_t nblocks = (uint32_t)((P + DUP_BLOCK - 1) / DUP_BLOCK);
+  if (tid == 0) s_blk[0] = atomicAdd(&ctrl[CTRL_DUP_TICKET], 1u);
+  __syncthreads();
+  uint32_t blk = s_blk[0];
+  // this thread's Gaussian of block `blk`: index in the depth order -> id -> radius -> centre
+  uint32_t gid = 0;
+  int radius = 0;
+  float2 xy = make_float2(0.f, 0.f);
+  if (blk < nblocks && (int)(blk * DUP_BLOCK) + tid < P) {
+    gid = __ldg(perm + blk * DUP_BLOCK + tid);
+    radius = __ldg(radii + gid);
+    xy = __ldg(reinterpret_cast<const float2*>(rec + gid));  // (stale for a culled Gaussian: unused, radius is 0)
+  }
+  for (int it = 0; blk < nblocks; it++) {
+    if (tid == 0) { s_blk[(it + 1) & 1] = atomicAdd(&ctrl[CTRL_DUP_TICKET], 1u); s_nbig = 0; }
     const int i = (int)blk * DUP_BLOCK + tid;
-    uint32_t x0 = 0, y0 = 0, x1 = 0, y1 = 0, gid = 0;
-    int radius = 0;
-    if (i < P) {
-      gid = __ldg(perm + i);
-      radius = __ldg(radii + gid);
-    }
-    if (radius > 0) {
-      const float2 xy = __ldg(reinterpret_cast<const float2*>(rec + gid));
-      get_rect(xy.x, xy.y, radius, gx, gy, x0, y0, x1, y1);
-    }
+    uint32_t x0 = 0, y0 = 0, x1 = 0, y1 = 0;
+    if (radius > 0) get_rect(xy.x, xy.y, radius, gx, gy, x0, y0, x1, y1);
     const uint32_t w = x1 - x0;
     const uint32_t cnt = w * (y1 - y0);  // == tiles_touched of this Gaussian
     // ---- block scan of the counts ----
@@ -325,7 +331,10 @@ dup_scan_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const 
       if (lane >= d) inc += n;
     }
     if (lane == 31) s_warp[warp] = inc;
-    __syncthreads();
+    __syncthreads();  // (1) warp sums, next ticket, big list reset
+    const uint32_t nblk = s_blk[(it + 1) & 1];
+    const bool nvalid = nblk < nblocks && (int)(nblk * DUP_BLOCK) + tid < P;
+    const uint32_t ngid = nvalid ? __ldg(perm + nblk * DUP_BLOCK + tid) : 0u;  // in flight during the fill
     uint32_t warp_prefix = 0, block_sum = 0;
 #pragma unroll
     for (int k = 0; k < DUP_BLOCK / 32; k++) {
@@ -333,7 +342,8 @@ dup_scan_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const 
       if (k < warp) warp_prefix += x;
       block_sum += x;
     }
-    // ---- base of the block: decoupled look-back by warp 0 (status word: [63:62] flag, [31:0] value) ----
+    // ---- base of the block: decoupled look-back by warp 0 (status word: [63:62] flag, [31:0] value), while the
+    // other warps already fill ----
     if (warp == 0) {
       if (lane == 0) status[blk] = (blk == 0 ? FLAG_INC : FLAG_AGG) | block_sum;
       uint32_t prefix = 0;
@@ -360,21 +370,17 @@ dup_scan_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const 
     }
     const uint32_t lend = warp_prefix + inc;  // block-local [lstart, lend) of this thread's instances
     const uint32_t lstart = lend - cnt;
-    const uint32_t origin = (y0 << 16) | x0;
-    if (cnt > DUP_BIG) {
+    const bool big = cnt > DUP_BIG;
+    if (big) {
       const uint32_t k = atomicAdd(&s_nbig, 1u);
-      s_bigrec[k] = make_uint4(lstart, cnt, w, origin);
+      s_bigrec[k] = make_uint4(lstart, cnt, w, (y0 << 16) | x0);
       s_biggid[k] = gid;
     }
-    __syncthreads();
-    const uint32_t base = s_base, nbig = s_nbig;
-    if (i < P) offsets[i] = base + lend;  // inclusive, as the stand-alone scan wrote it
-    // ---- emission, DUP_CHUNK slots at a time ----
-    for (uint32_t c0 = 0; c0 < block_sum; c0 += DUP_CHUNK) {
-      const uint32_t c1 = min(c0 + (uint32_t)DUP_CHUNK, block_sum);
-      if (cnt != 0u && cnt <= DUP_BIG && lstart < c1 && lend > c0) {
+    // this thread's words that fall into chunk [c0, c1): row-major walk of the rect, no division in the loop
+    auto fill = [&](uint32_t c0, uint32_t c1) {
+      if (cnt != 0u && !big && lstart < c1 && lend > c0) {
         const uint32_t a = max(lstart, c0), b = min(lend, c1);
-        uint32_t r = a - lstart;
+        const uint32_t r = a - lstart;
         uint32_t row = 0, col = r;
         if (r != 0u) { row = r / w; col = r - row * w; }  // only for a Gaussian cut by the chunk boundary
         uint32_t tile = (y0 + row) * (uint32_t)gx + x0 + col;
@@ -384,6 +390,18 @@ dup_scan_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const 
           if (col == w) { col = 0; tile += (uint32_t)gx - w; }
         }
       }
+    };
+    fill(0u, min((uint32_t)DUP_CHUNK, block_sum));
+    __syncthreads();  // (2) base, big list, first chunk (but for the big Gaussians)
+    const uint32_t base = s_base, nbig = s_nbig;
+    if (i < P) offsets[i] = base + lend;  // inclusive, as the stand-alone scan wrote it
+    // the rest of the next block's gathers (its index has arrived by now); the centre does not wait for the radius
+    const int nradius = nvalid ? __ldg(radii + ngid) : 0;
+    const float2 nxy = __ldg(reinterpret_cast<const float2*>(rec + ngid));
+    // ---- emission, DUP_CHUNK slots at a time ----
+    for (uint32_t c0 = 0; c0 < block_sum; c0 += DUP_CHUNK) {
+      const uint32_t c1 = min(c0 + (uint32_t)DUP_CHUNK, block_sum);
+      if (c0 > 0u) fill(c0, c1);
       for (uint32_t bi = 0; bi < nbig; bi++) {  // the block's big Gaussians, all threads together
         const uint4 br = s_bigrec[bi];
         const uint32_t a = max(br.x, c0), b = min(br.x + br.y, c1);
@@ -394,7 +412,7 @@ dup_scan_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const 
           s_words[sl - c0] = ((uint64_t)tile << id_bits) | (uint64_t)bgid;
         }
       }
-      __syncthreads();
+      if (c0 > 0u || nbig > 0u) __syncthreads();  // (3) only when something was filled after barrier (2)
       const uint32_t n = c1 - c0;
       for (uint32_t k0 = 0; k0 < n; k0 += DUP_BLOCK) {  // CTA-uniform trip count (warp-wide votes below)
         const uint32_t k = k0 + tid;
@@ -413,10 +431,15 @@ dup_scan_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const 
           if (ok && (peers & ((1u << lane) - 1)) == 0) atomicAdd(&s_hist[p * SORT_BINS + d], (uint32_t)__popc(peers));
         }
       }
-      __syncthreads();
+      __syncthreads();  // (4) the chunk is free again; also ends the block
     }
+    if (block_sum == 0u) __syncthreads();  // ends the block (big list counter, warp sums) when nothing was emitted
+    blk = nblk;
+    gid = ngid;
+    radius = nradius;
+    xy = nxy;
   }
-  // (all threads left the loop together after the barrier that published s_blk)
+  __syncthreads();
   for (int j = tid; j < passes * SORT_BINS; j += DUP_BLOCK)
     if (s_hist[j]) atomicAdd(&ghist[j], s_hist[j]);
 }
@@ -597,9 +620,11 @@ void launch_dup_scan(int P, int grid_x, int grid_y, const uint32_t* perm, const 
                      uint32_t* ghist, cudaStream_t s) {
   if (P <= 0) return;
   const int nblocks = (P + DUP_BLOCK - 1) / DUP_BLOCK;
-  const int grid = nblocks < 148 * 6 ? nblocks : 148 * 6;  // persistent CTAs (29 KB of shared memory each)
+  const int grid = nblocks < 148 * 6 ? nblocks : 148 * 6;  // persistent CTAs (34 KB of shared memory each)
   dup_scan_kernel<<<grid, DUP_BLOCK, 0, s>>>(P, grid_x, grid_y, perm, radii, g.rec, g.offsets, words,
-                                               (uint32_t)capacity, plan.id_bits, plan.passes, status, ctrl, ghist);
+                                               (uint32_t)capacity, plan.id_bits,
+                                               plan.passes < DUP_HIST_PASSES ? plan.passes : DUP_HIST_PASSES, status,
+                                               ctrl, ghist);
   count_launch();
 }
 
