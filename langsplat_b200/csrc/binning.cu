@@ -286,9 +286,8 @@ constexpr int DUP_HIST_PASSES = 4;
 
 // Barriers are what this kernel waits on (ncu, GPU call r2i, first version: 12 barrier-stall cycles per issued
 // instruction — every warp of a block sat behind warp 0's look-back before it could start filling).  So: the fill of
-// the first chunk does not need the block's base and runs BESIDE the look-back; the next block's ticket is taken one
-// block ahead and its (index, radius, centre) gathers — three dependent global loads — are issued while the current
-// block is still being emitted; a block that fits one chunk passes three barriers.
+// the first chunk does not need the block's base and runs BESIDE the look-back, and a block that fits one chunk
+// passes four barriers instead of eight.
 __global__ void __launch_bounds__(DUP_BLOCK)
 dup_scan_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const int32_t* __restrict__ radii,
                 const GeomRec* __restrict__ rec, uint32_t* __restrict__ offsets, uint64_t* __restrict__ words,
@@ -304,23 +303,23 @@ dup_scan_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const 
   for (int j = tid; j < passes * SORT_BINS; j += DUP_BLOCK) s_hist[j] = 0;
   if (blockIdx.x == 0 && tid == 0 && ctrl[CTRL_NUM_RENDERED] > capacity) atomicOr(&ctrl[CTRL_ERROR], ERR_OVERFLOW);
   const uint32_t nblocks = (uint32_t)((P + DUP_BLOCK - 1) / DUP_BLOCK);
-  if (tid == 0) s_blk[0] = atomicAdd(&ctrl[CTRL_DUP_TICKET], 1u);
-  __syncthreads();
-  uint32_t blk = s_blk[0];
-  // this thread's Gaussian of block `blk`: index in the depth order -> id -> radius -> centre
-  uint32_t gid = 0;
-  int radius = 0;
-  float2 xy = make_float2(0.f, 0.f);
-  if (blk < nblocks && (int)(blk * DUP_BLOCK) + tid < P) {
-    gid = __ldg(perm + blk * DUP_BLOCK + tid);
-    radius = __ldg(radii + gid);
-    xy = __ldg(reinterpret_cast<const float2*>(rec + gid));  // (stale for a culled Gaussian: unused, radius is 0)
-  }
-  for (int it = 0; blk < nblocks; it++) {
-    if (tid == 0) { s_blk[(it + 1) & 1] = atomicAdd(&ctrl[CTRL_DUP_TICKET], 1u); s_nbig = 0; }
+  for (;;) {
+    // (a ticket is only taken by a CTA that starts on the block at once: a block that is ticketed but idle would hold
+    // up the look-back of every block behind it — taking tickets one block ahead measured 112 instead of 87 us)
+    if (tid == 0) { s_blk[0] = atomicAdd(&ctrl[CTRL_DUP_TICKET], 1u); s_nbig = 0; }
+    __syncthreads();  // (0) the ticket; the previous block ended with a barrier
+    const uint32_t blk = s_blk[0];
+    if (blk >= nblocks) break;
     const int i = (int)blk * DUP_BLOCK + tid;
+    uint32_t gid = 0;
+    int radius = 0;
     uint32_t x0 = 0, y0 = 0, x1 = 0, y1 = 0;
-    if (radius > 0) get_rect(xy.x, xy.y, radius, gx, gy, x0, y0, x1, y1);
+    if (i < P) {
+      gid = __ldg(perm + i);
+      radius = __ldg(radii + gid);
+      const float2 xy = __ldg(reinterpret_cast<const float2*>(rec + gid));  // (not waiting for the radius; stale and
+      if (radius > 0) get_rect(xy.x, xy.y, radius, gx, gy, x0, y0, x1, y1);  //  unused for a culled Gaussian)
+    }
     const uint32_t w = x1 - x0;
     const uint32_t cnt = w * (y1 - y0);  // == tiles_touched of this Gaussian
     // ---- block scan of the counts ----
@@ -331,10 +330,7 @@ dup_scan_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const 
       if (lane >= d) inc += n;
     }
     if (lane == 31) s_warp[warp] = inc;
-    __syncthreads();  // (1) warp sums, next ticket, big list reset
-    const uint32_t nblk = s_blk[(it + 1) & 1];
-    const bool nvalid = nblk < nblocks && (int)(nblk * DUP_BLOCK) + tid < P;
-    const uint32_t ngid = nvalid ? __ldg(perm + nblk * DUP_BLOCK + tid) : 0u;  // in flight during the fill
+    __syncthreads();  // (1) warp sums
     uint32_t warp_prefix = 0, block_sum = 0;
 #pragma unroll
     for (int k = 0; k < DUP_BLOCK / 32; k++) {
@@ -395,9 +391,6 @@ dup_scan_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const 
     __syncthreads();  // (2) base, big list, first chunk (but for the big Gaussians)
     const uint32_t base = s_base, nbig = s_nbig;
     if (i < P) offsets[i] = base + lend;  // inclusive, as the stand-alone scan wrote it
-    // the rest of the next block's gathers (its index has arrived by now); the centre does not wait for the radius
-    const int nradius = nvalid ? __ldg(radii + ngid) : 0;
-    const float2 nxy = __ldg(reinterpret_cast<const float2*>(rec + ngid));
     // ---- emission, DUP_CHUNK slots at a time ----
     for (uint32_t c0 = 0; c0 < block_sum; c0 += DUP_CHUNK) {
       const uint32_t c1 = min(c0 + (uint32_t)DUP_CHUNK, block_sum);
@@ -434,12 +427,7 @@ dup_scan_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const 
       __syncthreads();  // (4) the chunk is free again; also ends the block
     }
     if (block_sum == 0u) __syncthreads();  // ends the block (big list counter, warp sums) when nothing was emitted
-    blk = nblk;
-    gid = ngid;
-    radius = nradius;
-    xy = nxy;
   }
-  __syncthreads();
   for (int j = tid; j < passes * SORT_BINS; j += DUP_BLOCK)
     if (s_hist[j]) atomicAdd(&ghist[j], s_hist[j]);
 }
