@@ -279,46 +279,47 @@ duplicate_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const
 //
 // Nothing here needs the instance count on the host: stores are clipped at `capacity`, and an overflow raises
 // ERR_OVERFLOW in ctrl (the forward then poisons its outputs, api.cu).
+//
+// Measured and dropped (GPU calls r2j, r2k; ncu on this version shows 12 barrier-stall cycles per issued instruction,
+// the block waiting for warp 0's look-back): filling the first chunk beside the look-back with 3 072-slot chunks and
+// half the barriers: 97 us instead of 87 at C2, 602 instead of 501 at C5; additionally taking the tickets one block
+// ahead to prefetch the (index, radius, centre) gathers: 112 / 1 214 us — a block that is ticketed but idle holds up
+// the look-back of every block behind it.
 // ------------------------------------------------------------------------------------------------------------
-constexpr int DUP_CHUNK = 3072;  // staged words per chunk (24 KB): most blocks (2 240 instances on average at C2) need one
+constexpr int DUP_CHUNK = 2048;  // staged words per chunk (16 KB)
 constexpr uint32_t DUP_BIG = 512;
-constexpr int DUP_HIST_PASSES = 4;
 
-// Barriers are what this kernel waits on (ncu, GPU call r2i, first version: 12 barrier-stall cycles per issued
-// instruction — every warp of a block sat behind warp 0's look-back before it could start filling).  So: the fill of
-// the first chunk does not need the block's base and runs BESIDE the look-back, and a block that fits one chunk
-// passes four barriers instead of eight.
 __global__ void __launch_bounds__(DUP_BLOCK)
 dup_scan_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const int32_t* __restrict__ radii,
                 const GeomRec* __restrict__ rec, uint32_t* __restrict__ offsets, uint64_t* __restrict__ words,
                 uint32_t capacity, int id_bits, int passes, volatile uint64_t* __restrict__ status,
                 uint32_t* __restrict__ ctrl, uint32_t* __restrict__ ghist) {
   __shared__ __align__(16) uint64_t s_words[DUP_CHUNK];
-  __shared__ uint32_t s_hist[DUP_HIST_PASSES * SORT_BINS];  // (tile ids are 32-bit: at most four 8-bit digits)
+  __shared__ uint32_t s_hist[SORT_MAX_PASSES * SORT_BINS];
   __shared__ uint32_t s_warp[DUP_BLOCK / 32];
-  __shared__ uint32_t s_blk[2], s_base, s_nbig;
+  __shared__ uint32_t s_blk, s_base, s_nbig;
   __shared__ uint4 s_bigrec[DUP_BLOCK];  // Gaussians emitted cooperatively: block-local start, count, width, y0<<16|x0
   __shared__ uint32_t s_biggid[DUP_BLOCK];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   for (int j = tid; j < passes * SORT_BINS; j += DUP_BLOCK) s_hist[j] = 0;
   if (blockIdx.x == 0 && tid == 0 && ctrl[CTRL_NUM_RENDERED] > capacity) atomicOr(&ctrl[CTRL_ERROR], ERR_OVERFLOW);
-  const uint32_t nblocks = (uint32_t)((P + DUP_BLOCK - 1) / DUP_BLOCK);
+  const int nblocks = (P + DUP_BLOCK - 1) / DUP_BLOCK;
   for (;;) {
-    // (a ticket is only taken by a CTA that starts on the block at once: a block that is ticketed but idle would hold
-    // up the look-back of every block behind it — taking tickets one block ahead measured 112 instead of 87 us)
-    if (tid == 0) { s_blk[0] = atomicAdd(&ctrl[CTRL_DUP_TICKET], 1u); s_nbig = 0; }
-    __syncthreads();  // (0) the ticket; the previous block ended with a barrier
-    const uint32_t blk = s_blk[0];
-    if (blk >= nblocks) break;
+    __syncthreads();  // previous block's shared state is no longer read
+    if (tid == 0) { s_blk = atomicAdd(&ctrl[CTRL_DUP_TICKET], 1u); s_nbig = 0; }
+    __syncthreads();
+    const uint32_t blk = s_blk;
+    if (blk >= (uint32_t)nblocks) break;
     const int i = (int)blk * DUP_BLOCK + tid;
-    uint32_t gid = 0;
+    uint32_t x0 = 0, y0 = 0, x1 = 0, y1 = 0, gid = 0;
     int radius = 0;
-    uint32_t x0 = 0, y0 = 0, x1 = 0, y1 = 0;
     if (i < P) {
       gid = __ldg(perm + i);
       radius = __ldg(radii + gid);
-      const float2 xy = __ldg(reinterpret_cast<const float2*>(rec + gid));  // (not waiting for the radius; stale and
-      if (radius > 0) get_rect(xy.x, xy.y, radius, gx, gy, x0, y0, x1, y1);  //  unused for a culled Gaussian)
+    }
+    if (radius > 0) {
+      const float2 xy = __ldg(reinterpret_cast<const float2*>(rec + gid));
+      get_rect(xy.x, xy.y, radius, gx, gy, x0, y0, x1, y1);
     }
     const uint32_t w = x1 - x0;
     const uint32_t cnt = w * (y1 - y0);  // == tiles_touched of this Gaussian
@@ -330,7 +331,7 @@ dup_scan_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const 
       if (lane >= d) inc += n;
     }
     if (lane == 31) s_warp[warp] = inc;
-    __syncthreads();  // (1) warp sums
+    __syncthreads();
     uint32_t warp_prefix = 0, block_sum = 0;
 #pragma unroll
     for (int k = 0; k < DUP_BLOCK / 32; k++) {
@@ -338,8 +339,7 @@ dup_scan_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const 
       if (k < warp) warp_prefix += x;
       block_sum += x;
     }
-    // ---- base of the block: decoupled look-back by warp 0 (status word: [63:62] flag, [31:0] value), while the
-    // other warps already fill ----
+    // ---- base of the block: decoupled look-back by warp 0 (status word: [63:62] flag, [31:0] value) ----
     if (warp == 0) {
       if (lane == 0) status[blk] = (blk == 0 ? FLAG_INC : FLAG_AGG) | block_sum;
       uint32_t prefix = 0;
@@ -366,17 +366,21 @@ dup_scan_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const 
     }
     const uint32_t lend = warp_prefix + inc;  // block-local [lstart, lend) of this thread's instances
     const uint32_t lstart = lend - cnt;
-    const bool big = cnt > DUP_BIG;
-    if (big) {
+    const uint32_t origin = (y0 << 16) | x0;
+    if (cnt > DUP_BIG) {
       const uint32_t k = atomicAdd(&s_nbig, 1u);
-      s_bigrec[k] = make_uint4(lstart, cnt, w, (y0 << 16) | x0);
+      s_bigrec[k] = make_uint4(lstart, cnt, w, origin);
       s_biggid[k] = gid;
     }
-    // this thread's words that fall into chunk [c0, c1): row-major walk of the rect, no division in the loop
-    auto fill = [&](uint32_t c0, uint32_t c1) {
-      if (cnt != 0u && !big && lstart < c1 && lend > c0) {
+    __syncthreads();
+    const uint32_t base = s_base, nbig = s_nbig;
+    if (i < P) offsets[i] = base + lend;  // inclusive, as the stand-alone scan wrote it
+    // ---- emission, DUP_CHUNK slots at a time ----
+    for (uint32_t c0 = 0; c0 < block_sum; c0 += DUP_CHUNK) {
+      const uint32_t c1 = min(c0 + (uint32_t)DUP_CHUNK, block_sum);
+      if (cnt != 0u && cnt <= DUP_BIG && lstart < c1 && lend > c0) {
         const uint32_t a = max(lstart, c0), b = min(lend, c1);
-        const uint32_t r = a - lstart;
+        uint32_t r = a - lstart;
         uint32_t row = 0, col = r;
         if (r != 0u) { row = r / w; col = r - row * w; }  // only for a Gaussian cut by the chunk boundary
         uint32_t tile = (y0 + row) * (uint32_t)gx + x0 + col;
@@ -386,15 +390,6 @@ dup_scan_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const 
           if (col == w) { col = 0; tile += (uint32_t)gx - w; }
         }
       }
-    };
-    fill(0u, min((uint32_t)DUP_CHUNK, block_sum));
-    __syncthreads();  // (2) base, big list, first chunk (but for the big Gaussians)
-    const uint32_t base = s_base, nbig = s_nbig;
-    if (i < P) offsets[i] = base + lend;  // inclusive, as the stand-alone scan wrote it
-    // ---- emission, DUP_CHUNK slots at a time ----
-    for (uint32_t c0 = 0; c0 < block_sum; c0 += DUP_CHUNK) {
-      const uint32_t c1 = min(c0 + (uint32_t)DUP_CHUNK, block_sum);
-      if (c0 > 0u) fill(c0, c1);
       for (uint32_t bi = 0; bi < nbig; bi++) {  // the block's big Gaussians, all threads together
         const uint4 br = s_bigrec[bi];
         const uint32_t a = max(br.x, c0), b = min(br.x + br.y, c1);
@@ -405,7 +400,7 @@ dup_scan_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const 
           s_words[sl - c0] = ((uint64_t)tile << id_bits) | (uint64_t)bgid;
         }
       }
-      if (c0 > 0u || nbig > 0u) __syncthreads();  // (3) only when something was filled after barrier (2)
+      __syncthreads();
       const uint32_t n = c1 - c0;
       for (uint32_t k0 = 0; k0 < n; k0 += DUP_BLOCK) {  // CTA-uniform trip count (warp-wide votes below)
         const uint32_t k = k0 + tid;
@@ -424,10 +419,10 @@ dup_scan_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const 
           if (ok && (peers & ((1u << lane) - 1)) == 0) atomicAdd(&s_hist[p * SORT_BINS + d], (uint32_t)__popc(peers));
         }
       }
-      __syncthreads();  // (4) the chunk is free again; also ends the block
+      __syncthreads();
     }
-    if (block_sum == 0u) __syncthreads();  // ends the block (big list counter, warp sums) when nothing was emitted
   }
+  // (all threads left the loop together after the barrier that published s_blk)
   for (int j = tid; j < passes * SORT_BINS; j += DUP_BLOCK)
     if (s_hist[j]) atomicAdd(&ghist[j], s_hist[j]);
 }
@@ -608,11 +603,9 @@ void launch_dup_scan(int P, int grid_x, int grid_y, const uint32_t* perm, const 
                      uint32_t* ghist, cudaStream_t s) {
   if (P <= 0) return;
   const int nblocks = (P + DUP_BLOCK - 1) / DUP_BLOCK;
-  const int grid = nblocks < 148 * 6 ? nblocks : 148 * 6;  // persistent CTAs (34 KB of shared memory each)
+  const int grid = nblocks < 148 * 6 ? nblocks : 148 * 6;  // persistent CTAs (29 KB of shared memory each)
   dup_scan_kernel<<<grid, DUP_BLOCK, 0, s>>>(P, grid_x, grid_y, perm, radii, g.rec, g.offsets, words,
-                                               (uint32_t)capacity, plan.id_bits,
-                                               plan.passes < DUP_HIST_PASSES ? plan.passes : DUP_HIST_PASSES, status,
-                                               ctrl, ghist);
+                                               (uint32_t)capacity, plan.id_bits, plan.passes, status, ctrl, ghist);
   count_launch();
 }
 
