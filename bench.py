@@ -495,6 +495,28 @@ def main():
     ms_total = max_over_ranks(ev0.elapsed_time(ev1), world, dev)
     launches = (lib.lsr_launch_count() - launches0) if lib else None
 
+    # config 5: the reference's call sequence — three independent forward calls, one per level (render.py:35-52,
+    # process.sh:19-32) — timed next to the batched variant that shares preprocess and binning between the levels
+    three_call = None
+    if fwd_only and args.impl == "ours" and not args.separate_levels:
+        with torch.no_grad():
+            def three_calls():
+                for lang in levels:
+                    forward(lang=lang)
+            for _ in range(3):
+                three_calls()
+            barrier(world)
+            ev0.record()
+            for _ in range(args.steps):
+                three_calls()
+            ev1.record()
+            barrier(world)
+        t3 = max_over_ranks(ev0.elapsed_time(ev1), world, dev)
+        three_call = {"value": world * len(levels) * args.steps / (t3 / 1000.0), "unit": "frames/s",
+                      "ms_per_frame": t3 / args.steps / len(levels),
+                      "what": "one GaussianRasterizer.forward per feature level, as render.py does; `value` is the "
+                              "batched forward_feature_levels"}
+
     # forward-only ms/frame (second half of BASELINE.json's metric)
     with torch.no_grad():
         for _ in range(3):
@@ -674,6 +696,7 @@ def main():
                              if async_fwd else "one host read-back of the instance count per frame, like the reference "
                                                "(rasterizer_impl.cu:284)"),
             "fwd_only_ms_per_frame": fwd_ms, "clocks": clocks,
+            "three_call_sequence": three_call,
             "value_mode": value_mode,
             "value_eager": frames_per_step * args.steps / (value_eager_ms_total / 1000.0),
             "fwd_only_ms_per_frame_eager": fwd_eager_ms,

@@ -213,46 +213,67 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
       s_m2d[3 * tid] = -o * (cx * Mx + cy * My) * ddelx_dx;
       s_m2d[3 * tid + 1] = -o * (cz * My + cy * Mx) * ddely_dy;
     }
-    const float x_grad_mul = (c2.txtz < -c2.limx || c2.txtz > c2.limx) ? 0.f : 1.f;
-    const float y_grad_mul = (c2.tytz < -c2.limy || c2.tytz > c2.limy) ? 0.f : 1.f;
-    const Mat3& T = c2.T;
-    const Mat3& Vrk = c2.Vrk;
-    const Mat3& Wm = c2.W;
-    const float a = c2.a, b = c2.b, c = c2.c;
-    const float denom = a * c - b * b;
-    float dL_da = 0, dL_db = 0, dL_dc = 0;
-    const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
-    if (denom2inv != 0) {
-      dL_da = denom2inv * (-c * c * dLc_x + 2 * b * c * dLc_y + (denom - a * c) * dLc_z);
-      dL_dc = denom2inv * (-a * a * dLc_z + 2 * a * b * dLc_y + (denom - a * c) * dLc_x);
-      dL_db = denom2inv * 2 * (b * c * dLc_x - (denom + 2 * b * b) * dLc_y + a * b * dLc_z);
-      dcov[0] = (T.m[0][0] * T.m[0][0] * dL_da + T.m[0][0] * T.m[1][0] * dL_db + T.m[1][0] * T.m[1][0] * dL_dc);
-      dcov[3] = (T.m[0][1] * T.m[0][1] * dL_da + T.m[0][1] * T.m[1][1] * dL_db + T.m[1][1] * T.m[1][1] * dL_dc);
-      dcov[5] = (T.m[0][2] * T.m[0][2] * dL_da + T.m[0][2] * T.m[1][2] * dL_db + T.m[1][2] * T.m[1][2] * dL_dc);
-      dcov[1] = 2 * T.m[0][0] * T.m[0][1] * dL_da + (T.m[0][0] * T.m[1][1] + T.m[0][1] * T.m[1][0]) * dL_db +
-                2 * T.m[1][0] * T.m[1][1] * dL_dc;
-      dcov[2] = 2 * T.m[0][0] * T.m[0][2] * dL_da + (T.m[0][0] * T.m[1][2] + T.m[0][2] * T.m[1][0]) * dL_db +
-                2 * T.m[1][0] * T.m[1][2] * dL_dc;
-      dcov[4] = 2 * T.m[0][2] * T.m[0][1] * dL_da + (T.m[0][1] * T.m[1][2] + T.m[0][2] * T.m[1][1]) * dL_db +
-                2 * T.m[1][1] * T.m[1][2] * dL_dc;
+    // Reverse mode through  conic = Sigma^-1,  Sigma = (Tm Vrk Tm^T) + 0.3 I,  Tm = the two rows of the projected
+    // Jacobian (W J)^T that matter,  J = J(t),  t = view * mean  — written as the matrix identities they are
+    // (the reference spells the same chain out entry by entry, backward.cu:196-270):
+    //   inverse:    dL/dSigma = -adj(Sigma) G adj(Sigma) / (det^2 + 1e-7),  G = [[g_xx, g_xy], [g_xy, g_yy]] the
+    //               gradient w.r.t. the conic's three stored entries (the regulariser is the reference's);
+    //   congruence: dL/dVrk = Tm^T D Tm,  dL/dTm = 2 D Tm Vrk,  D = dL/dSigma as a symmetric matrix;
+    //   product:    dL/dJ = dL/dTm W^T  (only J's four non-constant entries are read off).
+    const Mat3& Tm = c2.T;
+    const float sa = c2.a, sb = c2.b, sc = c2.c;
+    const float det = sa * sc - sb * sb;
+    const float scale = 1.0f / (det * det + 0.0000001f);
+    float D[2][2] = {{0.f, 0.f}, {0.f, 0.f}};  // dL/dSigma
+    if (scale != 0) {
+      const float adj[2][2] = {{sc, -sb}, {-sb, sa}};
+      const float G[2][2] = {{dLc_x, dLc_y}, {dLc_y, dLc_z}};
+      float GA[2][2];
+#pragma unroll
+      for (int r = 0; r < 2; r++)
+#pragma unroll
+        for (int q = 0; q < 2; q++) GA[r][q] = G[r][0] * adj[0][q] + G[r][1] * adj[1][q];
+#pragma unroll
+      for (int r = 0; r < 2; r++)
+#pragma unroll
+        for (int q = r; q < 2; q++) D[r][q] = D[q][r] = -scale * (adj[r][0] * GA[0][q] + adj[r][1] * GA[1][q]);
+      // dL/dVrk = Tm^T D Tm; the six stored entries of a symmetric matrix, off-diagonal ones counted twice
+      float DT[2][3];
+#pragma unroll
+      for (int r = 0; r < 2; r++)
+#pragma unroll
+        for (int k = 0; k < 3; k++) DT[r][k] = D[r][0] * Tm.m[0][k] + D[r][1] * Tm.m[1][k];
+      auto vrk_grad = [&](int i, int j) { return Tm.m[0][i] * DT[0][j] + Tm.m[1][i] * DT[1][j]; };
+      dcov[0] = vrk_grad(0, 0);
+      dcov[1] = 2.f * vrk_grad(0, 1);
+      dcov[2] = 2.f * vrk_grad(0, 2);
+      dcov[3] = vrk_grad(1, 1);
+      dcov[4] = 2.f * vrk_grad(1, 2);
+      dcov[5] = vrk_grad(2, 2);
     }
-    auto row = [&](int r, int k) { return T.m[r][0] * Vrk.m[k][0] + T.m[r][1] * Vrk.m[k][1] + T.m[r][2] * Vrk.m[k][2]; };
-    const float dL_dT00 = 2 * row(0, 0) * dL_da + row(1, 0) * dL_db;
-    const float dL_dT01 = 2 * row(0, 1) * dL_da + row(1, 1) * dL_db;
-    const float dL_dT02 = 2 * row(0, 2) * dL_da + row(1, 2) * dL_db;
-    const float dL_dT10 = 2 * row(1, 0) * dL_dc + row(0, 0) * dL_db;
-    const float dL_dT11 = 2 * row(1, 1) * dL_dc + row(0, 1) * dL_db;
-    const float dL_dT12 = 2 * row(1, 2) * dL_dc + row(0, 2) * dL_db;
-    const float dL_dJ00 = Wm.m[0][0] * dL_dT00 + Wm.m[0][1] * dL_dT01 + Wm.m[0][2] * dL_dT02;
-    const float dL_dJ02 = Wm.m[2][0] * dL_dT00 + Wm.m[2][1] * dL_dT01 + Wm.m[2][2] * dL_dT02;
-    const float dL_dJ11 = Wm.m[1][0] * dL_dT10 + Wm.m[1][1] * dL_dT11 + Wm.m[1][2] * dL_dT12;
-    const float dL_dJ12 = Wm.m[2][0] * dL_dT10 + Wm.m[2][1] * dL_dT11 + Wm.m[2][2] * dL_dT12;
-    const float tz = 1.f / c2.tz, tz2 = tz * tz, tz3 = tz2 * tz;
-    const float dL_dtx = x_grad_mul * -h_x * tz2 * dL_dJ02;
-    const float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
-    const float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * c2.tx) * tz3 * dL_dJ02 +
-                         (2 * h_y * c2.ty) * tz3 * dL_dJ12;
-    // transformVec4x3Transpose
+    // dL/dTm = 2 D (Tm Vrk)
+    float TV[2][3], dTm[2][3];
+#pragma unroll
+    for (int r = 0; r < 2; r++)
+#pragma unroll
+      for (int k = 0; k < 3; k++)
+        TV[r][k] = Tm.m[r][0] * c2.Vrk.m[0][k] + Tm.m[r][1] * c2.Vrk.m[1][k] + Tm.m[r][2] * c2.Vrk.m[2][k];
+#pragma unroll
+    for (int r = 0; r < 2; r++)
+#pragma unroll
+      for (int k = 0; k < 3; k++) dTm[r][k] = 2.f * (D[r][0] * TV[0][k] + D[r][1] * TV[1][k]);
+    // dL/dJ = dL/dTm W^T, read off at J = [[fx/z, 0, -fx x/z^2], [0, fy/z, -fy y/z^2]]
+    auto dJ = [&](int r, int col) {
+      return dTm[r][0] * c2.W.m[col][0] + dTm[r][1] * c2.W.m[col][1] + dTm[r][2] * c2.W.m[col][2];
+    };
+    const float gJ00 = dJ(0, 0), gJ02 = dJ(0, 2), gJ11 = dJ(1, 1), gJ12 = dJ(1, 2);
+    // J(t): the clamped x/z, y/z (forward: limx, limy) pass no gradient to t.x, t.y where the clamp was active
+    const bool x_free = !(c2.txtz < -c2.limx || c2.txtz > c2.limx), y_free = !(c2.tytz < -c2.limy || c2.tytz > c2.limy);
+    const float iz = 1.f / c2.tz, iz2 = iz * iz, iz3 = iz2 * iz;
+    const float dL_dtx = x_free ? -h_x * iz2 * gJ02 : 0.f;
+    const float dL_dty = y_free ? -h_y * iz2 * gJ12 : 0.f;
+    const float dL_dtz = -(h_x * gJ00 + h_y * gJ11) * iz2 + 2.f * (h_x * c2.tx * gJ02 + h_y * c2.ty * gJ12) * iz3;
+    // t = view * mean (rotation part): mean gets view^T dL/dt
     dmean.x = s_view[0] * dL_dtx + s_view[1] * dL_dty + s_view[2] * dL_dtz;
     dmean.y = s_view[4] * dL_dtx + s_view[5] * dL_dty + s_view[6] * dL_dtz;
     dmean.z = s_view[8] * dL_dtx + s_view[9] * dL_dty + s_view[10] * dL_dtz;
