@@ -52,6 +52,17 @@ struct __align__(16) Bwd2Smem {
 #ifndef LSR_BWD2_MINB
 #define LSR_BWD2_MINB 24
 #endif
+// Chain shorteners for the default walk (A/B switches): request the colour record with the geometry record, one
+// warp-wide vote per instance instead of three, read the next instance's record one iteration ahead.
+#ifndef LSR_BWD2_EARLY_CD
+#define LSR_BWD2_EARLY_CD 0
+#endif
+#ifndef LSR_BWD2_ONE_VOTE
+#define LSR_BWD2_ONE_VOTE 0
+#endif
+#ifndef LSR_BWD2_PREFETCH
+#define LSR_BWD2_PREFETCH 0
+#endif
 #ifndef LSR_BWD2_PIPE
 // 0: one instance at a time, early-outs, per-slot branches (the default).
 // 1: software-pipelined, branch-free walk: front half of instance j+1 next to the back half of instance j.  Measured
@@ -385,10 +396,23 @@ render_bwd2_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, 
     __syncwarp();  // everyone has left the previous batch
     const int nb = commit_batch(sm.batch, nxt, X0, Y0);
     nxt = fetch_instance(list, rec, range.x, top - 32 - lane);
+#if LSR_BWD2_PREFETCH
+    float4 a_nx = lds128(smA), bb_nx = lds128(smA + SM_B);  // record of instance 0 (garbage if nb == 0: unused)
+#endif
     for (int j = 0; j < nb; j++) {
       const uint32_t ad = smA + (uint32_t)j * (uint32_t)sizeof(float4);
+#if LSR_BWD2_PREFETCH
+      const float4 a = a_nx, bb = bb_nx;
+      a_nx = lds128(ad + (uint32_t)sizeof(float4));  // the next instance's record: its latency hides behind this one
+      bb_nx = lds128(ad + (uint32_t)sizeof(float4) + SM_B);
+#else
       const float4 a = lds128(ad);
       const float4 bb = lds128(ad + SM_B);  // cz, thr_m, opacity, position
+#endif
+#if LSR_BWD2_EARLY_CD
+      const float4 c = lds128(ad + SM_C);  // r, g, b, f0: requested with the geometry, not after the votes
+      const float4 d = lds128(ad + SM_D);  // f1, f2, id
+#endif
       const uint32_t fwd = __float_as_uint(bb.w);
       const float dx = __fadd_rn(a.x, -pxf);
       const float qx = __fmul_rn(a.z, dx), hx = __fmul_rn(a.w, dx);
@@ -403,12 +427,25 @@ render_bwd2_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, 
         // as in the forward.  The pre-test against thr_m avoids expf for pairs that certainly fail alpha >= 1/255.
         maybe[s] = (fwd < lastc[s]) && !(power[s] > 0.0f) && !(power[s] < bb.y);
       }
+#if !LSR_BWD2_ONE_VOTE
       bool any_maybe = false;
 #pragma unroll
       for (int s = 0; s < BLEND_SLOTS; s++) any_maybe |= maybe[s];
       if (!__any_sync(0xffffffffu, any_maybe)) continue;
+#endif
       float G[BLEND_SLOTS], alpha[BLEND_SLOTS];
       bool contrib[BLEND_SLOTS];
+#if LSR_BWD2_ONE_VOTE
+      bool mine = false;  // one warp-wide vote per instance instead of three: every vote is a stop in the dependent chain
+#pragma unroll
+      for (int s = 0; s < BLEND_SLOTS; s++) {
+        G[s] = expf(power[s]);
+        alpha[s] = fminf(0.99f, __fmul_rn(bb.z, G[s]));
+        contrib[s] = maybe[s] && !(alpha[s] < kAlphaMin);
+        mine |= contrib[s];
+      }
+      if (!__any_sync(0xffffffffu, mine)) continue;
+#else
       uint32_t call = 0u;
 #pragma unroll
       for (int s = 0; s < BLEND_SLOTS; s++) {
@@ -418,9 +455,12 @@ render_bwd2_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, 
         call |= __ballot_sync(0xffffffffu, contrib[s]);
       }
       if (call == 0u) continue;
+#endif
 
+#if !LSR_BWD2_EARLY_CD
       const float4 c = lds128(ad + SM_C);  // r, g, b, f0
       const float4 d = lds128(ad + SM_D);  // f1, f2, id
+#endif
       const uint32_t colofs = (uint32_t)(ncol * ROW * 4);
 #pragma unroll
       for (int s = 0; s < BLEND_SLOTS; s++) {
