@@ -392,10 +392,11 @@ def main():
         gt_f_h = None
 
     def gt_images(gt_c, gt_f):
-        """The step's ground truth as float32 [3,H,W] tensors on the device."""
+        """The step's ground truth [3,H,W] on the device: the colour image stays uint8 (langsplat_b200.l1_loss forms
+        u / 255 inside its kernels), the feature map is float32."""
         if not gt_u8:
             return gt_c, gt_f
-        return gt_c.to(torch.float32).mul_(1.0 / 255.0), lf_cache.get("view%d" % my_views[0], 1, H, W)[0]
+        return gt_c, lf_cache.get("view%d" % my_views[0], 1, H, W)[0]
 
     h2d_bytes = sum(t.numel() * t.element_size() for t in (gt_c_h, gt_f_h, view_h, proj_h, cam_h) if t is not None)
 

@@ -245,6 +245,13 @@ int lsr_l1_loss_forward(const float* pred, const float* gt, const float* mask, i
 /* dL_dpred[C,N] = (*grad_out) * sign(pred*mask - gt*mask) * mask / (C*N); grad_out is a DEVICE scalar. */
 int lsr_l1_loss_backward(const float* pred, const float* gt, const float* mask, int32_t C, int64_t N,
                          const float* grad_out, float* dL_dpred, void* stream);
+/* The same two with the ground truth as the 8-bit image it is stored as: gt = u / 255 (IEEE division, the value
+ * PILtoTorch, utils/general_utils.py:21-28, forms on the host before scene/cameras.py:39 uploads it as float32) is
+ * computed inside the kernels, so the float copy of the image never exists in device memory. */
+int lsr_l1_loss_forward_u8(const float* pred, const uint8_t* gt, const float* mask, int32_t C, int64_t N, float* loss,
+                           void* stream);
+int lsr_l1_loss_backward_u8(const float* pred, const uint8_t* gt, const float* mask, int32_t C, int64_t N,
+                            const float* grad_out, float* dL_dpred, void* stream);
 
 /* Fused per-Gaussian activations in front of the rasterizer: scales = exp(scaling)
  * (scene/gaussian_model.py:33,134-136), rotations = normalize(rotation) = q / max(||q||, 1e-12) (:40,138-140),

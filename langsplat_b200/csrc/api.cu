@@ -163,6 +163,22 @@ int lsr_l1_loss_backward(const float* pred, const float* gt, const float* mask, 
   return LSR_OK;
 }
 
+int lsr_l1_loss_forward_u8(const float* pred, const uint8_t* gt, const float* mask, int32_t C, int64_t N, float* loss,
+                           void* stream) {
+  if (C < 0 || N < 0) return fail(LSR_ERR_INVALID, "C < 0 or N < 0");
+  if (!loss || ((int64_t)C * N > 0 && (!pred || !gt))) return fail(LSR_ERR_INVALID, "null pointer");
+  LSR_CUDA(launch_l1_forward_u8(pred, gt, mask, C, N, loss, (cudaStream_t)stream));
+  return LSR_OK;
+}
+
+int lsr_l1_loss_backward_u8(const float* pred, const uint8_t* gt, const float* mask, int32_t C, int64_t N,
+                            const float* grad_out, float* dL_dpred, void* stream) {
+  if (C < 0 || N < 0) return fail(LSR_ERR_INVALID, "C < 0 or N < 0");
+  if ((int64_t)C * N > 0 && (!pred || !gt || !grad_out || !dL_dpred)) return fail(LSR_ERR_INVALID, "null pointer");
+  LSR_CUDA(launch_l1_backward_u8(pred, gt, mask, C, N, grad_out, dL_dpred, (cudaStream_t)stream));
+  return LSR_OK;
+}
+
 int lsr_sh_gradient_from_views(int32_t P, int32_t M, int32_t D, int32_t n_views, const float* means3D,
                                const float* campos, const float* g, float* dL_dsh, void* stream) {
   if (P < 0 || M < 0 || n_views < 0 || D < 0 || D > 3) return fail(LSR_ERR_INVALID, "bad size / degree");

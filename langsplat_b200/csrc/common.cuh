@@ -305,6 +305,11 @@ cudaError_t launch_l1_forward(const float* pred, const float* gt, const float* m
                               cudaStream_t s);
 cudaError_t launch_l1_backward(const float* pred, const float* gt, const float* mask, int C, int64_t N,
                                const float* grad_out, float* dL_dpred, cudaStream_t s);
+// ... with the ground truth as the stored 8-bit image (gt = u / 255 formed in the kernel)
+cudaError_t launch_l1_forward_u8(const float* pred, const uint8_t* gt, const float* mask, int C, int64_t N, float* loss,
+                                 cudaStream_t s);
+cudaError_t launch_l1_backward_u8(const float* pred, const uint8_t* gt, const float* mask, int C, int64_t N,
+                                  const float* grad_out, float* dL_dpred, cudaStream_t s);
 
 void count_launch(int n = 1);
 

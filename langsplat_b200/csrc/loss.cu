@@ -7,6 +7,9 @@
 // upstream scalar; writes dL_dpred = g * sign(pred*m - gt*m) * m / (C*N)).  HBM-bound: 8 B/element forward,
 // 12 B/element backward (+ 4/C B for the mask).
 // Arithmetic follows PyTorch's: the two products are rounded separately before the subtraction.
+// The ground truth may also be given as the 8-bit image it was stored as (GT = uint8_t): the kernels then form
+// gt = u / 255 themselves (IEEE division, the value utils/general_utils.py:23 PILtoTorch computes on the host), so the
+// float copy of the image is never written to HBM: 5 B/element forward, 9 B/element backward.
 #include "common.cuh"
 
 namespace lsr {
@@ -20,9 +23,18 @@ __device__ __forceinline__ float diff_masked(float p, float g, float m) {
   return __fsub_rn(__fmul_rn(p, m), __fmul_rn(g, m));
 }
 
-template <bool MASK>
+__device__ __forceinline__ float gt1(const float* gt, int64_t i) { return __ldg(gt + i); }
+__device__ __forceinline__ float gt1(const uint8_t* gt, int64_t i) { return __fdiv_rn((float)__ldg(gt + i), 255.0f); }
+__device__ __forceinline__ float4 gt4(const float* gt, int64_t v) { return __ldg(reinterpret_cast<const float4*>(gt) + v); }
+__device__ __forceinline__ float4 gt4(const uint8_t* gt, int64_t v) {
+  const uchar4 u = __ldg(reinterpret_cast<const uchar4*>(gt) + v);
+  return make_float4(__fdiv_rn((float)u.x, 255.0f), __fdiv_rn((float)u.y, 255.0f), __fdiv_rn((float)u.z, 255.0f),
+                     __fdiv_rn((float)u.w, 255.0f));
+}
+
+template <bool MASK, typename GT>
 __global__ void __launch_bounds__(LOSS_THREADS)
-l1_forward_kernel(const float* __restrict__ pred, const float* __restrict__ gt, const float* __restrict__ mask,
+l1_forward_kernel(const float* __restrict__ pred, const GT* __restrict__ gt, const float* __restrict__ mask,
                   int64_t N, int64_t total, float inv_count, bool vec_ok, float* __restrict__ loss) {
   __shared__ float s_part[LOSS_THREADS / 32];
   const int64_t nvec = total / 4;
@@ -31,12 +43,11 @@ l1_forward_kernel(const float* __restrict__ pred, const float* __restrict__ gt, 
   // pointer is 16-byte aligned (a contiguous view may start at any element of its storage)
   if (vec_ok) {
     const float4* p4 = reinterpret_cast<const float4*>(pred);
-    const float4* g4 = reinterpret_cast<const float4*>(gt);
     const int64_t nv_per_ch = N / 4;
     for (int64_t v = (int64_t)blockIdx.x * LOSS_THREADS * LOSS_VEC_PER_THREAD + threadIdx.x, it = 0;
          it < LOSS_VEC_PER_THREAD; it++, v += LOSS_THREADS) {
       if (v >= nvec) break;
-      const float4 p = __ldg(p4 + v), g = __ldg(g4 + v);
+      const float4 p = __ldg(p4 + v), g = gt4(gt, v);
       float4 m = make_float4(1.f, 1.f, 1.f, 1.f);
       if (MASK) m = __ldg(reinterpret_cast<const float4*>(mask) + (v % nv_per_ch));
       acc += fabsf(diff_masked(p.x, g.x, m.x)) + fabsf(diff_masked(p.y, g.y, m.y)) +
@@ -47,7 +58,7 @@ l1_forward_kernel(const float* __restrict__ pred, const float* __restrict__ gt, 
          it < LOSS_VEC_PER_THREAD * 4; it++, i += LOSS_THREADS) {
       if (i >= total) break;
       const float m = MASK ? __ldg(mask + (i % N)) : 1.f;
-      acc += fabsf(diff_masked(__ldg(pred + i), __ldg(gt + i), m));
+      acc += fabsf(diff_masked(__ldg(pred + i), gt1(gt, i), m));
     }
   }
 #pragma unroll
@@ -62,9 +73,9 @@ l1_forward_kernel(const float* __restrict__ pred, const float* __restrict__ gt, 
   }
 }
 
-template <bool MASK>
+template <bool MASK, typename GT>
 __global__ void __launch_bounds__(LOSS_THREADS)
-l1_backward_kernel(const float* __restrict__ pred, const float* __restrict__ gt, const float* __restrict__ mask,
+l1_backward_kernel(const float* __restrict__ pred, const GT* __restrict__ gt, const float* __restrict__ mask,
                    int64_t N, int64_t total, float inv_count, bool vec_ok, const float* __restrict__ grad_out,
                    float* __restrict__ dL_dpred) {
   const float gscale = __ldg(grad_out) * inv_count;
@@ -77,13 +88,12 @@ l1_backward_kernel(const float* __restrict__ pred, const float* __restrict__ gt,
   const int64_t nvec = total / 4;
   if (vec_ok) {
     const float4* p4 = reinterpret_cast<const float4*>(pred);
-    const float4* g4 = reinterpret_cast<const float4*>(gt);
     float4* o4 = reinterpret_cast<float4*>(dL_dpred);
     const int64_t nv_per_ch = N / 4;
     for (int64_t v = (int64_t)blockIdx.x * LOSS_THREADS * LOSS_VEC_PER_THREAD + threadIdx.x, it = 0;
          it < LOSS_VEC_PER_THREAD; it++, v += LOSS_THREADS) {
       if (v >= nvec) break;
-      const float4 p = __ldg(p4 + v), g = __ldg(g4 + v);
+      const float4 p = __ldg(p4 + v), g = gt4(gt, v);
       float4 m = make_float4(1.f, 1.f, 1.f, 1.f);
       if (MASK) m = __ldg(reinterpret_cast<const float4*>(mask) + (v % nv_per_ch));
       o4[v] = make_float4(grad1(p.x, g.x, m.x), grad1(p.y, g.y, m.y), grad1(p.z, g.z, m.z), grad1(p.w, g.w, m.w));
@@ -93,7 +103,7 @@ l1_backward_kernel(const float* __restrict__ pred, const float* __restrict__ gt,
          it < LOSS_VEC_PER_THREAD * 4; it++, i += LOSS_THREADS) {
       if (i >= total) break;
       const float m = MASK ? __ldg(mask + (i % N)) : 1.f;
-      dL_dpred[i] = grad1(__ldg(pred + i), __ldg(gt + i), m);
+      dL_dpred[i] = grad1(__ldg(pred + i), gt1(gt, i), m);
     }
   }
 }
@@ -107,36 +117,56 @@ inline unsigned loss_blocks(int64_t total) {
   return (unsigned)((total + per - 1) / per);
 }
 
-}  // namespace
-
-cudaError_t launch_l1_forward(const float* pred, const float* gt, const float* mask, int C, int64_t N, float* loss,
-                              cudaStream_t s) {
+template <typename GT>
+cudaError_t l1_forward(const float* pred, const GT* gt, const float* mask, int C, int64_t N, float* loss,
+                       cudaStream_t s) {
   cudaError_t e = cudaMemsetAsync(loss, 0, sizeof(float), s);
   if (e != cudaSuccess) return e;
   const int64_t total = (int64_t)C * N;
   if (total == 0) return cudaSuccess;
   const float inv = (float)(1.0 / (double)total);
-  const bool vec = (N % 4) == 0 && aligned16(pred, gt, mask);
-  if (mask) l1_forward_kernel<true><<<loss_blocks(total), LOSS_THREADS, 0, s>>>(pred, gt, mask, N, total, inv, vec, loss);
-  else l1_forward_kernel<false><<<loss_blocks(total), LOSS_THREADS, 0, s>>>(pred, gt, mask, N, total, inv, vec, loss);
+  // (uchar4 loads of an 8-bit ground truth need 4-byte alignment only)
+  const bool vec = (N % 4) == 0 && aligned16(pred, mask, nullptr) && (((uintptr_t)gt) & (sizeof(GT) * 4 - 1)) == 0;
+  if (mask) l1_forward_kernel<true, GT><<<loss_blocks(total), LOSS_THREADS, 0, s>>>(pred, gt, mask, N, total, inv, vec, loss);
+  else l1_forward_kernel<false, GT><<<loss_blocks(total), LOSS_THREADS, 0, s>>>(pred, gt, mask, N, total, inv, vec, loss);
   count_launch();
   return cudaGetLastError();
 }
 
-cudaError_t launch_l1_backward(const float* pred, const float* gt, const float* mask, int C, int64_t N,
-                               const float* grad_out, float* dL_dpred, cudaStream_t s) {
+template <typename GT>
+cudaError_t l1_backward(const float* pred, const GT* gt, const float* mask, int C, int64_t N, const float* grad_out,
+                        float* dL_dpred, cudaStream_t s) {
   const int64_t total = (int64_t)C * N;
   if (total == 0) return cudaSuccess;
   const float inv = (float)(1.0 / (double)total);
-  const bool vec = (N % 4) == 0 && aligned16(pred, gt, mask, dL_dpred);
+  const bool vec = (N % 4) == 0 && aligned16(pred, mask, dL_dpred) && (((uintptr_t)gt) & (sizeof(GT) * 4 - 1)) == 0;
   if (mask)
-    l1_backward_kernel<true><<<loss_blocks(total), LOSS_THREADS, 0, s>>>(pred, gt, mask, N, total, inv, vec, grad_out,
-                                                                         dL_dpred);
+    l1_backward_kernel<true, GT><<<loss_blocks(total), LOSS_THREADS, 0, s>>>(pred, gt, mask, N, total, inv, vec,
+                                                                             grad_out, dL_dpred);
   else
-    l1_backward_kernel<false><<<loss_blocks(total), LOSS_THREADS, 0, s>>>(pred, gt, mask, N, total, inv, vec, grad_out,
-                                                                          dL_dpred);
+    l1_backward_kernel<false, GT><<<loss_blocks(total), LOSS_THREADS, 0, s>>>(pred, gt, mask, N, total, inv, vec,
+                                                                              grad_out, dL_dpred);
   count_launch();
   return cudaGetLastError();
+}
+
+}  // namespace
+
+cudaError_t launch_l1_forward(const float* pred, const float* gt, const float* mask, int C, int64_t N, float* loss,
+                              cudaStream_t s) {
+  return l1_forward(pred, gt, mask, C, N, loss, s);
+}
+cudaError_t launch_l1_forward_u8(const float* pred, const uint8_t* gt, const float* mask, int C, int64_t N, float* loss,
+                                 cudaStream_t s) {
+  return l1_forward(pred, gt, mask, C, N, loss, s);
+}
+cudaError_t launch_l1_backward(const float* pred, const float* gt, const float* mask, int C, int64_t N,
+                               const float* grad_out, float* dL_dpred, cudaStream_t s) {
+  return l1_backward(pred, gt, mask, C, N, grad_out, dL_dpred, s);
+}
+cudaError_t launch_l1_backward_u8(const float* pred, const uint8_t* gt, const float* mask, int C, int64_t N,
+                                  const float* grad_out, float* dL_dpred, cudaStream_t s) {
+  return l1_backward(pred, gt, mask, C, N, grad_out, dL_dpred, s);
 }
 
 }  // namespace lsr

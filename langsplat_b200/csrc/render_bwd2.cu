@@ -33,6 +33,16 @@ namespace lsr {
 
 namespace {
 
+__device__ __forceinline__ float bwd_exp(float x) {
+#if LSR_BWD2_FAST_EXP
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x * 1.4426950408889634f));
+  return y;
+#else
+  return expf(x);
+#endif
+}
+
 constexpr int NCOL = 8;                // working instances per phase-B pass
 constexpr int PARTS = 32 / NCOL;       // lanes per instance in phase B
 constexpr int PART_PIX = 64 / PARTS;   // pixels per lane in phase B (16)
@@ -58,10 +68,19 @@ struct __align__(16) Bwd2Smem {
 #define LSR_BWD2_EARLY_CD 0
 #endif
 #ifndef LSR_BWD2_ONE_VOTE
-#define LSR_BWD2_ONE_VOTE 0
+// Measured (GPU call r2m, C2 / C3): three votes 826 / 538 us, one vote 802 / 520 us — every warp-wide vote is a stop
+// in the walk's dependent chain.  (Early colour record: no change; record prefetch: 937 us, it spills.)
+#define LSR_BWD2_ONE_VOTE 1
 #endif
 #ifndef LSR_BWD2_PREFETCH
 #define LSR_BWD2_PREFETCH 0
+#endif
+#ifndef LSR_BWD2_FAST_EXP
+// 1: G = ex2.approx(power * log2 e) (2 instructions) instead of expf (8: range reduction around the same MUFU.EX2).
+// Both are accurate to ~2 ulp, but they are different functions: a pair whose alpha sits within an ulp of 1/255 may be
+// kept here and dropped by the forward (or the reverse), which moves one pixel's T by 0.4 % — far inside the
+// gradients' 1e-4 relative L2 tolerance, but no longer the forward's exact decisions.
+#define LSR_BWD2_FAST_EXP 0
 #endif
 #ifndef LSR_BWD2_PIPE
 // 0: one instance at a time, early-outs, per-slot branches (the default).
@@ -439,12 +458,14 @@ render_bwd2_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, 
       bool mine = false;  // one warp-wide vote per instance instead of three: every vote is a stop in the dependent chain
 #pragma unroll
       for (int s = 0; s < BLEND_SLOTS; s++) {
-        G[s] = expf(power[s]);
+        G[s] = bwd_exp(power[s]);
         alpha[s] = fminf(0.99f, __fmul_rn(bb.z, G[s]));
         contrib[s] = maybe[s] && !(alpha[s] < kAlphaMin);
         mine |= contrib[s];
       }
+#if LSR_BWD2_ONE_VOTE == 1
       if (!__any_sync(0xffffffffu, mine)) continue;
+#endif  // (== 2: no vote at all; an instance nobody contributes to still takes a column of zeros)
 #else
       uint32_t call = 0u;
 #pragma unroll

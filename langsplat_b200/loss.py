@@ -4,6 +4,10 @@ Mirrors `l1_loss(network_output, gt)` of utils/loss_utils.py:17-18; with `mask` 
 as `l1_loss(language_feature * language_feature_mask, gt_language_feature * language_feature_mask)` without the
 two masked temporaries.  One CUDA kernel forward and one backward (csrc/loss.cu) instead of PyTorch's nine elementwise /
 reduction launches.  CUDA float32 only; no CPU path.
+
+`gt` may also be the uint8 image as it is stored on disk ([C,H,W], values 0..255): the kernels then form
+`gt = u / 255` themselves — the value utils/general_utils.py:23 (PILtoTorch) computes on the host — so a training loop
+uploads 1 byte per element per view instead of 4 and no float copy of the image is ever written to device memory.
 """
 from __future__ import annotations
 
@@ -46,7 +50,14 @@ def _mask_rows(mask: Optional[torch.Tensor], pred: torch.Tensor) -> Optional[tor
 class _L1Loss(torch.autograd.Function):
     @staticmethod
     def forward(ctx, pred, gt, mask):
-        pred_c, gt_c = _check(pred, "network_output"), _check(gt, "gt")
+        pred_c = _check(pred, "network_output")
+        u8 = gt.dtype == torch.uint8
+        if u8:
+            if not gt.is_cuda:
+                raise LsrError("l1_loss: gt must be a CUDA tensor (langsplat_b200 has no CPU path)")
+            gt_c = gt.contiguous()
+        else:
+            gt_c = _check(gt, "gt")
         if pred_c.shape != gt_c.shape:
             raise LsrError(f"l1_loss: shapes differ: {tuple(pred_c.shape)} vs {tuple(gt_c.shape)}")
         m = _mask_rows(mask, pred_c)
@@ -59,19 +70,20 @@ class _L1Loss(torch.autograd.Function):
         loss = torch.empty((), dtype=torch.float32, device=pred_c.device)
         stream = ctypes.c_void_p(torch.cuda.current_stream(pred_c.device).cuda_stream)
         with torch.cuda.device(pred_c.device):
-            rc = lib.lsr_l1_loss_forward(_ptr(pred_c), _ptr(gt_c), _ptr(m), C, N, _ptr(loss), stream)
+            fwd = lib.lsr_l1_loss_forward_u8 if u8 else lib.lsr_l1_loss_forward
+            rc = fwd(_ptr(pred_c), _ptr(gt_c), _ptr(m), C, N, _ptr(loss), stream)
         if rc != L.LSR_OK:
             raise LsrError(L.last_error())
         if total == 0:
             loss.fill_(float("nan"))  # torch: mean of an empty tensor
         ctx.save_for_backward(pred_c, gt_c, m if m is not None else torch.empty(0, device=pred_c.device))
-        ctx.dims = (C, N, m is not None)
+        ctx.dims = (C, N, m is not None, u8)
         return loss
 
     @staticmethod
     def backward(ctx, grad_out):
         pred_c, gt_c, m = ctx.saved_tensors
-        C, N, has_mask = ctx.dims
+        C, N, has_mask, u8 = ctx.dims
         if not ctx.needs_input_grad[0]:
             return None, None, None
         lib = L.load()
@@ -79,8 +91,8 @@ class _L1Loss(torch.autograd.Function):
         out = torch.empty_like(pred_c)
         stream = ctypes.c_void_p(torch.cuda.current_stream(pred_c.device).cuda_stream)
         with torch.cuda.device(pred_c.device):
-            rc = lib.lsr_l1_loss_backward(_ptr(pred_c), _ptr(gt_c), _ptr(m) if has_mask else None, C, N, _ptr(g),
-                                          _ptr(out), stream)
+            bwd = lib.lsr_l1_loss_backward_u8 if u8 else lib.lsr_l1_loss_backward
+            rc = bwd(_ptr(pred_c), _ptr(gt_c), _ptr(m) if has_mask else None, C, N, _ptr(g), _ptr(out), stream)
         if rc != L.LSR_OK:
             raise LsrError(L.last_error())
         return out, None, None

@@ -131,3 +131,35 @@ def test_cuda_l1_loss_misaligned_views():
     assert abs(ours.item() - ref.item()) <= 2e-6 * abs(ref.item())
     want = torch.sign(x.detach() * m - gt * m) * m / n
     np.testing.assert_allclose(x.grad.cpu().numpy(), want.cpu().numpy(), rtol=2e-7, atol=0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape,masked,offset", [((3, 1080, 1920), False, 0), ((3, 540, 960), True, 0),
+                                                 ((3, 37, 53), False, 0), ((3, 16, 16), True, 1)])
+def test_cuda_l1_loss_uint8_ground_truth(shape, masked, offset):
+    """gt handed over as the stored 8-bit image: the kernels form u / 255 themselves (IEEE division, the float value
+    utils/general_utils.py:23 computes on the host).  Must equal the float path on `gt_u8 / 255.0` bit for bit in the
+    gradient, and to summation order in the loss; offset 1 = a view that is not 4-byte aligned (scalar path)."""
+    from langsplat_b200 import l1_loss
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(21)
+    n = shape[0] * shape[1] * shape[2]
+    x = torch.rand(shape, generator=g).to(dev).requires_grad_(True)
+    raw = torch.randint(0, 256, (n + offset,), generator=g, dtype=torch.uint8).to(dev)
+    gt_u8 = raw[offset:].view(shape)
+    mask = (torch.rand((1,) + shape[1:], generator=g) > 0.25).to(dev) if masked else None
+    gt_f = (gt_u8.cpu() / 255.0).to(dev)  # PILtoTorch's arithmetic
+    assert gt_f.dtype == torch.float32
+    a = l1_loss(x, gt_u8, mask)
+    a.backward()
+    ga = x.grad.clone()
+    x.grad = None
+    b = l1_loss(x, gt_f, mask)
+    b.backward()
+    assert abs(a.item() - b.item()) <= 1e-6 * abs(b.item())
+    assert torch.equal(ga, x.grad)
+    m = mask.float() if masked else torch.ones((), device=dev)
+    ref = torch.abs(x.detach() * m - gt_f * m).mean()
+    assert abs(a.item() - ref.item()) <= 2e-6 * abs(ref.item())
+    with pytest.raises(Exception):
+        l1_loss(x, gt_u8.cpu(), mask)
