@@ -42,6 +42,7 @@ __device__ __forceinline__ float bwd_exp(float x) {
   return expf(x);
 #endif
 }
+constexpr float kAlphaBand = 4e-6f / 255.0f;  // LSR_BWD2_FAST_EXP == 2: |alpha - 1/255| below this -> expf decides
 
 constexpr int NCOL = 8;                // working instances per phase-B pass
 constexpr int PARTS = 32 / NCOL;       // lanes per instance in phase B
@@ -70,16 +71,20 @@ struct __align__(16) Bwd2Smem {
 #ifndef LSR_BWD2_ONE_VOTE
 // Measured (GPU call r2m, C2 / C3): three votes 826 / 538 us, one vote 802 / 520 us — every warp-wide vote is a stop
 // in the walk's dependent chain.  (Early colour record: no change; record prefetch: 937 us, it spills.)
-#define LSR_BWD2_ONE_VOTE 1
+// 2: no vote at all — an instance nobody contributes to (rare after the batch's rectangle test) takes a column of
+//    zeros.  GPU call r2n: 804 -> 802 us at C2, 522 -> 493 us at C3.
+#define LSR_BWD2_ONE_VOTE 2
 #endif
 #ifndef LSR_BWD2_PREFETCH
 #define LSR_BWD2_PREFETCH 0
 #endif
 #ifndef LSR_BWD2_FAST_EXP
 // 1: G = ex2.approx(power * log2 e) (2 instructions) instead of expf (8: range reduction around the same MUFU.EX2).
-// Both are accurate to ~2 ulp, but they are different functions: a pair whose alpha sits within an ulp of 1/255 may be
-// kept here and dropped by the forward (or the reverse), which moves one pixel's T by 0.4 % — far inside the
-// gradients' 1e-4 relative L2 tolerance, but no longer the forward's exact decisions.
+//    Both are accurate to ~2 ulp, but they are different functions: a pair whose alpha sits within an ulp of 1/255 may
+//    be kept here and dropped by the forward (or the reverse), which moves one pixel's T by 0.4 %.  Measured (GPU call
+//    r2n): 804 -> 774 us at C2, but the full-size C3 / C4 parity tests fail (means2D 2.7e-4 of the largest element).
+// 2: as 1, but a pair whose alpha lands within 4e-6 (relative) of 1/255 is re-evaluated with expf, so every keep /
+//    drop decision is the forward's (both functions are within 1e-6 of exp); G itself differs by <= 4e-7 relative.
 #define LSR_BWD2_FAST_EXP 0
 #endif
 #ifndef LSR_BWD2_PIPE
@@ -460,6 +465,18 @@ render_bwd2_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, 
       for (int s = 0; s < BLEND_SLOTS; s++) {
         G[s] = bwd_exp(power[s]);
         alpha[s] = fminf(0.99f, __fmul_rn(bb.z, G[s]));
+      }
+#if LSR_BWD2_FAST_EXP == 2
+      if (fabsf(alpha[0] - kAlphaMin) < kAlphaBand || fabsf(alpha[1] - kAlphaMin) < kAlphaBand) {
+#pragma unroll
+        for (int s = 0; s < BLEND_SLOTS; s++) {
+          G[s] = expf(power[s]);
+          alpha[s] = fminf(0.99f, __fmul_rn(bb.z, G[s]));
+        }
+      }
+#endif
+#pragma unroll
+      for (int s = 0; s < BLEND_SLOTS; s++) {
         contrib[s] = maybe[s] && !(alpha[s] < kAlphaMin);
         mine |= contrib[s];
       }
