@@ -791,7 +791,9 @@ def main():
         try:
             tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
             if args.config == 2 and args.P is None:
-                names_k = {"sort": "onesweep_kernel_instances", "depth_order": "onesweep_kernel_depth_order"}
+                names_k = {"sort": "onesweep_kernel_instances", "depth_order": "onesweep_kernel_depth_order",
+                           "duplicate": "dup_scan_kernel", "render_bwd": "render_bwd2_kernel",
+                           "tile_ranges": "finalize_tiles_kernel"}
                 traffic = {k: tj.get(names_k.get(k, k + "_kernel"), {}).get("dram_bytes_per_launch") for k in table}
                 for k, e in table.items():
                     if traffic.get(k):

@@ -85,6 +85,8 @@ struct __align__(16) Bwd2Smem {
 //    r2n): 804 -> 774 us at C2, but the full-size C3 / C4 parity tests fail (means2D 2.7e-4 of the largest element).
 // 2: as 1, but a pair whose alpha lands within 4e-6 (relative) of 1/255 is re-evaluated with expf, so every keep /
 //    drop decision is the forward's (both functions are within 1e-6 of exp); G itself differs by <= 4e-7 relative.
+//    Parity green, but SLOWER than expf (GPU call r2o: 819 against 800 us at C2, 529 against 492 us at C3): the band
+//    test and its branch cost more than the six instructions saved.  expf stays.
 #define LSR_BWD2_FAST_EXP 0
 #endif
 #ifndef LSR_BWD2_PIPE
