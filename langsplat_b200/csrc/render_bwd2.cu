@@ -89,6 +89,9 @@ struct __align__(16) Bwd2Smem {
 //    test and its branch cost more than the six instructions saved.  expf stays.
 #define LSR_BWD2_FAST_EXP 0
 #endif
+#ifndef LSR_BWD2_RED_EXPERIMENT
+#define LSR_BWD2_RED_EXPERIMENT 0  // 1 / 2: timing-only variants of the flush (see there); never shipped
+#endif
 #ifndef LSR_BWD2_PIPE
 // 0: one instance at a time, early-outs, per-slot branches (the default).
 // 1: software-pipelined, branch-free walk: front half of instance j+1 next to the back half of instance j.  Measured
@@ -230,6 +233,20 @@ render_bwd2_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, 
         v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
       }
     }
+#if LSR_BWD2_RED_EXPERIMENT == 1
+    // TIMING ONLY (wrong results): no REDs at all — the upper bound of what cheaper accumulation could return
+    if (pb_c < n_used && v[0] == 12345.678f && v[1] == -8765.4321f) atomicAdd(dL_dopacity, v[2]);
+    return;
+#elif LSR_BWD2_RED_EXPERIMENT == 2
+    // TIMING ONLY (wrong results): one 16-byte vector RED per lane instead of three scalar ones, all four lanes of
+    // an instance into its dL_dconic row — the cost of a packed per-Gaussian accumulation record
+    if (pb_c < n_used) {
+      float* dst = dL_dconic + (size_t)__float_as_uint(m.z) * 4;
+      asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(0.f)
+                   : "memory");
+    }
+    return;
+#endif
     if (pb_c < n_used) {
       const uint32_t gid = __float_as_uint(m.z);
       if (pb_q == 0) {
