@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define LSR_VERSION 2
+#define LSR_VERSION 3
 
 typedef enum lsr_status {
   LSR_OK = 0,
@@ -80,6 +80,12 @@ typedef struct lsr_grads {
   float* dL_dcolors_masked;     /* [P,3] optional: the SH gradient's per-view factor (dL_dcolor with the clamp mask of
                                    backward.cu:31-34 applied, zero for culled Gaussians).  Given instead of dL_dsh it
                                    makes lsr_backward skip the 16x larger dL_dsh; see lsr_sh_gradient_from_views */
+  float* blend_acc;             /* [P,16] optional scratch, 64-byte aligned: the blend backward's packed accumulation
+                                   record (one 64-byte record per Gaussian, added to with 16-byte vector reductions
+                                   instead of twelve scalar atomics into five tensors — the reference's atomicAdds of
+                                   backward.cu:552-582).  With it dL_dconic and (when shs are given) dL_dcolors may be
+                                   null, and lsr_backward zero-fills only the record; every gradient buffer passed is
+                                   still fully written.  Contents after the call are unspecified. */
 } lsr_grads;
 
 /* need_mask bits for lsr_backward: which groups of gradients the caller will read
@@ -377,6 +383,9 @@ uint64_t lsr_launch_count(void);
 
 const char* lsr_last_error(void);
 int lsr_version(void);
+/* 1 when lsr_backward uses lsr_grads::blend_acc (the default two-phase blend backward); 0 when the one-phase kernel
+ * was selected (environment LSR_BWD_V1=1) — the caller must then pass dL_dconic / dL_dcolors as before. */
+int lsr_blend_acc_supported(void);
 
 #ifdef __cplusplus
 }

@@ -48,7 +48,10 @@ class Inputs(Structure):
 class Grads(Structure):
     _fields_ = [(n, c_void_p) for n in ("dL_dmeans3D", "dL_dmeans2D", "dL_dsh", "dL_dcolors",
                                          "dL_dlanguage_feature", "dL_dopacity", "dL_dscales", "dL_drotations",
-                                         "dL_dcov3D", "dL_dconic", "dL_dcolors_masked")]
+                                         "dL_dcov3D", "dL_dconic", "dL_dcolors_masked", "blend_acc")]
+
+
+ABI_VERSION = 3  # LSR_VERSION of include/lsr_api.h this module's structures mirror
 
 
 PEER_HANDLE_BYTES, PEER_HEADER_BYTES, MAX_PEERS, MAX_VIEWS = 64, 256, 16, 64  # include/lsr_api.h
@@ -124,6 +127,7 @@ EXPORTS = {
     "lsr_launch_count": (c_uint64, []),
     "lsr_last_error": (c_char_p, []),
     "lsr_version": (c_int, []),
+    "lsr_blend_acc_supported": (c_int, []),
 }
 
 _lib = None
@@ -146,6 +150,9 @@ def load() -> ctypes.CDLL:
             raise ImportError(f"liblsr.so does not export {name}") from e
         fn.restype = res
         fn.argtypes = args
+    if lib.lsr_version() != ABI_VERSION:  # a stale build would read this module's structures with another layout
+        raise ImportError(f"{LIB_PATH} has ABI version {lib.lsr_version()}, this package needs {ABI_VERSION}: "
+                          "rebuild it (`make -C langsplat_b200/csrc`)")
     _lib = lib
     return lib
 

@@ -123,6 +123,7 @@ size_t lsr_array_offset(int which, int32_t P, int32_t width, int32_t height, int
 
 const char* lsr_last_error(void) { return g_err; }
 int lsr_version(void) { return LSR_VERSION; }
+int lsr_blend_acc_supported(void) { return blend_acc_supported() ? 1 : 0; }
 uint64_t lsr_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 void lsr_profile_enable(int on) {
@@ -696,27 +697,44 @@ int lsr_backward(const lsr_frame* frame, const lsr_inputs* in, const int32_t* ra
   const bool dcol = dL_dcolor != nullptr;
   const bool geom_need = (need_mask & LSR_NEED_GEOMETRY) != 0;
   if (!gr.dL_dmeans2D) return fail(LSR_ERR_INVALID, "dL_dmeans2D buffer is required");
-  if (geom_need && (!gr.dL_dconic || !gr.dL_dopacity)) return fail(LSR_ERR_INVALID, "dL_dconic / dL_dopacity required");
-  if (dcol && !gr.dL_dcolors) return fail(LSR_ERR_INVALID, "dL_dcolors buffer required when dL_dcolor is given");
+  const bool have_acc = gr.blend_acc != nullptr && blend_acc_supported();
+  if (geom_need && ((!gr.dL_dconic && !have_acc) || !gr.dL_dopacity))
+    return fail(LSR_ERR_INVALID, "dL_dconic / dL_dopacity required");
+  if (dcol && !gr.dL_dcolors && !have_acc)
+    return fail(LSR_ERR_INVALID, "dL_dcolors buffer required when dL_dcolor is given");
   if (feat && !gr.dL_dlanguage_feature) return fail(LSR_ERR_INVALID, "dL_dlanguage_feature buffer required");
   if (((((uintptr_t)gr.dL_dconic) | ((uintptr_t)gr.dL_drotations)) & 15) != 0)
     return fail(LSR_ERR_INVALID, "dL_dconic and dL_drotations must be 16-byte aligned (read / written as float4)");
   if (g_profile) g_have_b = false;
   prof(g_ev_b, 0, s);
+  // The packed accumulation record (lsr_grads::blend_acc): the blend kernel adds there and the kernel that follows
+  // (per-Gaussian backward, else unpack) writes every element of the per-tensor buffers — only the record is zeroed.
+  const bool run_pre_k = geom_need || (in->shs && (gr.dL_dsh || gr.dL_dcolors_masked) && dcol);
+  float* acc = have_acc ? gr.blend_acc : nullptr;
+  if (acc && (((uintptr_t)acc) & 63) != 0) return fail(LSR_ERR_INVALID, "blend_acc must be 64-byte aligned");
+  if (acc && run_pre_k && geom_need && !gr.dL_dopacity) return fail(LSR_ERR_INVALID, "dL_dopacity required");
   // zero what the blend kernel accumulates into; adjacent buffers are merged into one memset
   {
     std::vector<std::pair<char*, size_t>> z;
     const size_t n = (size_t)P * sizeof(float);
     auto add = [&](float* p, size_t k) { if (p) z.push_back({(char*)p, n * k}); };
-    add(gr.dL_dmeans2D, 3);
-    add(gr.dL_dconic, 4);
-    add(gr.dL_dopacity, 1);
-    add(gr.dL_dcolors, 3);
-    add(gr.dL_dlanguage_feature, 3);
+    if (acc) {
+      add(acc, ACC_FLOATS);
+      if (!dcol) add(gr.dL_dcolors, 3);  // (nothing is accumulated for it and nobody would write it)
+      if (!feat) add(gr.dL_dlanguage_feature, 3);
+      add(gr.dL_dconic, 4);  // (optional with a record: nothing ever lands in it)
+      if (!run_pre_k) add(gr.dL_dopacity, 1);
+    } else {
+      add(gr.dL_dmeans2D, 3);
+      add(gr.dL_dconic, 4);
+      add(gr.dL_dopacity, 1);
+      add(gr.dL_dcolors, 3);
+      add(gr.dL_dlanguage_feature, 3);
+    }
     // outputs the per-Gaussian kernel will not write in this configuration
     const bool run_pre = geom_need || (in->shs && (gr.dL_dsh || gr.dL_dcolors_masked) && dcol);
     if (!run_pre) { add(gr.dL_dmeans3D, 3); add(gr.dL_dcov3D, 6); add(gr.dL_dscales, 3); add(gr.dL_drotations, 4); }
-    if (!run_pre || !in->shs || !gr.dL_dcolors) { if (gr.dL_dsh && frame->M > 0) add(gr.dL_dsh, (size_t)frame->M * 3); }
+    if (!run_pre || !in->shs || !(gr.dL_dcolors || acc)) { if (gr.dL_dsh && frame->M > 0) add(gr.dL_dsh, (size_t)frame->M * 3); }
     if (run_pre && !in->scales) { add(gr.dL_dscales, 3); add(gr.dL_drotations, 4); }
     std::sort(z.begin(), z.end());
     size_t i = 0;
@@ -734,15 +752,18 @@ int lsr_backward(const lsr_frame* frame, const lsr_inputs* in, const int32_t* ra
   ImageView img = image_view(const_cast<void*>(image), W, H);
   launch_render_bwd(W, H, img.ranges, img.tile_order, (const uint32_t*)list, g.rec, frame->bg, frame->include_feature != 0,
                     img.final_T, img.n_contrib, dL_dcolor, dL_dfeature, need_mask, gr.dL_dmeans2D, gr.dL_dconic,
-                    gr.dL_dopacity, gr.dL_dcolors, gr.dL_dlanguage_feature, s);
+                    gr.dL_dopacity, gr.dL_dcolors, gr.dL_dlanguage_feature, acc, s);
   LSR_STAGE("render_bwd");
   prof(g_ev_b, 2, s);
   if (geom_need || (in->shs && (gr.dL_dsh || gr.dL_dcolors_masked) && dcol)) {
-    if (!gr.dL_dconic) return fail(LSR_ERR_INVALID, "dL_dconic required for the per-Gaussian backward");
+    if (!gr.dL_dconic && !acc) return fail(LSR_ERR_INVALID, "dL_dconic required for the per-Gaussian backward");
     const float focal_y = H / (2.0f * frame->tanfovy);
     const float focal_x = W / (2.0f * frame->tanfovx);
-    launch_preprocess_bwd(*frame, *in, focal_x, focal_y, radii, g, need_mask, gr, s);
+    launch_preprocess_bwd(*frame, *in, focal_x, focal_y, radii, g, need_mask, gr, acc, s);
     LSR_STAGE("preprocess_bwd");
+  } else if (acc) {
+    launch_unpack_acc(P, acc, gr.dL_dmeans2D, dcol ? gr.dL_dcolors : nullptr, feat ? gr.dL_dlanguage_feature : nullptr, s);
+    LSR_STAGE("unpack_acc");
   }
   prof(g_ev_b, 3, s);
   if (g_profile) g_have_b = true;

@@ -257,14 +257,23 @@ void launch_refeature_render(int P, int W, int H, const int32_t* radii, const fl
 void launch_render_bwd(int W, int H, const uint2* ranges, const uint32_t* order, const uint32_t* list, const GeomRec* rec, const float* bg,
                        bool include_feature, const float* final_T, const uint32_t* n_contrib, const float* dL_dcolor,
                        const float* dL_dfeature, uint32_t need_mask, float* dL_dmean2D, float* dL_dconic,
-                       float* dL_dopacity, float* dL_dcolors, float* dL_dfeat, cudaStream_t s);
+                       float* dL_dopacity, float* dL_dcolors, float* dL_dfeat, float* acc, cudaStream_t s);
+// Packed accumulation record of the blend backward (lsr_grads::blend_acc): ACC_FLOATS floats per Gaussian, 64-byte
+// aligned — (Mx, My, M0, 0) (Mxx, Mxy, Myy, 0) (dL_dcolour, 0) (dL_dfeature, 0); without LSR_NEED_GEOMETRY the first
+// quarter holds the finished (dL_dmean2D.x, .y, 0, 0) and the second stays zero.  With `acc` given the kernel adds
+// there (vector REDs) and leaves the five per-tensor buffers alone.
+constexpr int ACC_FLOATS = 16;
+bool blend_acc_supported();  // false when the one-phase kernel was selected (LSR_BWD_V1=1) or LSR_MOMENTS=0
+// acc -> dL_dmean2D [P,3], dL_dcolors [P,3], dL_dfeat [P,3] (each optional) when no per-Gaussian kernel follows
+void launch_unpack_acc(int P, const float* acc, float* dL_dmean2D, float* dL_dcolors, float* dL_dfeat, cudaStream_t s);
 // the two-phase variant of the same kernel (render_bwd2.cu), same contract
 void launch_render_bwd2(int W, int H, const uint2* ranges, const uint32_t* order, const uint32_t* list, const GeomRec* rec, const float* bg,
                         bool include_feature, const float* final_T, const uint32_t* n_contrib, const float* dL_dcolor,
                         const float* dL_dfeature, uint32_t need_mask, float* dL_dmean2D, float* dL_dconic,
-                        float* dL_dopacity, float* dL_dcolors, float* dL_dfeat, cudaStream_t s);
+                        float* dL_dopacity, float* dL_dcolors, float* dL_dfeat, float* acc, cudaStream_t s);
 void launch_preprocess_bwd(const lsr_frame& f, const lsr_inputs& in, float focal_x, float focal_y,
-                           const int32_t* radii, GeomView g, uint32_t need_mask, const lsr_grads& gr, cudaStream_t s);
+                           const int32_t* radii, GeomView g, uint32_t need_mask, const lsr_grads& gr, const float* acc,
+                           cudaStream_t s);
 // dL_dsh [P,M,3] = sum over V views of basis(normalize(mean - campos_v)) (x) g_v, g: [V,P,3] clamp-masked dL_dcolor
 void launch_sh_grad_views(int P, int D, int M, int V, const float* means3D, const float* campos, const float* g,
                           float* dL_dsh, cudaStream_t s);

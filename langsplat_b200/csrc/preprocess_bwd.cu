@@ -136,7 +136,12 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
                       float ddely_dy, float* __restrict__ dL_dmean2D,
                       const float* __restrict__ dL_dconic, const float* __restrict__ dL_dcolor,
                       float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
-                      float* __restrict__ dL_dscale, float* __restrict__ dL_drot, float* __restrict__ dL_dcolor_masked) {
+                      float* __restrict__ dL_dscale, float* __restrict__ dL_drot, float* __restrict__ dL_dcolor_masked,
+                      const float4* __restrict__ acc, float* __restrict__ dL_dopacity_out,
+                      float* __restrict__ dL_dcolor_out, float* __restrict__ dL_dfeat_out) {
+  // `acc` (lsr_grads::blend_acc): the blend kernel left everything it accumulated in one 64-byte record per Gaussian
+  // instead of dL_dmean2D / dL_dconic / dL_dcolor / dL_dopacity / dL_dlanguage_feature; this kernel then reads the
+  // record and WRITES those tensors (every element: zeros for Gaussians nobody touched)
   extern __shared__ __align__(16) float4 s_dyn[];
   __shared__ __align__(16) float s_xyz[BPRE_THREADS * 3];   // means3D in, dL_dmean3D out
   __shared__ __align__(16) float s_scl[BPRE_THREADS * 3];   // scales in, dL_dscale out
@@ -154,7 +159,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   // factored SH gradient: dL_dsh[k][ch] = basis_k(dir) * g[ch] with g = dL_dcolor masked by the clamp (backward.cu:31-34)
   // — a caller that wants the factor g instead of the 16x larger product passes dL_dcolor_masked and no dL_dsh
   const bool write_sh = dL_dsh != nullptr;
-  const bool do_sh = shs != nullptr && (write_sh || dL_dcolor_masked != nullptr) && dL_dcolor != nullptr;
+  const bool do_sh = shs != nullptr && (write_sh || dL_dcolor_masked != nullptr) && (dL_dcolor != nullptr || acc != nullptr);
   const bool do_scale = scales != nullptr && dL_dscale != nullptr;
   const bool valid = tid < count;
   const int idx = first + tid;
@@ -168,9 +173,16 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   // Everything this CTA reads is requested up front with cp.async: group 0 = the flat triplet arrays and the cov3D
   // rows (needed first), group 1 = the SH rows of the visible Gaussians, which then fly during the geometry backward.
   stage_flat_async<BPRE_THREADS>(means3D, s_xyz, (size_t)first * 3, count * 3, tid);
-  stage_flat_async<BPRE_THREADS>(dL_dmean2D, s_m2d, (size_t)first * 3, count * 3, tid);
+  if (!acc) stage_flat_async<BPRE_THREADS>(dL_dmean2D, s_m2d, (size_t)first * 3, count * 3, tid);
   if (do_scale) stage_flat_async<BPRE_THREADS>(scales, s_scl, (size_t)first * 3, count * 3, tid);
-  if (do_sh) stage_flat_async<BPRE_THREADS>(dL_dcolor, s_dcol, (size_t)first * 3, count * 3, tid);
+  if (do_sh && !acc) stage_flat_async<BPRE_THREADS>(dL_dcolor, s_dcol, (size_t)first * 3, count * 3, tid);
+  float4 rec_m = make_float4(0.f, 0.f, 0.f, 0.f), rec_q = rec_m, rec_c = rec_m, rec_f = rec_m;
+  if (acc && valid) {  // this thread's record: four 16-byte loads, in flight beside the cp.async groups
+    rec_m = __ldg(acc + 4 * (size_t)idx);
+    rec_q = __ldg(acc + 4 * (size_t)idx + 1);
+    rec_c = __ldg(acc + 4 * (size_t)idx + 2);
+    rec_f = __ldg(acc + 4 * (size_t)idx + 3);
+  }
   {
     const float2* src = reinterpret_cast<const float2*>(cov3Ds + wfirst * 6);
 #pragma unroll
@@ -185,6 +197,21 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   cp_async_commit();
   cp_async_wait<1>();
   __syncthreads();
+  if (acc) {
+    s_m2d[3 * tid] = rec_m.x; s_m2d[3 * tid + 1] = rec_m.y; s_m2d[3 * tid + 2] = 0.f;
+    s_dcol[3 * tid] = rec_c.x; s_dcol[3 * tid + 1] = rec_c.y; s_dcol[3 * tid + 2] = rec_c.z;
+    if (valid) {
+      if (dL_dopacity_out) dL_dopacity_out[idx] = rec_m.z;  // M0 = sum of G * dL_dalpha IS dL_dopacity
+      if (dL_dfeat_out) {
+        dL_dfeat_out[3 * (size_t)idx] = rec_f.x; dL_dfeat_out[3 * (size_t)idx + 1] = rec_f.y;
+        dL_dfeat_out[3 * (size_t)idx + 2] = rec_f.z;
+      }
+      if (dL_dcolor_out) {
+        dL_dcolor_out[3 * (size_t)idx] = rec_c.x; dL_dcolor_out[3 * (size_t)idx + 1] = rec_c.y;
+        dL_dcolor_out[3 * (size_t)idx + 2] = rec_c.z;
+      }
+    }
+  }
   float cov3D[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   if (vis) {
     const float2 a = wcov[lane * 3], b = wcov[lane * 3 + 1], c = wcov[lane * 3 + 2];
@@ -198,7 +225,8 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
     // ---------------- computeCov2DCUDA (backward.cu:144-274) ----------------
     Cov2D c2;
     compute_cov2D(mx, my, mz, h_x, h_y, tan_fovx, tan_fovy, cov3D, s_view, c2);
-    const float4 dcon = __ldg(reinterpret_cast<const float4*>(dL_dconic) + idx);
+    const float4 dcon = acc ? make_float4(rec_q.x, rec_q.y, 0.f, rec_q.z)
+                            : __ldg(reinterpret_cast<const float4*>(dL_dconic) + idx);
     float dLc_x = dcon.x, dLc_y = dcon.y, dLc_z = dcon.w;
     if (moments) {
       // dL_dconic = -0.5 * o * (Mxx, Mxy, Myy);  dL_dmean2D = -o * (cx*Mx + cy*My, cz*My + cy*Mx) * (W/2, H/2).
@@ -404,7 +432,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D, co
   s_scl[3 * tid] = dscale[0]; s_scl[3 * tid + 1] = dscale[1]; s_scl[3 * tid + 2] = dscale[2];
   __syncthreads();
   if (dL_dmean3D) unstage_flat<BPRE_THREADS>(dL_dmean3D, s_xyz, (size_t)first * 3, count * 3, tid);
-  if (moments) unstage_flat<BPRE_THREADS>(dL_dmean2D, s_m2d, (size_t)first * 3, count * 3, tid);
+  if (moments || acc) unstage_flat<BPRE_THREADS>(dL_dmean2D, s_m2d, (size_t)first * 3, count * 3, tid);
   if (do_sh && dL_dcolor_masked) unstage_flat<BPRE_THREADS>(dL_dcolor_masked, s_dcol, (size_t)first * 3, count * 3, tid);
   if (do_scale) unstage_flat<BPRE_THREADS>(dL_dscale, s_scl, (size_t)first * 3, count * 3, tid);
 }
@@ -487,10 +515,38 @@ sh_grad_views_kernel(int P, int D, int M, int V, const float* __restrict__ means
   }
 }
 
+// acc -> the per-tensor gradients, for backward passes that do not run the per-Gaussian kernel (feature-only training)
+__global__ void __launch_bounds__(256)
+unpack_acc_kernel(int P, const float4* __restrict__ acc, float* __restrict__ dL_dmean2D, float* __restrict__ dL_dcolors,
+                  float* __restrict__ dL_dfeat) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P) return;
+  if (dL_dmean2D) {
+    const float4 m = __ldg(acc + 4 * (size_t)idx);
+    dL_dmean2D[3 * (size_t)idx] = m.x; dL_dmean2D[3 * (size_t)idx + 1] = m.y; dL_dmean2D[3 * (size_t)idx + 2] = 0.f;
+  }
+  if (dL_dcolors) {
+    const float4 c = __ldg(acc + 4 * (size_t)idx + 2);
+    dL_dcolors[3 * (size_t)idx] = c.x; dL_dcolors[3 * (size_t)idx + 1] = c.y; dL_dcolors[3 * (size_t)idx + 2] = c.z;
+  }
+  if (dL_dfeat) {
+    const float4 f = __ldg(acc + 4 * (size_t)idx + 3);
+    dL_dfeat[3 * (size_t)idx] = f.x; dL_dfeat[3 * (size_t)idx + 1] = f.y; dL_dfeat[3 * (size_t)idx + 2] = f.z;
+  }
+}
+
 }  // namespace
 
+void launch_unpack_acc(int P, const float* acc, float* dL_dmean2D, float* dL_dcolors, float* dL_dfeat, cudaStream_t s) {
+  if (P <= 0) return;
+  unpack_acc_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, reinterpret_cast<const float4*>(acc), dL_dmean2D, dL_dcolors,
+                                                    dL_dfeat);
+  count_launch();
+}
+
 void launch_preprocess_bwd(const lsr_frame& f, const lsr_inputs& in, float focal_x, float focal_y,
-                           const int32_t* radii, GeomView g, uint32_t need_mask, const lsr_grads& gr, cudaStream_t s) {
+                           const int32_t* radii, GeomView g, uint32_t need_mask, const lsr_grads& gr, const float* acc,
+                           cudaStream_t s) {
   if (f.P <= 0) return;
   // the blend kernel leaves moments instead of gradients exactly when it ran in its GEOM mode (render_bwd.cu)
   const int moments = (LSR_MOMENTS && (need_mask & LSR_NEED_GEOMETRY)) ? 1 : 0;
@@ -509,7 +565,8 @@ void launch_preprocess_bwd(const lsr_frame& f, const lsr_inputs& in, float focal
       0.5f * f.width,                                                                                              \
       0.5f * f.height, gr.dL_dmeans2D, gr.dL_dconic,                                                               \
       gr.dL_dcolors, gr.dL_dmeans3D, gr.dL_dcov3D, gr.dL_dsh, gr.dL_dscales, gr.dL_drotations,                      \
-      gr.dL_dcolors_masked
+      gr.dL_dcolors_masked, reinterpret_cast<const float4*>(acc), acc ? gr.dL_dopacity : nullptr,                    \
+      acc ? gr.dL_dcolors : nullptr, acc ? gr.dL_dlanguage_feature : nullptr
   if (sh16) preprocess_bwd_kernel<true><<<blocks, BPRE_THREADS, BPRE_SH_SMEM, s>>>(LSR_BPRE_ARGS);
   else preprocess_bwd_kernel<false><<<blocks, BPRE_THREADS, BPRE_SH_SMEM, s>>>(LSR_BPRE_ARGS);
 #undef LSR_BPRE_ARGS

@@ -328,19 +328,28 @@ void launch_one(unsigned grid, cudaStream_t s, int W, int H, int tiles_x, const 
 
 }  // namespace
 
+bool blend_acc_supported() {
+#if LSR_MOMENTS
+  static const bool v1 = getenv("LSR_BWD_V1") != nullptr;
+  return !v1;
+#else
+  return false;
+#endif
+}
+
 void launch_render_bwd(int W, int H, const uint2* ranges, const uint32_t* order, const uint32_t* list,
                        const GeomRec* rec, const float* bg, bool include_feature, const float* final_T, const uint32_t* n_contrib, const float* dL_dcolor,
                        const float* dL_dfeature, uint32_t need_mask, float* dL_dmean2D, float* dL_dconic,
-                       float* dL_dopacity, float* dL_dcolors, float* dL_dfeat, cudaStream_t s) {
+                       float* dL_dopacity, float* dL_dcolors, float* dL_dfeat, float* acc, cudaStream_t s) {
 #if LSR_MOMENTS
   // the two-phase kernel (render_bwd2.cu) is the default; LSR_BWD_V1=1 selects this file's one-phase kernel (A/B)
-  static const bool v1 = getenv("LSR_BWD_V1") != nullptr;
-  if (!v1) {
+  if (blend_acc_supported()) {
     launch_render_bwd2(W, H, ranges, order, list, rec, bg, include_feature, final_T, n_contrib, dL_dcolor, dL_dfeature,
-                       need_mask, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolors, dL_dfeat, s);
+                       need_mask, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolors, dL_dfeat, acc, s);
     return;
   }
 #endif
+  (void)acc;  // the one-phase kernel accumulates into the per-tensor buffers only (lsr_backward passes no record then)
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
   if (tiles_x == 0 || tiles_y == 0) return;
   const unsigned grid = (unsigned)tiles_x * (unsigned)tiles_y * QUADS;

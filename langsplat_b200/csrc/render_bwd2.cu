@@ -89,9 +89,6 @@ struct __align__(16) Bwd2Smem {
 //    test and its branch cost more than the six instructions saved.  expf stays.
 #define LSR_BWD2_FAST_EXP 0
 #endif
-#ifndef LSR_BWD2_RED_EXPERIMENT
-#define LSR_BWD2_RED_EXPERIMENT 0  // 1 / 2: timing-only variants of the flush (see there); never shipped
-#endif
 #ifndef LSR_BWD2_PIPE
 // 0: one instance at a time, early-outs, per-slot branches (the default).
 // 1: software-pipelined, branch-free walk: front half of instance j+1 next to the back half of instance j.  Measured
@@ -108,7 +105,7 @@ render_bwd2_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, 
                    const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
                    const float* __restrict__ dL_dpixels, const float* __restrict__ dL_dpixels_F,
                    float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity,
-                   float* __restrict__ dL_dcolors, float* __restrict__ dL_dfeat) {
+                   float* __restrict__ dL_dcolors, float* __restrict__ dL_dfeat, float* __restrict__ acc) {
   __shared__ Bwd2Smem sm;
 
   const int lane = threadIdx.x;
@@ -233,20 +230,29 @@ render_bwd2_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, 
         v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
       }
     }
-#if LSR_BWD2_RED_EXPERIMENT == 1
-    // TIMING ONLY (wrong results): no REDs at all — the upper bound of what cheaper accumulation could return
-    if (pb_c < n_used && v[0] == 12345.678f && v[1] == -8765.4321f) atomicAdd(dL_dopacity, v[2]);
-    return;
-#elif LSR_BWD2_RED_EXPERIMENT == 2
-    // TIMING ONLY (wrong results): one 16-byte vector RED per lane instead of three scalar ones, all four lanes of
-    // an instance into its dL_dconic row — the cost of a packed per-Gaussian accumulation record
-    if (pb_c < n_used) {
-      float* dst = dL_dconic + (size_t)__float_as_uint(m.z) * 4;
-      asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(0.f)
-                   : "memory");
+    if (acc != nullptr) {
+      // Packed accumulation: the instance's four lanes each add their three sums (and a zero) to one 16-byte quarter
+      // of the Gaussian's 64-byte record with ONE vector RED — 1 instruction and 16 sectors per flush instead of 12
+      // instructions and 96 sectors.  ncu (profiles/r2o): the L1 data pipe was 76 % busy, a quarter of its wavefronts
+      // the scalar REDs; timing-only experiments (GPU call r2p): no REDs at all 740 us, vector REDs 740 us, scalar
+      // REDs 799 us.  The per-Gaussian kernel (or unpack_acc_kernel) reads the record back.
+      if (pb_c < n_used) {
+        float a0 = v[0], a1 = v[1], a2 = v[2];
+        bool live = pb_q == 0 || (pb_q == 1 && GEOM) || (pb_q == 2 && DCOL) || (pb_q == 3 && FEAT);
+        if (!GEOM && pb_q == 0) {  // nobody applies the coefficients later: finish dL_dmean2D here (see below)
+          const float4 cn = lds128(pb_conic);
+          a0 = -m.w * (cn.x * v[0] + cn.y * v[1]) * half_W;
+          a1 = -m.w * (cn.z * v[1] + cn.y * v[0]) * half_H;
+          a2 = 0.f;
+        }
+        if (live) {
+          float* dst = acc + (size_t)__float_as_uint(m.z) * ACC_FLOATS + pb_q * 4;
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(a0), "f"(a1), "f"(a2), "f"(0.f)
+                       : "memory");
+        }
+      }
+      return;
     }
-    return;
-#endif
     if (pb_c < n_used) {
       const uint32_t gid = __float_as_uint(m.z);
       if (pb_q == 0) {
@@ -574,10 +580,10 @@ template <bool FEAT, bool DCOL, bool GEOM>
 void launch_one(unsigned grid, cudaStream_t s, int W, int H, int tiles_x, const uint2* ranges, const uint32_t* order,
                 const uint32_t* list, const GeomRec* rec, const float* bg, const float* final_T, const uint32_t* n_contrib,
                 const float* dL_dcolor, const float* dL_dfeature, float* dL_dmean2D, float* dL_dconic,
-                float* dL_dopacity, float* dL_dcolors, float* dL_dfeat) {
+                float* dL_dopacity, float* dL_dcolors, float* dL_dfeat, float* acc) {
   render_bwd2_kernel<FEAT, DCOL, GEOM><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, order, list, rec, bg, final_T,
                                                          n_contrib, dL_dcolor, dL_dfeature, dL_dmean2D, dL_dconic,
-                                                         dL_dopacity, dL_dcolors, dL_dfeat);
+                                                         dL_dopacity, dL_dcolors, dL_dfeat, acc);
 }
 
 }  // namespace
@@ -586,7 +592,7 @@ void launch_render_bwd2(int W, int H, const uint2* ranges, const uint32_t* order
                         const GeomRec* rec, const float* bg, bool include_feature, const float* final_T,
                         const uint32_t* n_contrib, const float* dL_dcolor, const float* dL_dfeature, uint32_t need_mask,
                         float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolors, float* dL_dfeat,
-                        cudaStream_t s) {
+                        float* acc, cudaStream_t s) {
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
   if (tiles_x == 0 || tiles_y == 0) return;
   const unsigned grid = (unsigned)tiles_x * (unsigned)tiles_y * QUADS;
@@ -596,7 +602,7 @@ void launch_render_bwd2(int W, int H, const uint2* ranges, const uint32_t* order
   if (!feat && !dcol) return;  // no upstream gradient at all: everything stays zero
 #define LSR_BWD(F, D, G)                                                                                      \
   launch_one<F, D, G>(grid, s, W, H, tiles_x, ranges, order, list, rec, bg, final_T, n_contrib, dL_dcolor,   \
-                      dL_dfeature, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolors, dL_dfeat)
+                      dL_dfeature, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolors, dL_dfeat, acc)
   if (feat) {
     if (dcol) { if (geom) LSR_BWD(true, true, true); else LSR_BWD(true, true, false); }
     else      { if (geom) LSR_BWD(true, false, true); else LSR_BWD(true, false, false); }

@@ -66,6 +66,9 @@ _capacity_retries = 0  # how often lsr_forward had to be repeated with a larger 
 # forward / backward on that device (or, waiting, by `check_async_status()`): an instance list that turned out too
 # small raises LsrError there, and that frame's images were NaN-filled on the device, so an incomplete render can
 # never pass for a result.  Same kernels, same results as the synchronous path.
+_USE_BLEND_ACC = os.environ.get("LSR_BLEND_ACC", "1") != "0"  # packed accumulation record in the backward (A/B switch)
+
+
 class _AsyncConfig:
     enabled = os.environ.get("LSR_ASYNC_FORWARD", "0") not in ("", "0")
     capacity_margin = 1.5
@@ -419,35 +422,46 @@ def _backward_impl(state, grad_color, grad_feature, need_mask: int, want_sh: boo
     # zero-fills what the blend kernel accumulates into (adjacent ranges merge into one memset).
     factored = sh_factor_out is not None and run_pre and sh is not None and gc is not None
     n_sh = M * 3 if (run_pre and sh is not None and not factored) else 0
+    # The blend kernel accumulates into ONE packed 64-byte record per Gaussian ("acc", lsr_grads::blend_acc: 16-byte
+    # vector reductions instead of twelve scalar atomics into five tensors); the kernel behind it writes the tensors.
+    # No dL_dconic buffer then, and no dL_dcolors unless the caller gets it back (colors_precomp).  LSR_BLEND_ACC=0
+    # keeps the five accumulators (A/B, and what the one-phase kernel of LSR_BWD_V1=1 needs).
+    use_acc = _USE_BLEND_ACC and bool(lib.lsr_blend_acc_supported())
+    need_colors = not use_acc or sh is None
     sizes = [("rots", 4 if run_pre else 0), ("sh", n_sh), ("means3D", 3 if run_pre else 0),
-             ("scales", 3 if run_pre else 0), ("feat", 3), ("opac", 1), ("|", 0), ("conic", 4), ("means2D", 3),
-             ("colors", 3), ("cov3D", 6 if run_pre else 0)]
+             ("scales", 3 if run_pre else 0), ("feat", 3), ("opac", 1), ("|", 0), ("acc", 16 if use_acc else 0),
+             ("conic", 0 if use_acc else 4), ("means2D", 3), ("colors", 3 if need_colors else 0),
+             ("cov3D", 6 if run_pre else 0)]
     # A sink may provide the memory of the parameter gradients (PeerFactorExchange: peer-visible staging memory, so
     # that the all-reduce reads them in place); the internal accumulators then come from their own allocation.
     n_params = sum(n for _, n in sizes[:sizes.index(("|", 0))]) * P
     lead = sh_factor_out.new_flat(n_params, device) if factored and hasattr(sh_factor_out, "new_flat") else None
     if lead is None:
-        flat = torch.empty((sum(n for _, n in sizes) * P + 4,), **f32)
+        flat = torch.empty((sum(n for _, n in sizes) * P + 16,), **f32)
     else:
-        flat = torch.empty((sum(n for _, n in sizes) * P + 4 - n_params,), **f32)
+        flat = torch.empty((sum(n for _, n in sizes) * P + 16 - n_params,), **f32)
     part, off, buf = {}, 0, (flat if lead is None else lead)
     for name, n in sizes:
         if name == "|":
             if lead is None:
-                off = (off + 3) // 4 * 4
+                off = (off + 15) // 16 * 16  # the record needs 64-byte alignment (allocations start 512-byte aligned)
             else:
                 buf, off = flat, 0
             continue
         part[name] = buf[off:off + n * P] if n else None
         off += n * P
-    d_conic = part["conic"].view(P, 4)
+    d_conic = part["conic"].view(P, 4) if part["conic"] is not None else None
     d_means2D = part["means2D"].view(P, 3)
     d_opac = part["opac"].view(P, 1)
-    d_colors = part["colors"].view(P, 3)
+    d_colors = part["colors"].view(P, 3) if part["colors"] is not None else None
     d_feat = part["feat"].view(P, 3)
     g = L.Grads()
-    g.dL_dmeans2D, g.dL_dconic, g.dL_dopacity = d_means2D.data_ptr(), d_conic.data_ptr(), d_opac.data_ptr()
-    g.dL_dcolors, g.dL_dlanguage_feature = d_colors.data_ptr(), d_feat.data_ptr()
+    g.dL_dmeans2D, g.dL_dopacity, g.dL_dlanguage_feature = d_means2D.data_ptr(), d_opac.data_ptr(), d_feat.data_ptr()
+    g.dL_dconic = d_conic.data_ptr() if d_conic is not None else None
+    g.dL_dcolors = d_colors.data_ptr() if d_colors is not None else None
+    if use_acc:
+        g.blend_acc = part["acc"].data_ptr()
+        assert g.blend_acc % 64 == 0
     d_means3D = d_cov3D = d_sh = d_scales = d_rots = None
     if run_pre:
         d_means3D = part["means3D"].view(P, 3)

@@ -51,7 +51,7 @@ def test_struct_layouts_match_header_field_order():
 
 def test_size_queries_and_offsets():
     lib = L.load()
-    assert lib.lsr_version() == 2
+    assert lib.lsr_version() == 3 == L.ABI_VERSION
     assert lib.lsr_geom_bytes(0) >= 0
     P, W, H, cap = 1000, 250, 130, 5000
     g = lib.lsr_geom_bytes(P)
