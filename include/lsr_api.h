@@ -75,7 +75,7 @@ typedef struct lsr_grads {
   float* dL_dopacity;           /* [P] */
   float* dL_dscales;            /* [P,3] */
   float* dL_drotations;         /* [P,4] */
-  float* dL_dcov3D;             /* [P,6] */
+  float* dL_dcov3D;             /* [P,6], 8-byte aligned */
   float* dL_dconic;             /* [P,4] (internal in the reference; exposed for tests) */
   float* dL_dcolors_masked;     /* [P,3] optional: the SH gradient's per-view factor (dL_dcolor with the clamp mask of
                                    backward.cu:31-34 applied, zero for culled Gaussians).  Given instead of dL_dsh it

@@ -705,6 +705,8 @@ int lsr_backward(const lsr_frame* frame, const lsr_inputs* in, const int32_t* ra
   if (feat && !gr.dL_dlanguage_feature) return fail(LSR_ERR_INVALID, "dL_dlanguage_feature buffer required");
   if (((((uintptr_t)gr.dL_dconic) | ((uintptr_t)gr.dL_drotations)) & 15) != 0)
     return fail(LSR_ERR_INVALID, "dL_dconic and dL_drotations must be 16-byte aligned (read / written as float4)");
+  if ((((uintptr_t)gr.dL_dcov3D) & 7) != 0)
+    return fail(LSR_ERR_INVALID, "dL_dcov3D must be 8-byte aligned (written as float2)");
   if (g_profile) g_have_b = false;
   prof(g_ev_b, 0, s);
   // The packed accumulation record (lsr_grads::blend_acc): the blend kernel adds there and the kernel that follows

@@ -430,8 +430,8 @@ def _backward_impl(state, grad_color, grad_feature, need_mask: int, want_sh: boo
     need_colors = not use_acc or sh is None
     sizes = [("rots", 4 if run_pre else 0), ("sh", n_sh), ("means3D", 3 if run_pre else 0),
              ("scales", 3 if run_pre else 0), ("feat", 3), ("opac", 1), ("|", 0), ("acc", 16 if use_acc else 0),
-             ("conic", 0 if use_acc else 4), ("means2D", 3), ("colors", 3 if need_colors else 0),
-             ("cov3D", 6 if run_pre else 0)]
+             ("conic", 0 if use_acc else 4), ("cov3D", 6 if run_pre else 0), ("means2D", 3),
+             ("colors", 3 if need_colors else 0)]  # (cov3D is written as float2: it follows the 16-byte-aligned parts)
     # A sink may provide the memory of the parameter gradients (PeerFactorExchange: peer-visible staging memory, so
     # that the all-reduce reads them in place); the internal accumulators then come from their own allocation.
     n_params = sum(n for _, n in sizes[:sizes.index(("|", 0))]) * P

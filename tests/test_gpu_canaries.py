@@ -149,3 +149,26 @@ def test_async_forward_clips_an_overflowing_list(guarded):
         lsb.check_async_status()
         assert torch.isfinite(ok["color"]).all()
     guarded.check()
+
+
+@pytest.mark.parametrize("P", [8001, 4099])
+def test_odd_gaussian_counts_keep_every_vector_access_aligned(guarded, P):
+    """The backward's buffers are slices of one allocation whose offsets depend on P: with an odd P the float2 / float4
+    accesses (dL_dcov3D, dL_drotations, the accumulation record) must still land on aligned addresses — dense SH
+    gradient, factored SH gradient (no colour buffer at all) and precomputed colours."""
+    from langsplat_b200 import dist as D
+    scene, cams = syn.make_config(4, P=P, W=160, H=120, n_cameras=1)
+    dcol, dfeat = _grads(cams[0], 8)
+    names = ("means3D", "shs", "opacities", "scales", "rotations", "language_feature")
+    dense = run_module(R.GaussianRasterizer, R.GaussianRasterizationSettings, scene, cams[0], grads=(dcol, dfeat),
+                       requires=names)
+    with D.factored_sh_gradients() as factors:
+        fact = run_module(R.GaussianRasterizer, R.GaussianRasterizationSettings, scene, cams[0], grads=(dcol, dfeat),
+                          requires=names)
+    assert len(factors) == 1
+    for k in ("means3D", "scales", "rotations", "opacities", "language_feature"):
+        assert torch.isfinite(fact["grads"][k]).all() and torch.isfinite(dense["grads"][k]).all()
+    cp = torch.rand(P, 3, generator=torch.Generator().manual_seed(2))
+    run_module(R.GaussianRasterizer, R.GaussianRasterizationSettings, scene, cams[0], use_colors_precomp=cp,
+               grads=(dcol, dfeat), requires=("means3D", "colors_precomp", "opacities", "scales", "rotations"))
+    guarded.check()
