@@ -362,6 +362,20 @@ int lsr_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* k
                    uint64_t* keys_tmp, uint32_t* vals_tmp, int64_t n, int end_bit, void* work, size_t work_bytes,
                    void* stream);
 
+/* lsr_sort_pairs without any allocation by caller or library.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving
+ * loops, harnesses that forbid it).  Same kernels and same result as lsr_sort_pairs, but the work area and the two
+ * ping-pong buffers are a static device array inside the library (14.8 MB per GPU that loads liblsr.so, held until
+ * the process exits) instead of caller-provided memory: the caller passes only inputs and outputs.  The call makes
+ * no cudaMalloc / cudaFree / allocating library call.
+ * Limit: n <= LSR_SORT_STATIC_MAX_N pairs; a larger n is rejected with LSR_ERR_CAPACITY and a message.
+ * Every call on a device shares the one array: calls that overlap on the GPU (two streams, two host threads) race —
+ * issue them on one stream, or order them with events.  Nothing needs clearing between calls (the library re-zeroes
+ * the counters it needs). */
+#define LSR_SORT_STATIC_MAX_N 1048576
+int lsr_sort_pairs_static(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                          int64_t n, int end_bit, void* stream);
+
 /* Tests / debugging: writes the sorted instance keys of the most recent lsr_forward issued from this thread, in the
  * reference's format (tile_id << 32 | float bits of depth; point_list_keys of rasterizer_impl.cu:181-194), into
  * keys_out[num_rendered].  The forward orders the Gaussians by depth first and then sorts instance words

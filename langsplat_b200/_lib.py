@@ -51,6 +51,7 @@ class Grads(Structure):
                                          "dL_dcov3D", "dL_dconic", "dL_dcolors_masked", "blend_acc")]
 
 
+SORT_STATIC_MAX_N = 1 << 20  # LSR_SORT_STATIC_MAX_N: pairs the allocation-free sort's static scratch holds
 ABI_VERSION = 3  # LSR_VERSION of include/lsr_api.h this module's structures mirror
 
 
@@ -126,6 +127,7 @@ EXPORTS = {
     "lsr_profile_stage_name": (c_char_p, [c_int]),
     "lsr_launch_count": (c_uint64, []),
     "lsr_last_error": (c_char_p, []),
+    "lsr_sort_pairs_static": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "lsr_version": (c_int, []),
     "lsr_blend_acc_supported": (c_int, []),
 }

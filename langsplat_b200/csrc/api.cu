@@ -470,6 +470,19 @@ int lsr_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* k
   return LSR_OK;
 }
 
+int lsr_sort_pairs_static(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                          int64_t n, int end_bit, void* stream) {
+  if (n < 0) return fail(LSR_ERR_INVALID, "n < 0");
+  if (n == 0) return LSR_OK;
+  if (n > (int64_t)LSR_SORT_STATIC_MAX_N)
+    return fail(LSR_ERR_CAPACITY, "lsr_sort_pairs_static: n = %lld exceeds LSR_SORT_STATIC_MAX_N = %d pairs (the size "
+                "of the library's static scratch); use lsr_sort_pairs with caller-provided buffers",
+                (long long)n, (int)LSR_SORT_STATIC_MAX_N);
+  if (!keys_in || !vals_in || !keys_out || !vals_out) return fail(LSR_ERR_INVALID, "null pointer");
+  LSR_CUDA(sort_pairs_static(keys_in, vals_in, keys_out, vals_out, n, end_bit, (cudaStream_t)stream));
+  return LSR_OK;
+}
+
 static int check_frame(const lsr_frame* f, const lsr_inputs* in) {
   if (!f || !in) return fail(LSR_ERR_INVALID, "null frame / inputs");
   if (f->P < 0 || f->width <= 0 || f->height <= 0) return fail(LSR_ERR_INVALID, "bad P / image size");

@@ -197,6 +197,9 @@ struct SortPlan {
 };
 SortPlan make_sort_plan(uint32_t lo_min, uint32_t lo_max, int hi_bits, int id_bits);
 SortPlan make_sort_plan_bits(int end_bit);
+// allocation-free pair sort on the library's static device scratch (radix_sort.cu), n <= LSR_SORT_STATIC_MAX_N
+cudaError_t sort_pairs_static(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                              int64_t n, int end_bit, cudaStream_t s);
 // packed plan whose compacted key is `key_bits` wide (digits from bits [id_bits, id_bits + key_bits) of the word)
 SortPlan make_sort_plan_packed(int key_bits, int id_bits);
 

@@ -21,7 +21,23 @@
 //    order preserving and the keys in memory stay the reference's exact values.
 // HBM-bound: algorithmic bytes per element 24 per pass (12 read + 12 written).
 #include <algorithm>
+#include <mutex>
 #include "common.cuh"
+
+// ---- scratch of the allocation-free entry point (lsr_sort_pairs_static, bottom of this file) ----
+// Work area (histograms, tickets, look-back words) + the two ping-pong buffers for at most LSR_SORT_STATIC_MAX_N pairs:
+// 14.8 MB that every GPU which loads the library holds until the process exits.  In HOST code this name is only a
+// stand-in for the symbol; the device address comes from cudaGetSymbolAddress (static_sort_scratch() below).
+constexpr int64_t kStaticSortMaxN = LSR_SORT_STATIC_MAX_N;
+constexpr size_t kStaticAlign = 256;
+constexpr size_t static_up(size_t v) { return (v + kStaticAlign - 1) / kStaticAlign * kStaticAlign; }
+constexpr size_t kStaticNBlocks = (size_t)((kStaticSortMaxN + lsr::SORT_TILE - 1) / lsr::SORT_TILE) + 1;
+constexpr size_t kStaticWorkBytes = static_up(lsr::SORT_MAX_PASSES * lsr::SORT_BINS * 4) + static_up(lsr::SORT_MAX_PASSES * 4) +
+                                    static_up((size_t)lsr::SORT_MAX_PASSES * kStaticNBlocks * lsr::SORT_BINS * 4) + 256;
+constexpr size_t kStaticKeysOfs = static_up(kStaticWorkBytes);
+constexpr size_t kStaticValsOfs = kStaticKeysOfs + static_up((size_t)kStaticSortMaxN * 8);
+constexpr size_t kStaticScratchBytes = kStaticValsOfs + static_up((size_t)kStaticSortMaxN * 4);
+static __device__ __align__(256) unsigned char g_static_sort_scratch[kStaticScratchBytes];
 
 namespace lsr {
 
@@ -551,6 +567,41 @@ int sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_
     vsrc = vdst;
   }
   return passes;
+}
+
+// Allocation-free variant of the pair sort: same kernels, but the work area and the ping-pong buffers live in
+// g_static_sort_scratch.  Every call shares that array (it keeps the last call's contents: sort_prepare re-zeroes the
+// histograms, tickets and look-back words of the passes that will run; the ping-pong buffers are fully overwritten
+// before they are read), so two calls that overlap on the GPU — different streams, or different host threads — race.
+static cudaError_t static_sort_scratch(unsigned char** ptr) {
+  // once per device, with that device current: the symbol has one address per device
+  static std::mutex mu;
+  static unsigned char* addr[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lock(mu);
+  if (addr[dev] == nullptr) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_static_sort_scratch);
+    if (e != cudaSuccess) return e;
+    addr[dev] = static_cast<unsigned char*>(p);
+  }
+  *ptr = addr[dev];
+  return cudaSuccess;
+}
+
+cudaError_t sort_pairs_static(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                              int64_t n, int end_bit, cudaStream_t s) {
+  if (n <= 0) return cudaSuccess;
+  if (n > kStaticSortMaxN || sort_work_bytes(n) > kStaticWorkBytes) return cudaErrorInvalidValue;  // (the caller checks n)
+  unsigned char* base = nullptr;
+  cudaError_t e = static_sort_scratch(&base);
+  if (e != cudaSuccess) return e;
+  sort_pairs(keys_in, vals_in, keys_out, vals_out, reinterpret_cast<uint64_t*>(base + kStaticKeysOfs),
+             reinterpret_cast<uint32_t*>(base + kStaticValsOfs), n, make_sort_plan_bits(end_bit), false, base, s);
+  return cudaGetLastError();
 }
 
 }  // namespace lsr
