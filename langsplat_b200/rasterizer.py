@@ -66,7 +66,8 @@ _capacity_retries = 0  # how often lsr_forward had to be repeated with a larger 
 # forward / backward on that device (or, waiting, by `check_async_status()`): an instance list that turned out too
 # small raises LsrError there, and that frame's images were NaN-filled on the device, so an incomplete render can
 # never pass for a result.  Same kernels, same results as the synchronous path.
-_USE_BLEND_ACC = os.environ.get("LSR_BLEND_ACC", "1") != "0"  # packed accumulation record in the backward (A/B switch)
+# packed accumulation record in the backward: 0 = never (A/B), 1 = when the per-Gaussian kernel follows, 2 = always
+_USE_BLEND_ACC = int(os.environ.get("LSR_BLEND_ACC", "1"))
 
 
 class _AsyncConfig:
@@ -426,7 +427,9 @@ def _backward_impl(state, grad_color, grad_feature, need_mask: int, want_sh: boo
     # vector reductions instead of twelve scalar atomics into five tensors); the kernel behind it writes the tensors.
     # No dL_dconic buffer then, and no dL_dcolors unless the caller gets it back (colors_precomp).  LSR_BLEND_ACC=0
     # keeps the five accumulators (A/B, and what the one-phase kernel of LSR_BWD_V1=1 needs).
-    use_acc = _USE_BLEND_ACC and bool(lib.lsr_blend_acc_supported())
+    # Only when the per-Gaussian kernel follows (it reads the record for free): a feature-only backward would pay an
+    # extra unpack pass for nothing (GPU call r2s, C3: blend kernel 484 us either way, + 10 us of unpack and zero-fill).
+    use_acc = (_USE_BLEND_ACC == 2 or (_USE_BLEND_ACC == 1 and run_pre)) and bool(lib.lsr_blend_acc_supported())
     need_colors = not use_acc or sh is None
     sizes = [("rots", 4 if run_pre else 0), ("sh", n_sh), ("means3D", 3 if run_pre else 0),
              ("scales", 3 if run_pre else 0), ("feat", 3), ("opac", 1), ("|", 0), ("acc", 16 if use_acc else 0),

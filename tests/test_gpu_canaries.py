@@ -172,3 +172,28 @@ def test_odd_gaussian_counts_keep_every_vector_access_aligned(guarded, P):
     run_module(R.GaussianRasterizer, R.GaussianRasterizationSettings, scene, cams[0], use_colors_precomp=cp,
                grads=(dcol, dfeat), requires=("means3D", "colors_precomp", "opacities", "scales", "rotations"))
     guarded.check()
+
+
+@pytest.mark.parametrize("mode", ["feature_only", "means2D_and_colors"])
+def test_accumulation_record_without_the_per_gaussian_kernel(guarded, monkeypatch, mode):
+    """lsr_grads::blend_acc when no per-Gaussian kernel follows the blend kernel (feature-only training, or only the
+    screen-space / precomputed-colour gradients wanted): unpack_acc_kernel writes the tensors.  Same numbers as the
+    five-accumulator path, up to the order of the float atomics."""
+    scene, cams = syn.make_config(3, P=30_011, W=360, H=270)
+    kw = {}
+    if mode == "feature_only":
+        grads, requires = (None, _grads(cams[0], 4, feature_only=True)[1]), ("language_feature",)
+    else:
+        grads, requires = _grads(cams[0], 4), ("colors_precomp", "language_feature")
+        kw["use_colors_precomp"] = torch.rand(30_011, 3, generator=torch.Generator().manual_seed(1))
+    out = {}
+    for setting in (0, 2, 0):
+        monkeypatch.setattr(R, "_USE_BLEND_ACC", setting)
+        out.setdefault(setting, []).append(run_module(R.GaussianRasterizer, R.GaussianRasterizationSettings, scene,
+                                                      cams[0], grads=grads, requires=requires, **kw)["grads"])
+    for k in requires + ("means2D",):
+        a, b, again = out[0][0][k], out[2][0][k], out[0][1][k]
+        assert b is not None and torch.isfinite(b).all()
+        noise = float((a - again).abs().max()) / max(float(a.abs().max()), 1e-30)
+        assert float((a - b).abs().max()) <= max(1e-5, 4.0 * noise) * float(a.abs().max()), k
+    guarded.check()
