@@ -762,7 +762,10 @@ def main():
                "duplicate": 12 * P + 12 * V + 8 * Rn,
                "sort": Rn * (16 * t_passes + 4) + 16 * T, "tile_ranges": 20 * T,
                "render_fwd": 52 * Rn + 32 * N,
-               "bwd_zero_fill": 56 * P, "render_bwd": 52 * Rn + 32 * N + 48 * V, "preprocess_bwd": 236 * P + 303 * V}
+               # backward with the packed accumulation record (lsr_grads::blend_acc): 64 B per Gaussian zero-filled,
+               # added to by the blend kernel (visible ones), read back by the per-Gaussian kernel, which also writes
+               # the three tensors the blend kernel used to accumulate into directly (opacity, feature, means2D)
+               "bwd_zero_fill": 64 * P, "render_bwd": 52 * Rn + 32 * N + 64 * V, "preprocess_bwd": 276 * P + 303 * V}
         ins = {"render_fwd": 20 * Kx + 15 * Kc, "render_bwd": 20 * Kx + 54 * Kc}
         table = {}
         for k, ms in stages.items():
