@@ -657,6 +657,134 @@ def main():
         e2e_mode = "CUDA graph replay (langsplat_b200.graphs.GraphedStep)"
         for st in sets:
             st.step.check()
+    # ---- several ranks: the step WITH its exchange replayed from CUDA graphs.  The exchange is then all peer-memory
+    # kernels (factors pulled by the SH-gradient kernel, two-shot all-reduce of the other 56 B/Gaussian, barriers that
+    # count their epochs on the device: PeerFactorExchange(device_epochs=True)); one graph per payload slot, replayed
+    # alternately.  Same kernels as the eager loop above, whose figures stay in value_eager / e2e.eager_value.
+    peer_g = None
+    if (args.impl == "ours" and async_fwd and world > 1 and factored and peer is not None and not fwd_only
+            and not args.no_graph):
+        peer_g = make_peer_exchange(P, len(my_views), dev, grad_floats_per_gaussian=14, device_epochs=True)
+    if peer_g is not None:
+        from langsplat_b200.graphs import GraphedStep
+        params = {k: v.detach().clone().requires_grad_(v.requires_grad) for k, v in params.items()}
+        means2D = torch.zeros((P, 3), device=dev, requires_grad=True)
+        trainable_t = [params[k] for k in trainable] + [means2D]
+        i_sh, n_sh_coeffs = trainable.index("shs"), params["shs"].shape[1]
+        torch.cuda.synchronize()
+
+        def exchange_step(run_views, slot):
+            """run_views() yields (outputs, grad_outputs, loss) per view of this rank."""
+            def fn():
+                acc, loss = None, None
+                with factored_sh_gradients(peer_g.begin_step(slot=slot)):
+                    for outs, gouts, view_loss in run_views():
+                        g = torch.autograd.grad(outs, trainable_t, gouts, allow_unused=True)
+                        if acc is None:
+                            acc = list(g)  # the first view's gradients sit in the exchange's staging area
+                        else:
+                            for a, b in zip(acc, g):
+                                if a is not None and b is not None:
+                                    a.add_(b)
+                        loss = view_loss if loss is None or view_loss is None else loss + view_loss
+                others = [a for j, a in enumerate(acc[:-1]) if j != i_sh]
+                sh_grad, reduced = peer_g.exchange(params["means3D"], n_sh_coeffs, others)
+                return loss, sh_grad, reduced, acc[-1]
+            return GraphedStep(fn, warmup=2, capture_error_mode="thread_local")
+
+        def value_views():
+            for r in rasts:
+                color, feat, radii = r(means3D=params["means3D"], means2D=means2D, shs=params["shs"],
+                                       language_feature_precomp=params["language_feature"],
+                                       opacities=params["opacities"], scales=params["scales"],
+                                       rotations=params["rotations"])
+                yield [color, feat], [dcol, dfeat], None
+
+        n0 = lib.lsr_launch_count()
+        g_val = [exchange_step(value_views, 0), exchange_step(value_views, 1)]
+        launches_per_step = (lib.lsr_launch_count() - n0) // 6  # per graph: two warm-up runs + the capture
+        for i in range(4):
+            g_val[i & 1].replay()
+        barrier(world)
+        ev0.record()
+        for i in range(args.steps):
+            g_val[i & 1].replay()
+        ev1.record()
+        barrier(world)
+        for g_ in g_val:
+            g_.check()
+        ms_total = max_over_ranks(ev0.elapsed_time(ev1), world, dev)
+        launches = launches_per_step * args.steps
+        value_mode = ("CUDA graph replay of the step with its exchange (GraphedStep; peer-memory exchange with "
+                      "device-side barrier epochs, one graph per payload slot)")
+        exchange = ("SH gradient as per-view 12-byte factors read from peer memory over NVLink inside the SH-gradient "
+                    "kernel, the other 56 B/Gaussian by a two-shot all-reduce kernel over peer memory; no NCCL on the "
+                    "data path (graph replay); value_eager: " + exchange)
+
+        if len(my_views) == 1:  # end to end: one view per rank and step, as in the eager loop
+            class ViewSetMR:
+                pass
+
+            sets = []
+            for slot in range(2):
+                st = ViewSetMR()
+                st.gt_c = torch.empty_like(gt_c_h, device=dev)
+                st.gt_f = torch.empty_like(gt_f_h, device=dev) if gt_f_h is not None else None
+                st.view, st.proj, st.cam = (torch.empty_like(view_h, device=dev), torch.empty_like(proj_h, device=dev),
+                                            torch.empty_like(cam_h, device=dev))
+                st.ready = None
+                for dst, src in ((st.gt_c, gt_c_h), (st.gt_f, gt_f_h), (st.view, view_h), (st.proj, proj_h),
+                                 (st.cam, cam_h)):
+                    if dst is not None:
+                        dst.copy_(src)
+                r_st = GR(raster_settings=rs._replace(viewmatrix=st.view, projmatrix=st.proj, campos=st.cam))
+
+                def e2e_views(st=st, r_st=r_st):
+                    color, feat, radii = r_st(means3D=params["means3D"], means2D=means2D, shs=params["shs"],
+                                              language_feature_precomp=params["language_feature"],
+                                              opacities=params["opacities"], scales=params["scales"],
+                                              rotations=params["rotations"])
+                    gt_c, gt_f = gt_images(st.gt_c, st.gt_f)
+                    loss = l1_loss(color, gt_c) + l1_loss(feat, gt_f)
+                    yield [loss], None, loss
+
+                st.step = exchange_step(e2e_views, slot)
+                sets.append(st)
+
+            def issue_set_copy_mr(st):
+                with torch.cuda.stream(copy_stream):
+                    for dst, src in ((st.gt_c, gt_c_h), (st.gt_f, gt_f_h), (st.view, view_h), (st.proj, proj_h),
+                                     (st.cam, cam_h)):
+                        if dst is not None:
+                            dst.copy_(src, non_blocking=True)
+                    st.ready = torch.cuda.Event()
+                    st.ready.record(copy_stream)
+
+            counter_mr = [0]
+
+            def e2e_step_graph_mr():
+                st = sets[counter_mr[0] & 1]
+                if st.ready is None:
+                    issue_set_copy_mr(st)
+                torch.cuda.current_stream(dev).wait_event(st.ready)
+                loss = st.step.replay()[0]
+                issue_set_copy_mr(sets[(counter_mr[0] + 1) & 1])
+                counter_mr[0] += 1
+                return float(loss.item())
+
+            for _ in range(4):
+                e2e_step_graph_mr()
+            barrier(world)
+            ev0.record()
+            for _ in range(args.steps):
+                e2e_step_graph_mr()
+            ev1.record()
+            barrier(world)
+            e2e_ms_total = max_over_ranks(ev0.elapsed_time(ev1), world, dev)
+            e2e_mode = value_mode
+            for st in sets:
+                st.step.check()
+        peer_g.check()
     clocks = sampler.stop() if rank == 0 else None
 
     # ---- per-stage device times (CUDA events inside liblsr.so, same stream), one profiled pass of K steps ----
@@ -680,6 +808,8 @@ def main():
     if peer is not None:
         peer.check()  # a barrier that timed out would have produced garbage gradients: fail the run
         peer.close()
+    if peer_g is not None:
+        peer_g.close()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()

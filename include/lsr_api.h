@@ -213,6 +213,10 @@ int lsr_sh_gradient_from_view_ptrs(int32_t P, int32_t M, int32_t D, int32_t n_vi
  *   lsr_peer_status (returns LSR_ERR_CUDA, "peer barrier timed out") instead of hanging the device.
  * lsr_peer_signal / lsr_peer_wait: the two halves of the barrier, for a rank that has local work to run between
  *   "my remote writes are done" and "everybody's are".
+ * lsr_peer_sync_auto: the same barrier (mode 3), signal (1) or wait (2) with the epoch counted on the device (in the
+ *   own header: a signal advances it, a wait uses the value its signal left) instead of passed by the host, so that
+ *   the launch is identical every step and a step with its exchange can be replayed from a CUDA graph.  Every rank
+ *   must issue the same sequence of calls; do not mix with the explicit-epoch calls on the same buffers.
  * lsr_peer_allreduce: two-shot sum over the ranks through peer memory.  in[r] / out[r] = rank r's input / output
  *   vector of n_floats floats (16-byte aligned, n_floats % 4 == 0) as mapped in this process.  This rank reduces its
  *   own 1/world chunk from all inputs (fixed rank order: every rank ends with the same bits) and stores it into every
@@ -228,6 +232,7 @@ int lsr_peer_free(void* ptr);
 int lsr_peer_barrier(int32_t rank, int32_t world, void* const* headers, uint32_t epoch, void* stream);
 int lsr_peer_signal(int32_t rank, int32_t world, void* const* headers, uint32_t epoch, void* stream);
 int lsr_peer_wait(int32_t rank, int32_t world, void* const* headers, uint32_t epoch, void* stream);
+int lsr_peer_sync_auto(int32_t rank, int32_t world, void* const* headers, int32_t mode, void* stream);
 int lsr_peer_allreduce(int32_t rank, int32_t world, const float* const* in, float* const* out, int64_t n_floats,
                        void* stream);
 int lsr_peer_status(const void* own_buffer, void* stream);

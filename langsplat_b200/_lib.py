@@ -98,6 +98,7 @@ EXPORTS = {
     "lsr_peer_barrier": (c_int, [c_int32, c_int32, POINTER(c_void_p), c_uint32, c_void_p]),
     "lsr_peer_signal": (c_int, [c_int32, c_int32, POINTER(c_void_p), c_uint32, c_void_p]),
     "lsr_peer_wait": (c_int, [c_int32, c_int32, POINTER(c_void_p), c_uint32, c_void_p]),
+    "lsr_peer_sync_auto": (c_int, [c_int32, c_int32, POINTER(c_void_p), c_int32, c_void_p]),
     "lsr_peer_allreduce": (c_int, [c_int32, c_int32, POINTER(c_void_p), POINTER(c_void_p), c_int64, c_void_p]),
     "lsr_peer_status": (c_int, [c_void_p, c_void_p]),
     "lsr_peer_set_timeout_ms": (c_int, [c_uint64]),

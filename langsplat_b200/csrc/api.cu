@@ -265,6 +265,11 @@ int lsr_peer_wait(int32_t rank, int32_t world, void* const* headers, uint32_t ep
   return peer_sync(rank, world, headers, epoch, 2, stream);
 }
 
+int lsr_peer_sync_auto(int32_t rank, int32_t world, void* const* headers, int32_t mode, void* stream) {
+  if (mode < 1 || mode > 3) return fail(LSR_ERR_INVALID, "mode must be 1 (signal), 2 (wait) or 3 (barrier)");
+  return peer_sync(rank, world, headers, 0u, mode | 4, stream);
+}
+
 int lsr_peer_allreduce(int32_t rank, int32_t world, const float* const* in, float* const* out, int64_t n_floats,
                        void* stream) {
   if (world < 1 || world > LSR_MAX_PEERS || rank < 0 || rank >= world || !in || !out)

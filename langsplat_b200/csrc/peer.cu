@@ -13,6 +13,7 @@ namespace {
 struct PeerHeader {
   uint32_t arrived[LSR_MAX_PEERS];  // arrived[r] = last epoch rank r signalled to the owner of this header
   uint32_t timed_out;               // set by the owner's barrier kernel when a peer did not show up in time
+  uint32_t auto_epoch;              // the owner's own barrier count when the epochs are kept on the device (mode bit 2)
 };
 static_assert(sizeof(PeerHeader) <= LSR_PEER_HEADER_BYTES, "header does not fit");
 
@@ -35,9 +36,20 @@ __device__ __forceinline__ uint64_t globaltimer_ns() {
 
 // mode bit 0: signal, bit 1: wait.  Splitting the two lets a rank publish "my remote writes are done", run local work
 // that does not depend on the peers, and only then wait for them.
+// mode bit 2: the epoch lives in the own header instead of the kernel's arguments — a signal advances it, a wait alone
+// uses the value its signal left — so that the launch is the same every step and can be replayed from a CUDA graph
+// (every rank runs the same sequence of barriers, so the counts agree without the host).
 __global__ void __launch_bounds__(32) peer_barrier_kernel(PeerHeaders hs, int rank, int world, uint32_t epoch,
                                                           int mode, uint64_t timeout_ns) {
   const int r = threadIdx.x;
+  if (mode & 4) {
+    uint32_t e = 0;
+    if (r == 0) {
+      e = hs.h[rank]->auto_epoch + ((mode & 1) ? 1u : 0u);
+      if (mode & 1) hs.h[rank]->auto_epoch = e;
+    }
+    epoch = __shfl_sync(0xffffffffu, e, 0);
+  }
   __threadfence_system();
   if (r < world && (mode & 1)) {
     uint32_t* theirs = &hs.h[r]->arrived[rank];

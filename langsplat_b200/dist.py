@@ -184,7 +184,12 @@ class PeerFactorExchange:
     between, which that peer enqueues after the kernel that read the slot, so no slot is overwritten while in use.
     Every rank must run the same number of views per step, on the same stream from step to step."""
 
-    def __init__(self, P: int, views_per_rank: int, device, group=None, grad_floats_per_gaussian: int = 0):
+    def __init__(self, P: int, views_per_rank: int, device, group=None, grad_floats_per_gaussian: int = 0,
+                 device_epochs: bool = False):
+        """device_epochs: the barriers count their epochs on the device (lsr_peer_sync_auto) instead of taking them
+        from this object, so that a step with its exchange can be captured in a CUDA graph and replayed; the payload
+        slot of a step is then chosen by the caller (`begin_step(slot=...)`: capture one graph per slot and replay
+        them alternately — a rank may be a step ahead of a peer that still reads the previous step's factors)."""
         from . import _lib as L
         from .rasterizer import LsrError
         self._L, self._lib, self._err = L, L.load(), LsrError
@@ -231,6 +236,7 @@ class PeerFactorExchange:
                                         device=self.device).view(2, slot_floats)
         self._headers = (ctypes.c_void_p * self.world)(*self.bases)
         self.epoch, self._count, self._degree, self._barriers = 0, 0, 0, 0
+        self._slot, self.device_epochs = 0, bool(device_epochs)
         self._side = torch.cuda.Stream(device=self.device)
         # the sticky timed-out word of the own header, mirrored into pinned host memory behind every exchange and
         # looked at (without synchronising) when the next step begins
@@ -246,7 +252,17 @@ class PeerFactorExchange:
             raise self._err(self._L.last_error())
 
     # -- sink protocol (rasterizer._backward_impl) --
-    def begin_step(self) -> "PeerFactorExchange":
+    def _sync(self, mode: int, stream) -> None:
+        """mode 1: signal, 2: wait (for the epoch of the last signal), 3: barrier."""
+        if self.device_epochs:
+            self._check(self._lib.lsr_peer_sync_auto(self.rank, self.world, self._headers, mode, stream))
+            return
+        if mode & 1:
+            self._barriers += 1
+        fn = {1: self._lib.lsr_peer_signal, 2: self._lib.lsr_peer_wait, 3: self._lib.lsr_peer_barrier}[mode]
+        self._check(fn(self.rank, self.world, self._headers, self._barriers & 0xFFFFFFFF, stream))
+
+    def begin_step(self, slot: Optional[int] = None) -> "PeerFactorExchange":
         """Starts a step: the next `views_per_rank` backward passes write into this step's slot.  Returns the sink.
         Raises if a barrier of an earlier step timed out (a peer did not arrive within the time-out, LSR_PEER_TIMEOUT_MS
         / lsr_peer_set_timeout_ms, default 120 s): that step's sums were overwritten with NaN, never returned as
@@ -256,12 +272,13 @@ class PeerFactorExchange:
                             "that step's gradients were poisoned with NaN")
         self.epoch += 1
         self._count = 0
+        self._slot = (self.epoch & 1) if slot is None else (int(slot) & 1)  # consecutive steps must alternate
         return self
 
     def new_factor(self, P: int, device, campos: torch.Tensor, degree: int) -> torch.Tensor:
         if P != self.P or self._count >= self.V:
             raise self._err(f"PeerFactorExchange: built for {self.V} view(s) of {self.P} Gaussians per step")
-        i, slot = self._count, self._payload[self.epoch & 1]
+        i, slot = self._count, self._payload[self._slot]
         self._count += 1
         self._degree = int(degree)
         slot[self.cam_off + 4 * i: self.cam_off + 4 * i + 3].copy_(campos.reshape(3), non_blocking=True)
@@ -274,7 +291,7 @@ class PeerFactorExchange:
         if self.world == 1 or self._count != 0 or n_floats > self.grad_cap:  # asked before the view's new_factor;
             # grad_cap is 0 unless the exchange was built with grad_floats_per_gaussian (the all-reduce option)
             return None
-        return self._payload[self.epoch & 1][self.in_off:self.in_off + n_floats]
+        return self._payload[self._slot][self.in_off:self.in_off + n_floats]
 
     def finish(self, means3D: torch.Tensor, n_coeffs: int) -> torch.Tensor:
         """dL_dsh [P, n_coeffs, 3] summed over the views of all ranks; call once per step, after the backward passes.
@@ -294,7 +311,7 @@ class PeerFactorExchange:
             raise self._err("PeerFactorExchange: no view ran a backward this step")
         L, P, V = self._L, self.P, self._count
         stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
-        parity = self.epoch & 1
+        parity = self._slot
         slot = self._payload[parity]
         off = L.PEER_HEADER_BYTES + parity * self.slot_bytes
         # ---- stage the other gradients (adjacent slices travel as one copy) ----
@@ -332,14 +349,13 @@ class PeerFactorExchange:
         out = torch.empty((P, n_coeffs, 3), dtype=torch.float32, device=self.device)
         m3 = means3D.detach().contiguous()
         with torch.cuda.device(self.device):
-            self._barriers += 1
-            self._check(self._lib.lsr_peer_barrier(self.rank, self.world, self._headers,
-                                                   self._barriers & 0xFFFFFFFF, stream))
+            self._sync(3, stream)
             sh_stream = stream
             if total:  # the SH-gradient kernel runs beside the all-reduce kernel, on a second stream
                 main = torch.cuda.current_stream(self.device)
                 self._side.wait_stream(main)
-                out.record_stream(self._side)
+                if not self.device_epochs:  # (under capture the join below already orders every later use)
+                    out.record_stream(self._side)
                 sh_stream = ctypes.c_void_p(self._side.cuda_stream)
             self._check(self._lib.lsr_sh_gradient_from_view_ptrs(P, n_coeffs, self._degree, n,
                                                                  ctypes.c_void_p(m3.data_ptr()), g_ptrs, c_ptrs,
@@ -348,12 +364,9 @@ class PeerFactorExchange:
                 ins = (ctypes.c_void_p * self.world)(*[b + off + self.in_off * 4 for b in self.bases])
                 outs = (ctypes.c_void_p * self.world)(*[b + off + self.out_off * 4 for b in self.bases])
                 self._check(self._lib.lsr_peer_allreduce(self.rank, self.world, ins, outs, total, stream))
-                self._barriers += 1
-                self._check(self._lib.lsr_peer_signal(self.rank, self.world, self._headers,
-                                                      self._barriers & 0xFFFFFFFF, stream))
+                self._sync(1, stream)
                 main.wait_stream(self._side)
-                self._check(self._lib.lsr_peer_wait(self.rank, self.world, self._headers,
-                                                    self._barriers & 0xFFFFFFFF, stream))
+                self._sync(2, stream)
             # a barrier that gave up leaves incomplete sums behind: never let them pass for gradients
             own = ctypes.c_void_p(self.own)
             self._check(self._lib.lsr_peer_poison_on_timeout(own, ctypes.c_void_p(out.data_ptr()), out.numel(),
@@ -395,13 +408,13 @@ class PeerFactorExchange:
         self.own = None
 
 
-def make_peer_exchange(P: int, views_per_rank: int, device, group=None,
-                       grad_floats_per_gaussian: int = 0) -> Optional[PeerFactorExchange]:
+def make_peer_exchange(P: int, views_per_rank: int, device, group=None, grad_floats_per_gaussian: int = 0,
+                       device_epochs: bool = False) -> Optional[PeerFactorExchange]:
     """PeerFactorExchange if every rank could map every other rank's buffer, else None on all ranks (no NVLink /
     IPC between the processes): the caller then uses the all-gather path (`finish_sh_gradients`)."""
     ex, ok = None, 1
     try:
-        ex = PeerFactorExchange(P, views_per_rank, device, group, grad_floats_per_gaussian)
+        ex = PeerFactorExchange(P, views_per_rank, device, group, grad_floats_per_gaussian, device_epochs)
     except Exception as e:  # noqa: BLE001 — whatever failed, the decision must be collective
         ok, ex = 0, None
         print(f"[langsplat_b200.dist] peer exchange unavailable on this rank: {e}", file=sys.stderr)

@@ -32,7 +32,9 @@ class GraphedStep:
     """
 
     def __init__(self, fn: Callable[[], Any], warmup: int = 3, capacity_margin: Optional[float] = None,
-                 pool=None):
+                 pool=None, capture_error_mode: str = "global"):
+        """capture_error_mode: torch.cuda.graph's; "thread_local" when other threads of the process may call CUDA
+        while this one captures (torch.distributed's NCCL watchdog polls its events)."""
         if not torch.cuda.is_available():
             raise R.LsrError("GraphedStep needs a CUDA device (langsplat_b200 has no CPU path)")
         with R.async_forward(True, capacity_margin):
@@ -46,7 +48,7 @@ class GraphedStep:
             R.check_async_status()
             before = {k: len(v) for k, v in R._pending.items()}
             self.graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(self.graph, pool=pool):
+            with torch.cuda.graph(self.graph, pool=pool, capture_error_mode=capture_error_mode):
                 self.outputs = fn()
         # the forwards recorded by the capture: their status words are refreshed by every replay (same buffers), but
         # the stamp protocol cannot tell replays apart, so they leave the pending list and are read by check()

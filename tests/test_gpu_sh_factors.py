@@ -235,3 +235,48 @@ def test_peer_allreduce_two_ranks_in_one_process():
     bad = _ptr_array([ins[0].data_ptr() + 4, ins[1].data_ptr()])
     assert lib.lsr_peer_allreduce(0, 2, bad, op, n, stream) != L.LSR_OK and "aligned" in L.last_error()
     assert lib.lsr_peer_allreduce(0, 1, ip, op, 0, stream) == L.LSR_OK  # nothing to do
+
+
+def test_exchange_with_device_epochs_replays_from_cuda_graphs():
+    """PeerFactorExchange(device_epochs=True): the barriers count their epochs on the device, the payload slot is
+    chosen by the caller, so forward + backward + exchange of a step is captured once per slot and replayed — here with
+    one rank (the barrier signals and waits on itself; the multi-rank case runs in bench.py --gpus N)."""
+    from langsplat_b200.graphs import GraphedStep
+    dev = torch.device("cuda:0")
+    P = 8001
+    scene, cams = syn.make_config(4, P=P, W=160, H=120, n_cameras=2)
+    listed = _step(scene, cams, dev, 3, factored=True)
+    others = tuple(k for k in NAMES if k != "shs")
+    ex = D.PeerFactorExchange(P, 2, dev, device_epochs=True)
+    try:
+        params = {k: scene[k].to(dev).requires_grad_(True) for k in NAMES}
+        means2D = torch.zeros_like(params["means3D"], requires_grad=True)
+        grads_in = [[t.to(dev) for t in syn.make_grads(c.image_width, c.image_height, 300 + i)]
+                    for i, c in enumerate(cams)]
+        rasts = [R.GaussianRasterizer(settings_for(c, dev, sh_degree=3)) for c in cams]
+
+        def make(slot):
+            def fn():
+                acc = None
+                with D.factored_sh_gradients(ex.begin_step(slot=slot)):
+                    for rast, (dcol, dfeat) in zip(rasts, grads_in):
+                        color, feat, radii = rast(means3D=params["means3D"], means2D=means2D, shs=params["shs"],
+                                                  language_feature_precomp=params["language_feature"],
+                                                  opacities=params["opacities"], scales=params["scales"],
+                                                  rotations=params["rotations"])
+                        g = torch.autograd.grad([color, feat], [params[k] for k in others], [dcol, dfeat])
+                        acc = list(g) if acc is None else [a + b for a, b in zip(acc, g)]
+                sh, _ = ex.exchange(params["means3D"], 16, [])
+                return sh, acc
+            return fn
+
+        steps = [GraphedStep(make(0)), GraphedStep(make(1))]
+        for i in (0, 1, 0, 1, 1):
+            sh, acc = steps[i].replay()
+            steps[i].check()
+            assert rel_err(sh.cpu(), listed["shs"]) <= 1e-5
+            for k, g in zip(others, acc):
+                assert rel_err(g.cpu(), listed[k]) <= 1e-4, k
+        ex.check()
+    finally:
+        ex.close()
