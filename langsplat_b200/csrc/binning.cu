@@ -286,7 +286,7 @@ duplicate_kernel(int P, int gx, int gy, const uint32_t* __restrict__ perm, const
 // ahead to prefetch the (index, radius, centre) gathers: 112 / 1 214 us — a block that is ticketed but idle holds up
 // the look-back of every block behind it.
 // ------------------------------------------------------------------------------------------------------------
-constexpr int DUP_CHUNK = 2048;  // staged words per chunk (16 KB)
+constexpr int DUP_CHUNK = 8 * DUP_BLOCK;  // staged words per chunk (16 KB)
 constexpr uint32_t DUP_BIG = 512;
 
 __global__ void __launch_bounds__(DUP_BLOCK)
@@ -603,7 +603,8 @@ void launch_dup_scan(int P, int grid_x, int grid_y, const uint32_t* perm, const 
                      uint32_t* ghist, cudaStream_t s) {
   if (P <= 0) return;
   const int nblocks = (P + DUP_BLOCK - 1) / DUP_BLOCK;
-  const int grid = nblocks < 148 * 6 ? nblocks : 148 * 6;  // persistent CTAs (29 KB of shared memory each)
+  const int per_sm = 6 * 256 / DUP_BLOCK;
+  const int grid = nblocks < 148 * per_sm ? nblocks : 148 * per_sm;  // persistent CTAs (29 KB of shared memory each)
   dup_scan_kernel<<<grid, DUP_BLOCK, 0, s>>>(P, grid_x, grid_y, perm, radii, g.rec, g.offsets, words,
                                                (uint32_t)capacity, plan.id_bits, plan.passes, status, ctrl, ghist);
   count_launch();

@@ -109,7 +109,10 @@ inline size_t image_bytes(int W, int H) {
 constexpr int SORT_RADIX_BITS = 8;
 constexpr int SORT_BINS = 1 << SORT_RADIX_BITS;
 constexpr int SORT_THREADS = 256;
-constexpr int SORT_ITEMS = 16;
+#ifndef LSR_SORT_ITEMS
+#define LSR_SORT_ITEMS 16
+#endif
+constexpr int SORT_ITEMS = LSR_SORT_ITEMS;
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // keys per CTA per pass
 inline int sort_items_for(int64_t) { return SORT_ITEMS; }  // keys per thread (the kernel is templated on it)
 constexpr int SORT_MAX_PASSES = 8;
@@ -141,7 +144,10 @@ constexpr int SCAN_ITEMS = 8;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 inline size_t scan_nblocks(int P) { return (size_t)((P + SCAN_TILE - 1) / SCAN_TILE) + 1; }
 
-constexpr int DUP_BLOCK = 256;  // Gaussians per block of the duplication kernel (binning.cu)
+#ifndef LSR_DUP_BLOCK
+#define LSR_DUP_BLOCK 256
+#endif
+constexpr int DUP_BLOCK = LSR_DUP_BLOCK;  // Gaussians per block of the duplication kernel (binning.cu)
 inline size_t dup_nblocks(int P) { return (size_t)((P + DUP_BLOCK - 1) / DUP_BLOCK) + 1; }
 
 struct ScratchView {
