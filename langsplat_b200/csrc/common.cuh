@@ -110,7 +110,7 @@ constexpr int SORT_RADIX_BITS = 8;
 constexpr int SORT_BINS = 1 << SORT_RADIX_BITS;
 constexpr int SORT_THREADS = 256;
 #ifndef LSR_SORT_ITEMS
-#define LSR_SORT_ITEMS 16
+#define LSR_SORT_ITEMS 16  // GPU call r2y, C2 sort stage: 12 -> 136 us, 16 -> 132, 20 -> 159, 24 -> 174 (occupancy falls)
 #endif
 constexpr int SORT_ITEMS = LSR_SORT_ITEMS;
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // keys per CTA per pass
@@ -145,7 +145,7 @@ constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 inline size_t scan_nblocks(int P) { return (size_t)((P + SCAN_TILE - 1) / SCAN_TILE) + 1; }
 
 #ifndef LSR_DUP_BLOCK
-#define LSR_DUP_BLOCK 256
+#define LSR_DUP_BLOCK 256  // 128 (twice the resident blocks) measured slower: 107 against 87 us at C2, 652 against 501 at C5 (r2y)
 #endif
 constexpr int DUP_BLOCK = LSR_DUP_BLOCK;  // Gaussians per block of the duplication kernel (binning.cu)
 inline size_t dup_nblocks(int P) { return (size_t)((P + DUP_BLOCK - 1) / DUP_BLOCK) + 1; }
