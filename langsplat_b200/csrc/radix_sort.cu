@@ -166,6 +166,9 @@ __device__ __forceinline__ uint32_t sw(uint32_t p) { return p ^ ((p >> 4) & 15u)
 #ifndef LSR_SORT_MINB
 #define LSR_SORT_MINB 4  // CTAs per SM the register allocation aims at (4: 64 registers with ~100 B of spills)
 #endif
+#ifndef LSR_SORT_RANK2
+#define LSR_SORT_RANK2 0
+#endif
 #ifndef LSR_DEPTH_NB
 #define LSR_DEPTH_NB 8  // ranking of the depth-ordering passes: eight ballots (0 = MATCH.ANY: 77 vs 65 us for the
                        // three passes at C2, GPU call r2d: the low digits of a depth word mostly differ within a warp)
@@ -247,6 +250,31 @@ onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, c
   uint16_t rank[ITEMS];
   uint32_t* wh = s_whist + warp * BINS;
   const uint32_t lt = (1u << lane) - 1;
+#if LSR_SORT_RANK2
+  // Two loops: the ballots of all items first (independent of one another, so they pipeline), then the running counts,
+  // where only the lowest lane of a group of equal digits touches shared memory (load, add, store) and the others
+  // receive its old value by shuffle — the chain from one item to the next is that lane's LDS -> STS, not
+  // ballots -> LDS (all lanes) -> barrier -> STS -> barrier.
+  uint32_t peers_of[ITEMS];
+#pragma unroll
+  for (int i = 0; i < ITEMS; i++) {
+    const uint32_t d = (dig[i >> 2] >> (8 * (i & 3))) & 0xffu;
+    peers_of[i] = NB == 0 ? __match_any_sync(0xffffffffu, d) : (full ? match_digit<NB>(d) : match_digit<BITS>(d));
+  }
+#pragma unroll
+  for (int i = 0; i < ITEMS; i++) {
+    const uint32_t d = (dig[i >> 2] >> (8 * (i & 3))) & 0xffu;
+    const uint32_t peers = peers_of[i], lower = peers & lt;
+    uint32_t prev = 0;
+    if (lower == 0) {
+      prev = wh[d];
+      wh[d] = prev + __popc(peers);
+    }
+    __syncwarp();  // the store above is visible to whichever lane leads this digit's group in the next item
+    prev = __shfl_sync(0xffffffffu, prev, __ffs(peers) - 1);
+    rank[i] = (uint16_t)(prev + __popc(lower));
+  }
+#else
 #pragma unroll
   for (int i = 0; i < ITEMS; i++) {
     const uint32_t d = (dig[i >> 2] >> (8 * (i & 3))) & 0xffu;
@@ -259,6 +287,7 @@ onesweep_kernel(const uint64_t* __restrict__ kin, uint64_t* __restrict__ kout, c
     rank[i] = (uint16_t)(prev + __popc(lower));
     __syncwarp();
   }
+#endif
   __syncthreads();
 
   // ---- per bin (thread t == bin t): exclusive scan over warps, CTA bin scan, decoupled look-back ----
