@@ -167,6 +167,10 @@ __device__ __forceinline__ uint32_t sw(uint32_t p) { return p ^ ((p >> 4) & 15u)
 #define LSR_SORT_MINB 4  // CTAs per SM the register allocation aims at (4: 64 registers with ~100 B of spills)
 #endif
 #ifndef LSR_SORT_RANK2
+// 1: ranking as two loops (all ballots first; then only the lowest lane of a group of equal digits does the
+// shared-memory read-modify-write and the others take its old value by shuffle).  Fewer shared-memory accesses and a
+// shorter chain on paper, slower on the GPU (call r2aa, C2: instance sort 132 -> 147 us, depth ordering 67 -> 75 us;
+// with 80 registers 143 / 71): the divergent leader branch and the extra shuffle cost more than the all-lane LDS.
 #define LSR_SORT_RANK2 0
 #endif
 #ifndef LSR_DEPTH_NB

@@ -9,6 +9,7 @@ ops, samp = collections.Counter(), collections.Counter()
 tot = 0
 body = []
 for r in rows[2:]:
+    if r and r[0] == "Kernel Name": break  # (some exports list the kernel a second time: first section only)
     if len(r) <= smp: continue
     try: n, s = int(r[ii]), int(r[smp])
     except ValueError: continue
