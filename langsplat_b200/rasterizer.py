@@ -405,6 +405,31 @@ class ShFactorList(list):
         return t
 
 
+def _grad_layout(P: int, n_sh: int, run_pre: bool, use_acc: bool, need_colors: bool, external_params: bool):
+    """Offsets (in floats) of the backward's buffers inside ONE allocation: {name: (in the caller's parameter block?,
+    offset, length)}, the floats to allocate, the floats of the parameter block.
+    The parameter gradients come first and back to back (rotations, sh, means3D, scales, language feature, opacity — the
+    two that the kernels access as float4 lead, so they stay 16-byte aligned for any P), so that a data-parallel
+    caller can all-reduce them as ONE flat message (langsplat_b200.dist.coalesce); with `external_params` that block
+    lives in memory the caller provides.  The internal buffers follow from the next 64-byte boundary, widest access
+    first: the accumulation record (64-byte vector reductions), dL_dconic (float4), dL_dcov3D (float2), then the
+    triplets.  tests/test_layout.py checks the alignment of every vector access for odd P."""
+    sizes = [("rots", 4 if run_pre else 0), ("sh", n_sh), ("means3D", 3 if run_pre else 0),
+             ("scales", 3 if run_pre else 0), ("feat", 3), ("opac", 1), ("|", 0), ("acc", 16 if use_acc else 0),
+             ("conic", 0 if use_acc else 4), ("cov3D", 6 if run_pre else 0), ("means2D", 3),
+             ("colors", 3 if need_colors else 0)]
+    places, off, in_lead = {}, 0, external_params
+    n_params = sum(n for _, n in sizes[:sizes.index(("|", 0))]) * P
+    for name, n in sizes:
+        if name == "|":
+            off = 0 if external_params else (off + 15) // 16 * 16  # (torch allocations start 512-byte aligned)
+            in_lead = False
+            continue
+        places[name] = (in_lead, off, n * P)
+        off += n * P
+    return places, off + 16, n_params
+
+
 def _backward_impl(state, grad_color, grad_feature, need_mask: int, want_sh: bool, sh_factor_out=None):
     lib = L.load()
     _resolve(state, block=False)  # asynchronous forward: raises if its instance list is known to have overflowed
@@ -416,11 +441,8 @@ def _backward_impl(state, grad_color, grad_feature, need_mask: int, want_sh: boo
     gf = grad_feature.contiguous() if (grad_feature is not None and include_feature) else None
     geom_need = bool(need_mask & L.NEED_GEOMETRY)
     run_pre = geom_need or (sh is not None and want_sh and gc is not None)
-    # One allocation for everything.  The parameter gradients come first and back to back (rotations, sh, means3D,
-    # scales, language feature, opacity — the two the kernels access as float4 lead, so they stay 16-byte aligned
-    # for any P), so a data-parallel caller can all-reduce them as ONE flat message (langsplat_b200.dist.coalesce);
-    # the internal accumulators (conic, means2D, colours, cov3D) follow from the next 16-byte boundary.  The library
-    # zero-fills what the blend kernel accumulates into (adjacent ranges merge into one memset).
+    # One allocation for everything (_grad_layout).  The library zero-fills what the blend kernel accumulates into
+    # (adjacent ranges merge into one memset).
     factored = sh_factor_out is not None and run_pre and sh is not None and gc is not None
     n_sh = M * 3 if (run_pre and sh is not None and not factored) else 0
     # The blend kernel accumulates into ONE packed 64-byte record per Gaussian ("acc", lsr_grads::blend_acc: 16-byte
@@ -431,28 +453,15 @@ def _backward_impl(state, grad_color, grad_feature, need_mask: int, want_sh: boo
     # extra unpack pass for nothing (GPU call r2s, C3: blend kernel 484 us either way, + 10 us of unpack and zero-fill).
     use_acc = (_USE_BLEND_ACC == 2 or (_USE_BLEND_ACC == 1 and run_pre)) and bool(lib.lsr_blend_acc_supported())
     need_colors = not use_acc or sh is None
-    sizes = [("rots", 4 if run_pre else 0), ("sh", n_sh), ("means3D", 3 if run_pre else 0),
-             ("scales", 3 if run_pre else 0), ("feat", 3), ("opac", 1), ("|", 0), ("acc", 16 if use_acc else 0),
-             ("conic", 0 if use_acc else 4), ("cov3D", 6 if run_pre else 0), ("means2D", 3),
-             ("colors", 3 if need_colors else 0)]  # (cov3D is written as float2: it follows the 16-byte-aligned parts)
     # A sink may provide the memory of the parameter gradients (PeerFactorExchange: peer-visible staging memory, so
     # that the all-reduce reads them in place); the internal accumulators then come from their own allocation.
-    n_params = sum(n for _, n in sizes[:sizes.index(("|", 0))]) * P
+    n_params = _grad_layout(P, n_sh, run_pre, use_acc, need_colors, False)[2]
     lead = sh_factor_out.new_flat(n_params, device) if factored and hasattr(sh_factor_out, "new_flat") else None
-    if lead is None:
-        flat = torch.empty((sum(n for _, n in sizes) * P + 16,), **f32)
-    else:
-        flat = torch.empty((sum(n for _, n in sizes) * P + 16 - n_params,), **f32)
-    part, off, buf = {}, 0, (flat if lead is None else lead)
-    for name, n in sizes:
-        if name == "|":
-            if lead is None:
-                off = (off + 15) // 16 * 16  # the record needs 64-byte alignment (allocations start 512-byte aligned)
-            else:
-                buf, off = flat, 0
-            continue
-        part[name] = buf[off:off + n * P] if n else None
-        off += n * P
+    places, total, _ = _grad_layout(P, n_sh, run_pre, use_acc, need_colors, lead is not None)
+    flat = torch.empty((total,), **f32)
+    part = {}
+    for name, (in_lead, off, n) in places.items():
+        part[name] = (lead if in_lead else flat)[off:off + n] if n else None
     d_conic = part["conic"].view(P, 4) if part["conic"] is not None else None
     d_means2D = part["means2D"].view(P, 3)
     d_opac = part["opac"].view(P, 1)

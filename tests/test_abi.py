@@ -82,6 +82,30 @@ def test_argument_validation_happens_before_any_cuda_call():
     assert lib.lsr_sort_pairs(None, None, None, None, None, None, 10, 45, None, 0, None) == L.LSR_ERR_INVALID
     assert lib.lsr_sort_pairs(None, None, None, None, None, None, 0, 45, None, 0, None) == L.LSR_OK
     assert lib.lsr_profile_stage_name(0).decode() == "preprocess_fwd"
+    # the peer barrier with device-side epochs: mode and rank / world are checked on the host
+    hdrs = (ctypes.c_void_p * 2)(256, 512)  # never dereferenced
+    assert lib.lsr_peer_sync_auto(0, 2, hdrs, 0, None) == L.LSR_ERR_INVALID and "mode" in L.last_error()
+    assert lib.lsr_peer_sync_auto(0, 2, hdrs, 4, None) == L.LSR_ERR_INVALID
+    assert lib.lsr_peer_sync_auto(2, 2, hdrs, 3, None) == L.LSR_ERR_INVALID and "rank" in L.last_error()
+    assert lib.lsr_peer_sync_auto(0, L.MAX_PEERS + 1, hdrs, 3, None) == L.LSR_ERR_INVALID
+    # the backward's alignment contract (lsr_grads): checked before anything is launched
+    g = L.Grads()
+    f.P, f.width, f.height = 8, 16, 16
+    one = 4096
+    f.bg = f.viewmatrix = f.projmatrix = f.campos = one
+    i.means3D = i.opacities = i.shs = i.scales = i.rotations = one
+    f.M, f.D = 16, 3
+    g.dL_dmeans2D = g.dL_dopacity = g.dL_dconic = g.dL_dcolors = g.dL_dlanguage_feature = one
+    g.dL_dcov3D = one + 4
+    rc = lib.lsr_backward(ctypes.byref(f), ctypes.byref(i), ctypes.c_void_p(one), ctypes.c_void_p(one),
+                          ctypes.c_void_p(one), ctypes.c_void_p(one), ctypes.c_void_p(one), None, L.NEED_ALL,
+                          ctypes.byref(g), None)
+    assert rc == L.LSR_ERR_INVALID and "dL_dcov3D must be 8-byte aligned" in L.last_error()
+    g.dL_dcov3D, g.dL_drotations = one, one + 8
+    rc = lib.lsr_backward(ctypes.byref(f), ctypes.byref(i), ctypes.c_void_p(one), ctypes.c_void_p(one),
+                          ctypes.c_void_p(one), ctypes.c_void_p(one), ctypes.c_void_p(one), None, L.NEED_ALL,
+                          ctypes.byref(g), None)
+    assert rc == L.LSR_ERR_INVALID and "16-byte aligned" in L.last_error()
 
 
 def test_missing_library_fails_loudly(monkeypatch, tmp_path):
