@@ -1,7 +1,8 @@
 """Fused L1 loss: the oracle against golden vectors produced by the reference's own `l1_loss`
 (tests/golden/make_golden_loss.py), and — on the GPU — the CUDA kernels (public `l1_loss` -> C ABI) against the
 oracle, the golden vectors and PyTorch's own op sequence at full image size.
-Tolerances: the loss is a mean of |.| terms summed in a different order -> 1e-6 relative; the gradient is an exact
+Tolerances: the loss is a mean of |.| terms summed in a different order -> 1e-6 relative on the small cases, 4e-6 at
+full image size (the per-CTA partial sums are added by float atomics in completion order); the gradient is an exact
 product of the sign, the mask and a scalar -> bit-exact up to the rounding of grad_out/numel (1 ulp)."""
 import os
 
@@ -70,7 +71,7 @@ def test_cuda_l1_loss_full_size_vs_torch(shape, masked):
     x.grad = None
     ref = torch.abs(x * mask - gt * mask).mean() if masked else torch.abs(x - gt).mean()
     ref.backward()
-    assert abs(ours.item() - ref.item()) <= 2e-6 * abs(ref.item())
+    assert abs(ours.item() - ref.item()) <= 4e-6 * abs(ref.item())  # 6.2 M terms, per-CTA partials added by float atomics
     np.testing.assert_allclose(g_ours.cpu().numpy(), x.grad.cpu().numpy(), rtol=2e-7, atol=0)
 
 
@@ -107,7 +108,7 @@ def test_cuda_l1_loss_takes_the_bool_mask_train_py_passes():
     x.grad = None
     ref = torch.abs(x * mask - gt * mask).mean()
     ref.backward()
-    assert abs(ours.item() - ref.item()) <= 2e-6 * abs(ref.item())
+    assert abs(ours.item() - ref.item()) <= 4e-6 * abs(ref.item())  # 6.2 M terms, per-CTA partials added by float atomics
     np.testing.assert_allclose(g_ours.cpu().numpy(), x.grad.cpu().numpy(), rtol=2e-7, atol=0)
     assert abs(l1_loss(x, gt, mask.to(torch.uint8)).item() - ref.item()) <= 2e-6 * abs(ref.item())
 
@@ -156,10 +157,12 @@ def test_cuda_l1_loss_uint8_ground_truth(shape, masked, offset):
     x.grad = None
     b = l1_loss(x, gt_f, mask)
     b.backward()
-    assert abs(a.item() - b.item()) <= 1e-6 * abs(b.item())
+    # same per-element values; the per-CTA partial sums meet in one float atomicAdd in whatever order the CTAs finish
+    # (24 k of them at 1080p): two runs of the SAME kernel already differ by ~1e-6 relative
+    assert abs(a.item() - b.item()) <= 4e-6 * abs(b.item())
     assert torch.equal(ga, x.grad)
     m = mask.float() if masked else torch.ones((), device=dev)
     ref = torch.abs(x.detach() * m - gt_f * m).mean()
-    assert abs(a.item() - ref.item()) <= 2e-6 * abs(ref.item())
+    assert abs(a.item() - ref.item()) <= 4e-6 * abs(ref.item())
     with pytest.raises(Exception):
         l1_loss(x, gt_u8.cpu(), mask)
