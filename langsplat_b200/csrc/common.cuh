@@ -17,6 +17,9 @@ constexpr int TILE_PIX = TILE_X * TILE_Y;
 #ifndef LSR_TILE_ORDER
 #define LSR_TILE_ORDER 1  // blend kernels take the tiles heaviest first (shorter tail of the last wave)
 #endif
+#ifndef LSR_FWD_WEIGHT
+#define LSR_FWD_WEIGHT 0  // forward blend: one weight alpha * T per pair instead of the reference's per-channel order (A/B)
+#endif
 #ifndef LSR_FWD_PK
 #define LSR_FWD_PK 1  // forward blend: both pixels of a thread through packed fp32 (FFMA2) instructions
 #endif

@@ -128,6 +128,22 @@ render_fwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
           lim[s] = kDone;  // done (forward.cu:353-357)
           continue;
         }
+#if LSR_FWD_WEIGHT
+        // One blend weight per pair, w = alpha * T, instead of (channel * alpha) * T per channel (forward.cu:361-366):
+        // 7 instead of 12 instructions for the six channels.  Each term then differs from the reference's by at most
+        // one rounding (6e-8 relative): far inside the images' 1e-5 bar; alpha, T and every decision are untouched.
+        const float w = __fmul_rn(alpha, T[s]);
+        if (COLOR) {
+          C[s][0] = __fmaf_rn(w, c.x, C[s][0]);
+          C[s][1] = __fmaf_rn(w, c.y, C[s][1]);
+          C[s][2] = __fmaf_rn(w, c.z, C[s][2]);
+        }
+        if (FEAT) {
+          F[s][0] = __fmaf_rn(w, c.w, F[s][0]);
+          F[s][1] = __fmaf_rn(w, d.x, F[s][1]);
+          F[s][2] = __fmaf_rn(w, d.y, F[s][2]);
+        }
+#else
         if (COLOR) {
           C[s][0] = __fmaf_rn(T[s], __fmul_rn(c.x, alpha), C[s][0]);
           C[s][1] = __fmaf_rn(T[s], __fmul_rn(c.y, alpha), C[s][1]);
@@ -138,6 +154,7 @@ render_fwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
           F[s][1] = __fmaf_rn(T[s], __fmul_rn(d.x, alpha), F[s][1]);
           F[s][2] = __fmaf_rn(T[s], __fmul_rn(d.y, alpha), F[s][2]);
         }
+#endif
         T[s] = test_T;
         last_contributor[s] = __float_as_uint(pos_bits) + 1u;  // 1-based position in the tile's list (forward.cu:372)
       }
