@@ -22,7 +22,8 @@ constexpr int FWD_SLOTS = BLEND_SLOTS;
 
 // COLOR = false: feature-only re-blend of a frame whose geometry is already binned (lsr_forward_feature_level): the
 // same walk and the same decisions, but no RGB accumulation and no colour / final_T / n_contrib stores.
-template <bool FEAT, bool COLOR>
+// WEIGHT: one blend weight alpha * T per pair (opt-in, see fast_blend() below); false = the reference's rounding order
+template <bool FEAT, bool COLOR, bool WEIGHT>
 __global__ void __launch_bounds__(32)
 render_fwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, const uint32_t* __restrict__ order,
                   const uint32_t* __restrict__ list,
@@ -128,33 +129,33 @@ render_fwd_kernel(int W, int H, int tiles_x, const uint2* __restrict__ ranges, c
           lim[s] = kDone;  // done (forward.cu:353-357)
           continue;
         }
-#if LSR_FWD_WEIGHT
-        // One blend weight per pair, w = alpha * T, instead of (channel * alpha) * T per channel (forward.cu:361-366):
-        // 7 instead of 12 instructions for the six channels.  Each term then differs from the reference's by at most
-        // one rounding (6e-8 relative): far inside the images' 1e-5 bar; alpha, T and every decision are untouched.
-        const float w = __fmul_rn(alpha, T[s]);
-        if (COLOR) {
-          C[s][0] = __fmaf_rn(w, c.x, C[s][0]);
-          C[s][1] = __fmaf_rn(w, c.y, C[s][1]);
-          C[s][2] = __fmaf_rn(w, c.z, C[s][2]);
+        if (WEIGHT) {
+          // One blend weight per pair, w = alpha * T, instead of (channel * alpha) * T per channel
+          // (forward.cu:361-366): 7 instead of 12 instructions for the six channels.  Each term then differs from the
+          // reference's by at most one rounding; alpha, T and every decision are untouched.
+          const float w = __fmul_rn(alpha, T[s]);
+          if (COLOR) {
+            C[s][0] = __fmaf_rn(w, c.x, C[s][0]);
+            C[s][1] = __fmaf_rn(w, c.y, C[s][1]);
+            C[s][2] = __fmaf_rn(w, c.z, C[s][2]);
+          }
+          if (FEAT) {
+            F[s][0] = __fmaf_rn(w, c.w, F[s][0]);
+            F[s][1] = __fmaf_rn(w, d.x, F[s][1]);
+            F[s][2] = __fmaf_rn(w, d.y, F[s][2]);
+          }
+        } else {
+          if (COLOR) {
+            C[s][0] = __fmaf_rn(T[s], __fmul_rn(c.x, alpha), C[s][0]);
+            C[s][1] = __fmaf_rn(T[s], __fmul_rn(c.y, alpha), C[s][1]);
+            C[s][2] = __fmaf_rn(T[s], __fmul_rn(c.z, alpha), C[s][2]);
+          }
+          if (FEAT) {
+            F[s][0] = __fmaf_rn(T[s], __fmul_rn(c.w, alpha), F[s][0]);
+            F[s][1] = __fmaf_rn(T[s], __fmul_rn(d.x, alpha), F[s][1]);
+            F[s][2] = __fmaf_rn(T[s], __fmul_rn(d.y, alpha), F[s][2]);
+          }
         }
-        if (FEAT) {
-          F[s][0] = __fmaf_rn(w, c.w, F[s][0]);
-          F[s][1] = __fmaf_rn(w, d.x, F[s][1]);
-          F[s][2] = __fmaf_rn(w, d.y, F[s][2]);
-        }
-#else
-        if (COLOR) {
-          C[s][0] = __fmaf_rn(T[s], __fmul_rn(c.x, alpha), C[s][0]);
-          C[s][1] = __fmaf_rn(T[s], __fmul_rn(c.y, alpha), C[s][1]);
-          C[s][2] = __fmaf_rn(T[s], __fmul_rn(c.z, alpha), C[s][2]);
-        }
-        if (FEAT) {
-          F[s][0] = __fmaf_rn(T[s], __fmul_rn(c.w, alpha), F[s][0]);
-          F[s][1] = __fmaf_rn(T[s], __fmul_rn(d.x, alpha), F[s][1]);
-          F[s][2] = __fmaf_rn(T[s], __fmul_rn(d.y, alpha), F[s][2]);
-        }
-#endif
         T[s] = test_T;
         last_contributor[s] = __float_as_uint(pos_bits) + 1u;  // 1-based position in the tile's list (forward.cu:372)
       }
@@ -193,6 +194,15 @@ refeature_kernel(int P, const int32_t* __restrict__ radii, const float* __restri
 
 }  // namespace
 
+// With the reference's rounding order the images are BIT-IDENTICAL to the reference extension's (measured at C2 and
+// C3, profiles/r2ae/image_diff_main.log: 0 of 6.2 M pixels differ).  LSR_FAST_BLEND=1 (or a build with
+// -DLSR_FWD_WEIGHT=1) trades that for speed: render_fwd 440 -> 408 us at C2, 601.7 -> 612.1 frames/s, C5 458 -> 470;
+// a quarter of the pixels then differ by one or two ulp (max 2.4e-7, the images' bar is 1e-5).
+static bool fast_blend() {
+  static const bool on = LSR_FWD_WEIGHT != 0 || (getenv("LSR_FAST_BLEND") != nullptr && getenv("LSR_FAST_BLEND")[0] == '1');
+  return on;
+}
+
 void launch_render_fwd(int W, int H, const uint2* ranges, const uint32_t* order, const uint32_t* list, const GeomRec* rec, const float* bg,
                        bool include_feature, float* final_T, uint32_t* n_contrib, float* out_color,
                        float* out_feature, cudaStream_t s) {
@@ -200,11 +210,11 @@ void launch_render_fwd(int W, int H, const uint2* ranges, const uint32_t* order,
   if (tiles_x == 0 || tiles_y == 0) return;
   const unsigned grid = (unsigned)tiles_x * (unsigned)tiles_y * QUADS;
   if (include_feature)
-    render_fwd_kernel<true, true><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, order, list, rec, bg, final_T, n_contrib,
-                                                      out_color, out_feature);
-  else
-    render_fwd_kernel<false, true><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, order, list, rec, bg, final_T, n_contrib,
-                                                       out_color, out_feature);
+#define LSR_FWD(F, C, WT) render_fwd_kernel<F, C, WT><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, order, list, rec, bg, \
+                                                                        final_T, n_contrib, out_color, out_feature)
+  if (include_feature) { if (fast_blend()) LSR_FWD(true, true, true); else LSR_FWD(true, true, false); }
+  else                 { if (fast_blend()) LSR_FWD(false, true, true); else LSR_FWD(false, true, false); }
+#undef LSR_FWD
   count_launch();
 }
 
@@ -218,8 +228,12 @@ void launch_refeature_render(int P, int W, int H, const int32_t* radii, const fl
   }
   if (tiles_x == 0 || tiles_y == 0) return;
   const unsigned grid = (unsigned)tiles_x * (unsigned)tiles_y * QUADS;
-  render_fwd_kernel<true, false><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, order, list, rec, nullptr, nullptr, nullptr,
-                                                     nullptr, out_feature);
+  if (fast_blend())
+    render_fwd_kernel<true, false, true><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, order, list, rec, nullptr, nullptr,
+                                                             nullptr, nullptr, out_feature);
+  else
+    render_fwd_kernel<true, false, false><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, order, list, rec, nullptr, nullptr,
+                                                              nullptr, nullptr, out_feature);
   count_launch();
 }
 
