@@ -82,6 +82,10 @@ def parse_args():
     ap.add_argument("--separate-levels", action="store_true",
                     help="config 5, ours: three independent forward calls (the reference's call sequence, "
                          "render.py:35-52) instead of forward_feature_levels (A/B)")
+    ap.add_argument("--fast-blend", action="store_true",
+                    help="ours: LSR_FAST_BLEND=1 — one blend weight per (pixel, Gaussian) pair in the forward instead "
+                         "of the reference's per-channel rounding order (images then differ from the reference's by "
+                         "<= 2.4e-7 instead of being bit-identical; A/B, not the default)")
     return ap.parse_args()
 
 
@@ -233,7 +237,11 @@ def main():
     _REAL_STDOUT = os.dup(1)
     os.dup2(2, 1)  # anything else written to stdout (NCCL's version banner, warnings) goes to stderr
     rank, world, dev = init_dist(args.gpus)
+    if args.fast_blend:
+        os.environ["LSR_FAST_BLEND"] = "1"  # read by liblsr.so at its first forward
     GR, GS, impl_name = load_impl(args.impl)
+    if args.fast_blend and args.impl == "ours":
+        impl_name += " [LSR_FAST_BLEND=1: images within 2.4e-7 of the reference's instead of bit-identical]"
     async_fwd = args.impl == "ours" and not args.sync_forward
     if async_fwd:
         # the package's public switch: no host read-back inside the forward (the first frame on a device still runs
