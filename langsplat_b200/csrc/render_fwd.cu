@@ -209,7 +209,6 @@ void launch_render_fwd(int W, int H, const uint2* ranges, const uint32_t* order,
   const int tiles_x = (W + TILE_X - 1) / TILE_X, tiles_y = (H + TILE_Y - 1) / TILE_Y;
   if (tiles_x == 0 || tiles_y == 0) return;
   const unsigned grid = (unsigned)tiles_x * (unsigned)tiles_y * QUADS;
-  if (include_feature)
 #define LSR_FWD(F, C, WT) render_fwd_kernel<F, C, WT><<<grid, 32, 0, s>>>(W, H, tiles_x, ranges, order, list, rec, bg, \
                                                                         final_T, n_contrib, out_color, out_feature)
   if (include_feature) { if (fast_blend()) LSR_FWD(true, true, true); else LSR_FWD(true, true, false); }
